@@ -1,0 +1,628 @@
+"""Functional CPU restatement of the ESPnet2 Conformer CTC/attention train step.
+
+TEST INFRASTRUCTURE (see oracle/__init__.py).  Everything here is a function of
+``(state_dict, inputs)``: parameters are looked up by the *reference's*
+state_dict key names so that the same weights drive the reference, this oracle
+and the CUDA path.  All arithmetic is plain torch on CPU in the dtype of the
+inputs (fp32 by default, fp64 for tight checks); gradients come from torch
+autograd over these functions, so only the forward is restated.
+
+Reference paths are relative to /root/reference.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Dict, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+SD = Dict[str, torch.Tensor]
+
+
+# --------------------------------------------------------------------------- #
+# configuration
+# --------------------------------------------------------------------------- #
+@dataclass
+class EncCfg:
+    """ConformerEncoder hyper-parameters (espnet2/asr/encoder/conformer_encoder.py:82-111)."""
+
+    idim: int = 80
+    d: int = 512
+    heads: int = 8
+    ffn: int = 2048
+    blocks: int = 12
+    kernel: int = 31
+    rel_pos_type: str = "latest"  # or "legacy"
+
+
+@dataclass
+class DecCfg:
+    """TransformerDecoder hyper-parameters (espnet2/asr/decoder/transformer_decoder.py:232-280)."""
+
+    vocab: int = 600
+    d: int = 512
+    heads: int = 8
+    ffn: int = 2048
+    blocks: int = 6
+
+
+@dataclass
+class ModelCfg:
+    enc: EncCfg = field(default_factory=EncCfg)
+    dec: DecCfg = field(default_factory=DecCfg)
+    vocab: int = 600
+    ctc_weight: float = 0.3
+    lsm_weight: float = 0.1
+    n_fft: int = 512
+    hop: int = 128
+    n_mels: int = 80
+    fs: int = 16000
+
+
+# --------------------------------------------------------------------------- #
+# small helpers
+# --------------------------------------------------------------------------- #
+def pad_mask(lens: torch.Tensor, maxlen: int) -> torch.Tensor:
+    """True where PADDED.  espnet/nets/pytorch_backend/nets_utils.py:64-176."""
+    ar = torch.arange(maxlen, device=lens.device)
+    return ar[None, :] >= lens[:, None]
+
+
+def layer_norm(x: torch.Tensor, sd: SD, p: str, eps: float = 1e-12) -> torch.Tensor:
+    """espnet/nets/pytorch_backend/transformer/layer_norm.py:12-38 (eps=1e-12 at :23)."""
+    mu = x.mean(-1, keepdim=True)
+    var = ((x - mu) ** 2).mean(-1, keepdim=True)
+    return (x - mu) / torch.sqrt(var + eps) * sd[p + ".weight"] + sd[p + ".bias"]
+
+
+def linear(x: torch.Tensor, sd: SD, p: str) -> torch.Tensor:
+    y = x @ sd[p + ".weight"].t()
+    if p + ".bias" in sd:
+        y = y + sd[p + ".bias"]
+    return y
+
+
+def swish(x: torch.Tensor) -> torch.Tensor:
+    """espnet/nets/pytorch_backend/conformer/swish.py:13-18."""
+    return x * torch.sigmoid(x)
+
+
+# --------------------------------------------------------------------------- #
+# rel_shift index maps (bit-exact integer work)
+# --------------------------------------------------------------------------- #
+def rel_shift_index_latest(T: int) -> np.ndarray:
+    """Column of the un-shifted (T, 2T-1) matrix that lands at out[i, j].
+
+    espnet/nets/pytorch_backend/transformer/attention.py:240-263:
+    out[i, j] = bd[i, T-1-i+j].
+    """
+    i = np.arange(T)[:, None]
+    j = np.arange(T)[None, :]
+    return (T - 1 - i + j).astype(np.int64)
+
+
+def rel_shift_index_legacy(T: int) -> Tuple[np.ndarray, np.ndarray]:
+    """Legacy rel_shift (attention.py:145-165) as (row, col) gather maps into the
+    un-shifted (T, T) matrix; col == -1 marks the literal zero at j == i+1.
+
+    j <= i   -> bd[i,   T-1-(i-j)]
+    j == i+1 -> 0
+    j >  i+1 -> bd[i+1, j-i-2]
+    """
+    i = np.arange(T)[:, None] + np.zeros((1, T), dtype=np.int64)
+    j = np.arange(T)[None, :] + np.zeros((T, 1), dtype=np.int64)
+    row = np.where(j <= i, i, i + 1)
+    col = np.where(j <= i, T - 1 - (i - j), j - i - 2)
+    col = np.where(j == i + 1, -1, col)
+    row = np.where(j == i + 1, 0, row)
+    return row.astype(np.int64), col.astype(np.int64)
+
+
+# --------------------------------------------------------------------------- #
+# frontend: STFT -> power -> log-mel   (fp32 island)
+# --------------------------------------------------------------------------- #
+def slaney_mel_matrix(fs: int = 16000, n_fft: int = 512, n_mels: int = 80,
+                      fmin: float = 0.0, fmax: Optional[float] = None) -> np.ndarray:
+    """(n_fft//2+1, n_mels) Slaney-scale, area-normalised mel filterbank.
+
+    The reference takes this constant from librosa.filters.mel(htk=False)
+    (espnet2/layers/log_mel.py:36-52); librosa (>=0.8, setup.py:18) is absent
+    here, so this restates its published algorithm.  "mel matrix parity vs
+    librosa: unpinned" (no reference test stores values); it is cross-checked
+    against torchaudio.functional.melscale_fbanks(norm='slaney',
+    mel_scale='slaney') in tests/test_oracle_golden.py.
+    """
+    fmax = fs / 2 if fmax is None else fmax
+    f_sp = 200.0 / 3
+    min_log_hz = 1000.0
+    min_log_mel = min_log_hz / f_sp
+    logstep = math.log(6.4) / 27.0
+
+    def hz2mel(f):
+        f = np.asarray(f, dtype=np.float64)
+        lin = f / f_sp
+        log = min_log_mel + np.log(np.maximum(f, 1e-30) / min_log_hz) / logstep
+        return np.where(f >= min_log_hz, log, lin)
+
+    def mel2hz(m):
+        m = np.asarray(m, dtype=np.float64)
+        lin = f_sp * m
+        log = min_log_hz * np.exp(logstep * (m - min_log_mel))
+        return np.where(m >= min_log_mel, log, lin)
+
+    fft_f = np.linspace(0, fs / 2, n_fft // 2 + 1)
+    mel_f = mel2hz(np.linspace(hz2mel(fmin), hz2mel(fmax), n_mels + 2))
+    fdiff = np.diff(mel_f)
+    ramps = mel_f[:, None] - fft_f[None, :]
+    w = np.zeros((n_mels, n_fft // 2 + 1))
+    for m in range(n_mels):
+        lower = -ramps[m] / fdiff[m]
+        upper = ramps[m + 2] / fdiff[m + 1]
+        w[m] = np.maximum(0, np.minimum(lower, upper))
+    enorm = 2.0 / (mel_f[2:n_mels + 2] - mel_f[:n_mels])
+    w *= enorm[:, None]
+    return w.T.astype(np.float32)
+
+
+def frontend_logmel(wav: torch.Tensor, lens: torch.Tensor, melmat: torch.Tensor,
+                    n_fft: int = 512, hop: int = 128) -> Tuple[torch.Tensor, torch.Tensor]:
+    """DefaultFrontend.forward (espnet2/asr/frontend/default.py:82-117).
+
+    Stft (espnet2/layers/stft.py:83-170): centre reflect-pad n_fft//2, periodic
+    Hann window, onesided rFFT, frames past olens zeroed; power re^2+im^2
+    (default.py:110); LogMel (espnet2/layers/log_mel.py:62-79): matmul, clamp
+    1e-10, natural log, padded frames -> 0.
+    """
+    B, N = wav.shape
+    pad = n_fft // 2
+    x = F.pad(wav[:, None, :], (pad, pad), mode="reflect")[:, 0]
+    T_in = N // hop + 1
+    idx = torch.arange(T_in)[:, None] * hop + torch.arange(n_fft)[None, :]
+    frames = x[:, idx]  # (B, T_in, n_fft)
+    n = torch.arange(n_fft, dtype=wav.dtype)
+    window = 0.5 - 0.5 * torch.cos(2 * math.pi * n / n_fft)  # torch.hann_window(periodic)
+    spec = torch.fft.rfft(frames * window, dim=-1)
+    olens = (lens + 2 * pad - n_fft) // hop + 1
+    padm = pad_mask(olens, T_in)[:, :, None]
+    re = spec.real.masked_fill(padm, 0.0)
+    im = spec.imag.masked_fill(padm, 0.0)
+    power = re ** 2 + im ** 2
+    mel = torch.clamp(power @ melmat.to(power.dtype), min=1e-10).log()
+    return mel.masked_fill(padm, 0.0), olens
+
+
+# --------------------------------------------------------------------------- #
+# SpecAug + UtteranceMVN
+# --------------------------------------------------------------------------- #
+def _cubic_w(t: torch.Tensor, A: float = -0.75):
+    """Cubic-convolution weights (Keys, A=-0.75) as used by torch's bicubic
+    F.interpolate, which espnet2/layers/time_warp.py:33-38 calls."""
+    def c1(x):  # |x| <= 1
+        return ((A + 2) * x - (A + 3)) * x * x + 1
+
+    def c2(x):  # 1 < |x| < 2
+        return ((A * x - 5 * A) * x + 8 * A) * x - 4 * A
+
+    return c2(t + 1), c1(t), c1(1 - t), c2(2 - t)
+
+
+def cubic_resize_time(x: torch.Tensor, out_len: int) -> torch.Tensor:
+    """(T, F) -> (out_len, F): the time axis of F.interpolate(mode='bicubic',
+    align_corners=False) when the freq size is unchanged (then the freq axis is
+    the identity: source coordinate j+0.5-0.5=j, weights (0,1,0,0))."""
+    in_len = x.shape[0]
+    scale = in_len / out_len
+    dst = torch.arange(out_len, dtype=x.dtype)
+    src = (dst + 0.5) * scale - 0.5
+    i0 = torch.floor(src)
+    t = (src - i0)[:, None]
+    i0 = i0.long()
+    w = _cubic_w(t)
+    out = 0
+    for k in range(4):
+        idx = torch.clamp(i0 - 1 + k, 0, in_len - 1)
+        out = out + w[k] * x[idx]
+    return out
+
+
+def time_warp_one(x: torch.Tensor, center: int, warped: int) -> torch.Tensor:
+    """espnet2/layers/time_warp.py:9-46 for one un-padded utterance (T, F) with the
+    two RNG draws given (center ~ randint(W, T-W), warped ~ randint(c-W, c+W)+1)."""
+    left = cubic_resize_time(x[:center], warped)
+    right = cubic_resize_time(x[center:], x.shape[0] - warped)
+    return torch.cat([left, right], 0)
+
+
+def spec_augment(feats: torch.Tensor, lens: torch.Tensor, draws: dict, window: int = 5) -> torch.Tensor:
+    """SpecAug.forward (espnet2/asr/specaug/specaug.py:89-96) with the RNG draws
+    supplied: draws = {center (B,), warped (B,), f_len (B,nf), f_pos (B,nf),
+    t_len (B,nt), t_pos (B,nt)}; center < 0 means "no warp for this utterance"
+    (time_warp.py:24-25: t - W <= W).
+
+    TimeWarp (time_warp.py:65-88) runs per utterance on the UNPADDED slice and
+    re-pads with 0; mask_along_axis (mask_along_axis.py:8-68) zeroes
+    [pos, pos+len) along freq then along the padded time axis.
+    """
+    B, T, Fq = feats.shape
+    out = torch.zeros_like(feats)
+    for b in range(B):
+        L = int(lens[b])
+        xb = feats[b, :L]
+        c, w = int(draws["center"][b]), int(draws["warped"][b])
+        if c >= 0:
+            xb = time_warp_one(xb, c, w)
+        out[b, :L] = xb
+    ar_f = torch.arange(Fq)[None, None, :]
+    fm = ((draws["f_pos"][:, :, None] <= ar_f) & (ar_f < (draws["f_pos"] + draws["f_len"])[:, :, None])).any(1)
+    out = out.masked_fill(fm[:, None, :], 0.0)
+    ar_t = torch.arange(T)[None, None, :]
+    tm = ((draws["t_pos"][:, :, None] <= ar_t) & (ar_t < (draws["t_pos"] + draws["t_len"])[:, :, None])).any(1)
+    out = out.masked_fill(tm[:, :, None], 0.0)
+    return out
+
+
+def utterance_mvn(x: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
+    """espnet2/layers/utterance_mvn.py:45-88 (norm_means=True, norm_vars=False):
+    zero the padding, mean over valid frames, subtract from ALL frames."""
+    x = x.masked_fill(pad_mask(lens, x.shape[1])[:, :, None], 0.0)
+    mean = x.sum(1, keepdim=True) / lens.to(x.dtype)[:, None, None]
+    return x - mean
+
+
+# --------------------------------------------------------------------------- #
+# encoder
+# --------------------------------------------------------------------------- #
+def rel_pos_table(T: int, d: int, dtype=torch.float32) -> torch.Tensor:
+    """RelPositionalEncoding (espnet/nets/pytorch_backend/transformer/embedding.py:196-244):
+    rows are relative positions +(T-1) ... 0 ... -(T-1); sin on even, cos on odd."""
+    pos = torch.arange(T - 1, -T, -1, dtype=torch.float32)[:, None]
+    div = torch.exp(torch.arange(0, d, 2, dtype=torch.float32) * -(math.log(10000.0) / d))
+    pe = torch.zeros(2 * T - 1, d)
+    pe[:, 0::2] = torch.sin(pos * div)
+    pe[:, 1::2] = torch.cos(pos * div)
+    return pe.to(dtype)
+
+
+def legacy_pos_table(T: int, d: int, maxlen: int = 5000, dtype=torch.float32) -> torch.Tensor:
+    """LegacyRelPositionalEncoding (embedding.py:137-170, reverse=True at :153):
+    position[r] = maxlen-1-r, rows 0..T-1 taken."""
+    pos = torch.arange(maxlen - 1, maxlen - 1 - T, -1, dtype=torch.float32)[:, None]
+    div = torch.exp(torch.arange(0, d, 2, dtype=torch.float32) * -(math.log(10000.0) / d))
+    pe = torch.zeros(T, d)
+    pe[:, 0::2] = torch.sin(pos * div)
+    pe[:, 1::2] = torch.cos(pos * div)
+    return pe.to(dtype)
+
+
+def abs_pos_table(L: int, d: int, dtype=torch.float32) -> torch.Tensor:
+    """PositionalEncoding (embedding.py:59-80)."""
+    pos = torch.arange(0, L, dtype=torch.float32)[:, None]
+    div = torch.exp(torch.arange(0, d, 2, dtype=torch.float32) * -(math.log(10000.0) / d))
+    pe = torch.zeros(L, d)
+    pe[:, 0::2] = torch.sin(pos * div)
+    pe[:, 1::2] = torch.cos(pos * div)
+    return pe.to(dtype)
+
+
+def subsampled_len(T_in: int) -> int:
+    """espnet/nets/pytorch_backend/transformer/subsampling.py:57-59,87."""
+    return ((T_in - 1) // 2 - 1) // 2
+
+
+def subsampled_lens(ilens: torch.Tensor, T_in: int) -> torch.Tensor:
+    """olens = masks[:, :, :-2:2][:, :, :-2:2].sum() (subsampling.py:87,
+    conformer_encoder.py:365): kept mask positions are 0,4,8,... so
+    olens = min(T, ceil(ilens/4))."""
+    T = subsampled_len(T_in)
+    return torch.clamp((ilens + 3) // 4, max=T)
+
+
+def conv2d_subsample(x: torch.Tensor, sd: SD, p: str) -> torch.Tensor:
+    """Conv2dSubsampling.forward (subsampling.py:67-87) without the pos-enc:
+    conv(1->d,3,s2)+ReLU, conv(d->d,3,s2)+ReLU, (b,c,t,f)->(b,t,c*f), Linear."""
+    h = F.relu(F.conv2d(x[:, None], sd[p + ".conv.0.weight"], sd[p + ".conv.0.bias"], stride=2))
+    h = F.relu(F.conv2d(h, sd[p + ".conv.2.weight"], sd[p + ".conv.2.bias"], stride=2))
+    b, c, t, f = h.shape
+    h = h.transpose(1, 2).reshape(b, t, c * f)
+    return linear(h, sd, p + ".out.0")
+
+
+def mha_core(q, k, v, key_valid, extra_scores=None, causal=False):
+    """forward_attention (attention.py:64-96): scores already scaled; masked with
+    finfo.min, softmax, masked entries re-zeroed, @ v, heads merged."""
+    B, H, Tq, dk = q.shape
+    Tk = k.shape[2]
+    scores = q @ k.transpose(-2, -1)
+    if extra_scores is not None:
+        scores = scores + extra_scores
+    scores = scores / math.sqrt(dk)
+    valid = key_valid[:, None, None, :]  # (B,1,1,Tk)
+    if causal:
+        tri = torch.tril(torch.ones(Tq, Tk, dtype=torch.bool))
+        valid = valid & tri[None, None]
+    scores = scores.masked_fill(~valid, torch.finfo(scores.dtype).min)
+    attn = torch.softmax(scores, dim=-1).masked_fill(~valid, 0.0)
+    ctx = attn @ v
+    return ctx.transpose(1, 2).reshape(B, Tq, H * dk)
+
+
+def rel_pos_mhsa(x, pos_emb, key_valid, sd: SD, p: str, H: int, mode: str = "latest"):
+    """RelPositionMultiHeadedAttention.forward (attention.py:265-308) /
+    LegacyRelPositionMultiHeadedAttention.forward (attention.py:167-209).
+    rel_shift is applied through the integer index maps above instead of the
+    reference's pad/view trick."""
+    B, T, d = x.shape
+    dk = d // H
+    q = linear(x, sd, p + ".linear_q").view(B, T, H, dk)
+    k = linear(x, sd, p + ".linear_k").view(B, T, H, dk).transpose(1, 2)
+    v = linear(x, sd, p + ".linear_v").view(B, T, H, dk).transpose(1, 2)
+    pp = (pos_emb @ sd[p + ".linear_pos.weight"].t()).view(-1, H, dk).transpose(0, 1)  # (H, P, dk)
+    qu = (q + sd[p + ".pos_bias_u"]).transpose(1, 2)
+    qv = (q + sd[p + ".pos_bias_v"]).transpose(1, 2)
+    bd = qv @ pp.transpose(-2, -1)[None]  # (B,H,T,P)
+    if mode == "latest":
+        col = torch.from_numpy(rel_shift_index_latest(T))
+        bd = torch.gather(bd, 3, col[None, None].expand(B, H, T, T))
+    else:
+        row, col = rel_shift_index_legacy(T)
+        zero = torch.from_numpy(col < 0)
+        row_t = torch.from_numpy(row)
+        col_t = torch.from_numpy(np.maximum(col, 0))
+        bd = bd[:, :, row_t, col_t].masked_fill(zero[None, None], 0.0)
+    ctx = mha_core(qu, k, v, key_valid, extra_scores=bd)
+    return linear(ctx, sd, p + ".linear_out")
+
+
+def mha(xq, xkv, key_valid, sd: SD, p: str, H: int, causal: bool = False):
+    """MultiHeadedAttention.forward (attention.py:98-114)."""
+    B, Tq, d = xq.shape
+    Tk = xkv.shape[1]
+    dk = d // H
+    q = linear(xq, sd, p + ".linear_q").view(B, Tq, H, dk).transpose(1, 2)
+    k = linear(xkv, sd, p + ".linear_k").view(B, Tk, H, dk).transpose(1, 2)
+    v = linear(xkv, sd, p + ".linear_v").view(B, Tk, H, dk).transpose(1, 2)
+    return linear(mha_core(q, k, v, key_valid, causal=causal), sd, p + ".linear_out")
+
+
+def ffn(x, sd: SD, p: str, act):
+    """PositionwiseFeedForward.forward (positionwise_feed_forward.py:30-32)."""
+    return linear(act(linear(x, sd, p + ".w_1")), sd, p + ".w_2")
+
+
+def conv_module(x, sd: SD, p: str, kernel: int, training: bool = True, bn_stats_out: Optional[dict] = None):
+    """ConvolutionModule.forward (espnet/nets/pytorch_backend/conformer/convolution.py:56-79):
+    pw1 -> GLU(channel halves) -> depthwise(K, same pad) -> BatchNorm1d (training:
+    batch statistics over ALL B*T positions incl. padding, biased var, eps 1e-5)
+    -> Swish -> pw2.  Works channels-last; no transposes needed."""
+    B, T, d = x.shape
+    h = x @ sd[p + ".pointwise_conv1.weight"][:, :, 0].t() + sd[p + ".pointwise_conv1.bias"]
+    h = h[..., :d] * torch.sigmoid(h[..., d:])
+    hp = F.pad(h, (0, 0, (kernel - 1) // 2, (kernel - 1) // 2))
+    w = sd[p + ".depthwise_conv.weight"][:, 0, :]  # (d, K)
+    y = sd[p + ".depthwise_conv.bias"].expand(B, T, d).clone()
+    for k in range(kernel):
+        y = y + hp[:, k:k + T, :] * w[:, k]
+    if training:
+        mean = y.mean((0, 1))
+        var = ((y - mean) ** 2).mean((0, 1))
+        if bn_stats_out is not None:
+            n = B * T
+            bn_stats_out[p] = (mean.detach(), (var * n / max(n - 1, 1)).detach())
+    else:
+        mean, var = sd[p + ".norm.running_mean"], sd[p + ".norm.running_var"]
+    y = (y - mean) / torch.sqrt(var + 1e-5) * sd[p + ".norm.weight"] + sd[p + ".norm.bias"]
+    y = swish(y)
+    return y @ sd[p + ".pointwise_conv2.weight"][:, :, 0].t() + sd[p + ".pointwise_conv2.bias"]
+
+
+def conformer_block(x, pos_emb, key_valid, sd: SD, p: str, cfg: EncCfg, bn_stats_out=None):
+    """EncoderLayer.forward (espnet/nets/pytorch_backend/conformer/encoder_layer.py:76-157),
+    pre-LN macaron, dropout = 0."""
+    x = x + 0.5 * ffn(layer_norm(x, sd, p + ".norm_ff_macaron"), sd, p + ".feed_forward_macaron", swish)
+    x = x + rel_pos_mhsa(layer_norm(x, sd, p + ".norm_mha"), pos_emb, key_valid, sd, p + ".self_attn",
+                         cfg.heads, cfg.rel_pos_type)
+    x = x + conv_module(layer_norm(x, sd, p + ".norm_conv"), sd, p + ".conv_module", cfg.kernel,
+                        bn_stats_out=bn_stats_out)
+    x = x + 0.5 * ffn(layer_norm(x, sd, p + ".norm_ff"), sd, p + ".feed_forward", swish)
+    return layer_norm(x, sd, p + ".norm_final")
+
+
+def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_stats_out=None,
+                      return_blocks: bool = False):
+    """ConformerEncoder.forward (espnet2/asr/encoder/conformer_encoder.py:292-368)."""
+    T_in = feats.shape[1]
+    x = conv2d_subsample(feats, sd, p + ".embed") * math.sqrt(cfg.d)  # embedding.py:239
+    T = x.shape[1]
+    olens = subsampled_lens(ilens, T_in)
+    key_valid = ~pad_mask(olens, T)
+    if cfg.rel_pos_type == "latest":
+        pos_emb = rel_pos_table(T, cfg.d, x.dtype)
+    else:
+        pos_emb = legacy_pos_table(T, cfg.d, dtype=x.dtype)
+    outs = []
+    for n in range(cfg.blocks):
+        x = conformer_block(x, pos_emb, key_valid, sd, f"{p}.encoders.{n}", cfg, bn_stats_out)
+        if return_blocks:
+            outs.append(x)
+    x = layer_norm(x, sd, p + ".after_norm")
+    if return_blocks:
+        return x, olens, outs
+    return x, olens
+
+
+# --------------------------------------------------------------------------- #
+# CTC
+# --------------------------------------------------------------------------- #
+def ctc_extended_labels(labels: Sequence[int], blank: int = 0) -> Tuple[np.ndarray, np.ndarray]:
+    """Blank-extended label lattice (espnet/nets/pytorch_backend/gtn_ctc.py:26-36):
+    S = 2L+1 states, even = blank, odd = label[(s-1)//2]; skip arc s-2 -> s allowed
+    iff s odd, s > 1 and label != previous label."""
+    L = len(labels)
+    ext = np.full(2 * L + 1, blank, dtype=np.int64)
+    ext[1::2] = np.asarray(labels, dtype=np.int64)
+    skip = np.zeros(2 * L + 1, dtype=np.uint8)
+    for s in range(3, 2 * L + 1, 2):
+        skip[s] = ext[s] != ext[s - 2]
+    return ext, skip
+
+
+def ctc_loss_numpy(logits: np.ndarray, hlens, labels_list, blank: int = 0):
+    """fp64 log-space alpha/beta CTC over raw logits (T,B,V) with fused log_softmax.
+
+    Restates what espnet2/asr/ctc.py:52-63,82-95 asks of torch.nn.CTCLoss(
+    reduction='none', zero_infinity=True): per-utterance nll, and the gradient of
+    sum_b nll_b wrt the LOGITS, = softmax - occupancy for t < T_b, 0 beyond and 0 for
+    infeasible (inf) utterances.  Small cases only (python loops)."""
+    T, B, V = logits.shape
+    x = logits.astype(np.float64)
+    m = x.max(-1, keepdims=True)
+    lp = x - m - np.log(np.exp(x - m).sum(-1, keepdims=True))
+    nll = np.zeros(B)
+    grad = np.zeros_like(x)
+    for b in range(B):
+        Tb = int(hlens[b])
+        ext, skip = ctc_extended_labels(labels_list[b], blank)
+        S = len(ext)
+        NEG = -np.inf
+        a = np.full((Tb, S), NEG)
+        a[0, 0] = lp[0, b, ext[0]]
+        if S > 1:
+            a[0, 1] = lp[0, b, ext[1]]
+        for t in range(1, Tb):
+            for s in range(S):
+                c = [a[t - 1, s]]
+                if s >= 1:
+                    c.append(a[t - 1, s - 1])
+                if skip[s]:
+                    c.append(a[t - 1, s - 2])
+                mx = max(c)
+                if mx > NEG:
+                    a[t, s] = mx + math.log(sum(math.exp(v - mx) for v in c)) + lp[t, b, ext[s]]
+        fin = [a[Tb - 1, S - 1]] + ([a[Tb - 1, S - 2]] if S > 1 else [])
+        mx = max(fin)
+        if mx == NEG:
+            nll[b] = 0.0  # zero_infinity
+            continue
+        ll = mx + math.log(sum(math.exp(v - mx) for v in fin))
+        nll[b] = -ll
+        bt = np.full((Tb, S), NEG)
+        bt[Tb - 1, S - 1] = lp[Tb - 1, b, ext[S - 1]]
+        if S > 1:
+            bt[Tb - 1, S - 2] = lp[Tb - 1, b, ext[S - 2]]
+        for t in range(Tb - 2, -1, -1):
+            for s in range(S):
+                c = [bt[t + 1, s]]
+                if s + 1 < S:
+                    c.append(bt[t + 1, s + 1])
+                if s + 2 < S and skip[s + 2]:
+                    c.append(bt[t + 1, s + 2])
+                mx = max(c)
+                if mx > NEG:
+                    bt[t, s] = mx + math.log(sum(math.exp(v - mx) for v in c)) + lp[t, b, ext[s]]
+        for t in range(Tb):
+            occ = np.zeros(V)
+            for s in range(S):
+                ab = a[t, s] + bt[t, s]
+                if ab > NEG:
+                    occ[ext[s]] += math.exp(ab - ll - lp[t, b, ext[s]])
+            grad[t, b] = np.exp(lp[t, b]) - occ
+    return nll, grad
+
+
+def ctc_branch(enc_out, olens, text, text_lens, sd: SD, p: str = "ctc"):
+    """CTC.forward (espnet2/asr/ctc.py:72-97): ctc_lo, (T,B,V), log_softmax,
+    CTCLoss(none, zero_infinity), sum / B.  torch's own ctc_loss IS the
+    reference's arithmetic here (ctc.py:39-41)."""
+    logits = linear(enc_out, sd, p + ".ctc_lo").transpose(0, 1)
+    lp = logits.log_softmax(2)
+    tgt = torch.cat([text[i, :l] for i, l in enumerate(text_lens.tolist())])
+    loss = F.ctc_loss(lp, tgt, olens, text_lens, blank=0, reduction="none", zero_infinity=True)
+    return loss.sum() / enc_out.shape[0]
+
+
+# --------------------------------------------------------------------------- #
+# decoder + label smoothing
+# --------------------------------------------------------------------------- #
+def add_sos_eos(text, text_lens, sos: int, eos: int, ignore: int = -1):
+    """espnet/nets/pytorch_backend/transformer/add_sos_eos.py:12-31."""
+    B = text.shape[0]
+    L = int(text_lens.max()) + 1
+    ys_in = torch.full((B, L), eos, dtype=torch.long)
+    ys_out = torch.full((B, L), ignore, dtype=torch.long)
+    for b in range(B):
+        n = int(text_lens[b])
+        ys_in[b, 0] = sos
+        ys_in[b, 1:n + 1] = text[b, :n]
+        ys_out[b, :n] = text[b, :n]
+        ys_out[b, n] = eos
+    return ys_in, ys_out
+
+
+def transformer_decoder(memory, mem_lens, ys_in, ys_in_lens, sd: SD, cfg: DecCfg, p: str = "decoder"):
+    """TransformerDecoder.forward (espnet2/asr/decoder/transformer_decoder.py:92-145) with
+    DecoderLayer.forward (espnet/nets/pytorch_backend/transformer/decoder_layer.py:63-134)."""
+    B, L = ys_in.shape
+    x = sd[p + ".embed.0.weight"][ys_in] * math.sqrt(cfg.d) + abs_pos_table(L, cfg.d, memory.dtype)
+    tgt_valid = ~pad_mask(ys_in_lens, L)
+    mem_valid = ~pad_mask(mem_lens, memory.shape[1])
+    for n in range(cfg.blocks):
+        q = f"{p}.decoders.{n}"
+        h = layer_norm(x, sd, q + ".norm1")
+        x = x + mha(h, h, tgt_valid, sd, q + ".self_attn", cfg.heads, causal=True)
+        x = x + mha(layer_norm(x, sd, q + ".norm2"), memory, mem_valid, sd, q + ".src_attn", cfg.heads)
+        x = x + ffn(layer_norm(x, sd, q + ".norm3"), sd, q + ".feed_forward", F.relu)
+    x = layer_norm(x, sd, p + ".after_norm")
+    return linear(x, sd, p + ".output_layer")
+
+
+def label_smoothing_loss(logits, target, smoothing: float, ignore: int = -1):
+    """LabelSmoothingLoss.forward (label_smoothing_loss.py:41-63), normalize_length=False:
+    KL(true_dist || softmax) summed over non-ignored rows, / batch size."""
+    B, L, V = logits.shape
+    x = logits.reshape(-1, V)
+    t = target.reshape(-1)
+    ign = t == ignore
+    tt = t.masked_fill(ign, 0)
+    true = torch.full_like(x, smoothing / (V - 1))
+    true.scatter_(1, tt[:, None], 1.0 - smoothing)
+    kl = true * (torch.log(true) - torch.log_softmax(x, 1))
+    return kl.masked_fill(ign[:, None], 0.0).sum() / B
+
+
+def th_accuracy(logits, target, ignore: int = -1) -> float:
+    """espnet/nets/pytorch_backend/nets_utils.py:299-320."""
+    pred = logits.argmax(-1)
+    m = target != ignore
+    return float(((pred == target) & m).sum()) / float(m.sum())
+
+
+# --------------------------------------------------------------------------- #
+# whole step
+# --------------------------------------------------------------------------- #
+def asr_forward_from_feats(feats, feat_lens, text, text_lens, sd: SD, cfg: ModelCfg):
+    """ESPnetASRModel.forward from the encoder input on
+    (espnet2/asr/espnet_model.py:202-297): returns (loss, stats)."""
+    enc, olens = conformer_encoder(feats, feat_lens, sd, cfg.enc)
+    loss_ctc = ctc_branch(enc, olens, text, text_lens, sd)
+    sos = eos = cfg.vocab - 1  # espnet_model.py:75-82
+    ys_in, ys_out = add_sos_eos(text, text_lens, sos, eos)
+    dec = transformer_decoder(enc, olens, ys_in, text_lens + 1, sd, cfg.dec)
+    loss_att = label_smoothing_loss(dec, ys_out, cfg.lsm_weight)
+    acc = th_accuracy(dec, ys_out)
+    loss = cfg.ctc_weight * loss_ctc + (1 - cfg.ctc_weight) * loss_att  # espnet_model.py:284
+    return loss, {"loss_ctc": loss_ctc.detach(), "loss_att": loss_att.detach(), "acc": acc,
+                  "loss": loss.detach()}
+
+
+def asr_forward(speech, speech_lens, text, text_lens, sd: SD, cfg: ModelCfg, melmat, draws=None):
+    """ESPnetASRModel.forward from the raw waveform (espnet_model.py:169-297,
+    encode 319-377): frontend -> SpecAug (draws given; None = eval/no-aug) ->
+    UtteranceMVN -> encoder -> CTC + attention losses."""
+    feats, flens = frontend_logmel(speech, speech_lens, melmat, cfg.n_fft, cfg.hop)
+    if draws is not None:
+        feats = spec_augment(feats, flens, draws)
+    feats = utterance_mvn(feats, flens)
+    return asr_forward_from_feats(feats, flens, text, text_lens, sd, cfg)

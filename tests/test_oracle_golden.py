@@ -1,0 +1,135 @@
+"""Pin the CPU oracle (oracle/model.py) against outputs of the UNMODIFIED reference
+frozen in tests/golden/*.npz by oracle/make_golden.py.  CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model as om
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    z = np.load(os.path.join(GOLDEN, name))
+    return {k: z[k] for k in z.files}
+
+
+def tiny_cfg(rel):
+    return om.ModelCfg(enc=om.EncCfg(80, 16, 2, 32, 2, 7, rel), dec=om.DecCfg(20, 16, 2, 32, 2), vocab=20)
+
+
+@pytest.mark.parametrize("T", [1, 2, 3, 7, 16, 33, 64])
+def test_rel_shift_latest_bit_exact(T):
+    g = load("rel_shift.npz")
+    code = g[f"latest_{T}"]  # entries = row*10000 + col + 1 of the un-shifted matrix
+    col = om.rel_shift_index_latest(T)
+    row = np.arange(T)[:, None] + np.zeros((1, T), dtype=np.int64)
+    assert np.array_equal(code, row * 10000 + col + 1)
+
+
+@pytest.mark.parametrize("T", [1, 2, 3, 7, 16, 33, 64])
+def test_rel_shift_legacy_bit_exact(T):
+    g = load("rel_shift.npz")
+    code = g[f"legacy_{T}"]
+    row, col = om.rel_shift_index_legacy(T)
+    want = np.where(col < 0, 0, row * 10000 + col + 1)
+    assert np.array_equal(code, want)
+
+
+@pytest.mark.parametrize("case", ["loss_a", "loss_b", "ctc_fixture", "infeasible"])
+def test_ctc_numpy_vs_torch_fp64(case):
+    g = load("ctc.npz")
+    ys, yl = g[case + "/ys"], g[case + "/ylens"]
+    off = np.concatenate([[0], np.cumsum(yl)])
+    labels = [ys[off[i]:off[i + 1]].tolist() for i in range(len(yl))]
+    nll, grad = om.ctc_loss_numpy(g[case + "/logits"], g[case + "/hlens"], labels)
+    np.testing.assert_allclose(nll, g[case + "/nll"], rtol=1e-10, atol=1e-10)
+    np.testing.assert_allclose(grad, g[case + "/grad"], rtol=1e-9, atol=1e-10)
+
+
+def test_ctc_lattice_bit_exact():
+    ext, skip = om.ctc_extended_labels([3, 3, 5, 1, 1, 2])
+    assert ext.tolist() == [0, 3, 0, 3, 0, 5, 0, 1, 0, 1, 0, 2, 0]
+    assert skip.tolist() == [0, 0, 0, 0, 0, 1, 0, 1, 0, 0, 0, 1, 0]
+
+
+def test_ctc_module():
+    g = load("ctc.npz")
+    h = torch.tensor(g["module/h"], requires_grad=True)
+    sd = {"ctc.ctc_lo.weight": torch.tensor(g["module/w"], requires_grad=True), "ctc.ctc_lo.bias": torch.tensor(g["module/b"])}
+    loss = om.ctc_branch(h, torch.tensor([10, 8]), torch.tensor(g["module/y"]), torch.tensor([5, 2]), sd)
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), g["module/loss"], rtol=1e-6)
+    np.testing.assert_allclose(h.grad.numpy(), g["module/grad_h"], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(sd["ctc.ctc_lo.weight"].grad.numpy(), g["module/grad_w"], rtol=1e-5, atol=1e-7)
+
+
+def test_frontend_and_mvn():
+    g = load("frontend.npz")
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    np.testing.assert_allclose(mel.numpy(), g["melmat"], rtol=0, atol=0)
+    feats, flens = om.frontend_logmel(torch.tensor(g["wav"]), torch.tensor(g["lens"]), mel)
+    assert flens.tolist() == g["feat_lens"].tolist()
+    np.testing.assert_allclose(feats.numpy(), g["feats"], rtol=2e-4, atol=2e-4)
+    mvn = om.utterance_mvn(torch.tensor(g["feats"]), flens)
+    np.testing.assert_allclose(mvn.numpy(), g["mvn"], rtol=1e-5, atol=1e-5)
+    # STFT shape/length fixture of test/espnet2/layers/test_stft.py:10-16
+    assert g["stft_shape"].tolist() == [2, 16, 3, 2] and g["stft_lens"].tolist() == [16, 8]
+    f2, l2 = om.frontend_logmel(torch.randn(2, 30), torch.tensor([30, 15]),
+                                torch.ones(3, 1), n_fft=4, hop=2)
+    assert f2.shape[:2] == (2, 16) and l2.tolist() == [16, 8]
+
+
+def test_mel_matrix_vs_torchaudio():
+    ta = pytest.importorskip("torchaudio")
+    ref = ta.functional.melscale_fbanks(257, 0.0, 8000.0, 80, 16000, norm="slaney", mel_scale="slaney")
+    np.testing.assert_allclose(om.slaney_mel_matrix(), ref.numpy(), rtol=1e-5, atol=1e-7)
+
+
+def test_specaug_replay():
+    g = load("specaug.npz")
+    draws = {k: torch.tensor(g[k]) for k in ("center", "warped", "f_len", "f_pos", "t_len", "t_pos")}
+    y = om.spec_augment(torch.tensor(g["x"]), torch.tensor(g["lens"]), draws)
+    np.testing.assert_allclose(y.numpy(), g["y"], rtol=1e-5, atol=1e-5)
+
+
+def test_encoder_and_bn_running_stats():
+    g = load("encoder_bn.npz")
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/")}
+    stats = {}
+    enc, olens = om.conformer_encoder(torch.tensor(g["feats"]), torch.tensor(g["feat_lens"]), sd,
+                                      tiny_cfg("latest").enc, bn_stats_out=stats)
+    assert olens.tolist() == g["enc_lens"].tolist()
+    np.testing.assert_allclose(enc.numpy(), g["enc_out"], rtol=1e-4, atol=1e-5)
+    for p, (mean, var_unb) in stats.items():
+        rm = 0.9 * sd[p + ".norm.running_mean"] + 0.1 * mean
+        rv = 0.9 * sd[p + ".norm.running_var"] + 0.1 * var_unb
+        np.testing.assert_allclose(rm.numpy(), g["after/" + p + ".norm.running_mean"], rtol=1e-4, atol=1e-6)
+        np.testing.assert_allclose(rv.numpy(), g["after/" + p + ".norm.running_var"], rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("rel", ["latest", "legacy"])
+def test_whole_step_loss_and_grads(rel):
+    g = load(f"e2e_{rel}.npz")
+    sd = {k[3:]: torch.tensor(v).requires_grad_(v.dtype == np.float32) for k, v in g.items() if k.startswith("sd/")}
+    cfg = tiny_cfg(rel)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    loss, stats = om.asr_forward(torch.tensor(g["wav"]), torch.tensor(g["lens"]), torch.tensor(g["text"]),
+                                 torch.tensor(g["text_lens"]), sd, cfg, mel)
+    np.testing.assert_allclose(loss.item(), g["loss"].item(), rtol=2e-5)
+    np.testing.assert_allclose(stats["loss_ctc"].item(), g["loss_ctc"].item(), rtol=2e-5)
+    np.testing.assert_allclose(stats["loss_att"].item(), g["loss_att"].item(), rtol=2e-5)
+    assert abs(stats["acc"] - float(g["acc"].item())) < 1e-6
+    loss.backward()
+    worst = 0.0
+    for k, v in g.items():
+        if not k.startswith("grad/"):
+            continue
+        got = sd[k[5:]].grad
+        got = torch.zeros_like(sd[k[5:]]) if got is None else got
+        # linear_k.bias / depthwise bias grads are mathematically 0 (softmax shift, BN): abs floor
+        scale = max(np.abs(v).max(), 1e-3)
+        worst = max(worst, float(np.abs(got.numpy() - v).max() / scale))
+    assert worst < 2e-3, worst
