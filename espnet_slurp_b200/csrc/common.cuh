@@ -1,0 +1,148 @@
+// Common definitions for libb200slu (sm_100a only).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/b200slu.h"
+
+typedef __nv_bfloat16 bf16;
+
+// ---------------------------------------------------------------------------
+// error plumbing: never throw / abort across the C boundary
+// ---------------------------------------------------------------------------
+void b200slu_set_error(const char* fmt, ...);
+
+#define B2_CHECK_ARG(cond, ...)                       \
+  do {                                                \
+    if (!(cond)) {                                    \
+      b200slu_set_error(__VA_ARGS__);                 \
+      return B200SLU_EINVAL;                          \
+    }                                                 \
+  } while (0)
+
+#define B2_CUDA(call)                                                                  \
+  do {                                                                                 \
+    cudaError_t e_ = (call);                                                           \
+    if (e_ != cudaSuccess) {                                                           \
+      b200slu_set_error("%s:%d CUDA error: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      return B200SLU_ECUDA;                                                            \
+    }                                                                                  \
+  } while (0)
+
+#define B2_LAUNCH_CHECK()                                                              \
+  do {                                                                                 \
+    cudaError_t e_ = cudaGetLastError();                                               \
+    if (e_ != cudaSuccess) {                                                           \
+      b200slu_set_error("%s:%d launch error: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      return B200SLU_ECUDA;                                                            \
+    }                                                                                  \
+  } while (0)
+
+#define B2_TRY(expr)            \
+  do {                          \
+    int rc_ = (expr);           \
+    if (rc_ != 0) return rc_;   \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// per-family launch accounting + optional CUDA-event timing (bench.py roofline)
+// ---------------------------------------------------------------------------
+enum B2Family {
+  FAM_GEMM = 0,
+  FAM_ATTN,
+  FAM_LN,
+  FAM_CONVMOD,
+  FAM_SUBSAMPLE,
+  FAM_CTC,
+  FAM_FRONTEND,
+  FAM_LOSS,
+  FAM_ELEMWISE,
+  FAM_COUNT
+};
+
+struct B2ProfScope {
+  int fam;
+  cudaStream_t st;
+  cudaEvent_t e0, e1;
+  bool timed;
+  B2ProfScope(int fam, cudaStream_t st, double flops, double bytes);
+  ~B2ProfScope();
+};
+#define B2_SCOPE(fam, st, flops, bytes) B2ProfScope prof_scope_((fam), (st), (double)(flops), (double)(bytes))
+
+int b2_num_sms();
+
+// ---------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+__device__ __forceinline__ float swishf_(float x) { return x * sigmoidf_(x); }
+// d/dx [x*sigmoid(x)] = s + x*s*(1-s)
+__device__ __forceinline__ float swish_gradf_(float x) {
+  float s = sigmoidf_(x);
+  return s * (1.f + x * (1.f - s));
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
+  __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
+  return __bfloat1622float2(v);
+}
+
+// ---------------------------------------------------------------------------
+// counter-based dropout: Philox4x32-10 keyed by (seed, site); one call yields
+// 128 random bits = 8 x 16-bit lanes -> keep decisions for 8 consecutive
+// elements (element index = 8*ctr + lane).  Recomputed, never stored.
+// ---------------------------------------------------------------------------
+struct B2Dropout {
+  unsigned long long seed;  // per training step
+  unsigned int site;        // unique per dropout site
+  float p;                  // drop probability; 0 => disabled
+};
+
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+
+// keep-mask (bit i set = keep) for elements [8*group, 8*group+8)
+__device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned long long group) {
+  uint2 key = make_uint2((uint32_t)d.seed ^ (d.site * 0x9E3779B9u), (uint32_t)(d.seed >> 32) + d.site);
+  uint4 r = philox4x32_10(make_uint4((uint32_t)group, (uint32_t)(group >> 32), d.site, 0x5eedu), key);
+  uint32_t thr = (uint32_t)(d.p * 65536.f);
+  uint32_t m = 0;
+  m |= ((r.x & 0xffffu) >= thr) << 0;
+  m |= ((r.x >> 16) >= thr) << 1;
+  m |= ((r.y & 0xffffu) >= thr) << 2;
+  m |= ((r.y >> 16) >= thr) << 3;
+  m |= ((r.z & 0xffffu) >= thr) << 4;
+  m |= ((r.z >> 16) >= thr) << 5;
+  m |= ((r.w & 0xffffu) >= thr) << 6;
+  m |= ((r.w >> 16) >= thr) << 7;
+  return m;
+}

@@ -1,0 +1,109 @@
+// Runtime glue of libb200slu: error string, device properties, per-family launch accounting.
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void b200slu_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int b2_num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+
+namespace {
+struct FamStat {
+  long long launches = 0;
+  double flops = 0, bytes = 0, ms = 0;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+};
+FamStat g_fam[FAM_COUNT];
+bool g_timing = false;
+std::mutex g_mu;
+const char* kFamNames[FAM_COUNT] = {"gemm_tcgen05", "attention", "layernorm", "convmodule", "subsample",
+                                    "ctc", "frontend", "loss", "elementwise"};
+
+void drain(FamStat& f) {
+  for (auto& p : f.pending) {
+    float ms = 0;
+    cudaEventSynchronize(p.second);
+    cudaEventElapsedTime(&ms, p.first, p.second);
+    f.ms += ms;
+    cudaEventDestroy(p.first);
+    cudaEventDestroy(p.second);
+  }
+  f.pending.clear();
+}
+}  // namespace
+
+B2ProfScope::B2ProfScope(int fam_, cudaStream_t st_, double flops, double bytes) : fam(fam_), st(st_), timed(false) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  FamStat& f = g_fam[fam];
+  f.launches++;
+  f.flops += flops;
+  f.bytes += bytes;
+  if (g_timing) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cs);
+    if (cs == cudaStreamCaptureStatusNone) {
+      cudaEventCreate(&e0);
+      cudaEventCreate(&e1);
+      cudaEventRecord(e0, st);
+      timed = true;
+    }
+  }
+}
+B2ProfScope::~B2ProfScope() {
+  if (timed) {
+    cudaEventRecord(e1, st);
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_fam[fam].pending.emplace_back(e0, e1);
+  }
+}
+
+extern "C" {
+int b200slu_version(void) { return B200SLU_VERSION; }
+const char* b200slu_last_error(void) { return g_err; }
+void b200slu_prof_reset(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  for (auto& f : g_fam) {
+    drain(f);
+    f = FamStat();
+  }
+}
+void b200slu_prof_enable_timing(int on) { g_timing = on != 0; }
+int b200slu_prof_num_families(void) { return FAM_COUNT; }
+const char* b200slu_prof_family_name(int fam) { return (fam >= 0 && fam < FAM_COUNT) ? kFamNames[fam] : ""; }
+int b200slu_prof_get(int fam, double* out4) {
+  if (fam < 0 || fam >= FAM_COUNT || out4 == nullptr) return B200SLU_EINVAL;
+  std::lock_guard<std::mutex> lk(g_mu);
+  FamStat& f = g_fam[fam];
+  drain(f);
+  out4[0] = (double)f.launches;
+  out4[1] = f.ms;
+  out4[2] = f.flops;
+  out4[3] = f.bytes;
+  return 0;
+}
+long long b200slu_prof_total_launches(void) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  long long n = 0;
+  for (auto& f : g_fam) n += f.launches;
+  return n;
+}
+}

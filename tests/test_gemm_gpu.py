@@ -1,0 +1,86 @@
+"""tcgen05 GEMM vs torch fp32 matmul on the same bf16-rounded operands (GPU)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    from espnet_slurp_b200 import ops
+    return ops
+
+
+def ref_mm(a, b, trans):
+    a32, b32 = a.float(), b.float()
+    return (a32.t() @ b32) if trans else (a32 @ b32.t())
+
+
+SHAPES = [(128, 128, 64), (128, 128, 512), (256, 512, 512), (3968, 512, 512), (3968, 2048, 512), (1000, 600, 512),
+          (77, 40, 72), (4100, 1536, 512), (300, 512, 9728), (513, 1024, 2048)]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_tn(M, N, K):
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N * 3 + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+    out = ops.gemm(a, b, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    want = ref_mm(a, b, False)
+    err = (out - want).abs().max().item() / (want.abs().max().item() + 1e-6)
+    assert err < 1e-4, err
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (512, 512, 3968), (2048, 512, 4000), (512, 9728, 777), (600, 512, 1344),
+                                   (72, 40, 200)])
+def test_gemm_nt_wgrad(M, N, K):
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(K, M, device="cuda", generator=g).bfloat16()
+    b = torch.randn(K, N, device="cuda", generator=g).bfloat16()
+    out = torch.zeros(M, N, device="cuda")
+    ops.gemm(a, b, trans=True, out=out, accumulate=True)
+    ops.gemm(a, b, trans=True, out=out, accumulate=True)
+    torch.cuda.synchronize()
+    want = 2 * ref_mm(a, b, True)
+    err = (out - want).abs().max().item() / (want.abs().max().item() + 1e-6)
+    assert err < 1e-4, err
+
+
+def test_gemm_epilogue_bias_swish_residual():
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    M, N, K = 1000, 512, 256
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = (torch.randn(N, K, device="cuda", generator=g) * 0.1).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    out, pre = ops.gemm(a, b, bias=bias, act="swish", alpha=0.5, residual=res, pre_act_out=True, out_dtype=torch.float32)
+    y = ref_mm(a, b, False) + bias
+    want = res + 0.5 * y * torch.sigmoid(y)
+    assert (out - want).abs().max().item() < 2e-3
+    assert (pre.float() - y).abs().max().item() < 0.05
+    # activation-gradient epilogue: dH = (g @ W) * swish'(pre)
+    gy = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    out2 = ops.gemm(gy, b, act_grad_input=pre, act_grad="swish")
+    s = torch.sigmoid(pre.float())
+    want2 = ref_mm(gy, b, False) * (s * (1 + pre.float() * (1 - s)))
+    assert (out2.float() - want2).abs().max().item() < 0.05 * want2.abs().max().item()
+    out3 = ops.gemm(gy, b, act_grad_input=pre, act_grad="relu", bias=bias, act="relu")
+    want3 = torch.relu(ref_mm(gy, b, False) + bias) * (pre.float() > 0)
+    assert (out3.float() - want3).abs().max().item() < 0.02 * want3.abs().max().item()
+
+
+def test_gemm_dropout_statistics_and_determinism():
+    ops = _ops()
+    M, N, K = 2048, 512, 64
+    a = torch.ones(M, K, device="cuda").bfloat16()
+    b = torch.ones(N, K, device="cuda").bfloat16()
+    o1 = ops.gemm(a, b, dropout_p=0.1, seed=1234, site=7, out_dtype=torch.float32)
+    o2 = ops.gemm(a, b, dropout_p=0.1, seed=1234, site=7, out_dtype=torch.float32)
+    o3 = ops.gemm(a, b, dropout_p=0.1, seed=1234, site=8, out_dtype=torch.float32)
+    assert torch.equal(o1, o2) and not torch.equal(o1, o3)
+    keep = (o1 != 0).float().mean().item()
+    assert abs(keep - 0.9) < 0.005, keep
+    assert abs(o1.max().item() - 64 / 0.9) < 1e-3
