@@ -146,3 +146,53 @@ __device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned l
   m |= ((r.w >> 16) >= thr) << 7;
   return m;
 }
+
+// ---------------------------------------------------------------------------
+// 8-wide vector helpers (all memory-bound kernels work on groups of 8 contiguous elements:
+// one uint4 of bf16 or two float4 of f32; one Philox call yields the 8 dropout decisions).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void load8_f32(const float* p, float (&v)[8]) {
+  float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void store8_f32(float* p, const float (&v)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void load8_bf16(const bf16* p, float (&v)[8]) {
+  uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ void store8_bf16(bf16* p, const float (&v)[8]) {
+  *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                                            pack_bf16x2(v[6], v[7]));
+}
+// dropout on 8 consecutive elements whose first flat index is e0 (multiple of 8)
+__device__ __forceinline__ void dropout8(const B2Dropout& d, unsigned long long e0, float (&v)[8]) {
+  if (d.p > 0.f) {
+    const uint32_t keep = dropout_keep8(d, e0 >> 3);
+    const float inv = 1.f / (1.f - d.p);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = ((keep >> j) & 1u) ? v[j] * inv : 0.f;
+  }
+}
+__device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats of smem */) {
+  v = warp_sum(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  v = (threadIdx.x < nw) ? red[threadIdx.x] : 0.f;
+  if (w == 0) v = warp_sum(v);
+  if (threadIdx.x == 0) red[0] = v;
+  __syncthreads();
+  return red[0];
+}
+static inline int b2_grid_for(long long work_items, int threads, int per_sm = 8) {
+  long long blocks = (work_items + threads - 1) / threads;
+  long long cap = (long long)b2_num_sms() * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}

@@ -1,0 +1,325 @@
+// Conformer ConvolutionModule middle: GLU -> depthwise Conv1d(K, same padding) -> BatchNorm1d (training:
+// batch statistics over ALL B*T positions, padded frames included) -> Swish, forward and backward.
+//
+// Replaces espnet/nets/pytorch_backend/conformer/convolution.py:67-79 between the two pointwise convs
+// (which run on the tcgen05 GEMM).  Channels-last [B, T, C] throughout, so the reference's two
+// transposes (:67, :79) disappear.  Memory-bound; shared-memory staging of a (TT + K - 1) x 64 halo
+// tile, 16-byte vector loads, per-channel statistics reduced in shared memory then one atomic per
+// channel per block.  Algorithmic bytes per position (bf16): fwd pass A 2*(2C) + 2*C, pass B 2*C + 2*C.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TT = 32;    // output frames per block
+constexpr int CC = 64;    // channels per block
+constexpr int KMAX = 31;  // cnn_module_kernel upper bound (SLURP/LibriSpeech: 31; tiny fixtures: 7)
+
+// stage glu(pw1) for frames [t0 - pad, t0 + TT + pad) x channels [c0, c0 + CC) into smem (0 outside [0, T))
+__device__ __forceinline__ void stage_glu(const bf16* __restrict__ pw1, int b, int T, int C, int t0, int c0, int K,
+                                          float (*sm)[CC]) {
+  const int pad = (K - 1) / 2, nf = TT + K - 1;
+  for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
+    const int f = it / (CC / 8), cg = it - f * (CC / 8);
+    const int t = t0 - pad + f, c = c0 + cg * 8;
+    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (t >= 0 && t < T && c < C) {
+      float a[8], gt[8];
+      const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
+      load8_bf16(row + c, a);
+      load8_bf16(row + C + c, gt);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = a[j] * sigmoidf_(gt[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sm[f][cg * 8 + j] = g[j];
+  }
+}
+
+__global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict__ pw1, const float* __restrict__ w,
+                                                         const float* __restrict__ bias, int B, int T, int C, int K,
+                                                         bf16* __restrict__ out, float* __restrict__ sums) {
+  __shared__ float sm[TT + KMAX - 1][CC];
+  __shared__ float red[2][4][CC];
+  const int t0 = blockIdx.x * TT, c0 = blockIdx.y * CC, b = blockIdx.z;
+  stage_glu(pw1, b, T, C, t0, c0, K, sm);
+  __syncthreads();
+  const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;  // 4 frame lanes
+  const int c = c0 + cl;
+  float s1 = 0.f, s2 = 0.f;
+  if (c < C) {
+    float wr[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) wr[k] = k < K ? w[c * K + k] : 0.f;
+    const float bs = bias[c];
+    for (int f = fr; f < TT; f += 4) {
+      const int t = t0 + f;
+      if (t >= T) break;
+      float acc = bs;
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (k < K) acc += wr[k] * sm[f + k][cl];
+      out[((long long)b * T + t) * C + c] = __float2bfloat16(acc);
+      s1 += acc;
+      s2 += acc * acc;
+    }
+  }
+  red[0][fr][cl] = s1;
+  red[1][fr][cl] = s2;
+  __syncthreads();
+  if (fr == 0 && c < C && sums != nullptr) {
+    atomicAdd(sums + c, red[0][0][cl] + red[0][1][cl] + red[0][2][cl] + red[0][3][cl]);
+    atomicAdd(sums + C + c, red[1][0][cl] + red[1][1][cl] + red[1][2][cl] + red[1][3][cl]);
+  }
+}
+
+__global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict__ d_dw, const bf16* __restrict__ pw1,
+                                                         const float* __restrict__ w, int B, int T, int C, int K,
+                                                         bf16* __restrict__ d_pw1, float* __restrict__ dw_accum,
+                                                         float* __restrict__ dbias_accum) {
+  __shared__ float sg[TT + KMAX - 1][CC];  // glu halo tile
+  __shared__ float sd[TT + KMAX - 1][CC];  // d_dw halo tile
+  __shared__ float swg[CC][KMAX + 1];      // block partial of dW (+ dbias in the last slot)
+  const int t0 = blockIdx.x * TT, c0 = blockIdx.y * CC, b = blockIdx.z;
+  const int pad = (K - 1) / 2, nf = TT + K - 1;
+  stage_glu(pw1, b, T, C, t0, c0, K, sg);
+  for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
+    const int f = it / (CC / 8), cg = it - f * (CC / 8);
+    const int t = t0 - pad + f, c = c0 + cg * 8;
+    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (t >= 0 && t < T && c < C) load8_bf16(d_dw + ((long long)b * T + t) * C + c, g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sd[f][cg * 8 + j] = g[j];
+  }
+  for (int it = threadIdx.x; it < CC * (KMAX + 1); it += blockDim.x) (&swg[0][0])[it] = 0.f;
+  __syncthreads();
+  const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;
+  const int c = c0 + cl;
+  if (c < C) {
+    float wr[KMAX], acc[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      wr[k] = k < K ? w[c * K + k] : 0.f;
+      acc[k] = 0.f;
+    }
+    float accb = 0.f;
+    for (int f = fr; f < TT; f += 4) {
+      const int t = t0 + f;
+      if (t >= T) break;
+      // d_glu[t] = sum_k w[k] * d_dw[t - k + pad]
+      float dg = 0.f;
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (k < K) dg += wr[k] * sd[f + (K - 1) - k][cl];
+      const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
+      const float a = __bfloat162float(row[c]), gt = __bfloat162float(row[C + c]);
+      const float sgm = sigmoidf_(gt);
+      bf16* drow = d_pw1 + ((long long)b * T + t) * (2 * C);
+      drow[c] = __float2bfloat16(dg * sgm);
+      drow[C + c] = __float2bfloat16(dg * a * sgm * (1.f - sgm));
+      // dW[k] += d_dw[t] * glu[t + k - pad]
+      const float dv = sd[f + pad][cl];
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (k < K) acc[k] += dv * sg[f + k][cl];
+      accb += dv;
+    }
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k)
+      if (k < K) atomicAdd(&swg[cl][k], acc[k]);
+    atomicAdd(&swg[cl][KMAX], accb);
+  }
+  __syncthreads();
+  for (int it = threadIdx.x; it < CC * K; it += blockDim.x) {
+    const int ch = it / K, k = it - ch * K;
+    if (c0 + ch < C) atomicAdd(dw_accum + (long long)(c0 + ch) * K + k, swg[ch][k]);
+  }
+  if (threadIdx.x < CC && c0 + threadIdx.x < C) atomicAdd(dbias_accum + c0 + threadIdx.x, swg[threadIdx.x][KMAX]);
+}
+
+// BatchNorm1d training statistics: mean / rstd from the fp32 sums, running-stat update (momentum,
+// unbiased variance) exactly as torch.nn.BatchNorm1d does (convolution.py:45).
+__global__ void bn_finalize_kernel(const float* __restrict__ sums, int C, float n, float eps, float momentum,
+                                   float* __restrict__ mean_rstd, float* __restrict__ running_mean,
+                                   float* __restrict__ running_var, long long* __restrict__ num_batches) {
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < C; c += gridDim.x * blockDim.x) {
+    const float mean = sums[c] / n;
+    const float var = fmaxf(sums[C + c] / n - mean * mean, 0.f);
+    mean_rstd[c] = mean;
+    mean_rstd[C + c] = rsqrtf(var + eps);
+    if (running_mean != nullptr) {
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * (n / fmaxf(n - 1.f, 1.f));
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
+}
+
+__global__ void __launch_bounds__(256) bn_swish_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ mean_rstd,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           long long M, int C, bf16* __restrict__ y) {
+  const int gpr = C >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < M * gpr; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / gpr;
+    const int c = (int)(i - row * gpr) * 8;
+    float v[8], mu[8], rs[8], ga[8], be[8];
+    load8_bf16(x + row * C + c, v);
+    load8_f32(mean_rstd + c, mu);
+    load8_f32(mean_rstd + C + c, rs);
+    load8_f32(gamma + c, ga);
+    load8_f32(beta + c, be);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = swishf_((v[j] - mu[j]) * rs[j] * ga[j] + be[j]);
+    store8_bf16(y + row * C + c, v);
+  }
+}
+
+// sums2[c] += sum dz ; sums2[C + c] += sum dz * xhat   with dz = dy * swish'(gamma * xhat + beta)
+__global__ void __launch_bounds__(256) bn_swish_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                                  const float* __restrict__ mean_rstd,
+                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                  int M, int C, float* __restrict__ sums2) {
+  __shared__ float red[2][8][32][8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int g = blockIdx.x * 32 + tx;
+  const bool ok = g * 8 < C;
+  float a1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, a2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (ok) {
+    float mu[8], rs[8], ga[8], be[8];
+    load8_f32(mean_rstd + g * 8, mu);
+    load8_f32(mean_rstd + C + g * 8, rs);
+    load8_f32(gamma + g * 8, ga);
+    load8_f32(beta + g * 8, be);
+    for (long long r = (long long)blockIdx.y * 8 + ty; r < M; r += (long long)gridDim.y * 8) {
+      float d[8], v[8];
+      load8_bf16(dy + r * C + g * 8, d);
+      load8_bf16(x + r * C + g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float xh = (v[j] - mu[j]) * rs[j];
+        const float dz = d[j] * swish_gradf_(ga[j] * xh + be[j]);
+        a1[j] += dz;
+        a2[j] += dz * xh;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    red[0][ty][tx][j] = a1[j];
+    red[1][ty][tx][j] = a2[j];
+  }
+  __syncthreads();
+  if (ty < 2 && ok) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[ty][k][tx][j];
+      atomicAdd(sums2 + ty * C + g * 8 + j, s);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                                 const float* __restrict__ mean_rstd,
+                                                                 const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                 const float* __restrict__ sums2, long long M, int C,
+                                                                 bf16* __restrict__ dx, float* __restrict__ dgamma,
+                                                                 float* __restrict__ dbeta) {
+  const int gpr = C >> 3;
+  const float invn = 1.f / (float)M;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < M * gpr; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / gpr;
+    const int c = (int)(i - row * gpr) * 8;
+    float d[8], v[8], mu[8], rs[8], ga[8], be[8], s1[8], s2[8], o[8];
+    load8_bf16(dy + row * C + c, d);
+    load8_bf16(x + row * C + c, v);
+    load8_f32(mean_rstd + c, mu);
+    load8_f32(mean_rstd + C + c, rs);
+    load8_f32(gamma + c, ga);
+    load8_f32(beta + c, be);
+    load8_f32(sums2 + c, s1);
+    load8_f32(sums2 + C + c, s2);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float xh = (v[j] - mu[j]) * rs[j];
+      const float dz = d[j] * swish_gradf_(ga[j] * xh + be[j]);
+      o[j] = ga[j] * rs[j] * (dz - s1[j] * invn - xh * s2[j] * invn);
+    }
+    store8_bf16(dx + row * C + c, o);
+  }
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      dbeta[c] += sums2[c];
+      dgamma[c] += sums2[C + c];
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const float* bias, int B, int T, int C, int K, void* out,
+                                      float* bn_sums, void* stream) {
+  B2_CHECK_ARG(B > 0 && T > 0 && C % 8 == 0 && K % 2 == 1 && K <= KMAX, "glu_dwconv: C %% 8 == 0, odd K <= %d (C=%d K=%d)", KMAX,
+               C, K);
+  B2_CHECK_ARG(B <= 65535, "glu_dwconv: B too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((T + TT - 1) / TT, (C + CC - 1) / CC, B);
+  B2_SCOPE(FAM_CONVMOD, st, 2.0 * B * T * C * K, 6.0 * B * T * C);
+  glu_dw_fwd_kernel<<<grid, 256, 0, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out, bn_sums);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
+                                      float* dw_accum, float* dbias_accum, void* stream) {
+  B2_CHECK_ARG(B > 0 && T > 0 && C % 8 == 0 && K % 2 == 1 && K <= KMAX, "glu_dwconv_bwd: C %% 8 == 0, odd K <= %d", KMAX);
+  B2_CHECK_ARG(B <= 65535, "glu_dwconv_bwd: B too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((T + TT - 1) / TT, (C + CC - 1) / CC, B);
+  B2_SCOPE(FAM_CONVMOD, st, 4.0 * B * T * C * K, 10.0 * B * T * C);
+  glu_dw_bwd_kernel<<<grid, 256, 0, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,
+                                          dbias_accum);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_bn_finalize(const float* sums, int C, long long n, float eps, float momentum, float* mean_rstd,
+                                   float* running_mean, float* running_var, long long* num_batches_tracked, void* stream) {
+  B2_CHECK_ARG(C > 0 && n > 0, "bn_finalize: empty");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_CONVMOD, st, 0, 24.0 * C);
+  bn_finalize_kernel<<<(C + 255) / 256, 256, 0, st>>>(sums, C, (float)n, eps, momentum, mean_rstd, running_mean, running_var,
+                                                      num_batches_tracked);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_bn_swish_fwd(const void* x, const float* mean_rstd, const float* gamma, const float* beta, long long M,
+                                    int C, void* y, void* stream) {
+  B2_CHECK_ARG(M > 0 && C % 8 == 0, "bn_swish_fwd: C %% 8 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_CONVMOD, st, 0, 4.0 * M * C);
+  bn_swish_fwd_kernel<<<b2_grid_for(M * (C >> 3), 256), 256, 0, st>>>((const bf16*)x, mean_rstd, gamma, beta, M, C, (bf16*)y);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_bn_swish_bwd(const void* dy, const void* x, const float* mean_rstd, const float* gamma, const float* beta,
+                                    long long M, int C, float* sums2_zeroed, void* dx, float* dgamma_accum, float* dbeta_accum,
+                                    void* stream) {
+  B2_CHECK_ARG(M > 0 && M < (1LL << 31) && C % 8 == 0, "bn_swish_bwd: C %% 8 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((C + 255) / 256, 1);
+  long long gy = (M + 63) / 64;
+  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  grid.y = (unsigned)(gy < cap ? gy : cap);
+  B2_SCOPE(FAM_CONVMOD, st, 0, 10.0 * M * C);
+  bn_swish_bwd_reduce_kernel<<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, (int)M, C,
+                                                   sums2_zeroed);
+  B2_LAUNCH_CHECK();
+  bn_swish_bwd_apply_kernel<<<b2_grid_for(M * (C >> 3), 256), 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma,
+                                                                            beta, sums2_zeroed, M, C, (bf16*)dx, dgamma_accum,
+                                                                            dbeta_accum);
+  B2_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,225 @@
+// Small memory-bound helpers around the GEMMs: fp32->bf16 cast with scale/dropout, bias-gradient
+// column sums, the rel-pos bias add (attention.py:289-291) and the decoder token embedding
+// (transformer_decoder.py:72-77, embedding.py:82-94).  All are single-pass, 16-byte vectorised.
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, bf16* __restrict__ y, long long n, float alpha,
+                                                   B2Dropout drop) {
+  const long long ng = n >> 3;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ng; g += (long long)gridDim.x * blockDim.x) {
+    float v[8];
+    load8_f32(x + g * 8, v);
+    dropout8(drop, (unsigned long long)g * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= alpha;
+    store8_bf16(y + g * 8, v);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+    const long long i = (ng << 3) + threadIdx.x;
+    y[i] = __float2bfloat16(x[i] * alpha);
+  }
+}
+
+// out[n] += sum_m dy[m, n]   (dy bf16, row stride ld)
+__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ dy, int M, int N, long long ld,
+                                                     float* __restrict__ out) {
+  __shared__ float red[8][32][8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int g = blockIdx.x * 32 + tx;  // column group of 8
+  const bool ok = g * 8 < N;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (ok) {
+    for (long long r = (long long)blockIdx.y * 8 + ty; r < M; r += (long long)gridDim.y * 8) {
+      float v[8];
+      load8_bf16(dy + r * ld + g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][tx][j] = acc[j];
+  __syncthreads();
+  if (ty == 0 && ok) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[k][tx][j];
+      if (g * 8 + j < N) atomicAdd(out + g * 8 + j, s);
+    }
+  }
+}
+
+// q_u = q + pos_bias_u, q_v = q + pos_bias_v  (q = first d columns of the fused qkv rows)
+__global__ void __launch_bounds__(256) pos_bias_fwd_kernel(const bf16* __restrict__ q, long long ldq, const float* __restrict__ u,
+                                                           const float* __restrict__ v, long long M, int d,
+                                                           bf16* __restrict__ qu, bf16* __restrict__ qv) {
+  const int gpr = d >> 3;
+  const long long total = M * gpr;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / gpr;
+    const int c = (int)(i - row * gpr) * 8;
+    float x[8], bu[8], bv[8], o[8];
+    load8_bf16(q + row * ldq + c, x);
+    load8_f32(u + c, bu);
+    load8_f32(v + c, bv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = x[j] + bu[j];
+    store8_bf16(qu + row * d + c, o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = x[j] + bv[j];
+    store8_bf16(qv + row * d + c, o);
+  }
+}
+
+// dq = dq_u + dq_v (written into the fused dqkv rows); du += colsum(dq_u); dv += colsum(dq_v)
+__global__ void __launch_bounds__(256) pos_bias_bwd_kernel(const bf16* __restrict__ dqu, const bf16* __restrict__ dqv, int M,
+                                                           int d, bf16* __restrict__ dq, long long lddq,
+                                                           float* __restrict__ du, float* __restrict__ dv) {
+  __shared__ float red[2][8][32][8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int g = blockIdx.x * 32 + tx;
+  const bool ok = g * 8 < d;
+  float au[8] = {0, 0, 0, 0, 0, 0, 0, 0}, av[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (ok) {
+    for (long long r = (long long)blockIdx.y * 8 + ty; r < M; r += (long long)gridDim.y * 8) {
+      float a[8], b[8], o[8];
+      load8_bf16(dqu + r * d + g * 8, a);
+      load8_bf16(dqv + r * d + g * 8, b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        au[j] += a[j];
+        av[j] += b[j];
+        o[j] = a[j] + b[j];
+      }
+      store8_bf16(dq + r * lddq + g * 8, o);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    red[0][ty][tx][j] = au[j];
+    red[1][ty][tx][j] = av[j];
+  }
+  __syncthreads();
+  if (ty < 2 && ok) {
+    float* dst = ty == 0 ? du : dv;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[ty][k][tx][j];
+      atomicAdd(dst + g * 8 + j, s);
+    }
+  }
+}
+
+// x[r, :] = dropout(emb[tok[r], :] * scale + pe[r % L, :])   (fp32 residual stream)
+__global__ void __launch_bounds__(256) embed_fwd_kernel(const float* __restrict__ emb, const int* __restrict__ tok,
+                                                        const float* __restrict__ pe, long long R, int L, int d, float scale,
+                                                        float* __restrict__ x, B2Dropout drop) {
+  const int gpr = d >> 3;
+  const long long total = R * gpr;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / gpr;
+    const int c = (int)(i - row * gpr) * 8;
+    float e[8], p[8];
+    load8_f32(emb + (long long)tok[row] * d + c, e);
+    load8_f32(pe + (row % L) * d + c, p);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) e[j] = e[j] * scale + p[j];
+    dropout8(drop, (unsigned long long)row * d + c, e);
+    store8_f32(x + row * d + c, e);
+  }
+}
+
+// demb[tok[r], :] += scale * dropout(dx[r, :])
+__global__ void __launch_bounds__(256) embed_bwd_kernel(const float* __restrict__ dx, const int* __restrict__ tok, long long R,
+                                                        int d, float scale, float* __restrict__ demb, B2Dropout drop) {
+  const int gpr = d >> 3;
+  const long long total = R * gpr;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / gpr;
+    const int c = (int)(i - row * gpr) * 8;
+    float g[8];
+    load8_f32(dx + row * d + c, g);
+    dropout8(drop, (unsigned long long)row * d + c, g);
+    float* dst = demb + (long long)tok[row] * d + c;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(dst + j, g[j] * scale);
+  }
+}
+
+}  // namespace
+
+extern "C" int b200slu_cast_bf16(const float* x, void* y, long long n, float alpha, float drop_p, unsigned long long seed,
+                                 unsigned int site, void* stream) {
+  B2_CHECK_ARG(n > 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0, "cast_bf16: n > 0 and 16-byte aligned pointers");
+  B2_CHECK_ARG(!(drop_p > 0.f) || n % 8 == 0, "cast_bf16: dropout needs n %% 8 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * n);
+  cast_kernel<<<b2_grid_for(n >> 3, 256), 256, 0, st>>>(x, (bf16*)y, n, alpha, B2Dropout{seed, site, drop_p});
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_colsum_bf16(const void* dy, int M, int N, long long ld, float* out_accum, void* stream) {
+  B2_CHECK_ARG(M > 0 && N > 0 && ld % 8 == 0 && ld >= ((N + 7) / 8) * 8, "colsum: bad shape M=%d N=%d ld=%lld", M, N, ld);
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((N + 255) / 256, 1);
+  int gy = (M + 63) / 64;
+  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  grid.y = gy < cap ? gy : cap;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 2.0 * M * N);
+  colsum_kernel<<<grid, 256, 0, st>>>((const bf16*)dy, M, N, ld, out_accum);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_pos_bias_fwd(const void* q, long long ldq, const float* pos_bias_u, const float* pos_bias_v, int M,
+                                    int d, void* q_u, void* q_v, void* stream) {
+  B2_CHECK_ARG(M > 0 && d % 8 == 0 && ldq % 8 == 0, "pos_bias_fwd: d and ldq must be multiples of 8");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * d);
+  pos_bias_fwd_kernel<<<b2_grid_for((long long)M * (d >> 3), 256), 256, 0, st>>>((const bf16*)q, ldq, pos_bias_u, pos_bias_v, M,
+                                                                                  d, (bf16*)q_u, (bf16*)q_v);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
+                                    float* dv_accum, void* stream) {
+  B2_CHECK_ARG(M > 0 && d % 8 == 0 && lddq % 8 == 0, "pos_bias_bwd: d and lddq must be multiples of 8");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((d + 255) / 256, 1);
+  int gy = (M + 63) / 64;
+  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  grid.y = gy < cap ? gy : cap;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * d);
+  pos_bias_bwd_kernel<<<grid, 256, 0, st>>>((const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum, dv_accum);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_embed_fwd(const float* emb, const int* tokens, const float* pe, int R, int L, int d, float scale, float* x,
+                                 float drop_p, unsigned long long seed, unsigned int site, void* stream) {
+  B2_CHECK_ARG(R > 0 && L > 0 && d % 8 == 0, "embed_fwd: d must be a multiple of 8");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 12.0 * R * d);
+  embed_fwd_kernel<<<b2_grid_for((long long)R * (d >> 3), 256), 256, 0, st>>>(emb, tokens, pe, R, L, d, scale, x,
+                                                                              B2Dropout{seed, site, drop_p});
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_embed_bwd(const float* dx, const int* tokens, int R, int d, float scale, float* demb_accum, float drop_p,
+                                 unsigned long long seed, unsigned int site, void* stream) {
+  B2_CHECK_ARG(R > 0 && d % 8 == 0, "embed_bwd: d must be a multiple of 8");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 12.0 * R * d);
+  embed_bwd_kernel<<<b2_grid_for((long long)R * (d >> 3), 256), 256, 0, st>>>(dx, tokens, R, d, scale, demb_accum,
+                                                                              B2Dropout{seed, site, drop_p});
+  B2_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,192 @@
+// fp32 feature front-end: waveform -> log-mel (STFT fused), and SpecAug + utterance mean normalisation.
+//
+// logmel replaces DefaultFrontend.forward (espnet2/asr/frontend/default.py:82-117) = Stft
+// (espnet2/layers/stft.py:83-170: torch.stft, centre reflect-pad n_fft/2, periodic Hann, onesided,
+// frames past olens zeroed) -> power re^2+im^2 (default.py:110) -> LogMel (espnet2/layers/log_mel.py:
+// 62-79: matmul with the mel matrix, clamp 1e-10, natural log, padded frames 0).  One block per frame:
+// framing + window + radix-2 FFT in shared memory + power + mel + log, so the (B,257,T,2) spectrum
+// and five elementwise passes never touch HBM (read 4*N*B, write 4*T_in*n_mels*B bytes).
+//
+// specaug_mvn replaces SpecAug.forward (espnet2/asr/specaug/specaug.py:89-96: TimeWarp
+// espnet2/layers/time_warp.py:9-46,65-88 bicubic; MaskAlongAxis espnet2/layers/mask_along_axis.py:8-68
+// freq then time, fill 0) followed by UtteranceMVN (espnet2/layers/utterance_mvn.py:45-88, means only:
+// zero the padding, mean over valid frames, subtract from ALL frames).  The random draws stay on the
+// host (same torch RNG calls, same order as the reference, Appendix A.15) and arrive as small arrays.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) logmel_kernel(const float* __restrict__ wav, long long ldw, int N,
+                                                     const int* __restrict__ lens, const float* __restrict__ melmat, int n_fft,
+                                                     int log2n, int hop, int n_mels, int T, float* __restrict__ feats,
+                                                     int* __restrict__ flens) {
+  extern __shared__ float sm[];
+  float* re = sm;               // [n_fft]
+  float* im = sm + n_fft;       // [n_fft]
+  float* twc = im + n_fft;      // [n_fft/2] cos
+  float* tws = twc + n_fft / 2; // [n_fft/2] -sin
+  const int t = blockIdx.x, b = blockIdx.y;
+  const int pad = n_fft / 2;
+  const int olen = (lens[b] + 2 * pad - n_fft) / hop + 1;
+  if (t == 0 && threadIdx.x == 0 && flens != nullptr) flens[b] = olen;
+  float* out = feats + ((long long)b * T + t) * n_mels;
+  if (t >= olen) {
+    for (int m = threadIdx.x; m < n_mels; m += blockDim.x) out[m] = 0.f;
+    return;
+  }
+  const float* w = wav + (long long)b * ldw;
+  for (int i = threadIdx.x; i < n_fft; i += blockDim.x) {
+    int n = t * hop - pad + i;
+    if (n < 0) n = -n;                    // reflect (no edge repeat), over the padded batch width N
+    if (n >= N) n = 2 * (N - 1) - n;
+    const float win = 0.5f - 0.5f * cospif(2.f * (float)i / (float)n_fft);
+    const int rev = (int)(__brev((unsigned)i) >> (32 - log2n));
+    re[rev] = w[n] * win;
+    im[rev] = 0.f;
+  }
+  for (int k = threadIdx.x; k < n_fft / 2; k += blockDim.x) {
+    float s, c;
+    sincospif(-2.f * (float)k / (float)n_fft, &s, &c);
+    twc[k] = c;
+    tws[k] = s;
+  }
+  __syncthreads();
+  for (int s = 1; s <= log2n; ++s) {
+    const int half = 1 << (s - 1), stride = n_fft >> s;
+    for (int j = threadIdx.x; j < n_fft / 2; j += blockDim.x) {
+      const int grp = j >> (s - 1), pos = j & (half - 1);
+      const int i0 = (grp << s) + pos, i1 = i0 + half;
+      const float c = twc[pos * stride], sn = tws[pos * stride];
+      const float xr = re[i1] * c - im[i1] * sn, xi = re[i1] * sn + im[i1] * c;
+      const float ur = re[i0], ui = im[i0];
+      re[i0] = ur + xr;
+      im[i0] = ui + xi;
+      re[i1] = ur - xr;
+      im[i1] = ui - xi;
+    }
+    __syncthreads();
+  }
+  const int nbins = n_fft / 2 + 1;
+  for (int k = threadIdx.x; k < nbins; k += blockDim.x) re[k] = re[k] * re[k] + im[k] * im[k];  // power, in place
+  __syncthreads();
+  for (int m = threadIdx.x; m < n_mels; m += blockDim.x) {
+    float acc = 0.f;
+    for (int k = 0; k < nbins; ++k) acc += re[k] * melmat[k * n_mels + m];
+    out[m] = logf(fmaxf(acc, 1e-10f));
+  }
+}
+
+__device__ __forceinline__ void cubic_w(float t, float (&w)[4]) {
+  const float A = -0.75f;
+  const float x0 = t + 1.f, x1 = t, x2 = 1.f - t, x3 = 2.f - t;
+  w[0] = ((A * x0 - 5.f * A) * x0 + 8.f * A) * x0 - 4.f * A;
+  w[1] = ((A + 2.f) * x1 - (A + 3.f)) * x1 * x1 + 1.f;
+  w[2] = ((A + 2.f) * x2 - (A + 3.f)) * x2 * x2 + 1.f;
+  w[3] = ((A * x3 - 5.f * A) * x3 + 8.f * A) * x3 - 4.f * A;
+}
+
+// value of the time-warped utterance at (t, f): segment [seg0, seg0 + in_len) resized to out_len frames
+__device__ __forceinline__ float warp_sample(const float* __restrict__ x, int F, int f, int seg0, int in_len, int out_len, int dst) {
+  const float scale = (float)in_len / (float)out_len;
+  const float src = ((float)dst + 0.5f) * scale - 0.5f;
+  const float fl = floorf(src);
+  float w[4];
+  cubic_w(src - fl, w);
+  const int i0 = (int)fl;
+  float acc = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    int idx = i0 - 1 + k;
+    idx = max(0, min(in_len - 1, idx));
+    acc += w[k] * x[(long long)(seg0 + idx) * F + f];
+  }
+  return acc;
+}
+
+__global__ void __launch_bounds__(256) specaug_mvn_kernel(const float* __restrict__ x, int T, int F, const int* __restrict__ lens,
+                                                          const int* __restrict__ center, const int* __restrict__ warped,
+                                                          const int* __restrict__ fmask, int nf, const int* __restrict__ tmask,
+                                                          int nt, int do_mvn, float* __restrict__ y) {
+  extern __shared__ float sm[];  // [nfl][F] partial sums, then [F] means
+  const int b = blockIdx.x;
+  const int len = min(lens[b], T);
+  const float* xb = x + (long long)b * T * F;
+  float* yb = y + (long long)b * T * F;
+  const int nfl = blockDim.x / F;
+  const int fl = threadIdx.x / F, f = threadIdx.x - fl * F;
+  const bool active = fl < nfl;
+  const int c = center != nullptr ? center[b] : -1, wp = center != nullptr ? warped[b] : 0;
+  bool fdrop = false;
+  if (active)
+    for (int k = 0; k < nf; ++k) {
+      const int pos = fmask[(b * nf + k) * 2], ml = fmask[(b * nf + k) * 2 + 1];
+      fdrop = fdrop || (f >= pos && f < pos + ml);
+    }
+  float sum = 0.f;
+  if (active) {
+    for (int t = fl; t < T; t += nfl) {
+      float v = 0.f;
+      if (t < len) {
+        if (c >= 0) v = t < wp ? warp_sample(xb, F, f, 0, c, wp, t) : warp_sample(xb, F, f, c, len - c, len - wp, t - wp);
+        else v = xb[(long long)t * F + f];
+        bool drop = fdrop;
+        for (int k = 0; k < nt; ++k) {
+          const int pos = tmask[(b * nt + k) * 2], ml = tmask[(b * nt + k) * 2 + 1];
+          drop = drop || (t >= pos && t < pos + ml);
+        }
+        if (drop) v = 0.f;
+      }
+      yb[(long long)t * F + f] = v;
+      sum += v;
+    }
+    sm[fl * F + f] = sum;
+  }
+  __syncthreads();
+  if (!do_mvn) return;
+  if (threadIdx.x < F) {
+    float s = 0.f;
+    for (int k = 0; k < nfl; ++k) s += sm[k * F + threadIdx.x];
+    sm[nfl * F + threadIdx.x] = s / (float)len;
+  }
+  __syncthreads();
+  if (active) {
+    const float mean = sm[nfl * F + f];
+    for (int t = fl; t < T; t += nfl) yb[(long long)t * F + f] -= mean;
+  }
+}
+
+}  // namespace
+
+extern "C" int b200slu_logmel_fwd(const float* wav, long long ldw, int B, int N, const int* lens, const float* melmat, int n_fft,
+                                  int hop, int n_mels, float* feats, int* feat_lens, void* stream) {
+  int log2n = 0;
+  while ((1 << log2n) < n_fft) ++log2n;
+  B2_CHECK_ARG(B > 0 && B <= 65535 && N > n_fft / 2 && (1 << log2n) == n_fft && n_fft >= 4 && n_fft <= 4096 && hop > 0 &&
+                   n_mels > 0,
+               "logmel: need power-of-two 4 <= n_fft <= 4096 and N > n_fft/2 (N=%d n_fft=%d)", N, n_fft);
+  const int T = N / hop + 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = (size_t)3 * n_fft * sizeof(float);
+  B2_SCOPE(FAM_FRONTEND, st, (double)B * T * (5.0 * n_fft * log2n + 2.0 * (n_fft / 2 + 1) * n_mels),
+           4.0 * B * N + 4.0 * B * T * n_mels);
+  logmel_kernel<<<dim3(T, B), 256, smem, st>>>(wav, ldw, N, lens, melmat, n_fft, log2n, hop, n_mels, T, feats, feat_lens);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_specaug_mvn_fwd(const float* x, int B, int T, int F, const int* lens, const int* warp_center,
+                                       const int* warp_warped, const int* freq_masks, int n_freq_masks, const int* time_masks,
+                                       int n_time_masks, int do_mvn, float* y, void* stream) {
+  B2_CHECK_ARG(B > 0 && T > 0 && F > 0 && F <= 256, "specaug_mvn: need F <= 256 (F=%d)", F);
+  B2_CHECK_ARG((warp_center == nullptr) == (warp_warped == nullptr), "specaug_mvn: warp draws must come in pairs");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nfl = 256 / F;
+  const size_t smem = (size_t)(nfl + 1) * F * sizeof(float);
+  B2_SCOPE(FAM_FRONTEND, st, 0, 8.0 * B * T * F);
+  specaug_mvn_kernel<<<B, 256, smem, st>>>(x, T, F, lens, warp_center, warp_warped, freq_masks, n_freq_masks, time_masks,
+                                           n_time_masks, do_mvn, y);
+  B2_LAUNCH_CHECK();
+  return 0;
+}

@@ -7,10 +7,13 @@
 // positionwise_feed_forward.py:25-26; convolution.py:28-53; subsampling.py:56-65;
 // espnet2/asr/ctc.py:33; espnet2/asr/decoder/transformer_decoder.py:85.
 //
-// Two operand modes, one kernel:
-//   trans=0 ("TN"):  C[M,N] = A[M,K] . B[N,K]^T      A, B row-major, K contiguous   (fwd, dgrad)
-//   trans=1 ("NT"):  C[M,N] = A[K,M]^T . B[K,N]      A, B row-major, K = row index  (wgrad)
-// trans=1 uses MN-major UMMA descriptors so activations never get transposed in HBM.
+// Operand majorness is chosen per operand (4 instantiations of one kernel):
+//   trans_a=0: A is [M,K] row-major (K contiguous)      trans_a=1: A is [K,M] row-major (M contiguous)
+//   trans_b=0: B is [N,K] row-major (K contiguous)      trans_b=1: B is [K,N] row-major (N contiguous)
+//   (0,0) fwd   Y = X W^T        (0,1) dgrad  dX = dY W      (1,1) wgrad  dW = dY^T X
+// transposed operands use MN-major UMMA descriptors so nothing is ever transposed in HBM.
+// Two batch levels (inner, outer) with independent strides per operand (stride 0 = broadcast)
+// cover the per-(utterance, head) attention contractions: the TMA maps are 4-D.
 //
 // CTA = one 128 x BN output tile.  Warp roles: 0 = TMA producer, 1 = TMEM owner + MMA
 // issuer (one elected lane), 2..5 = epilogue (TMEM lane group = warp_id % 4).
@@ -58,6 +61,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -111,12 +120,14 @@ struct EpiArgs {
   bf16* pre_out;
   void* out;
   long long ldc, ldres, ldaux;
+  long long c_bs_inner, c_bs_outer;  // output batch strides (elements)
+  int a_bc_inner, a_bc_outer, b_bc_inner, b_bc_outer;  // 1 = operand indexed by that batch level, 0 = broadcast
   float alpha;
   int act, aux_mode, out_f32, accumulate;
   B2Dropout drop;
 };
 
-template <int BN, int STAGES, bool TRANS>
+template <int BN, int STAGES>
 struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
@@ -127,7 +138,8 @@ struct SmemLayout {
 };
 
 // One 32-column chunk of one accumulator row: fused epilogue + store.
-__device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32], int row, int col0, int N, bool first_split) {
+__device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32], int row, int col0, int N, bool first_split,
+                                               long long out_off) {
   const bool full = (col0 + 32 <= N);
   if (ep.bias != nullptr && first_split) {
     if (full) {
@@ -222,7 +234,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
     }
   }
   if (ep.out_f32) {
-    float* o = reinterpret_cast<float*>(ep.out) + (long long)row * ep.ldc + col0;
+    float* o = reinterpret_cast<float*>(ep.out) + out_off + (long long)row * ep.ldc + col0;
     if (ep.accumulate) {
 #pragma unroll
       for (int j = 0; j < 32; ++j)
@@ -236,7 +248,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
         if (col0 + j < N) o[j] = v[j];
     }
   } else {
-    bf16* o = reinterpret_cast<bf16*>(ep.out) + (long long)row * ep.ldc + col0;
+    bf16* o = reinterpret_cast<bf16*>(ep.out) + out_off + (long long)row * ep.ldc + col0;
     if (full) {
 #pragma unroll
       for (int j = 0; j < 32; j += 8) {
@@ -252,12 +264,13 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
   }
 }
 
-// Persistent: grid = min(#work units, #SMs); unit u = (tile, k-split), tiles n-fastest.
-template <int BN, int STAGES, bool TRANS>
+// Persistent: grid = min(#work units, #SMs); unit u = (batch, tile, k-split), tiles n-fastest.
+template <int BN, int STAGES, bool TA, bool TB>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                  int M, int N, int K, int tiles_n, int splits, int kb_per_split, int num_units, EpiArgs ep) {
-  using L = SmemLayout<BN, STAGES, TRANS>;
+                  int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
+                  int num_units, EpiArgs ep) {
+  using L = SmemLayout<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sbase = smem_u32(smem);
@@ -269,6 +282,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_kb_total = (K + BK - 1) / BK;
+  const int units_per_batch = tiles_per_batch * splits;
 
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -298,10 +312,13 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     if (lane == 0) {
       int i = 0;  // running k-block counter (ring position)
       for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-        const int tile = u / splits, sp = u - tile * splits;
+        const int batch = u / units_per_batch, r = u - batch * units_per_batch;
+        const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
+        const int tile = r / splits, sp = r - tile * splits;
         const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
         const int kb0 = sp * kb_per_split;
         const int nkb = min(kb_per_split, num_kb_total - kb0);
+        const int abi = bi * ep.a_bc_inner, abo = bo * ep.a_bc_outer, bbi = bi * ep.b_bc_inner, bbo = bo * ep.b_bc_outer;
         for (int kb = 0; kb < nkb; ++kb, ++i) {
           const int s = i % STAGES, it = i / STAGES;
           mbar_wait(bar_empty + s * 8, (it & 1) ^ 1);
@@ -309,25 +326,29 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           const uint32_t fb = bar_full + s * 8;
           mbar_expect_tx(fb, L::STAGE_BYTES);
           const int k = (kb0 + kb) * BK;
-          if (!TRANS) {
-            tma_load_2d(sa, &map_a, fb, k, tile_m * BM);   // box {64 k, 128 rows}
-            tma_load_2d(sb, &map_b, fb, k, tile_n * BN);   // box {64 k, BN rows}
+          if (!TA) {
+            tma_load_4d(sa, &map_a, fb, k, tile_m * BM, abi, abo);   // box {64 k, 128 rows}
           } else {
             // box {64 mn, 64 k-rows}; one box per 64-wide MN atom
 #pragma unroll
-            for (int a = 0; a < BM / 64; ++a) tma_load_2d(sa + a * (64 * BK * 2), &map_a, fb, tile_m * BM + a * 64, k);
+            for (int a = 0; a < BM / 64; ++a) tma_load_4d(sa + a * (64 * BK * 2), &map_a, fb, tile_m * BM + a * 64, k, abi, abo);
+          }
+          if (!TB) {
+            tma_load_4d(sb, &map_b, fb, k, tile_n * BN, bbi, bbo);   // box {64 k, BN rows}
+          } else {
 #pragma unroll
-            for (int b = 0; b < BN / 64; ++b) tma_load_2d(sb + b * (64 * BK * 2), &map_b, fb, tile_n * BN + b * 64, k);
+            for (int b = 0; b < BN / 64; ++b) tma_load_4d(sb + b * (64 * BK * 2), &map_b, fb, tile_n * BN + b * 64, k, bbi, bbo);
           }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(BN, TRANS, TRANS);
+    constexpr uint32_t idesc = make_idesc(BN, TA, TB);
     int i = 0, t = 0;
     for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
-      const int tile = u / splits, sp = u - tile * splits;
+      const int r = u % units_per_batch;
+      const int sp = r % splits;
       const int kb0 = sp * kb_per_split;
       const int nkb = min(kb_per_split, num_kb_total - kb0);
       const int buf = t & 1;
@@ -342,16 +363,10 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           const uint32_t sa = sbase + s * L::STAGE_BYTES, sb = sa + L::A_BYTES;
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
-            uint64_t da, db;
-            if (!TRANS) {
-              // K-major: 8-row groups 1024 B apart; advance 32 B per K=16 inside the swizzle span
-              da = make_smem_desc(sa + kk * 32, 16, 1024);
-              db = make_smem_desc(sb + kk * 32, 16, 1024);
-            } else {
-              // MN-major: 64-element MN atoms (64*BK*2 B apart = LBO), 8-row K groups 1024 B apart (SBO)
-              da = make_smem_desc(sa + kk * 2048, 64 * BK * 2, 1024);
-              db = make_smem_desc(sb + kk * 2048, 64 * BK * 2, 1024);
-            }
+            // K-major: 8-row groups 1024 B apart; advance 32 B per K=16 inside the swizzle span.
+            // MN-major: 64-element MN atoms (64*BK*2 B apart = LBO), 8-row K groups 1024 B apart (SBO).
+            const uint64_t da = TA ? make_smem_desc(sa + kk * 2048, 64 * BK * 2, 1024) : make_smem_desc(sa + kk * 32, 16, 1024);
+            const uint64_t db = TB ? make_smem_desc(sb + kk * 2048, 64 * BK * 2, 1024) : make_smem_desc(sb + kk * 32, 16, 1024);
             umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0);
           }
           umma_commit(bar_empty + s * 8);                       // frees the smem stage once these MMAs retire
@@ -367,8 +382,11 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const int half = ew >> 2;           // columns [half*BN/2, +BN/2)
     int t = 0;
     for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
-      const int tile = u / splits, sp = u - tile * splits;
+      const int batch = u / units_per_batch, r = u - batch * units_per_batch;
+      const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
+      const int tile = r / splits, sp = r - tile * splits;
       const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
+      const long long out_off = (long long)bo * ep.c_bs_outer + (long long)bi * ep.c_bs_inner;
       const int buf = t & 1;
       mbar_wait(bar_acc_full + buf * 8, (t >> 1) & 1);
       tcgen05_fence_after();
@@ -376,15 +394,15 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       const bool row_ok = row < M;
 #pragma unroll 1
       for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(tmem_base + ((uint32_t)(lane_grp * 32) << 16) + buf * BN + c0, r);
+        uint32_t r32[32];
+        tmem_ld32(tmem_base + ((uint32_t)(lane_grp * 32) << 16) + buf * BN + c0, r32);
         tmem_ld_wait();
         const int col0 = tile_n * BN + c0;
         if (row_ok && col0 < N) {
           float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          epilogue_chunk(ep, v, row, col0, N, sp == 0);
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r32[j]);
+          epilogue_chunk(ep, v, row, col0, N, sp == 0, out_off);
         }
       }
       tcgen05_fence_before();
@@ -417,56 +435,78 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-// 2-D bf16 row-major tensor [rows, cols] with row stride ld (elements); box = {box_cols, box_rows}.
-int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, int box_cols, int box_rows) {
+// 4-D bf16 tensor [n_outer, n_inner, rows, cols]: row stride ld, batch strides s_inner / s_outer (elements;
+// 0 = broadcast -> that dimension gets extent 1).  box = {box_cols, box_rows, 1, 1}.
+int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, long long n_inner,
+             long long s_inner, long long n_outer, long long s_outer, int box_cols, int box_rows) {
   EncodeTiledFn enc = get_encode();
   if (enc == nullptr) {
     b200slu_set_error("cuTensorMapEncodeTiled driver entry point unavailable");
     return B200SLU_ECUDA;
   }
-  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  if (s_inner == 0) n_inner = 1;
+  if (s_outer == 0) n_outer = 1;
+  if (n_inner == 1) s_inner = ld;  // any legal stride; the coordinate is always 0
+  if (n_outer == 1) s_outer = ld;
+  cuuint64_t dims[4] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)n_inner, (cuuint64_t)n_outer};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)s_inner * 2, (cuuint64_t)s_outer * 2};
+  cuuint32_t box[4] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    b200slu_set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld ld=%lld base=%p", (int)r, rows, cols, ld, base);
+    b200slu_set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld ld=%lld batch=(%lld x %lld, strides %lld %lld) base=%p",
+                      (int)r, rows, cols, ld, n_inner, n_outer, s_inner, s_outer, base);
     return B200SLU_ECUDA;
   }
   return 0;
 }
 
-template <int BN, int STAGES, bool TRANS>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, int M, int N, int K, int splits, int kb_per, const EpiArgs& ep,
-           cudaStream_t st) {
-  using L = SmemLayout<BN, STAGES, TRANS>;
-  auto kern = gemm_bf16_tcgen05<BN, STAGES, TRANS>;
+template <int BN, int STAGES, bool TA, bool TB>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, int M, int N, int K, int nbatch, int batch_inner, int splits,
+           int kb_per, const EpiArgs& ep, cudaStream_t st) {
+  using L = SmemLayout<BN, STAGES>;
+  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB>;
   static bool configured = false;
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     configured = true;
   }
   const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BM - 1) / BM;
-  const int units = tiles_n * tiles_m * splits;
-  const int grid = units < b2_num_sms() ? units : b2_num_sms();
-  kern<<<grid, NUM_THREADS, L::TOTAL, st>>>(ma, mb, M, N, K, tiles_n, splits, kb_per, units, ep);
+  const long long units = (long long)tiles_n * tiles_m * splits * nbatch;
+  B2_CHECK_ARG(units < (1LL << 30), "gemm: too many work units (%lld)", units);
+  const int grid = units < b2_num_sms() ? (int)units : b2_num_sms();
+  kern<<<grid, NUM_THREADS, L::TOTAL, st>>>(ma, mb, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
+                                            (int)units, ep);
   B2_LAUNCH_CHECK();
   return 0;
 }
 
 }  // namespace
 
-// Internal C++ entry (used by the composite layer functions as well as the C ABI).
-int b2_gemm(int trans, int M, int N, int K, const bf16* A, long long lda, const bf16* B, long long ldb, void* C, long long ldc,
-            const b200slu_epilogue_t* e, cudaStream_t st) {
+// Internal C++ entry (used by the C ABI below).
+int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_t st) {
+  B2_CHECK_ARG(g != nullptr, "gemm: null descriptor");
+  const int M = g->M, N = g->N, K = g->K;
+  const int nbi = g->batch_inner > 0 ? g->batch_inner : 1, nbo = g->batch_outer > 0 ? g->batch_outer : 1;
+  const int nbatch = nbi * nbo;
   B2_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
-  B2_CHECK_ARG(((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0 && lda % 8 == 0 && ldb % 8 == 0,
-               "gemm: operands must be 16-byte aligned with row strides multiple of 8 elements");
+  B2_CHECK_ARG(((uintptr_t)g->A % 16) == 0 && ((uintptr_t)g->B % 16) == 0 && g->lda % 8 == 0 && g->ldb % 8 == 0,
+               "gemm: operands must be 16-byte aligned with row strides multiple of 8 elements (lda=%lld ldb=%lld)", g->lda,
+               g->ldb);
+  B2_CHECK_ARG(g->a_stride_inner % 8 == 0 && g->a_stride_outer % 8 == 0 && g->b_stride_inner % 8 == 0 &&
+                   g->b_stride_outer % 8 == 0,
+               "gemm: batch strides must be multiples of 8 elements");
   EpiArgs ep{};
-  ep.out = C;
-  ep.ldc = ldc;
+  ep.out = g->C;
+  ep.ldc = g->ldc;
+  ep.c_bs_inner = g->c_stride_inner;
+  ep.c_bs_outer = g->c_stride_outer;
+  ep.a_bc_inner = g->a_stride_inner != 0;
+  ep.a_bc_outer = g->a_stride_outer != 0;
+  ep.b_bc_inner = g->b_stride_inner != 0;
+  ep.b_bc_outer = g->b_stride_outer != 0;
   ep.alpha = 1.f;
   if (e != nullptr) {
     ep.bias = e->bias;
@@ -484,17 +524,20 @@ int b2_gemm(int trans, int M, int N, int K, const bf16* A, long long lda, const 
     ep.drop.seed = e->dropout_seed;
     ep.drop.site = e->dropout_site;
   }
+  B2_CHECK_ARG(nbatch == 1 || (ep.res == nullptr && ep.aux == nullptr && ep.pre_out == nullptr && !(ep.drop.p > 0.f)),
+               "gemm: batched mode supports only bias / activation / alpha epilogues");
   B2_CHECK_ARG(!(ep.drop.p > 0.f) || N % 8 == 0, "gemm: dropout epilogue needs N %% 8 == 0");
   B2_CHECK_ARG(!ep.accumulate || ep.out_f32, "gemm: accumulate needs fp32 output");
   const int vec = ep.out_f32 ? 4 : 8;
-  B2_CHECK_ARG(ldc % vec == 0 && ((uintptr_t)C % 16) == 0, "gemm: output must be 16-byte aligned, ldc %% %d == 0", vec);
+  B2_CHECK_ARG(g->ldc % vec == 0 && ((uintptr_t)g->C % 16) == 0 && g->c_stride_inner % vec == 0 && g->c_stride_outer % vec == 0,
+               "gemm: output must be 16-byte aligned, ldc / batch strides %% %d == 0", vec);
   B2_CHECK_ARG(ep.res == nullptr || (ep.ldres % 4 == 0 && ((uintptr_t)ep.res % 16) == 0), "gemm: residual alignment");
+  B2_CHECK_ARG(ep.aux == nullptr || (ep.ldaux % 8 == 0 && ((uintptr_t)ep.aux % 16) == 0), "gemm: act_grad_input alignment");
   B2_CHECK_ARG(ep.bias == nullptr || ((uintptr_t)ep.bias % 16) == 0, "gemm: bias alignment");
 
   const int num_kb = (K + BK - 1) / BK;
   int splits = 1;
-  // BN: 256-wide tiles only when that still fills the machine; otherwise 128.
-  const long long tiles128 = (long long)((M + BM - 1) / BM) * ((N + 127) / 128);
+  const long long tiles128 = (long long)((M + BM - 1) / BM) * ((N + 127) / 128) * nbatch;
   if (ep.accumulate) {
     // split-K (wgrad: K = B*T is long, the output is small): target >= 2 CTAs per SM
     const int want = (int)((2LL * b2_num_sms() + tiles128 - 1) / tiles128);
@@ -504,20 +547,34 @@ int b2_gemm(int trans, int M, int N, int K, const bf16* A, long long lda, const 
   splits = (num_kb + kb_per - 1) / kb_per;
 
   CUtensorMap ma, mb;
-  const double flops = 2.0 * M * N * (double)K;
-  B2_SCOPE(FAM_GEMM, st, flops, 2.0 * ((double)M * K + (double)N * K) + (ep.out_f32 ? 4.0 : 2.0) * M * N);
-  if (!trans) {
-    B2_TRY(make_map(&ma, A, M, K, lda, BK, BM));
-    B2_TRY(make_map(&mb, B, N, K, ldb, BK, 128));
-    return launch<128, 6, false>(ma, mb, M, N, K, splits, kb_per, ep, st);
-  } else {
-    B2_TRY(make_map(&ma, A, K, M, lda, 64, BK));
-    B2_TRY(make_map(&mb, B, K, N, ldb, 64, BK));
-    return launch<128, 6, true>(ma, mb, M, N, K, splits, kb_per, ep, st);
-  }
+  const double flops = 2.0 * M * N * (double)K * nbatch;
+  B2_SCOPE(FAM_GEMM, st, flops, nbatch * (2.0 * ((double)M * K + (double)N * K) + (ep.out_f32 ? 4.0 : 2.0) * M * N));
+  if (!g->trans_a)
+    B2_TRY(make_map(&ma, g->A, M, K, g->lda, nbi, g->a_stride_inner, nbo, g->a_stride_outer, BK, BM));
+  else
+    B2_TRY(make_map(&ma, g->A, K, M, g->lda, nbi, g->a_stride_inner, nbo, g->a_stride_outer, 64, BK));
+  if (!g->trans_b)
+    B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, 128));
+  else
+    B2_TRY(make_map(&mb, g->B, K, N, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, 64, BK));
+  if (!g->trans_a && !g->trans_b) return launch<128, 6, false, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
+  if (!g->trans_a && g->trans_b) return launch<128, 6, false, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
+  if (g->trans_a && !g->trans_b) return launch<128, 6, true, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
+  return launch<128, 6, true, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
+}
+
+extern "C" int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epilogue, void* stream) {
+  return b2_gemm_ex(g, epilogue, (cudaStream_t)stream);
 }
 
 extern "C" int b200slu_gemm_bf16(int trans, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
                                  void* C, long long ldc, const b200slu_epilogue_t* epilogue, void* stream) {
-  return b2_gemm(trans, M, N, K, (const bf16*)A, lda, (const bf16*)B, ldb, C, ldc, epilogue, (cudaStream_t)stream);
+  b200slu_gemm_t g{};
+  g.trans_a = g.trans_b = trans;
+  g.M = M; g.N = N; g.K = K;
+  g.A = A; g.lda = lda;
+  g.B = B; g.ldb = ldb;
+  g.C = C; g.ldc = ldc;
+  g.batch_inner = g.batch_outer = 1;
+  return b2_gemm_ex(&g, epilogue, (cudaStream_t)stream);
 }

@@ -1,0 +1,205 @@
+// LayerNorm forward / backward over the last dimension, warp per row, fp32 statistics.
+//
+// Replaces espnet/nets/pytorch_backend/transformer/layer_norm.py:12-38 (eps = 1e-12 at :23) at the
+// five call sites of conformer/encoder_layer.py:97-149, conformer_encoder.py:362-363 and the
+// decoder's norm1/2/3 + after_norm (decoder_layer.py:63-134, transformer_decoder.py:139-141).
+// The residual stream is fp32; the normalised output feeds a tensor-core GEMM, so the forward can
+// emit bf16 and/or fp32, and the backward fuses (a) the residual-path gradient add and (b) the
+// bf16 "branch gradient" alpha*dropout(dx) that the next dgrad GEMM consumes.
+// Memory-bound: algorithmic bytes fwd = M*D*(4 + 2|4), bwd = M*D*(dy + 4 + 4 [+4] [+2]).
+#include "common.cuh"
+
+namespace {
+
+template <int NG>  // NG groups of 8 columns per lane: D <= NG*256
+__global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                     const float* __restrict__ beta, int M, int D, float eps,
+                                                     bf16* __restrict__ y16, float* __restrict__ y32,
+                                                     float* __restrict__ stats) {
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int ngroups = D >> 3;
+  for (long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < M;
+       row += (long long)gridDim.x * warps_per_block) {
+    const float* xr = x + row * D;
+    float v[NG][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        load8_f32(xr + g * 8, v[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[i][j];
+      }
+    }
+    const float mean = warp_sum(s) / (float)D;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[i][j] - mean;
+          q += d * d;
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)D + eps);
+    if (lane == 0 && stats != nullptr) {
+      stats[row * 2] = mean;
+      stats[row * 2 + 1] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        float ga[8], be[8], o[8];
+        load8_f32(gamma + g * 8, ga);
+        load8_f32(beta + g * 8, be);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * ga[j] + be[j];
+        if (y16 != nullptr) store8_bf16(y16 + row * D + g * 8, o);
+        if (y32 != nullptr) store8_f32(y32 + row * D + g * 8, o);
+      }
+    }
+  }
+}
+
+template <int NG, bool DY_F32>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
+                                                     const float* __restrict__ gamma, const float* __restrict__ stats,
+                                                     const float* __restrict__ dx_add, int M, int D, float* __restrict__ dx,
+                                                     float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                     bf16* __restrict__ g16, float g_alpha, B2Dropout drop) {
+  extern __shared__ float sm[];  // [2][D] block partials of dgamma / dbeta
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int ngroups = D >> 3;
+  for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) sm[i] = 0.f;
+  __syncthreads();
+  float dg[NG][8], db[NG][8];
+#pragma unroll
+  for (int i = 0; i < NG; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f;
+
+  for (long long row = (long long)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < M;
+       row += (long long)gridDim.x * warps_per_block) {
+    const float mean = stats[row * 2], rstd = stats[row * 2 + 1];
+    float xh[NG][8], dyg[NG][8];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        float xv[8], dyv[8], ga[8];
+        load8_f32(x + row * D + g * 8, xv);
+        if (DY_F32)
+          load8_f32(reinterpret_cast<const float*>(dy_) + row * D + g * 8, dyv);
+        else
+          load8_bf16(reinterpret_cast<const bf16*>(dy_) + row * D + g * 8, dyv);
+        load8_f32(gamma + g * 8, ga);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xv[j] - mean) * rstd;
+          dyg[i][j] = dyv[j] * ga[j];
+          c1 += dyg[i][j];
+          c2 += dyg[i][j] * xh[i][j];
+          dg[i][j] += dyv[j] * xh[i][j];
+          db[i][j] += dyv[j];
+        }
+      }
+    }
+    c1 = warp_sum(c1) / (float)D;
+    c2 = warp_sum(c2) / (float)D;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (dyg[i][j] - c1 - xh[i][j] * c2);
+        if (dx_add != nullptr) {
+          float a[8];
+          load8_f32(dx_add + row * D + g * 8, a);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += a[j];
+        }
+        store8_f32(dx + row * D + g * 8, o);
+        if (g16 != nullptr) {
+          dropout8(drop, (unsigned long long)row * D + g * 8, o);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] *= g_alpha;
+          store8_bf16(g16 + row * D + g * 8, o);
+        }
+      }
+    }
+  }
+  // block reduction of the parameter gradients, then one atomic per column per block
+#pragma unroll
+  for (int i = 0; i < NG; ++i) {
+    const int g = lane + 32 * i;
+    if (g < ngroups) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&sm[g * 8 + j], dg[i][j]);
+        atomicAdd(&sm[D + g * 8 + j], db[i][j]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    atomicAdd(dgamma + i, sm[i]);
+    atomicAdd(dbeta + i, sm[D + i]);
+  }
+}
+
+}  // namespace
+
+extern "C" int b200slu_layernorm_fwd(const float* x, const float* gamma, const float* beta, int M, int D, float eps,
+                                     void* y_bf16, float* y_f32, float* stats, void* stream) {
+  B2_CHECK_ARG(M > 0 && D > 0 && D % 8 == 0 && D <= 2048, "layernorm: need D %% 8 == 0 and D <= 2048 (M=%d D=%d)", M, D);
+  B2_CHECK_ARG(y_bf16 != nullptr || y_f32 != nullptr, "layernorm: no output");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int grid = b2_grid_for((long long)M * 32, 256, 8);
+  B2_SCOPE(FAM_LN, st, 0, (double)M * D * (4.0 + (y_bf16 ? 2.0 : 0.0) + (y_f32 ? 4.0 : 0.0)));
+#define LN_F(NG) ln_fwd_kernel<NG><<<grid, 256, 0, st>>>(x, gamma, beta, M, D, eps, (bf16*)y_bf16, y_f32, stats)
+  if (D <= 256) LN_F(1);
+  else if (D <= 512) LN_F(2);
+  else if (D <= 1024) LN_F(4);
+  else LN_F(8);
+#undef LN_F
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float* x, const float* gamma, const float* stats,
+                                     const float* dx_add, int M, int D, float* dx, float* dgamma, float* dbeta,
+                                     void* g_bf16, float g_alpha, float drop_p, unsigned long long seed, unsigned int site,
+                                     void* stream) {
+  B2_CHECK_ARG(M > 0 && D > 0 && D % 8 == 0 && D <= 2048, "layernorm_bwd: need D %% 8 == 0 and D <= 2048 (M=%d D=%d)", M, D);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int grid = b2_grid_for((long long)M * 32, 256, 4);
+  B2Dropout drop{seed, site, drop_p};
+  const size_t smem = 2 * (size_t)D * sizeof(float);
+  B2_SCOPE(FAM_LN, st, 0,
+           (double)M * D * ((dy_is_f32 ? 4.0 : 2.0) + 4.0 + 4.0 + (dx_add ? 4.0 : 0.0) + (g_bf16 ? 2.0 : 0.0)));
+#define LN_B(NG)                                                                                                         \
+  do {                                                                                                                   \
+    if (dy_is_f32)                                                                                                       \
+      ln_bwd_kernel<NG, true><<<grid, 256, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta,             \
+                                                       (bf16*)g_bf16, g_alpha, drop);                                    \
+    else                                                                                                                 \
+      ln_bwd_kernel<NG, false><<<grid, 256, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta,            \
+                                                        (bf16*)g_bf16, g_alpha, drop);                                   \
+  } while (0)
+  if (D <= 256) LN_B(1);
+  else if (D <= 512) LN_B(2);
+  else if (D <= 1024) LN_B(4);
+  else LN_B(8);
+#undef LN_B
+  B2_LAUNCH_CHECK();
+  return 0;
+}

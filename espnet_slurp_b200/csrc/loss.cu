@@ -1,0 +1,135 @@
+// Label-smoothing KL loss + accuracy of the attention decoder, forward and gradient in one pass.
+//
+// Replaces LabelSmoothingLoss.forward (espnet/nets/pytorch_backend/transformer/label_smoothing_loss.py:41-63,
+// normalize_length=False) and th_accuracy (espnet/nets/pytorch_backend/nets_utils.py:299-320):
+//   true_dist = eps/(V-1) everywhere, 1-eps at the target; loss = sum KL(true || softmax(x)) over rows whose
+//   target != ignore, divided by the batch size by the caller; acc = mean(argmax == target) over those rows.
+// The reference makes 7 passes over (B*L, V) (clone, fill, scatter, log_softmax, kl_div, masked_fill, sum);
+// here each logit row is read once (it stays in L1/L2 for the second sweep) and its gradient
+// scale * (softmax - true_dist) is written once: algorithmic bytes 4*R*V read + (2|4)*R*V written.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) lsm_kernel(const float* __restrict__ x, long long ldv, int V, const int* __restrict__ tgt,
+                                                  int ignore, float eps, float gscale, float* __restrict__ loss_rows,
+                                                  int* __restrict__ correct_rows, float* __restrict__ g32, bf16* __restrict__ g16,
+                                                  long long ldg) {
+  __shared__ float red[32];
+  __shared__ int redi[32];
+  const long long r = blockIdx.x;
+  const int t = tgt[r];
+  const int Vp = (int)ldg;
+  if (t == ignore || t < 0 || t >= V) {
+    if (threadIdx.x == 0) {
+      loss_rows[r] = 0.f;
+      correct_rows[r] = -1;  // not counted
+    }
+    for (int v = threadIdx.x; v < Vp; v += blockDim.x) {
+      if (g32 != nullptr) g32[r * ldg + v] = 0.f;
+      if (g16 != nullptr) g16[r * ldg + v] = __float2bfloat16(0.f);
+    }
+    return;
+  }
+  const float* row = x + r * ldv;
+  float mx = -INFINITY, sumx = 0.f;
+  int arg = 0x7fffffff;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) {
+    const float xv = row[v];
+    sumx += xv;
+    if (xv > mx) {
+      mx = xv;
+      arg = v;
+    }
+  }
+  // block arg-max (lowest index among equal maxima, like torch.argmax on CPU)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > mx || (om == mx && oa < arg)) {
+      mx = om;
+      arg = oa;
+    }
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (lane == 0) {
+    red[w] = mx;
+    redi[w] = arg;
+  }
+  __syncthreads();
+  mx = red[0];
+  arg = redi[0];
+  for (int k = 1; k < nw; ++k)
+    if (red[k] > mx || (red[k] == mx && redi[k] < arg)) {
+      mx = red[k];
+      arg = redi[k];
+    }
+  __syncthreads();
+  sumx = block_sum(sumx, red);
+  float se = 0.f;
+  for (int v = threadIdx.x; v < V; v += blockDim.x) se += expf(row[v] - mx);
+  se = block_sum(se, red);
+  const float lse = mx + logf(se);
+  const float conf = 1.f - eps, low = eps / (float)(V - 1);
+  if (threadIdx.x == 0) {
+    const float lp_t = row[t] - lse;
+    const float sum_lp = sumx - (float)V * lse;
+    float loss = conf > 0.f ? conf * (logf(conf) - lp_t) : 0.f;
+    if (low > 0.f) loss += low * ((float)(V - 1) * logf(low) - (sum_lp - lp_t));
+    loss_rows[r] = loss;
+    correct_rows[r] = arg == t ? 1 : 0;
+  }
+  for (int v = threadIdx.x; v < Vp; v += blockDim.x) {
+    float g = 0.f;
+    if (v < V) g = gscale * (expf(row[v] - lse) - (v == t ? conf : low));
+    if (g32 != nullptr) g32[r * ldg + v] = g;
+    if (g16 != nullptr) g16[r * ldg + v] = __float2bfloat16(g);
+  }
+}
+
+// stats[0] = sum loss rows, stats[1] = #correct, stats[2] = #counted rows
+__global__ void lsm_finish_kernel(const float* __restrict__ loss_rows, const int* __restrict__ correct_rows, long long R,
+                                  float* __restrict__ stats) {
+  __shared__ float red[32];
+  float s = 0.f, c = 0.f, n = 0.f;
+  for (long long r = threadIdx.x; r < R; r += blockDim.x) {
+    s += loss_rows[r];
+    const int k = correct_rows[r];
+    if (k >= 0) {
+      n += 1.f;
+      c += (float)k;
+    }
+  }
+  s = block_sum(s, red);
+  c = block_sum(c, red);
+  n = block_sum(n, red);
+  if (threadIdx.x == 0) {
+    stats[0] = s;
+    stats[1] = c;
+    stats[2] = n;
+  }
+}
+
+}  // namespace
+
+extern "C" long long b200slu_lsm_workspace_size(long long R) { return R * 8; }
+
+extern "C" int b200slu_lsm_loss_fwd_bwd(const float* logits, long long ldv, long long R, int V, const int* targets, int ignore_id,
+                                        float smoothing, float grad_scale, void* workspace, float* stats3, float* grad_f32,
+                                        void* grad_bf16, long long ldg, void* stream) {
+  B2_CHECK_ARG(R > 0 && R < (1LL << 31) && V > 1 && ldv >= V, "lsm_loss: bad shape R=%lld V=%d", R, V);
+  B2_CHECK_ARG((grad_f32 == nullptr && grad_bf16 == nullptr) || ldg >= V, "lsm_loss: ldg < V");
+  cudaStream_t st = (cudaStream_t)stream;
+  float* loss_rows = (float*)workspace;
+  int* correct_rows = (int*)(loss_rows + R);
+  B2_SCOPE(FAM_LOSS, st, 0, (double)R * V * (4.0 + (grad_f32 ? 4.0 : 0.0) + (grad_bf16 ? 2.0 : 0.0)));
+  lsm_kernel<<<(unsigned)R, 256, 0, st>>>(logits, ldv, V, targets, ignore_id, smoothing, grad_scale, loss_rows, correct_rows,
+                                          grad_f32, (bf16*)grad_bf16, (grad_f32 || grad_bf16) ? ldg : 0);
+  B2_LAUNCH_CHECK();
+  lsm_finish_kernel<<<1, 256, 0, st>>>(loss_rows, correct_rows, R, stats3);
+  B2_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,236 @@
+// Masked softmax over attention scores with rel_shift folded into the score indexing, fwd + bwd.
+//
+// Replaces forward_attention (espnet/nets/pytorch_backend/transformer/attention.py:64-96) and the
+// rel_shift + add + scale of RelPositionMultiHeadedAttention.forward (:297-306, rel_shift :240-263)
+// / LegacyRelPositionMultiHeadedAttention.forward (:196-207, rel_shift :145-165):
+//   s[i,j] = (ac[i,j] + shift(bd)[i,j]) * scale ; masked keys (j >= len[b], or j > i when causal) get
+//   probability exactly 0 (the reference fills finfo.min, softmaxes and re-zeroes) ; dropout.
+//   latest: shift(bd)[i,j] = bd[i, T-1-i+j]                         (bd is T x (2T-1))
+//   legacy: j<=i -> bd[i, T-1-(i-j)] ; j==i+1 -> 0 ; j>i+1 -> bd[i+1, j-i-2]   (bd is T x T)
+// The (un-shifted) bd matrix is never re-laid-out: the shift is an index computation here, and in
+// the backward the gradient is scattered straight back into the un-shifted layout.
+// Score tensors are head-major [H, B, Tq, ld]; one warp owns one row; lanes own groups of 8 keys.
+#include "common.cuh"
+
+namespace {
+
+struct SmArgs {
+  int H, B, Tq, Tk;
+  long long ld_ac, ld_bd, ld_p;
+  int mode, causal;
+  float scale;
+  const int* lens;  // [B] valid keys per utterance
+};
+
+__device__ __forceinline__ float bd_term(const float* __restrict__ bd, long long hb, int i, int j, int T, long long ld_bd,
+                                         int mode) {
+  if (mode == B200SLU_RELPOS_LATEST) return bd[(hb * T + i) * ld_bd + (T - 1 - i + j)];
+  if (mode == B200SLU_RELPOS_LEGACY) {
+    if (j <= i) return bd[(hb * T + i) * ld_bd + (T - 1 - i + j)];
+    if (j == i + 1) return 0.f;
+    return bd[(hb * T + i + 1) * ld_bd + (j - i - 2)];
+  }
+  return 0.f;
+}
+
+template <int NG>
+__global__ void __launch_bounds__(256) softmax_fwd_kernel(const float* __restrict__ ac, const float* __restrict__ bd, SmArgs a,
+                                                          bf16* __restrict__ p, bf16* __restrict__ pd, B2Dropout drop) {
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const long long rows = (long long)a.H * a.B * a.Tq;
+  const int ngroups = (int)(a.ld_p >> 3);
+  for (long long r = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * wpb) {
+    const long long hb = r / a.Tq;
+    const int i = (int)(r - hb * a.Tq);
+    const int b = (int)(hb % a.B);
+    int nvalid = a.lens != nullptr ? a.lens[b] : a.Tk;
+    nvalid = min(nvalid, a.Tk);
+    if (a.causal) nvalid = min(nvalid, i + 1);
+    float s[NG][8];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int k = 0; k < NG; ++k) {
+      const int g = lane + 32 * k;
+      if (g < ngroups) {
+        float v[8];
+        load8_f32(ac + r * a.ld_ac + g * 8, v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int j = g * 8 + e;
+          if (j < nvalid) {
+            s[k][e] = (v[e] + bd_term(bd, hb, i, j, a.Tq, a.ld_bd, a.mode)) * a.scale;
+            mx = fmaxf(mx, s[k][e]);
+          } else {
+            s[k][e] = -INFINITY;
+          }
+        }
+      }
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < NG; ++k) {
+      const int g = lane + 32 * k;
+      if (g < ngroups) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          s[k][e] = (s[k][e] == -INFINITY) ? 0.f : __expf(s[k][e] - mx);
+          sum += s[k][e];
+        }
+      }
+    }
+    sum = warp_sum(sum);
+    const float inv = sum > 0.f ? 1.f / sum : 0.f;
+#pragma unroll
+    for (int k = 0; k < NG; ++k) {
+      const int g = lane + 32 * k;
+      if (g < ngroups) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s[k][e] *= inv;
+        store8_bf16(p + r * a.ld_p + g * 8, s[k]);
+        if (pd != p) {
+          dropout8(drop, (unsigned long long)r * a.ld_p + g * 8, s[k]);
+          store8_bf16(pd + r * a.ld_p + g * 8, s[k]);
+        }
+      }
+    }
+  }
+}
+
+template <int NG>
+__global__ void __launch_bounds__(256) softmax_bwd_kernel(const float* __restrict__ dpd, const bf16* __restrict__ p, SmArgs a,
+                                                          bf16* __restrict__ dac, bf16* __restrict__ dbd, B2Dropout drop) {
+  extern __shared__ float sm[];  // [warps][ld_p] staged d(score) row for the un-shift scatter
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const long long rows = (long long)a.H * a.B * a.Tq;
+  const int ngroups = (int)(a.ld_p >> 3);
+  float* row_sm = sm + (size_t)w * a.ld_p;
+  const int T = a.Tq;
+  for (long long r = (long long)blockIdx.x * wpb + w; r < rows; r += (long long)gridDim.x * wpb) {
+    const long long hb = r / a.Tq;
+    const int i = (int)(r - hb * a.Tq);
+    float pv[NG][8], dp[NG][8];
+    float dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < NG; ++k) {
+      const int g = lane + 32 * k;
+      if (g < ngroups) {
+        load8_bf16(p + r * a.ld_p + g * 8, pv[k]);
+        load8_f32(dpd + r * a.ld_p + g * 8, dp[k]);
+        dropout8(drop, (unsigned long long)r * a.ld_p + g * 8, dp[k]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          if (g * 8 + e >= a.Tk) dp[k][e] = 0.f;  // padding columns of dpd are unspecified
+          dot += dp[k][e] * pv[k][e];
+        }
+      }
+    }
+    dot = warp_sum(dot);
+#pragma unroll
+    for (int k = 0; k < NG; ++k) {
+      const int g = lane + 32 * k;
+      if (g < ngroups) {
+        float ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          ds[e] = pv[k][e] * (dp[k][e] - dot) * a.scale;
+          if (dbd != nullptr) row_sm[g * 8 + e] = ds[e];
+        }
+        store8_bf16(dac + r * a.ld_p + g * 8, ds);
+      }
+    }
+    if (dbd != nullptr) {
+      __syncwarp();
+      bf16* own = dbd + (hb * T + i) * a.ld_bd;
+      if (a.mode == B200SLU_RELPOS_LATEST) {
+        const int lo = T - 1 - i;  // column of j = 0
+        for (int n = lane; n < a.ld_bd; n += 32) {
+          const int j = n - lo;
+          own[n] = __float2bfloat16((j >= 0 && j < T) ? row_sm[j] : 0.f);
+        }
+      } else {  // legacy
+        const int lo = T - 1 - i;
+        for (int n = lane; n < a.ld_bd; n += 32) {
+          if (n >= lo && n < T) own[n] = __float2bfloat16(row_sm[n - lo]);           // j = n - lo <= i
+          else if (n >= T || i == 0) own[n] = __float2bfloat16(0.f);               // padding / never-read part of row 0
+        }
+        if (i + 1 < T) {
+          bf16* nxt = own + a.ld_bd;
+          for (int j = i + 2 + lane; j < T; j += 32) nxt[j - i - 2] = __float2bfloat16(row_sm[j]);
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+int check(const SmArgs& a) {
+  B2_CHECK_ARG(a.H > 0 && a.B > 0 && a.Tq > 0 && a.Tk > 0, "softmax: empty problem");
+  B2_CHECK_ARG(a.ld_p % 8 == 0 && a.ld_p >= a.Tk && a.ld_ac >= a.ld_p && a.ld_ac % 4 == 0,
+               "softmax: ld_p %% 8 == 0, ld_p >= Tk, ld_ac >= ld_p (ld_p=%lld ld_ac=%lld Tk=%d)", a.ld_p, a.ld_ac, a.Tk);
+  B2_CHECK_ARG(a.ld_p <= 2048, "softmax: at most 2048 keys per row (got ld %lld)", a.ld_p);
+  if (a.mode == B200SLU_RELPOS_LATEST)
+    B2_CHECK_ARG(a.Tq == a.Tk && a.ld_bd >= 2 * a.Tq - 1, "softmax: latest rel-pos needs Tq == Tk and ld_bd >= 2T-1");
+  else if (a.mode == B200SLU_RELPOS_LEGACY)
+    B2_CHECK_ARG(a.Tq == a.Tk && a.ld_bd >= a.Tq, "softmax: legacy rel-pos needs Tq == Tk and ld_bd >= T");
+  else
+    B2_CHECK_ARG(a.mode == B200SLU_RELPOS_NONE, "softmax: unknown rel-pos mode %d", a.mode);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200slu_softmax_fwd(const float* ac, long long ld_ac, const float* bd, long long ld_bd, const int* key_lens, int H,
+                                   int B, int Tq, int Tk, int relpos_mode, int causal, float scale, void* p, void* p_drop,
+                                   long long ld_p, float drop_p, unsigned long long seed, unsigned int site, void* stream) {
+  SmArgs a{H, B, Tq, Tk, ld_ac, ld_bd, ld_p, relpos_mode, causal, scale, key_lens};
+  B2_TRY(check(a));
+  B2_CHECK_ARG(p != nullptr && p_drop != nullptr && (drop_p > 0.f) == (p != p_drop),
+               "softmax_fwd: p_drop must alias p iff dropout is off");
+  B2_CHECK_ARG(relpos_mode == B200SLU_RELPOS_NONE || bd != nullptr, "softmax_fwd: bd missing");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long rows = (long long)H * B * Tq;
+  const int grid = b2_grid_for(rows * 32, 256, 8);
+  B2_SCOPE(FAM_ATTN, st, 0, (double)rows * Tk * (4.0 + (relpos_mode ? 4.0 : 0.0) + 2.0 + (drop_p > 0.f ? 2.0 : 0.0)));
+  B2Dropout drop{seed, site, drop_p};
+#define SM_F(NG) softmax_fwd_kernel<NG><<<grid, 256, 0, st>>>(ac, bd, a, (bf16*)p, (bf16*)p_drop, drop)
+  if (ld_p <= 256) SM_F(1);
+  else if (ld_p <= 512) SM_F(2);
+  else if (ld_p <= 1024) SM_F(4);
+  else SM_F(8);
+#undef SM_F
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_softmax_bwd(const float* dp_drop, const void* p, long long ld_p, int H, int B, int Tq, int Tk,
+                                   int relpos_mode, float scale, void* d_ac, void* d_bd, long long ld_bd, float drop_p,
+                                   unsigned long long seed, unsigned int site, void* stream) {
+  SmArgs a{H, B, Tq, Tk, ld_p, ld_bd, ld_p, relpos_mode, 0, scale, nullptr};
+  B2_TRY(check(a));
+  B2_CHECK_ARG(ld_bd % 8 == 0 || relpos_mode == B200SLU_RELPOS_NONE, "softmax_bwd: ld_bd %% 8 == 0");
+  B2_CHECK_ARG((relpos_mode == B200SLU_RELPOS_NONE) == (d_bd == nullptr), "softmax_bwd: d_bd must be given iff rel-pos mode");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long rows = (long long)H * B * Tq;
+  const int threads = 256;
+  const size_t smem = d_bd != nullptr ? (size_t)(threads / 32) * ld_p * sizeof(float) : 0;
+  const int grid = b2_grid_for(rows * 32, threads, 4);
+  B2_SCOPE(FAM_ATTN, st, 0, (double)rows * Tk * (4.0 + 2.0 + 2.0) + (d_bd ? 2.0 * rows * ld_bd : 0.0));
+  B2Dropout drop{seed, site, drop_p};
+#define SM_B(NG)                                                                                                  \
+  do {                                                                                                            \
+    static bool cfg = false;                                                                                      \
+    if (!cfg) {                                                                                                   \
+      B2_CUDA(cudaFuncSetAttribute(softmax_bwd_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536)); \
+      cfg = true;                                                                                                 \
+    }                                                                                                             \
+    softmax_bwd_kernel<NG><<<grid, threads, smem, st>>>(dp_drop, (const bf16*)p, a, (bf16*)d_ac, (bf16*)d_bd, drop); \
+  } while (0)
+  if (ld_p <= 256) SM_B(1);
+  else if (ld_p <= 512) SM_B(2);
+  else if (ld_p <= 1024) SM_B(4);
+  else SM_B(8);
+#undef SM_B
+  B2_LAUNCH_CHECK();
+  return 0;
+}

@@ -89,6 +89,114 @@ typedef struct {
 int b200slu_gemm_bf16(int trans, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb, void* C,
                       long long ldc, const b200slu_epilogue_t* epilogue, void* stream);
 
+/* General form: per-operand majorness and two batch levels (inner, outer), e.g. (head, utterance)
+ * for the attention contractions of attention.py:64-96,281-308 (torch.matmul call sites).
+ *   trans_a=0: A[M,K] row-major      trans_a=1: A[K,M] row-major
+ *   trans_b=0: B[N,K] row-major      trans_b=1: B[K,N] row-major
+ * Batch strides are in elements; 0 broadcasts the operand over that level.  In batched mode
+ * only bias / act / alpha / out_f32 / accumulate epilogue fields may be used. */
+typedef struct {
+  int trans_a, trans_b;
+  int M, N, K;
+  const void* A;
+  long long lda, a_stride_inner, a_stride_outer;
+  const void* B;
+  long long ldb, b_stride_inner, b_stride_outer;
+  void* C;
+  long long ldc, c_stride_inner, c_stride_outer;
+  int batch_inner, batch_outer;
+} b200slu_gemm_t;
+int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epilogue, void* stream);
+
+/* ---- K5: LayerNorm ---------------------------------------------------------------------------
+ * espnet/nets/pytorch_backend/transformer/layer_norm.py:12-38 at conformer/encoder_layer.py:97-149,
+ * espnet2/asr/encoder/conformer_encoder.py:362-363, transformer/decoder_layer.py:63-134.
+ * x f32 [M,D]; outputs bf16 and/or f32; stats f32 [M,2] = (mean, rstd). */
+int b200slu_layernorm_fwd(const float* x, const float* gamma, const float* beta, int M, int D, float eps, void* y_bf16,
+                          float* y_f32, float* stats, void* stream);
+/* dx = LN'(dy) (+ dx_add); dgamma/dbeta accumulated; optional g_bf16 = bf16(g_alpha * dropout(dx)),
+ * the branch gradient the next dgrad GEMM consumes (encoder_layer.py:101,129,138,144). */
+int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float* x, const float* gamma, const float* stats,
+                          const float* dx_add, int M, int D, float* dx, float* dgamma_accum, float* dbeta_accum, void* g_bf16,
+                          float g_alpha, float drop_p, unsigned long long seed, unsigned int site, void* stream);
+
+/* ---- small helpers around the GEMMs ---------------------------------------------------------- */
+/* y = bf16(alpha * dropout(x)) (weight casts; embedding.py:244 dropout on pos_emb) */
+int b200slu_cast_bf16(const float* x, void* y, long long n, float alpha, float drop_p, unsigned long long seed,
+                      unsigned int site, void* stream);
+/* out[n] += sum_m dy[m,n]: bias gradients of every nn.Linear / Conv1d(k=1) */
+int b200slu_colsum_bf16(const void* dy, int M, int N, long long ld, float* out_accum, void* stream);
+/* q_u = q + pos_bias_u, q_v = q + pos_bias_v (attention.py:289-291); q = first d columns of rows of stride ldq */
+int b200slu_pos_bias_fwd(const void* q, long long ldq, const float* pos_bias_u, const float* pos_bias_v, int M, int d,
+                         void* q_u, void* q_v, void* stream);
+int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
+                         float* dv_accum, void* stream);
+/* decoder input: x = dropout(emb[tok] * scale + pe[pos]) (transformer_decoder.py:72-77, embedding.py:82-94) */
+int b200slu_embed_fwd(const float* emb, const int* tokens, const float* pe, int R, int L, int d, float scale, float* x,
+                      float drop_p, unsigned long long seed, unsigned int site, void* stream);
+int b200slu_embed_bwd(const float* dx, const int* tokens, int R, int d, float scale, float* demb_accum, float drop_p,
+                      unsigned long long seed, unsigned int site, void* stream);
+
+/* ---- K1/K10: masked softmax with rel_shift folded into the indexing ---------------------------
+ * attention.py:64-96 (forward_attention), :240-263 / :145-165 (rel_shift latest / legacy), :297-306.
+ * Score tensors are head-major [H, B, Tq, ld]; ac f32 = (q+u)k^T, bd f32 = un-shifted (q+v)p^T.
+ * p = probabilities (bf16), p_drop = dropout(p) (must alias p iff drop_p == 0). */
+int b200slu_softmax_fwd(const float* ac, long long ld_ac, const float* bd, long long ld_bd, const int* key_lens, int H, int B,
+                        int Tq, int Tk, int relpos_mode, int causal, float scale, void* p, void* p_drop, long long ld_p,
+                        float drop_p, unsigned long long seed, unsigned int site, void* stream);
+/* d_ac (bf16 [H,B,Tq,ld_p]) and, for rel-pos modes, d_bd (bf16, un-shifted layout [H,B,T,ld_bd]) */
+int b200slu_softmax_bwd(const float* dp_drop, const void* p, long long ld_p, int H, int B, int Tq, int Tk, int relpos_mode,
+                        float scale, void* d_ac, void* d_bd, long long ld_bd, float drop_p, unsigned long long seed,
+                        unsigned int site, void* stream);
+/* rel_shift source index (bit-exact index test): returns row * 65536 + col + 1 of the un-shifted matrix that lands at
+ * out[i, j], or 0 for the literal zero of the legacy variant. */
+long long b200slu_rel_shift_index(int i, int j, int T, int mode);
+
+/* ---- K4: ConvolutionModule middle (convolution.py:67-79), channels-last bf16 ------------------ */
+int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const float* bias, int B, int T, int C, int K, void* out,
+                           float* bn_sums_zeroed /* [2C] */, void* stream);
+int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
+                           float* dw_accum, float* dbias_accum, void* stream);
+int b200slu_bn_finalize(const float* sums, int C, long long n, float eps, float momentum, float* mean_rstd /* [2C] */,
+                        float* running_mean, float* running_var, long long* num_batches_tracked, void* stream);
+int b200slu_bn_swish_fwd(const void* x, const float* mean_rstd, const float* gamma, const float* beta, long long M, int C,
+                         void* y, void* stream);
+int b200slu_bn_swish_bwd(const void* dy, const void* x, const float* mean_rstd, const float* gamma, const float* beta,
+                         long long M, int C, float* sums2_zeroed /* [2C] */, void* dx, float* dgamma_accum, float* dbeta_accum,
+                         void* stream);
+
+/* ---- K3: Conv2dSubsampling (subsampling.py:53-87) ---------------------------------------------- */
+int b200slu_conv1_fwd(const float* x, const float* w, const float* bias, int B, int Tin, int F, int C, void* h1, void* stream);
+int b200slu_conv1_bwd(const void* dh1, const float* x, int B, int Tin, int F, int C, float* dw_accum, float* db_accum,
+                      void* stream);
+int b200slu_im2col3x3s2(const void* h1, int B, int T1, int F1, int C, void* col, void* stream);
+int b200slu_col2im3x3s2_relu(const void* dcol, const void* h1, int B, int T1, int F1, int C, void* dh1, void* stream);
+
+/* ---- K6: CTC (espnet2/asr/ctc.py:52-63,82-95; lattice espnet/nets/pytorch_backend/gtn_ctc.py:26-36) -----
+ * logits f32 [B,T,ldv] (log_softmax fused); labels int32 [B,Lmax]; all lengths int32 on the device. */
+long long b200slu_ctc_workspace_size(int B, int T, int Lmax);
+int b200slu_ctc_fwd(const float* logits, long long ldv, int B, int T, int V, const int* hlens, const int* labels, int Lmax,
+                    const int* label_lens, int blank, void* workspace, float* loss_per_utt, float* loss_sum, void* stream);
+int b200slu_ctc_bwd(const float* logits, long long ldv, int B, int T, int V, const int* hlens, const int* labels, int Lmax,
+                    const int* label_lens, int blank, const void* workspace, float scale, float* grad_f32, void* grad_bf16,
+                    long long ldg, void* stream);
+
+/* ---- K9: label-smoothing loss + accuracy (label_smoothing_loss.py:41-63, nets_utils.py:299-320) -------
+ * stats3 = {sum of row losses, #correct, #counted rows}; grad = grad_scale * (softmax - true_dist). */
+long long b200slu_lsm_workspace_size(long long R);
+int b200slu_lsm_loss_fwd_bwd(const float* logits, long long ldv, long long R, int V, const int* targets, int ignore_id,
+                             float smoothing, float grad_scale, void* workspace, float* stats3, float* grad_f32, void* grad_bf16,
+                             long long ldg, void* stream);
+
+/* ---- K7/K8: front-end (default.py:82-117, stft.py:83-170, log_mel.py:62-79; specaug.py:89-96,
+ * time_warp.py:9-46, mask_along_axis.py:8-68, utterance_mvn.py:45-88) ------------------------------ */
+int b200slu_logmel_fwd(const float* wav, long long ldw, int B, int N, const int* lens, const float* melmat, int n_fft, int hop,
+                       int n_mels, float* feats, int* feat_lens, void* stream);
+/* masks are int32 [B, n, 2] = (pos, len); warp_center < 0 (or NULL) = no time warp for that utterance */
+int b200slu_specaug_mvn_fwd(const float* x, int B, int T, int F, const int* lens, const int* warp_center, const int* warp_warped,
+                            const int* freq_masks, int n_freq_masks, const int* time_masks, int n_time_masks, int do_mvn,
+                            float* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
