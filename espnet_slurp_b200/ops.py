@@ -1,49 +1,46 @@
-"""Thin per-kernel Python wrappers over the C ABI (used by the drop-in modules and tests).
+"""Per-kernel Python wrappers over the C ABI of libb200slu (include/b200slu.h).
 
-Every function takes/returns CUDA torch tensors; torch only owns memory and streams.
+Every function takes / returns CUDA torch tensors; torch only owns memory and streams.  There is
+no CPU or eager-PyTorch fallback: a missing library or a non-zero status raises.
+
+Conventions shared with the step orchestration (``espnet_slurp_b200.step``):
+  * activations fed to GEMMs are bf16, the residual stream / statistics / losses are fp32;
+  * ``drop`` is ``None`` or ``(p, seed, site)``: counter-based Philox dropout, regenerated (never
+    stored) in the backward from the same triple;
+  * attention score tensors are head-major ``[H, B, Tq, ld]`` with ``ld`` = keys rounded up to 8.
 """
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional
+from typing import Optional, Tuple
 
 import torch
 
 from . import _lib
-from ._lib import Epilogue, check, ptr, stream_ptr
+from ._lib import Epilogue, GemmDesc, check, ptr, stream_ptr
 
 ACT = {None: 0, "none": 0, "swish": 1, "relu": 2}
+RELPOS = {None: 0, "none": 0, "latest": 1, "legacy": 2}
+Drop = Optional[Tuple[float, int, int]]
 
 
-def gemm(a: torch.Tensor, b: torch.Tensor, *, trans: bool = False, bias: Optional[torch.Tensor] = None,
-         act: Optional[str] = None, alpha: float = 1.0, residual: Optional[torch.Tensor] = None,
-         act_grad_input: Optional[torch.Tensor] = None, act_grad: Optional[str] = None,
-         pre_act_out: bool = False, out_dtype=torch.bfloat16, out: Optional[torch.Tensor] = None,
-         accumulate: bool = False, dropout_p: float = 0.0, seed: int = 0, site: int = 0):
-    """trans=False: a[M,K] @ b[N,K]^T ; trans=True: a[K,M]^T @ b[K,N].  bf16 in, fused epilogue."""
-    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_cuda
-    assert a.stride(-1) == 1 and b.stride(-1) == 1
-    if not trans:
-        M, K = a.shape
-        N = b.shape[0]
-        assert b.shape[1] == K
-    else:
-        K, M = a.shape
-        N = b.shape[1]
-        assert b.shape[0] == K
-    if out is None:
-        out = torch.empty(M, N, device=a.device, dtype=out_dtype)
+def _drop(drop: Drop):
+    if drop is None or drop[0] <= 0.0:
+        return 0.0, 0, 0
+    return float(drop[0]), int(drop[1]), int(drop[2])
+
+
+def round8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre_act_out, out, accumulate, drop):
     ep = Epilogue()
-    ep.bias = bias.data_ptr() if bias is not None else None
+    ep.bias = ptr(bias)
     ep.act = ACT[act]
-    pre = None
-    if pre_act_out:
-        pre = torch.empty(M, N, device=a.device, dtype=torch.bfloat16)
-        ep.pre_act_out = pre.data_ptr()
+    ep.pre_act_out = ptr(pre_act_out)
     ep.alpha = alpha
-    ep.dropout_p = dropout_p
-    ep.dropout_seed = seed
-    ep.dropout_site = site
+    ep.dropout_p, ep.dropout_seed, ep.dropout_site = _drop(drop)
     if act_grad_input is not None:
         ep.act_grad_input = act_grad_input.data_ptr()
         ep.ld_act_grad_input = act_grad_input.stride(0)
@@ -54,8 +51,335 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans: bool = False, bias: Optiona
         ep.ld_residual = residual.stride(0)
     ep.out_f32 = 1 if out.dtype == torch.float32 else 0
     ep.accumulate = 1 if accumulate else 0
-    rc = _lib.lib().b200slu_gemm_bf16(C.c_int(1 if trans else 0), M, N, K, ptr(a), C.c_longlong(a.stride(0)), ptr(b),
-                                      C.c_longlong(b.stride(0)), ptr(out), C.c_longlong(out.stride(0)), C.byref(ep),
-                                      stream_ptr())
-    check(rc, "gemm_bf16")
-    return (out, pre) if pre_act_out else out
+    return ep
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, trans: bool = False, trans_a: Optional[bool] = None,
+         trans_b: Optional[bool] = None, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
+         alpha: float = 1.0, residual: Optional[torch.Tensor] = None, act_grad_input: Optional[torch.Tensor] = None,
+         act_grad: Optional[str] = None, pre_act_out=False, out_dtype=torch.bfloat16,
+         out: Optional[torch.Tensor] = None, accumulate: bool = False, drop: Drop = None,
+         dropout_p: float = 0.0, seed: int = 0, site: int = 0):
+    """C[M,N] = op(A) op(B)^T with the fused epilogue of b200slu_epilogue_t.
+
+    trans_a=False: a is [M,K]; True: a is [K,M].  trans_b=False: b is [N,K]; True: b is [K,N].
+    (``trans`` sets both.)  ``pre_act_out`` may be True (allocate) or a bf16 [M,N] tensor.
+    """
+    ta = trans if trans_a is None else trans_a
+    tb = trans if trans_b is None else trans_b
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_cuda
+    assert a.stride(-1) == 1 and b.stride(-1) == 1
+    (M, K) = (a.shape[1], a.shape[0]) if ta else (a.shape[0], a.shape[1])
+    (N, Kb) = (b.shape[1], b.shape[0]) if tb else (b.shape[0], b.shape[1])
+    assert K == Kb, (a.shape, b.shape, ta, tb)
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=out_dtype)
+    pre = None
+    if pre_act_out is True:
+        pre = torch.empty(M, N, device=a.device, dtype=torch.bfloat16)
+    elif pre_act_out is not False and pre_act_out is not None:
+        pre = pre_act_out
+    if pre is not None:
+        assert pre.stride(0) == out.stride(0)
+    if drop is None and dropout_p > 0.0:
+        drop = (dropout_p, seed, site)
+    ep = _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre, out, accumulate, drop)
+    g = GemmDesc()
+    g.trans_a, g.trans_b = int(ta), int(tb)
+    g.M, g.N, g.K = M, N, K
+    g.A, g.lda = a.data_ptr(), a.stride(0)
+    g.B, g.ldb = b.data_ptr(), b.stride(0)
+    g.C, g.ldc = out.data_ptr(), out.stride(0)
+    g.batch_inner = g.batch_outer = 1
+    check(_lib.lib().b200slu_gemm_bf16_ex(C.addressof(g), C.addressof(ep), stream_ptr()), "gemm_bf16")
+    return (out, pre) if pre_act_out is True else out
+
+
+def _bgemm(ta, tb, M, N, K, A, lda, a_si, a_so, Bm, ldb, b_si, b_so, Cm, ldc, c_si, c_so, nbi, nbo, accumulate=False):
+    g = GemmDesc()
+    g.trans_a, g.trans_b = int(ta), int(tb)
+    g.M, g.N, g.K = M, N, K
+    g.A, g.lda, g.a_stride_inner, g.a_stride_outer = A.data_ptr(), lda, a_si, a_so
+    g.B, g.ldb, g.b_stride_inner, g.b_stride_outer = Bm.data_ptr(), ldb, b_si, b_so
+    g.C, g.ldc, g.c_stride_inner, g.c_stride_outer = Cm.data_ptr(), ldc, c_si, c_so
+    g.batch_inner, g.batch_outer = nbi, nbo
+    ep = Epilogue()
+    ep.alpha = 1.0
+    ep.out_f32 = 1 if Cm.dtype == torch.float32 else 0
+    ep.accumulate = 1 if accumulate else 0
+    check(_lib.lib().b200slu_gemm_bf16_ex(C.addressof(g), C.addressof(ep), stream_ptr()), "gemm_bf16_ex")
+
+
+# ---- the four batched attention contractions (x, y are [rows, H*dk] bf16 views with row stride ld) ------------
+def attn_f1(x, y, B: int, Tx: int, Ty: int, H: int, y_bcast: bool = False):
+    """out[h,b,i,j] = sum_c x[b*Tx+i, h*dk+c] * y[b*Ty+j, h*dk+c]  -> f32 [H,B,Tx,round8(Ty)]
+    (y_bcast: y is [Ty, H*dk], shared by all utterances)."""
+    dk = x.shape[1] // H
+    ld = round8(Ty)
+    out = torch.empty(H, B, Tx, ld, device=x.device, dtype=torch.float32)
+    _bgemm(0, 0, Tx, Ty, dk, x, x.stride(0), dk, Tx * x.stride(0), y, y.stride(0), dk, 0 if y_bcast else Ty * y.stride(0),
+           out, ld, B * Tx * ld, Tx * ld, H, B)
+    return out
+
+
+def attn_f2(s, y, B: int, Tq: int, Tk: int, H: int, out=None, y_bcast: bool = False):
+    """out[b*Tq+i, h*dk+c] = sum_j s[h,b,i,j] * y[b*Tk+j, h*dk+c]  -> bf16 [B*Tq, H*dk] (or into ``out`` view)."""
+    dk = y.shape[1] // H
+    ld = s.shape[-1]
+    if out is None:
+        out = torch.empty(B * Tq, H * dk, device=s.device, dtype=torch.bfloat16)
+    _bgemm(0, 1, Tq, dk, Tk, s, ld, B * Tq * ld, Tq * ld, y, y.stride(0), dk, 0 if y_bcast else Tk * y.stride(0),
+           out, out.stride(0), dk, Tq * out.stride(0), H, B)
+    return out
+
+
+def attn_f3(s, x, B: int, Tq: int, Tk: int, H: int, out=None):
+    """out[b*Tk+j, h*dk+c] = sum_i s[h,b,i,j] * x[b*Tq+i, h*dk+c]  -> bf16 [B*Tk, H*dk] (or into ``out`` view)."""
+    dk = x.shape[1] // H
+    ld = s.shape[-1]
+    if out is None:
+        out = torch.empty(B * Tk, H * dk, device=s.device, dtype=torch.bfloat16)
+    _bgemm(1, 1, Tk, dk, Tq, s, ld, B * Tq * ld, Tq * ld, x, x.stride(0), dk, Tq * x.stride(0),
+           out, out.stride(0), dk, Tk * out.stride(0), H, B)
+    return out
+
+
+def attn_f4(s, x, B: int, T: int, P: int, H: int, out):
+    """out[n, h*dk+c] += sum_{b,i} s[h,b,i,n] * x[b*T+i, h*dk+c]  (f32 [P, H*dk], accumulated; split-K atomics)."""
+    dk = x.shape[1] // H
+    ld = s.shape[-1]
+    _bgemm(1, 1, P, dk, B * T, s, ld, B * T * ld, 0, x, x.stride(0), dk, 0, out, out.stride(0), dk, 0, H, 1,
+           accumulate=True)
+    return out
+
+
+# ---- LayerNorm ------------------------------------------------------------------------------------------------
+def layernorm_fwd(x, gamma, beta, eps: float = 1e-12, want_bf16: bool = True, want_f32: bool = False):
+    M, D = x.shape
+    y16 = torch.empty(M, D, device=x.device, dtype=torch.bfloat16) if want_bf16 else None
+    y32 = torch.empty(M, D, device=x.device, dtype=torch.float32) if want_f32 else None
+    stats = torch.empty(M, 2, device=x.device, dtype=torch.float32)
+    check(_lib.lib().b200slu_layernorm_fwd(ptr(x), ptr(gamma), ptr(beta), M, D, eps, ptr(y16), ptr(y32), ptr(stats),
+                                           stream_ptr()), "layernorm_fwd")
+    return y16, y32, stats
+
+
+def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g: bool = False, g_alpha: float = 1.0,
+                  g_drop: Drop = None):
+    M, D = x.shape
+    dx = torch.empty(M, D, device=x.device, dtype=torch.float32)
+    g16 = torch.empty(M, D, device=x.device, dtype=torch.bfloat16) if want_g else None
+    p, seed, site = _drop(g_drop)
+    check(_lib.lib().b200slu_layernorm_bwd(ptr(dy), int(dy.dtype == torch.float32), ptr(x), ptr(gamma), ptr(stats),
+                                           ptr(dx_add), M, D, ptr(dx), ptr(dgamma), ptr(dbeta), ptr(g16), g_alpha, p, seed,
+                                           site, stream_ptr()), "layernorm_bwd")
+    return dx, g16
+
+
+# ---- small helpers ----------------------------------------------------------------------------------------------
+def cast_bf16(x, alpha: float = 1.0, drop: Drop = None, out=None):
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    p, seed, site = _drop(drop)
+    check(_lib.lib().b200slu_cast_bf16(ptr(x), ptr(out), x.numel(), alpha, p, seed, site, stream_ptr()), "cast_bf16")
+    return out
+
+
+def colsum(dy, out_accum, n: Optional[int] = None):
+    M = dy.shape[0]
+    N = dy.shape[1] if n is None else n
+    check(_lib.lib().b200slu_colsum_bf16(ptr(dy), M, N, dy.stride(0), ptr(out_accum), stream_ptr()), "colsum")
+    return out_accum
+
+
+def pos_bias_fwd(q, u, v):
+    M, d = q.shape
+    qu = torch.empty(M, d, device=q.device, dtype=torch.bfloat16)
+    qv = torch.empty(M, d, device=q.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_pos_bias_fwd(ptr(q), q.stride(0), ptr(u), ptr(v), M, d, ptr(qu), ptr(qv), stream_ptr()),
+          "pos_bias_fwd")
+    return qu, qv
+
+
+def pos_bias_bwd(dqu, dqv, dq_out, du, dv):
+    M, d = dqu.shape
+    check(_lib.lib().b200slu_pos_bias_bwd(ptr(dqu), ptr(dqv), M, d, ptr(dq_out), dq_out.stride(0), ptr(du), ptr(dv),
+                                          stream_ptr()), "pos_bias_bwd")
+
+
+def embed_fwd(emb, tokens, pe, L: int, scale: float, drop: Drop = None):
+    R, d = tokens.numel(), emb.shape[1]
+    x = torch.empty(R, d, device=emb.device, dtype=torch.float32)
+    p, seed, site = _drop(drop)
+    check(_lib.lib().b200slu_embed_fwd(ptr(emb), ptr(tokens), ptr(pe), R, L, d, scale, ptr(x), p, seed, site, stream_ptr()),
+          "embed_fwd")
+    return x
+
+
+def embed_bwd(dx, tokens, scale: float, demb, drop: Drop = None):
+    R, d = dx.shape
+    p, seed, site = _drop(drop)
+    check(_lib.lib().b200slu_embed_bwd(ptr(dx), ptr(tokens), R, d, scale, ptr(demb), p, seed, site, stream_ptr()),
+          "embed_bwd")
+
+
+# ---- softmax ------------------------------------------------------------------------------------------------------
+def softmax_fwd(ac, bd, key_lens, Tk: int, mode: str, causal: bool, scale: float, drop: Drop = None):
+    H, B, Tq, ld = ac.shape
+    p = torch.empty(H, B, Tq, ld, device=ac.device, dtype=torch.bfloat16)
+    dp, seed, site = _drop(drop)
+    pd = torch.empty_like(p) if dp > 0.0 else p
+    check(_lib.lib().b200slu_softmax_fwd(ptr(ac), ld, ptr(bd), bd.shape[-1] if bd is not None else 0, ptr(key_lens), H, B, Tq,
+                                         Tk, RELPOS[mode], int(causal), scale, ptr(p), ptr(pd), ld, dp, seed, site,
+                                         stream_ptr()), "softmax_fwd")
+    return p, pd
+
+
+def softmax_bwd(dpd, p, Tk: int, mode: str, scale: float, ld_bd: int = 0, drop: Drop = None):
+    H, B, Tq, ld = p.shape
+    dac = torch.empty(H, B, Tq, ld, device=p.device, dtype=torch.bfloat16)
+    dbd = torch.empty(H, B, Tq, ld_bd, device=p.device, dtype=torch.bfloat16) if RELPOS[mode] else None
+    dp, seed, site = _drop(drop)
+    check(_lib.lib().b200slu_softmax_bwd(ptr(dpd), ptr(p), ld, H, B, Tq, Tk, RELPOS[mode], scale, ptr(dac), ptr(dbd), ld_bd,
+                                         dp, seed, site, stream_ptr()), "softmax_bwd")
+    return dac, dbd
+
+
+# ---- conv module --------------------------------------------------------------------------------------------------
+def glu_dwconv_fwd(pw1, w, bias, B: int, T: int, K: int):
+    Cc = pw1.shape[1] // 2
+    out = torch.empty(B * T, Cc, device=pw1.device, dtype=torch.bfloat16)
+    sums = torch.zeros(2 * Cc, device=pw1.device, dtype=torch.float32)
+    check(_lib.lib().b200slu_glu_dwconv_fwd(ptr(pw1), ptr(w), ptr(bias), B, T, Cc, K, ptr(out), ptr(sums), stream_ptr()),
+          "glu_dwconv_fwd")
+    return out, sums
+
+
+def glu_dwconv_bwd(d_out, pw1, w, B: int, T: int, K: int, dw, dbias):
+    Cc = pw1.shape[1] // 2
+    d_pw1 = torch.empty(B * T, 2 * Cc, device=pw1.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_glu_dwconv_bwd(ptr(d_out), ptr(pw1), ptr(w), B, T, Cc, K, ptr(d_pw1), ptr(dw), ptr(dbias),
+                                            stream_ptr()), "glu_dwconv_bwd")
+    return d_pw1
+
+
+def bn_finalize(sums, n: int, eps: float, momentum: float, running_mean=None, running_var=None, num_batches=None):
+    Cc = sums.numel() // 2
+    mr = torch.empty(2 * Cc, device=sums.device, dtype=torch.float32)
+    check(_lib.lib().b200slu_bn_finalize(ptr(sums), Cc, n, eps, momentum, ptr(mr), ptr(running_mean), ptr(running_var),
+                                         ptr(num_batches), stream_ptr()), "bn_finalize")
+    return mr
+
+
+def bn_swish_fwd(x, mean_rstd, gamma, beta):
+    M, Cc = x.shape
+    y = torch.empty(M, Cc, device=x.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_bn_swish_fwd(ptr(x), ptr(mean_rstd), ptr(gamma), ptr(beta), M, Cc, ptr(y), stream_ptr()),
+          "bn_swish_fwd")
+    return y
+
+
+def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta):
+    M, Cc = x.shape
+    dx = torch.empty(M, Cc, device=x.device, dtype=torch.bfloat16)
+    sums2 = torch.zeros(2 * Cc, device=x.device, dtype=torch.float32)
+    check(_lib.lib().b200slu_bn_swish_bwd(ptr(dy), ptr(x), ptr(mean_rstd), ptr(gamma), ptr(beta), M, Cc, ptr(sums2), ptr(dx),
+                                          ptr(dgamma), ptr(dbeta), stream_ptr()), "bn_swish_bwd")
+    return dx
+
+
+# ---- subsampling --------------------------------------------------------------------------------------------------
+def conv1_fwd(x, w, bias):
+    B, Tin, F = x.shape
+    Cc = w.shape[0]
+    T1, F1 = (Tin - 3) // 2 + 1, (F - 3) // 2 + 1
+    h1 = torch.empty(B, T1, F1, Cc, device=x.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_conv1_fwd(ptr(x), ptr(w), ptr(bias), B, Tin, F, Cc, ptr(h1), stream_ptr()), "conv1_fwd")
+    return h1
+
+
+def conv1_bwd(dh1, x, dw, db):
+    B, Tin, F = x.shape
+    Cc = dh1.shape[-1]
+    check(_lib.lib().b200slu_conv1_bwd(ptr(dh1), ptr(x), B, Tin, F, Cc, ptr(dw), ptr(db), stream_ptr()), "conv1_bwd")
+
+
+def im2col(h1):
+    B, T1, F1, Cc = h1.shape
+    T2, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
+    col = torch.empty(B * T2 * F2, 9 * Cc, device=h1.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_im2col3x3s2(ptr(h1), B, T1, F1, Cc, ptr(col), stream_ptr()), "im2col")
+    return col
+
+
+def col2im_relu(dcol, h1):
+    B, T1, F1, Cc = h1.shape
+    dh1 = torch.empty_like(h1)
+    check(_lib.lib().b200slu_col2im3x3s2_relu(ptr(dcol), ptr(h1), B, T1, F1, Cc, ptr(dh1), stream_ptr()), "col2im")
+    return dh1
+
+
+# ---- losses -------------------------------------------------------------------------------------------------------
+def ctc_fwd(logits, V: int, hlens, labels, label_lens, blank: int = 0):
+    """logits f32 [B,T,ldv]; returns (loss_per_utt [B], loss_sum [1], workspace)."""
+    B, T, ldv = logits.shape
+    Lmax = labels.shape[1]
+    ws = torch.empty(_lib.lib().b200slu_ctc_workspace_size(B, T, Lmax), device=logits.device, dtype=torch.uint8)
+    loss = torch.empty(B, device=logits.device, dtype=torch.float32)
+    loss_sum = torch.empty(1, device=logits.device, dtype=torch.float32)
+    check(_lib.lib().b200slu_ctc_fwd(ptr(logits), ldv, B, T, V, ptr(hlens), ptr(labels), Lmax, ptr(label_lens), blank, ptr(ws),
+                                     ptr(loss), ptr(loss_sum), stream_ptr()), "ctc_fwd")
+    return loss, loss_sum, ws
+
+
+def ctc_bwd(logits, V: int, hlens, labels, label_lens, ws, scale: float, blank: int = 0, want_f32: bool = False,
+            want_bf16: bool = True):
+    B, T, ldv = logits.shape
+    Lmax = labels.shape[1]
+    ldg = round8(V)
+    g32 = torch.empty(B, T, ldg, device=logits.device, dtype=torch.float32) if want_f32 else None
+    g16 = torch.empty(B, T, ldg, device=logits.device, dtype=torch.bfloat16) if want_bf16 else None
+    check(_lib.lib().b200slu_ctc_bwd(ptr(logits), ldv, B, T, V, ptr(hlens), ptr(labels), Lmax, ptr(label_lens), blank, ptr(ws),
+                                     scale, ptr(g32), ptr(g16), ldg, stream_ptr()), "ctc_bwd")
+    return g32, g16
+
+
+def lsm_loss(logits, V: int, targets, smoothing: float, grad_scale: float, ignore: int = -1, want_f32: bool = False,
+             want_bf16: bool = True):
+    """logits f32 [R,ldv]; returns (stats3 = [sum loss, #correct, #rows], grad_f32, grad_bf16)."""
+    R, ldv = logits.shape
+    ldg = round8(V)
+    ws = torch.empty(_lib.lib().b200slu_lsm_workspace_size(R), device=logits.device, dtype=torch.uint8)
+    stats = torch.empty(3, device=logits.device, dtype=torch.float32)
+    g32 = torch.empty(R, ldg, device=logits.device, dtype=torch.float32) if want_f32 else None
+    g16 = torch.empty(R, ldg, device=logits.device, dtype=torch.bfloat16) if want_bf16 else None
+    check(_lib.lib().b200slu_lsm_loss_fwd_bwd(ptr(logits), ldv, R, V, ptr(targets), ignore, smoothing, grad_scale, ptr(ws),
+                                              ptr(stats), ptr(g32), ptr(g16), ldg, stream_ptr()), "lsm_loss")
+    return stats, g32, g16
+
+
+# ---- front-end ----------------------------------------------------------------------------------------------------
+def logmel(wav, lens, melmat, n_fft: int = 512, hop: int = 128):
+    B, N = wav.shape
+    T = N // hop + 1
+    n_mels = melmat.shape[1]
+    feats = torch.empty(B, T, n_mels, device=wav.device, dtype=torch.float32)
+    flens = torch.empty(B, device=wav.device, dtype=torch.int32)
+    check(_lib.lib().b200slu_logmel_fwd(ptr(wav), wav.stride(0), B, N, ptr(lens), ptr(melmat), n_fft, hop, n_mels, ptr(feats),
+                                        ptr(flens), stream_ptr()), "logmel")
+    return feats, flens
+
+
+def specaug_mvn(x, lens, center=None, warped=None, fmask=None, tmask=None, do_mvn: bool = True):
+    B, T, F = x.shape
+    y = torch.empty_like(x)
+    nf = fmask.shape[1] if fmask is not None else 0
+    nt = tmask.shape[1] if tmask is not None else 0
+    check(_lib.lib().b200slu_specaug_mvn_fwd(ptr(x), B, T, F, ptr(lens), ptr(center), ptr(warped), ptr(fmask), nf, ptr(tmask),
+                                             nt, int(do_mvn), ptr(y), stream_ptr()), "specaug_mvn")
+    return y
+
+
+def rel_shift_index(i: int, j: int, T: int, mode: str) -> int:
+    return _lib.lib().b200slu_rel_shift_index(i, j, T, RELPOS[mode])

@@ -1,0 +1,510 @@
+"""Forward + hand-written backward of the Conformer CTC/attention train step over the libb200slu kernels.
+
+This is the host-side orchestration only: every arithmetic step is one call into ``ops`` (= one or two
+CUDA kernels behind the C ABI).  There is no autograd inside; the drop-in modules (``modules.py``) expose
+each sub-network to PyTorch as ONE ``torch.autograd.Function`` whose backward calls the ``*_bwd`` functions
+here.  No host<->device synchronisation happens anywhere in this file (lengths stay on the device), so
+a whole step can be captured in a CUDA graph.
+
+Reference being reproduced (paths relative to the reference root):
+  EncoderLayer.forward            espnet/nets/pytorch_backend/conformer/encoder_layer.py:76-157
+  RelPositionMultiHeadedAttention espnet/nets/pytorch_backend/transformer/attention.py:265-308 (legacy :167-209)
+  ConvolutionModule.forward       espnet/nets/pytorch_backend/conformer/convolution.py:56-79
+  PositionwiseFeedForward         espnet/nets/pytorch_backend/transformer/positionwise_feed_forward.py:30-32
+  Conv2dSubsampling.forward       espnet/nets/pytorch_backend/transformer/subsampling.py:67-87
+  ConformerEncoder.forward        espnet2/asr/encoder/conformer_encoder.py:292-368
+  TransformerDecoder.forward      espnet2/asr/decoder/transformer_decoder.py:92-145, decoder_layer.py:63-134
+  CTC.forward                     espnet2/asr/ctc.py:72-97
+  LabelSmoothingLoss / accuracy   label_smoothing_loss.py:41-63, nets_utils.py:299-320
+  ESPnetASRModel.forward          espnet2/asr/espnet_model.py:169-297
+
+Tensors: ``P`` name -> fp32 parameter (reference state_dict names, plus fused views such as
+``...self_attn.linear_qkv.weight``), ``W`` name -> bf16 copy in the layout the GEMM wants,
+``G`` name -> fp32 gradient accumulator (same layout as ``W``).  See ``params.py``.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Dict, Optional
+
+import torch
+
+from . import ops as K  # tests substitute a torch emulation of the same functions for CPU checks of this file
+
+F32 = torch.float32
+
+
+@dataclass
+class EncCfg:
+    idim: int = 80
+    d: int = 512
+    heads: int = 8
+    ffn: int = 2048
+    blocks: int = 12
+    kernel: int = 31
+    rel_pos_type: str = "latest"
+    dropout: float = 0.1
+    pos_dropout: float = 0.1
+    att_dropout: float = 0.1
+
+
+@dataclass
+class DecCfg:
+    vocab: int = 600
+    d: int = 512
+    heads: int = 8
+    ffn: int = 2048
+    blocks: int = 6
+    dropout: float = 0.1
+    pos_dropout: float = 0.1
+    self_att_dropout: float = 0.0
+    src_att_dropout: float = 0.0
+
+
+class StepCtx:
+    """Per-step dropout bookkeeping: one Philox seed per step, one site id per dropout call site."""
+
+    def __init__(self, seed: int = 0, training: bool = True):
+        self.seed = int(seed)
+        self.training = training
+        self._site = 0
+
+    def drop(self, p: float):
+        """Allocate a site; returns the (p, seed, site) triple or None when dropout is inactive."""
+        self._site += 1
+        if not self.training or p <= 0.0:
+            return None
+        return (float(p), self.seed, self._site)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# position tables (constants; built once per length with torch, like the reference's extend_pe)
+# ------------------------------------------------------------------------------------------------------------------
+_PE_CACHE: Dict[tuple, torch.Tensor] = {}
+
+
+def _sinusoid(pos: torch.Tensor, d: int) -> torch.Tensor:
+    div = torch.exp(torch.arange(0, d, 2, dtype=F32) * -(math.log(10000.0) / d))
+    pe = torch.zeros(pos.numel(), d, dtype=F32)
+    pe[:, 0::2] = torch.sin(pos[:, None] * div)
+    pe[:, 1::2] = torch.cos(pos[:, None] * div)
+    return pe
+
+
+def pos_table(kind: str, n: int, d: int, device) -> torch.Tensor:
+    """kind = 'latest' (embedding.py:196-244: rows +(T-1)..-(T-1)), 'legacy' (embedding.py:137-170, reverse, maxlen 5000)
+    or 'abs' (embedding.py:59-94)."""
+    key = (kind, n, d, str(device))
+    if key not in _PE_CACHE:
+        if kind == "latest":
+            pos = torch.arange(n - 1, -n, -1, dtype=F32)
+        elif kind == "legacy":
+            pos = torch.arange(4999, 4999 - n, -1, dtype=F32)
+        else:
+            pos = torch.arange(0, n, dtype=F32)
+        _PE_CACHE[key] = _sinusoid(pos, d).to(device).contiguous()
+    return _PE_CACHE[key]
+
+
+def subsampled_len(t_in: int) -> int:
+    """subsampling.py:57-59,87"""
+    return ((t_in - 1) // 2 - 1) // 2
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# position-wise feed-forward branch:  x + scale * dropout(w_2(dropout(act(w_1(LN(x))))))
+# ------------------------------------------------------------------------------------------------------------------
+def ffn_fwd(x, P, W, pre: str, norm: str, act: str, scale: float, p_drop: float, ctx: StepCtx):
+    ln, _, st = K.layernorm_fwd(x, P[norm + ".weight"], P[norm + ".bias"])
+    d1, d2 = ctx.drop(p_drop), ctx.drop(p_drop)
+    h, hpre = K.gemm(ln, W[pre + ".w_1.weight"], bias=P[pre + ".w_1.bias"], act=act, pre_act_out=True, drop=d1)
+    y = K.gemm(h, W[pre + ".w_2.weight"], bias=P[pre + ".w_2.bias"], alpha=scale, residual=x, drop=d2, out_dtype=F32)
+    return y, (x, ln, st, hpre, h, d1, d2, pre, norm, act, scale)
+
+
+def ffn_bwd(dy, saved, P, W, G):
+    x, ln, st, hpre, h, d1, d2, pre, norm, act, scale = saved
+    g = K.cast_bf16(dy, alpha=scale, drop=d2)
+    K.colsum(g, G[pre + ".w_2.bias"])
+    K.gemm(g, h, trans=True, out=G[pre + ".w_2.weight"], accumulate=True)
+    dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad=act, drop=d1)
+    K.colsum(dh, G[pre + ".w_1.bias"])
+    K.gemm(dh, ln, trans=True, out=G[pre + ".w_1.weight"], accumulate=True)
+    dln = K.gemm(dh, W[pre + ".w_1.weight"], trans_b=True)
+    dx, _ = K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dy)
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# multi-head attention core shared by the encoder (rel-pos) and the decoder (plain): scores -> softmax -> context
+# ------------------------------------------------------------------------------------------------------------------
+def relmha_fwd(x, pos16, klens, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: StepCtx):
+    d, H = cfg.d, cfg.heads
+    a = p + ".self_attn"
+    ln, _, st = K.layernorm_fwd(x, P[norm + ".weight"], P[norm + ".bias"])
+    qkv = K.gemm(ln, W[a + ".linear_qkv.weight"], bias=P[a + ".linear_qkv.bias"])
+    q, k, v = qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:]
+    qu, qv = K.pos_bias_fwd(q, P[a + ".pos_bias_u"].reshape(-1), P[a + ".pos_bias_v"].reshape(-1))
+    pp = K.gemm(pos16, W[a + ".linear_pos.weight"])
+    Pn = pos16.shape[0]
+    ac = K.attn_f1(qu, k, B, T, T, H)
+    bd = K.attn_f1(qv, pp, B, T, Pn, H, y_bcast=True)
+    da, do = ctx.drop(cfg.att_dropout), ctx.drop(cfg.dropout)
+    scale = 1.0 / math.sqrt(d // H)
+    pr, pd = K.softmax_fwd(ac, bd, klens, T, cfg.rel_pos_type, False, scale, drop=da)
+    c = K.attn_f2(pd, v, B, T, T, H)
+    y = K.gemm(c, W[a + ".linear_out.weight"], bias=P[a + ".linear_out.bias"], residual=x, drop=do, out_dtype=F32)
+    return y, (x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, bd.shape[-1])
+
+
+def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int):
+    x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, ld_bd = saved
+    d, H = cfg.d, cfg.heads
+    a = p + ".self_attn"
+    k, v = qkv[:, d:2 * d], qkv[:, 2 * d:]
+    g = K.cast_bf16(dy, alpha=1.0, drop=do)
+    K.colsum(g, G[a + ".linear_out.bias"])
+    K.gemm(g, c, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
+    dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
+    dqkv = torch.empty_like(qkv)
+    dpd = K.attn_f1(dc, v, B, T, T, H)
+    K.attn_f3(pd, dc, B, T, T, H, out=dqkv[:, 2 * d:])
+    dac, dbd = K.softmax_bwd(dpd, pr, T, cfg.rel_pos_type, scale, ld_bd=ld_bd, drop=da)
+    dqu = K.attn_f2(dac, k, B, T, T, H)
+    K.attn_f3(dac, qu, B, T, T, H, out=dqkv[:, d:2 * d])
+    dqv = K.attn_f2(dbd, pp, B, T, Pn, H, y_bcast=True)
+    dpp = torch.zeros(Pn, d, device=x.device, dtype=F32)
+    K.attn_f4(dbd, qv, B, T, Pn, H, dpp)
+    K.gemm(K.cast_bf16(dpp), pos16, trans=True, out=G[a + ".linear_pos.weight"], accumulate=True)
+    K.pos_bias_bwd(dqu, dqv, dqkv[:, :d], G[a + ".pos_bias_u"].reshape(-1), G[a + ".pos_bias_v"].reshape(-1))
+    K.colsum(dqkv, G[a + ".linear_qkv.bias"])
+    K.gemm(dqkv, ln, trans=True, out=G[a + ".linear_qkv.weight"], accumulate=True)
+    dln = K.gemm(dqkv, W[a + ".linear_qkv.weight"], trans_b=True)
+    dx, _ = K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dy)
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# convolution module branch
+# ------------------------------------------------------------------------------------------------------------------
+def convmod_fwd(x, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: StepCtx, bn_buffers=None):
+    cm = p + ".conv_module"
+    ln, _, st = K.layernorm_fwd(x, P[norm + ".weight"], P[norm + ".bias"])
+    pw1 = K.gemm(ln, W[cm + ".pointwise_conv1.weight"], bias=P[cm + ".pointwise_conv1.bias"])
+    wdw = P[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel)
+    dw, sums = K.glu_dwconv_fwd(pw1, wdw, P[cm + ".depthwise_conv.bias"], B, T, cfg.kernel)
+    rm = rv = nb = None
+    if bn_buffers is not None and ctx.training:
+        rm, rv, nb = bn_buffers[cm + ".norm.running_mean"], bn_buffers[cm + ".norm.running_var"], \
+            bn_buffers[cm + ".norm.num_batches_tracked"]
+    mr = K.bn_finalize(sums, B * T, 1e-5, 0.1, rm, rv, nb)
+    bs = K.bn_swish_fwd(dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"])
+    do = ctx.drop(cfg.dropout)
+    y = K.gemm(bs, W[cm + ".pointwise_conv2.weight"], bias=P[cm + ".pointwise_conv2.bias"], residual=x, drop=do,
+               out_dtype=F32)
+    return y, (x, ln, st, pw1, dw, mr, bs, do)
+
+
+def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int):
+    x, ln, st, pw1, dw, mr, bs, do = saved
+    cm = p + ".conv_module"
+    g = K.cast_bf16(dy, alpha=1.0, drop=do)
+    K.colsum(g, G[cm + ".pointwise_conv2.bias"])
+    K.gemm(g, bs, trans=True, out=G[cm + ".pointwise_conv2.weight"], accumulate=True)
+    dbs = K.gemm(g, W[cm + ".pointwise_conv2.weight"], trans_b=True)
+    ddw = K.bn_swish_bwd(dbs, dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"], G[cm + ".norm.weight"],
+                         G[cm + ".norm.bias"])
+    wdw = P[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel)
+    dpw1 = K.glu_dwconv_bwd(ddw, pw1, wdw, B, T, cfg.kernel, G[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel),
+                            G[cm + ".depthwise_conv.bias"])
+    K.colsum(dpw1, G[cm + ".pointwise_conv1.bias"])
+    K.gemm(dpw1, ln, trans=True, out=G[cm + ".pointwise_conv1.weight"], accumulate=True)
+    dln = K.gemm(dpw1, W[cm + ".pointwise_conv1.weight"], trans_b=True)
+    dx, _ = K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dy)
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# one Conformer block
+# ------------------------------------------------------------------------------------------------------------------
+def enc_layer_fwd(x, pos16, klens, P, W, p: str, cfg: EncCfg, B: int, T: int, ctx: StepCtx, bn_buffers=None):
+    x, s1 = ffn_fwd(x, P, W, p + ".feed_forward_macaron", p + ".norm_ff_macaron", "swish", 0.5, cfg.dropout, ctx)
+    x, s2 = relmha_fwd(x, pos16, klens, P, W, p, p + ".norm_mha", cfg, B, T, ctx)
+    x, s3 = convmod_fwd(x, P, W, p, p + ".norm_conv", cfg, B, T, ctx, bn_buffers)
+    x, s4 = ffn_fwd(x, P, W, p + ".feed_forward", p + ".norm_ff", "swish", 0.5, cfg.dropout, ctx)
+    _, y, st = K.layernorm_fwd(x, P[p + ".norm_final.weight"], P[p + ".norm_final.bias"], want_bf16=False, want_f32=True)
+    return y, (s1, s2, s3, s4, x, st)
+
+
+def enc_layer_bwd(dy, saved, pos16, P, W, G, p: str, cfg: EncCfg, B: int, T: int):
+    s1, s2, s3, s4, x4, st = saved
+    n = p + ".norm_final"
+    dx, _ = K.layernorm_bwd(dy, x4, P[n + ".weight"], st, G[n + ".weight"], G[n + ".bias"])
+    dx = ffn_bwd(dx, s4, P, W, G)
+    dx = convmod_bwd(dx, s3, P, W, G, p, p + ".norm_conv", cfg, B, T)
+    dx = relmha_bwd(dx, s2, pos16, P, W, G, p, p + ".norm_mha", cfg, B, T)
+    dx = ffn_bwd(dx, s1, P, W, G)
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# encoder: Conv2dSubsampling + rel-pos encoding + N blocks + after_norm
+# ------------------------------------------------------------------------------------------------------------------
+def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder", bn_buffers=None):
+    """feats f32 [B, T_in, idim], flens int32 [B] (device).  Returns (enc f32 [B*T, d], enc16 bf16, olens int32, saved)."""
+    B, Tin, _ = feats.shape
+    e = p + ".embed"
+    C_ = P[e + ".conv.0.weight"].shape[0]
+    h1 = K.conv1_fwd(feats, P[e + ".conv.0.weight"].reshape(C_, 9), P[e + ".conv.0.bias"])
+    _, T1, F1, _ = h1.shape
+    T, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
+    col = K.im2col(h1)
+    h2 = K.gemm(col, W[e + ".conv.2.weight"], bias=P[e + ".conv.2.bias"], act="relu")
+    del col  # recomputed in the backward (it is 9x the size of h1)
+    h2v = h2.view(B * T, F2 * C_)
+    dpos = ctx.drop(cfg.pos_dropout)
+    x = K.gemm(h2v, W[e + ".out.0.weight"], bias=P[e + ".out.0.bias"], alpha=math.sqrt(cfg.d), drop=dpos, out_dtype=F32)
+    # RelPositionalEncoding: table rows + dropout (embedding.py:228-244 / 156-170)
+    Pn = 2 * T - 1 if cfg.rel_pos_type == "latest" else T
+    dpe = ctx.drop(cfg.pos_dropout)
+    pos16 = K.cast_bf16(pos_table(cfg.rel_pos_type, T if cfg.rel_pos_type == "latest" else Pn, cfg.d, feats.device), drop=dpe)
+    olens = torch.clamp((flens + 3) // 4, max=T).to(torch.int32)  # mask[:, :, :-2:2][:, :, :-2:2] (subsampling.py:87)
+    layers = []
+    for n in range(cfg.blocks):
+        x, s = enc_layer_fwd(x, pos16, olens, P, W, f"{p}.encoders.{n}", cfg, B, T, ctx, bn_buffers)
+        layers.append(s)
+    enc16, enc, st = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"], want_bf16=True, want_f32=True)
+    return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, B, T)
+
+
+def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder"):
+    """denc f32 [B*T, d]: gradient w.r.t. the encoder output.  Accumulates every encoder parameter gradient into G."""
+    feats, h1, h2v, dpos, pos16, layers, xl, st, B, T = saved
+    e = p + ".embed"
+    dx, _ = K.layernorm_bwd(denc, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
+    for n in reversed(range(cfg.blocks)):
+        dx = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T)
+        layers[n] = None  # free the block's activations as we go
+    C_ = h1.shape[-1]
+    g = K.cast_bf16(dx, alpha=math.sqrt(cfg.d), drop=dpos)
+    K.colsum(g, G[e + ".out.0.bias"])
+    K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
+    dh2 = K.gemm(g, W[e + ".out.0.weight"], trans_b=True, act_grad_input=h2v, act_grad="relu").view(-1, C_)
+    K.colsum(dh2, G[e + ".conv.2.bias"])
+    col = K.im2col(h1)
+    K.gemm(dh2, col, trans=True, out=G[e + ".conv.2.weight"], accumulate=True)
+    del col
+    dcol = K.gemm(dh2, W[e + ".conv.2.weight"], trans_b=True)
+    dh1 = K.col2im_relu(dcol, h1)
+    del dcol
+    K.conv1_bwd(dh1, feats, G[e + ".conv.0.weight"].reshape(C_, 9), G[e + ".conv.0.bias"])
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# decoder
+# ------------------------------------------------------------------------------------------------------------------
+def _mha_fwd(xq16, kv_src16, q_w: str, kv_w: str, P, W, a: str, klens, B, Tq, Tk, H, d, causal, p_att, ctx, fused_qkv):
+    """Plain MultiHeadedAttention (attention.py:98-114) up to (not including) linear_out."""
+    if fused_qkv:
+        qkv = K.gemm(xq16, W[a + ".linear_qkv.weight"], bias=P[a + ".linear_qkv.bias"])
+        q, k, v = qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:]
+        proj = (qkv,)
+    else:
+        q = K.gemm(xq16, W[a + ".linear_q.weight"], bias=P[a + ".linear_q.bias"])
+        kv = K.gemm(kv_src16, W[a + ".linear_kv.weight"], bias=P[a + ".linear_kv.bias"])
+        k, v = kv[:, :d], kv[:, d:]
+        proj = (q, kv)
+    ac = K.attn_f1(q, k, B, Tq, Tk, H)
+    da = ctx.drop(p_att)
+    scale = 1.0 / math.sqrt(d // H)
+    pr, pd = K.softmax_fwd(ac, None, klens, Tk, "none", causal, scale, drop=da)
+    c = K.attn_f2(pd, v, B, Tq, Tk, H)
+    return c, (proj, pr, pd, da, scale)
+
+
+def dec_layer_fwd(x, mem16, ylens, mlens, P, W, p: str, cfg: DecCfg, B: int, L: int, T: int, ctx: StepCtx):
+    d, H = cfg.d, cfg.heads
+    # masked self-attention (decoder_layer.py:88-110)
+    ln1, _, st1 = K.layernorm_fwd(x, P[p + ".norm1.weight"], P[p + ".norm1.bias"])
+    c1, sa = _mha_fwd(ln1, None, "", "", P, W, p + ".self_attn", ylens, B, L, L, H, d, True, cfg.self_att_dropout, ctx, True)
+    do1 = ctx.drop(cfg.dropout)
+    x1 = K.gemm(c1, W[p + ".self_attn.linear_out.weight"], bias=P[p + ".self_attn.linear_out.bias"], residual=x, drop=do1,
+                out_dtype=F32)
+    # source attention over the encoder memory (decoder_layer.py:112-123)
+    ln2, _, st2 = K.layernorm_fwd(x1, P[p + ".norm2.weight"], P[p + ".norm2.bias"])
+    c2, ca = _mha_fwd(ln2, mem16, "", "", P, W, p + ".src_attn", mlens, B, L, T, H, d, False, cfg.src_att_dropout, ctx, False)
+    do2 = ctx.drop(cfg.dropout)
+    x2 = K.gemm(c2, W[p + ".src_attn.linear_out.weight"], bias=P[p + ".src_attn.linear_out.bias"], residual=x1, drop=do2,
+                out_dtype=F32)
+    # feed-forward, ReLU (decoder_layer.py:125-131)
+    x3, sf = ffn_fwd(x2, P, W, p + ".feed_forward", p + ".norm3", "relu", 1.0, cfg.dropout, ctx)
+    return x3, (x, ln1, st1, c1, sa, do1, x1, ln2, st2, c2, ca, do2, sf)
+
+
+def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, L: int, T: int):
+    """Returns dx; accumulates the memory gradient into dmem (f32 [B*T, d], in place via the GEMM residual input)."""
+    x, ln1, st1, c1, sa, do1, x1, ln2, st2, c2, ca, do2, sf = saved
+    d, H = cfg.d, cfg.heads
+    dx2 = ffn_bwd(dy, sf, P, W, G)
+    # ---- source attention
+    a = p + ".src_attn"
+    (q, kv), pr, pd, da, scale = ca
+    k, v = kv[:, :d], kv[:, d:]
+    g = K.cast_bf16(dx2, alpha=1.0, drop=do2)
+    K.colsum(g, G[a + ".linear_out.bias"])
+    K.gemm(g, c2, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
+    dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
+    dkv = torch.empty_like(kv)
+    dpd = K.attn_f1(dc, v, B, L, T, H)
+    K.attn_f3(pd, dc, B, L, T, H, out=dkv[:, d:])
+    dac, _ = K.softmax_bwd(dpd, pr, T, "none", scale, drop=da)
+    dq = K.attn_f2(dac, k, B, L, T, H)
+    K.attn_f3(dac, q, B, L, T, H, out=dkv[:, :d])
+    K.colsum(dkv, G[a + ".linear_kv.bias"])
+    K.gemm(dkv, mem16, trans=True, out=G[a + ".linear_kv.weight"], accumulate=True)
+    K.gemm(dkv, W[a + ".linear_kv.weight"], trans_b=True, residual=dmem, out=dmem)
+    K.colsum(dq, G[a + ".linear_q.bias"])
+    K.gemm(dq, ln2, trans=True, out=G[a + ".linear_q.weight"], accumulate=True)
+    dln2 = K.gemm(dq, W[a + ".linear_q.weight"], trans_b=True)
+    dx1, _ = K.layernorm_bwd(dln2, x1, P[p + ".norm2.weight"], st2, G[p + ".norm2.weight"], G[p + ".norm2.bias"], dx_add=dx2)
+    # ---- self attention
+    a = p + ".self_attn"
+    (qkv,), pr, pd, da, scale = sa
+    q, k, v = qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:]
+    g = K.cast_bf16(dx1, alpha=1.0, drop=do1)
+    K.colsum(g, G[a + ".linear_out.bias"])
+    K.gemm(g, c1, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
+    dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
+    dqkv = torch.empty_like(qkv)
+    dpd = K.attn_f1(dc, v, B, L, L, H)
+    K.attn_f3(pd, dc, B, L, L, H, out=dqkv[:, 2 * d:])
+    dac, _ = K.softmax_bwd(dpd, pr, L, "none", scale, drop=da)
+    K.attn_f2(dac, k, B, L, L, H, out=dqkv[:, :d])
+    K.attn_f3(dac, q, B, L, L, H, out=dqkv[:, d:2 * d])
+    K.colsum(dqkv, G[a + ".linear_qkv.bias"])
+    K.gemm(dqkv, ln1, trans=True, out=G[a + ".linear_qkv.weight"], accumulate=True)
+    dln1 = K.gemm(dqkv, W[a + ".linear_qkv.weight"], trans_b=True)
+    dx, _ = K.layernorm_bwd(dln1, x, P[p + ".norm1.weight"], st1, G[p + ".norm1.weight"], G[p + ".norm1.bias"], dx_add=dx1)
+    return dx
+
+
+def decoder_fwd(mem16, mlens, ys_in, ys_in_lens, P, W, cfg: DecCfg, ctx: StepCtx, B: int, T: int, p: str = "decoder"):
+    """mem16 bf16 [B*T, d]; ys_in int32 [B, L]; returns (logits f32 [B*L, round8(V)] (columns >= V unspecified), saved)."""
+    L = ys_in.shape[1]
+    tok = ys_in.reshape(-1)
+    de = ctx.drop(cfg.pos_dropout)
+    x = K.embed_fwd(P[p + ".embed.0.weight"], tok, pos_table("abs", L, cfg.d, mem16.device), L, math.sqrt(cfg.d), drop=de)
+    layers = []
+    for n in range(cfg.blocks):
+        x, s = dec_layer_fwd(x, mem16, ys_in_lens, mlens, P, W, f"{p}.decoders.{n}", cfg, B, L, T, ctx)
+        layers.append(s)
+    ln, _, st = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"])
+    V = cfg.vocab
+    logits = torch.empty(B * L, K.round8(V), device=mem16.device, dtype=F32)
+    K.gemm(ln, W[p + ".output_layer.weight"], bias=P[p + ".output_layer.bias"], out=logits)
+    return logits, (tok, de, layers, x, ln, st, L)
+
+
+def decoder_bwd(dlogits16, dmem, saved, mem16, P, W, G, cfg: DecCfg, B: int, T: int, p: str = "decoder"):
+    """dlogits16 bf16 [B*L, round8(V)]; dmem f32 [B*T, d] is accumulated in place."""
+    tok, de, layers, xl, ln, st, L = saved
+    V = cfg.vocab
+    gl = dlogits16[:, :V]
+    K.colsum(dlogits16, G[p + ".output_layer.bias"], n=V)
+    K.gemm(gl, ln, trans=True, out=G[p + ".output_layer.weight"], accumulate=True)
+    dln = K.gemm(gl, W[p + ".output_layer.weight"], trans_b=True)
+    dx, _ = K.layernorm_bwd(dln, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
+    for n in reversed(range(cfg.blocks)):
+        dx = dec_layer_bwd(dx, dmem, layers[n], mem16, P, W, G, f"{p}.decoders.{n}", cfg, B, L, T)
+        layers[n] = None
+    K.embed_bwd(dx, tok, math.sqrt(cfg.d), G[p + ".embed.0.weight"], drop=de)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# heads: CTC and label-smoothing attention loss (each computes its own input gradient in the same pass)
+# ------------------------------------------------------------------------------------------------------------------
+def ctc_head(enc16, olens, labels, label_lens, P, W, G, V: int, B: int, T: int, weight: float, p: str = "ctc",
+             want_grad: bool = True):
+    """CTC.forward (espnet2/asr/ctc.py:72-97) + its backward.  Returns (loss_ctc scalar tensor = sum/B, denc f32 or None).
+    ``weight`` = d(total loss)/d(loss_ctc); the gradient written is already scaled by it."""
+    logits = torch.empty(B * T, K.round8(V), device=enc16.device, dtype=F32)
+    K.gemm(enc16, W[p + ".ctc_lo.weight"], bias=P[p + ".ctc_lo.bias"], out=logits)
+    l3 = logits.view(B, T, -1)
+    _, loss_sum, ws = K.ctc_fwd(l3, V, olens, labels, label_lens, blank=0)
+    loss = loss_sum / B
+    if not want_grad:
+        return loss, None
+    _, g16 = K.ctc_bwd(l3, V, olens, labels, label_lens, ws, weight / B, blank=0)
+    g16 = g16.view(B * T, -1)
+    gl = g16[:, :V]
+    K.colsum(g16, G[p + ".ctc_lo.bias"], n=V)
+    K.gemm(gl, enc16, trans=True, out=G[p + ".ctc_lo.weight"], accumulate=True)
+    denc = K.gemm(gl, W[p + ".ctc_lo.weight"], trans_b=True, out_dtype=F32)
+    return loss, denc
+
+
+def att_head(logits, ys_out, V: int, B: int, smoothing: float, weight: float):
+    """LabelSmoothingLoss + th_accuracy.  Returns (loss_att scalar tensor, acc scalar tensor, dlogits bf16)."""
+    stats, _, g16 = K.lsm_loss(logits, V, ys_out.reshape(-1), smoothing, weight / B)
+    return stats[0:1] / B, stats[1:2] / stats[2:3], g16
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# whole step from encoder input on (espnet_model.py:202-297): loss + all parameter gradients
+# ------------------------------------------------------------------------------------------------------------------
+@dataclass
+class ModelCfg:
+    enc: EncCfg = field(default_factory=EncCfg)
+    dec: DecCfg = field(default_factory=DecCfg)
+    vocab: int = 600
+    ctc_weight: float = 0.3
+    lsm_weight: float = 0.1
+    n_fft: int = 512
+    hop: int = 128
+    n_mels: int = 80
+
+
+def add_sos_eos(text, text_lens, sos: int, eos: int, ignore: int = -1):
+    """add_sos_eos.py:12-31 without a host loop: text int [B, Lmax] (padding arbitrary), text_lens [B] -> ys_in, ys_out int32 [B, Lmax+1]."""
+    B, Lm = text.shape
+    ar = torch.arange(Lm + 1, device=text.device)[None, :]
+    tl = text_lens[:, None].to(torch.long)
+    t = text.to(torch.long)
+    shifted = torch.cat([torch.full((B, 1), sos, device=text.device, dtype=torch.long), t], 1)
+    ys_in = torch.where(ar <= tl, shifted, torch.full_like(shifted, eos))
+    padded = torch.cat([t, torch.full((B, 1), eos, device=text.device, dtype=torch.long)], 1)
+    ys_out = torch.where(ar < tl, padded, torch.where(ar == tl, torch.full_like(padded, eos), torch.full_like(padded, ignore)))
+    return ys_in.to(torch.int32).contiguous(), ys_out.to(torch.int32).contiguous()
+
+
+def train_step_from_feats(feats, flens, text, text_lens, P, W, G, cfg: ModelCfg, ctx: StepCtx, bn_buffers=None,
+                          grad_scale: float = 1.0, after_enc_bwd_hook=None):
+    """feats f32 [B,T_in,idim] (already normalised), flens int32 [B], text int32 [B,Lmax], text_lens int32 [B] -- all on the
+    device.  Runs forward and backward; parameter gradients (times grad_scale) are ACCUMULATED into G.
+    Returns dict(loss, loss_ctc, loss_att, acc) of 1-element device tensors (no synchronisation)."""
+    B = feats.shape[0]
+    V = cfg.vocab
+    enc, enc16, olens, s_enc = encoder_fwd(feats, flens, P, W, cfg.enc, ctx, bn_buffers=bn_buffers)
+    T = s_enc[-1]
+    wc, wa = cfg.ctc_weight * grad_scale, (1.0 - cfg.ctc_weight) * grad_scale
+    text = text.to(torch.int32)
+    tl = text_lens.to(torch.int32)
+    loss_ctc, denc = ctc_head(enc16, olens, text.contiguous(), tl, P, W, G, V, B, T, wc)
+    ys_in, ys_out = add_sos_eos(text, tl, V - 1, V - 1)
+    ylens = (tl + 1).to(torch.int32)
+    logits, s_dec = decoder_fwd(enc16, olens, ys_in, ylens, P, W, cfg.dec, ctx, B, T)
+    loss_att, acc, dlogits = att_head(logits, ys_out, V, B, cfg.lsm_weight, wa)
+    decoder_bwd(dlogits, denc, s_dec, enc16, P, W, G, cfg.dec, B, T)
+    del s_dec
+    encoder_bwd(denc, s_enc, P, W, G, cfg.enc)
+    loss = cfg.ctc_weight * loss_ctc + (1.0 - cfg.ctc_weight) * loss_att
+    return {"loss": loss, "loss_ctc": loss_ctc, "loss_att": loss_att, "acc": acc}
+
+
+def frontend_fwd(speech, speech_lens, melmat, cfg: ModelCfg, draws: Optional[dict] = None):
+    """DefaultFrontend -> SpecAug (draws: dict of int32 device arrays or None) -> UtteranceMVN (espnet_model.py:319-338)."""
+    feats, flens = K.logmel(speech, speech_lens.to(torch.int32), melmat, cfg.n_fft, cfg.hop)
+    d = draws or {}
+    feats = K.specaug_mvn(feats, flens, d.get("center"), d.get("warped"), d.get("fmask"), d.get("tmask"), do_mvn=True)
+    return feats, flens

@@ -1,0 +1,90 @@
+"""CPU check of the host logic: the step orchestration (forward + hand-written backward, buffer layouts, fused
+projections, gradient re-layouts) run over the plain-torch emulation of the kernels (tests/emul_ops.py) must reproduce
+the UNMODIFIED reference's loss and every parameter gradient frozen in tests/golden/e2e_{latest,legacy}.npz."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import emul_ops
+from espnet_slurp_b200 import params as bparams
+from espnet_slurp_b200 import step as bstep
+from oracle import model as om
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture()
+def emulated(monkeypatch):
+    monkeypatch.setattr(bstep, "K", emul_ops)
+    monkeypatch.setattr(emul_ops, "exact", True)
+    yield
+    bstep._PE_CACHE.clear()
+
+
+def tiny_cfg(rel):
+    enc = bstep.EncCfg(80, 16, 2, 32, 2, 7, rel, 0.0, 0.0, 0.0)
+    dec = bstep.DecCfg(20, 16, 2, 32, 2, 0.0, 0.0, 0.0, 0.0)
+    return bstep.ModelCfg(enc=enc, dec=dec, vocab=20)
+
+
+def run_step(g, rel):
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/") and v.dtype == np.float32}
+    pack = bparams.ParamPack(sd, lowp=torch.float32)
+    pack.refresh()
+    pack.zero_grad()
+    cfg = tiny_cfg(rel)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    feats, flens = bstep.frontend_fwd(torch.tensor(g["wav"]), torch.tensor(g["lens"]), mel, cfg)
+    out = bstep.train_step_from_feats(feats, flens, torch.tensor(g["text"]), torch.tensor(g["text_lens"]), pack.P, pack.W,
+                                      pack.G, cfg, bstep.StepCtx(0, True))
+    pack.finalize_grads()
+    return out, pack
+
+
+@pytest.mark.parametrize("rel", ["latest", "legacy"])
+def test_emulated_step_matches_reference_golden(emulated, rel):
+    z = np.load(os.path.join(GOLDEN, f"e2e_{rel}.npz"))
+    g = {k: z[k] for k in z.files}
+    out, pack = run_step(g, rel)
+    np.testing.assert_allclose(out["loss_ctc"].item(), g["loss_ctc"].item(), rtol=5e-5)
+    np.testing.assert_allclose(out["loss_att"].item(), g["loss_att"].item(), rtol=5e-5)
+    np.testing.assert_allclose(out["loss"].item(), g["loss"].item(), rtol=5e-5)
+    assert abs(out["acc"].item() - float(g["acc"].item())) < 1e-6
+    worst, worst_name = 0.0, ""
+    for k, v in g.items():
+        if not k.startswith("grad/"):
+            continue
+        got = pack.grads()[k[5:]].numpy()
+        err = float(np.abs(got - v).max() / max(np.abs(v).max(), 1e-3))
+        if err > worst:
+            worst, worst_name = err, k
+    assert worst < 3e-3, (worst, worst_name)
+
+
+def test_add_sos_eos_matches_oracle():
+    text = torch.tensor([[5, 6, 7, 8], [3, 4, -1, -1], [9, 2, 11, -1]])
+    tl = torch.tensor([4, 2, 3])
+    a, b = bstep.add_sos_eos(text, tl, 19, 19)
+    ra, rb = om.add_sos_eos(text, tl, 19, 19)
+    assert torch.equal(a.long(), ra) and torch.equal(b.long(), rb)
+
+
+def test_param_pack_fusions_are_views():
+    d = 16
+    sd = {}
+    for n in ("q", "k", "v", "out"):
+        sd[f"decoder.decoders.0.self_attn.linear_{n}.weight"] = torch.randn(d, d)
+        sd[f"decoder.decoders.0.self_attn.linear_{n}.bias"] = torch.randn(d)
+        sd[f"decoder.decoders.0.src_attn.linear_{n}.weight"] = torch.randn(d, d)
+        sd[f"decoder.decoders.0.src_attn.linear_{n}.bias"] = torch.randn(d)
+    pack = bparams.ParamPack(sd)
+    qkv = torch.cat([sd[f"decoder.decoders.0.self_attn.linear_{n}.weight"] for n in "qkv"])
+    pack.flat16.copy_(pack.flat32.bfloat16())
+    assert torch.equal(pack.W["decoder.decoders.0.self_attn.linear_qkv.weight"].float(), qkv.bfloat16().float())
+    kvb = torch.cat([sd[f"decoder.decoders.0.src_attn.linear_{n}.bias"] for n in "kv"])
+    assert torch.equal(pack.P["decoder.decoders.0.src_attn.linear_kv.bias"], kvb)
+    pack.G["decoder.decoders.0.self_attn.linear_qkv.weight"][d:2 * d] += 1.0
+    assert torch.all(pack.grads()["decoder.decoders.0.self_attn.linear_k.weight"] == 1.0)
+    assert torch.all(pack.grads()["decoder.decoders.0.self_attn.linear_q.weight"] == 0.0)
