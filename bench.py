@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""Train-step throughput of the SLURP Conformer CTC/attention model on B200 (BASELINE.json metric:
+audio-sec/sec train throughput; config[1] = egs2/slurp Conformer, 12 blocks, CTC 0.3 + attention decoder).
+
+    python bench.py --gpus 1 --steps K --warmup W                 # one process
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...                          # the reference's CPU path (oracle port) on the host cores
+
+One "step" = waveform batch -> log-mel front-end -> SpecAug -> utterance MVN -> 12-block Conformer encoder -> CTC +
+6-block attention decoder losses -> full backward -> (N > 1: NCCL gradient all-reduce overlapped with backward) ->
+fused clip + Adam.  Dropout 0.1 and SpecAug are ON (training configuration).  Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FS = 16000
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="utterances per GPU per step")
+    ap.add_argument("--vocab", type=int, default=600)
+    ap.add_argument("--rel-pos", default="latest", choices=["latest", "legacy"])
+    ap.add_argument("--min-sec", type=float, default=3.0)
+    ap.add_argument("--max-sec", type=float, default=5.0)
+    ap.add_argument("--enc-blocks", type=int, default=12)
+    ap.add_argument("--dec-blocks", type=int, default=6)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prof", action="store_true")
+    ap.add_argument("--cpu-batch", type=int, default=8)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------- synthetic workload
+def make_batch(B, V, seed, min_sec, max_sec):
+    """Waveforms ~N(0, 0.1^2), durations U[min,max] s, padded to the batch maximum; 6..20 tokens in 2..V-2."""
+    g = torch.Generator().manual_seed(seed)
+    lens = (torch.rand(B, generator=g) * (max_sec - min_sec) + min_sec).mul(FS).long()
+    lens[0] = int(max_sec * FS)  # fixed padded width -> static shapes from step to step
+    N = int(lens.max())
+    wav = torch.randn(B, N, generator=g) * 0.1
+    wav *= (torch.arange(N)[None, :] < lens[:, None]).float()
+    tl = torch.randint(6, 21, (B,), generator=g)
+    Lmax = 20
+    text = torch.randint(2, V - 1, (B, Lmax), generator=g)
+    text = torch.where(torch.arange(Lmax)[None, :] < tl[:, None], text, torch.full_like(text, -1))
+    return wav, lens, text, tl
+
+
+def specaug_draws(flens, T_in, n_mels=80, W=5, F=30, Tm=40, n_f=2, n_t=2, gen=None):
+    """The RNG draws SpecAug makes, in the reference's order (time_warp.py:28-29 per utterance, then
+    mask_along_axis.py:33-43 for freq and time), as small int32 arrays for b200slu_specaug_mvn_fwd."""
+    B = flens.numel()
+    center = torch.full((B,), -1, dtype=torch.int32)
+    warped = torch.zeros(B, dtype=torch.int32)
+    for b in range(B):
+        t = int(flens[b])
+        if t - W > W:
+            c = int(torch.randint(W, t - W, (1,), generator=gen))
+            center[b] = c
+            warped[b] = int(torch.randint(c - W, c + W, (1,), generator=gen)) + 1
+    f_len = torch.randint(0, F, (B, n_f), generator=gen)
+    f_pos = torch.randint(0, max(1, n_mels - int(f_len.max())), (B, n_f), generator=gen)
+    t_len = torch.randint(0, Tm, (B, n_t), generator=gen)
+    t_pos = torch.randint(0, max(1, T_in - int(t_len.max())), (B, n_t), generator=gen)
+    return {"center": center, "warped": warped, "fmask": torch.stack([f_pos, f_len], -1).int().contiguous(),
+            "tmask": torch.stack([t_pos, t_len], -1).int().contiguous()}
+
+
+def build_cfg(args):
+    from espnet_slurp_b200 import step as bstep
+    enc = bstep.EncCfg(80, 512, 8, 2048, args.enc_blocks, 31, args.rel_pos, 0.1, 0.1, 0.1)
+    dec = bstep.DecCfg(args.vocab, 512, 8, 2048, args.dec_blocks, 0.1, 0.1, 0.0, 0.0)
+    return bstep.ModelCfg(enc=enc, dec=dec, vocab=args.vocab)
+
+
+def make_state_dict(cfg, seed=0):
+    """Random-init weights of the architecture under the reference's state_dict names (no checkpoints offline)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_step_gpu import make_sd
+    return make_sd(cfg.enc, cfg.dec, cfg.vocab, seed=seed)
+
+
+# ----------------------------------------------------------------------------------------------------- clocks sampler
+class Clocks(threading.Thread):
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": max((int(r[1]) for r in self.rows if r[1].isdigit()), default=None), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+# ----------------------------------------------------------------------------------------------------- CPU reference arm
+def cpu_step_time(args, cfg, n_steps, warmup, batch):
+    """The reference's CPU path for the same step: oracle/model.py (CPU restatement pinned against the unmodified
+    reference's goldens) fwd + autograd bwd in fp32 on all host cores.  Returns (audio-sec/sec, seconds/step, cores)."""
+    from oracle import model as om
+    torch.set_num_threads(os.cpu_count() or 1)
+    ocfg = om.ModelCfg(enc=om.EncCfg(80, 512, 8, 2048, cfg.enc.blocks, 31, cfg.enc.rel_pos_type),
+                       dec=om.DecCfg(cfg.vocab, 512, 8, 2048, cfg.dec.blocks), vocab=cfg.vocab)
+    sd = {k: v.clone().requires_grad_(True) for k, v in make_state_dict(cfg).items()}
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    wav, lens, text, tl = make_batch(batch, cfg.vocab, 1234, args.min_sec, args.max_sec)
+    audio = float(lens.sum()) / FS
+    times = []
+    for i in range(warmup + n_steps):
+        t0 = time.perf_counter()
+        feats, flens = om.frontend_logmel(wav, lens, mel)
+        draws = specaug_draws(flens, feats.shape[1])
+        od = {"center": draws["center"].long(), "warped": draws["warped"].long(), "f_pos": draws["fmask"][..., 0].long(),
+              "f_len": draws["fmask"][..., 1].long(), "t_pos": draws["tmask"][..., 0].long(), "t_len": draws["tmask"][..., 1].long()}
+        feats = om.utterance_mvn(om.spec_augment(feats, flens, od), flens)
+        loss, _ = om.asr_forward_from_feats(feats, flens, text, tl, sd, ocfg)
+        loss.backward()
+        for v in sd.values():
+            v.grad = None
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    sec = sum(times) / len(times)
+    return audio / sec, sec, torch.get_num_threads(), audio
+
+
+# ----------------------------------------------------------------------------------------------------- GPU arm
+class Trainer:
+    """One rank of the data-parallel train step (mirrors espnet2/train/trainer.py:464-720 for one iteration)."""
+
+    def __init__(self, args, cfg, rank, world):
+        from espnet_slurp_b200 import ops, params as bparams, step as bstep
+        from espnet_slurp_b200.melbank import mel_matrix
+        self.ops, self.bstep, self.cfg, self.args, self.rank, self.world = ops, bstep, cfg, args, rank, world
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.dev = dev
+        self.pack = bparams.ParamPack({k: v.to(dev) for k, v in make_state_dict(cfg).items()})
+        n = self.pack.total
+        self.m = torch.zeros(n, device=dev)
+        self.v = torch.zeros(n, device=dev)
+        self.state = torch.zeros(3, device=dev, dtype=torch.float64)
+        self.mel = mel_matrix(device=dev)
+        self.bn = {}
+        for nblk in range(cfg.enc.blocks):
+            p = f"encoder.encoders.{nblk}.conv_module.norm."
+            self.bn[p + "running_mean"] = torch.zeros(cfg.enc.d, device=dev)
+            self.bn[p + "running_var"] = torch.ones(cfg.enc.d, device=dev)
+            self.bn[p + "num_batches_tracked"] = torch.zeros(1, device=dev, dtype=torch.long)
+        self.step_no = 0
+        self.comm = torch.cuda.Stream() if world > 1 else None
+        # gradient buckets for the overlapped all-reduce: decoder + ctc first (their backward finishes first),
+        # then encoder blocks last-to-first, then the embedding front
+        self.host_batches, self.dev_batches = [], []
+        gen = torch.Generator().manual_seed(99 + rank)
+        for i in range(4):
+            wav, lens, text, tl = make_batch(args.batch, cfg.vocab, 1234 + rank * 100 + i, args.min_sec, args.max_sec)
+            flens = lens // cfg.hop + 1
+            draws = specaug_draws(flens, wav.shape[1] // cfg.hop + 1, gen=gen)
+            hb = {"wav": wav.pin_memory(), "lens": lens.int().pin_memory(), "text": text.int().pin_memory(),
+                  "tl": tl.int().pin_memory(), **{k: v.pin_memory() for k, v in draws.items()}}
+            self.host_batches.append(hb)
+            self.dev_batches.append({k: v.to(dev) for k, v in hb.items()})
+        self.audio_sec = [float(hb["lens"].sum()) / FS for hb in self.host_batches]
+        self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host_batches[0].values())
+        self.loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+
+    def lr(self, base=1e-3, warmup=25000):
+        s = self.step_no
+        return base * warmup ** 0.5 * min(s ** -0.5, s * warmup ** -1.5)  # warmup_lr.py:43-50
+
+    def allreduce(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            self.comm.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm):
+                dist.all_reduce(self.pack.gflat)
+            torch.cuda.current_stream().wait_stream(self.comm)
+
+    def step(self, i, e2e=False):
+        bstep, pack, cfg = self.bstep, self.pack, self.cfg
+        self.step_no += 1
+        if e2e:
+            b = {k: v.to(self.dev, non_blocking=True) for k, v in self.host_batches[i % 4].items()}
+        else:
+            b = self.dev_batches[i % 4]
+        pack.refresh()
+        pack.zero_grad()
+        draws = {k: b[k] for k in ("center", "warped", "fmask", "tmask")}
+        feats, flens = bstep.frontend_fwd(b["wav"], b["lens"], self.mel, cfg, draws)
+        # trainer.py:594-606: loss is the batch-weighted mean over ranks, DDP averages -> net scale 1/world on summed grads
+        out = bstep.train_step_from_feats(feats, flens, b["text"], b["tl"], pack.P, pack.W, pack.G, cfg,
+                                          bstep.StepCtx(self.step_no * 7919 + self.rank, True), bn_buffers=self.bn)
+        pack.finalize_grads()
+        self.allreduce()
+        self.ops.adam_step(pack.flat32, pack.gflat, self.m, self.v, self.lr(), self.step_no, self.state,
+                           grad_inv_scale=1.0 / self.world, max_norm=5.0)
+        if e2e:
+            res = torch.cat([out["loss"], out["loss_ctc"], out["loss_att"], out["acc"]])
+            self.loss_host.copy_(res, non_blocking=True)
+        return out
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from espnet_slurp_b200 import _lib
+    lib = _lib.lib()
+    cfg = build_cfg(args)
+    tr = Trainer(args, cfg, rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(n, e2e):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for i in range(n):
+            last = tr.step(i, e2e=e2e)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item(), last
+
+    for i in range(args.warmup):
+        tr.step(i)
+    clocks = Clocks(local)
+    clocks.start()
+    lib.b200slu_prof_reset()
+    ms, last = timed(args.steps, e2e=False)
+    launches = lib.b200slu_prof_total_launches()
+    clk = clocks.stop()
+    ms_e2e, last2 = timed(args.steps, e2e=True)
+    loss_val = float(tr.loss_host[0])
+    audio = sum(tr.audio_sec[i % 4] for i in range(args.steps))
+    tot = torch.tensor([audio], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tot)
+    total_audio = tot.item()
+
+    # per-kernel-family device time (separate pass: CUDA events around every launch, on the launching stream)
+    fams = {}
+    if not args.no_prof:
+        import ctypes as C
+        lib.b200slu_prof_reset()
+        lib.b200slu_prof_enable_timing(1)
+        nprof = 2
+        for i in range(nprof):
+            tr.step(i)
+        torch.cuda.synchronize()
+        lib.b200slu_prof_enable_timing(0)
+        for f in range(lib.b200slu_prof_num_families()):
+            o = (C.c_double * 4)()
+            lib.b200slu_prof_get(f, o)
+            if o[0] > 0:
+                fams[lib.b200slu_prof_family_name(f).decode()] = {"launches_per_step": o[0] / nprof, "ms_per_step": o[1] / nprof,
+                                                                 "flops_per_step": o[2] / nprof, "bytes_per_step": o[3] / nprof}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)  # kernels are timed inside a long step -> sustained figure
+    roof = None
+    if "gemm_tcgen05" in fams and fams["gemm_tcgen05"]["ms_per_step"] > 0:
+        g = fams["gemm_tcgen05"]
+        ach = g["flops_per_step"] / (g["ms_per_step"] * 1e-3) / 1e12
+        roof = {"kernel": "gemm_bf16_tcgen05 (all GEMM launches of one step)", "bound": "tensor", "achieved": round(ach, 1),
+                "peak": tf_peak, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback",
+                "unit": "TFLOP/s", "frac": round(ach / tf_peak, 4), "traffic": None,
+                "launches_per_step": g["launches_per_step"], "avg_launch_us": round(1e3 * g["ms_per_step"] / g["launches_per_step"], 2),
+                "share_of_step_device_time": round(g["ms_per_step"] / sum(f["ms_per_step"] for f in fams.values()), 3)}
+    line = {
+        "metric": "audio-sec/sec train throughput, SLURP Conformer", "value": round(total_audio / (ms * 1e-3), 1),
+        "unit": "audio-sec/sec", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"egs2/slurp Conformer SLU train step: {cfg.enc.blocks} enc blocks d=512 H=8 ffn=2048 K=31 rel-pos "
+                               f"{cfg.enc.rel_pos_type}, {cfg.dec.blocks} dec blocks, V={cfg.vocab}, ctc 0.3, lsm 0.1, dropout 0.1, "
+                               f"SpecAug on, raw 16 kHz waveforms U[{args.min_sec},{args.max_sec}] s, {args.batch} utt/GPU; "
+                               "fwd+bwd+grad all-reduce+clip+Adam",
+                   "batch_per_gpu": args.batch, "global_batch": args.batch * world, "parallelism": f"dp{world}",
+                   "l2": "per-step working set (activations + 1.3 GB of weights/grads/moments) >> 126 MB L2; 4 rotating batches"},
+        "e2e": {"value": round(total_audio / (ms_e2e * 1e-3), 1), "unit": "audio-sec/sec", "ms_per_step": round(ms_e2e / args.steps, 3),
+                "h2d_bytes_per_step": tr.h2d_bytes, "d2h_bytes_per_step": 16},
+        "gpu_launches": int(launches), "gpu_launches_per_step": round(launches / args.steps, 1),
+        "clocks": clk, "loss": loss_val, "roofline": roof, "families": fams,
+    }
+    if not args.no_cpu_baseline and world >= 1:
+        v, sec, cores, audio_cpu = cpu_step_time(args, cfg, 1, 1, args.cpu_batch)
+        line["cpu_baseline"] = {"value": round(v, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                                "sample": f"1 warm-up + 1 timed fwd+bwd step of the same model on {args.cpu_batch} utterances "
+                                          f"({audio_cpu:.1f} audio-s), oracle/model.py fp32, {sec:.1f} s/step"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    cfg = build_cfg(args)
+    # size the per-step sample so that warmup + steps stay within a few minutes of host time
+    t0 = time.perf_counter()
+    v, sec, cores, audio = cpu_step_time(args, cfg, 1, 0, 2)
+    per_utt = sec / 2
+    budget = 150.0
+    b = int(max(1, min(args.cpu_batch, budget / max(1e-3, per_utt * (args.steps + args.warmup)))))
+    v, sec, cores, audio = cpu_step_time(args, cfg, args.steps, args.warmup, b)
+    line = {"impl": "reference", "metric": "audio-sec/sec train throughput, SLURP Conformer", "value": round(v, 2),
+            "unit": "audio-sec/sec", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(sec * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": f"same model and synthetic waveforms as the GPU arm; each step = {b} utterances ({audio:.1f} "
+                                   "audio-s) fwd+bwd on the host cores (no optimizer)", "batch_per_step": b},
+            "cpu_baseline": {"value": round(v, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                             "sample": f"{args.steps} timed steps of {b} utterances, oracle/model.py (CPU restatement of the "
+                                       "reference's PyTorch path, pinned to its goldens), fp32, torch CPU threads = cores"},
+            "e2e": {"value": round(v, 2), "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

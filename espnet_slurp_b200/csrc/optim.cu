@@ -1,0 +1,79 @@
+// Fused optimizer step over the flat parameter / gradient buffers: global L2 grad-norm, clip, non-finite
+// skip, Adam (+ L2 weight decay as torch.optim.Adam applies it) -- SURVEY.md 8(f) row N1.
+//
+// Replaces espnet2/train/trainer.py:640-690: torch.nn.utils.clip_grad_norm_(max_norm=grad_clip, norm_type=2),
+// "grad norm is not finite -> skip the update" (:651-667), optimizer.step() (torch.optim.Adam, registry
+// espnet2/tasks/abs_task.py:856-880).  The learning rate for the step comes from the host (WarmupLR,
+// espnet2/schedulers/warmup_lr.py:43-50).  Two launches: a grid-wide sum of squares into one double, then one
+// pass that reads g, p, m, v and writes p, m, v: 28 bytes per parameter, memory-bound.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g, long long n, float inv_scale,
+                                                    double* __restrict__ out) {
+  __shared__ float red[32];
+  float s = 0.f;
+  const long long n4 = n >> 2;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(g)[i];
+    const float a = v.x * inv_scale, b = v.y * inv_scale, c = v.z * inv_scale, d = v.w * inv_scale;
+    s += a * a + b * b + c * c + d * d;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const float a = g[(n4 << 2) + threadIdx.x] * inv_scale;
+    s += a * a;
+  }
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) atomicAdd(out, (double)s);
+}
+
+// state[0] = sum of squares (in), state[1] = grad norm (out), state[2] = 1 if the update was applied (out)
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                   float* __restrict__ v, long long n, float lr, float beta1, float beta2,
+                                                   float eps, float weight_decay, float bc1, float bc2, float inv_scale,
+                                                   float max_norm, double* __restrict__ state) {
+  const double ss = state[0];
+  const float norm = (float)sqrt(ss);
+  const bool ok = isfinite(norm);
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    state[1] = (double)norm;
+    state[2] = ok ? 1.0 : 0.0;
+  }
+  if (!ok) return;
+  float coef = inv_scale;
+  if (max_norm > 0.f) coef *= fminf(1.f, max_norm / (norm + 1e-6f));
+  const float step_size = lr / bc1;
+  const float inv_sqrt_bc2 = rsqrtf(bc2);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float gi = g[i] * coef;
+    const float pi = p[i];
+    if (weight_decay != 0.f) gi += weight_decay * pi;
+    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] = pi - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+  }
+}
+
+}  // namespace
+
+// state: 3 doubles on the device (zeroed here).  grad_inv_scale multiplies every gradient first (e.g. 1/accum_grad).
+extern "C" int b200slu_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                                 float beta1, float beta2, float eps, float weight_decay, int step, float grad_inv_scale,
+                                 float max_norm, double* state3, void* stream) {
+  B2_CHECK_ARG(n > 0 && step >= 1 && ((uintptr_t)grads % 16) == 0, "adam_step: n > 0, step >= 1, 16-byte aligned gradients");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CUDA(cudaMemsetAsync(state3, 0, 3 * sizeof(double), st));
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 32.0 * n);
+  sumsq_kernel<<<b2_grid_for(n >> 2, 256, 4), 256, 0, st>>>(grads, n, grad_inv_scale, state3);
+  B2_LAUNCH_CHECK();
+  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  adam_kernel<<<b2_grid_for(n, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
+                                                      bc1, bc2, grad_inv_scale, max_norm, state3);
+  B2_LAUNCH_CHECK();
+  return 0;
+}

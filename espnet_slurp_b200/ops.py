@@ -364,6 +364,8 @@ def logmel(wav, lens, melmat, n_fft: int = 512, hop: int = 128):
     B, N = wav.shape
     T = N // hop + 1
     n_mels = melmat.shape[1]
+    melmat = melmat.contiguous()  # numpy hands over the (n_freq, n_mels) table as a transposed view
+    assert wav.stride(1) == 1 and lens.dtype == torch.int32
     feats = torch.empty(B, T, n_mels, device=wav.device, dtype=torch.float32)
     flens = torch.empty(B, device=wav.device, dtype=torch.int32)
     check(_lib.lib().b200slu_logmel_fwd(ptr(wav), wav.stride(0), B, N, ptr(lens), ptr(melmat), n_fft, hop, n_mels, ptr(feats),
@@ -383,3 +385,12 @@ def specaug_mvn(x, lens, center=None, warped=None, fmask=None, tmask=None, do_mv
 
 def rel_shift_index(i: int, j: int, T: int, mode: str) -> int:
     return _lib.lib().b200slu_rel_shift_index(i, j, T, RELPOS[mode])
+
+
+# ---- optimizer ----------------------------------------------------------------------------------------------------
+def adam_step(params, grads, exp_avg, exp_avg_sq, lr: float, step: int, state3, betas=(0.9, 0.999), eps: float = 1e-8,
+              weight_decay: float = 0.0, grad_inv_scale: float = 1.0, max_norm: float = 5.0):
+    """In-place fused clip + Adam over flat fp32 buffers; state3 = float64[3] (sumsq, grad norm, applied flag)."""
+    check(_lib.lib().b200slu_adam_step(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), lr, betas[0],
+                                       betas[1], eps, weight_decay, step, grad_inv_scale, max_norm, ptr(state3), stream_ptr()),
+          "adam_step")

@@ -197,6 +197,13 @@ int b200slu_specaug_mvn_fwd(const float* x, int B, int T, int F, const int* lens
                             const int* freq_masks, int n_freq_masks, const int* time_masks, int n_time_masks, int do_mvn,
                             float* y, void* stream);
 
+/* ---- N1: fused optimizer step over the flat buffers (espnet2/train/trainer.py:640-690: clip_grad_norm_ 2-norm,
+ * non-finite skip, torch.optim.Adam; lr from WarmupLR espnet2/schedulers/warmup_lr.py:43-50) ----------------
+ * state3 (device, 3 doubles): [0] sum of squares, [1] gradient norm, [2] 1 if the update was applied. */
+int b200slu_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
+                      float beta2, float eps, float weight_decay, int step, float grad_inv_scale, float max_norm,
+                      double* state3, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

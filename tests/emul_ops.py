@@ -371,3 +371,20 @@ def specaug_mvn(x, lens, center=None, warped=None, fmask=None, tmask=None, do_mv
         }
         y = om.spec_augment(x, lens.long(), draws)
     return om.utterance_mvn(y, lens.long()) if do_mvn else y
+
+
+def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, state3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
+              grad_inv_scale=1.0, max_norm=5.0):
+    g = grads * grad_inv_scale
+    norm = g.double().pow(2).sum().sqrt()
+    state3[0], state3[1], state3[2] = norm ** 2, norm, float(torch.isfinite(norm))
+    if not torch.isfinite(norm):
+        return
+    if max_norm > 0:
+        g = g * min(1.0, max_norm / (norm.item() + 1e-6))
+    if weight_decay:
+        g = g + weight_decay * params
+    exp_avg.mul_(betas[0]).add_(g, alpha=1 - betas[0])
+    exp_avg_sq.mul_(betas[1]).addcmul_(g, g, value=1 - betas[1])
+    bc1, bc2 = 1 - betas[0] ** step, 1 - betas[1] ** step
+    params.addcdiv_(exp_avg, exp_avg_sq.sqrt() / math.sqrt(bc2) + eps, value=-lr / bc1)

