@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--dec-blocks", type=int, default=6)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-prof", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-batch", type=int, default=8)
     return ap.parse_args()
 
@@ -212,28 +213,59 @@ class Trainer:
                 dist.all_reduce(self.pack.gflat)
             torch.cuda.current_stream().wait_stream(self.comm)
 
-    def step(self, i, e2e=False):
-        bstep, pack, cfg = self.bstep, self.pack, self.cfg
-        self.step_no += 1
-        if e2e:
-            b = {k: v.to(self.dev, non_blocking=True) for k, v in self.host_batches[i % 4].items()}
-        else:
-            b = self.dev_batches[i % 4]
+    # ---- the step body: only device-resident inputs (self.inp, the 24-byte step params), no host values -> capturable
+    def body(self):
+        bstep, pack, cfg, b = self.bstep, self.pack, self.cfg, self.inp
         pack.refresh()
         pack.zero_grad()
         draws = {k: b[k] for k in ("center", "warped", "fmask", "tmask")}
         feats, flens = bstep.frontend_fwd(b["wav"], b["lens"], self.mel, cfg, draws)
         # trainer.py:594-606: loss is the batch-weighted mean over ranks, DDP averages -> net scale 1/world on summed grads
         out = bstep.train_step_from_feats(feats, flens, b["text"], b["tl"], pack.P, pack.W, pack.G, cfg,
-                                          bstep.StepCtx(self.step_no * 7919 + self.rank, True), bn_buffers=self.bn)
+                                          bstep.StepCtx(1000003 * (self.rank + 1), True), bn_buffers=self.bn)
         pack.finalize_grads()
+        self.res = torch.cat([out["loss"], out["loss_ctc"], out["loss_att"], out["acc"]])
+
+    def tail(self):
         self.allreduce()
-        self.ops.adam_step(pack.flat32, pack.gflat, self.m, self.v, self.lr(), self.step_no, self.state,
+        self.ops.adam_step(self.pack.flat32, self.pack.gflat, self.m, self.v, 0.0, 0, self.state,
                            grad_inv_scale=1.0 / self.world, max_norm=5.0)
+
+    def setup_static(self):
+        import numpy as np
+        self.inp = {k: torch.empty_like(v) for k, v in self.dev_batches[0].items()}
+        self.sp_host = torch.zeros(64, 24, dtype=torch.uint8).pin_memory()
+        self.sp_np = self.sp_host.numpy().view(np.dtype([("seed", "<u8"), ("lr", "<f4"), ("bc1", "<f4"), ("bc2", "<f4"), ("pad", "<f4")]))
+        self.sp_dev = torch.zeros(24, dtype=torch.uint8, device=self.dev)
+        self.ops.set_step_params(self.sp_dev)
+        self.graph = None
+
+    def capture(self):
+        """Whole step (cast -> front-end -> fwd -> bwd [-> Adam when single-GPU]) as ONE CUDA graph."""
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.body()
+            if self.world == 1:
+                self.tail()
+        self.graph = g
+
+    def step(self, i, e2e=False):
+        self.step_no += 1
+        slot = self.step_no % 64
+        self.sp_np[slot] = (self.step_no * 0x9E3779B97F4A7C15 % (1 << 64), self.lr(), 1 - 0.9 ** self.step_no, 1 - 0.999 ** self.step_no, 0.0)
+        self.sp_dev.copy_(self.sp_host[slot], non_blocking=True)
+        src = self.host_batches[i % 4] if e2e else self.dev_batches[i % 4]
+        for k, v in src.items():
+            self.inp[k].copy_(v, non_blocking=True)
+        if self.graph is not None:
+            self.graph.replay()
+            if self.world > 1:
+                self.tail()
+        else:
+            self.body()
+            self.tail()
         if e2e:
-            res = torch.cat([out["loss"], out["loss_ctc"], out["loss_att"], out["acc"]])
-            self.loss_host.copy_(res, non_blocking=True)
-        return out
+            self.loss_host.copy_(self.res, non_blocking=True)
 
 
 def run_ours(args):
@@ -268,13 +300,22 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item(), last
 
+    tr.setup_static()
+    for i in range(2):
+        tr.step(i)  # eager: one-time kernel attribute / driver-entry-point setup happens outside any capture
+    torch.cuda.synchronize()
+    lib.b200slu_prof_reset()
+    tr.step(2)
+    tr.launches_per_step = lib.b200slu_prof_total_launches()  # counted on an eager step; a graph replay issues the same kernels
+    if not args.no_graph:
+        tr.capture()
     for i in range(args.warmup):
         tr.step(i)
     clocks = Clocks(local)
     clocks.start()
     lib.b200slu_prof_reset()
     ms, last = timed(args.steps, e2e=False)
-    launches = lib.b200slu_prof_total_launches()
+    launches = lib.b200slu_prof_total_launches() if args.no_graph else tr.launches_per_step * args.steps
     clk = clocks.stop()
     ms_e2e, last2 = timed(args.steps, e2e=True)
     loss_val = float(tr.loss_host[0])
@@ -291,6 +332,7 @@ def run_ours(args):
         lib.b200slu_prof_reset()
         lib.b200slu_prof_enable_timing(1)
         nprof = 2
+        tr.graph = None  # eager launches so that every kernel can be bracketed by events
         for i in range(nprof):
             tr.step(i)
         torch.cuda.synchronize()
@@ -328,7 +370,7 @@ def run_ours(args):
         "config": {"workload": f"egs2/slurp Conformer SLU train step: {cfg.enc.blocks} enc blocks d=512 H=8 ffn=2048 K=31 rel-pos "
                                f"{cfg.enc.rel_pos_type}, {cfg.dec.blocks} dec blocks, V={cfg.vocab}, ctc 0.3, lsm 0.1, dropout 0.1, "
                                f"SpecAug on, raw 16 kHz waveforms U[{args.min_sec},{args.max_sec}] s, {args.batch} utt/GPU; "
-                               "fwd+bwd+grad all-reduce+clip+Adam",
+                               "fwd+bwd+grad all-reduce+clip+Adam" + ("" if args.no_graph else "; whole step replayed as one CUDA graph"),
                    "batch_per_gpu": args.batch, "global_batch": args.batch * world, "parallelism": f"dp{world}",
                    "l2": "per-step working set (activations + 1.3 GB of weights/grads/moments) >> 126 MB L2; 4 rotating batches"},
         "e2e": {"value": round(total_audio / (ms_e2e * 1e-3), 1), "unit": "audio-sec/sec", "ms_per_step": round(ms_e2e / args.steps, 3),

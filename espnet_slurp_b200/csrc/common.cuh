@@ -115,7 +115,20 @@ struct B2Dropout {
   unsigned long long seed;  // per training step
   unsigned int site;        // unique per dropout site
   float p;                  // drop probability; 0 => disabled
+  const unsigned long long* dev_seed;  // optional device-resident per-step seed, XORed in (CUDA-graph replays)
 };
+
+// Device-resident per-step parameters registered with b200slu_set_step_params (runtime.cu): lets a captured CUDA
+// graph of the whole step be replayed with a fresh dropout seed / learning rate by updating 24 bytes.
+struct B2StepParams {
+  unsigned long long seed;
+  float lr, bc1, bc2, reserved;
+};
+const B2StepParams* b2_step_params();
+static inline B2Dropout b2_make_drop(float p, unsigned long long seed, unsigned int site) {
+  const B2StepParams* sp = b2_step_params();
+  return B2Dropout{seed, site, p, sp ? &sp->seed : nullptr};
+}
 
 __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
@@ -132,7 +145,8 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 
 // keep-mask (bit i set = keep) for elements [8*group, 8*group+8)
 __device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned long long group) {
-  uint2 key = make_uint2((uint32_t)d.seed ^ (d.site * 0x9E3779B9u), (uint32_t)(d.seed >> 32) + d.site);
+  const unsigned long long sd = d.dev_seed != nullptr ? (d.seed ^ *d.dev_seed) : d.seed;
+  uint2 key = make_uint2((uint32_t)sd ^ (d.site * 0x9E3779B9u), (uint32_t)(sd >> 32) + d.site);
   uint4 r = philox4x32_10(make_uint4((uint32_t)group, (uint32_t)(group >> 32), d.site, 0x5eedu), key);
   uint32_t thr = (uint32_t)(d.p * 65536.f);
   uint32_t m = 0;

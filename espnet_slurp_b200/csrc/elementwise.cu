@@ -159,7 +159,7 @@ extern "C" int b200slu_cast_bf16(const float* x, void* y, long long n, float alp
   B2_CHECK_ARG(!(drop_p > 0.f) || n % 8 == 0, "cast_bf16: dropout needs n %% 8 == 0");
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * n);
-  cast_kernel<<<b2_grid_for(n >> 3, 256), 256, 0, st>>>(x, (bf16*)y, n, alpha, B2Dropout{seed, site, drop_p});
+  cast_kernel<<<b2_grid_for(n >> 3, 256), 256, 0, st>>>(x, (bf16*)y, n, alpha, b2_make_drop(drop_p, seed, site));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -208,7 +208,7 @@ extern "C" int b200slu_embed_fwd(const float* emb, const int* tokens, const floa
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 12.0 * R * d);
   embed_fwd_kernel<<<b2_grid_for((long long)R * (d >> 3), 256), 256, 0, st>>>(emb, tokens, pe, R, L, d, scale, x,
-                                                                              B2Dropout{seed, site, drop_p});
+                                                                              b2_make_drop(drop_p, seed, site));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -219,7 +219,7 @@ extern "C" int b200slu_embed_bwd(const float* dx, const int* tokens, int R, int 
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 12.0 * R * d);
   embed_bwd_kernel<<<b2_grid_for((long long)R * (d >> 3), 256), 256, 0, st>>>(dx, tokens, R, d, scale, demb_accum,
-                                                                              B2Dropout{seed, site, drop_p});
+                                                                              b2_make_drop(drop_p, seed, site));
   B2_LAUNCH_CHECK();
   return 0;
 }

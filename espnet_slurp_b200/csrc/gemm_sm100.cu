@@ -520,9 +520,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     ep.act = e->act;
     ep.out_f32 = e->out_f32;
     ep.accumulate = e->accumulate;
-    ep.drop.p = e->dropout_p;
-    ep.drop.seed = e->dropout_seed;
-    ep.drop.site = e->dropout_site;
+    ep.drop = b2_make_drop(e->dropout_p, e->dropout_seed, e->dropout_site);
   }
   B2_CHECK_ARG(nbatch == 1 || (ep.res == nullptr && ep.aux == nullptr && ep.pre_out == nullptr && !(ep.drop.p > 0.f)),
                "gemm: batched mode supports only bias / activation / alpha epilogues");

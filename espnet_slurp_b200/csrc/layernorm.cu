@@ -182,7 +182,7 @@ extern "C" int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float*
   B2_CHECK_ARG(M > 0 && D > 0 && D % 8 == 0 && D <= 2048, "layernorm_bwd: need D %% 8 == 0 and D <= 2048 (M=%d D=%d)", M, D);
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = b2_grid_for((long long)M * 32, 256, 4);
-  B2Dropout drop{seed, site, drop_p};
+  B2Dropout drop = b2_make_drop(drop_p, seed, site);
   const size_t smem = 2 * (size_t)D * sizeof(float);
   B2_SCOPE(FAM_LN, st, 0,
            (double)M * D * ((dy_is_f32 ? 4.0 : 2.0) + 4.0 + 4.0 + (dx_add ? 4.0 : 0.0) + (g_bf16 ? 2.0 : 0.0)));

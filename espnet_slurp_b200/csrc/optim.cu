@@ -34,7 +34,13 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ g,
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, long long n, float lr, float beta1, float beta2,
                                                    float eps, float weight_decay, float bc1, float bc2, float inv_scale,
-                                                   float max_norm, double* __restrict__ state) {
+                                                   float max_norm, double* __restrict__ state,
+                                                   const B2StepParams* __restrict__ sp) {
+  if (sp != nullptr) {  // per-step values live on the device (CUDA-graph replay): lr, 1 - beta1^t, 1 - beta2^t
+    lr = sp->lr;
+    bc1 = sp->bc1;
+    bc2 = sp->bc2;
+  }
   const double ss = state[0];
   const float norm = (float)sqrt(ss);
   const bool ok = isfinite(norm);
@@ -62,18 +68,21 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
 }  // namespace
 
 // state: 3 doubles on the device (zeroed here).  grad_inv_scale multiplies every gradient first (e.g. 1/accum_grad).
+// step >= 1: lr and the bias corrections come from the arguments; step == 0: from the registered device step params.
 extern "C" int b200slu_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                                  float beta1, float beta2, float eps, float weight_decay, int step, float grad_inv_scale,
                                  float max_norm, double* state3, void* stream) {
-  B2_CHECK_ARG(n > 0 && step >= 1 && ((uintptr_t)grads % 16) == 0, "adam_step: n > 0, step >= 1, 16-byte aligned gradients");
+  B2_CHECK_ARG(n > 0 && step >= 0 && ((uintptr_t)grads % 16) == 0, "adam_step: n > 0, step >= 0, 16-byte aligned gradients");
+  B2_CHECK_ARG(step >= 1 || b2_step_params() != nullptr, "adam_step: step == 0 needs b200slu_set_step_params");
   cudaStream_t st = (cudaStream_t)stream;
   B2_CUDA(cudaMemsetAsync(state3, 0, 3 * sizeof(double), st));
   B2_SCOPE(FAM_ELEMWISE, st, 0, 32.0 * n);
   sumsq_kernel<<<b2_grid_for(n >> 2, 256, 4), 256, 0, st>>>(grads, n, grad_inv_scale, state3);
   B2_LAUNCH_CHECK();
-  const float bc1 = 1.f - powf(beta1, (float)step), bc2 = 1.f - powf(beta2, (float)step);
+  const float bc1 = step >= 1 ? 1.f - powf(beta1, (float)step) : 1.f, bc2 = step >= 1 ? 1.f - powf(beta2, (float)step) : 1.f;
   adam_kernel<<<b2_grid_for(n, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
-                                                      bc1, bc2, grad_inv_scale, max_norm, state3);
+                                                      bc1, bc2, grad_inv_scale, max_norm, state3,
+                                                      step >= 1 ? nullptr : b2_step_params());
   B2_LAUNCH_CHECK();
   return 0;
 }

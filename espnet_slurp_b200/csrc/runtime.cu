@@ -16,6 +16,13 @@ void b200slu_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static const B2StepParams* g_step_params = nullptr;
+const B2StepParams* b2_step_params() { return g_step_params; }
+extern "C" int b200slu_set_step_params(const void* dev_ptr) {
+  g_step_params = (const B2StepParams*)dev_ptr;
+  return 0;
+}
+
 int b2_num_sms() {
   static int n = 0;
   if (n == 0) {

@@ -192,7 +192,7 @@ extern "C" int b200slu_softmax_fwd(const float* ac, long long ld_ac, const float
   const long long rows = (long long)H * B * Tq;
   const int grid = b2_grid_for(rows * 32, 256, 8);
   B2_SCOPE(FAM_ATTN, st, 0, (double)rows * Tk * (4.0 + (relpos_mode ? 4.0 : 0.0) + 2.0 + (drop_p > 0.f ? 2.0 : 0.0)));
-  B2Dropout drop{seed, site, drop_p};
+  B2Dropout drop = b2_make_drop(drop_p, seed, site);
 #define SM_F(NG) softmax_fwd_kernel<NG><<<grid, 256, 0, st>>>(ac, bd, a, (bf16*)p, (bf16*)p_drop, drop)
   if (ld_p <= 256) SM_F(1);
   else if (ld_p <= 512) SM_F(2);
@@ -216,7 +216,7 @@ extern "C" int b200slu_softmax_bwd(const float* dp_drop, const void* p, long lon
   const size_t smem = d_bd != nullptr ? (size_t)(threads / 32) * ld_p * sizeof(float) : 0;
   const int grid = b2_grid_for(rows * 32, threads, 4);
   B2_SCOPE(FAM_ATTN, st, 0, (double)rows * Tk * (4.0 + 2.0 + 2.0) + (d_bd ? 2.0 * rows * ld_bd : 0.0));
-  B2Dropout drop{seed, site, drop_p};
+  B2Dropout drop = b2_make_drop(drop_p, seed, site);
 #define SM_B(NG)                                                                                                  \
   do {                                                                                                            \
     static bool cfg = false;                                                                                      \

@@ -394,3 +394,8 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, lr: float, step: int, state3, 
     check(_lib.lib().b200slu_adam_step(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), lr, betas[0],
                                        betas[1], eps, weight_decay, step, grad_inv_scale, max_norm, ptr(state3), stream_ptr()),
           "adam_step")
+
+
+def set_step_params(dev_tensor):
+    """Register (or with None unregister) the 24-byte device buffer {u64 seed; f32 lr, bc1, bc2, pad}."""
+    check(_lib.lib().b200slu_set_step_params(ptr(dev_tensor)), "set_step_params")

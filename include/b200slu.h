@@ -51,6 +51,12 @@ int b200slu_prof_get(int fam, double* out4);
 /* total kernel launches issued by this library since the last reset */
 long long b200slu_prof_total_launches(void);
 
+/* Device-resident per-step parameters {uint64 dropout seed; float lr, 1-beta1^t, 1-beta2^t, reserved} (24 bytes).
+ * When registered, every dropout site XORs the device seed into its seed argument and b200slu_adam_step(step = 0)
+ * reads lr / bias corrections from it, so a CUDA graph of the whole step replays with fresh values after a 24-byte
+ * copy.  NULL unregisters.  Process-global (one training process per GPU, abs_task.py:1049-1070). */
+int b200slu_set_step_params(const void* dev_ptr);
+
 /* ---- K2: GEMM with fused epilogue ------------------------------------------------------
  * Replaces the nn.Linear / Conv1d(k=1) / im2col-Conv2d GEMMs:
  *   espnet/nets/pytorch_backend/transformer/attention.py:33-36,232 (linear_q/k/v/out/pos)

@@ -1,0 +1,86 @@
+"""Time every distinct GEMM call of one train step in isolation (CUDA events) -> table sorted by total time per step."""
+import sys, os, json, collections
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import ctypes as C
+from espnet_slurp_b200 import ops, _lib
+
+calls = collections.OrderedDict()
+lib = _lib.lib()
+orig = lib.b200slu_gemm_bf16_ex
+
+def key_of(g, ep):
+    return (g.trans_a, g.trans_b, g.M, g.N, g.K, g.batch_inner, g.batch_outer, int(bool(ep.bias)), ep.act, int(bool(ep.pre_act_out)),
+            int(ep.dropout_p > 0), int(bool(ep.act_grad_input)), int(bool(ep.residual)), ep.out_f32, ep.accumulate)
+
+class Rec:
+    def __call__(self, gp, epp, st):
+        g = C.cast(gp, C.POINTER(_lib.GemmDesc)).contents
+        ep = C.cast(epp, C.POINTER(_lib.Epilogue)).contents
+        k = key_of(g, ep)
+        if k not in calls:
+            gc, ec = _lib.GemmDesc(), _lib.Epilogue()
+            C.memmove(C.addressof(gc), gp, C.sizeof(gc)); C.memmove(C.addressof(ec), epp, C.sizeof(ec))
+            calls[k] = [0, gc, ec]
+        calls[k][0] += 1
+        return orig(gp, epp, st)
+
+def main():
+    sys.argv = [sys.argv[0]] + sys.argv[1:]
+    import bench
+    args = bench.parse()
+    cfg = bench.build_cfg(args)
+    torch.cuda.set_device(0)
+    tr = bench.Trainer(args, cfg, 0, 1)
+    tr.setup_static()
+    tr.step(0)
+    torch.cuda.synchronize()
+    lib.b200slu_gemm_bf16_ex = Rec()
+    keep = []
+    # keep every buffer of the recorded step alive: run body with references retained by disabling frees is hard, so
+    # re-time each config on fresh scratch buffers of the same shape instead
+    tr.step(1)
+    torch.cuda.synchronize()
+    lib.b200slu_gemm_bf16_ex = orig
+    rows = []
+    st = torch.cuda.current_stream().cuda_stream
+    for k, (n, g, ep) in calls.items():
+        ta, tb, M, N, K, bi, bo = k[:7]
+        nb = bi * bo
+        # fresh operands with the recorded strides (attention operands are views with row stride 512/1536)
+        def alloc(rows_, ld, si, so, nbi, nbo):
+            span = max(rows_ * ld, si * nbi if si else 0, so * nbo if so else 0, 1) + 4096
+            return torch.randn(span, device="cuda").bfloat16()
+        Ar = (K if ta else M); Br = (K if tb else N)
+        A = alloc(Ar, g.lda, g.a_stride_inner, g.a_stride_outer, bi, bo)
+        Bm = alloc(Br, g.ldb, g.b_stride_inner, g.b_stride_outer, bi, bo)
+        csz = max(M * g.ldc, g.c_stride_inner * bi, g.c_stride_outer * bo) + 4096
+        Cm = torch.zeros(csz, device="cuda", dtype=torch.float32 if ep.out_f32 else torch.bfloat16)
+        g.A, g.B, g.C = A.data_ptr(), Bm.data_ptr(), Cm.data_ptr()
+        bufs = []
+        if ep.bias: t = torch.zeros(N + 8, device="cuda"); ep.bias = t.data_ptr(); bufs.append(t)
+        if ep.pre_act_out: t = torch.zeros(csz, device="cuda", dtype=torch.bfloat16); ep.pre_act_out = t.data_ptr(); bufs.append(t)
+        if ep.act_grad_input: t = torch.randn(M * ep.ld_act_grad_input + 4096, device="cuda").bfloat16(); ep.act_grad_input = t.data_ptr(); bufs.append(t)
+        if ep.residual: t = torch.zeros(M * ep.ld_residual + 4096, device="cuda"); ep.residual = t.data_ptr(); bufs.append(t)
+        for _ in range(3):
+            _lib.check(orig(C.addressof(g), C.addressof(ep), st))
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 20
+        e0.record()
+        for _ in range(reps):
+            orig(C.addressof(g), C.addressof(ep), st)
+        e1.record(); torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / reps
+        fl = 2.0 * M * N * K * nb
+        rows.append((n * us, n, us, fl / us / 1e6, k))
+    rows.sort(reverse=True)
+    tot = sum(r[0] for r in rows)
+    print(f"total GEMM time/step (isolated, back-to-back, warm L2): {tot/1e3:.2f} ms over {sum(r[1] for r in rows)} launches")
+    print("tot_us  n  us/launch  TFLOP/s  (ta,tb,M,N,K,bi,bo,bias,act,pre,drop,actgrad,res,f32,acc)")
+    for r in rows:
+        print(f"{r[0]:9.1f} {r[1]:4d} {r[2]:8.1f} {r[3]:8.1f}  {r[4]}")
+
+if __name__ == "__main__":
+    main()
