@@ -20,7 +20,7 @@ class Epilogue(C.Structure):
     _fields_ = [
         ("bias", C.c_void_p),
         ("act", C.c_int),
-        ("pre_act_out", C.c_void_p),
+        ("act_grad_out", C.c_void_p),
         ("alpha", C.c_float),
         ("dropout_p", C.c_float),
         ("dropout_seed", C.c_ulonglong),

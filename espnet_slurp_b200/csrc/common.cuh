@@ -89,7 +89,13 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+// sigmoid through ONE MUFU op (tanh.approx, rel. error 2^-11, far below the bf16 storage rounding of every consumer):
+// the exp + reciprocal form made the Swish epilogues of the FFN GEMMs MUFU-bound.
+__device__ __forceinline__ float sigmoidf_(float x) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * x));
+  return fmaf(0.5f, t, 0.5f);
+}
 __device__ __forceinline__ float swishf_(float x) { return x * sigmoidf_(x); }
 // d/dx [x*sigmoid(x)] = s + x*s*(1-s)
 __device__ __forceinline__ float swish_gradf_(float x) {
@@ -107,9 +113,9 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
 }
 
 // ---------------------------------------------------------------------------
-// counter-based dropout: Philox4x32-10 keyed by (seed, site); one call yields
+// counter-based dropout: splitmix64 keyed by (seed, site); two evaluations yield
 // 128 random bits = 8 x 16-bit lanes -> keep decisions for 8 consecutive
-// elements (element index = 8*ctr + lane).  Recomputed, never stored.
+// elements (element index = 8*group + lane).  Recomputed, never stored.
 // ---------------------------------------------------------------------------
 struct B2Dropout {
   unsigned long long seed;  // per training step
@@ -130,34 +136,31 @@ static inline B2Dropout b2_make_drop(float p, unsigned long long seed, unsigned 
   return B2Dropout{seed, site, p, sp ? &sp->seed : nullptr};
 }
 
-__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
-  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
-    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
-    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
-    key.x += W0;
-    key.y += W1;
-  }
-  return ctr;
+// splitmix64 finaliser: 64 well-mixed bits from a 64-bit counter (2 multiplies; ~3x cheaper than Philox4x32-10, which
+// made the dropout epilogues of the FFN GEMMs ALU-bound -- profiles/r1_gemm_shapes_v0.txt)
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
 }
 
-// keep-mask (bit i set = keep) for elements [8*group, 8*group+8)
+// keep-mask (bit i set = keep) for elements [8*group, 8*group+8): 8 x 16-bit uniform lanes compared with p * 65536
 __device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned long long group) {
   const unsigned long long sd = d.dev_seed != nullptr ? (d.seed ^ *d.dev_seed) : d.seed;
-  uint2 key = make_uint2((uint32_t)sd ^ (d.site * 0x9E3779B9u), (uint32_t)(sd >> 32) + d.site);
-  uint4 r = philox4x32_10(make_uint4((uint32_t)group, (uint32_t)(group >> 32), d.site, 0x5eedu), key);
-  uint32_t thr = (uint32_t)(d.p * 65536.f);
+  const unsigned long long key = splitmix64(sd + 0x9E3779B97F4A7C15ull * (unsigned long long)(d.site + 1u));
+  const unsigned long long c = key + (group << 1) * 0x9E3779B97F4A7C15ull;
+  const unsigned long long z0 = splitmix64(c), z1 = splitmix64(c + 0x9E3779B97F4A7C15ull);
+  const uint32_t thr = (uint32_t)(d.p * 65536.f);
+  const uint32_t a = (uint32_t)z0, b = (uint32_t)(z0 >> 32), e = (uint32_t)z1, f = (uint32_t)(z1 >> 32);
   uint32_t m = 0;
-  m |= ((r.x & 0xffffu) >= thr) << 0;
-  m |= ((r.x >> 16) >= thr) << 1;
-  m |= ((r.y & 0xffffu) >= thr) << 2;
-  m |= ((r.y >> 16) >= thr) << 3;
-  m |= ((r.z & 0xffffu) >= thr) << 4;
-  m |= ((r.z >> 16) >= thr) << 5;
-  m |= ((r.w & 0xffffu) >= thr) << 6;
-  m |= ((r.w >> 16) >= thr) << 7;
+  m |= ((a & 0xffffu) >= thr) << 0;
+  m |= ((a >> 16) >= thr) << 1;
+  m |= ((b & 0xffffu) >= thr) << 2;
+  m |= ((b >> 16) >= thr) << 3;
+  m |= ((e & 0xffffu) >= thr) << 4;
+  m |= ((e >> 16) >= thr) << 5;
+  m |= ((f & 0xffffu) >= thr) << 6;
+  m |= ((f >> 16) >= thr) << 7;
   return m;
 }
 

@@ -35,6 +35,11 @@ __device__ __forceinline__ void stage_glu(const bf16* __restrict__ pw1, int b, i
   }
 }
 
+// Each thread owns one channel and FR = 8 consecutive output frames: the K + 7 staged inputs it needs are read from
+// shared memory once into a sliding register window (4.75 LDS per output instead of K), weights stay in registers.
+constexpr int FR = 8;
+static_assert(TT == 4 * FR, "4 frame lanes of FR frames per block tile");
+
 __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict__ pw1, const float* __restrict__ w,
                                                          const float* __restrict__ bias, int B, int T, int C, int K,
                                                          bf16* __restrict__ out, float* __restrict__ sums) {
@@ -43,7 +48,7 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
   const int t0 = blockIdx.x * TT, c0 = blockIdx.y * CC, b = blockIdx.z;
   stage_glu(pw1, b, T, C, t0, c0, K, sm);
   __syncthreads();
-  const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;  // 4 frame lanes
+  const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;  // 4 frame lanes x FR frames
   const int c = c0 + cl;
   float s1 = 0.f, s2 = 0.f;
   if (c < C) {
@@ -51,16 +56,27 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
 #pragma unroll
     for (int k = 0; k < KMAX; ++k) wr[k] = k < K ? w[c * K + k] : 0.f;
     const float bs = bias[c];
-    for (int f = fr; f < TT; f += 4) {
-      const int t = t0 + f;
-      if (t >= T) break;
-      float acc = bs;
+    float acc[FR];
 #pragma unroll
-      for (int k = 0; k < KMAX; ++k)
-        if (k < K) acc += wr[k] * sm[f + k][cl];
-      out[((long long)b * T + t) * C + c] = __float2bfloat16(acc);
-      s1 += acc;
-      s2 += acc * acc;
+    for (int o = 0; o < FR; ++o) acc[o] = bs;
+    const int f0 = fr * FR;
+#pragma unroll
+    for (int j = 0; j < FR + KMAX - 1; ++j) {
+      if (j < FR + K - 1) {
+        const float v = sm[f0 + j][cl];
+#pragma unroll
+        for (int o = 0; o < FR; ++o)
+          if (j - o >= 0 && j - o < KMAX) acc[o] += wr[j - o] * v;  // wr[k] = 0 for k >= K
+      }
+    }
+#pragma unroll
+    for (int o = 0; o < FR; ++o) {
+      const int t = t0 + f0 + o;
+      if (t < T) {
+        out[((long long)b * T + t) * C + c] = __float2bfloat16(acc[o]);
+        s1 += acc[o];
+        s2 += acc[o] * acc[o];
+      }
     }
   }
   red[0][fr][cl] = s1;
@@ -72,6 +88,8 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
   }
 }
 
+// Backward: grid (channel tiles, utterance chunks); each block walks all its (utterance, time tile) pairs and keeps the
+// depthwise weight gradient in registers across them, so the global atomics are per block, not per tile.
 __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict__ d_dw, const bf16* __restrict__ pw1,
                                                          const float* __restrict__ w, int B, int T, int C, int K,
                                                          bf16* __restrict__ d_pw1, float* __restrict__ dw_accum,
@@ -79,50 +97,74 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
   __shared__ float sg[TT + KMAX - 1][CC];  // glu halo tile
   __shared__ float sd[TT + KMAX - 1][CC];  // d_dw halo tile
   __shared__ float swg[CC][KMAX + 1];      // block partial of dW (+ dbias in the last slot)
-  const int t0 = blockIdx.x * TT, c0 = blockIdx.y * CC, b = blockIdx.z;
+  const int c0 = blockIdx.x * CC;
   const int pad = (K - 1) / 2, nf = TT + K - 1;
-  stage_glu(pw1, b, T, C, t0, c0, K, sg);
-  for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
-    const int f = it / (CC / 8), cg = it - f * (CC / 8);
-    const int t = t0 - pad + f, c = c0 + cg * 8;
-    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (t >= 0 && t < T && c < C) load8_bf16(d_dw + ((long long)b * T + t) * C + c, g);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sd[f][cg * 8 + j] = g[j];
-  }
-  for (int it = threadIdx.x; it < CC * (KMAX + 1); it += blockDim.x) (&swg[0][0])[it] = 0.f;
-  __syncthreads();
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;
   const int c = c0 + cl;
+  const int ntt = (T + TT - 1) / TT;
+  float wrev[KMAX], acc[KMAX];  // wrev[m] = w[K-1-m]: keeps every register-array index a compile-time constant
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    wrev[k] = (c < C && k < K) ? w[c * K + (K - 1 - k)] : 0.f;
+    acc[k] = 0.f;
+  }
+  float accb = 0.f;
+  for (int it = threadIdx.x; it < CC * (KMAX + 1); it += blockDim.x) (&swg[0][0])[it] = 0.f;
+  for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
+    const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
+    __syncthreads();  // previous tile fully consumed
+    stage_glu(pw1, b, T, C, t0, c0, K, sg);
+    for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
+      const int f = it / (CC / 8), cg = it - f * (CC / 8);
+      const int t = t0 - pad + f, cc = c0 + cg * 8;
+      float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (t >= 0 && t < T && cc < C) load8_bf16(d_dw + ((long long)b * T + t) * C + cc, g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sd[f][cg * 8 + j] = g[j];
+    }
+    __syncthreads();
+    if (c < C) {
+      const int f0 = fr * FR;
+      float dg[FR], dv[FR];
+#pragma unroll
+      for (int o = 0; o < FR; ++o) {
+        dg[o] = 0.f;
+        dv[o] = sd[f0 + o + pad][cl];  // d_dw at the thread's own frames (0 beyond T by staging)
+        accb += dv[o];
+      }
+#pragma unroll
+      for (int j = 0; j < FR + KMAX - 1; ++j) {
+        if (j < FR + K - 1) {
+          // d_glu[f0+o] = sum_k w[k] * d_dw[f0 + o - k + pad]  = sum over staged row j = o + (K-1) - k
+          const float dj = sd[f0 + j][cl];
+          const float gj = sg[f0 + j][cl];
+#pragma unroll
+          for (int o = 0; o < FR; ++o) {
+            // forward tap index of staged row j for output o: k = j - o (glu[f0+o+k] feeds out[f0+o])
+            if (j - o >= 0 && j - o < KMAX) acc[j - o] += dv[o] * gj;
+          }
+#pragma unroll
+          for (int o = 0; o < FR; ++o) {
+            // backward: d_dw[f0+o - k + pad] sits in staged row j = o + (K-1) - k  ->  w[k] = wrev[j - o]
+            if (j - o >= 0 && j - o < KMAX) dg[o] += wrev[j - o] * dj;
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 0; o < FR; ++o) {
+        const int t = t0 + f0 + o;
+        if (t < T) {
+          const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
+          const float a = __bfloat162float(row[c]), gt = __bfloat162float(row[C + c]);
+          const float sgm = sigmoidf_(gt);
+          bf16* drow = d_pw1 + ((long long)b * T + t) * (2 * C);
+          drow[c] = __float2bfloat16(dg[o] * sgm);
+          drow[C + c] = __float2bfloat16(dg[o] * a * sgm * (1.f - sgm));
+        }
+      }
+    }
+  }
   if (c < C) {
-    float wr[KMAX], acc[KMAX];
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-      wr[k] = k < K ? w[c * K + k] : 0.f;
-      acc[k] = 0.f;
-    }
-    float accb = 0.f;
-    for (int f = fr; f < TT; f += 4) {
-      const int t = t0 + f;
-      if (t >= T) break;
-      // d_glu[t] = sum_k w[k] * d_dw[t - k + pad]
-      float dg = 0.f;
-#pragma unroll
-      for (int k = 0; k < KMAX; ++k)
-        if (k < K) dg += wr[k] * sd[f + (K - 1) - k][cl];
-      const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
-      const float a = __bfloat162float(row[c]), gt = __bfloat162float(row[C + c]);
-      const float sgm = sigmoidf_(gt);
-      bf16* drow = d_pw1 + ((long long)b * T + t) * (2 * C);
-      drow[c] = __float2bfloat16(dg * sgm);
-      drow[C + c] = __float2bfloat16(dg * a * sgm * (1.f - sgm));
-      // dW[k] += d_dw[t] * glu[t + k - pad]
-      const float dv = sd[f + pad][cl];
-#pragma unroll
-      for (int k = 0; k < KMAX; ++k)
-        if (k < K) acc[k] += dv * sg[f + k][cl];
-      accb += dv;
-    }
 #pragma unroll
     for (int k = 0; k < KMAX; ++k)
       if (k < K) atomicAdd(&swg[cl][k], acc[k]);
@@ -275,7 +317,10 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
   B2_CHECK_ARG(B > 0 && T > 0 && C % 8 == 0 && K % 2 == 1 && K <= KMAX, "glu_dwconv_bwd: C %% 8 == 0, odd K <= %d", KMAX);
   B2_CHECK_ARG(B <= 65535, "glu_dwconv_bwd: B too large");
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((T + TT - 1) / TT, (C + CC - 1) / CC, B);
+  const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT - 1) / TT);
+  int gy = (2 * b2_num_sms() + ctiles - 1) / ctiles;
+  if (gy > units) gy = units;
+  dim3 grid(ctiles, gy);
   B2_SCOPE(FAM_CONVMOD, st, 4.0 * B * T * C * K, 10.0 * B * T * C);
   glu_dw_bwd_kernel<<<grid, 256, 0, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,
                                           dbias_accum);

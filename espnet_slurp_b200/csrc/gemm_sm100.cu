@@ -17,6 +17,8 @@
 //
 // CTA = one 128 x BN output tile.  Warp roles: 0 = TMA producer, 1 = TMEM owner + MMA
 // issuer (one elected lane), 2..5 = epilogue (TMEM lane group = warp_id % 4).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -154,27 +156,26 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
         if (col0 + j < N) v[j] += ep.bias[col0 + j];
     }
   }
-  if (ep.pre_out != nullptr) {
-    bf16* p = ep.pre_out + (long long)row * ep.ldc + col0;
-    if (full) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 8) {
-        uint4 u = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                             pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-        *reinterpret_cast<uint4*>(p + j) = u;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) p[j] = __float2bfloat16(v[j]);
-    }
-  }
+  // activation (+ its derivative when the backward wants it saved) and dropout share one pass; the saved derivative
+  // already carries the dropout multiplier, so the dgrad epilogue is a single multiply (no MUFU, no hash)
+  float dv[32];
+  const bool want_d = ep.pre_out != nullptr;
   if (ep.act == B200SLU_ACT_SWISH) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = swishf_(v[j]);
+    for (int j = 0; j < 32; ++j) {
+      const float sg = sigmoidf_(v[j]);
+      if (want_d) dv[j] = sg * (1.f + v[j] * (1.f - sg));
+      v[j] *= sg;
+    }
   } else if (ep.act == B200SLU_ACT_RELU) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+    for (int j = 0; j < 32; ++j) {
+      if (want_d) dv[j] = v[j] > 0.f ? 1.f : 0.f;
+      v[j] = fmaxf(v[j], 0.f);
+    }
+  } else if (want_d) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) dv[j] = 1.f;
   }
   if (ep.drop.p > 0.f) {
     const float inv = 1.f / (1.f - ep.drop.p);
@@ -183,7 +184,26 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
     for (int g = 0; g < 4; ++g) {
       uint32_t keep = dropout_keep8(ep.drop, (e0 >> 3) + g);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[g * 8 + j] = ((keep >> j) & 1u) ? v[g * 8 + j] * inv : 0.f;
+      for (int j = 0; j < 8; ++j) {
+        const float m = ((keep >> j) & 1u) ? inv : 0.f;
+        v[g * 8 + j] *= m;
+        if (want_d) dv[g * 8 + j] *= m;
+      }
+    }
+  }
+  if (want_d) {
+    bf16* p = ep.pre_out + (long long)row * ep.ldc + col0;
+    if (full) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        uint4 u = make_uint4(pack_bf16x2(dv[j], dv[j + 1]), pack_bf16x2(dv[j + 2], dv[j + 3]),
+                             pack_bf16x2(dv[j + 4], dv[j + 5]), pack_bf16x2(dv[j + 6], dv[j + 7]));
+        *reinterpret_cast<uint4*>(p + j) = u;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < N) p[j] = __float2bfloat16(dv[j]);
     }
   }
   if (ep.alpha != 1.f) {
@@ -200,7 +220,10 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           float2 x = unpack_bf16x2(w[q]);
-          if (ep.aux_mode == B200SLU_ACT_SWISH) {
+          if (ep.aux_mode == B200SLU_ACT_MUL) {
+            v[j + 2 * q] *= x.x;
+            v[j + 2 * q + 1] *= x.y;
+          } else if (ep.aux_mode == B200SLU_ACT_SWISH) {
             v[j + 2 * q] *= swish_gradf_(x.x);
             v[j + 2 * q + 1] *= swish_gradf_(x.y);
           } else {
@@ -214,7 +237,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
       for (int j = 0; j < 32; ++j) {
         if (col0 + j < N) {
           float x = __bfloat162float(a[j]);
-          v[j] *= (ep.aux_mode == B200SLU_ACT_SWISH) ? swish_gradf_(x) : (x > 0.f ? 1.f : 0.f);
+          v[j] *= (ep.aux_mode == B200SLU_ACT_MUL) ? x : (ep.aux_mode == B200SLU_ACT_SWISH) ? swish_gradf_(x) : (x > 0.f ? 1.f : 0.f);
         }
       }
     }
@@ -236,9 +259,17 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32]
   if (ep.out_f32) {
     float* o = reinterpret_cast<float*>(ep.out) + out_off + (long long)row * ep.ldc + col0;
     if (ep.accumulate) {
+      if (full) {  // split-K partial sums: 16-byte vector reductions (4x fewer L2 atomic requests than scalar RED)
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (full || col0 + j < N) atomicAdd(o + j, v[j]);
+        for (int j = 0; j < 32; j += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]),
+                       "f"(v[j + 3])
+                       : "memory");
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < N) atomicAdd(o + j, v[j]);
+      }
     } else if (full) {
 #pragma unroll
       for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -392,16 +423,20 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       tcgen05_fence_after();
       const int row = tile_m * BM + lane_grp * 32 + lane;
       const bool row_ok = row < M;
-#pragma unroll 1
-      for (int c0 = half * (BN / 2); c0 < (half + 1) * (BN / 2); c0 += 32) {
-        uint32_t r32[32];
-        tmem_ld32(tmem_base + ((uint32_t)(lane_grp * 32) << 16) + buf * BN + c0, r32);
+      // TMEM -> registers is double-buffered: the load of chunk i+1 is in flight while chunk i runs the epilogue math
+      constexpr int NCHUNK = BN / 64;  // 32-column chunks per column half
+      const uint32_t tbase = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + buf * BN + half * (BN / 2);
+      uint32_t r32[2][32];
+      tmem_ld32(tbase, r32[0]);
+#pragma unroll
+      for (int ci = 0; ci < NCHUNK; ++ci) {
         tmem_ld_wait();
-        const int col0 = tile_n * BN + c0;
+        if (ci + 1 < NCHUNK) tmem_ld32(tbase + (ci + 1) * 32, r32[(ci + 1) & 1]);
+        const int col0 = tile_n * BN + half * (BN / 2) + ci * 32;
         if (row_ok && col0 < N) {
           float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r32[j]);
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r32[ci & 1][j]);
           epilogue_chunk(ep, v, row, col0, N, sp == 0, out_off);
         }
       }
@@ -515,7 +550,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     ep.aux = (const bf16*)e->act_grad_input;
     ep.ldaux = e->ld_act_grad_input;
     ep.aux_mode = e->act_grad;
-    ep.pre_out = (bf16*)e->pre_act_out;
+    ep.pre_out = (bf16*)e->act_grad_out;
     ep.alpha = e->alpha;
     ep.act = e->act;
     ep.out_f32 = e->out_f32;
@@ -535,6 +570,19 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
 
   const int num_kb = (K + BK - 1) / BK;
   int splits = 1;
+  // Tile width: a 128x128 single-CTA tile reads 32 KB of shared memory per 256 MMA cycles (= the 128 B/clk port limit);
+  // 128x256 reads 48 KB per 512 cycles and lets the tensor pipe run ahead.  Take the wide tile when it does not cost
+  // more in wave quantisation than it gains (relative per-tile costs measured: profiles/r1_gemm_shapes_*.txt).
+  int bn = 128;
+  {
+    const long long sms = b2_num_sms();
+    const long long tm = (M + BM - 1) / BM;
+    const long long t128 = tm * ((N + 127) / 128) * nbatch, t256 = tm * ((N + 255) / 256) * nbatch;
+    const double c128 = (double)((t128 + sms - 1) / sms) * 1.0, c256 = (double)((t256 + sms - 1) / sms) * 1.45;
+    if (N >= 256 && !ep.accumulate && c256 < c128) bn = 256;
+    static const int force_bn = getenv("B200SLU_GEMM_BN") ? atoi(getenv("B200SLU_GEMM_BN")) : 0;  // tuning experiments only
+    if (force_bn == 128 || (force_bn == 256 && N >= 256 && !ep.accumulate)) bn = force_bn;
+  }
   const long long tiles128 = (long long)((M + BM - 1) / BM) * ((N + 127) / 128) * nbatch;
   if (ep.accumulate) {
     // split-K (wgrad: K = B*T is long, the output is small): target >= 2 CTAs per SM
@@ -552,13 +600,19 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   else
     B2_TRY(make_map(&ma, g->A, K, M, g->lda, nbi, g->a_stride_inner, nbo, g->a_stride_outer, 64, BK));
   if (!g->trans_b)
-    B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, 128));
+    B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, bn));
   else
     B2_TRY(make_map(&mb, g->B, K, N, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, 64, BK));
-  if (!g->trans_a && !g->trans_b) return launch<128, 6, false, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
-  if (!g->trans_a && g->trans_b) return launch<128, 6, false, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
-  if (g->trans_a && !g->trans_b) return launch<128, 6, true, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
-  return launch<128, 6, true, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);
+#define B2_GEMM_DISPATCH(BN_, ST_)                                                                                    \
+  do {                                                                                                                \
+    if (!g->trans_a && !g->trans_b) return launch<BN_, ST_, false, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st); \
+    if (!g->trans_a && g->trans_b) return launch<BN_, ST_, false, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);   \
+    if (g->trans_a && !g->trans_b) return launch<BN_, ST_, true, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);   \
+    return launch<BN_, ST_, true, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);                       \
+  } while (0)
+  if (bn == 256) B2_GEMM_DISPATCH(256, 4);
+  B2_GEMM_DISPATCH(128, 6);
+#undef B2_GEMM_DISPATCH
 }
 
 extern "C" int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epilogue, void* stream) {

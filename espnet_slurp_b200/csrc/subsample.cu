@@ -10,41 +10,43 @@
 
 namespace {
 
-// x [B, Tin, F] f32 -> h1 [B, T1, F1, C] bf16 ;  grid (T1, B)
+// x [B, Tin, F] f32 -> h1 [B, T1, F1, C] bf16 ;  grid (ceil(T1 / TR1), B).  Each thread keeps the 9 taps + bias of its
+// 8 channels in registers and walks the output pixels of TR1 rows; the 2*TR1+1 input rows sit in shared memory
+// (broadcast reads), every store is one 16-byte vector and a warp writes 512 contiguous bytes.
+constexpr int TR1 = 8;
 __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ bias, int Tin, int F, int C, int T1, int F1,
                                                         bf16* __restrict__ h1) {
-  extern __shared__ float sm[];
-  float* sw = sm;            // [9][C] taps, channel-contiguous
-  float* sb = sm + 9 * C;    // [C]
-  float* sx = sb + C;        // [3][F]
-  const int t = blockIdx.x, b = blockIdx.y;
-  for (int i = threadIdx.x; i < 9 * C; i += blockDim.x) {
-    const int c = i / 9, k = i - c * 9;
-    sw[k * C + c] = w[i];
-  }
-  for (int i = threadIdx.x; i < C; i += blockDim.x) sb[i] = bias[i];
-  for (int i = threadIdx.x; i < 3 * F; i += blockDim.x) {
-    const int kh = i / F, f = i - kh * F;
-    sx[i] = x[((long long)b * Tin + 2 * t + kh) * F + f];
-  }
+  extern __shared__ float sx[];  // [2*TR1+1][F]
+  const int tb = blockIdx.x * TR1, b = blockIdx.y;
+  const int nt = min(TR1, T1 - tb), nrows = 2 * nt + 1;
+  for (int i = threadIdx.x; i < nrows * F; i += blockDim.x) sx[i] = x[((long long)b * Tin + 2 * tb) * F + i];
   __syncthreads();
   const int ncg = C >> 3;
-  bf16* orow = h1 + ((long long)b * T1 + t) * F1 * C;
-  for (int it = threadIdx.x; it < F1 * ncg; it += blockDim.x) {
-    const int f = it / ncg, c = (it - f * ncg) * 8;
-    float acc[8];
+  const int npl = blockDim.x / ncg;  // position lanes (4 for C = 512)
+  for (int cg = threadIdx.x % ncg, pl = threadIdx.x / ncg; pl < npl && cg < ncg; cg += ncg) {
+    float wr[9][8], bs[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = sb[c + j];
+    for (int j = 0; j < 8; ++j) {
+      bs[j] = bias[cg * 8 + j];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      const float xv = sx[(k / 3) * F + 2 * f + (k % 3)];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += xv * sw[k * C + c + j];
+      for (int k = 0; k < 9; ++k) wr[k][j] = w[(cg * 8 + j) * 9 + k];
     }
+    for (int p = pl; p < nt * F1; p += npl) {
+      const int tl = p / F1, f = p - tl * F1;
+      float acc[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
-    store8_bf16(orow + (long long)f * C + c, acc);
+      for (int j = 0; j < 8; ++j) acc[j] = bs[j];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const float xv = sx[(2 * tl + k / 3) * F + 2 * f + (k % 3)];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += xv * wr[k][j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
+      store8_bf16(h1 + (((long long)b * T1 + tb + tl) * F1 + f) * C + cg * 8, acc);
+    }
   }
 }
 
@@ -163,10 +165,10 @@ extern "C" int b200slu_conv1_fwd(const float* x, const float* w, const float* bi
   B2_CHECK_ARG(B > 0 && Tin >= 3 && F >= 3 && C % 8 == 0 && B <= 65535, "conv1_fwd: bad shape B=%d Tin=%d F=%d C=%d", B, Tin, F, C);
   const int T1 = (Tin - 3) / 2 + 1, F1 = (F - 3) / 2 + 1;
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t smem = (size_t)(10 * C + 3 * F) * sizeof(float);
-  B2_CHECK_ARG(smem <= 48 * 1024, "conv1_fwd: C too large for the shared-memory tap table");
+  const size_t smem = (size_t)(2 * TR1 + 1) * F * sizeof(float);
+  B2_CHECK_ARG(smem <= 48 * 1024 && C <= 2048, "conv1_fwd: F or C too large");
   B2_SCOPE(FAM_SUBSAMPLE, st, 18.0 * B * T1 * F1 * C, 4.0 * B * Tin * F + 2.0 * B * T1 * F1 * C);
-  conv1_fwd_kernel<<<dim3(T1, B), 256, smem, st>>>(x, w, bias, Tin, F, C, T1, F1, (bf16*)h1);
+  conv1_fwd_kernel<<<dim3((T1 + TR1 - 1) / TR1, B), 256, smem, st>>>(x, w, bias, Tin, F, C, T1, F1, (bf16*)h1);
   B2_LAUNCH_CHECK();
   return 0;
 }

@@ -19,7 +19,7 @@ import torch
 from . import _lib
 from ._lib import Epilogue, GemmDesc, check, ptr, stream_ptr
 
-ACT = {None: 0, "none": 0, "swish": 1, "relu": 2}
+ACT = {None: 0, "none": 0, "swish": 1, "relu": 2, "mul": 3}
 RELPOS = {None: 0, "none": 0, "latest": 1, "legacy": 2}
 Drop = Optional[Tuple[float, int, int]]
 
@@ -38,7 +38,7 @@ def _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre_act_out,
     ep = Epilogue()
     ep.bias = ptr(bias)
     ep.act = ACT[act]
-    ep.pre_act_out = ptr(pre_act_out)
+    ep.act_grad_out = ptr(pre_act_out)
     ep.alpha = alpha
     ep.dropout_p, ep.dropout_seed, ep.dropout_site = _drop(drop)
     if act_grad_input is not None:
@@ -57,14 +57,16 @@ def _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre_act_out,
 def gemm(a: torch.Tensor, b: torch.Tensor, *, trans: bool = False, trans_a: Optional[bool] = None,
          trans_b: Optional[bool] = None, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
          alpha: float = 1.0, residual: Optional[torch.Tensor] = None, act_grad_input: Optional[torch.Tensor] = None,
-         act_grad: Optional[str] = None, pre_act_out=False, out_dtype=torch.bfloat16,
+         act_grad: Optional[str] = None, act_grad_out=False, out_dtype=torch.bfloat16,
          out: Optional[torch.Tensor] = None, accumulate: bool = False, drop: Drop = None,
          dropout_p: float = 0.0, seed: int = 0, site: int = 0):
     """C[M,N] = op(A) op(B)^T with the fused epilogue of b200slu_epilogue_t.
 
     trans_a=False: a is [M,K]; True: a is [K,M].  trans_b=False: b is [N,K]; True: b is [K,N].
-    (``trans`` sets both.)  ``pre_act_out`` may be True (allocate) or a bf16 [M,N] tensor.
+    (``trans`` sets both.)  ``act_grad_out`` (True = allocate, or a bf16 [M,N] tensor) receives act'(y) times the
+    element's dropout multiplier; feed it back as ``act_grad_input`` with ``act_grad="mul"`` in the dgrad GEMM.
     """
+    pre_act_out = act_grad_out
     ta = trans if trans_a is None else trans_a
     tb = trans if trans_b is None else trans_b
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_cuda

@@ -118,7 +118,7 @@ def subsampled_len(t_in: int) -> int:
 def ffn_fwd(x, P, W, pre: str, norm: str, act: str, scale: float, p_drop: float, ctx: StepCtx):
     ln, _, st = K.layernorm_fwd(x, P[norm + ".weight"], P[norm + ".bias"])
     d1, d2 = ctx.drop(p_drop), ctx.drop(p_drop)
-    h, hpre = K.gemm(ln, W[pre + ".w_1.weight"], bias=P[pre + ".w_1.bias"], act=act, pre_act_out=True, drop=d1)
+    h, hpre = K.gemm(ln, W[pre + ".w_1.weight"], bias=P[pre + ".w_1.bias"], act=act, act_grad_out=True, drop=d1)
     y = K.gemm(h, W[pre + ".w_2.weight"], bias=P[pre + ".w_2.bias"], alpha=scale, residual=x, drop=d2, out_dtype=F32)
     return y, (x, ln, st, hpre, h, d1, d2, pre, norm, act, scale)
 
@@ -128,7 +128,7 @@ def ffn_bwd(dy, saved, P, W, G):
     g = K.cast_bf16(dy, alpha=scale, drop=d2)
     K.colsum(g, G[pre + ".w_2.bias"])
     K.gemm(g, h, trans=True, out=G[pre + ".w_2.weight"], accumulate=True)
-    dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad=act, drop=d1)
+    dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad="mul")  # hpre = act' * dropout mask
     K.colsum(dh, G[pre + ".w_1.bias"])
     K.gemm(dh, ln, trans=True, out=G[pre + ".w_1.weight"], accumulate=True)
     dln = K.gemm(dh, W[pre + ".w_1.weight"], trans_b=True)

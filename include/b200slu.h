@@ -31,6 +31,7 @@ extern "C" {
 #define B200SLU_ACT_NONE 0
 #define B200SLU_ACT_SWISH 1 /* espnet/nets/pytorch_backend/conformer/swish.py:13-18 */
 #define B200SLU_ACT_RELU 2  /* decoder FFN default, positionwise_feed_forward.py:22 */
+#define B200SLU_ACT_MUL 3   /* act_grad only: multiply by a saved derivative (see act_grad_out) */
 
 #define B200SLU_RELPOS_NONE 0   /* MultiHeadedAttention, attention.py:98-114 */
 #define B200SLU_RELPOS_LATEST 1 /* RelPositionMultiHeadedAttention.rel_shift, attention.py:240-263 */
@@ -66,16 +67,17 @@ int b200slu_set_step_params(const void* dev_ptr);
  *   espnet2/asr/ctc.py:33 (ctc_lo), espnet2/asr/decoder/transformer_decoder.py:85 (output_layer)
  *
  *   y   = acc + bias                      (bias: f32 [N] or NULL)
- *   pre_act_out <- bf16(y)                (optional, ld = ldc)
+ *   act_grad_out <- bf16(act'(y) * m)     (optional, ld = ldc; m = dropout multiplier of the element: 0 or 1/(1-p))
  *   y   = act(y); y = dropout(y); y *= alpha
- *   y  *= act'(act_grad_input)            (optional bf16 [M,N]; act_grad = SWISH / RELU)
+ *   y  *= act'(act_grad_input)            (optional bf16 [M,N]; act_grad = SWISH / RELU: input is the pre-activation
+ *                                          (for RELU the post-activation works too); MUL: input is a saved act_grad_out)
  *   y  += residual                        (optional f32 [M,N])
  *   C   = y  (bf16 or f32), or C += y atomically when accumulate (f32 only; enables split-K)
  */
 typedef struct {
   const float* bias;
   int act;
-  void* pre_act_out;
+  void* act_grad_out;
   float alpha;
   float dropout_p;
   unsigned long long dropout_seed;

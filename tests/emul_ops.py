@@ -43,6 +43,10 @@ def _act(y, act):
 
 
 def _act_grad(x, act):
+    if act == "mul":
+        return x
+    if act == "none" or act is None:
+        return torch.ones_like(x)
     if act == "swish":
         s = torch.sigmoid(x)
         return s * (1 + x * (1 - s))
@@ -50,7 +54,7 @@ def _act_grad(x, act):
 
 
 def gemm(a, b, *, trans=False, trans_a=None, trans_b=None, bias=None, act=None, alpha=1.0, residual=None,
-         act_grad_input=None, act_grad=None, pre_act_out=False, out_dtype=None, out=None, accumulate=False, drop=None,
+         act_grad_input=None, act_grad=None, act_grad_out=False, out_dtype=None, out=None, accumulate=False, drop=None,
          dropout_p=0.0, seed=0, site=0):
     _nodrop(drop)
     assert dropout_p == 0.0
@@ -62,7 +66,8 @@ def gemm(a, b, *, trans=False, trans_a=None, trans_b=None, bias=None, act=None, 
     N = y.shape[1]
     if bias is not None:
         y = y + bias[:N]
-    pre = _r(y) if pre_act_out is not False and pre_act_out is not None else None
+    pre_act_out = act_grad_out
+    pre = _r(_act_grad(y, act)) if pre_act_out is not False and pre_act_out is not None else None
     y = _act(y, act) * alpha
     if act_grad_input is not None:
         y = y * _act_grad(act_grad_input.float(), act_grad)
