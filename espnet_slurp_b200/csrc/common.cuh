@@ -144,13 +144,25 @@ __device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
   return z ^ (z >> 31);
 }
 
-// keep-mask (bit i set = keep) for elements [8*group, 8*group+8): 8 x 16-bit uniform lanes compared with p * 65536
-__device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned long long group) {
+// Per-site dropout key, hoisted out of the element loops: one splitmix of (seed, site) per thread per kernel.
+struct B2DropKey {
+  unsigned long long key;
+  uint32_t thr;  // drop when the 16-bit uniform lane < thr = p * 65536
+  float inv;     // 1 / (1 - p)
+};
+__device__ __forceinline__ B2DropKey dropout_key(const B2Dropout& d) {
+  B2DropKey k;
   const unsigned long long sd = d.dev_seed != nullptr ? (d.seed ^ *d.dev_seed) : d.seed;
-  const unsigned long long key = splitmix64(sd + 0x9E3779B97F4A7C15ull * (unsigned long long)(d.site + 1u));
-  const unsigned long long c = key + (group << 1) * 0x9E3779B97F4A7C15ull;
+  k.key = splitmix64(sd + 0x9E3779B97F4A7C15ull * (unsigned long long)(d.site + 1u));
+  k.thr = (uint32_t)(d.p * 65536.f);
+  k.inv = 1.f / (1.f - d.p);
+  return k;
+}
+// keep-mask (bit i set = keep) for elements [8*group, 8*group+8): 8 x 16-bit uniform lanes compared with p * 65536
+__device__ __forceinline__ uint32_t dropout_keep8(const B2DropKey& k, unsigned long long group) {
+  const unsigned long long c = k.key + (group << 1) * 0x9E3779B97F4A7C15ull;
   const unsigned long long z0 = splitmix64(c), z1 = splitmix64(c + 0x9E3779B97F4A7C15ull);
-  const uint32_t thr = (uint32_t)(d.p * 65536.f);
+  const uint32_t thr = k.thr;
   const uint32_t a = (uint32_t)z0, b = (uint32_t)(z0 >> 32), e = (uint32_t)z1, f = (uint32_t)(z1 >> 32);
   uint32_t m = 0;
   m |= ((a & 0xffffu) >= thr) << 0;
@@ -162,6 +174,9 @@ __device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned l
   m |= ((f & 0xffffu) >= thr) << 6;
   m |= ((f >> 16) >= thr) << 7;
   return m;
+}
+__device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned long long group) {
+  return dropout_keep8(dropout_key(d), group);
 }
 
 // ---------------------------------------------------------------------------

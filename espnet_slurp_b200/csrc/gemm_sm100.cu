@@ -25,8 +25,6 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle span
-constexpr int NUM_EPI_WARPS = 8;
-constexpr int NUM_THREADS = 64 + 32 * NUM_EPI_WARPS;
 
 // ----------------------------------------------------------------------------- PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -97,6 +95,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout), SWIZZLE_128B, version 1.
@@ -126,8 +133,24 @@ struct EpiArgs {
   int a_bc_inner, a_bc_outer, b_bc_inner, b_bc_outer;  // 1 = operand indexed by that batch level, 0 = broadcast
   float alpha;
   int act, aux_mode, out_f32, accumulate;
+  uint32_t flags;  // EF_* summary of the fields above (what the generic kernel branches on)
+  int debug;  // tuning experiments only (B200SLU_GEMM_DEBUG): 1 = no stores, 2 = no epilogue, 4 = no TMA loads,
+              // 16 = CTA 0 records phase cycle counts into dbg_out (printed by the host after a synchronize)
+  long long* dbg_out;
   B2Dropout drop;
 };
+
+// Epilogue feature bits.  A kernel instantiated with EF != EF_GENERIC has its epilogue resolved at compile time: the
+// K = 512 GEMMs of the encoder leave ~250 issue cycles per 16-column slice per warp, which a chain of
+// load-constant / test / branch decisions per feature does not fit into (measured: 840 cycles per slice).
+enum : uint32_t {
+  EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
+  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_GENERIC = 1u << 31
+};
+// Epilogue warps: 16 (4 per TMEM lane quadrant = 4 per scheduler, 96 registers each) hide the epilogue latencies best;
+// the generic kernel and the residual epilogues (two fp32 prefetch buffers) need the 168 registers of the 8-warp shape.
+__host__ __device__ constexpr int epi_warps(uint32_t ef) { return (ef & (EF_GENERIC | EF_RES)) ? 8 : 16; }
+__host__ __device__ constexpr int num_threads(uint32_t ef) { return 64 + 32 * epi_warps(ef); }
 
 template <int BN, int STAGES>
 struct SmemLayout {
@@ -136,168 +159,173 @@ struct SmemLayout {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
   static constexpr int NUM_BARS = 2 * STAGES + 4;
-  static constexpr int TOTAL = BAR_OFF + NUM_BARS * 8 + 16 + 1024;  // + alignment slack
+  static constexpr int BIAS_OFF = BAR_OFF + NUM_BARS * 8 + 16;       // per-tile bias slice, one segment per epilogue warp
+  static constexpr int BIAS_BYTES = 4 * BN * 4;                      // 4 lane quadrants x BN floats
+  static constexpr int TOTAL = BIAS_OFF + BIAS_BYTES + 1024;         // + alignment slack
 };
 
-// One 32-column chunk of one accumulator row: fused epilogue + store.
-__device__ __forceinline__ void epilogue_chunk(const EpiArgs& ep, float (&v)[32], int row, int col0, int N, bool first_split,
-                                               long long out_off) {
-  const bool full = (col0 + 32 <= N);
-  if (ep.bias != nullptr && first_split) {
-    if (full) {
+// ----------------------------------------------------------------------------- fused epilogue
+// Per-thread, per-tile constants of the epilogue (hoisted out of the column loop).
+struct EpiRow {
+  const float* res;   // residual row (or nullptr)
+  const bf16* aux;    // activation-derivative row (or nullptr)
+  bf16* dact;         // saved act' * dropout-multiplier row (or nullptr)
+  void* out;          // output row
+  unsigned long long e0;  // flat element index of (row, 0) for the dropout counter
+};
+
+// The arithmetic of 8 consecutive columns.  b = bias, x = aux (bf16 widened), r = residual; d receives the saved
+// derivative.  F is a compile-time constant in the specialised kernels and a register in the generic one.
+template <uint32_t EF>
+__device__ __forceinline__ void epi_math8(uint32_t rt_flags, const EpiArgs& ep, const B2DropKey& dk, float alpha,
+                                          unsigned long long e0, int col, float (&v)[8], const float (&b)[8],
+                                          const float (&x)[8], const float (&r)[8], float (&d)[8]) {
+  const uint32_t F = (EF & EF_GENERIC) ? rt_flags : EF;
+  if (F & EF_BIAS) {
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        float4 b = *reinterpret_cast<const float4*>(ep.bias + col0 + j);
-        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) v[j] += ep.bias[col0 + j];
-    }
+    for (int j = 0; j < 8; ++j) v[j] += b[j];
   }
-  // activation (+ its derivative when the backward wants it saved) and dropout share one pass; the saved derivative
-  // already carries the dropout multiplier, so the dgrad epilogue is a single multiply (no MUFU, no hash)
-  float dv[32];
-  const bool want_d = ep.pre_out != nullptr;
-  if (ep.act == B200SLU_ACT_SWISH) {
+  if (F & EF_SWISH) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
+    for (int j = 0; j < 8; ++j) {
       const float sg = sigmoidf_(v[j]);
-      if (want_d) dv[j] = sg * (1.f + v[j] * (1.f - sg));
-      v[j] *= sg;
+      const float t = v[j] * sg;           // swish
+      d[j] = fmaf(t, 1.f - sg, sg);        // swish' = sg + swish * (1 - sg)
+      v[j] = t;
     }
-  } else if (ep.act == B200SLU_ACT_RELU) {
+  } else if (F & EF_RELU) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      if (want_d) dv[j] = v[j] > 0.f ? 1.f : 0.f;
+    for (int j = 0; j < 8; ++j) {
+      d[j] = v[j] > 0.f ? 1.f : 0.f;
       v[j] = fmaxf(v[j], 0.f);
     }
-  } else if (want_d) {
+  } else {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) dv[j] = 1.f;
+    for (int j = 0; j < 8; ++j) d[j] = 1.f;
   }
-  if (ep.drop.p > 0.f) {
-    const float inv = 1.f / (1.f - ep.drop.p);
-    const unsigned long long e0 = (unsigned long long)row * (unsigned long long)N + col0;  // N % 8 == 0 (host check)
+  if (F & EF_DROP) {
+    // alpha rides on the keep multiplier (the host clears EF_ALPHA when EF_DROP is set)
+    const uint32_t keep = dropout_keep8(dk, (e0 + (unsigned long long)col) >> 3);
+    const float mv = dk.inv * alpha;
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      uint32_t keep = dropout_keep8(ep.drop, (e0 >> 3) + g);
+    for (int j = 0; j < 8; ++j) {
+      const bool kp = (keep >> j) & 1u;
+      v[j] *= kp ? mv : 0.f;
+      if (F & EF_DACT) d[j] *= kp ? dk.inv : 0.f;
+    }
+  } else if (F & EF_ALPHA) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= alpha;
+  }
+  if (F & EF_AUX_MUL) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= x[j];
+  } else if (F & EF_AUX_SWISH) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] *= swish_gradf_(x[j]);
+  } else if (F & EF_AUX_RELU) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = x[j] > 0.f ? v[j] : 0.f;
+  }
+  if (F & EF_RES) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] += r[j];
+  }
+}
+
+// Residual / saved-derivative operands of one 16-column slice, fetched one slice ahead of their use.
+struct EpiPre {
+  float r[2][8];
+  uint4 x[2];
+};
+template <uint32_t EF>
+__device__ __forceinline__ void epi_prefetch(uint32_t rt_flags, const EpiRow& er, int col0, int N, EpiPre& p) {
+  const uint32_t F = (EF & EF_GENERIC) ? rt_flags : EF;
+  if (col0 + 16 <= N) {
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+      if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) p.x[g] = *reinterpret_cast<const uint4*>(er.aux + col0 + g * 8);
+      if (F & EF_RES) load8_f32(er.res + col0 + g * 8, p.r[g]);
+    }
+  }
+}
+
+// One 16-column slice of one accumulator row.  Whole slices take the vector path; the ragged last slice of a row
+// (N % 16 != 0) takes a guarded scalar path around the same arithmetic.  bias_s: this slice's 16 bias values in shared
+// memory (zero-filled past N).  rt_flags already has the split-K gating applied (bias / residual on the first split).
+template <uint32_t EF>
+__device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs& ep, const B2DropKey& dk, const EpiRow& er,
+                                               float alpha, const float* bias_s, const EpiPre& pre, const uint32_t (&acc)[16],
+                                               int col0, int N, int debug) {
+  const uint32_t F = (EF & EF_GENERIC) ? rt_flags : EF;
+  if (col0 + 16 <= N) {
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+      const int c = col0 + g * 8;
+      float w[8], d[8], b[8] = {}, x[8] = {};
+      if (F & EF_BIAS) load8_f32(bias_s + g * 8, b);
+      if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) {
+        const float2 x0 = unpack_bf16x2(pre.x[g].x), x1 = unpack_bf16x2(pre.x[g].y), x2 = unpack_bf16x2(pre.x[g].z),
+                     x3 = unpack_bf16x2(pre.x[g].w);
+        x[0] = x0.x; x[1] = x0.y; x[2] = x1.x; x[3] = x1.y; x[4] = x2.x; x[5] = x2.y; x[6] = x3.x; x[7] = x3.y;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = __uint_as_float(acc[g * 8 + j]);
+      epi_math8<EF>(rt_flags, ep, dk, alpha, er.e0, c, w, b, x, pre.r[g], d);
+      if ((EF & EF_GENERIC) && (debug & 1)) {
+        if (w[0] == 1.2345e-30f && d[3] == 3.3e-33f) store8_f32(reinterpret_cast<float*>(er.out) + c, w);
+        continue;
+      }
+      if (F & EF_DACT) store8_bf16(er.dact + c, d);
+      if (F & EF_F32) {
+        float* o = reinterpret_cast<float*>(er.out) + c;
+        if (F & EF_ACC) {  // split-K partial sums: 16-byte vector reductions (4x fewer L2 requests than scalar RED)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o), "f"(w[0]), "f"(w[1]), "f"(w[2]), "f"(w[3])
+                       : "memory");
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + 4), "f"(w[4]), "f"(w[5]), "f"(w[6]), "f"(w[7])
+                       : "memory");
+        } else {
+          store8_f32(o, w);
+        }
+      } else {
+        store8_bf16(reinterpret_cast<bf16*>(er.out) + c, w);
+      }
+    }
+  } else {
+#pragma unroll 1
+    for (int g = 0; g < 2; ++g) {
+      const int c = col0 + g * 8;
+      if (c >= N) break;
+      float w[8], b[8], x[8], r[8], d[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float m = ((keep >> j) & 1u) ? inv : 0.f;
-        v[g * 8 + j] *= m;
-        if (want_d) dv[g * 8 + j] *= m;
+        const bool ok = c + j < N;
+        w[j] = __uint_as_float(g == 0 ? acc[j] : acc[8 + j]);  // select, not a dynamic index: acc stays in registers
+        b[j] = (F & EF_BIAS) ? bias_s[g * 8 + j] : 0.f;
+        x[j] = ((F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) && ok) ? __bfloat162float(er.aux[c + j]) : 0.f;
+        r[j] = ((F & EF_RES) && ok) ? er.res[c + j] : 0.f;
       }
-    }
-  }
-  if (want_d) {
-    bf16* p = ep.pre_out + (long long)row * ep.ldc + col0;
-    if (full) {
+      epi_math8<EF>(rt_flags, ep, dk, alpha, er.e0, c, w, b, x, r, d);
 #pragma unroll
-      for (int j = 0; j < 32; j += 8) {
-        uint4 u = make_uint4(pack_bf16x2(dv[j], dv[j + 1]), pack_bf16x2(dv[j + 2], dv[j + 3]),
-                             pack_bf16x2(dv[j + 4], dv[j + 5]), pack_bf16x2(dv[j + 6], dv[j + 7]));
-        *reinterpret_cast<uint4*>(p + j) = u;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) p[j] = __float2bfloat16(dv[j]);
-    }
-  }
-  if (ep.alpha != 1.f) {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] *= ep.alpha;
-  }
-  if (ep.aux != nullptr) {
-    const bf16* a = ep.aux + (long long)row * ep.ldaux + col0;
-    if (full) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 8) {
-        uint4 u = *reinterpret_cast<const uint4*>(a + j);
-        uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          float2 x = unpack_bf16x2(w[q]);
-          if (ep.aux_mode == B200SLU_ACT_MUL) {
-            v[j + 2 * q] *= x.x;
-            v[j + 2 * q + 1] *= x.y;
-          } else if (ep.aux_mode == B200SLU_ACT_SWISH) {
-            v[j + 2 * q] *= swish_gradf_(x.x);
-            v[j + 2 * q + 1] *= swish_gradf_(x.y);
+      for (int j = 0; j < 8; ++j) {
+        if (c + j < N) {
+          if (F & EF_DACT) er.dact[c + j] = __float2bfloat16(d[j]);
+          if (F & EF_F32) {
+            float* o = reinterpret_cast<float*>(er.out) + c + j;
+            if (F & EF_ACC) atomicAdd(o, w[j]);
+            else *o = w[j];
           } else {
-            v[j + 2 * q] = x.x > 0.f ? v[j + 2 * q] : 0.f;
-            v[j + 2 * q + 1] = x.y > 0.f ? v[j + 2 * q + 1] : 0.f;
+            reinterpret_cast<bf16*>(er.out)[c + j] = __float2bfloat16(w[j]);
           }
         }
       }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (col0 + j < N) {
-          float x = __bfloat162float(a[j]);
-          v[j] *= (ep.aux_mode == B200SLU_ACT_MUL) ? x : (ep.aux_mode == B200SLU_ACT_SWISH) ? swish_gradf_(x) : (x > 0.f ? 1.f : 0.f);
-        }
-      }
-    }
-  }
-  if (ep.res != nullptr) {
-    const float* rp = ep.res + (long long)row * ep.ldres + col0;
-    if (full) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        float4 b = *reinterpret_cast<const float4*>(rp + j);
-        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) v[j] += rp[j];
-    }
-  }
-  if (ep.out_f32) {
-    float* o = reinterpret_cast<float*>(ep.out) + out_off + (long long)row * ep.ldc + col0;
-    if (ep.accumulate) {
-      if (full) {  // split-K partial sums: 16-byte vector reductions (4x fewer L2 atomic requests than scalar RED)
-#pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j), "f"(v[j]), "f"(v[j + 1]), "f"(v[j + 2]),
-                       "f"(v[j + 3])
-                       : "memory");
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (col0 + j < N) atomicAdd(o + j, v[j]);
-      }
-    } else if (full) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) o[j] = v[j];
-    }
-  } else {
-    bf16* o = reinterpret_cast<bf16*>(ep.out) + out_off + (long long)row * ep.ldc + col0;
-    if (full) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 8) {
-        uint4 u = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                             pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-        *reinterpret_cast<uint4*>(o + j) = u;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < N) o[j] = __float2bfloat16(v[j]);
     }
   }
 }
 
 // Persistent: grid = min(#work units, #SMs); unit u = (batch, tile, k-split), tiles n-fastest.
-template <int BN, int STAGES, bool TA, bool TB>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <int BN, int STAGES, bool TA, bool TB, uint32_t EF>
+__global__ void __launch_bounds__(num_threads(EF), 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                   int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
                   int num_units, EpiArgs ep) {
@@ -324,7 +352,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar_acc_full + b * 8, 1);
-      mbar_init(bar_acc_empty + b * 8, NUM_EPI_WARPS);
+      mbar_init(bar_acc_empty + b * 8, epi_warps(EF));
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -352,9 +380,13 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const int abi = bi * ep.a_bc_inner, abo = bo * ep.a_bc_outer, bbi = bi * ep.b_bc_inner, bbo = bo * ep.b_bc_outer;
         for (int kb = 0; kb < nkb; ++kb, ++i) {
           const int s = i % STAGES, it = i / STAGES;
+          const bool rec = (EF & EF_GENERIC) && (ep.debug & 16) && blockIdx.x == 0;
+          const long long c0 = rec ? clock64() : 0;
           mbar_wait(bar_empty + s * 8, (it & 1) ^ 1);
+          if (rec) ep.dbg_out[7] += clock64() - c0;  // producer: waiting for a free stage
           const uint32_t sa = sbase + s * L::STAGE_BYTES, sb = sa + L::A_BYTES;
           const uint32_t fb = bar_full + s * 8;
+          if ((EF & EF_GENERIC) && (ep.debug & 4)) { mbar_arrive(fb); continue; }
           mbar_expect_tx(fb, L::STAGE_BYTES);
           const int k = (kb0 + kb) * BK;
           if (!TA) {
@@ -375,22 +407,30 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc(BN, TA, TB);
-    int i = 0, t = 0;
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
-      const int r = u % units_per_batch;
-      const int sp = r % splits;
-      const int kb0 = sp * kb_per_split;
-      const int nkb = min(kb_per_split, num_kb_total - kb0);
-      const int buf = t & 1;
-      mbar_wait(bar_acc_empty + buf * 8, ((t >> 1) & 1) ^ 1);  // epilogue drained this buffer
-      tcgen05_fence_after();
-      const uint32_t d_tmem = tmem_base + buf * BN;
-      for (int kb = 0; kb < nkb; ++kb, ++i) {
-        const int s = i % STAGES, it = i / STAGES;
-        mbar_wait(bar_full + s * 8, it & 1);
+    // One lane runs the whole loop: a warp-wide poll + __syncwarp per k-block costs 14 % of the MMA rate
+    // (tools/mma_rate2.cu: 146 vs 128 cycles per 128x256x16 MMA).
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BN, TA, TB);
+      int i = 0, t = 0;
+      const bool rec = (EF & EF_GENERIC) && (ep.debug & 16) && blockIdx.x == 0;
+      long long w_full = 0, w_acc = 0, t_begin = rec ? clock64() : 0;
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
+        const int r = u % units_per_batch;
+        const int sp = r % splits;
+        const int kb0 = sp * kb_per_split;
+        const int nkb = min(kb_per_split, num_kb_total - kb0);
+        const int buf = t & 1;
+        long long c0 = rec ? clock64() : 0;
+        mbar_wait(bar_acc_empty + buf * 8, ((t >> 1) & 1) ^ 1);  // epilogue drained this buffer
+        if (rec) w_acc += clock64() - c0;
         tcgen05_fence_after();
-        if (lane == 0) {
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int kb = 0; kb < nkb; ++kb, ++i) {
+          const int s = i % STAGES, it = i / STAGES;
+          c0 = rec ? clock64() : 0;
+          mbar_wait(bar_full + s * 8, it & 1);
+          if (rec) w_full += clock64() - c0;
+          tcgen05_fence_after();
           const uint32_t sa = sbase + s * L::STAGE_BYTES, sb = sa + L::A_BYTES;
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
@@ -400,17 +440,34 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             const uint64_t db = TB ? make_smem_desc(sb + kk * 2048, 64 * BK * 2, 1024) : make_smem_desc(sb + kk * 32, 16, 1024);
             umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0);
           }
-          umma_commit(bar_empty + s * 8);                       // frees the smem stage once these MMAs retire
+          umma_commit(bar_empty + s * 8);                          // frees the smem stage once these MMAs retire
           if (kb == nkb - 1) umma_commit(bar_acc_full + buf * 8);  // accumulator complete
         }
-        __syncwarp();
+      }
+      if (rec) {
+        ep.dbg_out[0] = clock64() - t_begin;  // MMA issue loop, total
+        ep.dbg_out[1] = w_full;               //   of which waiting for operands
+        ep.dbg_out[2] = w_acc;                //   of which waiting for a drained accumulator
+        ep.dbg_out[3] = i;                    // k-blocks issued
+        ep.dbg_out[4] = t;                    // tiles
       }
     }
+    __syncwarp();
   } else {
-    // ===================== epilogue (8 warps: 4 lane groups x 2 column halves) =====================
+    // ===================== epilogue (4 lane quadrants x 2 or 4 column groups of warps) =====================
+    constexpr uint32_t EFC = EF;
+    constexpr int CGROUPS = epi_warps(EF) / 4;
+    constexpr int WCOLS = BN / CGROUPS;  // columns per warp
+    constexpr int NPAIR = WCOLS / 32;    // pairs of 16-column slices per warp
     const int ew = warp - 2;
-    const int lane_grp = warp & 3;      // TMEM lanes [32*lane_grp, +32) -- hardware rule: warp_id % 4
-    const int half = ew >> 2;           // columns [half*BN/2, +BN/2)
+    const int lane_grp = warp & 3;       // TMEM lanes [32*lane_grp, +32) -- hardware rule: warp_id % 4
+    const int cgrp = ew >> 2;            // columns [cgrp*WCOLS, +WCOLS) of the tile
+    float* bias_s = reinterpret_cast<float*>(smem + L::BIAS_OFF) + (lane_grp * CGROUPS + cgrp) * WCOLS;
+    B2DropKey dk = {0ull, 0u, 1.f};
+    if (((EFC & EF_GENERIC) ? ep.flags : EFC) & EF_DROP) dk = dropout_key(ep.drop);
+    const float alpha = ep.alpha;
+    const float* __restrict__ bias = ep.bias;
+    const int debug = (EFC & EF_GENERIC) ? ep.debug : 0;
     int t = 0;
     for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
       const int batch = u / units_per_batch, r = u - batch * units_per_batch;
@@ -419,30 +476,60 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
       const long long out_off = (long long)bo * ep.c_bs_outer + (long long)bi * ep.c_bs_inner;
       const int buf = t & 1;
-      mbar_wait(bar_acc_full + buf * 8, (t >> 1) & 1);
-      tcgen05_fence_after();
       const int row = tile_m * BM + lane_grp * 32 + lane;
       const bool row_ok = row < M;
-      // TMEM -> registers is double-buffered: the load of chunk i+1 is in flight while chunk i runs the epilogue math
-      constexpr int NCHUNK = BN / 64;  // 32-column chunks per column half
-      const uint32_t tbase = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + buf * BN + half * (BN / 2);
-      uint32_t r32[2][32];
-      tmem_ld32(tbase, r32[0]);
-#pragma unroll
-      for (int ci = 0; ci < NCHUNK; ++ci) {
+      const int colw = tile_n * BN + cgrp * WCOLS;
+      // split-K: bias / residual belong to the first split only
+      const uint32_t rtf = (sp == 0) ? ep.flags : (ep.flags & ~(EF_BIAS | EF_RES));
+      const uint32_t F = (EFC & EF_GENERIC) ? rtf : EFC;
+      EpiRow er;
+      er.res = ep.res + (long long)row * ep.ldres;
+      er.aux = ep.aux + (long long)row * ep.ldaux;
+      er.dact = ep.pre_out + (long long)row * ep.ldc;
+      er.out = (F & EF_F32) ? (void*)(reinterpret_cast<float*>(ep.out) + out_off + (long long)row * ep.ldc)
+                            : (void*)(reinterpret_cast<bf16*>(ep.out) + out_off + (long long)row * ep.ldc);
+      er.e0 = (unsigned long long)row * (unsigned long long)N;
+      // this warp's bias slice -> shared memory and the first slice's operands -> registers, both before the wait
+      // for the accumulator so their latency hides behind the MMAs of the tile
+      if (F & EF_BIAS) {
+        __syncwarp();  // the previous tile's reads of bias_s are done
+        for (int c = lane; c < WCOLS; c += 32) bias_s[c] = (colw + c < N) ? bias[colw + c] : 0.f;
+      }
+      EpiPre pa, pb;
+      if (!(EFC & EF_GENERIC) && row_ok) epi_prefetch<EFC>(rtf, er, colw, N, pa);
+      if (F & EF_BIAS) __syncwarp();
+      const bool rec = (EFC & EF_GENERIC) && (ep.debug & 16) && blockIdx.x == 0 && ew == 0 && lane == 0;
+      long long c0 = rec ? clock64() : 0;
+      mbar_wait(bar_acc_full + buf * 8, (t >> 1) & 1);
+      if (rec) { long long c1 = clock64(); ep.dbg_out[5] += c1 - c0; c0 = c1; }
+      tcgen05_fence_after();
+      // TMEM -> registers is double-buffered in 16-column slices: the load of slice i+1 is in flight while slice i
+      // runs the epilogue math.  The loop walks slice PAIRS and is not unrolled, so the (long) body exists twice only.
+      const uint32_t tbase = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + buf * BN + cgrp * WCOLS;
+      uint32_t ra[16], rb[16];
+      tmem_ld16(tbase, ra);
+#pragma unroll 1
+      for (int cp = 0; cp < NPAIR; ++cp) {
+        const int c0 = colw + cp * 32, c1 = c0 + 16, c2 = c0 + 32;
         tmem_ld_wait();
-        if (ci + 1 < NCHUNK) tmem_ld32(tbase + (ci + 1) * 32, r32[(ci + 1) & 1]);
-        const int col0 = tile_n * BN + half * (BN / 2) + ci * 32;
-        if (row_ok && col0 < N) {
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r32[ci & 1][j]);
-          epilogue_chunk(ep, v, row, col0, N, sp == 0, out_off);
+        tmem_ld16(tbase + cp * 32 + 16, rb);
+        if (row_ok && c0 < N && !(debug & 2)) {
+          if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c0, N, pa);
+          else if (c1 < N) epi_prefetch<EFC>(rtf, er, c1, N, pb);
+          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32, pa, ra, c0, N, debug);
+        }
+        tmem_ld_wait();
+        if (cp + 1 < NPAIR) tmem_ld16(tbase + cp * 32 + 32, ra);
+        if (row_ok && c1 < N && !(debug & 2)) {
+          if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c1, N, pb);
+          else if (cp + 1 < NPAIR && c2 < N) epi_prefetch<EFC>(rtf, er, c2, N, pa);
+          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32 + 16, pb, rb, c1, N, debug);
         }
       }
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_acc_empty + buf * 8);
+      if (rec) ep.dbg_out[6] += clock64() - c0;  // epilogue warp 0: busy cycles (dbg_out[5] = waiting for accumulators)
     }
   }
   tcgen05_fence_before();
@@ -498,11 +585,11 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return 0;
 }
 
-template <int BN, int STAGES, bool TA, bool TB>
+template <int BN, int STAGES, bool TA, bool TB, uint32_t EF>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, int M, int N, int K, int nbatch, int batch_inner, int splits,
            int kb_per, const EpiArgs& ep, cudaStream_t st) {
   using L = SmemLayout<BN, STAGES>;
-  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB>;
+  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF>;
   static bool configured = false;
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -512,9 +599,25 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, int M, int N, int K, in
   const long long units = (long long)tiles_n * tiles_m * splits * nbatch;
   B2_CHECK_ARG(units < (1LL << 30), "gemm: too many work units (%lld)", units);
   const int grid = units < b2_num_sms() ? (int)units : b2_num_sms();
-  kern<<<grid, NUM_THREADS, L::TOTAL, st>>>(ma, mb, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
-                                            (int)units, ep);
+  EpiArgs epl = ep;
+  static long long* dbg_buf = nullptr;
+  if ((EF & EF_GENERIC) && (ep.debug & 16)) {
+    if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 8 * sizeof(long long)));
+    B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 8 * sizeof(long long), st));
+    epl.dbg_out = dbg_buf;
+  }
+  kern<<<grid, num_threads(EF), L::TOTAL, st>>>(ma, mb, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
+                                                (int)units, epl);
   B2_LAUNCH_CHECK();
+  if ((EF & EF_GENERIC) && (ep.debug & 16)) {
+    long long h[8];
+    B2_CUDA(cudaStreamSynchronize(st));
+    B2_CUDA(cudaMemcpy(h, dbg_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr,
+            "[gemm dbg] M=%d N=%d K=%d BN=%d TA=%d TB=%d splits=%d grid=%d | CTA0: tiles=%lld kblocks=%lld mma_loop=%lld cyc "
+            "(wait operands %lld, wait accumulator %lld) | epi warp0: wait acc %lld, busy %lld | producer wait stage %lld\n",
+            M, N, K, BN, (int)TA, (int)TB, splits, grid, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[7]);
+  }
   return 0;
 }
 
@@ -556,7 +659,26 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     ep.out_f32 = e->out_f32;
     ep.accumulate = e->accumulate;
     ep.drop = b2_make_drop(e->dropout_p, e->dropout_seed, e->dropout_site);
+    static const int dbg = getenv("B200SLU_GEMM_DEBUG") ? atoi(getenv("B200SLU_GEMM_DEBUG")) : 0;
+    ep.debug = dbg;
   }
+  {
+    uint32_t f = 0;
+    if (ep.bias != nullptr) f |= EF_BIAS;
+    if (ep.act == B200SLU_ACT_SWISH) f |= EF_SWISH;
+    if (ep.act == B200SLU_ACT_RELU) f |= EF_RELU;
+    if (ep.pre_out != nullptr) f |= EF_DACT;
+    if (ep.drop.p > 0.f) f |= EF_DROP;
+    if (ep.alpha != 1.f && !(f & EF_DROP)) f |= EF_ALPHA;  // with dropout, alpha rides on the keep multiplier
+    if (ep.aux != nullptr)
+      f |= ep.aux_mode == B200SLU_ACT_MUL ? EF_AUX_MUL : ep.aux_mode == B200SLU_ACT_SWISH ? EF_AUX_SWISH : EF_AUX_RELU;
+    if (ep.res != nullptr) f |= EF_RES;
+    if (ep.out_f32) f |= EF_F32;
+    if (ep.accumulate) f |= EF_ACC;
+    ep.flags = f;
+  }
+  B2_CHECK_ARG(e == nullptr || e->act == B200SLU_ACT_NONE || e->act == B200SLU_ACT_SWISH || e->act == B200SLU_ACT_RELU,
+               "gemm: act must be NONE / SWISH / RELU");
   B2_CHECK_ARG(nbatch == 1 || (ep.res == nullptr && ep.aux == nullptr && ep.pre_out == nullptr && !(ep.drop.p > 0.f)),
                "gemm: batched mode supports only bias / activation / alpha epilogues");
   B2_CHECK_ARG(!(ep.drop.p > 0.f) || N % 8 == 0, "gemm: dropout epilogue needs N %% 8 == 0");
@@ -569,25 +691,39 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   B2_CHECK_ARG(ep.bias == nullptr || ((uintptr_t)ep.bias % 16) == 0, "gemm: bias alignment");
 
   const int num_kb = (K + BK - 1) / BK;
-  int splits = 1;
-  // Tile width: a 128x128 single-CTA tile reads 32 KB of shared memory per 256 MMA cycles (= the 128 B/clk port limit);
-  // 128x256 reads 48 KB per 512 cycles and lets the tensor pipe run ahead.  Take the wide tile when it does not cost
-  // more in wave quantisation than it gains (relative per-tile costs measured: profiles/r1_gemm_shapes_*.txt).
-  int bn = 128;
+  // Tile width and split-K factor from a small cost model (units of one k-block of a 128-wide tile):
+  //  * a tcgen05 MMA with N = 128 retires no faster than one with N = 256 (tools/mma_rate2.cu: 114-127 vs 128 cycles),
+  //    so the wide tile does twice the work per tensor-pipe cycle; it pays 1.15x per k-block for the larger L2 -> SM load;
+  //  * every tile adds its epilogue / pipeline turn-around;
+  //  * the persistent grid runs ceil(units / SMs) waves, each as long as its longest unit.
+  //  Split-K only for accumulating outputs (wgrad: K = B*T is long, the output is small).
+  int bn = 128, splits = 1;
   {
     const long long sms = b2_num_sms();
     const long long tm = (M + BM - 1) / BM;
-    const long long t128 = tm * ((N + 127) / 128) * nbatch, t256 = tm * ((N + 255) / 256) * nbatch;
-    const double c128 = (double)((t128 + sms - 1) / sms) * 1.0, c256 = (double)((t256 + sms - 1) / sms) * 1.45;
-    if (N >= 256 && !ep.accumulate && c256 < c128) bn = 256;
+    double best = 1e300;
+    for (int cand = 0; cand < 2; ++cand) {
+      const int cbn = cand == 0 ? 128 : 256;
+      if (cbn == 256 && N < 256) continue;
+      const long long tiles = tm * ((N + cbn - 1) / cbn) * nbatch;
+      const double w = cbn == 256 ? 1.15 : 1.0, c = cbn == 256 ? 4.0 : 2.0;
+      const int max_s = ep.accumulate ? max(1, num_kb / 4) : 1;
+      for (int sp = 1; sp <= max_s && sp <= 64; ++sp) {
+        const int kbs = (num_kb + sp - 1) / sp;
+        const long long waves = (tiles * sp + sms - 1) / sms;
+        const double cost = (double)waves * (kbs * w + c);
+        if (cost < best * 0.999) {
+          best = cost;
+          bn = cbn;
+          splits = sp;
+        }
+      }
+    }
     static const int force_bn = getenv("B200SLU_GEMM_BN") ? atoi(getenv("B200SLU_GEMM_BN")) : 0;  // tuning experiments only
-    if (force_bn == 128 || (force_bn == 256 && N >= 256 && !ep.accumulate)) bn = force_bn;
-  }
-  const long long tiles128 = (long long)((M + BM - 1) / BM) * ((N + 127) / 128) * nbatch;
-  if (ep.accumulate) {
-    // split-K (wgrad: K = B*T is long, the output is small): target >= 2 CTAs per SM
-    const int want = (int)((2LL * b2_num_sms() + tiles128 - 1) / tiles128);
-    splits = max(1, min(want, num_kb / 4 > 0 ? num_kb / 4 : 1));
+    if (force_bn == 128 || (force_bn == 256 && N >= 256)) {
+      if (force_bn != bn) splits = 1;
+      bn = force_bn;
+    }
   }
   const int kb_per = (num_kb + splits - 1) / splits;
   splits = (num_kb + kb_per - 1) / kb_per;
@@ -603,16 +739,48 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, bn));
   else
     B2_TRY(make_map(&mb, g->B, K, N, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, 64, BK));
-#define B2_GEMM_DISPATCH(BN_, ST_)                                                                                    \
-  do {                                                                                                                \
-    if (!g->trans_a && !g->trans_b) return launch<BN_, ST_, false, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st); \
-    if (!g->trans_a && g->trans_b) return launch<BN_, ST_, false, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);   \
-    if (g->trans_a && !g->trans_b) return launch<BN_, ST_, true, false>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);   \
-    return launch<BN_, ST_, true, true>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st);                       \
-  } while (0)
-  if (bn == 256) B2_GEMM_DISPATCH(256, 4);
-  B2_GEMM_DISPATCH(128, 6);
-#undef B2_GEMM_DISPATCH
+  // Specialised epilogues for the hot GEMMs of the train step; anything else runs the generic kernel.
+#define B2_L(BN_, ST_, TA_, TB_, EF_) return launch<BN_, ST_, TA_, TB_, EF_>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st)
+#define B2_CASE(BN_, ST_, TA_, TB_, EF_) \
+  if (ep.flags == (EF_)) B2_L(BN_, ST_, TA_, TB_, (EF_))
+  const bool dbg_generic = ep.debug != 0;
+  if (bn == 256) {
+    if (!g->trans_a && !g->trans_b) {  // forward:  y = x W^T
+      if (!dbg_generic) {
+        B2_CASE(256, 4, false, false, EF_BIAS);
+        B2_CASE(256, 4, false, false, EF_BIAS | EF_SWISH | EF_DACT | EF_DROP);
+        B2_CASE(256, 4, false, false, EF_BIAS | EF_RELU | EF_DACT | EF_DROP);
+        B2_CASE(256, 4, false, false, EF_BIAS | EF_DROP | EF_RES | EF_F32);
+        B2_CASE(256, 4, false, false, EF_BIAS | EF_RELU);
+        B2_CASE(256, 4, false, false, EF_BIAS | EF_F32);
+      }
+      B2_L(256, 4, false, false, EF_GENERIC);
+    }
+    if (!g->trans_a && g->trans_b) {  // dgrad:  dx = dy W
+      if (!dbg_generic) {
+        B2_CASE(256, 4, false, true, 0u);
+        B2_CASE(256, 4, false, true, EF_AUX_MUL);
+        B2_CASE(256, 4, false, true, EF_AUX_RELU);
+        B2_CASE(256, 4, false, true, EF_RES | EF_F32);
+        B2_CASE(256, 4, false, true, EF_F32);
+      }
+      B2_L(256, 4, false, true, EF_GENERIC);
+    }
+    if (g->trans_a && g->trans_b) {  // wgrad:  dW += dy^T x
+      if (!dbg_generic) B2_CASE(256, 4, true, true, EF_F32 | EF_ACC);
+      B2_L(256, 4, true, true, EF_GENERIC);
+    }
+    B2_L(256, 4, true, false, EF_GENERIC);
+  }
+  if (!g->trans_a && !g->trans_b) B2_L(128, 6, false, false, EF_GENERIC);
+  if (!g->trans_a && g->trans_b) B2_L(128, 6, false, true, EF_GENERIC);
+  if (g->trans_a && g->trans_b) {
+    if (!dbg_generic) B2_CASE(128, 6, true, true, EF_F32 | EF_ACC);
+    B2_L(128, 6, true, true, EF_GENERIC);
+  }
+  B2_L(128, 6, true, false, EF_GENERIC);
+#undef B2_CASE
+#undef B2_L
 }
 
 extern "C" int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epilogue, void* stream) {

@@ -56,13 +56,20 @@ def test_gemm_epilogue_bias_swish_residual():
     b = (torch.randn(N, K, device="cuda", generator=g) * 0.1).bfloat16()
     bias = torch.randn(N, device="cuda", generator=g)
     res = torch.randn(M, N, device="cuda", generator=g)
-    out, pre = ops.gemm(a, b, bias=bias, act="swish", alpha=0.5, residual=res, pre_act_out=True, out_dtype=torch.float32)
+    out, dact = ops.gemm(a, b, bias=bias, act="swish", alpha=0.5, residual=res, act_grad_out=True, out_dtype=torch.float32)
     y = ref_mm(a, b, False) + bias
     want = res + 0.5 * y * torch.sigmoid(y)
-    assert (out - want).abs().max().item() < 2e-3
-    assert (pre.float() - y).abs().max().item() < 0.05
-    # activation-gradient epilogue: dH = (g @ W) * swish'(pre)
+    assert (out - want).abs().max().item() < 3e-3
+    sg = torch.sigmoid(y)
+    want_d = sg * (1 + y * (1 - sg))   # swish'(y): what the forward saves for the dgrad epilogue
+    assert (dact.float() - want_d).abs().max().item() < 0.01
+    # saved-derivative epilogue: dH = (g @ W) * dact
     gy = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    out1 = ops.gemm(gy, b, act_grad_input=dact, act_grad="mul")
+    want1 = ref_mm(gy, b, False) * dact.float()
+    assert (out1.float() - want1).abs().max().item() < 0.02 * want1.abs().max().item()
+    # activation-gradient epilogue from a pre-activation tensor: dH = (g @ W) * swish'(pre)
+    pre = y.bfloat16()
     out2 = ops.gemm(gy, b, act_grad_input=pre, act_grad="swish")
     s = torch.sigmoid(pre.float())
     want2 = ref_mm(gy, b, False) * (s * (1 + pre.float() * (1 - s)))
@@ -70,6 +77,16 @@ def test_gemm_epilogue_bias_swish_residual():
     out3 = ops.gemm(gy, b, act_grad_input=pre, act_grad="relu", bias=bias, act="relu")
     want3 = torch.relu(ref_mm(gy, b, False) + bias) * (pre.float() > 0)
     assert (out3.float() - want3).abs().max().item() < 0.02 * want3.abs().max().item()
+    # ReLU forward saves a 0/1 mask; with dropout the saved tensor carries the element's multiplier
+    o4, d4 = ops.gemm(a, b, bias=bias, act="relu", act_grad_out=True, drop=(0.25, 11, 3))
+    o4f, d4f = o4.float(), d4.float()
+    yb = torch.relu(y)
+    kept = d4f > 0
+    assert ((d4f == 0) | ((d4f - 1 / 0.75).abs() < 0.01)).all()
+    assert ((o4f - yb / 0.75).abs()[kept] < 0.02 * yb.abs().max()).all()
+    assert (o4f[(y > 0.05) & ~kept] == 0).all()
+    frac = kept[y > 0].float().mean().item()
+    assert abs(frac - 0.75) < 0.01
 
 
 def test_gemm_dropout_statistics_and_determinism():

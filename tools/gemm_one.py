@@ -1,24 +1,21 @@
-"""Run a few representative GEMM launches (for ncu --set full captures)."""
-import sys, os
+"""Four representative GEMM launches of the train step, three rounds (ncu: -k regex:gemm_bf16 -s 8 -c 4 = third round)."""
+import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import torch
 from espnet_slurp_b200 import ops
+
 torch.manual_seed(0)
-B, T, H, d = 64, 155, 8, 512
-M = B * T
-x = torch.randn(M, 3 * d, device="cuda").bfloat16()
-w1 = torch.randn(2048, d, device="cuda").bfloat16()
-ln = torch.randn(M, d, device="cuda").bfloat16()
-bias = torch.randn(2048, device="cuda")
+M, d, F = 9920, 512, 2048
+x = torch.randn(M, d, device="cuda").bfloat16()
+h = torch.randn(M, F, device="cuda").bfloat16()
+w1 = (torch.randn(F, d, device="cuda") * 0.05).bfloat16()
+w2 = (torch.randn(d, F, device="cuda") * 0.05).bfloat16()
+b1 = torch.randn(F, device="cuda"); b2 = torch.randn(d, device="cuda")
+res = torch.randn(M, d, device="cuda")
+dact = torch.rand(M, F, device="cuda").bfloat16()
 for it in range(3):
-    # 1: attention scores, batched (155x155x64) x 512
-    s = ops.attn_f1(x[:, :d], x[:, d:2 * d], B, T, T, H)
-    # 2: FFN w_1 forward with bias + swish + pre-act + dropout
-    h, pre = ops.gemm(ln, w1, bias=bias, act="swish", pre_act_out=True, drop=(0.1, 1, 2))
-    # 3: plain dgrad 9920x512x2048
-    g = ops.gemm(h, w1, trans_b=True)
-    # 4: wgrad split-K 2048x512 K=9920
-    acc = torch.zeros(2048, d, device="cuda")
-    ops.gemm(h, ln, trans=True, out=acc, accumulate=True)
+    ops.gemm(x, w1, bias=b1)                                                             # 1: bias only, N=2048 K=512
+    ops.gemm(x, w1, bias=b1, act="swish", act_grad_out=True, drop=(0.1, 1, 2))           # 2: FFN w_1 forward
+    ops.gemm(x, w2, trans_b=True, act_grad_input=dact, act_grad="mul")                   # 3: FFN w_1 dgrad
+    ops.gemm(h, w2, bias=b2, drop=(0.1, 1, 3), residual=res, alpha=0.5, out_dtype=torch.float32)  # 4: FFN w_2 forward
 torch.cuda.synchronize()
 print("ok")

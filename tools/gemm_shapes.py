@@ -11,7 +11,7 @@ lib = _lib.lib()
 orig = lib.b200slu_gemm_bf16_ex
 
 def key_of(g, ep):
-    return (g.trans_a, g.trans_b, g.M, g.N, g.K, g.batch_inner, g.batch_outer, int(bool(ep.bias)), ep.act, int(bool(ep.pre_act_out)),
+    return (g.trans_a, g.trans_b, g.M, g.N, g.K, g.batch_inner, g.batch_outer, int(bool(ep.bias)), ep.act, int(bool(ep.act_grad_out)),
             int(ep.dropout_p > 0), int(bool(ep.act_grad_input)), int(bool(ep.residual)), ep.out_f32, ep.accumulate)
 
 class Rec:
@@ -60,7 +60,7 @@ def main():
         g.A, g.B, g.C = A.data_ptr(), Bm.data_ptr(), Cm.data_ptr()
         bufs = []
         if ep.bias: t = torch.zeros(N + 8, device="cuda"); ep.bias = t.data_ptr(); bufs.append(t)
-        if ep.pre_act_out: t = torch.zeros(csz, device="cuda", dtype=torch.bfloat16); ep.pre_act_out = t.data_ptr(); bufs.append(t)
+        if ep.act_grad_out: t = torch.zeros(csz, device="cuda", dtype=torch.bfloat16); ep.act_grad_out = t.data_ptr(); bufs.append(t)
         if ep.act_grad_input: t = torch.randn(M * ep.ld_act_grad_input + 4096, device="cuda").bfloat16(); ep.act_grad_input = t.data_ptr(); bufs.append(t)
         if ep.residual: t = torch.zeros(M * ep.ld_residual + 4096, device="cuda"); ep.residual = t.data_ptr(); bufs.append(t)
         for _ in range(3):
