@@ -69,6 +69,25 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+// Bulk tensor stores (shared -> global) of one staged box; the .add form is the split-K reduction.
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map), "r"(src),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map),
+               "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -147,9 +166,8 @@ enum : uint32_t {
   EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
   EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_GENERIC = 1u << 31
 };
-// Epilogue warps: 16 (4 per TMEM lane quadrant = 4 per scheduler, 96 registers each) hide the epilogue latencies best;
-// the generic kernel and the residual epilogues (two fp32 prefetch buffers) need the 168 registers of the 8-warp shape.
-__host__ __device__ constexpr int epi_warps(uint32_t ef) { return (ef & (EF_GENERIC | EF_RES)) ? 8 : 16; }
+// Epilogue warps: 2 per TMEM lane quadrant (16 warps at 96 registers each measured slower than 8 at 168).
+__host__ __device__ constexpr int epi_warps(uint32_t) { return 8; }
 __host__ __device__ constexpr int num_threads(uint32_t ef) { return 64 + 32 * epi_warps(ef); }
 
 template <int BN, int STAGES>
@@ -157,8 +175,11 @@ struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
   static constexpr int NUM_BARS = 2 * STAGES + 4;
+  // output staging for the TMA stores: per epilogue warp two boxes of 32 rows x 128 B (SWIZZLE_128B), 1024-B aligned
+  static constexpr int STG_OFF = STAGES * STAGE_BYTES;
+  static constexpr int STG_BYTES = 8 * 2 * 4096;
+  static constexpr int BAR_OFF = STG_OFF + STG_BYTES;
   static constexpr int BIAS_OFF = BAR_OFF + NUM_BARS * 8 + 16;       // per-tile bias slice, one segment per epilogue warp
   static constexpr int BIAS_BYTES = 4 * BN * 4;                      // 4 lane quadrants x BN floats
   static constexpr int TOTAL = BIAS_OFF + BIAS_BYTES + 1024;         // + alignment slack
@@ -169,8 +190,6 @@ struct SmemLayout {
 struct EpiRow {
   const float* res;   // residual row (or nullptr)
   const bf16* aux;    // activation-derivative row (or nullptr)
-  bf16* dact;         // saved act' * dropout-multiplier row (or nullptr)
-  void* out;          // output row
   unsigned long long e0;  // flat element index of (row, 0) for the dropout counter
 };
 
@@ -250,75 +269,60 @@ __device__ __forceinline__ void epi_prefetch(uint32_t rt_flags, const EpiRow& er
   }
 }
 
-// One 16-column slice of one accumulator row.  Whole slices take the vector path; the ragged last slice of a row
-// (N % 16 != 0) takes a guarded scalar path around the same arithmetic.  bias_s: this slice's 16 bias values in shared
-// memory (zero-filled past N).  rt_flags already has the split-K gating applied (bias / residual on the first split).
+// One 16-column slice (index sl within the warp's columns) of one accumulator row: fused arithmetic, then the results
+// go to this lane's row of the staging boxes in shared memory (SWIZZLE_128B: 16-byte chunk c of row r sits at
+// r*128 + ((c ^ (r & 7)) << 4), which is also bank-conflict-free for the 32 lanes writing 32 rows).  The boxes leave
+// through TMA bulk stores, which clip rows >= M and columns >= N; only the operand LOADS of a ragged last slice
+// (N % 16 != 0) need guarding.  bias_s: this slice's 16 bias values in shared memory (zero-filled past N).
+// rt_flags already has the split-K gating applied (bias / residual on the first split only).
 template <uint32_t EF>
 __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs& ep, const B2DropKey& dk, const EpiRow& er,
                                                float alpha, const float* bias_s, const EpiPre& pre, const uint32_t (&acc)[16],
-                                               int col0, int N, int debug) {
+                                               int col0, int N, int sl, int lane, uint32_t stg_out, uint32_t stg_d) {
   const uint32_t F = (EF & EF_GENERIC) ? rt_flags : EF;
-  if (col0 + 16 <= N) {
+  const uint32_t rowoff = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
+  const bool whole = col0 + 16 <= N;
 #pragma unroll
-    for (int g = 0; g < 2; ++g) {
-      const int c = col0 + g * 8;
-      float w[8], d[8], b[8] = {}, x[8] = {};
-      if (F & EF_BIAS) load8_f32(bias_s + g * 8, b);
+  for (int g = 0; g < 2; ++g) {
+    const int c = col0 + g * 8;
+    float w[8], d[8], b[8] = {}, x[8] = {}, r[8] = {};
+    if (F & EF_BIAS) load8_f32(bias_s + g * 8, b);
+    if (whole) {
       if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) {
         const float2 x0 = unpack_bf16x2(pre.x[g].x), x1 = unpack_bf16x2(pre.x[g].y), x2 = unpack_bf16x2(pre.x[g].z),
                      x3 = unpack_bf16x2(pre.x[g].w);
         x[0] = x0.x; x[1] = x0.y; x[2] = x1.x; x[3] = x1.y; x[4] = x2.x; x[5] = x2.y; x[6] = x3.x; x[7] = x3.y;
       }
+      if (F & EF_RES) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) w[j] = __uint_as_float(acc[g * 8 + j]);
-      epi_math8<EF>(rt_flags, ep, dk, alpha, er.e0, c, w, b, x, pre.r[g], d);
-      if ((EF & EF_GENERIC) && (debug & 1)) {
-        if (w[0] == 1.2345e-30f && d[3] == 3.3e-33f) store8_f32(reinterpret_cast<float*>(er.out) + c, w);
-        continue;
+        for (int j = 0; j < 8; ++j) r[j] = pre.r[g][j];
       }
-      if (F & EF_DACT) store8_bf16(er.dact + c, d);
-      if (F & EF_F32) {
-        float* o = reinterpret_cast<float*>(er.out) + c;
-        if (F & EF_ACC) {  // split-K partial sums: 16-byte vector reductions (4x fewer L2 requests than scalar RED)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o), "f"(w[0]), "f"(w[1]), "f"(w[2]), "f"(w[3])
-                       : "memory");
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + 4), "f"(w[4]), "f"(w[5]), "f"(w[6]), "f"(w[7])
-                       : "memory");
-        } else {
-          store8_f32(o, w);
-        }
-      } else {
-        store8_bf16(reinterpret_cast<bf16*>(er.out) + c, w);
-      }
-    }
-  } else {
-#pragma unroll 1
-    for (int g = 0; g < 2; ++g) {
-      const int c = col0 + g * 8;
-      if (c >= N) break;
-      float w[8], b[8], x[8], r[8], d[8];
+    } else {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const bool ok = c + j < N;
-        w[j] = __uint_as_float(g == 0 ? acc[j] : acc[8 + j]);  // select, not a dynamic index: acc stays in registers
-        b[j] = (F & EF_BIAS) ? bias_s[g * 8 + j] : 0.f;
-        x[j] = ((F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) && ok) ? __bfloat162float(er.aux[c + j]) : 0.f;
-        r[j] = ((F & EF_RES) && ok) ? er.res[c + j] : 0.f;
+        if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) x[j] = ok ? __bfloat162float(er.aux[c + j]) : 0.f;
+        if (F & EF_RES) r[j] = ok ? er.res[c + j] : 0.f;
       }
-      epi_math8<EF>(rt_flags, ep, dk, alpha, er.e0, c, w, b, x, r, d);
+    }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        if (c + j < N) {
-          if (F & EF_DACT) er.dact[c + j] = __float2bfloat16(d[j]);
-          if (F & EF_F32) {
-            float* o = reinterpret_cast<float*>(er.out) + c + j;
-            if (F & EF_ACC) atomicAdd(o, w[j]);
-            else *o = w[j];
-          } else {
-            reinterpret_cast<bf16*>(er.out)[c + j] = __float2bfloat16(w[j]);
-          }
-        }
-      }
+    for (int j = 0; j < 8; ++j) w[j] = __uint_as_float(acc[g * 8 + j]);
+    epi_math8<EF>(rt_flags, ep, dk, alpha, er.e0, c, w, b, x, r, d);
+    if (F & EF_DACT) {
+      const uint32_t ch = (uint32_t)((sl & 3) * 2 + g);
+      sts128(stg_d + rowoff + ((ch ^ sw) << 4), pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]),
+             pack_bf16x2(d[6], d[7]));
+    }
+    if (F & EF_F32) {
+      const uint32_t ch = (uint32_t)((sl & 1) * 4 + g * 2);
+      sts128(stg_out + rowoff + ((ch ^ sw) << 4), __float_as_uint(w[0]), __float_as_uint(w[1]), __float_as_uint(w[2]),
+             __float_as_uint(w[3]));
+      sts128(stg_out + rowoff + (((ch + 1) ^ sw) << 4), __float_as_uint(w[4]), __float_as_uint(w[5]), __float_as_uint(w[6]),
+             __float_as_uint(w[7]));
+    } else {
+      const uint32_t ch = (uint32_t)((sl & 3) * 2 + g);
+      sts128(stg_out + rowoff + ((ch ^ sw) << 4), pack_bf16x2(w[0], w[1]), pack_bf16x2(w[2], w[3]), pack_bf16x2(w[4], w[5]),
+             pack_bf16x2(w[6], w[7]));
     }
   }
 }
@@ -327,7 +331,7 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
 template <int BN, int STAGES, bool TA, bool TB, uint32_t EF>
 __global__ void __launch_bounds__(num_threads(EF), 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                  int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
+                  const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_d, int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
                   int num_units, EpiArgs ep) {
   using L = SmemLayout<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
@@ -346,6 +350,8 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
+    if (((EF & EF_GENERIC) ? ep.flags : EF) & EF_DACT) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_d) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_full + s * 8, 1);
       mbar_init(bar_empty + s * 8, 1);
@@ -380,7 +386,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const int abi = bi * ep.a_bc_inner, abo = bo * ep.a_bc_outer, bbi = bi * ep.b_bc_inner, bbo = bo * ep.b_bc_outer;
         for (int kb = 0; kb < nkb; ++kb, ++i) {
           const int s = i % STAGES, it = i / STAGES;
-          const bool rec = (EF & EF_GENERIC) && (ep.debug & 16) && blockIdx.x == 0;
+          const bool rec = (ep.debug & 16) && blockIdx.x == 0;
           const long long c0 = rec ? clock64() : 0;
           mbar_wait(bar_empty + s * 8, (it & 1) ^ 1);
           if (rec) ep.dbg_out[7] += clock64() - c0;  // producer: waiting for a free stage
@@ -412,7 +418,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(BN, TA, TB);
       int i = 0, t = 0;
-      const bool rec = (EF & EF_GENERIC) && (ep.debug & 16) && blockIdx.x == 0;
+      const bool rec = (ep.debug & 16) && blockIdx.x == 0;
       long long w_full = 0, w_acc = 0, t_begin = rec ? clock64() : 0;
       for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
         const int r = u % units_per_batch;
@@ -454,7 +460,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     __syncwarp();
   } else {
-    // ===================== epilogue (4 lane quadrants x 2 or 4 column groups of warps) =====================
+    // ===================== epilogue (8 warps: 4 lane quadrants x 2 column halves) =====================
     constexpr uint32_t EFC = EF;
     constexpr int CGROUPS = epi_warps(EF) / 4;
     constexpr int WCOLS = BN / CGROUPS;  // columns per warp
@@ -463,31 +469,31 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const int lane_grp = warp & 3;       // TMEM lanes [32*lane_grp, +32) -- hardware rule: warp_id % 4
     const int cgrp = ew >> 2;            // columns [cgrp*WCOLS, +WCOLS) of the tile
     float* bias_s = reinterpret_cast<float*>(smem + L::BIAS_OFF) + (lane_grp * CGROUPS + cgrp) * WCOLS;
+    const uint32_t stg0 = sbase + L::STG_OFF + ew * 8192, stg1 = stg0 + 4096;
     B2DropKey dk = {0ull, 0u, 1.f};
     if (((EFC & EF_GENERIC) ? ep.flags : EFC) & EF_DROP) dk = dropout_key(ep.drop);
     const float alpha = ep.alpha;
     const float* __restrict__ bias = ep.bias;
     const int debug = (EFC & EF_GENERIC) ? ep.debug : 0;
     int t = 0;
+    uint32_t nflush = 0;  // boxes of the main output flushed so far by this warp (selects the staging buffer)
     for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
       const int batch = u / units_per_batch, r = u - batch * units_per_batch;
       const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
       const int tile = r / splits, sp = r - tile * splits;
       const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
-      const long long out_off = (long long)bo * ep.c_bs_outer + (long long)bi * ep.c_bs_inner;
       const int buf = t & 1;
-      const int row = tile_m * BM + lane_grp * 32 + lane;
+      const int row0 = tile_m * BM + lane_grp * 32, row = row0 + lane;
       const bool row_ok = row < M;
       const int colw = tile_n * BN + cgrp * WCOLS;
       // split-K: bias / residual belong to the first split only
       const uint32_t rtf = (sp == 0) ? ep.flags : (ep.flags & ~(EF_BIAS | EF_RES));
       const uint32_t F = (EFC & EF_GENERIC) ? rtf : EFC;
+      // with a saved-derivative output the two boxes are (out, dact); otherwise they double-buffer the output
+      const bool two_out = (F & EF_DACT) != 0;
       EpiRow er;
       er.res = ep.res + (long long)row * ep.ldres;
       er.aux = ep.aux + (long long)row * ep.ldaux;
-      er.dact = ep.pre_out + (long long)row * ep.ldc;
-      er.out = (F & EF_F32) ? (void*)(reinterpret_cast<float*>(ep.out) + out_off + (long long)row * ep.ldc)
-                            : (void*)(reinterpret_cast<bf16*>(ep.out) + out_off + (long long)row * ep.ldc);
       er.e0 = (unsigned long long)row * (unsigned long long)N;
       // this warp's bias slice -> shared memory and the first slice's operands -> registers, both before the wait
       // for the accumulator so their latency hides behind the MMAs of the tile
@@ -498,7 +504,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       EpiPre pa, pb;
       if (!(EFC & EF_GENERIC) && row_ok) epi_prefetch<EFC>(rtf, er, colw, N, pa);
       if (F & EF_BIAS) __syncwarp();
-      const bool rec = (EFC & EF_GENERIC) && (ep.debug & 16) && blockIdx.x == 0 && ew == 0 && lane == 0;
+      const bool rec = (ep.debug & 16) && blockIdx.x == 0 && ew == 0 && lane == 0;
       long long c0 = rec ? clock64() : 0;
       mbar_wait(bar_acc_full + buf * 8, (t >> 1) & 1);
       if (rec) { long long c1 = clock64(); ep.dbg_out[5] += c1 - c0; c0 = c1; }
@@ -510,27 +516,60 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       tmem_ld16(tbase, ra);
 #pragma unroll 1
       for (int cp = 0; cp < NPAIR; ++cp) {
-        const int c0 = colw + cp * 32, c1 = c0 + 16, c2 = c0 + 32;
+        const int c0c = colw + cp * 32, c1c = c0c + 16, c2c = c0c + 32;
+        const int sl0 = cp * 2, sl1 = sl0 + 1;
+        // A box of the main output spans 4 slices (bf16, 64 columns) or 2 slices (fp32, 32 columns).
+        const bool box_start = (F & EF_F32) ? true : ((cp & 1) == 0);
+        const bool box_end = (F & EF_F32) ? true : ((cp & 1) == 1);
+        const uint32_t so = two_out ? stg0 : ((nflush & 1) ? stg1 : stg0);
+        long long q0 = rec ? clock64() : 0;
+        if (box_start) {
+          // the bulk store that last read this staging box must have finished reading it
+          if (lane == 0) {
+            if (two_out) bulk_wait_read<0>();
+            else bulk_wait_read<1>();
+          }
+          __syncwarp();
+        }
+        if (rec) { const long long q1 = clock64(); ep.dbg_out[8] += q1 - q0; q0 = q1; }
         tmem_ld_wait();
+        if (rec) { const long long q1 = clock64(); ep.dbg_out[9] += q1 - q0; q0 = q1; }
         tmem_ld16(tbase + cp * 32 + 16, rb);
-        if (row_ok && c0 < N && !(debug & 2)) {
-          if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c0, N, pa);
-          else if (c1 < N) epi_prefetch<EFC>(rtf, er, c1, N, pb);
-          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32, pa, ra, c0, N, debug);
+        if (row_ok && c0c < N && !(debug & 2)) {
+          if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c0c, N, pa);
+          else if (c1c < N) epi_prefetch<EFC>(rtf, er, c1c, N, pb);
+          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32, pa, ra, c0c, N, sl0, lane, so, stg1);
         }
         tmem_ld_wait();
         if (cp + 1 < NPAIR) tmem_ld16(tbase + cp * 32 + 32, ra);
-        if (row_ok && c1 < N && !(debug & 2)) {
-          if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c1, N, pb);
-          else if (cp + 1 < NPAIR && c2 < N) epi_prefetch<EFC>(rtf, er, c2, N, pa);
-          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32 + 16, pb, rb, c1, N, debug);
+        if (row_ok && c1c < N && !(debug & 2)) {
+          if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c1c, N, pb);
+          else if (cp + 1 < NPAIR && c2c < N) epi_prefetch<EFC>(rtf, er, c2c, N, pa);
+          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32 + 16, pb, rb, c1c, N, sl1, lane, so, stg1);
         }
+        if (rec) { const long long q1 = clock64(); ep.dbg_out[10] += q1 - q0; q0 = q1; }
+        if (box_end && !(debug & 1)) {
+          fence_async_smem();  // generic-proxy writes of every lane -> visible to the async proxy
+          __syncwarp();
+          const int bcol = (F & EF_F32) ? c0c : c0c - 32;  // first column of the box
+          if (lane == 0) {
+            if (bcol < N && row0 < M) {
+              if (F & EF_ACC) tma_reduce_add_4d(&map_c, so, bcol, row0, bi, bo);
+              else tma_store_4d(&map_c, so, bcol, row0, bi, bo);
+              if (two_out) tma_store_4d(&map_d, stg1, bcol, row0, bi, bo);
+            }
+            bulk_commit();  // also when nothing was stored: keeps the group count in step with the staging buffers
+          }
+          if (!two_out) ++nflush;
+        }
+        if (rec) { const long long q1 = clock64(); ep.dbg_out[11] += q1 - q0; q0 = q1; }
       }
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_acc_empty + buf * 8);
       if (rec) ep.dbg_out[6] += clock64() - c0;  // epilogue warp 0: busy cycles (dbg_out[5] = waiting for accumulators)
     }
+    if (lane == 0) bulk_wait_read<0>();  // the staging boxes are no longer being read when the CTA exits
   }
   tcgen05_fence_before();
   __syncthreads();
@@ -557,10 +596,10 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
-// 4-D bf16 tensor [n_outer, n_inner, rows, cols]: row stride ld, batch strides s_inner / s_outer (elements;
-// 0 = broadcast -> that dimension gets extent 1).  box = {box_cols, box_rows, 1, 1}.
+// 4-D tensor [n_outer, n_inner, rows, cols] of bf16 (esize 2) or fp32 (esize 4): row stride ld, batch strides
+// s_inner / s_outer (elements; 0 = broadcast -> that dimension gets extent 1).  box = {box_cols, box_rows, 1, 1}.
 int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld, long long n_inner,
-             long long s_inner, long long n_outer, long long s_outer, int box_cols, int box_rows) {
+             long long s_inner, long long n_outer, long long s_outer, int box_cols, int box_rows, int esize = 2) {
   EncodeTiledFn enc = get_encode();
   if (enc == nullptr) {
     b200slu_set_error("cuTensorMapEncodeTiled driver entry point unavailable");
@@ -571,22 +610,22 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   if (n_inner == 1) s_inner = ld;  // any legal stride; the coordinate is always 0
   if (n_outer == 1) s_outer = ld;
   cuuint64_t dims[4] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)n_inner, (cuuint64_t)n_outer};
-  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)s_inner * 2, (cuuint64_t)s_outer * 2};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * esize, (cuuint64_t)s_inner * esize, (cuuint64_t)s_outer * esize};
   cuuint32_t box[4] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(m, esize == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    b200slu_set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld ld=%lld batch=(%lld x %lld, strides %lld %lld) base=%p",
-                      (int)r, rows, cols, ld, n_inner, n_outer, s_inner, s_outer, base);
+    b200slu_set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld ld=%lld esize=%d batch=(%lld x %lld, strides %lld %lld) base=%p",
+                      (int)r, rows, cols, ld, esize, n_inner, n_outer, s_inner, s_outer, base);
     return B200SLU_ECUDA;
   }
   return 0;
 }
 
 template <int BN, int STAGES, bool TA, bool TB, uint32_t EF>
-int launch(const CUtensorMap& ma, const CUtensorMap& mb, int M, int N, int K, int nbatch, int batch_inner, int splits,
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md, int M, int N, int K, int nbatch, int batch_inner, int splits,
            int kb_per, const EpiArgs& ep, cudaStream_t st) {
   using L = SmemLayout<BN, STAGES>;
   auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF>;
@@ -601,22 +640,24 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, int M, int N, int K, in
   const int grid = units < b2_num_sms() ? (int)units : b2_num_sms();
   EpiArgs epl = ep;
   static long long* dbg_buf = nullptr;
-  if ((EF & EF_GENERIC) && (ep.debug & 16)) {
-    if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 8 * sizeof(long long)));
-    B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 8 * sizeof(long long), st));
+  if (ep.debug & 16) {
+    if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 12 * sizeof(long long)));
+    B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 12 * sizeof(long long), st));
     epl.dbg_out = dbg_buf;
   }
-  kern<<<grid, num_threads(EF), L::TOTAL, st>>>(ma, mb, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
+  kern<<<grid, num_threads(EF), L::TOTAL, st>>>(ma, mb, mc, md, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
                                                 (int)units, epl);
   B2_LAUNCH_CHECK();
-  if ((EF & EF_GENERIC) && (ep.debug & 16)) {
-    long long h[8];
+  if (ep.debug & 16) {
+    long long h[12];
     B2_CUDA(cudaStreamSynchronize(st));
     B2_CUDA(cudaMemcpy(h, dbg_buf, sizeof(h), cudaMemcpyDeviceToHost));
     fprintf(stderr,
             "[gemm dbg] M=%d N=%d K=%d BN=%d TA=%d TB=%d splits=%d grid=%d | CTA0: tiles=%lld kblocks=%lld mma_loop=%lld cyc "
-            "(wait operands %lld, wait accumulator %lld) | epi warp0: wait acc %lld, busy %lld | producer wait stage %lld\n",
-            M, N, K, BN, (int)TA, (int)TB, splits, grid, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[7]);
+            "(wait operands %lld, wait accumulator %lld) | epi warp0: wait acc %lld, busy %lld [staging free %lld, tmem wait %lld, "
+            "slices %lld, flush %lld] | producer wait stage %lld | EF=%u\n",
+            M, N, K, BN, (int)TA, (int)TB, splits, grid, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[8], h[9], h[10], h[11], h[7],
+            (unsigned)EF);
   }
   return 0;
 }
@@ -683,6 +724,8 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
                "gemm: batched mode supports only bias / activation / alpha epilogues");
   B2_CHECK_ARG(!(ep.drop.p > 0.f) || N % 8 == 0, "gemm: dropout epilogue needs N %% 8 == 0");
   B2_CHECK_ARG(!ep.accumulate || ep.out_f32, "gemm: accumulate needs fp32 output");
+  B2_CHECK_ARG(ep.pre_out == nullptr || (!ep.out_f32 && g->ldc % 8 == 0 && ((uintptr_t)ep.pre_out % 16) == 0),
+               "gemm: act_grad_out needs a bf16 output and shares its row stride");
   const int vec = ep.out_f32 ? 4 : 8;
   B2_CHECK_ARG(g->ldc % vec == 0 && ((uintptr_t)g->C % 16) == 0 && g->c_stride_inner % vec == 0 && g->c_stride_outer % vec == 0,
                "gemm: output must be 16-byte aligned, ldc / batch strides %% %d == 0", vec);
@@ -739,46 +782,71 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, bn));
   else
     B2_TRY(make_map(&mb, g->B, K, N, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, 64, BK));
+  // output boxes: 32 rows x 128 bytes, one per epilogue warp and flush
+  CUtensorMap mc, md;
+  B2_TRY(make_map(&mc, g->C, M, N, g->ldc, nbi, g->c_stride_inner, nbo, g->c_stride_outer, ep.out_f32 ? 32 : 64, 32,
+                  ep.out_f32 ? 4 : 2));
+  if (ep.pre_out != nullptr)
+    B2_TRY(make_map(&md, ep.pre_out, M, N, g->ldc, 1, 0, 1, 0, 64, 32, 2));
+  else
+    md = mc;
   // Specialised epilogues for the hot GEMMs of the train step; anything else runs the generic kernel.
-#define B2_L(BN_, ST_, TA_, TB_, EF_) return launch<BN_, ST_, TA_, TB_, EF_>(ma, mb, M, N, K, nbatch, nbi, splits, kb_per, ep, st)
+#define B2_L(BN_, ST_, TA_, TB_, EF_) return launch<BN_, ST_, TA_, TB_, EF_>(ma, mb, mc, md, M, N, K, nbatch, nbi, splits, kb_per, ep, st)
 #define B2_CASE(BN_, ST_, TA_, TB_, EF_) \
   if (ep.flags == (EF_)) B2_L(BN_, ST_, TA_, TB_, (EF_))
-  const bool dbg_generic = ep.debug != 0;
+  const bool dbg_generic = (ep.debug & ~16) != 0;
   if (bn == 256) {
     if (!g->trans_a && !g->trans_b) {  // forward:  y = x W^T
       if (!dbg_generic) {
-        B2_CASE(256, 4, false, false, EF_BIAS);
-        B2_CASE(256, 4, false, false, EF_BIAS | EF_SWISH | EF_DACT | EF_DROP);
-        B2_CASE(256, 4, false, false, EF_BIAS | EF_RELU | EF_DACT | EF_DROP);
-        B2_CASE(256, 4, false, false, EF_BIAS | EF_DROP | EF_RES | EF_F32);
-        B2_CASE(256, 4, false, false, EF_BIAS | EF_RELU);
-        B2_CASE(256, 4, false, false, EF_BIAS | EF_F32);
+        B2_CASE(256, 3, false, false, EF_BIAS);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_SWISH | EF_DACT | EF_DROP);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_RELU | EF_DACT | EF_DROP);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_DROP | EF_RES | EF_F32);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_RELU);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_F32);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_DROP | EF_F32);
+        B2_CASE(256, 3, false, false, EF_F32);
+        B2_CASE(256, 3, false, false, 0u);
       }
-      B2_L(256, 4, false, false, EF_GENERIC);
+      B2_L(256, 3, false, false, EF_GENERIC);
     }
     if (!g->trans_a && g->trans_b) {  // dgrad:  dx = dy W
       if (!dbg_generic) {
-        B2_CASE(256, 4, false, true, 0u);
-        B2_CASE(256, 4, false, true, EF_AUX_MUL);
-        B2_CASE(256, 4, false, true, EF_AUX_RELU);
-        B2_CASE(256, 4, false, true, EF_RES | EF_F32);
-        B2_CASE(256, 4, false, true, EF_F32);
+        B2_CASE(256, 3, false, true, 0u);
+        B2_CASE(256, 3, false, true, EF_AUX_MUL);
+        B2_CASE(256, 3, false, true, EF_AUX_RELU);
+        B2_CASE(256, 3, false, true, EF_RES | EF_F32);
+        B2_CASE(256, 3, false, true, EF_F32);
       }
-      B2_L(256, 4, false, true, EF_GENERIC);
+      B2_L(256, 3, false, true, EF_GENERIC);
     }
     if (g->trans_a && g->trans_b) {  // wgrad:  dW += dy^T x
-      if (!dbg_generic) B2_CASE(256, 4, true, true, EF_F32 | EF_ACC);
-      B2_L(256, 4, true, true, EF_GENERIC);
+      if (!dbg_generic) B2_CASE(256, 3, true, true, EF_F32 | EF_ACC);
+      B2_L(256, 3, true, true, EF_GENERIC);
     }
-    B2_L(256, 4, true, false, EF_GENERIC);
+    B2_L(256, 3, true, false, EF_GENERIC);
   }
-  if (!g->trans_a && !g->trans_b) B2_L(128, 6, false, false, EF_GENERIC);
-  if (!g->trans_a && g->trans_b) B2_L(128, 6, false, true, EF_GENERIC);
+  // narrow tiles: the batched attention contractions (N = T or d_k) and small-N heads
+  if (!g->trans_a && !g->trans_b) {
+    if (!dbg_generic) {
+      B2_CASE(128, 4, false, false, EF_F32);
+      B2_CASE(128, 4, false, false, 0u);
+      B2_CASE(128, 4, false, false, EF_BIAS);
+    }
+    B2_L(128, 4, false, false, EF_GENERIC);
+  }
+  if (!g->trans_a && g->trans_b) {
+    if (!dbg_generic) B2_CASE(128, 4, false, true, 0u);
+    B2_L(128, 4, false, true, EF_GENERIC);
+  }
   if (g->trans_a && g->trans_b) {
-    if (!dbg_generic) B2_CASE(128, 6, true, true, EF_F32 | EF_ACC);
-    B2_L(128, 6, true, true, EF_GENERIC);
+    if (!dbg_generic) {
+      B2_CASE(128, 4, true, true, EF_F32 | EF_ACC);
+      B2_CASE(128, 4, true, true, 0u);
+    }
+    B2_L(128, 4, true, true, EF_GENERIC);
   }
-  B2_L(128, 6, true, false, EF_GENERIC);
+  B2_L(128, 4, true, false, EF_GENERIC);
 #undef B2_CASE
 #undef B2_L
 }

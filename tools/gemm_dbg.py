@@ -11,6 +11,7 @@ w2 = (torch.randn(d, F, device="cuda") * 0.05).bfloat16()
 b1 = torch.randn(F, device="cuda")
 for rep in range(2):
     ops.gemm(x[:128 * 37], w1[:1024]);  torch.cuda.synchronize()              # 148 tiles, K=512
+    ops.gemm(x[:128 * 37], w1[:1024], bias=b1[:1024]);  torch.cuda.synchronize()   # same, specialised bias kernel
     ops.gemm(h[:128 * 37], w2[:256].repeat(4, 1)); torch.cuda.synchronize()   # 148 tiles, K=2048
     ops.gemm(x, w1, bias=b1); torch.cuda.synchronize()                         # ffn1 bias only
     ops.gemm(h, w1, trans_b=True); torch.cuda.synchronize()                    # ffn2 dgrad
