@@ -22,6 +22,59 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, 
   }
 }
 
+// y = bf16(alpha * dropout(x)) and colsum[n] += sum_m alpha * dropout(x)[m, n] in one pass over x (the backward of
+// "x + dropout(branch)" feeds both the dgrad/wgrad GEMMs (y) and the bias gradient of the branch's last Linear).
+__global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restrict__ x, bf16* __restrict__ y, int M, int N,
+                                                          float alpha, B2Dropout drop, float* __restrict__ out) {
+  __shared__ float red[8][32][8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int g = blockIdx.x * 32 + tx;  // column group of 8 (N % 8 == 0)
+  const bool ok = g * 8 < N;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (ok) {
+    B2DropKey dk = {0ull, 0u, 1.f};
+    if (drop.p > 0.f) dk = dropout_key(drop);
+    const long long step = (long long)gridDim.y * 8;
+    for (long long r0 = (long long)blockIdx.y * 8 + ty; r0 < M; r0 += 4 * step) {
+      float v[4][8];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // four independent rows in flight per thread
+        const long long r = r0 + u * step;
+        if (r < M) load8_f32(x + r * N + g * 8, v[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long r = r0 + u * step;
+        if (r < M) {
+          if (drop.p > 0.f) {
+            const uint32_t keep = dropout_keep8(dk, (unsigned long long)(r * N + g * 8) >> 3);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[u][j] = ((keep >> j) & 1u) ? v[u][j] * dk.inv : 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[u][j] *= alpha;
+            acc[j] += v[u][j];
+          }
+          store8_bf16(y + r * N + g * 8, v[u]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][tx][j] = acc[j];
+  __syncthreads();
+  if (ty == 0 && ok) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) s += red[k][tx][j];
+      atomicAdd(out + g * 8 + j, s);
+    }
+  }
+}
+
 // out[n] += sum_m dy[m, n]   (dy bf16, row stride ld)
 __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ dy, int M, int N, long long ld,
                                                      float* __restrict__ out) {
@@ -31,11 +84,20 @@ __global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ dy
   const bool ok = g * 8 < N;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (ok) {
-    for (long long r = (long long)blockIdx.y * 8 + ty; r < M; r += (long long)gridDim.y * 8) {
-      float v[8];
-      load8_bf16(dy + r * ld + g * 8, v);
+    const long long step = (long long)gridDim.y * 8;
+    for (long long r0 = (long long)blockIdx.y * 8 + ty; r0 < M; r0 += 4 * step) {
+      uint4 raw[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      for (int u = 0; u < 4; ++u) {  // four independent rows in flight per thread
+        const long long r = r0 + u * step;
+        raw[u] = r < M ? *reinterpret_cast<const uint4*>(dy + r * ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float2 a = unpack_bf16x2(raw[u].x), b = unpack_bf16x2(raw[u].y), c = unpack_bf16x2(raw[u].z),
+                     d = unpack_bf16x2(raw[u].w);
+        acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
+      }
     }
   }
 #pragma unroll
@@ -164,11 +226,26 @@ extern "C" int b200slu_cast_bf16(const float* x, void* y, long long n, float alp
   return 0;
 }
 
+extern "C" int b200slu_cast_colsum_bf16(const float* x, void* y, int M, int N, float alpha, float drop_p,
+                                        unsigned long long seed, unsigned int site, float* colsum_accum, void* stream) {
+  B2_CHECK_ARG(M > 0 && N > 0 && N % 8 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0,
+               "cast_colsum: N %% 8 == 0 and 16-byte aligned pointers (M=%d N=%d)", M, N);
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((N + 255) / 256, 1);
+  const int gy = (M + 31) / 32;
+  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  grid.y = gy < cap ? gy : cap;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * N);
+  cast_colsum_kernel<<<grid, 256, 0, st>>>(x, (bf16*)y, M, N, alpha, b2_make_drop(drop_p, seed, site), colsum_accum);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int b200slu_colsum_bf16(const void* dy, int M, int N, long long ld, float* out_accum, void* stream) {
   B2_CHECK_ARG(M > 0 && N > 0 && ld % 8 == 0 && ld >= ((N + 7) / 8) * 8, "colsum: bad shape M=%d N=%d ld=%lld", M, N, ld);
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((N + 255) / 256, 1);
-  int gy = (M + 63) / 64;
+  int gy = (M + 31) / 32;
   const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 2.0 * M * N);

@@ -179,11 +179,17 @@ def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g: bool 
 
 
 # ---- small helpers ----------------------------------------------------------------------------------------------
-def cast_bf16(x, alpha: float = 1.0, drop: Drop = None, out=None):
+def cast_bf16(x, alpha: float = 1.0, drop: Drop = None, out=None, colsum_out=None):
+    """bf16(alpha * dropout(x)); with ``colsum_out`` (f32 [N], accumulated) also the column sums of a 2-D x."""
     assert x.dtype == torch.float32 and x.is_contiguous()
     if out is None:
         out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
     p, seed, site = _drop(drop)
+    if colsum_out is not None:
+        M, N = x.shape
+        check(_lib.lib().b200slu_cast_colsum_bf16(ptr(x), ptr(out), M, N, alpha, p, seed, site, ptr(colsum_out), stream_ptr()),
+              "cast_colsum")
+        return out
     check(_lib.lib().b200slu_cast_bf16(ptr(x), ptr(out), x.numel(), alpha, p, seed, site, stream_ptr()), "cast_bf16")
     return out
 

@@ -125,8 +125,7 @@ def ffn_fwd(x, P, W, pre: str, norm: str, act: str, scale: float, p_drop: float,
 
 def ffn_bwd(dy, saved, P, W, G):
     x, ln, st, hpre, h, d1, d2, pre, norm, act, scale = saved
-    g = K.cast_bf16(dy, alpha=scale, drop=d2)
-    K.colsum(g, G[pre + ".w_2.bias"])
+    g = K.cast_bf16(dy, alpha=scale, drop=d2, colsum_out=G[pre + ".w_2.bias"])
     K.gemm(g, h, trans=True, out=G[pre + ".w_2.weight"], accumulate=True)
     dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad="mul")  # hpre = act' * dropout mask
     K.colsum(dh, G[pre + ".w_1.bias"])
@@ -163,8 +162,7 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
     d, H = cfg.d, cfg.heads
     a = p + ".self_attn"
     k, v = qkv[:, d:2 * d], qkv[:, 2 * d:]
-    g = K.cast_bf16(dy, alpha=1.0, drop=do)
-    K.colsum(g, G[a + ".linear_out.bias"])
+    g = K.cast_bf16(dy, alpha=1.0, drop=do, colsum_out=G[a + ".linear_out.bias"])
     K.gemm(g, c, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
@@ -209,8 +207,7 @@ def convmod_fwd(x, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: St
 def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int):
     x, ln, st, pw1, dw, mr, bs, do = saved
     cm = p + ".conv_module"
-    g = K.cast_bf16(dy, alpha=1.0, drop=do)
-    K.colsum(g, G[cm + ".pointwise_conv2.bias"])
+    g = K.cast_bf16(dy, alpha=1.0, drop=do, colsum_out=G[cm + ".pointwise_conv2.bias"])
     K.gemm(g, bs, trans=True, out=G[cm + ".pointwise_conv2.weight"], accumulate=True)
     dbs = K.gemm(g, W[cm + ".pointwise_conv2.weight"], trans_b=True)
     ddw = K.bn_swish_bwd(dbs, dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"], G[cm + ".norm.weight"],
@@ -287,8 +284,7 @@ def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder"):
         dx = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T)
         layers[n] = None  # free the block's activations as we go
     C_ = h1.shape[-1]
-    g = K.cast_bf16(dx, alpha=math.sqrt(cfg.d), drop=dpos)
-    K.colsum(g, G[e + ".out.0.bias"])
+    g = K.cast_bf16(dx, alpha=math.sqrt(cfg.d), drop=dpos, colsum_out=G[e + ".out.0.bias"])
     K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
     dh2 = K.gemm(g, W[e + ".out.0.weight"], trans_b=True, act_grad_input=h2v, act_grad="relu").view(-1, C_)
     K.colsum(dh2, G[e + ".conv.2.bias"])
@@ -351,8 +347,7 @@ def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, 
     a = p + ".src_attn"
     (q, kv), pr, pd, da, scale = ca
     k, v = kv[:, :d], kv[:, d:]
-    g = K.cast_bf16(dx2, alpha=1.0, drop=do2)
-    K.colsum(g, G[a + ".linear_out.bias"])
+    g = K.cast_bf16(dx2, alpha=1.0, drop=do2, colsum_out=G[a + ".linear_out.bias"])
     K.gemm(g, c2, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dkv = torch.empty_like(kv)
@@ -372,8 +367,7 @@ def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, 
     a = p + ".self_attn"
     (qkv,), pr, pd, da, scale = sa
     q, k, v = qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:]
-    g = K.cast_bf16(dx1, alpha=1.0, drop=do1)
-    K.colsum(g, G[a + ".linear_out.bias"])
+    g = K.cast_bf16(dx1, alpha=1.0, drop=do1, colsum_out=G[a + ".linear_out.bias"])
     K.gemm(g, c1, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)

@@ -132,6 +132,11 @@ int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float* x, const f
 /* y = bf16(alpha * dropout(x)) (weight casts; embedding.py:244 dropout on pos_emb) */
 int b200slu_cast_bf16(const float* x, void* y, long long n, float alpha, float drop_p, unsigned long long seed,
                       unsigned int site, void* stream);
+/* y = bf16(alpha * dropout(x)) for x f32 [M,N] (N % 8 == 0) and colsum_accum[n] += sum_m of the same values: the backward
+   of "x + dropout(branch(x))" (encoder_layer.py:118-175) produces the branch gradient and the bias gradient of the
+   branch's last Linear in one pass */
+int b200slu_cast_colsum_bf16(const float* x, void* y, int M, int N, float alpha, float drop_p, unsigned long long seed,
+                             unsigned int site, float* colsum_accum, void* stream);
 /* out[n] += sum_m dy[m,n]: bias gradients of every nn.Linear / Conv1d(k=1) */
 int b200slu_colsum_bf16(const void* dy, int M, int N, long long ld, float* out_accum, void* stream);
 /* q_u = q + pos_bias_u, q_v = q + pos_bias_v (attention.py:289-291); q = first d columns of rows of stride ldq */

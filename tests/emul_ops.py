@@ -145,9 +145,11 @@ def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g=False,
     return dx, (_r(dx * g_alpha) if want_g else None)
 
 
-def cast_bf16(x, alpha=1.0, drop=None, out=None):
+def cast_bf16(x, alpha=1.0, drop=None, out=None, colsum_out=None):
     _nodrop(drop)
     y = _r(x * alpha)
+    if colsum_out is not None:
+        colsum_out += (x * alpha).float().sum(0)
     if out is not None:
         out.copy_(y.to(out.dtype))
         return out

@@ -111,6 +111,17 @@ def test_cast_colsum_posbias_embed():
     acc2 = torch.zeros(20, device="cuda")
     K().colsum(dy.cuda()[:, :24], acc2, n=20)
     close(acc2, dy.float()[:, :20].sum(0), 1e-4, "colsum ragged")
+    # fused cast + column sums (branch gradient + bias gradient in one pass), with and without dropout
+    xg = rnd(1237, 520, seed=6)
+    accf = torch.full((520,), 2.0, device="cuda")
+    yg = K().cast_bf16(xg.cuda(), alpha=0.5, colsum_out=accf)
+    close(yg, xg * 0.5, 1e-2, "cast_colsum y")
+    close(accf, 2 + (xg * 0.5).sum(0), 1e-4, "cast_colsum sums")
+    accd = torch.zeros(520, device="cuda")
+    yd = K().cast_bf16(xg.cuda(), alpha=1.0, drop=(0.2, 77, 5), colsum_out=accd)
+    yd2 = K().cast_bf16(xg.cuda(), alpha=1.0, drop=(0.2, 77, 5))     # same hash stream as the plain cast
+    assert torch.equal(yd, yd2)
+    close(accd, yd.float().sum(0), 2e-2, "cast_colsum dropout sums")
     M, d = 333, 64
     qkv = rnd(M, 3 * d, seed=3).to(BF)
     u, v = rnd(d, seed=4), rnd(d, seed=5)
