@@ -1,0 +1,142 @@
+"""Data-parallel plumbing of the train step: one process per GPU, torch.distributed (NCCL over NVLink/NVSwitch).
+
+Mirrors what the reference does with DistributedDataParallel:
+  * each global mini-batch is dealt ``batch[rank::world_size]`` (espnet2/tasks/abs_task.py:1534-1542),
+  * each rank runs the full model on its shard; BatchNorm statistics stay per rank (convolution.py:45),
+  * the loss is the batch-weighted mean over ranks: the trainer multiplies each rank's loss by
+    ``B_rank * world / sum(B)`` before DDP's mean (espnet2/train/trainer.py:594-606),
+  * gradients are averaged with one bucketed all-reduce overlapped with the backward.
+
+The path has exactly one exchange step, the gradient all-reduce; no other collective touches the data path.  The
+gradients already sit in ONE flat fp32 buffer (params.ParamPack.gflat), so a bucket is a contiguous slice and needs no
+copy; buckets are issued on a side stream as soon as the backward has finished the parameters they cover, in the order
+the backward finishes them: decoder + CTC head first, then the encoder blocks last to first, then the subsampling
+front.  NCCL's NVLS / in-switch reduction is used when the fabric offers it; nothing here depends on link count.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_batch(batch: Sequence, rank: int, world: int):
+    """The reference's sharding of one mini-batch of utterance keys (abs_task.py:1534-1542): ``batch[rank::world]``."""
+    if len(batch) < world:
+        raise RuntimeError(f"The batch-size must be equal or more than world_size: {len(batch)} < {world}")  # :1528-1532
+    return batch[rank::world]
+
+
+def loss_weight(batch_size: int, device, group=None) -> float:
+    """``B_rank * world / sum_r B_r``: the factor that turns DDP's plain mean into the batch-weighted mean
+    (trainer.py:594-606).  One tiny all-reduce; 1.0 when every rank holds the same number of utterances."""
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return 1.0
+    t = torch.tensor([float(batch_size)], device=device)
+    dist.all_reduce(t, group=group)
+    return float(batch_size) * dist.get_world_size(group) / float(t.item())
+
+
+class GradReducer:
+    """Bucketed all-reduce of the flat gradient buffer, overlapped with the backward."""
+
+    def __init__(self, pack, world: Optional[int] = None, group=None, bucket_bytes: int = 64 << 20, overlap: bool = True):
+        self.pack, self.group = pack, group
+        self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
+        self.overlap = overlap
+        self.cuda = pack.gflat.is_cuda
+        self.comm = torch.cuda.Stream(device=pack.gflat.device) if (self.cuda and self.world > 1) else None
+        self.stages = self._plan(bucket_bytes)
+        self._issued = 0
+        self.handles = []
+
+    # -- bucket plan ---------------------------------------------------------------------------------------------------
+    def _plan(self, bucket_bytes: int) -> List[Tuple[str, int, int]]:
+        """[(stage, lo, hi)] slices of gflat in backward-completion order.  Stages: "heads" (decoder + ctc, final once
+        the decoder backward is done), "enc<n>" (final once encoder block n is done; small neighbours are merged up to
+        bucket_bytes and keyed by the LAST block of the merge to finish), "front" (embed + anything else, final after
+        ParamPack.finalize_grads)."""
+        pk = self.pack
+        end = {n: pk.offs[n] + (pk.shapes_numel(n) + 7) // 8 * 8 for n in pk.names}
+        spans: Dict[str, List[int]] = {}
+
+        def add(key, n):
+            lo, hi = pk.offs[n], end[n]
+            s = spans.setdefault(key, [lo, hi])
+            s[0], s[1] = min(s[0], lo), max(s[1], hi)
+
+        for n in pk.names:
+            if n.startswith("decoder.") or n.startswith("ctc."):
+                add("heads", n)
+            elif n.startswith("encoder.encoders."):
+                add("enc%d" % int(n.split(".")[2]), n)
+            else:
+                add("front", n)
+        out: List[Tuple[str, int, int]] = []
+        if "heads" in spans:
+            out.append(("heads", spans["heads"][0], spans["heads"][1]))
+        blocks = sorted((int(k[3:]) for k in spans if k.startswith("enc")), reverse=True)
+        cur = None
+        for b in blocks:  # merge neighbouring blocks (contiguous in gflat) until the bucket is large enough
+            lo, hi = spans["enc%d" % b]
+            if cur is None:
+                cur = [b, lo, hi]
+            elif lo == cur[2] or hi == cur[1]:
+                cur = [b, min(cur[1], lo), max(cur[2], hi)]
+            else:
+                out.append(("enc%d" % cur[0], cur[1], cur[2]))
+                cur = [b, lo, hi]
+            if (cur[2] - cur[1]) * 4 >= bucket_bytes:
+                out.append(("enc%d" % cur[0], cur[1], cur[2]))
+                cur = None
+        if cur is not None:
+            out.append(("enc%d" % cur[0], cur[1], cur[2]))
+        # whatever is left (front of the encoder, after_norm, gaps) goes last
+        covered = sorted((lo, hi) for _, lo, hi in out)
+        pos = 0
+        for lo, hi in covered + [(pk.total, pk.total)]:
+            if lo > pos:
+                out.append(("front", pos, lo))
+            pos = max(pos, hi)
+        return out
+
+    # -- per step ------------------------------------------------------------------------------------------------------
+    def begin(self):
+        self._issued = 0
+        self.handles = []
+
+    def ready(self, stage: str):
+        """Called by the step when ``stage`` ("heads", "enc<n>", "front") has its final gradients: issue, in plan order,
+        every bucket up to and including that stage."""
+        if self.world == 1:
+            return
+        if not self.overlap and stage != "front":
+            return
+        upto = max((i for i, (s, _, _) in enumerate(self.stages) if s == stage), default=-1)
+        if stage == "front":
+            upto = len(self.stages) - 1
+        if upto < self._issued:
+            return
+        if self.comm is not None:
+            self.comm.wait_stream(torch.cuda.current_stream())
+        for i in range(self._issued, upto + 1):
+            _, lo, hi = self.stages[i]
+            view = self.pack.gflat[lo:hi]
+            if self.comm is not None:
+                with torch.cuda.stream(self.comm):
+                    dist.all_reduce(view, group=self.group)
+            else:
+                self.handles.append(dist.all_reduce(view, group=self.group, async_op=True))
+        self._issued = upto + 1
+
+    def finish(self):
+        """All buckets reduced (SUM) and visible to the current stream; the caller divides by world in the optimizer."""
+        if self.world == 1:
+            return
+        self.ready("front")
+        if self.comm is not None:
+            torch.cuda.current_stream().wait_stream(self.comm)
+        for h in self.handles:
+            h.wait()
+        self.handles = []

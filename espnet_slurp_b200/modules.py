@@ -1,0 +1,644 @@
+"""Drop-in modules for the reference's plugin registry.
+
+Each class keeps the reference class's constructor keywords, forward signature, state_dict names / shapes / default
+initialisation and error behaviour, and runs on the B200 kernels of ``libb200slu.so``.  A maintainer registers them in
+``espnet2/tasks/asr.py``; the recipe YAMLs, checkpoints and ``--init_param`` keep working.
+
+    reference class (file:line)                                            replacement here
+    ConformerEncoder   espnet2/asr/encoder/conformer_encoder.py:39-368     ConformerEncoder
+    TransformerDecoder espnet2/asr/decoder/transformer_decoder.py:232-280  TransformerDecoder
+    CTC                espnet2/asr/ctc.py:9-127                            CTC
+    DefaultFrontend    espnet2/asr/frontend/default.py:18-131              DefaultFrontend
+    SpecAug            espnet2/asr/specaug/specaug.py:12-96                SpecAug
+    UtteranceMVN       espnet2/layers/utterance_mvn.py:9-88                UtteranceMVN
+    ESPnetASRModel     espnet2/asr/espnet_model.py:39-297                  ESPnetASRModel (whole step fused: one
+                                                                           forward+backward pass over the kernels)
+
+The torch sub-modules created in the constructors (nn.Linear, nn.Conv2d, nn.LayerNorm, ...) are parameter containers
+only: they give the reference's names, shapes, default init and BatchNorm buffers; their own ``forward`` is never
+called.  Options the kernels do not implement raise ``NotImplementedError`` in the constructor -- there is no CPU or
+eager fallback, and a module on a non-CUDA device raises at the first call.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence, Tuple, Union
+
+import torch
+import torch.nn as nn
+
+from . import melbank
+from . import step as S
+from .params import ParamPack
+
+
+class TooShortUttError(Exception):
+    """espnet/nets/pytorch_backend/transformer/subsampling.py:14-28 (same constructor and attributes)."""
+
+    def __init__(self, message, actual_size, limit):
+        super().__init__(message)
+        self.actual_size = actual_size
+        self.limit = limit
+
+
+def check_short_utt(ins, size):
+    """subsampling.py:31-46 for the layers this package implements (Conv2dSubsampling: kernel 3, stride 2, twice)."""
+    if isinstance(ins, Conv2dSubsampling) and size < 7:
+        return True, 7
+    return False, -1
+
+
+def _unsupported(cond: bool, what: str):
+    if cond:
+        raise NotImplementedError(f"espnet_slurp_b200: {what} is outside the B200 hot path (SURVEY.md 8a); "
+                                  "use the reference module for this configuration")
+
+
+def _need_cuda(t: torch.Tensor, who: str):
+    if t.device.type != "cuda":
+        raise RuntimeError(f"{who}: espnet_slurp_b200 modules run on a CUDA device (sm_100a) only; there is no CPU fallback")
+
+
+class _Packed(nn.Module):
+    """Shared plumbing: the module's parameters live in one flat fp32 buffer (+ bf16 copy + flat gradient buffer)."""
+
+    _prefix = ""
+
+    def _named(self) -> Dict[str, torch.Tensor]:
+        return {self._prefix + n: p for n, p in self.named_parameters()}
+
+    def _pack(self) -> ParamPack:
+        pp: Optional[ParamPack] = self.__dict__.get("_pp")
+        named = self._named()
+        first = next(iter(named.values()))
+        _need_cuda(first, type(self).__name__)
+        stale = pp is None or pp.device != first.device
+        if not stale:  # .to() / .cuda() / load of new Parameter objects re-creates storage: re-adopt
+            for n, p in named.items():
+                if p.data_ptr() != pp.P[n].data_ptr():
+                    stale = True
+                    break
+        if stale:
+            pp = ParamPack(named, device=first.device, adopt=True)
+            self.__dict__["_pp"] = pp
+        return pp
+
+    def _bn_buffers(self) -> Dict[str, torch.Tensor]:
+        return {self._prefix + n: b for n, b in self.named_buffers()}
+
+    def _ctx(self) -> S.StepCtx:
+        # one dropout seed per call, drawn from torch's generator so torch.manual_seed() makes runs reproducible
+        seed = int(torch.randint(0, 2 ** 31 - 1, (1,)).item()) if self.training else 0
+        return S.StepCtx(seed=seed, training=self.training)
+
+
+def _grads_out(pp: ParamPack, names: Sequence[str], scale) -> List[torch.Tensor]:
+    """Parameter gradients in the reference layout, as fresh tensors (autograd may keep them as .grad)."""
+    pp.finalize_grads()
+    return [pp.Gref[n] * scale for n in names]
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# frontend / specaug / normalize  (no parameters, no gradient: the waveform carries none)
+# ----------------------------------------------------------------------------------------------------------------------
+class DefaultFrontend(nn.Module):
+    """STFT (n_fft 512, hann, center, reflect pad) -> power -> Slaney mel -> log; default.py:82-131, stft.py:56-170,
+    log_mel.py:57-84.  Same constructor keywords as default.py:25-44."""
+
+    def __init__(self, fs: Union[int, str] = 16000, n_fft: int = 512, win_length: int = None, hop_length: int = 128,
+                 window: Optional[str] = "hann", center: bool = True, normalized: bool = False, onesided: bool = True,
+                 n_mels: int = 80, fmin: int = None, fmax: int = None, htk: bool = False, frontend_conf=None,
+                 apply_stft: bool = True):
+        super().__init__()
+        if isinstance(fs, str):
+            fs = int(float(fs.lower().replace("k", "")) * (1000 if "k" in fs.lower() else 1))
+        _unsupported(win_length not in (None, n_fft), "win_length != n_fft")
+        _unsupported(window != "hann" or not center or normalized or not onesided, "a non-default STFT window/centering")
+        _unsupported(htk, "HTK mel scale")
+        _unsupported(bool(frontend_conf), "WPE / beamforming frontend_conf")
+        _unsupported(not apply_stft, "apply_stft=False")
+        self.fs, self.n_fft, self.hop_length, self.n_mels = fs, n_fft, hop_length, n_mels
+        fmin = 0.0 if fmin is None else fmin
+        fmax = fs / 2 if fmax is None else fmax
+        self.register_buffer("melmat", melbank.mel_matrix(fs, n_fft, n_mels, float(fmin), float(fmax)).float(),
+                             persistent=False)
+
+    def output_size(self) -> int:
+        return self.n_mels
+
+    def forward(self, input: torch.Tensor, input_lengths: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        _need_cuda(input, "DefaultFrontend")
+        if self.melmat.device != input.device:
+            self.melmat = self.melmat.to(input.device)
+        feats, flens = S.K.logmel(input.float().contiguous(), input_lengths.to(device=input.device, dtype=torch.int32),
+                                  self.melmat, self.n_fft, self.hop_length)
+        return feats, flens.to(torch.long)
+
+
+def specaug_draws(flens: torch.Tensor, T_in: int, n_mels: int, W: Optional[int], F: Optional[Tuple[int, int]], n_f: int,
+                  Tm: Optional[Tuple[int, int]], n_t: int, gen=None) -> Dict[str, Optional[torch.Tensor]]:
+    """The random draws SpecAug makes, in the reference's order: time_warp.py:28-29 once per utterance, then
+    mask_along_axis.py:33-43 for the frequency masks and for the time masks (one (B, n) draw each, shared max width)."""
+    B = flens.numel()
+    out: Dict[str, Optional[torch.Tensor]] = {"center": None, "warped": None, "fmask": None, "tmask": None}
+    if W is not None:
+        center = torch.full((B,), -1, dtype=torch.int32)
+        warped = torch.zeros(B, dtype=torch.int32)
+        fl = flens.tolist()
+        for b in range(B):
+            t = int(fl[b])
+            if t - W > W:
+                c = int(torch.randint(W, t - W, (1,), generator=gen))
+                center[b] = c
+                warped[b] = int(torch.randint(c - W, c + W, (1,), generator=gen)) + 1
+        out["center"], out["warped"] = center, warped
+    if F is not None:
+        f_len = torch.randint(F[0], F[1], (B, n_f), generator=gen)
+        f_pos = torch.randint(0, max(1, n_mels - int(f_len.max())), (B, n_f), generator=gen)
+        out["fmask"] = torch.stack([f_pos, f_len], -1).int().contiguous()
+    if Tm is not None:
+        t_len = torch.randint(Tm[0], Tm[1], (B, n_t), generator=gen)
+        t_pos = torch.randint(0, max(1, T_in - int(t_len.max())), (B, n_t), generator=gen)
+        out["tmask"] = torch.stack([t_pos, t_len], -1).int().contiguous()
+    return out
+
+
+def _range(x) -> Optional[Tuple[int, int]]:
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return (0, x)
+    return (int(x[0]), int(x[1]))
+
+
+class SpecAug(nn.Module):
+    """Time warp (bicubic, window W) + frequency masks + time masks, specaug.py:89-96.  Same keywords as :27-45."""
+
+    def __init__(self, apply_time_warp: bool = True, time_warp_window: int = 5, time_warp_mode: str = "bicubic",
+                 apply_freq_mask: bool = True, freq_mask_width_range: Union[int, Sequence[int]] = (0, 20),
+                 num_freq_mask: int = 2, apply_time_mask: bool = True,
+                 time_mask_width_range: Optional[Union[int, Sequence[int]]] = None,
+                 time_mask_width_ratio_range: Optional[Union[float, Sequence[float]]] = None, num_time_mask: int = 2):
+        super().__init__()
+        if not apply_time_warp and not apply_time_mask and not apply_freq_mask:
+            raise ValueError("Either one of time_warp, time_mask, or freq_mask should be applied")
+        if apply_time_mask and time_mask_width_range is not None and time_mask_width_ratio_range is not None:
+            raise ValueError('Either one of "time_mask_width_range" or "time_mask_width_ratio_range" can be used')
+        _unsupported(apply_time_warp and time_warp_mode != "bicubic", "time_warp_mode != bicubic")
+        _unsupported(apply_time_mask and time_mask_width_range is None, "time_mask_width_ratio_range masks")
+        self.W = time_warp_window if apply_time_warp else None
+        self.F = _range(freq_mask_width_range) if apply_freq_mask else None
+        self.Tm = _range(time_mask_width_range) if apply_time_mask else None
+        self.n_f, self.n_t = num_freq_mask, num_time_mask
+
+    def forward(self, x: torch.Tensor, x_lengths: Optional[torch.Tensor] = None):
+        _need_cuda(x, "SpecAug")
+        B, T, Fd = x.shape
+        lens = x_lengths if x_lengths is not None else torch.full((B,), T, dtype=torch.long)
+        d = specaug_draws(lens.cpu(), T, Fd, self.W, self.F, self.n_f, self.Tm, self.n_t)
+        dev = {k: (v.to(x.device) if v is not None else None) for k, v in d.items()}
+        y = S.K.specaug_mvn(x.float().contiguous(), lens.to(device=x.device, dtype=torch.int32), dev["center"], dev["warped"],
+                            dev["fmask"], dev["tmask"], do_mvn=False)
+        return y, x_lengths
+
+
+class UtteranceMVN(nn.Module):
+    """Per-utterance mean normalisation over the valid frames, utterance_mvn.py:45-88 (norm_vars=False as in the recipes)."""
+
+    def __init__(self, norm_means: bool = True, norm_vars: bool = False, eps: float = 1.0e-20):
+        super().__init__()
+        _unsupported(norm_vars or not norm_means, "UtteranceMVN with norm_vars=True or norm_means=False")
+        self.norm_means, self.norm_vars, self.eps = norm_means, norm_vars, eps
+
+    def extra_repr(self):
+        return f"norm_means={self.norm_means}, norm_vars={self.norm_vars}"
+
+    def forward(self, x: torch.Tensor, ilens: Optional[torch.Tensor] = None):
+        _need_cuda(x, "UtteranceMVN")
+        B, T, _ = x.shape
+        lens = ilens if ilens is not None else torch.full((B,), T, dtype=torch.long)
+        y = S.K.specaug_mvn(x.float().contiguous(), lens.to(device=x.device, dtype=torch.int32), do_mvn=True)
+        return y, ilens
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# parameter containers with the reference's attribute names (=> identical state_dict keys, shapes and default init)
+# ----------------------------------------------------------------------------------------------------------------------
+class Conv2dSubsampling(nn.Module):
+    """subsampling.py:49-65: conv = [Conv2d(1,C,3,2), ReLU, Conv2d(C,C,3,2), ReLU]; out = [Linear(C*F2, C), pos_enc]."""
+
+    def __init__(self, idim: int, odim: int):
+        super().__init__()
+        self.conv = nn.Sequential(nn.Conv2d(1, odim, 3, 2), nn.ReLU(), nn.Conv2d(odim, odim, 3, 2), nn.ReLU())
+        self.out = nn.Sequential(nn.Linear(odim * (((idim - 1) // 2 - 1) // 2), odim), nn.Identity())
+
+
+class _RelPosAttnParams(nn.Module):
+    """attention.py:24-38 + 217-238 (linear_pos without bias, pos_bias_u / pos_bias_v xavier-uniform)."""
+
+    def __init__(self, n_head: int, n_feat: int):
+        super().__init__()
+        self.linear_q = nn.Linear(n_feat, n_feat)
+        self.linear_k = nn.Linear(n_feat, n_feat)
+        self.linear_v = nn.Linear(n_feat, n_feat)
+        self.linear_out = nn.Linear(n_feat, n_feat)
+        self.linear_pos = nn.Linear(n_feat, n_feat, bias=False)
+        self.pos_bias_u = nn.Parameter(torch.Tensor(n_head, n_feat // n_head))
+        self.pos_bias_v = nn.Parameter(torch.Tensor(n_head, n_feat // n_head))
+        nn.init.xavier_uniform_(self.pos_bias_u)
+        nn.init.xavier_uniform_(self.pos_bias_v)
+
+
+class _AttnParams(nn.Module):
+    def __init__(self, n_feat: int):
+        super().__init__()
+        self.linear_q = nn.Linear(n_feat, n_feat)
+        self.linear_k = nn.Linear(n_feat, n_feat)
+        self.linear_v = nn.Linear(n_feat, n_feat)
+        self.linear_out = nn.Linear(n_feat, n_feat)
+
+
+class _FFNParams(nn.Module):
+    def __init__(self, idim: int, hidden: int):
+        super().__init__()
+        self.w_1 = nn.Linear(idim, hidden)
+        self.w_2 = nn.Linear(hidden, idim)
+
+
+class _ConvModuleParams(nn.Module):
+    """convolution.py:22-54."""
+
+    def __init__(self, channels: int, kernel_size: int):
+        super().__init__()
+        assert (kernel_size - 1) % 2 == 0
+        self.pointwise_conv1 = nn.Conv1d(channels, 2 * channels, 1)
+        self.depthwise_conv = nn.Conv1d(channels, channels, kernel_size, padding=(kernel_size - 1) // 2, groups=channels)
+        self.norm = nn.BatchNorm1d(channels)
+        self.pointwise_conv2 = nn.Conv1d(channels, channels, 1)
+
+
+class _LayerNorm(nn.LayerNorm):
+    def __init__(self, n: int):
+        super().__init__(n, eps=1e-12)  # layer_norm.py:23
+
+
+class _EncoderLayerParams(nn.Module):
+    """conformer/encoder_layer.py:45-74 attribute names."""
+
+    def __init__(self, size: int, heads: int, ffn: int, kernel: int):
+        super().__init__()
+        self.self_attn = _RelPosAttnParams(heads, size)
+        self.feed_forward = _FFNParams(size, ffn)
+        self.feed_forward_macaron = _FFNParams(size, ffn)
+        self.conv_module = _ConvModuleParams(size, kernel)
+        self.norm_ff = _LayerNorm(size)
+        self.norm_mha = _LayerNorm(size)
+        self.norm_ff_macaron = _LayerNorm(size)
+        self.norm_conv = _LayerNorm(size)
+        self.norm_final = _LayerNorm(size)
+
+
+class _DecoderLayerParams(nn.Module):
+    """transformer/decoder_layer.py:40-61 attribute names."""
+
+    def __init__(self, size: int, ffn: int):
+        super().__init__()
+        self.self_attn = _AttnParams(size)
+        self.src_attn = _AttnParams(size)
+        self.feed_forward = _FFNParams(size, ffn)
+        self.norm1 = _LayerNorm(size)
+        self.norm2 = _LayerNorm(size)
+        self.norm3 = _LayerNorm(size)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# autograd glue: the kernels' hand-written backward behind torch.autograd.Function
+# ----------------------------------------------------------------------------------------------------------------------
+def _i32(t: torch.Tensor, device) -> torch.Tensor:
+    return t.to(device=device, dtype=torch.int32).contiguous()
+
+
+class _EncoderFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod: "ConformerEncoder", xs: torch.Tensor, ilens: torch.Tensor, *params):
+        pp = mod._pack()
+        pp.refresh()
+        B = xs.shape[0]
+        bn = mod._bn_buffers()
+        enc, _, olens, saved = S.encoder_fwd(xs.float().contiguous(), _i32(ilens, xs.device), pp.P, pp.W, mod._cfg, mod._ctx(),
+                                             p="encoder", bn_buffers=bn)
+        ctx.mod, ctx.saved = mod, saved
+        olens = olens.to(torch.long)
+        ctx.mark_non_differentiable(olens)
+        return enc.view(B, -1, mod._cfg.d), olens
+
+    @staticmethod
+    def backward(ctx, denc, _dolens):
+        mod = ctx.mod
+        pp = mod._pp
+        pp.zero_grad()
+        d = mod._cfg.d
+        S.encoder_bwd(denc.float().contiguous().view(-1, d), ctx.saved, pp.P, pp.W, pp.G, mod._cfg, p="encoder")
+        ctx.saved = None
+        return (None, None, None, *_grads_out(pp, mod._names, 1.0))
+
+
+class _DecoderFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod: "TransformerDecoder", hs: torch.Tensor, hlens, ys_in, ys_in_lens, *params):
+        pp = mod._pack()
+        pp.refresh()
+        B, T, d = hs.shape
+        mem16 = S.K.cast_bf16(hs.float().contiguous().view(B * T, d))
+        logits, saved = S.decoder_fwd(mem16, _i32(hlens, hs.device), _i32(ys_in, hs.device), _i32(ys_in_lens, hs.device), pp.P,
+                                      pp.W, mod._cfg, mod._ctx(), B, T, p="decoder")
+        ctx.mod, ctx.saved, ctx.mem16, ctx.dims = mod, saved, mem16, (B, T, d, ys_in.shape[1])
+        V = mod._cfg.vocab
+        return logits[:, :V].reshape(B, ys_in.shape[1], V)
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        mod = ctx.mod
+        pp = mod._pp
+        pp.zero_grad()
+        B, T, d, L = ctx.dims
+        V = mod._cfg.vocab
+        g16 = torch.zeros(B * L, S.K.round8(V), device=dlogits.device, dtype=torch.bfloat16)
+        g16[:, :V] = dlogits.reshape(B * L, V)
+        dmem = torch.zeros(B * T, d, device=dlogits.device, dtype=torch.float32)
+        S.decoder_bwd(g16, dmem, ctx.saved, ctx.mem16, pp.P, pp.W, pp.G, mod._cfg, B, T, p="decoder")
+        ctx.saved = ctx.mem16 = None
+        return (None, dmem.view(B, T, d), None, None, None, *_grads_out(pp, mod._names, 1.0))
+
+
+class _CTCFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod: "CTC", hs: torch.Tensor, hlens, ys_pad, ys_lens, *params):
+        pp = mod._pack()
+        pp.refresh()
+        pp.zero_grad()
+        B, T, d = hs.shape
+        enc16 = S.K.cast_bf16(hs.float().contiguous().view(B * T, d))
+        # the loss and its gradients (w.r.t. the encoder output and ctc_lo) come out of one pass over the lattice
+        loss, denc = S.ctc_head(enc16, _i32(hlens, hs.device), _i32(ys_pad, hs.device), _i32(ys_lens, hs.device), pp.P, pp.W,
+                                pp.G, mod._odim, B, T, 1.0, p="ctc", want_grad=True)
+        ctx.mod, ctx.denc, ctx.dims = mod, denc, (B, T, d)
+        ctx.gen = mod._gen = mod.__dict__.get("_gen", 0) + 1
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        mod = ctx.mod
+        if ctx.gen != mod._gen:
+            raise RuntimeError("CTC: a later forward() overwrote this call's gradient buffers; call backward() first")
+        B, T, d = ctx.dims
+        return (None, (ctx.denc * g).view(B, T, d), None, None, None, *_grads_out(mod._pp, mod._names, g))
+
+
+class _ModelFn(torch.autograd.Function):
+    """Whole train step (espnet_model.py:202-297 from the normalised features on): forward AND backward run inside
+    forward() -- the backward kernels consume activations while they are hot and free them block by block --
+    and autograd's backward() only scales the stored gradients by d(total)/d(loss)."""
+
+    @staticmethod
+    def forward(ctx, model: "ESPnetASRModel", want: bool, feats, flens, text, text_lens, *params):
+        # want: gradients requested (decided by the caller: grad mode is always off inside Function.forward)
+        pp = model._pack()
+        pp.refresh()
+        if want:
+            pp.zero_grad()
+        out = S.train_step_from_feats(feats, _i32(flens, feats.device), _i32(text, feats.device), _i32(text_lens, feats.device),
+                                      pp.P, pp.W, pp.G, model._cfg, model._ctx(), bn_buffers=model._bn_buffers(),
+                                      want_grad=want)
+        ctx.model = model
+        ctx.gen = model._gen = model.__dict__.get("_gen", 0) + 1
+        for k in ("loss_ctc", "loss_att", "acc"):
+            ctx.mark_non_differentiable(out[k])
+        return out["loss"].reshape(()), out["loss_ctc"].reshape(()), out["loss_att"].reshape(()), out["acc"].reshape(())
+
+    @staticmethod
+    def backward(ctx, g, *_):
+        model = ctx.model
+        if ctx.gen != model._gen:
+            raise RuntimeError("ESPnetASRModel: a later forward() overwrote this step's gradient buffers; call backward() "
+                               "before the next forward()")
+        return (None, None, None, None, None, None, *_grads_out(model._pp, model._names, g))
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# the plugin classes
+# ----------------------------------------------------------------------------------------------------------------------
+class ConformerEncoder(_Packed):
+    """conformer_encoder.py:39-368.  Implemented configuration: conv2d input layer, rel_pos / rel_selfattn
+    (latest and legacy), macaron FFN (linear, swish), conv module, pre-norm; the rest raises NotImplementedError."""
+
+    _prefix = "encoder."
+
+    def __init__(self, input_size: int, output_size: int = 256, attention_heads: int = 4, linear_units: int = 2048,
+                 num_blocks: int = 6, dropout_rate: float = 0.1, positional_dropout_rate: float = 0.1,
+                 attention_dropout_rate: float = 0.0, input_layer: str = "conv2d", normalize_before: bool = True,
+                 concat_after: bool = False, positionwise_layer_type: str = "linear", positionwise_conv_kernel_size: int = 3,
+                 macaron_style: bool = False, rel_pos_type: str = "legacy", pos_enc_layer_type: str = "rel_pos",
+                 selfattention_layer_type: str = "rel_selfattn", activation_type: str = "swish", use_cnn_module: bool = True,
+                 zero_triu: bool = False, cnn_module_kernel: int = 31, padding_idx: int = -1,
+                 interctc_layer_idx: List[int] = [], interctc_use_conditioning: bool = False,
+                 stochastic_depth_rate: Union[float, List[float]] = 0.0, layer_drop_rate: float = 0.0,
+                 max_pos_emb_len: int = 5000):
+        super().__init__()
+        self._output_size = output_size
+        if rel_pos_type == "legacy":  # conformer_encoder.py:116-120
+            if pos_enc_layer_type == "rel_pos":
+                pos_enc_layer_type = "legacy_rel_pos"
+            if selfattention_layer_type == "rel_selfattn":
+                selfattention_layer_type = "legacy_rel_selfattn"
+        elif rel_pos_type != "latest":
+            raise ValueError("unknown rel_pos_type: " + rel_pos_type)
+        _unsupported(input_layer != "conv2d", f"input_layer={input_layer!r}")
+        _unsupported(not normalize_before or concat_after, "post-norm / concat_after blocks")
+        _unsupported(positionwise_layer_type != "linear", f"positionwise_layer_type={positionwise_layer_type!r}")
+        _unsupported(not macaron_style or not use_cnn_module, "blocks without the macaron FFN or the conv module")
+        _unsupported(pos_enc_layer_type not in ("rel_pos", "legacy_rel_pos") or
+                     selfattention_layer_type not in ("rel_selfattn", "legacy_rel_selfattn"), "non-relative attention")
+        if (pos_enc_layer_type == "rel_pos") != (selfattention_layer_type == "rel_selfattn"):
+            raise ValueError("pos_enc_layer_type and selfattention_layer_type must both be legacy or both be latest")
+        _unsupported(activation_type != "swish", f"activation_type={activation_type!r}")
+        _unsupported(zero_triu, "zero_triu")
+        _unsupported(len(interctc_layer_idx) > 0 or interctc_use_conditioning, "intermediate CTC")
+        sd = stochastic_depth_rate
+        _unsupported((any(sd) if isinstance(sd, (list, tuple)) else sd != 0.0) or layer_drop_rate != 0.0,
+                     "stochastic depth / layer drop")
+        _unsupported(output_size % attention_heads != 0 or output_size % 8 != 0 or (output_size // attention_heads) % 8 != 0,
+                     "head sizes that are not multiples of 8")
+        self.embed = Conv2dSubsampling(input_size, output_size)
+        self.encoders = nn.ModuleList(_EncoderLayerParams(output_size, attention_heads, linear_units, cnn_module_kernel)
+                                      for _ in range(num_blocks))
+        self.after_norm = _LayerNorm(output_size)
+        self.interctc_layer_idx = interctc_layer_idx
+        self.interctc_use_conditioning = interctc_use_conditioning
+        self.conditioning_layer = None
+        self._cfg = S.EncCfg(input_size, output_size, attention_heads, linear_units, num_blocks, cnn_module_kernel,
+                             "latest" if pos_enc_layer_type == "rel_pos" else "legacy", dropout_rate, positional_dropout_rate,
+                             attention_dropout_rate)
+        self._names = [self._prefix + n for n, _ in self.named_parameters()]
+
+    def output_size(self) -> int:
+        return self._output_size
+
+    def forward(self, xs_pad: torch.Tensor, ilens: torch.Tensor, prev_states: torch.Tensor = None, ctc=None
+                ) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
+        _need_cuda(xs_pad, "ConformerEncoder")
+        short, limit = check_short_utt(self.embed, xs_pad.size(1))
+        if short:  # conformer_encoder.py:320-327
+            raise TooShortUttError(f"has {xs_pad.size(1)} frames and is too short for subsampling "
+                                   f"(it needs more than {limit} frames), return empty results", xs_pad.size(1), limit)
+        xs, olens = _EncoderFn.apply(self, xs_pad, ilens, *self.parameters())
+        return xs, olens, None
+
+
+class TransformerDecoder(_Packed):
+    """transformer_decoder.py:232-280 / 92-145 (training forward).  Implemented: embed input layer, output layer,
+    pre-norm blocks, sinusoidal PositionalEncoding."""
+
+    _prefix = "decoder."
+
+    def __init__(self, vocab_size: int, encoder_output_size: int, attention_heads: int = 4, linear_units: int = 2048,
+                 num_blocks: int = 6, dropout_rate: float = 0.1, positional_dropout_rate: float = 0.1,
+                 self_attention_dropout_rate: float = 0.0, src_attention_dropout_rate: float = 0.0, input_layer: str = "embed",
+                 use_output_layer: bool = True, pos_enc_class=None, normalize_before: bool = True, concat_after: bool = False,
+                 layer_drop_rate: float = 0.0):
+        super().__init__()
+        _unsupported(input_layer != "embed" or not use_output_layer, "a decoder without embed input / output layer")
+        _unsupported(pos_enc_class is not None and getattr(pos_enc_class, "__name__", "") != "PositionalEncoding",
+                     "a non-default pos_enc_class")
+        _unsupported(not normalize_before or concat_after or layer_drop_rate != 0.0, "post-norm / concat_after / layer drop")
+        d = encoder_output_size
+        self.embed = nn.Sequential(nn.Embedding(vocab_size, d), nn.Identity())
+        self.decoders = nn.ModuleList(_DecoderLayerParams(d, linear_units) for _ in range(num_blocks))
+        self.after_norm = _LayerNorm(d)
+        self.output_layer = nn.Linear(d, vocab_size)
+        self._cfg = S.DecCfg(vocab_size, d, attention_heads, linear_units, num_blocks, dropout_rate, positional_dropout_rate,
+                             self_attention_dropout_rate, src_attention_dropout_rate)
+        self._names = [self._prefix + n for n, _ in self.named_parameters()]
+
+    def forward(self, hs_pad: torch.Tensor, hlens: torch.Tensor, ys_in_pad: torch.Tensor, ys_in_lens: torch.Tensor
+                ) -> Tuple[torch.Tensor, torch.Tensor]:
+        _need_cuda(hs_pad, "TransformerDecoder")
+        x = _DecoderFn.apply(self, hs_pad, hlens, ys_in_pad, ys_in_lens, *self.parameters())
+        return x, ys_in_lens.to(hs_pad.device)
+
+
+class CTC(_Packed):
+    """ctc.py:9-127: ctc_lo projection + log_softmax + CTC loss (sum / batch, zero_infinity)."""
+
+    _prefix = "ctc."
+
+    def __init__(self, odim: int, encoder_output_size: int, dropout_rate: float = 0.0, ctc_type: str = "builtin",
+                 reduce: bool = True, ignore_nan_grad: bool = None, zero_infinity: bool = True):
+        super().__init__()
+        _unsupported(ctc_type != "builtin", f"ctc_type={ctc_type!r}")
+        _unsupported(not reduce, "reduce=False")
+        if ignore_nan_grad is not None:
+            zero_infinity = ignore_nan_grad
+        _unsupported(not zero_infinity, "zero_infinity=False")
+        _unsupported(dropout_rate != 0.0, "CTC dropout")
+        self.dropout_rate, self.ctc_type, self.reduce = dropout_rate, ctc_type, reduce
+        self.ctc_lo = nn.Linear(encoder_output_size, odim)
+        self._odim = odim
+        self._names = [self._prefix + n for n, _ in self.named_parameters()]
+
+    def forward(self, hs_pad, hlens, ys_pad, ys_lens):
+        _need_cuda(hs_pad, "CTC")
+        return _CTCFn.apply(self, hs_pad, hlens, ys_pad, ys_lens, *self.parameters())
+
+    def _logits(self, hs_pad):
+        pp = self._pack()
+        pp.refresh()
+        B, T, d = hs_pad.shape
+        V = self._odim
+        out = torch.empty(B * T, S.K.round8(V), device=hs_pad.device, dtype=torch.float32)
+        S.K.gemm(S.K.cast_bf16(hs_pad.float().contiguous().view(B * T, d)), pp.W["ctc.ctc_lo.weight"],
+                 bias=pp.P["ctc.ctc_lo.bias"], out=out)
+        return out[:, :V].reshape(B, T, V)
+
+    def softmax(self, hs_pad):
+        return torch.softmax(self._logits(hs_pad), dim=2)
+
+    def log_softmax(self, hs_pad):
+        return torch.log_softmax(self._logits(hs_pad), dim=2)
+
+    def argmax(self, hs_pad):
+        return torch.argmax(self._logits(hs_pad), dim=2)
+
+
+class ESPnetASRModel(_Packed):
+    """espnet_model.py:39-297, CTC/attention hybrid branch, with the whole forward+backward fused (``_ModelFn``)."""
+
+    _prefix = ""
+
+    def __init__(self, vocab_size: int, token_list: Union[Tuple[str, ...], List[str]], frontend, specaug, normalize,
+                 preencoder, encoder: ConformerEncoder, postencoder, decoder: TransformerDecoder, ctc: CTC, joint_network=None,
+                 ctc_weight: float = 0.5, interctc_weight: float = 0.0, ignore_id: int = -1, lsm_weight: float = 0.0,
+                 length_normalized_loss: bool = False, report_cer: bool = True, report_wer: bool = True,
+                 sym_space: str = "<space>", sym_blank: str = "<blank>", sym_sos: str = "<sos/eos>", sym_eos: str = "<sos/eos>",
+                 extract_feats_in_collect_stats: bool = True, lang_token_id: int = -1):
+        assert 0.0 <= ctc_weight <= 1.0, ctc_weight
+        assert 0.0 <= interctc_weight < 1.0, interctc_weight
+        super().__init__()
+        _unsupported(preencoder is not None or postencoder is not None or joint_network is not None,
+                     "pre/post-encoders and transducer joint networks")
+        _unsupported(ctc_weight in (0.0, 1.0), "pure attention (ctc_weight 0) or pure CTC (ctc_weight 1) training")
+        _unsupported(interctc_weight != 0.0 or length_normalized_loss or lang_token_id != -1,
+                     "interctc / length-normalised loss / language tokens")
+        _unsupported(not isinstance(encoder, ConformerEncoder) or not isinstance(decoder, TransformerDecoder) or
+                     not isinstance(ctc, CTC), "mixing reference encoder/decoder/ctc modules into the fused model")
+        token_list = list(token_list)
+        self.blank_id = token_list.index(sym_blank) if sym_blank in token_list else 0
+        _unsupported(self.blank_id != 0, "a blank symbol that is not token 0")
+        self.sos = token_list.index(sym_sos) if sym_sos in token_list else vocab_size - 1
+        self.eos = token_list.index(sym_eos) if sym_eos in token_list else vocab_size - 1
+        _unsupported(self.sos != vocab_size - 1 or self.eos != vocab_size - 1, "sos/eos other than the last token")
+        self.vocab_size, self.ignore_id, self.ctc_weight, self.interctc_weight = vocab_size, ignore_id, ctc_weight, 0.0
+        self.token_list = token_list
+        self.frontend, self.specaug, self.normalize = frontend, specaug, normalize
+        self.preencoder = self.postencoder = None
+        self.encoder, self.decoder, self.ctc = encoder, decoder, ctc
+        self.extract_feats_in_collect_stats = extract_feats_in_collect_stats
+        self._cfg = S.ModelCfg(enc=encoder._cfg, dec=decoder._cfg, vocab=vocab_size, ctc_weight=ctc_weight, lsm_weight=lsm_weight)
+        self._names = [n for n, _ in self.named_parameters()]
+
+    # espnet_model.py:379-396
+    def _extract_feats(self, speech, speech_lengths):
+        assert speech_lengths.dim() == 1, speech_lengths.shape
+        speech = speech[:, : speech_lengths.max()]
+        if self.frontend is not None:
+            return self.frontend(speech, speech_lengths)
+        return speech, speech_lengths
+
+    def collect_feats(self, speech, speech_lengths, text, text_lengths, **kwargs) -> Dict[str, torch.Tensor]:
+        feats, feats_lengths = self._extract_feats(speech, speech_lengths)
+        return {"feats": feats, "feats_lengths": feats_lengths}
+
+    def forward(self, speech: torch.Tensor, speech_lengths: torch.Tensor, text: torch.Tensor, text_lengths: torch.Tensor,
+                **kwargs) -> Tuple[torch.Tensor, Dict[str, torch.Tensor], torch.Tensor]:
+        assert text_lengths.dim() == 1, text_lengths.shape
+        assert speech.shape[0] == speech_lengths.shape[0] == text.shape[0] == text_lengths.shape[0], \
+            (speech.shape, speech_lengths.shape, text.shape, text_lengths.shape)  # espnet_model.py:186-193
+        _need_cuda(speech, "ESPnetASRModel")
+        batch_size = speech.shape[0]
+        text = text[:, : text_lengths.max()]
+        feats, flens = self._extract_feats(speech, speech_lengths)
+        if self.specaug is not None and self.training:
+            feats, flens = self.specaug(feats, flens)
+        if self.normalize is not None:
+            feats, flens = self.normalize(feats, flens)
+        short, limit = check_short_utt(self.encoder.embed, feats.size(1))
+        if short:
+            raise TooShortUttError(f"has {feats.size(1)} frames and is too short for subsampling "
+                                   f"(it needs more than {limit} frames), return empty results", feats.size(1), limit)
+        want = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        loss, loss_ctc, loss_att, acc = _ModelFn.apply(self, want, feats.float().contiguous(), flens, text, text_lengths,
+                                                       *self.parameters())
+        stats = dict(loss_ctc=loss_ctc.detach()[None], cer_ctc=None, loss_att=loss_att.detach()[None], acc=acc.detach()[None],
+                     cer=None, wer=None, loss=loss.detach()[None])
+        weight = torch.tensor([batch_size], dtype=torch.long, device=loss.device)
+        return loss[None], stats, weight

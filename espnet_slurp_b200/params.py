@@ -139,5 +139,11 @@ class ParamPack:
                 _, d_, C_, F2 = sp
                 self.Gref[n].view(d_, C_, F2).copy_(self.G[n].view(d_, F2, C_).permute(0, 2, 1))
 
+    def shapes_numel(self, n: str) -> int:
+        num = 1
+        for s in self.shapes[n]:
+            num *= s
+        return num
+
     def grads(self) -> Dict[str, torch.Tensor]:
         return self.Gref

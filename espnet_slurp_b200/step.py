@@ -196,7 +196,12 @@ def convmod_fwd(x, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: St
     if bn_buffers is not None and ctx.training:
         rm, rv, nb = bn_buffers[cm + ".norm.running_mean"], bn_buffers[cm + ".norm.running_var"], \
             bn_buffers[cm + ".norm.num_batches_tracked"]
-    mr = K.bn_finalize(sums, B * T, 1e-5, 0.1, rm, rv, nb)
+    if not ctx.training and bn_buffers is not None:
+        # eval mode: running statistics (convolution.py:45 BatchNorm1d in eval)
+        mr = torch.cat([bn_buffers[cm + ".norm.running_mean"].float(),
+                        torch.rsqrt(bn_buffers[cm + ".norm.running_var"].float() + 1e-5)]).contiguous()
+    else:
+        mr = K.bn_finalize(sums, B * T, 1e-5, 0.1, rm, rv, nb)
     bs = K.bn_swish_fwd(dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"])
     do = ctx.drop(cfg.dropout)
     y = K.gemm(bs, W[cm + ".pointwise_conv2.weight"], bias=P[cm + ".pointwise_conv2.bias"], residual=x, drop=do,
@@ -275,14 +280,17 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, B, T)
 
 
-def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder"):
-    """denc f32 [B*T, d]: gradient w.r.t. the encoder output.  Accumulates every encoder parameter gradient into G."""
+def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=None):
+    """denc f32 [B*T, d]: gradient w.r.t. the encoder output.  Accumulates every encoder parameter gradient into G.
+    on_ready("enc<n>") is called when block n's parameter gradients are final (data-parallel bucket hook)."""
     feats, h1, h2v, dpos, pos16, layers, xl, st, B, T = saved
     e = p + ".embed"
     dx, _ = K.layernorm_bwd(denc, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
     for n in reversed(range(cfg.blocks)):
         dx = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T)
         layers[n] = None  # free the block's activations as we go
+        if on_ready is not None:
+            on_ready("enc%d" % n)
     C_ = h1.shape[-1]
     g = K.cast_bf16(dx, alpha=math.sqrt(cfg.d), drop=dpos, colsum_out=G[e + ".out.0.bias"])
     K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
@@ -473,7 +481,7 @@ def add_sos_eos(text, text_lens, sos: int, eos: int, ignore: int = -1):
 
 
 def train_step_from_feats(feats, flens, text, text_lens, P, W, G, cfg: ModelCfg, ctx: StepCtx, bn_buffers=None,
-                          grad_scale: float = 1.0, after_enc_bwd_hook=None):
+                          grad_scale: float = 1.0, on_ready=None, want_grad: bool = True):
     """feats f32 [B,T_in,idim] (already normalised), flens int32 [B], text int32 [B,Lmax], text_lens int32 [B] -- all on the
     device.  Runs forward and backward; parameter gradients (times grad_scale) are ACCUMULATED into G.
     Returns dict(loss, loss_ctc, loss_att, acc) of 1-element device tensors (no synchronisation)."""
@@ -484,14 +492,17 @@ def train_step_from_feats(feats, flens, text, text_lens, P, W, G, cfg: ModelCfg,
     wc, wa = cfg.ctc_weight * grad_scale, (1.0 - cfg.ctc_weight) * grad_scale
     text = text.to(torch.int32)
     tl = text_lens.to(torch.int32)
-    loss_ctc, denc = ctc_head(enc16, olens, text.contiguous(), tl, P, W, G, V, B, T, wc)
+    loss_ctc, denc = ctc_head(enc16, olens, text.contiguous(), tl, P, W, G, V, B, T, wc, want_grad=want_grad)
     ys_in, ys_out = add_sos_eos(text, tl, V - 1, V - 1)
     ylens = (tl + 1).to(torch.int32)
     logits, s_dec = decoder_fwd(enc16, olens, ys_in, ylens, P, W, cfg.dec, ctx, B, T)
     loss_att, acc, dlogits = att_head(logits, ys_out, V, B, cfg.lsm_weight, wa)
-    decoder_bwd(dlogits, denc, s_dec, enc16, P, W, G, cfg.dec, B, T)
-    del s_dec
-    encoder_bwd(denc, s_enc, P, W, G, cfg.enc)
+    if want_grad:
+        decoder_bwd(dlogits, denc, s_dec, enc16, P, W, G, cfg.dec, B, T)
+        del s_dec
+        if on_ready is not None:
+            on_ready("heads")  # decoder + CTC head gradients are final
+        encoder_bwd(denc, s_enc, P, W, G, cfg.enc, on_ready=on_ready)
     loss = cfg.ctc_weight * loss_ctc + (1.0 - cfg.ctc_weight) * loss_att
     return {"loss": loss, "loss_ctc": loss_ctc, "loss_att": loss_att, "acc": acc}
 

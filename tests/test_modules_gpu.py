@@ -1,0 +1,201 @@
+"""Drop-in modules (espnet_slurp_b200.modules) on the GPU: same fixtures as the reference's own module tests
+(test/espnet2/asr/encoder/test_conformer_encoder.py:40-63, test/espnet2/asr/decoder/test_transformer_decoder.py:34-50,
+test/espnet2/asr/test_ctc.py:7-14, test/espnet2/asr/test_espnet_model.py:13-38), checked against the CPU oracle with
+the bf16 tolerances stated in tests/test_step_gpu.py."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model as om
+from test_step_gpu import grad_report, make_sd
+
+pytestmark = pytest.mark.gpu
+
+
+def M():
+    import espnet_slurp_b200.modules as m
+    return m
+
+
+def _load(module, sd, prefix):
+    own = module.state_dict()
+    new = {k: (sd[prefix + k] if prefix + k in sd else v) for k, v in own.items()}
+    module.load_state_dict(new)
+
+
+def _grads(module, prefix):
+    return {prefix + n: (p.grad if p.grad is not None else torch.zeros_like(p)) for n, p in module.named_parameters()}
+
+
+def _batch(B=3, Tin=150, V=50, seed=5):
+    g = torch.Generator().manual_seed(seed)
+    feats = torch.randn(B, Tin, 80, generator=g)
+    flens = torch.tensor([Tin, Tin - 19, Tin - 60][:B])
+    for b in range(B):
+        feats[b, flens[b]:] = 0.3
+    tl = torch.tensor([9, 4, 6][:B])
+    text = torch.full((B, 9), -1, dtype=torch.long)
+    for b in range(B):
+        text[b, : tl[b]] = torch.randint(1, V - 1, (int(tl[b]),), generator=g)
+    return feats, flens, text, tl
+
+
+@pytest.mark.parametrize("rel", ["latest", "legacy"])
+def test_conformer_encoder_forward_backward(rel):
+    m = M()
+    d, H, F, K, nb = 256, 4, 512, 15, 2
+    enc = m.ConformerEncoder(80, output_size=d, attention_heads=H, linear_units=F, num_blocks=nb, dropout_rate=0.0,
+                             positional_dropout_rate=0.0, attention_dropout_rate=0.0, macaron_style=True, rel_pos_type=rel,
+                             cnn_module_kernel=K).cuda()
+    ocfg = om.EncCfg(80, d, H, F, nb, K, rel)
+    sd = make_sd(ocfg, om.DecCfg(20, d, H, F, 0), 20, seed=1)
+    _load(enc, sd, "encoder.")
+    feats, flens, _, _ = _batch()
+    x = feats.cuda()
+    y, olens, _none = enc(x, flens.cuda())
+    assert _none is None and y.shape == (3, 36, d) and olens.dtype == torch.long
+    w = torch.randn(y.shape, generator=torch.Generator().manual_seed(2))
+    (y * w.cuda()).sum().backward()
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items() if k.startswith("encoder.")}
+    oy, oolens = om.conformer_encoder(feats, flens, osd, ocfg)
+    (oy * w).sum().backward()
+    assert oolens.tolist() == olens.tolist()
+    err = (y.detach().cpu() - oy.detach()).abs().max().item() / oy.abs().max().item()
+    assert err < 0.03, err
+    want = {k: (v.grad.numpy() if v.grad is not None else np.zeros(v.shape, np.float32)) for k, v in osd.items()}
+    rows = grad_report(_grads(enc, "encoder."), want)
+    assert rows[0][0] < 0.08, rows[:6]
+    # BatchNorm running statistics moved (train mode) and eval mode runs on them
+    assert float(enc.encoders[0].conv_module.norm.num_batches_tracked) == 1
+    enc.eval()
+    with torch.no_grad():
+        ye, _, _ = enc(x, flens.cuda())
+    assert torch.isfinite(ye).all()
+
+
+def test_encoder_too_short_and_unsupported():
+    m = M()
+    enc = m.ConformerEncoder(80, 64, 4, 128, 1, macaron_style=True, rel_pos_type="latest").cuda()
+    with pytest.raises(m.TooShortUttError) as e:
+        enc(torch.randn(2, 6, 80).cuda(), torch.tensor([6, 5]).cuda())
+    assert e.value.actual_size == 6 and e.value.limit == 7
+
+
+def test_transformer_decoder_forward_backward():
+    m = M()
+    d, H, F, V, nb = 256, 4, 512, 50, 2
+    dec = m.TransformerDecoder(V, d, attention_heads=H, linear_units=F, num_blocks=nb, dropout_rate=0.0,
+                               positional_dropout_rate=0.0).cuda()
+    ocfg = om.DecCfg(V, d, H, F, nb)
+    sd = make_sd(om.EncCfg(80, d, H, F, 0, 15, "latest"), ocfg, V, seed=4)
+    _load(dec, sd, "decoder.")
+    g = torch.Generator().manual_seed(9)
+    B, T, L = 3, 40, 10
+    mem = torch.randn(B, T, d, generator=g)
+    mlens = torch.tensor([40, 33, 20])
+    ys = torch.randint(1, V - 1, (B, L), generator=g)
+    ylens = torch.tensor([10, 7, 5])
+    memc = mem.cuda().requires_grad_(True)
+    out, olens = dec(memc, mlens.cuda(), ys.cuda(), ylens.cuda())
+    assert out.shape == (B, L, V) and olens.tolist() == ylens.tolist()
+    w = torch.randn(B, L, V, generator=g) * (torch.arange(L)[None, :, None] < ylens[:, None, None])
+    (out * w.cuda()).sum().backward()
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items() if k.startswith("decoder.")}
+    omem = mem.clone().requires_grad_(True)
+    oout = om.transformer_decoder(omem, mlens, ys, ylens, osd, ocfg)
+    oout = oout[0] if isinstance(oout, tuple) else oout
+    (oout * w).sum().backward()
+    valid = (torch.arange(L)[None, :] < ylens[:, None])
+    err = ((out.detach().cpu() - oout.detach()).abs() * valid[..., None]).max().item() / oout.abs().max().item()
+    assert err < 0.03, err
+    want = {k: (v.grad.numpy() if v.grad is not None else np.zeros(v.shape, np.float32)) for k, v in osd.items()}
+    rows = grad_report(_grads(dec, "decoder."), want)
+    assert rows[0][0] < 0.08, rows[:6]
+    mvalid = (torch.arange(T)[None, :] < mlens[:, None])[..., None]
+    gm, go = memc.grad.cpu() * mvalid, omem.grad * mvalid
+    assert ((gm - go).norm() / go.norm()).item() < 0.05
+
+
+@pytest.mark.parametrize("hl,yl", [([11, 17, 15], [4, 2, 3]), ([4], [1])])  # test/test_loss.py:12-48 length sets, V=7
+def test_ctc_module(hl, yl):
+    m = M()
+    V, d, B, T = 7, 64, len(hl), max(hl)
+    ctc = m.CTC(V, d).cuda()
+    g = torch.Generator().manual_seed(3)
+    hs = torch.randn(B, T, d, generator=g)
+    ys = torch.full((B, max(yl)), -1, dtype=torch.long)
+    for b in range(B):
+        ys[b, : yl[b]] = torch.randint(1, V, (yl[b],), generator=g)
+    hsc = hs.cuda().requires_grad_(True)
+    loss = ctc(hsc, torch.tensor(hl).cuda(), ys.cuda(), torch.tensor(yl).cuda())
+    (loss * 2.0).backward()
+    W = ctc.ctc_lo.weight.detach().cpu().bfloat16().float().requires_grad_(True)
+    bvec = ctc.ctc_lo.bias.detach().cpu().requires_grad_(True)
+    hso = hs.bfloat16().float().requires_grad_(True)
+    lp = torch.log_softmax(hso @ W.t() + bvec, -1).transpose(0, 1)
+    tgt = torch.cat([ys[b, : yl[b]] for b in range(B)])
+    ref = torch.nn.functional.ctc_loss(lp, tgt, torch.tensor(hl), torch.tensor(yl), reduction="sum", zero_infinity=True) / B
+    (ref * 2.0).backward()
+    np.testing.assert_allclose(loss.item(), ref.item(), rtol=2e-3)
+    assert ((hsc.grad.cpu() - hso.grad).norm() / hso.grad.norm()).item() < 0.02
+    assert ((ctc.ctc_lo.weight.grad.cpu() - W.grad).norm() / W.grad.norm()).item() < 0.02
+    assert ((ctc.ctc_lo.bias.grad.cpu() - bvec.grad).norm() / bvec.grad.norm()).item() < 0.02
+    assert ctc.argmax(hs.cuda()).shape == (B, T) and ctc.log_softmax(hs.cuda()).shape == (B, T, V)
+
+
+def test_espnet_asr_model_from_waveform():
+    m = M()
+    d, H, F, K, V = 256, 4, 512, 15, 50
+    enc = m.ConformerEncoder(80, d, H, F, 2, 0.0, 0.0, 0.0, macaron_style=True, rel_pos_type="latest", cnn_module_kernel=K)
+    dec = m.TransformerDecoder(V, d, H, F, 1, 0.0, 0.0)
+    ctc = m.CTC(V, d)
+    tokens = ["<blank>", "<unk>"] + [f"t{i}" for i in range(V - 3)] + ["<sos/eos>"]
+    model = m.ESPnetASRModel(V, tokens, m.DefaultFrontend(), None, m.UtteranceMVN(), None, enc, None, dec, ctc, None,
+                             ctc_weight=0.3, lsm_weight=0.1).cuda()
+    ocfg = om.ModelCfg(enc=om.EncCfg(80, d, H, F, 2, K, "latest"), dec=om.DecCfg(V, d, H, F, 1), vocab=V)
+    sd = make_sd(ocfg.enc, ocfg.dec, V, seed=7)
+    _load(model, sd, "")
+    g = torch.Generator().manual_seed(11)
+    B = 3
+    lens = torch.tensor([16000, 14000, 9000])
+    wav = torch.randn(B, 16000, generator=g) * 0.1
+    for b in range(B):
+        wav[b, lens[b]:] = 0
+    _, _, text, tl = _batch(V=V)
+    loss, stats, weight = model(wav.cuda(), lens.cuda(), text.cuda(), tl.cuda())
+    assert loss.shape == (1,) and weight.tolist() == [B] and set(stats) >= {"loss", "loss_att", "loss_ctc", "acc", "cer", "wer"}
+    (loss * 3.0).backward()
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    mel = torch.from_numpy(om.slaney_mel_matrix()) if isinstance(om.slaney_mel_matrix(), np.ndarray) else om.slaney_mel_matrix()
+    oloss, ostats = om.asr_forward(wav, lens, text, tl, osd, ocfg, mel)
+    (oloss * 3.0).backward()
+    np.testing.assert_allclose(stats["loss_ctc"].item(), ostats["loss_ctc"].item(), rtol=2e-2)
+    np.testing.assert_allclose(stats["loss_att"].item(), ostats["loss_att"].item(), rtol=2e-2)
+    np.testing.assert_allclose(loss.item(), oloss.item(), rtol=2e-2)
+    want = {k: (v.grad.numpy() if v.grad is not None else np.zeros(v.shape, np.float32)) for k, v in osd.items()}
+    rows = grad_report(_grads(model, ""), want)
+    assert rows[0][0] < 0.08, rows[:6]
+    # a stale backward is an error, not a silent wrong gradient
+    l1, _, _ = model(wav.cuda(), lens.cuda(), text.cuda(), tl.cuda())
+    l2, _, _ = model(wav.cuda(), lens.cuda(), text.cuda(), tl.cuda())
+    with pytest.raises(RuntimeError):
+        l1.sum().backward()
+    # eval / no_grad forward
+    model.eval()
+    with torch.no_grad():
+        le, se, _ = model(wav.cuda(), lens.cuda(), text.cuda(), tl.cuda())
+    assert torch.isfinite(le).all()
+
+
+def test_specaug_and_mvn_modules():
+    m = M()
+    torch.manual_seed(0)
+    sa = m.SpecAug(time_warp_window=5, freq_mask_width_range=(0, 30), time_mask_width_range=(0, 40))
+    x = torch.randn(4, 300, 80).cuda()
+    lens = torch.tensor([300, 280, 200, 120]).cuda()
+    y, yl = sa(x, lens)
+    assert y.shape == x.shape and yl is lens
+    assert (y == 0).float().mean().item() > 0.01          # masks landed
+    z, _ = m.UtteranceMVN()(x, lens)
+    for b in range(4):
+        assert z[b, : int(lens[b])].mean(0).abs().max().item() < 1e-4
