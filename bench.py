@@ -35,7 +35,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="utterances per GPU per step")
+    ap.add_argument("--batch", type=int, default=128, help="utterances per GPU per step (SURVEY 8d sweep: 8, 32, 128)")
     ap.add_argument("--vocab", type=int, default=600)
     ap.add_argument("--rel-pos", default="latest", choices=["latest", "legacy"])
     ap.add_argument("--min-sec", type=float, default=3.0)

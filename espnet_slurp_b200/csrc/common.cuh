@@ -221,6 +221,35 @@ __device__ __forceinline__ float block_sum(float v, float* red /* >= 32 floats o
   __syncthreads();
   return red[0];
 }
+// ---------------------------------------------------------------------------
+// Programmatic dependent launch: a train step is ~1150 short kernels in one stream, so the launch-to-launch gap is a
+// real share of the step.  Every kernel launched through b2_launch() (a) lets its successor start launching as soon as
+// all of its own CTAs are running (griddepcontrol.launch_dependents at the top) and (b) does its local set-up, then
+// blocks in griddepcontrol.wait until its predecessor has completed and flushed -- before its first global access.
+// Ordering and memory visibility along the stream are unchanged; only launch latency and prologues overlap.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void b2_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void b2_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void b2_pdl_entry() {
+  b2_pdl_launch_dependents();
+  b2_pdl_wait();
+}
+bool b2_pdl_enabled();  // runtime.cu: B200SLU_PDL=0 turns the launch attribute off (the device-side instructions are no-ops then)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t b2_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = b2_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 static inline int b2_grid_for(long long work_items, int threads, int per_sm = 8) {
   long long blocks = (work_items + threads - 1) / threads;
   long long cap = (long long)b2_num_sms() * per_sm;

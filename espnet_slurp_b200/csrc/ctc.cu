@@ -25,16 +25,28 @@
 namespace {
 
 constexpr float NEG_INF = -INFINITY;
-
-__device__ __forceinline__ float lse2(float a, float b) {
-  const float m = fmaxf(a, b);
-  if (m == NEG_INF) return NEG_INF;
-  return m + logf(expf(a - m) + expf(b - m));
+// The lattice runs in the log2 domain with ex2.approx / lg2.approx (one MUFU op each, rel. error 2^-22) and a FINITE
+// stand-in for log(0): with -1e30 the 3-way logsumexp needs no special case (exp2 of the differences is 1 or 0, the
+// result stays ~-1e30), and an all-impossible row shows up as a total log-likelihood below -1e29.
+constexpr float NEG_BIG = -1.0e30f;
+constexpr float LOG2E = 1.4426950408889634f, LN2 = 0.6931471805599453f;
+__device__ __forceinline__ float ex2_(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
-__device__ __forceinline__ float lse3(float a, float b, float c) {
+__device__ __forceinline__ float lg2_(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lse2(float a, float b) {  // log2 domain
+  const float m = fmaxf(a, b);
+  return m + lg2_(ex2_(a - m) + ex2_(b - m));
+}
+__device__ __forceinline__ float lse3(float a, float b, float c) {  // log2 domain
   const float m = fmaxf(a, fmaxf(b, c));
-  if (m == NEG_INF) return NEG_INF;
-  return m + logf(expf(a - m) + expf(b - m) + expf(c - m));
+  return m + lg2_(ex2_(a - m) + ex2_(b - m) + ex2_(c - m));
 }
 
 __device__ __forceinline__ int ext_label(const int* __restrict__ lab, int s, int blank) { return (s & 1) ? lab[s >> 1] : blank; }
@@ -48,26 +60,62 @@ __global__ void __launch_bounds__(256) ctc_prep_kernel(const float* __restrict__
   const int t = blockIdx.x, b = blockIdx.y;
   if (t >= hlens[b]) return;
   const float* row = logits + ((long long)b * T + t) * ldv;
-  float mx = NEG_INF;
-  for (int v = threadIdx.x; v < V; v += blockDim.x) mx = fmaxf(mx, row[v]);
-  mx = warp_max(mx);
+  // ONE pass over the row: per-thread running (max, sum of 2^((x - max) log2 e)), merged across the block afterwards
+  float m = NEG_BIG, sm = 0.f;
+  if (ldv % 4 == 0 && ((uintptr_t)logits % 16) == 0) {
+    for (int v = threadIdx.x * 4; v < V; v += blockDim.x * 4) {
+      float x[4];
+      if (v + 4 <= V) {
+        const float4 q = *reinterpret_cast<const float4*>(row + v);
+        x[0] = q.x; x[1] = q.y; x[2] = q.z; x[3] = q.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x[j] = v + j < V ? row[v + j] : NEG_BIG;
+      }
+      const float lm = fmaxf(fmaxf(x[0], x[1]), fmaxf(x[2], x[3]));
+      if (lm > m) {
+        sm *= ex2_((m - lm) * LOG2E);
+        m = lm;
+      }
+      const float mb = m * LOG2E;
+      sm += ex2_(fmaf(x[0], LOG2E, -mb)) + ex2_(fmaf(x[1], LOG2E, -mb)) + ex2_(fmaf(x[2], LOG2E, -mb)) + ex2_(fmaf(x[3], LOG2E, -mb));
+    }
+  } else {
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+      const float x = row[v];
+      if (x > m) {
+        sm *= ex2_((m - x) * LOG2E);
+        m = x;
+      }
+      sm += ex2_((x - m) * LOG2E);
+    }
+  }
+  float mx = warp_max(m);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
   __syncthreads();
   mx = red[0];
   for (int w = 1; w < (blockDim.x >> 5); ++w) mx = fmaxf(mx, red[w]);
-  float sum = 0.f;
-  for (int v = threadIdx.x; v < V; v += blockDim.x) sum += expf(row[v] - mx);
+  float sum = sm * ex2_((m - mx) * LOG2E);  // threads that saw no element hold (NEG_BIG, 0) -> 0
   sum = block_sum(sum, red);
   const float lse = mx + logf(sum);
   if (threadIdx.x == 0) lse_out[(long long)b * T + t] = lse;
   const int S = 2 * llens[b] + 1;
   const int* lab = labels + (long long)b * Lmax;
   float* e = em + ((long long)b * T + t) * Smax;
-  for (int s = threadIdx.x; s < S; s += blockDim.x) e[s] = row[ext_label(lab, s, blank)] - lse;
+  for (int s = threadIdx.x; s < S; s += blockDim.x) e[s] = (row[ext_label(lab, s, blank)] - lse) * LOG2E;  // log2 units
 }
 
 // ---- 2. lattice: block = 2 warps per utterance -------------------------------------------------
-template <int C>  // states per lane; S <= 32*C
+// max over the warp in one instruction: order-preserving float -> int map, redux.sync, map back
+__device__ __forceinline__ float warp_max_fast(float x) {
+  int i = __float_as_int(x);
+  i ^= (i >> 31) & 0x7fffffff;
+  i = __reduce_max_sync(0xffffffffu, i);
+  i ^= (i >> 31) & 0x7fffffff;
+  return __int_as_float(i);
+}
+
+template <int C, int D>  // C states per lane (S <= 32*C); D frames of emission prefetch
 __global__ void __launch_bounds__(64) ctc_lattice_kernel(const float* __restrict__ em, int T, int Smax,
                                                          const int* __restrict__ hlens, const int* __restrict__ labels, int Lmax,
                                                          const int* __restrict__ llens, int blank, float* __restrict__ alpha,
@@ -89,7 +137,8 @@ __global__ void __launch_bounds__(64) ctc_lattice_kernel(const float* __restrict
     const int s = dir == 0 ? s0 + i : s0 + i + 2;
     skip[i] = (s < S) && (s & 1) && s > 1 && (lab[s >> 1] != lab[(s >> 1) - 1]);
   }
-  float a[C], e_next[C];
+  float a[C];
+  float e[D][C];  // emissions of the next D frames: the loads are D frames ahead of their use (L2 latency off the chain)
   double offset = 0.0;
   const int t_first = dir == 0 ? 0 : Tb - 1;
   const int step = dir == 0 ? 1 : -1;
@@ -97,72 +146,84 @@ __global__ void __launch_bounds__(64) ctc_lattice_kernel(const float* __restrict
   for (int i = 0; i < C; ++i) {
     const int s = s0 + i;
     const bool init = dir == 0 ? (s < 2) : (s >= S - 2);
-    a[i] = (s < S && init) ? eb[(long long)t_first * Smax + s] : NEG_INF;
+    a[i] = (s < S && init) ? eb[(long long)t_first * Smax + s] : NEG_BIG;
   }
-  for (int n = 0; n < Tb; ++n) {
-    const int t = t_first + n * step;
-    if (n > 0) {
+#pragma unroll
+  for (int j = 0; j < D; ++j) {
+    const int nn = 1 + j;
+#pragma unroll
+    for (int i = 0; i < C; ++i)
+      e[j][i] = (nn < Tb && s0 + i < S) ? eb[(long long)(t_first + nn * step) * Smax + s0 + i] : 0.f;
+  }
+  // renormalise the row by its maximum (one redux instruction) and store it
+  auto renorm_store = [&](int t) {
+    float m = NEG_BIG;
+#pragma unroll
+    for (int i = 0; i < C; ++i) m = fmaxf(m, a[i]);
+    m = warp_max_fast(m);
+    offset += (double)m;  // an impossible row (m ~ -1e30) drives the total below -1e29: reported as infeasible
+#pragma unroll
+    for (int i = 0; i < C; ++i) a[i] = fmaxf(a[i] - m, NEG_BIG);
+#pragma unroll
+    for (int i = 0; i < C; ++i)
+      if (s0 + i < S) out[(long long)t * Smax + s0 + i] = a[i];
+  };
+  renorm_store(t_first);
+  for (int n0 = 1; n0 < Tb; n0 += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const int n = n0 + j;
+      if (n >= Tb) break;
+      const int t = t_first + n * step;
       // neighbours across the chunk boundary
       float p1, p2;  // alpha: states s0-1, s0-2 ; beta: states s0+C, s0+C+1
       if (dir == 0) {
         p1 = __shfl_up_sync(0xffffffffu, a[C - 1], 1);
         p2 = C >= 2 ? __shfl_up_sync(0xffffffffu, a[C >= 2 ? C - 2 : 0], 1) : __shfl_up_sync(0xffffffffu, a[0], 2);
-        if (lane == 0) p1 = p2 = NEG_INF;
-        if (C < 2 && lane == 1) p2 = NEG_INF;
+        if (lane == 0) p1 = p2 = NEG_BIG;
+        if (C < 2 && lane == 1) p2 = NEG_BIG;
 #pragma unroll
         for (int i = C - 1; i >= 0; --i) {
-          const float m1 = i >= 1 ? a[i - 1] : p1;
-          const float m2 = i >= 2 ? a[i - 2] : (i == 1 ? p1 : p2);
-          const float m2b = (C >= 2 && i == 0) ? p2 : m2;
-          const float v = lse3(a[i], m1, skip[i] ? m2b : NEG_INF);
-          a[i] = (s0 + i < S) ? v + e_next[i] : NEG_INF;
+          const float m1 = i >= 1 ? a[i >= 1 ? i - 1 : 0] : p1;
+          const float m2 = i >= 2 ? a[i >= 2 ? i - 2 : 0] : (i == 1 ? p1 : p2);
+          const float v = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG);
+          a[i] = (s0 + i < S) ? v + e[j][i] : NEG_BIG;
         }
       } else {
         p1 = __shfl_down_sync(0xffffffffu, a[0], 1);
         p2 = C >= 2 ? __shfl_down_sync(0xffffffffu, a[C >= 2 ? 1 : 0], 1) : __shfl_down_sync(0xffffffffu, a[0], 2);
-        if (lane == 31) p1 = p2 = NEG_INF;
-        if (C < 2 && lane == 30) p2 = NEG_INF;
+        if (lane == 31) p1 = p2 = NEG_BIG;
+        if (C < 2 && lane == 30) p2 = NEG_BIG;
 #pragma unroll
         for (int i = 0; i < C; ++i) {
           const float m1 = i + 1 < C ? a[i + 1 < C ? i + 1 : 0] : p1;
           const float m2 = i + 2 < C ? a[i + 2 < C ? i + 2 : 0] : (i + 2 == C ? p1 : p2);
-          const float v = lse3(a[i], m1, skip[i] ? m2 : NEG_INF);
-          a[i] = (s0 + i < S) ? v + e_next[i] : NEG_INF;
+          const float v = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG);
+          a[i] = (s0 + i < S) ? v + e[j][i] : NEG_BIG;
         }
       }
+      // refill this slot with the emissions of frame n + D
+      const int nf = n + D;
+      if (nf < Tb) {
+#pragma unroll
+        for (int i = 0; i < C; ++i) e[j][i] = (s0 + i < S) ? eb[(long long)(t_first + nf * step) * Smax + s0 + i] : 0.f;
+      }
+      renorm_store(t);
     }
-    // prefetch the next frame's emissions while this frame is renormalised and stored
-    const int tn = t + step;
-    if (n + 1 < Tb) {
-#pragma unroll
-      for (int i = 0; i < C; ++i) e_next[i] = (s0 + i < S) ? eb[(long long)tn * Smax + s0 + i] : 0.f;
-    }
-    float m = NEG_INF;
-#pragma unroll
-    for (int i = 0; i < C; ++i) m = fmaxf(m, a[i]);
-    m = warp_max(m);
-    if (m != NEG_INF) {
-      offset += (double)m;
-#pragma unroll
-      for (int i = 0; i < C; ++i) a[i] -= m;
-    }
-#pragma unroll
-    for (int i = 0; i < C; ++i)
-      if (s0 + i < S) out[(long long)t * Smax + s0 + i] = a[i];
   }
   if (dir == 0) {
     // log-likelihood = offsets + lse(alpha~(S-1), alpha~(S-2)) at the last frame
-    float fin = NEG_INF;
+    float fin = NEG_BIG;
 #pragma unroll
     for (int i = 0; i < C; ++i)
       if (s0 + i == S - 1 || s0 + i == S - 2) fin = lse2(fin, a[i]);
     // combine the (at most two) lanes holding the final states
     float mx = warp_max(fin);
-    float sum = (fin == NEG_INF || mx == NEG_INF) ? 0.f : expf(fin - mx);
+    float sum = ex2_(fin - mx);
     sum = warp_sum(sum);
     if (lane == 0) {
-      const double ll = (mx == NEG_INF) ? -INFINITY : offset + (double)mx + log((double)sum);
-      nll[b] = (float)(-ll);  // +inf when infeasible; zero_infinity is applied by ctc_finish_kernel
+      const double ll2 = offset + (double)mx + log2((double)sum);  // log2 of the sequence likelihood
+      nll[b] = (ll2 < -1.0e29) ? INFINITY : (float)(-ll2 * 0.6931471805599453);  // +inf when infeasible (zero_infinity later)
     }
   }
 }
@@ -190,7 +251,7 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const float* __restrict__
                                                        const float* __restrict__ em, const float* __restrict__ alpha,
                                                        const float* __restrict__ beta, int Smax, const int* __restrict__ feasible,
                                                        float scale, float* __restrict__ g32, bf16* __restrict__ g16,
-                                                       long long ldg) {
+                                                       long long ldg, bool vec4) {
   extern __shared__ float occ[];  // [V]
   __shared__ float red[32];
   const int t = blockIdx.x, b = blockIdx.y;
@@ -218,23 +279,39 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const float* __restrict__
   mx = red[0];
   for (int w = 1; w < (blockDim.x >> 5); ++w) mx = fmaxf(mx, red[w]);
   float sum = 0.f;
-  for (int s = threadIdx.x; s < S; s += blockDim.x) {
-    const float z = ar[s] + br[s] - er[s];
-    sum += (z == NEG_INF) ? 0.f : expf(z - mx);
-  }
+  for (int s = threadIdx.x; s < S; s += blockDim.x) sum += ex2_(ar[s] + br[s] - er[s] - mx);  // log2 domain; impossible states -> 0
   sum = block_sum(sum, red);  // contains the barriers that also order the occ[] zeroing
   const float inv = sum > 0.f ? 1.f / sum : 0.f;
   for (int s = threadIdx.x; s < S; s += blockDim.x) {
-    const float z = ar[s] + br[s] - er[s];
-    if (z != NEG_INF) atomicAdd(&occ[ext_label(lab, s, blank)], expf(z - mx) * inv);
+    const float o = ex2_(ar[s] + br[s] - er[s] - mx) * inv;
+    if (o > 0.f) atomicAdd(&occ[ext_label(lab, s, blank)], o);
   }
   __syncthreads();
-  const float lse = lse_in[r];
+  const float lse2 = lse_in[r] * LOG2E;
   const float* row = logits + r * ldv;
-  for (int v = threadIdx.x; v < Vp; v += blockDim.x) {
-    const float g = v < V ? scale * (expf(row[v] - lse) - occ[v]) : 0.f;
-    if (g32 != nullptr) g32[r * ldg + v] = g;
-    if (g16 != nullptr) g16[r * ldg + v] = __float2bfloat16(g);
+  if (vec4) {  // rows 16-byte aligned, ldg % 4 == 0: 16-byte loads and stores
+    for (int v = threadIdx.x * 4; v < Vp; v += blockDim.x * 4) {
+      float g[4];
+      if (v + 4 <= V) {
+        const float4 x = *reinterpret_cast<const float4*>(row + v);
+        g[0] = scale * (ex2_(fmaf(x.x, LOG2E, -lse2)) - occ[v]);
+        g[1] = scale * (ex2_(fmaf(x.y, LOG2E, -lse2)) - occ[v + 1]);
+        g[2] = scale * (ex2_(fmaf(x.z, LOG2E, -lse2)) - occ[v + 2]);
+        g[3] = scale * (ex2_(fmaf(x.w, LOG2E, -lse2)) - occ[v + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[j] = v + j < V ? scale * (ex2_(fmaf(row[v + j], LOG2E, -lse2)) - occ[v + j]) : 0.f;
+      }
+      if (g32 != nullptr) *reinterpret_cast<float4*>(g32 + r * ldg + v) = make_float4(g[0], g[1], g[2], g[3]);
+      if (g16 != nullptr)
+        *reinterpret_cast<uint2*>(g16 + r * ldg + v) = make_uint2(pack_bf16x2(g[0], g[1]), pack_bf16x2(g[2], g[3]));
+    }
+  } else {
+    for (int v = threadIdx.x; v < Vp; v += blockDim.x) {
+      const float g = v < V ? scale * (ex2_(fmaf(row[v], LOG2E, -lse2)) - occ[v]) : 0.f;
+      if (g32 != nullptr) g32[r * ldg + v] = g;
+      if (g16 != nullptr) g16[r * ldg + v] = __float2bfloat16(g);
+    }
   }
 }
 
@@ -267,7 +344,7 @@ extern "C" int b200slu_ctc_fwd(const float* logits, long long ldv, int B, int T,
                                               Smax);
   B2_LAUNCH_CHECK();
 #define LAT(C)                                                                                                              \
-  ctc_lattice_kernel<C><<<B, 64, 0, st>>>(em, T, Smax, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, alpha, beta, \
+  ctc_lattice_kernel<C, (C <= 8 ? 4 : 2)><<<B, 64, 0, st>>>(em, T, Smax, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, alpha, beta, \
                                           nll_raw)
   if (Smax <= 64) LAT(2);
   else if (Smax <= 128) LAT(4);
@@ -300,9 +377,11 @@ extern "C" int b200slu_ctc_bwd(const float* logits, long long ldv, int B, int T,
     cfg = true;
   }
   B2_SCOPE(FAM_CTC, st, 0, (double)B * T * V * (4.0 + (grad_f32 ? 4.0 : 0.0) + (grad_bf16 ? 2.0 : 0.0)) + 12.0 * n);
+  const bool vec4 = ldv % 4 == 0 && ldg % 4 == 0 && ((uintptr_t)logits % 16) == 0 &&
+                    (grad_f32 == nullptr || ((uintptr_t)grad_f32 % 16) == 0) && (grad_bf16 == nullptr || ((uintptr_t)grad_bf16 % 8) == 0);
   ctc_grad_kernel<<<dim3(T, B), 256, (size_t)V * 4, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank,
                                                           lse, em, alpha, beta, Smax, feasible, scale, grad_f32, (bf16*)grad_bf16,
-                                                          ldg);
+                                                          ldg, vec4);
   B2_LAUNCH_CHECK();
   return 0;
 }

@@ -347,6 +347,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const int num_kb_total = (K + BK - 1) / BK;
   const int units_per_batch = tiles_per_batch * splits;
 
+  b2_pdl_launch_dependents();  // the next kernel of the stream may start launching; it waits for us before reading
   if (threadIdx.x == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
@@ -371,6 +372,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  b2_pdl_wait();  // barrier init / TMEM allocation / descriptor prefetch overlapped the predecessor; its data is needed from here on
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -645,9 +647,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 12 * sizeof(long long), st));
     epl.dbg_out = dbg_buf;
   }
-  kern<<<grid, num_threads(EF), L::TOTAL, st>>>(ma, mb, mc, md, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
-                                                (int)units, epl);
-  B2_LAUNCH_CHECK();
+  B2_CUDA(b2_launch(kern, dim3(grid), dim3(num_threads(EF)), (size_t)L::TOTAL, st, ma, mb, mc, md, M, N, K, tiles_n,
+                    tiles_n * tiles_m, batch_inner, splits, kb_per, (int)units, epl));
   if (ep.debug & 16) {
     long long h[12];
     B2_CUDA(cudaStreamSynchronize(st));

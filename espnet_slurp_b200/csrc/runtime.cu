@@ -5,6 +5,8 @@
 #include <mutex>
 #include <vector>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 static thread_local char g_err[512] = "";
@@ -126,4 +128,9 @@ extern "C" long long b200slu_rel_shift_index(int i, int j, int T, int mode) {
     return (long long)(i + 1) * 65536 + (j - i - 2) + 1;
   }
   return -1;
+}
+
+bool b2_pdl_enabled() {
+  static const bool on = !(getenv("B200SLU_PDL") != nullptr && atoi(getenv("B200SLU_PDL")) == 0);
+  return on;
 }
