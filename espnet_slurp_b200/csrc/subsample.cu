@@ -75,17 +75,30 @@ __global__ void __launch_bounds__(256) conv1_bwd_kernel(const bf16* __restrict__
     }
     __syncthreads();
     if (pl < npl) {
-      for (int f = pl; f < F1; f += npl) {
-        float g[8];
-        load8_bf16(dh1 + (((long long)b * T1 + t) * F1 + f) * C + cg * 8, g);
+      constexpr int U = 5;  // independent 16-byte loads in flight per thread (the kernel is latency-bound otherwise)
+      for (int f0 = pl; f0 < F1; f0 += npl * U) {
+        uint4 raw[U];
 #pragma unroll
-        for (int k = 0; k < 9; ++k) {
-          const float xv = sx[(k / 3) * F + 2 * f + (k % 3)];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[k][j] += g[j] * xv;
+        for (int u = 0; u < U; ++u) {
+          const int f = f0 + u * npl;
+          raw[u] = f < F1 ? *reinterpret_cast<const uint4*>(dh1 + (((long long)b * T1 + t) * F1 + f) * C + cg * 8)
+                          : make_uint4(0u, 0u, 0u, 0u);
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[9][j] += g[j];
+        for (int u = 0; u < U; ++u) {
+          const int f = min(f0 + u * npl, F1 - 1);  // out-of-range slots carry zeros
+          const float2 g0 = unpack_bf16x2(raw[u].x), g1 = unpack_bf16x2(raw[u].y), g2 = unpack_bf16x2(raw[u].z),
+                       g3 = unpack_bf16x2(raw[u].w);
+          const float g[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
+#pragma unroll
+          for (int k = 0; k < 9; ++k) {
+            const float xv = sx[(k / 3) * F + 2 * f + (k % 3)];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[k][j] += g[j] * xv;
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[9][j] += g[j];
+        }
       }
     }
   }

@@ -82,6 +82,7 @@ class StepCtx:
 # position tables (constants; built once per length with torch, like the reference's extend_pe)
 # ------------------------------------------------------------------------------------------------------------------
 _PE_CACHE: Dict[tuple, torch.Tensor] = {}
+KEEP_IM2COL_BYTES = 8 << 30
 
 
 def _sinusoid(pos: torch.Tensor, d: int) -> torch.Tensor:
@@ -263,7 +264,10 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     T, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
     col = K.im2col(h1)
     h2 = K.gemm(col, W[e + ".conv.2.weight"], bias=P[e + ".conv.2.bias"], act="relu")
-    del col  # recomputed in the backward (it is 9x the size of h1)
+    # the im2col matrix (9x the conv.0 output: 27 MB per utterance of 5 s) is kept for the wgrad GEMM while it fits
+    # comfortably (<= 8 GB of the 180 GB), else dropped here and rebuilt in the backward
+    if col.numel() * 2 > KEEP_IM2COL_BYTES:
+        col = None
     h2v = h2.view(B * T, F2 * C_)
     dpos = ctx.drop(cfg.pos_dropout)
     x = K.gemm(h2v, W[e + ".out.0.weight"], bias=P[e + ".out.0.bias"], alpha=math.sqrt(cfg.d), drop=dpos, out_dtype=F32)
@@ -277,13 +281,13 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
         x, s = enc_layer_fwd(x, pos16, olens, P, W, f"{p}.encoders.{n}", cfg, B, T, ctx, bn_buffers)
         layers.append(s)
     enc16, enc, st = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"], want_bf16=True, want_f32=True)
-    return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, B, T)
+    return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, col, B, T)
 
 
 def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=None):
     """denc f32 [B*T, d]: gradient w.r.t. the encoder output.  Accumulates every encoder parameter gradient into G.
     on_ready("enc<n>") is called when block n's parameter gradients are final (data-parallel bucket hook)."""
-    feats, h1, h2v, dpos, pos16, layers, xl, st, B, T = saved
+    feats, h1, h2v, dpos, pos16, layers, xl, st, col, B, T = saved
     e = p + ".embed"
     dx, _ = K.layernorm_bwd(denc, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
     for n in reversed(range(cfg.blocks)):
@@ -296,7 +300,8 @@ def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=
     K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
     dh2 = K.gemm(g, W[e + ".out.0.weight"], trans_b=True, act_grad_input=h2v, act_grad="relu").view(-1, C_)
     K.colsum(dh2, G[e + ".conv.2.bias"])
-    col = K.im2col(h1)
+    if col is None:
+        col = K.im2col(h1)
     K.gemm(dh2, col, trans=True, out=G[e + ".conv.2.weight"], accumulate=True)
     del col
     dcol = K.gemm(dh2, W[e + ".conv.2.weight"], trans_b=True)
