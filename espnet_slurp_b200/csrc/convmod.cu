@@ -10,11 +10,15 @@
 
 namespace {
 
-constexpr int TT = 32;    // output frames per block
 constexpr int CC = 64;    // channels per block
 constexpr int KMAX = 31;  // cnn_module_kernel upper bound (SLURP/LibriSpeech: 31; tiny fixtures: 7)
+// Output frames per block are a template parameter TT (multiple of 32): the K - 1 halo frames are staged (and their GLU
+// recomputed) once per TT outputs, so a longer tile cuts both the redundant loads and the per-block weight fetch.
+// KT = compile-time kernel size (31 for every recipe; 0 = run-time K <= KMAX for the small test fixtures): with KT the
+// tap loops carry no run-time predicates (they were 70 % of the instructions of the first version).
 
 // stage glu(pw1) for frames [t0 - pad, t0 + TT + pad) x channels [c0, c0 + CC) into smem (0 outside [0, T))
+template <int TT>
 __device__ __forceinline__ void stage_glu(const bf16* __restrict__ pw1, int b, int T, int C, int t0, int c0, int K,
                                           float (*sm)[CC]) {
   const int pad = (K - 1) / 2, nf = TT + K - 1;
@@ -30,52 +34,60 @@ __device__ __forceinline__ void stage_glu(const bf16* __restrict__ pw1, int b, i
 #pragma unroll
       for (int j = 0; j < 8; ++j) g[j] = a[j] * sigmoidf_(gt[j]);
     }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sm[f][cg * 8 + j] = g[j];
+    float4* dst = reinterpret_cast<float4*>(&sm[f][cg * 8]);
+    dst[0] = make_float4(g[0], g[1], g[2], g[3]);
+    dst[1] = make_float4(g[4], g[5], g[6], g[7]);
   }
 }
 
-// Each thread owns one channel and FR = 8 consecutive output frames: the K + 7 staged inputs it needs are read from
-// shared memory once into a sliding register window (4.75 LDS per output instead of K), weights stay in registers.
+// Each thread owns one channel and, per 32-frame sub-tile, FR = 8 consecutive output frames: the K + 7 staged inputs
+// it needs are read from shared memory once into a sliding register window (4.75 LDS per output instead of K),
+// weights stay in registers for the whole tile.
 constexpr int FR = 8;
-static_assert(TT == 4 * FR, "4 frame lanes of FR frames per block tile");
 
+template <int TT, int KT>
 __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict__ pw1, const float* __restrict__ w,
-                                                         const float* __restrict__ bias, int B, int T, int C, int K,
+                                                         const float* __restrict__ bias, int B, int T, int C, int Krt,
                                                          bf16* __restrict__ out, float* __restrict__ sums) {
-  __shared__ float sm[TT + KMAX - 1][CC];
+  static_assert(TT % (4 * FR) == 0, "tile = whole sub-tiles of 4 frame lanes x FR frames");
+  __shared__ __align__(16) float sm[TT + KMAX - 1][CC];
   __shared__ float red[2][4][CC];
+  const int K = KT > 0 ? KT : Krt;
   const int t0 = blockIdx.x * TT, c0 = blockIdx.y * CC, b = blockIdx.z;
-  stage_glu(pw1, b, T, C, t0, c0, K, sm);
-  __syncthreads();
+  stage_glu<TT>(pw1, b, T, C, t0, c0, K, sm);
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;  // 4 frame lanes x FR frames
   const int c = c0 + cl;
+  float wr[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) wr[k] = (c < C && k < K) ? w[c * K + k] : 0.f;
+  const float bs = c < C ? bias[c] : 0.f;
+  __syncthreads();
   float s1 = 0.f, s2 = 0.f;
   if (c < C) {
-    float wr[KMAX];
+#pragma unroll 1
+    for (int sub = 0; sub < TT / (4 * FR); ++sub) {
+      const int f0 = sub * 4 * FR + fr * FR;
+      if (t0 + f0 >= T) break;
+      float acc[FR];
 #pragma unroll
-    for (int k = 0; k < KMAX; ++k) wr[k] = k < K ? w[c * K + k] : 0.f;
-    const float bs = bias[c];
-    float acc[FR];
+      for (int o = 0; o < FR; ++o) acc[o] = bs;
 #pragma unroll
-    for (int o = 0; o < FR; ++o) acc[o] = bs;
-    const int f0 = fr * FR;
+      for (int j = 0; j < FR + KMAX - 1; ++j) {
+        if (KT > 0 ? (j < FR + KT - 1) : (j < FR + K - 1)) {
+          const float v = sm[f0 + j][cl];
 #pragma unroll
-    for (int j = 0; j < FR + KMAX - 1; ++j) {
-      if (j < FR + K - 1) {
-        const float v = sm[f0 + j][cl];
-#pragma unroll
-        for (int o = 0; o < FR; ++o)
-          if (j - o >= 0 && j - o < KMAX) acc[o] += wr[j - o] * v;  // wr[k] = 0 for k >= K
+          for (int o = 0; o < FR; ++o)
+            if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) acc[o] += wr[j - o] * v;  // wr[k] = 0 for k >= K
+        }
       }
-    }
 #pragma unroll
-    for (int o = 0; o < FR; ++o) {
-      const int t = t0 + f0 + o;
-      if (t < T) {
-        out[((long long)b * T + t) * C + c] = __float2bfloat16(acc[o]);
-        s1 += acc[o];
-        s2 += acc[o] * acc[o];
+      for (int o = 0; o < FR; ++o) {
+        const int t = t0 + f0 + o;
+        if (t < T) {
+          out[((long long)b * T + t) * C + c] = __float2bfloat16(acc[o]);
+          s1 += acc[o];
+          s2 += acc[o] * acc[o];
+        }
       }
     }
   }
@@ -90,13 +102,16 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
 
 // Backward: grid (channel tiles, utterance chunks); each block walks all its (utterance, time tile) pairs and keeps the
 // depthwise weight gradient in registers across them, so the global atomics are per block, not per tile.
+template <int TT, int KT>
 __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict__ d_dw, const bf16* __restrict__ pw1,
-                                                         const float* __restrict__ w, int B, int T, int C, int K,
+                                                         const float* __restrict__ w, int B, int T, int C, int Krt,
                                                          bf16* __restrict__ d_pw1, float* __restrict__ dw_accum,
                                                          float* __restrict__ dbias_accum) {
-  __shared__ float sg[TT + KMAX - 1][CC];  // glu halo tile
-  __shared__ float sd[TT + KMAX - 1][CC];  // d_dw halo tile
-  __shared__ float swg[CC][KMAX + 1];      // block partial of dW (+ dbias in the last slot)
+  extern __shared__ __align__(16) float dyn_smem[];
+  float (*sg)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                             // glu halo tile  [TT+KMAX-1][CC]
+  float (*sd)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + (TT + KMAX - 1) * CC);      // d_dw halo tile
+  float (*swg)[KMAX + 1] = reinterpret_cast<float (*)[KMAX + 1]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);  // dW partial (+ dbias)
+  const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
   const int pad = (K - 1) / 2, nf = TT + K - 1;
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;
@@ -113,18 +128,22 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
   for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
     const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
     __syncthreads();  // previous tile fully consumed
-    stage_glu(pw1, b, T, C, t0, c0, K, sg);
+    stage_glu<TT>(pw1, b, T, C, t0, c0, K, sg);
     for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
       const int f = it / (CC / 8), cg = it - f * (CC / 8);
       const int t = t0 - pad + f, cc = c0 + cg * 8;
       float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       if (t >= 0 && t < T && cc < C) load8_bf16(d_dw + ((long long)b * T + t) * C + cc, g);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) sd[f][cg * 8 + j] = g[j];
+      float4* dst = reinterpret_cast<float4*>(&sd[f][cg * 8]);
+      dst[0] = make_float4(g[0], g[1], g[2], g[3]);
+      dst[1] = make_float4(g[4], g[5], g[6], g[7]);
     }
     __syncthreads();
     if (c < C) {
-      const int f0 = fr * FR;
+#pragma unroll 1
+     for (int sub = 0; sub < TT / (4 * FR); ++sub) {
+      const int f0 = sub * 4 * FR + fr * FR;
+      if (t0 + f0 >= T) break;
       float dg[FR], dv[FR];
 #pragma unroll
       for (int o = 0; o < FR; ++o) {
@@ -134,19 +153,19 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
       }
 #pragma unroll
       for (int j = 0; j < FR + KMAX - 1; ++j) {
-        if (j < FR + K - 1) {
+        if (KT > 0 ? (j < FR + KT - 1) : (j < FR + K - 1)) {
           // d_glu[f0+o] = sum_k w[k] * d_dw[f0 + o - k + pad]  = sum over staged row j = o + (K-1) - k
           const float dj = sd[f0 + j][cl];
           const float gj = sg[f0 + j][cl];
 #pragma unroll
           for (int o = 0; o < FR; ++o) {
             // forward tap index of staged row j for output o: k = j - o (glu[f0+o+k] feeds out[f0+o])
-            if (j - o >= 0 && j - o < KMAX) acc[j - o] += dv[o] * gj;
+            if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) acc[j - o] += dv[o] * gj;
           }
 #pragma unroll
           for (int o = 0; o < FR; ++o) {
             // backward: d_dw[f0+o - k + pad] sits in staged row j = o + (K-1) - k  ->  w[k] = wrev[j - o]
-            if (j - o >= 0 && j - o < KMAX) dg[o] += wrev[j - o] * dj;
+            if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) dg[o] += wrev[j - o] * dj;
           }
         }
       }
@@ -162,6 +181,7 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
           drow[C + c] = __float2bfloat16(dg[o] * a * sgm * (1.f - sgm));
         }
       }
+     }
     }
   }
   if (c < C) {
@@ -305,9 +325,18 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
                C, K);
   B2_CHECK_ARG(B <= 65535, "glu_dwconv: B too large");
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((T + TT - 1) / TT, (C + CC - 1) / CC, B);
   B2_SCOPE(FAM_CONVMOD, st, 2.0 * B * T * C * K, 6.0 * B * T * C);
-  glu_dw_fwd_kernel<<<grid, 256, 0, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out, bn_sums);
+  // tile length: 96 frames (halo overhead 1.31x) unless the utterances are short
+#define B2_FWD(TT_, KT_)                                                                                              \
+  glu_dw_fwd_kernel<TT_, KT_><<<dim3((T + TT_ - 1) / TT_, (C + CC - 1) / CC, B), 256, 0, st>>>((const bf16*)pw1, w, bias, B, T, C, K, \
+                                                                                                (bf16*)out, bn_sums)
+  if (K == 31) {
+    if (T > 64) B2_FWD(96, 31);
+    else B2_FWD(32, 31);
+  } else {
+    B2_FWD(32, 0);
+  }
+#undef B2_FWD
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -317,13 +346,29 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
   B2_CHECK_ARG(B > 0 && T > 0 && C % 8 == 0 && K % 2 == 1 && K <= KMAX, "glu_dwconv_bwd: C %% 8 == 0, odd K <= %d", KMAX);
   B2_CHECK_ARG(B <= 65535, "glu_dwconv_bwd: B too large");
   cudaStream_t st = (cudaStream_t)stream;
-  const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT - 1) / TT);
-  int gy = (2 * b2_num_sms() + ctiles - 1) / ctiles;
-  if (gy > units) gy = units;
-  dim3 grid(ctiles, gy);
   B2_SCOPE(FAM_CONVMOD, st, 4.0 * B * T * C * K, 10.0 * B * T * C);
-  glu_dw_bwd_kernel<<<grid, 256, 0, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,
-                                          dbias_accum);
+#define B2_BWD(TT_, KT_)                                                                                                     \
+  do {                                                                                                                       \
+    const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                                 \
+    int gy = (2 * b2_num_sms() + ctiles - 1) / ctiles;                                                                       \
+    if (gy > units) gy = units;                                                                                              \
+    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 1)) * sizeof(float);                               \
+    auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
+    static bool cfg = false;                                                                                                 \
+    if (!cfg) {                                                                                                              \
+      B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                           \
+      cfg = true;                                                                                                            \
+    }                                                                                                                        \
+    kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,  \
+                                              dbias_accum);                                                                  \
+  } while (0)
+  if (K == 31) {
+    if (T > 64) B2_BWD(96, 31);
+    else B2_BWD(32, 31);
+  } else {
+    B2_BWD(32, 0);
+  }
+#undef B2_BWD
   B2_LAUNCH_CHECK();
   return 0;
 }
