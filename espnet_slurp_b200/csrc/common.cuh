@@ -250,6 +250,44 @@ static inline cudaError_t b2_launch(void (*kern)(KArgs...), dim3 grid, dim3 bloc
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
+// ---------------------------------------------------------------------------
+// Column-sum kernels (elementwise.cu, convmod.cu).  Same-address atomics from different SMs retire at one per ~70 ns (measured: +5.2 us for 74
+// more blocks per column), so the number of blocks that contribute to one output column is what the kernel's tail
+// costs.  A block is therefore a NARROW strip -- 8 column groups of 8 (64 columns: one 128-byte segment of a bf16
+// row per 8 lanes, four rows per warp-wide load) x 64 row lanes -- which makes grid.x = N / 64 wide and grid.y
+// (blocks per column) ~ SMs / grid.x small.  Every thread keeps CS_U independent 16-byte row loads in flight
+// (512 threads x 8 x 16 B = 64 KB per block).  The block reduces its row lanes through shared memory and issues ONE
+// atomic per column.
+constexpr int CS_TX = 8;                       // column groups of 8 per block
+constexpr int CS_ROWS = 512 / CS_TX;           // row lanes per block
+constexpr int CS_COLS = CS_TX * 8;             // columns per block
+constexpr int CS_U = 8;                        // rows in flight per thread
+
+__device__ __forceinline__ void colsum_block_reduce(float (&acc)[8], float (*red)[CS_COLS + 1], int tx, int ty, int N,
+                                                    float* __restrict__ out) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[ty][tx * 8 + j] = acc[j];
+  __syncthreads();
+  // 512 threads: 64 columns x 8 partial sums over 8 row lanes each, then a shuffle over the 8 partials
+  const int col = threadIdx.x >> 3, part = threadIdx.x & 7;
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < CS_ROWS / 8; ++k) s += red[part * (CS_ROWS / 8) + k][col];
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  // a warp holds four consecutive columns (lanes 0, 8, 16, 24): one 16-byte vector atomic instead of four scalar ones
+  const int lane = threadIdx.x & 31;
+  const float s1 = __shfl_sync(0xffffffffu, s, 8), s2 = __shfl_sync(0xffffffffu, s, 16), s3 = __shfl_sync(0xffffffffu, s, 24);
+  const int c = blockIdx.x * CS_COLS + col, c0 = c - (lane >> 3);  // c0: the warp's first column
+  const bool vec = c0 + 3 < N && (((uintptr_t)(out + c0)) & 15) == 0;
+  if (vec) {
+    if (lane == 0) atomicAdd(reinterpret_cast<float4*>(out + c0), make_float4(s, s1, s2, s3));
+  } else if (part == 0 && c < N) {
+    atomicAdd(out + c, s);
+  }
+}
+
 static inline int b2_grid_for(long long work_items, int threads, int per_sm = 8) {
   long long blocks = (work_items + threads - 1) / threads;
   long long cap = (long long)b2_num_sms() * per_sm;

@@ -53,16 +53,22 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
   __shared__ __align__(16) float sm[TT + KMAX - 1][CC];
   __shared__ float red[2][4][CC];
   const int K = KT > 0 ? KT : Krt;
-  const int t0 = blockIdx.x * TT, c0 = blockIdx.y * CC, b = blockIdx.z;
-  stage_glu<TT>(pw1, b, T, C, t0, c0, K, sm);
+  const int c0 = blockIdx.x * CC;
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;  // 4 frame lanes x FR frames
   const int c = c0 + cl;
   float wr[KMAX];
 #pragma unroll
   for (int k = 0; k < KMAX; ++k) wr[k] = (c < C && k < K) ? w[c * K + k] : 0.f;
   const float bs = c < C ? bias[c] : 0.f;
-  __syncthreads();
+  const int ntt = (T + TT - 1) / TT;
   float s1 = 0.f, s2 = 0.f;
+  // Each block walks its (utterance, time tile) units and keeps the BatchNorm partial sums in registers across them:
+  // the atomics on `sums` are per block (grid.y per channel), not per tile -- same-address atomics retire serially.
+  for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
+  const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
+  __syncthreads();  // previous tile fully consumed
+  stage_glu<TT>(pw1, b, T, C, t0, c0, K, sm);
+  __syncthreads();
   if (c < C) {
 #pragma unroll 1
     for (int sub = 0; sub < TT / (4 * FR); ++sub) {
@@ -90,6 +96,7 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
         }
       }
     }
+  }
   }
   red[0][fr][cl] = s1;
   red[1][fr][cl] = s2;
@@ -236,49 +243,53 @@ __global__ void __launch_bounds__(256) bn_swish_fwd_kernel(const bf16* __restric
 }
 
 // sums2[c] += sum dz ; sums2[C + c] += sum dz * xhat   with dz = dy * swish'(gamma * xhat + beta)
-__global__ void __launch_bounds__(256) bn_swish_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                                                  const float* __restrict__ mean_rstd,
-                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                  int M, int C, float* __restrict__ sums2) {
-  __shared__ float red[2][8][32][8];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int g = blockIdx.x * 32 + tx;
-  const bool ok = g * 8 < C;
+__global__ void __launch_bounds__(512, 1) bn_swish_bwd_reduce_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                                     const float* __restrict__ mean_rstd,
+                                                                     const float* __restrict__ gamma,
+                                                                     const float* __restrict__ beta, int M, int C,
+                                                                     float* __restrict__ sums2) {
+  // narrow column strips (common.cuh): few blocks per output column, one vector atomic per four columns
+  __shared__ float red[2][CS_ROWS][CS_COLS + 1];
+  const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
+  const int g = blockIdx.x * CS_TX + tx;
   float a1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, a2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (ok) {
+  if (g * 8 < C) {
     float mu[8], rs[8], ga[8], be[8];
     load8_f32(mean_rstd + g * 8, mu);
     load8_f32(mean_rstd + C + g * 8, rs);
     load8_f32(gamma + g * 8, ga);
     load8_f32(beta + g * 8, be);
-    for (long long r = (long long)blockIdx.y * 8 + ty; r < M; r += (long long)gridDim.y * 8) {
-      float d[8], v[8];
-      load8_bf16(dy + r * C + g * 8, d);
-      load8_bf16(x + r * C + g * 8, v);
+    constexpr int U = 4;
+    const long long step = (long long)gridDim.y * CS_ROWS;
+    for (long long r0 = (long long)blockIdx.y * CS_ROWS + ty; r0 < M; r0 += U * step) {
+      uint4 rd[U], rx[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float xh = (v[j] - mu[j]) * rs[j];
-        const float dz = d[j] * swish_gradf_(ga[j] * xh + be[j]);
-        a1[j] += dz;
-        a2[j] += dz * xh;
+      for (int u = 0; u < U; ++u) {
+        const long long r = r0 + u * step;
+        rd[u] = r < M ? *reinterpret_cast<const uint4*>(dy + r * C + g * 8) : make_uint4(0u, 0u, 0u, 0u);  // dy = 0: no contribution
+        rx[u] = r < M ? *reinterpret_cast<const uint4*>(x + r * C + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t wd[4] = {rd[u].x, rd[u].y, rd[u].z, rd[u].w}, wx[4] = {rx[u].x, rx[u].y, rx[u].z, rx[u].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 d2 = unpack_bf16x2(wd[q]), x2 = unpack_bf16x2(wx[q]);
+          const float dd[2] = {d2.x, d2.y}, xx[2] = {x2.x, x2.y};
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int j = 2 * q + h;
+            const float xh = (xx[h] - mu[j]) * rs[j];
+            const float dz = dd[h] * swish_gradf_(ga[j] * xh + be[j]);
+            a1[j] += dz;
+            a2[j] += dz * xh;
+          }
+        }
       }
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    red[0][ty][tx][j] = a1[j];
-    red[1][ty][tx][j] = a2[j];
-  }
-  __syncthreads();
-  if (ty < 2 && ok) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float s = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) s += red[ty][k][tx][j];
-      atomicAdd(sums2 + ty * C + g * 8 + j, s);
-    }
-  }
+  colsum_block_reduce(a1, red[0], tx, ty, C, sums2);
+  colsum_block_reduce(a2, red[1], tx, ty, C, sums2 + C);
 }
 
 __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
@@ -328,8 +339,13 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
   B2_SCOPE(FAM_CONVMOD, st, 2.0 * B * T * C * K, 6.0 * B * T * C);
   // tile length: 96 frames (halo overhead 1.31x) unless the utterances are short
 #define B2_FWD(TT_, KT_)                                                                                              \
-  glu_dw_fwd_kernel<TT_, KT_><<<dim3((T + TT_ - 1) / TT_, (C + CC - 1) / CC, B), 256, 0, st>>>((const bf16*)pw1, w, bias, B, T, C, K, \
-                                                                                                (bf16*)out, bn_sums)
+  do {                                                                                                                \
+    const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                          \
+    int gy = (4 * b2_num_sms() + ctiles - 1) / ctiles;                                                                \
+    if (gy > units) gy = units;                                                                                       \
+    glu_dw_fwd_kernel<TT_, KT_><<<dim3(ctiles, gy), 256, 0, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out,  \
+                                                                  bn_sums);                                           \
+  } while (0)
   if (K == 31) {
     if (T > 64) B2_FWD(96, 31);
     else B2_FWD(32, 31);
@@ -399,12 +415,12 @@ extern "C" int b200slu_bn_swish_bwd(const void* dy, const void* x, const float* 
                                     void* stream) {
   B2_CHECK_ARG(M > 0 && M < (1LL << 31) && C % 8 == 0, "bn_swish_bwd: C %% 8 == 0");
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((C + 255) / 256, 1);
-  long long gy = (M + 63) / 64;
-  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  dim3 grid((C + CS_COLS - 1) / CS_COLS, 1);
+  long long gy = (M + CS_ROWS * 4 - 1) / (CS_ROWS * 4);
+  const int cap = (b2_num_sms() + grid.x - 1) / grid.x;  // one 512-thread block (128 registers) per SM
   grid.y = (unsigned)(gy < cap ? gy : cap);
   B2_SCOPE(FAM_CONVMOD, st, 0, 10.0 * M * C);
-  bn_swish_bwd_reduce_kernel<<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, (int)M, C,
+  bn_swish_bwd_reduce_kernel<<<grid, 512, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, (int)M, C,
                                                    sums2_zeroed);
   B2_LAUNCH_CHECK();
   bn_swish_bwd_apply_kernel<<<b2_grid_for(M * (C >> 3), 256), 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma,

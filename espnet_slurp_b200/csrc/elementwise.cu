@@ -1,6 +1,8 @@
 // Small memory-bound helpers around the GEMMs: fp32->bf16 cast with scale/dropout, bias-gradient
 // column sums, the rel-pos bias add (attention.py:289-291) and the decoder token embedding
 // (transformer_decoder.py:72-77, embedding.py:82-94).  All are single-pass, 16-byte vectorised.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -24,26 +26,28 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, 
 
 // y = bf16(alpha * dropout(x)) and colsum[n] += sum_m alpha * dropout(x)[m, n] in one pass over x (the backward of
 // "x + dropout(branch)" feeds both the dgrad/wgrad GEMMs (y) and the bias gradient of the branch's last Linear).
-__global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restrict__ x, bf16* __restrict__ y, int M, int N,
-                                                          float alpha, B2Dropout drop, float* __restrict__ out) {
-  __shared__ float red[8][32][8];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int g = blockIdx.x * 32 + tx;  // column group of 8 (N % 8 == 0)
+__global__ void __launch_bounds__(512, 2) cast_colsum_kernel(const float* __restrict__ x, bf16* __restrict__ y, int M,
+                                                                      int N, float alpha, B2Dropout drop,
+                                                                      float* __restrict__ out) {
+  __shared__ float red[CS_ROWS][CS_COLS + 1];
+  const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
+  const int g = blockIdx.x * CS_TX + tx;  // column group of 8 (N % 8 == 0)
   const bool ok = g * 8 < N;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (ok) {
     B2DropKey dk = {0ull, 0u, 1.f};
     if (drop.p > 0.f) dk = dropout_key(drop);
-    const long long step = (long long)gridDim.y * 8;
-    for (long long r0 = (long long)blockIdx.y * 8 + ty; r0 < M; r0 += 4 * step) {
-      float v[4][8];
+    constexpr int U = 3;  // fp32 rows are two 16-byte loads per thread (4 rows would spill at 64 registers)
+    const long long step = (long long)gridDim.y * CS_ROWS;
+    for (long long r0 = (long long)blockIdx.y * CS_ROWS + ty; r0 < M; r0 += U * step) {
+      float v[U][8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {  // four independent rows in flight per thread
+      for (int u = 0; u < U; ++u) {
         const long long r = r0 + u * step;
         if (r < M) load8_f32(x + r * N + g * 8, v[u]);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         const long long r = r0 + u * step;
         if (r < M) {
           if (drop.p > 0.f) {
@@ -61,57 +65,35 @@ __global__ void __launch_bounds__(256) cast_colsum_kernel(const float* __restric
       }
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) red[ty][tx][j] = acc[j];
-  __syncthreads();
-  if (ty == 0 && ok) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float s = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) s += red[k][tx][j];
-      atomicAdd(out + g * 8 + j, s);
-    }
-  }
+  colsum_block_reduce(acc, red, tx, ty, N, out);
 }
 
 // out[n] += sum_m dy[m, n]   (dy bf16, row stride ld)
-__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ dy, int M, int N, long long ld,
-                                                     float* __restrict__ out) {
-  __shared__ float red[8][32][8];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int g = blockIdx.x * 32 + tx;  // column group of 8
+__global__ void __launch_bounds__(512, 2) colsum_kernel(const bf16* __restrict__ dy, int M, int N, long long ld,
+                                                                 float* __restrict__ out) {
+  __shared__ float red[CS_ROWS][CS_COLS + 1];
+  const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
+  const int g = blockIdx.x * CS_TX + tx;  // column group of 8
   const bool ok = g * 8 < N;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (ok) {
-    const long long step = (long long)gridDim.y * 8;
-    for (long long r0 = (long long)blockIdx.y * 8 + ty; r0 < M; r0 += 4 * step) {
-      uint4 raw[4];
+    const long long step = (long long)gridDim.y * CS_ROWS;
+    for (long long r0 = (long long)blockIdx.y * CS_ROWS + ty; r0 < M; r0 += CS_U * step) {
+      uint4 raw[CS_U];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {  // four independent rows in flight per thread
+      for (int u = 0; u < CS_U; ++u) {
         const long long r = r0 + u * step;
         raw[u] = r < M ? *reinterpret_cast<const uint4*>(dy + r * ld + g * 8) : make_uint4(0u, 0u, 0u, 0u);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < CS_U; ++u) {
         const float2 a = unpack_bf16x2(raw[u].x), b = unpack_bf16x2(raw[u].y), c = unpack_bf16x2(raw[u].z),
                      d = unpack_bf16x2(raw[u].w);
         acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
       }
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) red[ty][tx][j] = acc[j];
-  __syncthreads();
-  if (ty == 0 && ok) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float s = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) s += red[k][tx][j];
-      if (g * 8 + j < N) atomicAdd(out + g * 8 + j, s);
-    }
-  }
+  colsum_block_reduce(acc, red, tx, ty, N, out);
 }
 
 // q_u = q + pos_bias_u, q_v = q + pos_bias_v  (q = first d columns of the fused qkv rows)
@@ -137,44 +119,42 @@ __global__ void __launch_bounds__(256) pos_bias_fwd_kernel(const bf16* __restric
 }
 
 // dq = dq_u + dq_v (written into the fused dqkv rows); du += colsum(dq_u); dv += colsum(dq_v)
-__global__ void __launch_bounds__(256) pos_bias_bwd_kernel(const bf16* __restrict__ dqu, const bf16* __restrict__ dqv, int M,
-                                                           int d, bf16* __restrict__ dq, long long lddq,
-                                                           float* __restrict__ du, float* __restrict__ dv) {
-  __shared__ float red[2][8][32][8];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int g = blockIdx.x * 32 + tx;
-  const bool ok = g * 8 < d;
+__global__ void __launch_bounds__(512, 1) pos_bias_bwd_kernel(const bf16* __restrict__ dqu, const bf16* __restrict__ dqv, int M,
+                                                              int d, bf16* __restrict__ dq, long long lddq,
+                                                              float* __restrict__ du, float* __restrict__ dv) {
+  __shared__ float red[2][CS_ROWS][CS_COLS + 1];
+  const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
+  const int g = blockIdx.x * CS_TX + tx;
   float au[8] = {0, 0, 0, 0, 0, 0, 0, 0}, av[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (ok) {
-    for (long long r = (long long)blockIdx.y * 8 + ty; r < M; r += (long long)gridDim.y * 8) {
-      float a[8], b[8], o[8];
-      load8_bf16(dqu + r * d + g * 8, a);
-      load8_bf16(dqv + r * d + g * 8, b);
+  if (g * 8 < d) {
+    constexpr int U = 4;
+    const long long step = (long long)gridDim.y * CS_ROWS;
+    for (long long r0 = (long long)blockIdx.y * CS_ROWS + ty; r0 < M; r0 += U * step) {
+      uint4 ra[U], rb[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        au[j] += a[j];
-        av[j] += b[j];
-        o[j] = a[j] + b[j];
+      for (int u = 0; u < U; ++u) {
+        const long long r = r0 + u * step;
+        ra[u] = r < M ? *reinterpret_cast<const uint4*>(dqu + r * d + g * 8) : make_uint4(0u, 0u, 0u, 0u);
+        rb[u] = r < M ? *reinterpret_cast<const uint4*>(dqv + r * d + g * 8) : make_uint4(0u, 0u, 0u, 0u);
       }
-      store8_bf16(dq + r * lddq + g * 8, o);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long r = r0 + u * step;
+        const uint32_t wa[4] = {ra[u].x, ra[u].y, ra[u].z, ra[u].w}, wb[4] = {rb[u].x, rb[u].y, rb[u].z, rb[u].w};
+        float o[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 a = unpack_bf16x2(wa[q]), b = unpack_bf16x2(wb[q]);
+          au[2 * q] += a.x; au[2 * q + 1] += a.y;
+          av[2 * q] += b.x; av[2 * q + 1] += b.y;
+          o[2 * q] = a.x + b.x; o[2 * q + 1] = a.y + b.y;
+        }
+        if (r < M) store8_bf16(dq + r * lddq + g * 8, o);
+      }
     }
   }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    red[0][ty][tx][j] = au[j];
-    red[1][ty][tx][j] = av[j];
-  }
-  __syncthreads();
-  if (ty < 2 && ok) {
-    float* dst = ty == 0 ? du : dv;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float s = 0.f;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) s += red[ty][k][tx][j];
-      atomicAdd(dst + g * 8 + j, s);
-    }
-  }
+  colsum_block_reduce(au, red[0], tx, ty, d, du);
+  colsum_block_reduce(av, red[1], tx, ty, d, dv);
 }
 
 // x[r, :] = dropout(emb[tok[r], :] * scale + pe[r % L, :])   (fp32 residual stream)
@@ -213,6 +193,11 @@ __global__ void __launch_bounds__(256) embed_bwd_kernel(const float* __restrict_
   }
 }
 
+int colsum_blocks_per_sm() {
+  static const int v = getenv("B200SLU_COLSUM_BPS") ? atoi(getenv("B200SLU_COLSUM_BPS")) : 2;  // tuning knob
+  return v > 0 ? v : 2;
+}
+
 }  // namespace
 
 extern "C" int b200slu_cast_bf16(const float* x, void* y, long long n, float alpha, float drop_p, unsigned long long seed,
@@ -231,12 +216,12 @@ extern "C" int b200slu_cast_colsum_bf16(const float* x, void* y, int M, int N, f
   B2_CHECK_ARG(M > 0 && N > 0 && N % 8 == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0,
                "cast_colsum: N %% 8 == 0 and 16-byte aligned pointers (M=%d N=%d)", M, N);
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((N + 255) / 256, 1);
-  const int gy = (M + 31) / 32;
-  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  dim3 grid((N + CS_COLS - 1) / CS_COLS, 1);
+  const int gy = (M + CS_ROWS * 3 - 1) / (CS_ROWS * 3);
+  const int cap = (colsum_blocks_per_sm() * b2_num_sms() + grid.x - 1) / grid.x;
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * N);
-  cast_colsum_kernel<<<grid, 256, 0, st>>>(x, (bf16*)y, M, N, alpha, b2_make_drop(drop_p, seed, site), colsum_accum);
+  cast_colsum_kernel<<<grid, 512, 0, st>>>(x, (bf16*)y, M, N, alpha, b2_make_drop(drop_p, seed, site), colsum_accum);
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -244,12 +229,12 @@ extern "C" int b200slu_cast_colsum_bf16(const float* x, void* y, int M, int N, f
 extern "C" int b200slu_colsum_bf16(const void* dy, int M, int N, long long ld, float* out_accum, void* stream) {
   B2_CHECK_ARG(M > 0 && N > 0 && ld % 8 == 0 && ld >= ((N + 7) / 8) * 8, "colsum: bad shape M=%d N=%d ld=%lld", M, N, ld);
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((N + 255) / 256, 1);
-  int gy = (M + 31) / 32;
-  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  dim3 grid((N + CS_COLS - 1) / CS_COLS, 1);
+  int gy = (M + CS_ROWS * CS_U - 1) / (CS_ROWS * CS_U);
+  const int cap = (colsum_blocks_per_sm() * b2_num_sms() + grid.x - 1) / grid.x;
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 2.0 * M * N);
-  colsum_kernel<<<grid, 256, 0, st>>>((const bf16*)dy, M, N, ld, out_accum);
+  colsum_kernel<<<grid, 512, 0, st>>>((const bf16*)dy, M, N, ld, out_accum);
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -269,12 +254,12 @@ extern "C" int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, i
                                     float* dv_accum, void* stream) {
   B2_CHECK_ARG(M > 0 && d % 8 == 0 && lddq % 8 == 0, "pos_bias_bwd: d and lddq must be multiples of 8");
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((d + 255) / 256, 1);
-  int gy = (M + 63) / 64;
-  const int cap = (4 * b2_num_sms() + grid.x - 1) / grid.x;
+  dim3 grid((d + CS_COLS - 1) / CS_COLS, 1);
+  int gy = (M + CS_ROWS * 4 - 1) / (CS_ROWS * 4);
+  const int cap = (b2_num_sms() + grid.x - 1) / grid.x;  // one 512-thread block per SM
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * d);
-  pos_bias_bwd_kernel<<<grid, 256, 0, st>>>((const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum, dv_accum);
+  pos_bias_bwd_kernel<<<grid, 512, 0, st>>>((const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum, dv_accum);
   B2_LAUNCH_CHECK();
   return 0;
 }

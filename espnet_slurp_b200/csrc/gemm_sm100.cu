@@ -69,6 +69,31 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+// CTA-pair form: the data lands in this CTA's shared memory, the transaction bytes are signalled on a barrier that
+// may live in the peer (leader) CTA -- bar is a shared::cluster address.
+__device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cta address -> shared::cluster address of the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release;\n\tbarrier.cluster.wait.acquire;" ::: "memory");
+}
 // Bulk tensor stores (shared -> global) of one staged box; the .add form is the split-K reduction.
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map), "r"(src),
@@ -101,6 +126,21 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// CTA-pair MMA (M = 256: 128 rows per CTA; each CTA supplies half of B's N rows) -- issued by the leader CTA only.
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+// ... and its completion, signalled on the barrier at this offset in BOTH CTAs of the pair.
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
@@ -136,9 +176,9 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   return d;
 }
 // Instruction descriptor (cute::UMMA::InstrDescriptor): bf16 x bf16 -> f32, M=128, N=n.
-__host__ __device__ constexpr uint32_t make_idesc(int n, int a_mn_major, int b_mn_major) {
+__host__ __device__ constexpr uint32_t make_idesc(int n, int a_mn_major, int b_mn_major, int m = BM) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
-         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 struct EpiArgs {
@@ -166,23 +206,47 @@ enum : uint32_t {
   EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
   EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_GENERIC = 1u << 31
 };
-// Epilogue warps: 2 per TMEM lane quadrant (16 warps at 96 registers each measured slower than 8 at 168).
-__host__ __device__ constexpr int epi_warps(uint32_t) { return 8; }
-__host__ __device__ constexpr int num_threads(uint32_t ef) { return 64 + 32 * epi_warps(ef); }
+// Epilogue warps: 2 per TMEM lane quadrant for the register-heavy epilogues (168 registers each).
+// 16 warps (4 per quadrant, 64 columns each) halve the epilogue time of the light epilogues (bias-only: 6500 -> 3300
+// cycles per tile) but their 64 KB of staging costs a stage of the operand ring, and the ring depth is what bounds the
+// main loop (TMA round trip): measured 26.2 us against 23.9 us on the 9920 x 2048 x 512 forward.  Kept switchable.
+constexpr uint32_t EF_LIGHT = 0;  // EF_BIAS | EF_RELU | EF_F32 | EF_ACC | EF_AUX_MUL | EF_AUX_RELU | EF_ALPHA;
+__host__ __device__ constexpr int epi_warps(uint32_t ef, int bn) {
+  return (EF_LIGHT != 0 && bn == 256 && (ef & ~EF_LIGHT) == 0) ? 16 : 8;
+}
+__host__ __device__ constexpr int num_threads(uint32_t ef, int bn) { return 64 + 32 * epi_warps(ef, bn); }
 
-template <int BN, int STAGES>
+// Staging boxes per epilogue warp for the TMA stores.  Two when the kernel writes two outputs per box (saved
+// derivative), when it flushes a box every 32 columns (fp32 output, not the one-epilogue-per-long-K wgrad) or in the
+// generic kernel; otherwise one, and the shared memory goes to a deeper operand ring: the main loop is bound by the
+// TMA round trip (free stage -> L2 -> full stage ~ 2000+ cycles against 512 cycles of MMA per stage), so bytes in
+// flight are what buys tensor-pipe utilisation.
+__host__ __device__ constexpr int stg_bufs(uint32_t ef, int bn) {
+  return epi_warps(ef, bn) == 16 ? 1 : ((ef & (EF_DACT | EF_GENERIC)) || ((ef & EF_F32) && !(ef & EF_ACC))) ? 2 : 1;
+}
+template <int BN, int CG>
+__host__ __device__ constexpr int num_stages(uint32_t ef) {
+  // 227 KB minus staging, barriers and the bias slice, in stages of (128 + BN / CG) x 64 bf16
+  return (232448 - epi_warps(ef, BN) * stg_bufs(ef, BN) * 4096 - 2 * BN * 4 - 256) / ((BM + BN / CG) * BK * 2);
+}
+
+// CG = CTAs per MMA (tcgen05 cta_group): with CG = 2 a CTA pair owns a 256 x BN tile, each CTA holding its own 128
+// rows of A and HALF of B's rows -- 32 KB instead of 48 KB of L2 traffic per CTA and k-block, which is what bounds
+// the K = 512 .. 2048 GEMMs of the step (L2 -> SM tops out near 6300 B/clk chip-wide).
+template <int BN, int STAGES, int STGB, int CG, int EW = 8>
 struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (BN / CG) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int NUM_BARS = 2 * STAGES + 4;
-  // output staging for the TMA stores: per epilogue warp two boxes of 32 rows x 128 B (SWIZZLE_128B), 1024-B aligned
+  // output staging for the TMA stores: per epilogue warp STGB boxes of 32 rows x 128 B (SWIZZLE_128B), 1024-B aligned
   static constexpr int STG_OFF = STAGES * STAGE_BYTES;
-  static constexpr int STG_BYTES = 8 * 2 * 4096;
+  static constexpr int STG_BYTES = EW * STGB * 4096;
   static constexpr int BAR_OFF = STG_OFF + STG_BYTES;
-  static constexpr int BIAS_OFF = BAR_OFF + NUM_BARS * 8 + 16;       // per-tile bias slice, one segment per epilogue warp
-  static constexpr int BIAS_BYTES = 4 * BN * 4;                      // 4 lane quadrants x BN floats
-  static constexpr int TOTAL = BIAS_OFF + BIAS_BYTES + 1024;         // + alignment slack
+  static constexpr int BIAS_OFF = BAR_OFF + NUM_BARS * 8 + 16;       // per-tile bias slice, double-buffered by tile parity
+  static constexpr int BIAS_BYTES = 2 * BN * 4;
+  static constexpr int TOTAL = BIAS_OFF + BIAS_BYTES;                // the dynamic segment is declared 1024-B aligned
+  static_assert(TOTAL <= 232448, "shared memory budget");
 };
 
 // ----------------------------------------------------------------------------- fused epilogue
@@ -328,15 +392,20 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
 }
 
 // Persistent: grid = min(#work units, #SMs); unit u = (batch, tile, k-split), tiles n-fastest.
-template <int BN, int STAGES, bool TA, bool TB, uint32_t EF>
-__global__ void __launch_bounds__(num_threads(EF), 1)
+template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG>
+__global__ void __launch_bounds__(num_threads(EF, BN), 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_d, int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
                   int num_units, EpiArgs ep) {
-  using L = SmemLayout<BN, STAGES>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  constexpr int STGB = stg_bufs(EF, BN);
+  using L = SmemLayout<BN, STAGES, STGB, CG, epi_warps(EF, BN)>;
+  constexpr int TM = BM * CG;  // rows of one work unit (this CTA owns rows [cta_rank * BM, +BM) of it)
+  const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
+  const int first_unit = blockIdx.x / CG, unit_step = gridDim.x / CG;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
   const uint32_t sbase = smem_u32(smem);
+  if (sbase & 1023u) __trap();  // SWIZZLE_128B operand tiles and staging boxes need 1024-B alignment
   const uint32_t bar_full = sbase + L::BAR_OFF;
   const uint32_t bar_empty = bar_full + STAGES * 8;
   const uint32_t bar_acc_full = bar_empty + STAGES * 8;   // [2]
@@ -359,17 +428,24 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar_acc_full + b * 8, 1);
-      mbar_init(bar_acc_empty + b * 8, epi_warps(EF));
+      mbar_init(bar_acc_empty + b * 8, epi_warps(EF, BN) * CG);  // CG = 2: both CTAs' epilogue warps release the leader
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) {  // TMEM: two accumulator buffers of BN fp32 columns x 128 lanes
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  if (warp == 1) {  // TMEM: two accumulator buffers of BN fp32 columns x 128 lanes (in each CTA of a pair)
+    if (CG == 1) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CG == 1) __syncthreads();
+  else cluster_sync_all();  // the peer's barriers are initialised before anything signals them
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   b2_pdl_wait();  // barrier init / TMEM allocation / descriptor prefetch overlapped the predecessor; its data is needed from here on
@@ -378,7 +454,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     // ===================== TMA producer =====================
     if (lane == 0) {
       int i = 0;  // running k-block counter (ring position)
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      for (int u = first_unit; u < num_units; u += unit_step) {
         const int batch = u / units_per_batch, r = u - batch * units_per_batch;
         const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
         const int tile = r / splits, sp = r - tile * splits;
@@ -393,22 +469,33 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           mbar_wait(bar_empty + s * 8, (it & 1) ^ 1);
           if (rec) ep.dbg_out[7] += clock64() - c0;  // producer: waiting for a free stage
           const uint32_t sa = sbase + s * L::STAGE_BYTES, sb = sa + L::A_BYTES;
-          const uint32_t fb = bar_full + s * 8;
-          if ((EF & EF_GENERIC) && (ep.debug & 4)) { mbar_arrive(fb); continue; }
-          mbar_expect_tx(fb, L::STAGE_BYTES);
+          // the full barrier of a pair lives in the leader CTA and counts the bytes of both CTAs' loads
+          const uint32_t fb = CG == 2 ? mapa_rank(bar_full + s * 8, 0) : bar_full + s * 8;
+          if ((EF & EF_GENERIC) && (ep.debug & 4)) {
+            if (cta_rank == 0) mbar_arrive(bar_full + s * 8);
+            continue;
+          }
+          if (cta_rank == 0) mbar_expect_tx(bar_full + s * 8, CG * L::STAGE_BYTES);
           const int k = (kb0 + kb) * BK;
+          const int arow = tile_m * TM + (int)cta_rank * BM;               // this CTA's rows of A
+          constexpr int BNL = BN / CG;                                     // ... and its share of B's rows
+          const int brow = tile_n * BN + (int)cta_rank * BNL;
+          auto load = [&](uint32_t dst, const CUtensorMap* m, int c0, int c1, int c2, int c3) {
+            if (CG == 2) tma_load_4d_pair(dst, m, fb, c0, c1, c2, c3);
+            else tma_load_4d(dst, m, fb, c0, c1, c2, c3);
+          };
           if (!TA) {
-            tma_load_4d(sa, &map_a, fb, k, tile_m * BM, abi, abo);   // box {64 k, 128 rows}
+            load(sa, &map_a, k, arow, abi, abo);   // box {64 k, 128 rows}
           } else {
             // box {64 mn, 64 k-rows}; one box per 64-wide MN atom
 #pragma unroll
-            for (int a = 0; a < BM / 64; ++a) tma_load_4d(sa + a * (64 * BK * 2), &map_a, fb, tile_m * BM + a * 64, k, abi, abo);
+            for (int a = 0; a < BM / 64; ++a) load(sa + a * (64 * BK * 2), &map_a, arow + a * 64, k, abi, abo);
           }
           if (!TB) {
-            tma_load_4d(sb, &map_b, fb, k, tile_n * BN, bbi, bbo);   // box {64 k, BN rows}
+            load(sb, &map_b, k, brow, bbi, bbo);   // box {64 k, BNL rows}
           } else {
 #pragma unroll
-            for (int b = 0; b < BN / 64; ++b) tma_load_4d(sb + b * (64 * BK * 2), &map_b, fb, tile_n * BN + b * 64, k, bbi, bbo);
+            for (int b = 0; b < BNL / 64; ++b) load(sb + b * (64 * BK * 2), &map_b, brow + b * 64, k, bbi, bbo);
           }
         }
       }
@@ -417,12 +504,12 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     // ===================== MMA issuer =====================
     // One lane runs the whole loop: a warp-wide poll + __syncwarp per k-block costs 14 % of the MMA rate
     // (tools/mma_rate2.cu: 146 vs 128 cycles per 128x256x16 MMA).
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(BN, TA, TB);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc(BN, TA, TB, TM);
       int i = 0, t = 0;
       const bool rec = (ep.debug & 16) && blockIdx.x == 0;
       long long w_full = 0, w_acc = 0, t_begin = rec ? clock64() : 0;
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
+      for (int u = first_unit; u < num_units; u += unit_step, ++t) {
         const int r = u % units_per_batch;
         const int sp = r % splits;
         const int kb0 = sp * kb_per_split;
@@ -446,10 +533,16 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             // MN-major: 64-element MN atoms (64*BK*2 B apart = LBO), 8-row K groups 1024 B apart (SBO).
             const uint64_t da = TA ? make_smem_desc(sa + kk * 2048, 64 * BK * 2, 1024) : make_smem_desc(sa + kk * 32, 16, 1024);
             const uint64_t db = TB ? make_smem_desc(sb + kk * 2048, 64 * BK * 2, 1024) : make_smem_desc(sb + kk * 32, 16, 1024);
-            umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0);
+            if (CG == 2) umma_bf16_pair(d_tmem, da, db, idesc, (kb | kk) != 0);
+            else umma_bf16(d_tmem, da, db, idesc, (kb | kk) != 0);
           }
-          umma_commit(bar_empty + s * 8);                          // frees the smem stage once these MMAs retire
-          if (kb == nkb - 1) umma_commit(bar_acc_full + buf * 8);  // accumulator complete
+          if (CG == 2) {
+            umma_commit_pair(bar_empty + s * 8);                          // both producers get their stage back
+            if (kb == nkb - 1) umma_commit_pair(bar_acc_full + buf * 8);  // both CTAs' epilogues
+          } else {
+            umma_commit(bar_empty + s * 8);                          // frees the smem stage once these MMAs retire
+            if (kb == nkb - 1) umma_commit(bar_acc_full + buf * 8);  // accumulator complete
+          }
         }
       }
       if (rec) {
@@ -464,14 +557,14 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   } else {
     // ===================== epilogue (8 warps: 4 lane quadrants x 2 column halves) =====================
     constexpr uint32_t EFC = EF;
-    constexpr int CGROUPS = epi_warps(EF) / 4;
+    constexpr int CGROUPS = epi_warps(EF, BN) / 4;
     constexpr int WCOLS = BN / CGROUPS;  // columns per warp
     constexpr int NPAIR = WCOLS / 32;    // pairs of 16-column slices per warp
     const int ew = warp - 2;
     const int lane_grp = warp & 3;       // TMEM lanes [32*lane_grp, +32) -- hardware rule: warp_id % 4
     const int cgrp = ew >> 2;            // columns [cgrp*WCOLS, +WCOLS) of the tile
-    float* bias_s = reinterpret_cast<float*>(smem + L::BIAS_OFF) + (lane_grp * CGROUPS + cgrp) * WCOLS;
-    const uint32_t stg0 = sbase + L::STG_OFF + ew * 8192, stg1 = stg0 + 4096;
+    float* const bias_base = reinterpret_cast<float*>(smem + L::BIAS_OFF) + cgrp * WCOLS;
+    const uint32_t stg0 = sbase + L::STG_OFF + ew * (STGB * 4096), stg1 = stg0 + (STGB - 1) * 4096;
     B2DropKey dk = {0ull, 0u, 1.f};
     if (((EFC & EF_GENERIC) ? ep.flags : EFC) & EF_DROP) dk = dropout_key(ep.drop);
     const float alpha = ep.alpha;
@@ -479,13 +572,13 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     const int debug = (EFC & EF_GENERIC) ? ep.debug : 0;
     int t = 0;
     uint32_t nflush = 0;  // boxes of the main output flushed so far by this warp (selects the staging buffer)
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x, ++t) {
+    for (int u = first_unit; u < num_units; u += unit_step, ++t) {
       const int batch = u / units_per_batch, r = u - batch * units_per_batch;
       const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
       const int tile = r / splits, sp = r - tile * splits;
       const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
       const int buf = t & 1;
-      const int row0 = tile_m * BM + lane_grp * 32, row = row0 + lane;
+      const int row0 = tile_m * TM + (int)cta_rank * BM + lane_grp * 32, row = row0 + lane;
       const bool row_ok = row < M;
       const int colw = tile_n * BN + cgrp * WCOLS;
       // split-K: bias / residual belong to the first split only
@@ -499,13 +592,18 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       er.e0 = (unsigned long long)row * (unsigned long long)N;
       // this warp's bias slice -> shared memory and the first slice's operands -> registers, both before the wait
       // for the accumulator so their latency hides behind the MMAs of the tile
-      if (F & EF_BIAS) {
-        __syncwarp();  // the previous tile's reads of bias_s are done
-        for (int c = lane; c < WCOLS; c += 32) bias_s[c] = (colw + c < N) ? bias[colw + c] : 0.f;
+      // The four warps of a column half share one bias slice (tile parity selects the buffer; the named barrier
+      // below keeps the four within one tile of each other, so buffer t&1 is no longer read when tile t+2 fills it).
+      const float* bias_s = bias_base + (t & 1) * BN;
+      const bool has_bias = (ep.flags & EF_BIAS) != 0;  // uniform over the CTA's tiles (F drops it on later k-splits)
+      if (((EFC & EF_GENERIC) || (EFC & EF_BIAS)) && has_bias) {
+        static_assert(WCOLS == 128 || WCOLS == 64, "bias staging assumes 4 warps x 32 lanes cover the half tile");
+        const int c = lane_grp * 32 + lane;
+        if (c < WCOLS) bias_base[(t & 1) * BN + c] = (colw + c < N) ? bias[colw + c] : 0.f;
       }
       EpiPre pa, pb;
       if (!(EFC & EF_GENERIC) && row_ok) epi_prefetch<EFC>(rtf, er, colw, N, pa);
-      if (F & EF_BIAS) __syncwarp();
+      if (((EFC & EF_GENERIC) || (EFC & EF_BIAS)) && has_bias) asm volatile("bar.sync %0, 128;" ::"r"(1 + cgrp) : "memory");
       const bool rec = (ep.debug & 16) && blockIdx.x == 0 && ew == 0 && lane == 0;
       long long c0 = rec ? clock64() : 0;
       mbar_wait(bar_acc_full + buf * 8, (t >> 1) & 1);
@@ -523,12 +621,12 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         // A box of the main output spans 4 slices (bf16, 64 columns) or 2 slices (fp32, 32 columns).
         const bool box_start = (F & EF_F32) ? true : ((cp & 1) == 0);
         const bool box_end = (F & EF_F32) ? true : ((cp & 1) == 1);
-        const uint32_t so = two_out ? stg0 : ((nflush & 1) ? stg1 : stg0);
+        const uint32_t so = (two_out || STGB == 1) ? stg0 : ((nflush & 1) ? stg1 : stg0);
         long long q0 = rec ? clock64() : 0;
         if (box_start) {
           // the bulk store that last read this staging box must have finished reading it
           if (lane == 0) {
-            if (two_out) bulk_wait_read<0>();
+            if (two_out || STGB == 1) bulk_wait_read<0>();
             else bulk_wait_read<1>();
           }
           __syncwarp();
@@ -568,16 +666,21 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       }
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_acc_empty + buf * 8);
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cluster(mapa_rank(bar_acc_empty + buf * 8, 0));
+        else mbar_arrive(bar_acc_empty + buf * 8);
+      }
       if (rec) ep.dbg_out[6] += clock64() - c0;  // epilogue warp 0: busy cycles (dbg_out[5] = waiting for accumulators)
     }
     if (lane == 0) bulk_wait_read<0>();  // the staging boxes are no longer being read when the CTA exits
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CG == 1) __syncthreads();
+  else cluster_sync_all();  // neither CTA's shared memory / TMEM goes away while the other may still touch it
   if (warp == 1) {
     tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN) : "memory");
+    if (CG == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN) : "memory");
   }
 }
 
@@ -626,20 +729,21 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return 0;
 }
 
-template <int BN, int STAGES, bool TA, bool TB, uint32_t EF>
+template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md, int M, int N, int K, int nbatch, int batch_inner, int splits,
            int kb_per, const EpiArgs& ep, cudaStream_t st) {
-  using L = SmemLayout<BN, STAGES>;
-  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF>;
+  using L = SmemLayout<BN, STAGES, stg_bufs(EF, BN), CG, epi_warps(EF, BN)>;
+  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF, CG>;
   static bool configured = false;
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     configured = true;
   }
-  const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BM - 1) / BM;
+  const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BM * CG - 1) / (BM * CG);
   const long long units = (long long)tiles_n * tiles_m * splits * nbatch;
   B2_CHECK_ARG(units < (1LL << 30), "gemm: too many work units (%lld)", units);
-  const int grid = units < b2_num_sms() ? (int)units : b2_num_sms();
+  const int slots = b2_num_sms() / CG;  // CTAs (CG = 1) or CTA pairs (CG = 2: one pair per TPC)
+  const int grid = (units < slots ? (int)units : slots) * CG;
   EpiArgs epl = ep;
   static long long* dbg_buf = nullptr;
   if (ep.debug & 16) {
@@ -647,17 +751,36 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 12 * sizeof(long long), st));
     epl.dbg_out = dbg_buf;
   }
-  B2_CUDA(b2_launch(kern, dim3(grid), dim3(num_threads(EF)), (size_t)L::TOTAL, st, ma, mb, mc, md, M, N, K, tiles_n,
-                    tiles_n * tiles_m, batch_inner, splits, kb_per, (int)units, epl));
+  if (CG == 1) {
+    B2_CUDA(b2_launch(kern, dim3(grid), dim3(num_threads(EF, BN)), (size_t)L::TOTAL, st, ma, mb, mc, md, M, N, K, tiles_n,
+                      tiles_n * tiles_m, batch_inner, splits, kb_per, (int)units, epl));
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(num_threads(EF, BN));
+    cfg.dynamicSmemBytes = (size_t)L::TOTAL;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = b2_pdl_enabled() ? 2 : 1;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, md, M, N, K, tiles_n, tiles_n * tiles_m, batch_inner, splits, kb_per,
+                               (int)units, epl));
+  }
   if (ep.debug & 16) {
     long long h[12];
     B2_CUDA(cudaStreamSynchronize(st));
     B2_CUDA(cudaMemcpy(h, dbg_buf, sizeof(h), cudaMemcpyDeviceToHost));
     fprintf(stderr,
-            "[gemm dbg] M=%d N=%d K=%d BN=%d TA=%d TB=%d splits=%d grid=%d | CTA0: tiles=%lld kblocks=%lld mma_loop=%lld cyc "
+            "[gemm dbg] M=%d N=%d K=%d BN=%d CG=%d TA=%d TB=%d splits=%d grid=%d | CTA0: tiles=%lld kblocks=%lld mma_loop=%lld cyc "
             "(wait operands %lld, wait accumulator %lld) | epi warp0: wait acc %lld, busy %lld [staging free %lld, tmem wait %lld, "
             "slices %lld, flush %lld] | producer wait stage %lld | EF=%u\n",
-            M, N, K, BN, (int)TA, (int)TB, splits, grid, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[8], h[9], h[10], h[11], h[7],
+            M, N, K, BN, CG, (int)TA, (int)TB, splits, grid, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[8], h[9], h[10], h[11], h[7],
             (unsigned)EF);
   }
   return 0;
@@ -741,32 +864,37 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   //  * every tile adds its epilogue / pipeline turn-around;
   //  * the persistent grid runs ceil(units / SMs) waves, each as long as its longest unit.
   //  Split-K only for accumulating outputs (wgrad: K = B*T is long, the output is small).
-  int bn = 128, splits = 1;
+  //  * a CTA pair (cta_group::2, 256 x 256 tile) loads 32 KB instead of 48 KB per CTA and k-block and its ring is 5-6
+  //    stages deep: measured 8 % faster per k-block once K >= 1024 (long main loops), slower below (the pair's
+  //    cross-CTA barrier latencies are paid per tile); unbatched GEMMs only.
+  int bn = 128, splits = 1, cg = 1;
   {
+    static const int force_bn = getenv("B200SLU_GEMM_BN") ? atoi(getenv("B200SLU_GEMM_BN")) : 0;  // tuning experiments only
+    static const int force_cg = getenv("B200SLU_GEMM_CG") ? atoi(getenv("B200SLU_GEMM_CG")) : 0;
     const long long sms = b2_num_sms();
-    const long long tm = (M + BM - 1) / BM;
     double best = 1e300;
-    for (int cand = 0; cand < 2; ++cand) {
-      const int cbn = cand == 0 ? 128 : 256;
+    for (int cand = 0; cand < 3; ++cand) {
+      const int cbn = cand == 0 ? 128 : 256, ccg = cand == 2 ? 2 : 1;
       if (cbn == 256 && N < 256) continue;
+      if (ccg == 2 && (nbatch != 1 || M <= BM || (force_cg != 2 && num_kb / (ep.accumulate ? 8 : 1) < 16))) continue;
+      if ((force_bn == 128 || (force_bn == 256 && N >= 256)) && cbn != force_bn) continue;
+      if (force_cg != 0 && cbn == 256 && ccg != force_cg && !(force_cg == 2 && (nbatch != 1 || M <= BM))) continue;
+      const long long tm = (M + BM * ccg - 1) / (BM * ccg);
       const long long tiles = tm * ((N + cbn - 1) / cbn) * nbatch;
-      const double w = cbn == 256 ? 1.15 : 1.0, c = cbn == 256 ? 4.0 : 2.0;
+      const long long slots = sms / ccg;
+      const double w = ccg == 2 ? 1.05 : cbn == 256 ? 1.15 : 1.0, c = cbn == 256 ? 4.0 : 2.0;
       const int max_s = ep.accumulate ? max(1, num_kb / 4) : 1;
       for (int sp = 1; sp <= max_s && sp <= 64; ++sp) {
         const int kbs = (num_kb + sp - 1) / sp;
-        const long long waves = (tiles * sp + sms - 1) / sms;
+        const long long waves = (tiles * sp + slots - 1) / slots;
         const double cost = (double)waves * (kbs * w + c);
         if (cost < best * 0.999) {
           best = cost;
           bn = cbn;
+          cg = ccg;
           splits = sp;
         }
       }
-    }
-    static const int force_bn = getenv("B200SLU_GEMM_BN") ? atoi(getenv("B200SLU_GEMM_BN")) : 0;  // tuning experiments only
-    if (force_bn == 128 || (force_bn == 256 && N >= 256)) {
-      if (force_bn != bn) splits = 1;
-      bn = force_bn;
     }
   }
   const int kb_per = (num_kb + splits - 1) / splits;
@@ -780,7 +908,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   else
     B2_TRY(make_map(&ma, g->A, K, M, g->lda, nbi, g->a_stride_inner, nbo, g->a_stride_outer, 64, BK));
   if (!g->trans_b)
-    B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, bn));
+    B2_TRY(make_map(&mb, g->B, N, K, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, BK, bn / cg));
   else
     B2_TRY(make_map(&mb, g->B, K, N, g->ldb, nbi, g->b_stride_inner, nbo, g->b_stride_outer, 64, BK));
   // output boxes: 32 rows x 128 bytes, one per epilogue warp and flush
@@ -792,7 +920,12 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   else
     md = mc;
   // Specialised epilogues for the hot GEMMs of the train step; anything else runs the generic kernel.
-#define B2_L(BN_, ST_, TA_, TB_, EF_) return launch<BN_, ST_, TA_, TB_, EF_>(ma, mb, mc, md, M, N, K, nbatch, nbi, splits, kb_per, ep, st)
+#define B2_ARGS ma, mb, mc, md, M, N, K, nbatch, nbi, splits, kb_per, ep, st
+#define B2_L(BN_, ST_, TA_, TB_, EF_)                                                          \
+  do {                                                                                         \
+    if (BN_ == 256 && cg == 2) return launch<256, num_stages<256, 2>(EF_), TA_, TB_, EF_, 2>(B2_ARGS); \
+    return launch<BN_, num_stages<BN_, 1>(EF_), TA_, TB_, EF_, 1>(B2_ARGS);                     \
+  } while (0)
 #define B2_CASE(BN_, ST_, TA_, TB_, EF_) \
   if (ep.flags == (EF_)) B2_L(BN_, ST_, TA_, TB_, (EF_))
   const bool dbg_generic = (ep.debug & ~16) != 0;
@@ -850,6 +983,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   B2_L(128, 4, true, false, EF_GENERIC);
 #undef B2_CASE
 #undef B2_L
+#undef B2_ARGS
 }
 
 extern "C" int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epilogue, void* stream) {

@@ -7,6 +7,8 @@
 // emit bf16 and/or fp32, and the backward fuses (a) the residual-path gradient add and (b) the
 // bf16 "branch gradient" alpha*dropout(dx) that the next dgrad GEMM consumes.
 // Memory-bound: algorithmic bytes fwd = M*D*(4 + 2|4), bwd = M*D*(dy + 4 + 4 [+4] [+2]).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -68,7 +70,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x
 }
 
 template <int NG, bool DY_F32>
-__global__ void __launch_bounds__(256) ln_bwd_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
+__global__ void __launch_bounds__(NG <= 2 ? 512 : 256) ln_bwd_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
                                                      const float* __restrict__ gamma, const float* __restrict__ stats,
                                                      const float* __restrict__ dx_add, int M, int D, float* __restrict__ dx,
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -150,9 +152,21 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const void* __restrict__ dy
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    atomicAdd(dgamma + i, sm[i]);
-    atomicAdd(dbeta + i, sm[D + i]);
+  // Same-address atomics from different SMs retire serially (tens of ns each): one 16-byte vector atomic per four
+  // columns and block, and as few, fat blocks as keep the loads in flight (host side).  Summing the block partials
+  // across a thread-block cluster through DSMEM first was measured slower (59 us against 45 us: the cluster's
+  // co-scheduling and its two cluster barriers cost more than the atomics they save).
+  const bool vec4 = (((uintptr_t)dgamma | (uintptr_t)dbeta) & 15) == 0 && (D & 3) == 0;
+  if (vec4) {
+    for (int i = threadIdx.x; i < D / 4; i += blockDim.x) {
+      atomicAdd(reinterpret_cast<float4*>(dgamma) + i, reinterpret_cast<const float4*>(sm)[i]);
+      atomicAdd(reinterpret_cast<float4*>(dbeta) + i, reinterpret_cast<const float4*>(sm + D)[i]);
+    }
+  } else {
+    for (int i = threadIdx.x; i < D; i += blockDim.x) {
+      atomicAdd(dgamma + i, sm[i]);
+      atomicAdd(dbeta + i, sm[D + i]);
+    }
   }
 }
 
@@ -181,7 +195,11 @@ extern "C" int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float*
                                      void* stream) {
   B2_CHECK_ARG(M > 0 && D > 0 && D % 8 == 0 && D <= 2048, "layernorm_bwd: need D %% 8 == 0 and D <= 2048 (M=%d D=%d)", M, D);
   cudaStream_t st = (cudaStream_t)stream;
-  const int grid = b2_grid_for((long long)M * 32, 256, 4);
+  // one 512-thread block per SM (16 row-warps, <= 128 registers): the block count is the atomic count per column
+  static const int bps = getenv("B200SLU_LN_BPS") ? atoi(getenv("B200SLU_LN_BPS")) : 1;  // tuning knobs
+  static const int thr = getenv("B200SLU_LN_THREADS") ? atoi(getenv("B200SLU_LN_THREADS")) : 512;
+  const int threads = D <= 512 ? thr : 256;  // wider rows hold more registers per lane
+  const int grid = b2_grid_for((long long)M * 32, threads, (bps > 0 ? bps : 1) * (512 / threads));
   B2Dropout drop = b2_make_drop(drop_p, seed, site);
   const size_t smem = 2 * (size_t)D * sizeof(float);
   B2_SCOPE(FAM_LN, st, 0,
@@ -189,10 +207,10 @@ extern "C" int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float*
 #define LN_B(NG)                                                                                                         \
   do {                                                                                                                   \
     if (dy_is_f32)                                                                                                       \
-      ln_bwd_kernel<NG, true><<<grid, 256, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta,             \
+      ln_bwd_kernel<NG, true><<<grid, threads, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta,             \
                                                        (bf16*)g_bf16, g_alpha, drop);                                    \
     else                                                                                                                 \
-      ln_bwd_kernel<NG, false><<<grid, 256, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta,            \
+      ln_bwd_kernel<NG, false><<<grid, threads, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta,            \
                                                         (bf16*)g_bf16, g_alpha, drop);                                   \
   } while (0)
   if (D <= 256) LN_B(1);

@@ -91,6 +91,37 @@ def test_gemm_epilogue_bias_swish_residual():
     assert abs(frac - 0.75) < 0.01
 
 
+@pytest.mark.parametrize("M,N,K", [(1000, 512, 2048), (333, 600, 1024), (4100, 768, 4608)])
+def test_gemm_cta_pair_epilogues(M, N, K):
+    """K >= 1024, unbatched: the host picks the CTA-pair kernel (cta_group::2, 256-row tiles).  Ragged M / N edges,
+    every majorness, bias + residual (fp32), saved-derivative product, split-K accumulation."""
+    ops = _ops()
+    g = torch.Generator(device="cuda").manual_seed(M + 3 * N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    w = (torch.randn(N, K, device="cuda", generator=g) * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    res = torch.randn(M, N, device="cuda", generator=g)
+    y = ref_mm(a, w, False)
+    scale = y.abs().max().item()
+    out = ops.gemm(a, w, bias=bias, residual=res, alpha=0.5, out_dtype=torch.float32)
+    assert (out - (res + 0.5 * (y + bias))).abs().max().item() < 2e-4 * scale + 1e-4
+    outb = ops.gemm(a, w, bias=bias, act="relu")
+    assert (outb.float() - torch.relu(y + bias)).abs().max().item() < 0.01 * scale
+    # dgrad: dX[M,K'] = dY[M,N'] W[N',K'] with N' playing K (long), mul epilogue
+    wt = (torch.randn(K, N, device="cuda", generator=g) * 0.05).bfloat16()       # [K_contract, N_out]
+    d = torch.rand(M, N, device="cuda", generator=g).bfloat16()
+    o2 = ops.gemm(a, wt, trans_b=True, act_grad_input=d, act_grad="mul")
+    want2 = (a.float() @ wt.float()) * d.float()
+    assert (o2.float() - want2).abs().max().item() < 0.02 * want2.abs().max().item()
+    # wgrad: dW[N, K2] += dY^T X over M rows (contraction = M)
+    x2 = torch.randn(M, 512, device="cuda", generator=g).bfloat16()
+    dy = torch.randn(M, N, device="cuda", generator=g).bfloat16()
+    acc = torch.ones(N, 512, device="cuda")
+    ops.gemm(dy, x2, trans=True, out=acc, accumulate=True)
+    want3 = 1 + dy.float().t() @ x2.float()
+    assert (acc - want3).abs().max().item() < 1e-4 * want3.abs().max().item() + 1e-3
+
+
 def test_gemm_dropout_statistics_and_determinism():
     ops = _ops()
     M, N, K = 2048, 512, 64
