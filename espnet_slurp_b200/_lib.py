@@ -80,7 +80,8 @@ _SIGNATURES = {
     "b200slu_bn_swish_fwd": [_P, _P, _P, _P, _L, _I, _P, _P],
     "b200slu_bn_swish_bwd": [_P, _P, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P],
     "b200slu_conv1_fwd": [_P, _P, _P, _I, _I, _I, _I, _P, _P],
-    "b200slu_conv1_bwd": [_P, _P, _I, _I, _I, _I, _P, _P, _P],
+    "b200slu_conv1_bwd_workspace_size": [_I, _I, _I, _I],
+    "b200slu_conv1_bwd": [_P, _P, _I, _I, _I, _I, _P, _P, _P, _L, _P],
     "b200slu_im2col3x3s2": [_P, _I, _I, _I, _I, _P, _P],
     "b200slu_col2im3x3s2_relu": [_P, _P, _I, _I, _I, _I, _P, _P],
     "b200slu_ctc_workspace_size": [_I, _I, _I],
@@ -100,6 +101,7 @@ _RESTYPES = {
     "b200slu_prof_reset": None,
     "b200slu_prof_enable_timing": None,
     "b200slu_ctc_workspace_size": C.c_longlong,
+    "b200slu_conv1_bwd_workspace_size": C.c_longlong,
     "b200slu_lsm_workspace_size": C.c_longlong,
     "b200slu_rel_shift_index": C.c_longlong,
 }

@@ -288,6 +288,9 @@ __device__ __forceinline__ void colsum_block_reduce(float (&acc)[8], float (*red
   }
 }
 
+// gemm_sm100.cu: the GEMM behind b200slu_gemm_bf16_ex, for kernels families that contain one (subsample.cu)
+int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_t st);
+
 static inline int b2_grid_for(long long work_items, int threads, int per_sm = 8) {
   long long blocks = (work_items + threads - 1) / threads;
   long long cap = (long long)b2_num_sms() * per_sm;

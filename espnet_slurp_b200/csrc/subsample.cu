@@ -51,123 +51,128 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
 }
 
 // dW[c][k] += sum_{b,t,f} dh1[b,t,f,c] * x[b,2t+kh,2f+kw] ; db[c] += sum dh1   (dh1 already ReLU-masked)
-// grid (ceil(T1 / ROWS), B)
-constexpr int ROWS = 16;
-__global__ void __launch_bounds__(256) conv1_bwd_kernel(const bf16* __restrict__ dh1, const float* __restrict__ x, int Tin, int F,
-                                                        int C, int T1, int F1, float* __restrict__ dw, float* __restrict__ db) {
-  extern __shared__ float sm[];
-  float* sacc = sm;             // [C][10]
-  float* sx = sm + 10 * C;      // [3][F]
-  const int b = blockIdx.y, tbeg = blockIdx.x * ROWS, tend = min(T1, tbeg + ROWS);
-  const int ncg = C >> 3;
-  const int cg = threadIdx.x % ncg, pl = threadIdx.x / ncg, npl = blockDim.x / ncg;
-  for (int i = threadIdx.x; i < 10 * C; i += blockDim.x) sacc[i] = 0.f;
-  float acc[10][8];
+// A reduction over B*T1*F1 pixels of a [pixels, C] matrix against 9 taps (+ a column of ones for the bias): a
+// wgrad-shaped GEMM  [C, 16] = dh1^T [C, pixels] . patches [pixels, 16]  on the tensor cores (split-K over the
+// pixels), bound by reading dh1 once from HBM.  (The CUDA-core version was bound by 80 FMAs per 16 bytes of dh1 and by
+// 2560 blocks x 5120 same-address atomics: 1.6 ms against 0.25 ms of HBM time at 128 utterances.)
+// patches[p, k] = bf16(x[b, 2t+kh, 2f+kw]) for k = kh*3+kw < 9, 1 for k = 9, 0 for k = 10..15.
+__global__ void __launch_bounds__(256) conv1_patch_kernel(const float* __restrict__ x, int B, int Tin, int F, int T1, int F1,
+                                                          bf16* __restrict__ patches) {
+  const long long total = (long long)B * T1 * F1;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (long long)gridDim.x * blockDim.x) {
+    const int f = (int)(p % F1);
+    const long long bt = p / F1;
+    const int t = (int)(bt % T1);
+    const long long b = bt / T1;
+    const float* xp = x + (b * Tin + 2 * t) * F + 2 * f;
+    float v[16];
 #pragma unroll
-  for (int k = 0; k < 10; ++k)
+    for (int k = 0; k < 9; ++k) v[k] = xp[(k / 3) * F + (k % 3)];
+    v[9] = 1.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
-  for (int t = tbeg; t < tend; ++t) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < 3 * F; i += blockDim.x) {
-      const int kh = i / F, f = i - kh * F;
-      sx[i] = x[((long long)b * Tin + 2 * t + kh) * F + f];
-    }
-    __syncthreads();
-    if (pl < npl) {
-      constexpr int U = 5;  // independent 16-byte loads in flight per thread (the kernel is latency-bound otherwise)
-      for (int f0 = pl; f0 < F1; f0 += npl * U) {
-        uint4 raw[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int f = f0 + u * npl;
-          raw[u] = f < F1 ? *reinterpret_cast<const uint4*>(dh1 + (((long long)b * T1 + t) * F1 + f) * C + cg * 8)
-                          : make_uint4(0u, 0u, 0u, 0u);
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int f = min(f0 + u * npl, F1 - 1);  // out-of-range slots carry zeros
-          const float2 g0 = unpack_bf16x2(raw[u].x), g1 = unpack_bf16x2(raw[u].y), g2 = unpack_bf16x2(raw[u].z),
-                       g3 = unpack_bf16x2(raw[u].w);
-          const float g[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
-#pragma unroll
-          for (int k = 0; k < 9; ++k) {
-            const float xv = sx[(k / 3) * F + 2 * f + (k % 3)];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[k][j] += g[j] * xv;
-          }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[9][j] += g[j];
-        }
-      }
-    }
+    for (int k = 10; k < 16; ++k) v[k] = 0.f;
+    store8_bf16(patches + p * 16, *reinterpret_cast<float (*)[8]>(&v[0]));
+    store8_bf16(patches + p * 16 + 8, *reinterpret_cast<float (*)[8]>(&v[8]));
   }
-  if (pl < npl) {
-#pragma unroll
-    for (int k = 0; k < 10; ++k)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(&sacc[(cg * 8 + j) * 10 + k], acc[k][j]);
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 10 * C; i += blockDim.x) {
+}
+
+// dw[c*9 + k] += acc[c][k] (k < 9), db[c] += acc[c][9]
+__global__ void __launch_bounds__(256) conv1_wgrad_scatter_kernel(const float* __restrict__ acc, int C, float* __restrict__ dw,
+                                                                  float* __restrict__ db) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < C * 10) {
     const int c = i / 10, k = i - c * 10;
-    if (k < 9) atomicAdd(dw + c * 9 + k, sacc[i]);
-    else atomicAdd(db + c, sacc[i]);
+    if (k < 9) dw[c * 9 + k] += acc[c * 16 + k];
+    else db[c] += acc[c * 16 + 9];
   }
 }
 
 // col[(b,t,f), (kh,kw,c)] = h1[b, 2t+kh, 2f+kw, c]
+// grid (T2, B): a block copies one output row (b, t): F2 pixels x 9 taps x C channels.  A warp takes (pixel, tap)
+// pairs -- each a contiguous C-channel run on both sides -- four at a time, so every lane has >= 4 independent 16-byte
+// loads in flight and the index arithmetic is per warp, not per element.
 __global__ void __launch_bounds__(256) im2col_kernel(const bf16* __restrict__ h1, int B, int T1, int F1, int C, int T2, int F2,
                                                      bf16* __restrict__ col) {
-  const int ncg = C >> 3;
-  const long long total = (long long)B * T2 * F2 * 9 * ncg;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % ncg);
-    long long r = i / ncg;
-    const int k = (int)(r % 9);
-    r /= 9;  // output pixel (b, t, f)
-    const int f = (int)(r % F2);
-    const long long bt = r / F2;
-    const int t = (int)(bt % T2);
-    const long long b = bt / T2;
-    const int kh = k / 3, kw = k - kh * 3;
-    const uint4 v = *reinterpret_cast<const uint4*>(h1 + (((b * T1 + 2 * t + kh) * F1) + 2 * f + kw) * C + cg * 8);
-    *reinterpret_cast<uint4*>(col + (r * 9 + k) * C + cg * 8) = v;
+  const int t = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int ncg = C >> 3, npairs = F2 * 9;
+  const bf16* src_row = h1 + ((long long)b * T1 + 2 * t) * F1 * C;
+  bf16* dst_row = col + ((long long)b * T2 + t) * F2 * 9 * C;
+  constexpr int U = 4;
+  for (int p0 = warp; p0 < npairs; p0 += nwarps * U) {
+    const bf16* src[U];
+    bf16* dst[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int pk = min(p0 + u * nwarps, npairs - 1);
+      const int f = pk / 9, k = pk - f * 9, kh = k / 3, kw = k - kh * 3;
+      src[u] = src_row + ((long long)kh * F1 + 2 * f + kw) * C;
+      dst[u] = dst_row + (long long)pk * C;
+    }
+    for (int cg = lane; cg < ncg; cg += 32) {
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) v[u] = *reinterpret_cast<const uint4*>(src[u] + cg * 8);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (p0 + u * nwarps < npairs) *reinterpret_cast<uint4*>(dst[u] + cg * 8) = v[u];
+    }
   }
 }
 
 // dh1[b,r,g,c] = (h1 > 0) * sum over taps (kh,kw) with 2t+kh = r, 2f+kw = g of dcol[(b,t,f),(kh,kw,c)]
+// grid (T1, B): a block produces one row (b, r) of dh1; a warp takes pixels g.  Which taps contribute is uniform per
+// block (kh) and per warp (kw); all (<= 4) tap loads and the ReLU-mask load of a lane are issued before any use.
 __global__ void __launch_bounds__(256) col2im_relu_kernel(const bf16* __restrict__ dcol, const bf16* __restrict__ h1, int B, int T1,
                                                           int F1, int C, int T2, int F2, bf16* __restrict__ dh1) {
+  const int r = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int ncg = C >> 3;
-  const long long total = (long long)B * T1 * F1 * ncg;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % ncg);
-    long long p = i / ncg;
-    const int g = (int)(p % F1);
-    const long long br = p / F1;
-    const int r = (int)(br % T1);
-    const long long b = br / T1;
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  // rows of dcol that feed this h1 row: r = 2t + kh
+  // r even -> kh in {0, 2}, r odd -> kh = 1: two fixed slots with validity flags
+  const int kh0 = (r & 1) ? 1 : 0;
+  const int khs[2] = {kh0, 2}, ts[2] = {(r - kh0) >> 1, (r - 2) >> 1};
+  const bool okt[2] = {ts[0] < T2, !(r & 1) && r >= 2 && ts[1] < T2};
+  const long long row = ((long long)b * T1 + r) * F1;
+  for (int g = warp; g < F1; g += nwarps) {
+    // taps along f: g even -> kw in {0, 2}, g odd -> kw = 1; slot q = 2 * a + (0 | 1) with a the kh slot
+    const int kw0 = (g & 1) ? 1 : 0, f0 = (g - kw0) >> 1, f1 = (g - 2) >> 1;
+    const bool okf0 = f0 < F2, okf1 = !(g & 1) && g >= 2 && f1 < F2;
+    const bf16* src[4];
+    bool ok[4];
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int tt = r - kh;
-      if (tt < 0 || (tt & 1) || (tt >> 1) >= T2) continue;
-#pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int ff = g - kw;
-        if (ff < 0 || (ff & 1) || (ff >> 1) >= F2) continue;
-        float v[8];
-        load8_bf16(dcol + ((((b * T2 + (tt >> 1)) * F2 + (ff >> 1)) * 9) + kh * 3 + kw) * C + cg * 8, v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += v[j];
-      }
+    for (int a = 0; a < 2; ++a) {
+      const long long base = ((long long)b * T2 + ts[a]) * F2;
+      src[2 * a] = dcol + ((base + f0) * 9 + khs[a] * 3 + kw0) * C;
+      src[2 * a + 1] = dcol + ((base + f1) * 9 + khs[a] * 3 + 2) * C;
+      ok[2 * a] = okt[a] && okf0;
+      ok[2 * a + 1] = okt[a] && okf1;
     }
-    float h[8];
-    load8_bf16(h1 + p * C + cg * 8, h);
+    for (int cg = lane; cg < ncg; cg += 32) {
+      uint4 v[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = h[j] > 0.f ? acc[j] : 0.f;
-    store8_bf16(dh1 + p * C + cg * 8, acc);
+      for (int q = 0; q < 4; ++q) v[q] = ok[q] ? *reinterpret_cast<const uint4*>(src[q] + cg * 8) : make_uint4(0u, 0u, 0u, 0u);
+      const uint4 hv = *reinterpret_cast<const uint4*>(h1 + (row + g) * C + cg * 8);
+      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t w4[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 p2 = unpack_bf16x2(w4[e]);
+          acc[2 * e] += p2.x;
+          acc[2 * e + 1] += p2.y;
+        }
+      }
+      const uint32_t h4[4] = {hv.x, hv.y, hv.z, hv.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 hh = unpack_bf16x2(h4[e]);
+        if (!(hh.x > 0.f)) acc[2 * e] = 0.f;
+        if (!(hh.y > 0.f)) acc[2 * e + 1] = 0.f;
+      }
+      store8_bf16(dh1 + (row + g) * C + cg * 8, acc);
+    }
   }
 }
 
@@ -186,16 +191,49 @@ extern "C" int b200slu_conv1_fwd(const float* x, const float* w, const float* bi
   return 0;
 }
 
+extern "C" long long b200slu_conv1_bwd_workspace_size(int B, int Tin, int F, int C) {
+  if (B <= 0 || Tin < 3 || F < 3 || C <= 0) return 0;
+  const long long T1 = (Tin - 3) / 2 + 1, F1 = (F - 3) / 2 + 1;
+  return B * T1 * F1 * 16 * 2 + (long long)C * 16 * 4 + 256;
+}
+
 extern "C" int b200slu_conv1_bwd(const void* dh1, const float* x, int B, int Tin, int F, int C, float* dw_accum, float* db_accum,
-                                 void* stream) {
+                                 void* workspace, long long workspace_bytes, void* stream) {
   B2_CHECK_ARG(B > 0 && Tin >= 3 && F >= 3 && C % 8 == 0 && C <= 2048 && B <= 65535, "conv1_bwd: bad shape");
   const int T1 = (Tin - 3) / 2 + 1, F1 = (F - 3) / 2 + 1;
+  const long long pixels = (long long)B * T1 * F1;
+  B2_CHECK_ARG(workspace != nullptr && ((uintptr_t)workspace % 256) == 0 &&
+                   workspace_bytes >= b200slu_conv1_bwd_workspace_size(B, Tin, F, C),
+               "conv1_bwd: workspace of b200slu_conv1_bwd_workspace_size() bytes, 256-byte aligned, required");
+  B2_CHECK_ARG(pixels < (1LL << 31), "conv1_bwd: too many pixels");
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t smem = (size_t)(10 * C + 3 * F) * sizeof(float);
-  B2_CHECK_ARG(smem <= 48 * 1024, "conv1_bwd: C too large");
-  B2_SCOPE(FAM_SUBSAMPLE, st, 20.0 * B * T1 * F1 * C, 2.0 * B * T1 * F1 * C);
-  conv1_bwd_kernel<<<dim3((T1 + ROWS - 1) / ROWS, B), 256, smem, st>>>((const bf16*)dh1, x, Tin, F, C, T1, F1, dw_accum,
-                                                                       db_accum);
+  bf16* patches = (bf16*)workspace;
+  float* acc = (float*)((char*)workspace + ((pixels * 32 + 255) / 256) * 256);
+  {
+    B2_SCOPE(FAM_SUBSAMPLE, st, 0, 4.0 * B * Tin * F + 32.0 * pixels);
+    conv1_patch_kernel<<<b2_grid_for(pixels, 256, 8), 256, 0, st>>>(x, B, Tin, F, T1, F1, patches);
+    B2_LAUNCH_CHECK();
+    B2_CUDA(cudaMemsetAsync(acc, 0, (size_t)C * 16 * sizeof(float), st));
+  }
+  b200slu_gemm_t g = {};
+  g.trans_a = 1;
+  g.trans_b = 1;
+  g.M = C;
+  g.N = 16;
+  g.K = (int)pixels;
+  g.A = dh1;
+  g.lda = C;
+  g.B = patches;
+  g.ldb = 16;
+  g.C = acc;
+  g.ldc = 16;
+  g.batch_inner = g.batch_outer = 1;
+  b200slu_epilogue_t e = {};
+  e.alpha = 1.f;
+  e.out_f32 = 1;
+  e.accumulate = 1;
+  B2_TRY(b2_gemm_ex(&g, &e, st));
+  conv1_wgrad_scatter_kernel<<<(C * 10 + 255) / 256, 256, 0, st>>>(acc, C, dw_accum, db_accum);
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -206,7 +244,8 @@ extern "C" int b200slu_im2col3x3s2(const void* h1, int B, int T1, int F1, int C,
   cudaStream_t st = (cudaStream_t)stream;
   const long long items = (long long)B * T2 * F2 * 9 * (C >> 3);
   B2_SCOPE(FAM_SUBSAMPLE, st, 0, 32.0 * items);
-  im2col_kernel<<<b2_grid_for(items, 256, 16), 256, 0, st>>>((const bf16*)h1, B, T1, F1, C, T2, F2, (bf16*)col);
+  B2_CHECK_ARG(B <= 65535, "im2col: B too large");
+  im2col_kernel<<<dim3(T2, B), 256, 0, st>>>((const bf16*)h1, B, T1, F1, C, T2, F2, (bf16*)col);
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -217,8 +256,8 @@ extern "C" int b200slu_col2im3x3s2_relu(const void* dcol, const void* h1, int B,
   cudaStream_t st = (cudaStream_t)stream;
   const long long items = (long long)B * T1 * F1 * (C >> 3);
   B2_SCOPE(FAM_SUBSAMPLE, st, 0, 16.0 * B * T2 * F2 * 9 * (C >> 3) + 32.0 * items);
-  col2im_relu_kernel<<<b2_grid_for(items, 256, 16), 256, 0, st>>>((const bf16*)dcol, (const bf16*)h1, B, T1, F1, C, T2, F2,
-                                                                  (bf16*)dh1);
+  B2_CHECK_ARG(B <= 65535, "col2im: B too large");
+  col2im_relu_kernel<<<dim3(T1, B), 256, 0, st>>>((const bf16*)dcol, (const bf16*)h1, B, T1, F1, C, T2, F2, (bf16*)dh1);
   B2_LAUNCH_CHECK();
   return 0;
 }

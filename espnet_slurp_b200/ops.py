@@ -310,7 +310,10 @@ def conv1_fwd(x, w, bias):
 def conv1_bwd(dh1, x, dw, db):
     B, Tin, F = x.shape
     Cc = dh1.shape[-1]
-    check(_lib.lib().b200slu_conv1_bwd(ptr(dh1), ptr(x), B, Tin, F, Cc, ptr(dw), ptr(db), stream_ptr()), "conv1_bwd")
+    nbytes = int(_lib.lib().b200slu_conv1_bwd_workspace_size(B, Tin, F, Cc))
+    ws = torch.empty(nbytes, device=x.device, dtype=torch.uint8)   # bf16 patches [pixels,16] + fp32 accumulator [C,16]
+    check(_lib.lib().b200slu_conv1_bwd(ptr(dh1), ptr(x), B, Tin, F, Cc, ptr(dw), ptr(db), ptr(ws), nbytes, stream_ptr()),
+          "conv1_bwd")
 
 
 def im2col(h1):

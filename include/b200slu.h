@@ -180,8 +180,11 @@ int b200slu_bn_swish_bwd(const void* dy, const void* x, const float* mean_rstd, 
 
 /* ---- K3: Conv2dSubsampling (subsampling.py:53-87) ---------------------------------------------- */
 int b200slu_conv1_fwd(const float* x, const float* w, const float* bias, int B, int Tin, int F, int C, void* h1, void* stream);
+/* conv1 weight / bias gradient as a tensor-core reduction over the B*T1*F1 pixels; the 3x3 input patches (bf16) and the
+ * [C,16] fp32 accumulator live in a caller-provided workspace (256-byte aligned). */
+long long b200slu_conv1_bwd_workspace_size(int B, int Tin, int F, int C);
 int b200slu_conv1_bwd(const void* dh1, const float* x, int B, int Tin, int F, int C, float* dw_accum, float* db_accum,
-                      void* stream);
+                      void* workspace, long long workspace_bytes, void* stream);
 int b200slu_im2col3x3s2(const void* h1, int B, int T1, int F1, int C, void* col, void* stream);
 int b200slu_col2im3x3s2_relu(const void* dcol, const void* h1, int B, int T1, int F1, int C, void* dh1, void* stream);
 

@@ -291,7 +291,7 @@ def conv1_bwd(dh1, x, dw, db):
     C = dh1.shape[-1]
     wl = torch.zeros(C, 1, 3, 3, requires_grad=True)
     bl = torch.zeros(C, requires_grad=True)
-    y = F.conv2d(x[:, None], wl, bl, stride=2)
+    y = F.conv2d(x.bfloat16().float()[:, None], wl, bl, stride=2)   # the wgrad GEMM reads bf16 input patches
     y.backward(dh1.float().permute(0, 3, 1, 2))
     dw += wl.grad.reshape(dw.shape)
     db += bl.grad
