@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x
 }
 
 template <int NG, bool DY_F32>
-__global__ void __launch_bounds__(NG <= 2 ? 512 : 256) ln_bwd_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
+__global__ void __launch_bounds__(NG <= 2 ? 384 : 256, 1) ln_bwd_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
                                                      const float* __restrict__ gamma, const float* __restrict__ stats,
                                                      const float* __restrict__ dx_add, int M, int D, float* __restrict__ dx,
                                                      float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -91,6 +91,15 @@ __global__ void __launch_bounds__(NG <= 2 ? 512 : 256) ln_bwd_kernel(const void*
        row += (long long)gridDim.x * warps_per_block) {
     const float mean = stats[row * 2], rstd = stats[row * 2 + 1];
     float xh[NG][8], dyg[NG][8];
+    // the residual-path gradient is fetched with the row's other loads (one memory round trip per row, not two)
+    float addv[NG <= 2 ? NG : 1][8];
+    if (NG <= 2 && dx_add != nullptr) {
+#pragma unroll
+      for (int i = 0; i < (NG <= 2 ? NG : 1); ++i) {
+        const int g = lane + 32 * i;
+        if (g < ngroups) load8_f32(dx_add + row * D + g * 8, addv[i]);
+      }
+    }
     float c1 = 0.f, c2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NG; ++i) {
@@ -124,10 +133,15 @@ __global__ void __launch_bounds__(NG <= 2 ? 512 : 256) ln_bwd_kernel(const void*
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rstd * (dyg[i][j] - c1 - xh[i][j] * c2);
         if (dx_add != nullptr) {
-          float a[8];
-          load8_f32(dx_add + row * D + g * 8, a);
+          if (NG <= 2) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] += a[j];
+            for (int j = 0; j < 8; ++j) o[j] += addv[NG <= 2 ? i : 0][j];
+          } else {
+            float a[8];
+            load8_f32(dx_add + row * D + g * 8, a);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] += a[j];
+          }
         }
         store8_f32(dx + row * D + g * 8, o);
         if (g16 != nullptr) {
@@ -197,9 +211,9 @@ extern "C" int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float*
   cudaStream_t st = (cudaStream_t)stream;
   // one 512-thread block per SM (16 row-warps, <= 128 registers): the block count is the atomic count per column
   static const int bps = getenv("B200SLU_LN_BPS") ? atoi(getenv("B200SLU_LN_BPS")) : 1;  // tuning knobs
-  static const int thr = getenv("B200SLU_LN_THREADS") ? atoi(getenv("B200SLU_LN_THREADS")) : 512;
+  static const int thr = getenv("B200SLU_LN_THREADS") ? atoi(getenv("B200SLU_LN_THREADS")) : 384;
   const int threads = D <= 512 ? thr : 256;  // wider rows hold more registers per lane
-  const int grid = b2_grid_for((long long)M * 32, threads, (bps > 0 ? bps : 1) * (512 / threads));
+  const int grid = b2_grid_for((long long)M * 32, threads, (bps > 0 ? bps : 1) * (threads <= 256 ? 2 : 1));
   B2Dropout drop = b2_make_drop(drop_p, seed, site);
   const size_t smem = 2 * (size_t)D * sizeof(float);
   B2_SCOPE(FAM_LN, st, 0,
