@@ -133,7 +133,7 @@ class Clocks(threading.Thread):
 
 
 # ----------------------------------------------------------------------------------------------------- CPU reference arm
-def cpu_step_time(args, cfg, n_steps, warmup, batch):
+def cpu_step_time(args, cfg, n_steps, warmup, batch, min_seconds=0.0):
     """The reference's CPU path for the same step: oracle/model.py (CPU restatement pinned against the unmodified
     reference's goldens) fwd + autograd bwd in fp32 on all host cores.  Returns (audio-sec/sec, seconds/step, cores)."""
     from oracle import model as om
@@ -145,7 +145,12 @@ def cpu_step_time(args, cfg, n_steps, warmup, batch):
     wav, lens, text, tl = make_batch(batch, cfg.vocab, 1234, args.min_sec, args.max_sec)
     audio = float(lens.sum()) / FS
     times = []
-    for i in range(warmup + n_steps):
+    i = -1
+    while True:
+        i += 1
+        # n_steps timed steps, and then more until the timed sample is at least min_seconds long (bounded)
+        if i >= warmup + n_steps and (sum(times) >= min_seconds or len(times) >= 40):
+            break
         t0 = time.perf_counter()
         feats, flens = om.frontend_logmel(wav, lens, mel)
         draws = specaug_draws(flens, feats.shape[1])
@@ -160,7 +165,7 @@ def cpu_step_time(args, cfg, n_steps, warmup, batch):
         if i >= warmup:
             times.append(dt)
     sec = sum(times) / len(times)
-    return audio / sec, sec, torch.get_num_threads(), audio
+    return audio / sec, sec, torch.get_num_threads(), audio, len(times)
 
 
 # ----------------------------------------------------------------------------------------------------- GPU arm
@@ -356,12 +361,20 @@ def run_ours(args):
         pass
     tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)  # kernels are timed inside a long step -> sustained figure
     roof = None
+    traffic = None
+    try:  # DRAM bytes per GEMM launch from the committed ncu capture of this command (tools/ncu_step_summary.py)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_step_ncu_summary.json")))
+        if tj.get("batch_per_gpu") == args.batch:
+            traffic = tj["gemm"]["dram_bytes_per_launch"]
+    except Exception:
+        pass
     if "gemm_tcgen05" in fams and fams["gemm_tcgen05"]["ms_per_step"] > 0:
         g = fams["gemm_tcgen05"]
         ach = g["flops_per_step"] / (g["ms_per_step"] * 1e-3) / 1e12
         roof = {"kernel": "gemm_bf16_tcgen05 (all GEMM launches of one step)", "bound": "tensor", "achieved": round(ach, 1),
                 "peak": tf_peak, "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback",
-                "unit": "TFLOP/s", "frac": round(ach / tf_peak, 4), "traffic": None,
+                "unit": "TFLOP/s", "frac": round(ach / tf_peak, 4), "traffic": traffic,
+                "algorithmic_bytes_per_launch": round(g["bytes_per_step"] / g["launches_per_step"], 1),
                 "launches_per_step": g["launches_per_step"], "avg_launch_us": round(1e3 * g["ms_per_step"] / g["launches_per_step"], 2),
                 "share_of_step_device_time": round(g["ms_per_step"] / sum(f["ms_per_step"] for f in fams.values()), 3)}
     line = {
@@ -381,10 +394,11 @@ def run_ours(args):
         "clocks": clk, "loss": loss_val, "roofline": roof, "families": fams,
     }
     if not args.no_cpu_baseline and world >= 1:
-        v, sec, cores, audio_cpu = cpu_step_time(args, cfg, 1, 1, args.cpu_batch)
+        v, sec, cores, audio_cpu, nt = cpu_step_time(args, cfg, 2, 1, args.cpu_batch, min_seconds=12.0)
         line["cpu_baseline"] = {"value": round(v, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
-                                "sample": f"1 warm-up + 1 timed fwd+bwd step of the same model on {args.cpu_batch} utterances "
-                                          f"({audio_cpu:.1f} audio-s), oracle/model.py fp32, {sec:.1f} s/step"}
+                                "sample": f"1 warm-up + {nt} timed fwd+bwd steps ({nt * sec:.1f} s of CPU work) of the same model on "
+                                          f"{args.cpu_batch} utterances per step ({audio_cpu:.1f} audio-s), oracle/model.py fp32 "
+                                          f"on {cores} torch threads, {sec:.2f} s/step"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -397,11 +411,11 @@ def run_reference(args):
     cfg = build_cfg(args)
     # size the per-step sample so that warmup + steps stay within a few minutes of host time
     t0 = time.perf_counter()
-    v, sec, cores, audio = cpu_step_time(args, cfg, 1, 0, 2)
+    v, sec, cores, audio, _ = cpu_step_time(args, cfg, 1, 0, 2)
     per_utt = sec / 2
     budget = 150.0
     b = int(max(1, min(args.cpu_batch, budget / max(1e-3, per_utt * (args.steps + args.warmup)))))
-    v, sec, cores, audio = cpu_step_time(args, cfg, args.steps, args.warmup, b)
+    v, sec, cores, audio, _ = cpu_step_time(args, cfg, args.steps, args.warmup, b)
     line = {"impl": "reference", "metric": "audio-sec/sec train throughput, SLURP Conformer", "value": round(v, 2),
             "unit": "audio-sec/sec", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(sec * 1e3, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",

@@ -164,6 +164,182 @@ __global__ void __launch_bounds__(256) softmax_bwd_kernel(const float* __restric
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Short rows (the SLURP utterances give T ~ 155 keys = 20 groups of 8): LPR lanes own a row and a warp works on
+// 32 / LPR rows at once, so all 32 lanes are busy (20 of 32 with a warp per row), a warp has 4x the bytes in flight
+// and the row reductions are log2(LPR) shuffle steps.  Modes NONE and LATEST (LEGACY keeps the warp-per-row kernels).
+template <int LPR>
+__device__ __forceinline__ float seg_max(float v) {
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+template <int LPR>
+__device__ __forceinline__ float seg_sum(float v) {
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <int LPR, int NGL>
+__global__ void __launch_bounds__(256) softmax_fwd_rows_kernel(const float* __restrict__ ac, const float* __restrict__ bd,
+                                                               SmArgs a, bf16* __restrict__ p, bf16* __restrict__ pd,
+                                                               B2Dropout drop) {
+  constexpr int RPW = 32 / LPR;
+  const int lane = threadIdx.x & 31, sub = lane / LPR, l = lane % LPR, wpb = blockDim.x >> 5;
+  const long long rows = (long long)a.H * a.B * a.Tq;
+  const int ngroups = (int)(a.ld_p >> 3);
+  B2DropKey dk = {0ull, 0u, 1.f};
+  if (drop.p > 0.f) dk = dropout_key(drop);
+  for (long long rw = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); rw * RPW < rows; rw += (long long)gridDim.x * wpb) {
+    const long long r = rw * RPW + sub;
+    const bool live = r < rows;
+    const long long hb = live ? r / a.Tq : 0;
+    const int i = live ? (int)(r - hb * a.Tq) : 0;
+    int nvalid = 0;
+    if (live) {
+      nvalid = a.lens != nullptr ? a.lens[(int)(hb % a.B)] : a.Tk;
+      nvalid = min(nvalid, a.Tk);
+      if (a.causal) nvalid = min(nvalid, i + 1);
+    }
+    const float* bdr = (a.mode == B200SLU_RELPOS_LATEST) ? bd + (hb * a.Tq + i) * a.ld_bd + (a.Tq - 1 - i) : nullptr;
+    float s[NGL][8];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int k = 0; k < NGL; ++k) {
+      const int g = l + LPR * k;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s[k][e] = -INFINITY;
+      if (g < ngroups && g * 8 < nvalid) {
+        float v[8], t[8];
+        load8_f32(ac + r * a.ld_ac + g * 8, v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) t[e] = (bdr != nullptr && g * 8 + e < nvalid) ? bdr[g * 8 + e] : 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          if (g * 8 + e < nvalid) {
+            s[k][e] = (v[e] + t[e]) * a.scale;
+            mx = fmaxf(mx, s[k][e]);
+          }
+        }
+      }
+    }
+    mx = seg_max<LPR>(mx);
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < NGL; ++k) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        s[k][e] = (s[k][e] == -INFINITY) ? 0.f : __expf(s[k][e] - mx);
+        sum += s[k][e];
+      }
+    }
+    sum = seg_sum<LPR>(sum);
+    const float inv = sum > 0.f ? 1.f / sum : 0.f;
+    if (live) {
+#pragma unroll
+      for (int k = 0; k < NGL; ++k) {
+        const int g = l + LPR * k;
+        if (g < ngroups) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) s[k][e] *= inv;
+          store8_bf16(p + r * a.ld_p + g * 8, s[k]);
+          if (pd != p) {
+            if (drop.p > 0.f) {
+              const uint32_t keep = dropout_keep8(dk, (unsigned long long)(r * a.ld_p + g * 8) >> 3);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) s[k][e] = ((keep >> e) & 1u) ? s[k][e] * dk.inv : 0.f;
+            }
+            store8_bf16(pd + r * a.ld_p + g * 8, s[k]);
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int LPR, int NGL>
+__global__ void __launch_bounds__(256) softmax_bwd_rows_kernel(const float* __restrict__ dpd, const bf16* __restrict__ p,
+                                                               SmArgs a, bf16* __restrict__ dac, bf16* __restrict__ dbd,
+                                                               B2Dropout drop) {
+  extern __shared__ float sm[];  // [warps][32 / LPR][ld_p] staged d(score) rows for the un-shift scatter
+  constexpr int RPW = 32 / LPR;
+  const int lane = threadIdx.x & 31, sub = lane / LPR, l = lane % LPR, w = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const long long rows = (long long)a.H * a.B * a.Tq;
+  const int ngroups = (int)(a.ld_p >> 3);
+  const int T = a.Tq;
+  float* row_sm = sm + ((size_t)w * RPW + sub) * a.ld_p;
+  B2DropKey dk = {0ull, 0u, 1.f};
+  if (drop.p > 0.f) dk = dropout_key(drop);
+  for (long long rw = (long long)blockIdx.x * wpb + w; rw * RPW < rows; rw += (long long)gridDim.x * wpb) {
+    const long long r = rw * RPW + sub;
+    const bool live = r < rows;
+    float pv[NGL][8], dp[NGL][8];
+    float dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < NGL; ++k) {
+      const int g = l + LPR * k;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) pv[k][e] = dp[k][e] = 0.f;
+      if (live && g < ngroups) {
+        load8_bf16(p + r * a.ld_p + g * 8, pv[k]);
+        load8_f32(dpd + r * a.ld_p + g * 8, dp[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < NGL; ++k) {
+      const int g = l + LPR * k;
+      if (live && g < ngroups) {
+        if (drop.p > 0.f) {
+          const uint32_t keep = dropout_keep8(dk, (unsigned long long)(r * a.ld_p + g * 8) >> 3);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dp[k][e] = ((keep >> e) & 1u) ? dp[k][e] * dk.inv : 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          if (g * 8 + e >= a.Tk) dp[k][e] = 0.f;  // padding columns of dpd are unspecified
+          dot += dp[k][e] * pv[k][e];
+        }
+      }
+    }
+    dot = seg_sum<LPR>(dot);
+#pragma unroll
+    for (int k = 0; k < NGL; ++k) {
+      const int g = l + LPR * k;
+      if (live && g < ngroups) {
+        float ds[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ds[e] = pv[k][e] * (dp[k][e] - dot) * a.scale;
+        if (dbd != nullptr) {
+          float4* dst = reinterpret_cast<float4*>(row_sm + g * 8);
+          dst[0] = make_float4(ds[0], ds[1], ds[2], ds[3]);
+          dst[1] = make_float4(ds[4], ds[5], ds[6], ds[7]);
+        }
+        store8_bf16(dac + r * a.ld_p + g * 8, ds);
+      }
+    }
+    if (dbd != nullptr) {  // latest: dbd[i, n] = ds[i, n - (T-1-i)] inside the band, 0 outside; 8 outputs per lane and store
+      __syncwarp();
+      if (live) {
+        const long long hb = r / a.Tq;
+        const int i = (int)(r - hb * a.Tq);
+        bf16* own = dbd + (hb * T + i) * a.ld_bd;
+        const int lo = T - 1 - i;
+        for (int gq = l; gq < (int)(a.ld_bd >> 3); gq += LPR) {
+          float o[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int j = gq * 8 + e - lo;
+            o[e] = (j >= 0 && j < T) ? row_sm[j] : 0.f;
+          }
+          store8_bf16(own + gq * 8, o);
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
 int check(const SmArgs& a) {
   B2_CHECK_ARG(a.H > 0 && a.B > 0 && a.Tq > 0 && a.Tk > 0, "softmax: empty problem");
   B2_CHECK_ARG(a.ld_p % 8 == 0 && a.ld_p >= a.Tk && a.ld_ac >= a.ld_p && a.ld_ac % 4 == 0,
@@ -193,6 +369,17 @@ extern "C" int b200slu_softmax_fwd(const float* ac, long long ld_ac, const float
   const int grid = b2_grid_for(rows * 32, 256, 8);
   B2_SCOPE(FAM_ATTN, st, 0, (double)rows * Tk * (4.0 + (relpos_mode ? 4.0 : 0.0) + 2.0 + (drop_p > 0.f ? 2.0 : 0.0)));
   B2Dropout drop = b2_make_drop(drop_p, seed, site);
+#define SM_FR(LPR, NGL)                                                                                            \
+  softmax_fwd_rows_kernel<LPR, NGL><<<b2_grid_for((rows + 32 / LPR - 1) / (32 / LPR) * 32, 256, 8), 256, 0, st>>>( \
+      ac, bd, a, (bf16*)p, (bf16*)p_drop, drop)
+  if (relpos_mode != B200SLU_RELPOS_LEGACY && ld_p <= 512) {
+    if (ld_p <= 192) SM_FR(8, 3);
+    else if (ld_p <= 256) SM_FR(8, 4);
+    else SM_FR(16, 4);
+    B2_LAUNCH_CHECK();
+    return 0;
+  }
+#undef SM_FR
 #define SM_F(NG) softmax_fwd_kernel<NG><<<grid, 256, 0, st>>>(ac, bd, a, (bf16*)p, (bf16*)p_drop, drop)
   if (ld_p <= 256) SM_F(1);
   else if (ld_p <= 512) SM_F(2);
@@ -217,6 +404,20 @@ extern "C" int b200slu_softmax_bwd(const float* dp_drop, const void* p, long lon
   const int grid = b2_grid_for(rows * 32, threads, 4);
   B2_SCOPE(FAM_ATTN, st, 0, (double)rows * Tk * (4.0 + 2.0 + 2.0) + (d_bd ? 2.0 * rows * ld_bd : 0.0));
   B2Dropout drop = b2_make_drop(drop_p, seed, site);
+#define SM_BR(LPR, NGL)                                                                                                   \
+  do {                                                                                                                    \
+    const size_t smr = d_bd != nullptr ? (size_t)(threads / 32) * (32 / LPR) * ld_p * sizeof(float) : 0;                  \
+    softmax_bwd_rows_kernel<LPR, NGL><<<b2_grid_for((rows + 32 / LPR - 1) / (32 / LPR) * 32, threads, 4), threads, smr, st>>>( \
+        dp_drop, (const bf16*)p, a, (bf16*)d_ac, (bf16*)d_bd, drop);                                                      \
+  } while (0)
+  if (relpos_mode != B200SLU_RELPOS_LEGACY && ld_p <= 512) {
+    if (ld_p <= 192) SM_BR(8, 3);
+    else if (ld_p <= 256) SM_BR(8, 4);
+    else SM_BR(16, 4);
+    B2_LAUNCH_CHECK();
+    return 0;
+  }
+#undef SM_BR
 #define SM_B(NG)                                                                                                  \
   do {                                                                                                            \
     static bool cfg = false;                                                                                      \
