@@ -158,22 +158,42 @@ __device__ __forceinline__ B2DropKey dropout_key(const B2Dropout& d) {
   k.inv = 1.f / (1.f - d.p);
   return k;
 }
-// keep-mask (bit i set = keep) for elements [8*group, 8*group+8): 8 x 16-bit uniform lanes compared with p * 65536
+// 8 x 16-bit uniform lanes for elements [8*group, 8*group+8): ONE splitmix64 of the group counter plus one more
+// multiply-xorshift round for the second 64 bits (two full splitmix64 per group were ~40 % of the instructions of the
+// FFN w_1 forward epilogue, which is issue-bound).  Every kernel derives its decisions from these lanes, so forward and
+// backward of a site agree whichever form (bit mask / multipliers) they use.
+__device__ __forceinline__ void dropout_lanes8(const B2DropKey& k, unsigned long long group, uint32_t (&w)[4]) {
+  const unsigned long long z0 = splitmix64(k.key + group * 0x9E3779B97F4A7C15ull);
+  unsigned long long z1 = (z0 ^ (z0 >> 29)) * 0xD6E8FEB86659FD93ull;
+  z1 ^= z1 >> 32;
+  w[0] = (uint32_t)z0;
+  w[1] = (uint32_t)(z0 >> 32);
+  w[2] = (uint32_t)z1;
+  w[3] = (uint32_t)(z1 >> 32);
+}
+// keep-mask (bit i set = keep): lane >= p * 65536
 __device__ __forceinline__ uint32_t dropout_keep8(const B2DropKey& k, unsigned long long group) {
-  const unsigned long long c = k.key + (group << 1) * 0x9E3779B97F4A7C15ull;
-  const unsigned long long z0 = splitmix64(c), z1 = splitmix64(c + 0x9E3779B97F4A7C15ull);
+  uint32_t w[4];
+  dropout_lanes8(k, group, w);
   const uint32_t thr = k.thr;
-  const uint32_t a = (uint32_t)z0, b = (uint32_t)(z0 >> 32), e = (uint32_t)z1, f = (uint32_t)(z1 >> 32);
   uint32_t m = 0;
-  m |= ((a & 0xffffu) >= thr) << 0;
-  m |= ((a >> 16) >= thr) << 1;
-  m |= ((b & 0xffffu) >= thr) << 2;
-  m |= ((b >> 16) >= thr) << 3;
-  m |= ((e & 0xffffu) >= thr) << 4;
-  m |= ((e >> 16) >= thr) << 5;
-  m |= ((f & 0xffffu) >= thr) << 6;
-  m |= ((f >> 16) >= thr) << 7;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    m |= ((w[q] & 0xffffu) >= thr) << (2 * q);
+    m |= ((w[q] >> 16) >= thr) << (2 * q + 1);
+  }
   return m;
+}
+// the same decisions as multipliers: mul[i] = keep ? scale : 0
+__device__ __forceinline__ void dropout_mul8(const B2DropKey& k, unsigned long long group, float scale, float (&mul)[8]) {
+  uint32_t w[4];
+  dropout_lanes8(k, group, w);
+  const uint32_t thr = k.thr;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    mul[2 * q] = (w[q] & 0xffffu) >= thr ? scale : 0.f;
+    mul[2 * q + 1] = (w[q] >> 16) >= thr ? scale : 0.f;
+  }
 }
 __device__ __forceinline__ uint32_t dropout_keep8(const B2Dropout& d, unsigned long long group) {
   return dropout_keep8(dropout_key(d), group);

@@ -288,13 +288,22 @@ __device__ __forceinline__ void epi_math8(uint32_t rt_flags, const EpiArgs& ep, 
   }
   if (F & EF_DROP) {
     // alpha rides on the keep multiplier (the host clears EF_ALPHA when EF_DROP is set)
-    const uint32_t keep = dropout_keep8(dk, (e0 + (unsigned long long)col) >> 3);
-    const float mv = dk.inv * alpha;
+    float mul[8];
+    if (F & EF_DACT) {
+      dropout_mul8(dk, (e0 + (unsigned long long)col) >> 3, dk.inv, mul);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const bool kp = (keep >> j) & 1u;
-      v[j] *= kp ? mv : 0.f;
-      if (F & EF_DACT) d[j] *= kp ? dk.inv : 0.f;
+      for (int j = 0; j < 8; ++j) {
+        d[j] *= mul[j];
+        v[j] *= mul[j];
+      }
+      if (alpha != 1.f) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= alpha;
+      }
+    } else {
+      dropout_mul8(dk, (e0 + (unsigned long long)col) >> 3, dk.inv * alpha, mul);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] *= mul[j];
     }
   } else if (F & EF_ALPHA) {
 #pragma unroll
