@@ -210,24 +210,26 @@ enum : uint32_t {
 // 16 warps (4 per quadrant, 64 columns each) halve the epilogue time of the light epilogues (bias-only: 6500 -> 3300
 // cycles per tile) but their 64 KB of staging costs a stage of the operand ring, and the ring depth is what bounds the
 // main loop (TMA round trip): measured 26.2 us against 23.9 us on the 9920 x 2048 x 512 forward.  Kept switchable.
+// Also measured on the CTA-pair kernels (32 KB stages leave room for both): conv2 dgrad 1651 us with 16 warps against
+// 1530 us with 8.  Kept switchable.
 constexpr uint32_t EF_LIGHT = 0;  // EF_BIAS | EF_RELU | EF_F32 | EF_ACC | EF_AUX_MUL | EF_AUX_RELU | EF_ALPHA;
-__host__ __device__ constexpr int epi_warps(uint32_t ef, int bn) {
-  return (EF_LIGHT != 0 && bn == 256 && (ef & ~EF_LIGHT) == 0) ? 16 : 8;
+__host__ __device__ constexpr int epi_warps(uint32_t ef, int bn, int cg) {
+  return (EF_LIGHT != 0 && cg == 2 && bn == 256 && (ef & ~EF_LIGHT) == 0) ? 16 : 8;
 }
-__host__ __device__ constexpr int num_threads(uint32_t ef, int bn) { return 64 + 32 * epi_warps(ef, bn); }
+__host__ __device__ constexpr int num_threads(uint32_t ef, int bn, int cg) { return 64 + 32 * epi_warps(ef, bn, cg); }
 
 // Staging boxes per epilogue warp for the TMA stores.  Two when the kernel writes two outputs per box (saved
 // derivative), when it flushes a box every 32 columns (fp32 output, not the one-epilogue-per-long-K wgrad) or in the
 // generic kernel; otherwise one, and the shared memory goes to a deeper operand ring: the main loop is bound by the
 // TMA round trip (free stage -> L2 -> full stage ~ 2000+ cycles against 512 cycles of MMA per stage), so bytes in
 // flight are what buys tensor-pipe utilisation.
-__host__ __device__ constexpr int stg_bufs(uint32_t ef, int bn) {
-  return epi_warps(ef, bn) == 16 ? 1 : ((ef & (EF_DACT | EF_GENERIC)) || ((ef & EF_F32) && !(ef & EF_ACC))) ? 2 : 1;
+__host__ __device__ constexpr int stg_bufs(uint32_t ef, int bn, int cg) {
+  return epi_warps(ef, bn, cg) == 16 ? 1 : ((ef & (EF_DACT | EF_GENERIC)) || ((ef & EF_F32) && !(ef & EF_ACC))) ? 2 : 1;
 }
 template <int BN, int CG>
 __host__ __device__ constexpr int num_stages(uint32_t ef) {
   // 227 KB minus staging, barriers and the bias slice, in stages of (128 + BN / CG) x 64 bf16
-  return (232448 - epi_warps(ef, BN) * stg_bufs(ef, BN) * 4096 - 2 * BN * 4 - 256) / ((BM + BN / CG) * BK * 2);
+  return (232448 - epi_warps(ef, BN, CG) * stg_bufs(ef, BN, CG) * 4096 - 2 * BN * 4 - 256) / ((BM + BN / CG) * BK * 2);
 }
 
 // CG = CTAs per MMA (tcgen05 cta_group): with CG = 2 a CTA pair owns a 256 x BN tile, each CTA holding its own 128
@@ -402,12 +404,12 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
 
 // Persistent: grid = min(#work units, #SMs); unit u = (batch, tile, k-split), tiles n-fastest.
 template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG>
-__global__ void __launch_bounds__(num_threads(EF, BN), 1)
+__global__ void __launch_bounds__(num_threads(EF, BN, CG), 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_d, int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
                   int num_units, EpiArgs ep) {
-  constexpr int STGB = stg_bufs(EF, BN);
-  using L = SmemLayout<BN, STAGES, STGB, CG, epi_warps(EF, BN)>;
+  constexpr int STGB = stg_bufs(EF, BN, CG);
+  using L = SmemLayout<BN, STAGES, STGB, CG, epi_warps(EF, BN, CG)>;
   constexpr int TM = BM * CG;  // rows of one work unit (this CTA owns rows [cta_rank * BM, +BM) of it)
   const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
   const int first_unit = blockIdx.x / CG, unit_step = gridDim.x / CG;
@@ -437,7 +439,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar_acc_full + b * 8, 1);
-      mbar_init(bar_acc_empty + b * 8, epi_warps(EF, BN) * CG);  // CG = 2: both CTAs' epilogue warps release the leader
+      mbar_init(bar_acc_empty + b * 8, epi_warps(EF, BN, CG) * CG);  // CG = 2: both CTAs' epilogue warps release the leader
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -566,7 +568,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   } else {
     // ===================== epilogue (8 warps: 4 lane quadrants x 2 column halves) =====================
     constexpr uint32_t EFC = EF;
-    constexpr int CGROUPS = epi_warps(EF, BN) / 4;
+    constexpr int CGROUPS = epi_warps(EF, BN, CG) / 4;
     constexpr int WCOLS = BN / CGROUPS;  // columns per warp
     constexpr int NPAIR = WCOLS / 32;    // pairs of 16-column slices per warp
     const int ew = warp - 2;
@@ -741,7 +743,7 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
 template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md, int M, int N, int K, int nbatch, int batch_inner, int splits,
            int kb_per, const EpiArgs& ep, cudaStream_t st) {
-  using L = SmemLayout<BN, STAGES, stg_bufs(EF, BN), CG, epi_warps(EF, BN)>;
+  using L = SmemLayout<BN, STAGES, stg_bufs(EF, BN, CG), CG, epi_warps(EF, BN, CG)>;
   auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF, CG>;
   static bool configured = false;
   if (!configured) {
@@ -761,12 +763,12 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     epl.dbg_out = dbg_buf;
   }
   if (CG == 1) {
-    B2_CUDA(b2_launch(kern, dim3(grid), dim3(num_threads(EF, BN)), (size_t)L::TOTAL, st, ma, mb, mc, md, M, N, K, tiles_n,
+    B2_CUDA(b2_launch(kern, dim3(grid), dim3(num_threads(EF, BN, CG)), (size_t)L::TOTAL, st, ma, mb, mc, md, M, N, K, tiles_n,
                       tiles_n * tiles_m, batch_inner, splits, kb_per, (int)units, epl));
   } else {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(num_threads(EF, BN));
+    cfg.blockDim = dim3(num_threads(EF, BN, CG));
     cfg.dynamicSmemBytes = (size_t)L::TOTAL;
     cfg.stream = st;
     cudaLaunchAttribute attr[2];
@@ -885,7 +887,12 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     for (int cand = 0; cand < 3; ++cand) {
       const int cbn = cand == 0 ? 128 : 256, ccg = cand == 2 ? 2 : 1;
       if (cbn == 256 && N < 256) continue;
-      if (ccg == 2 && (nbatch != 1 || M <= BM || (force_cg != 2 && num_kb / (ep.accumulate ? 8 : 1) < 16))) continue;
+      // pairs pay off on long main loops, or when a pair runs so many tiles that its start-up / drain is amortised
+      // (conv2 dgrad, K = 512, 358 tiles per pair: 1530 us against 1697 us)
+      const long long pair_tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256);
+      if (ccg == 2 && (nbatch != 1 || M <= BM ||
+                       (force_cg != 2 && num_kb / (ep.accumulate ? 8 : 1) < 16 && pair_tiles < 32 * (sms / 2))))
+        continue;
       if ((force_bn == 128 || (force_bn == 256 && N >= 256)) && cbn != force_bn) continue;
       if (force_cg != 0 && cbn == 256 && ccg != force_cg && !(force_cg == 2 && (nbatch != 1 || M <= BM))) continue;
       const long long tm = (M + BM * ccg - 1) / (BM * ccg);
