@@ -882,11 +882,12 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   {
     static const int force_bn = getenv("B200SLU_GEMM_BN") ? atoi(getenv("B200SLU_GEMM_BN")) : 0;  // tuning experiments only
     static const int force_cg = getenv("B200SLU_GEMM_CG") ? atoi(getenv("B200SLU_GEMM_CG")) : 0;
+    static const int wide_min = getenv("B200SLU_GEMM_WIDE_MIN") ? atoi(getenv("B200SLU_GEMM_WIDE_MIN")) : 129;  // N in (128, 256): one wide tile beats 128 + a sliver
     const long long sms = b2_num_sms();
     double best = 1e300;
     for (int cand = 0; cand < 3; ++cand) {
       const int cbn = cand == 0 ? 128 : 256, ccg = cand == 2 ? 2 : 1;
-      if (cbn == 256 && N < 256) continue;
+      if (cbn == 256 && N < wide_min) continue;
       // pairs pay off on long main loops, or when a pair runs so many tiles that its start-up / drain is amortised
       // (conv2 dgrad, K = 512, 358 tiles per pair: 1530 us against 1697 us)
       const long long pair_tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256);
