@@ -117,7 +117,8 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
   extern __shared__ __align__(16) float dyn_smem[];
   float (*sg)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                             // glu halo tile  [TT+KMAX-1][CC]
   float (*sd)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + (TT + KMAX - 1) * CC);      // d_dw halo tile
-  float (*swg)[KMAX + 1] = reinterpret_cast<float (*)[KMAX + 1]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);  // dW partial (+ dbias)
+  // dW partial (+ dbias); rows padded to an odd stride so that the 32 channels of a warp hit 32 different banks
+  float (*swg)[KMAX + 2] = reinterpret_cast<float (*)[KMAX + 2]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);
   const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
   const int pad = (K - 1) / 2, nf = TT + K - 1;
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
     acc[k] = 0.f;
   }
   float accb = 0.f;
-  for (int it = threadIdx.x; it < CC * (KMAX + 1); it += blockDim.x) (&swg[0][0])[it] = 0.f;
+  for (int it = threadIdx.x; it < CC * (KMAX + 2); it += blockDim.x) (&swg[0][0])[it] = 0.f;
   for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
     const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
     __syncthreads();  // previous tile fully consumed
@@ -152,6 +153,15 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
       const int f0 = sub * 4 * FR + fr * FR;
       if (t0 + f0 >= T) break;
       float dg[FR], dv[FR];
+      // the GLU inputs of the thread's own frames (for d_a, d_gate) are fetched now; their latency hides under the taps
+      bf16 pa[FR], pg[FR];
+#pragma unroll
+      for (int o = 0; o < FR; ++o) {
+        const int t = min(t0 + f0 + o, T - 1);
+        const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
+        pa[o] = row[c];
+        pg[o] = row[C + c];
+      }
 #pragma unroll
       for (int o = 0; o < FR; ++o) {
         dg[o] = 0.f;
@@ -180,8 +190,7 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
       for (int o = 0; o < FR; ++o) {
         const int t = t0 + f0 + o;
         if (t < T) {
-          const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
-          const float a = __bfloat162float(row[c]), gt = __bfloat162float(row[C + c]);
+          const float a = __bfloat162float(pa[o]), gt = __bfloat162float(pg[o]);
           const float sgm = sigmoidf_(gt);
           bf16* drow = d_pw1 + ((long long)b * T + t) * (2 * C);
           drow[c] = __float2bfloat16(dg[o] * sgm);
@@ -223,22 +232,51 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sums, int C, float 
   if (blockIdx.x == 0 && threadIdx.x == 0 && num_batches != nullptr) *num_batches += 1;
 }
 
+// A thread owns one group of 8 channels (its BatchNorm constants live in registers, folded to one FMA per element) and
+// walks rows with BN_U independent 16-byte loads in flight; block = 64 channel groups x 4 row lanes, grid (C/512, rows).
+constexpr int BN_U = 4;
 __global__ void __launch_bounds__(256) bn_swish_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ mean_rstd,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            long long M, int C, bf16* __restrict__ y) {
-  const int gpr = C >> 3;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < M * gpr; i += (long long)gridDim.x * blockDim.x) {
-    const long long row = i / gpr;
-    const int c = (int)(i - row * gpr) * 8;
-    float v[8], mu[8], rs[8], ga[8], be[8];
-    load8_bf16(x + row * C + c, v);
+  const int cg = blockIdx.x * 64 + (threadIdx.x & 63), rl = threadIdx.x >> 6;
+  if (cg * 8 >= C) return;
+  const int c = cg * 8;
+  float sc[8], sh[8];
+  {
+    float mu[8], rs[8], ga[8], be[8];
     load8_f32(mean_rstd + c, mu);
     load8_f32(mean_rstd + C + c, rs);
     load8_f32(gamma + c, ga);
     load8_f32(beta + c, be);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = swishf_((v[j] - mu[j]) * rs[j] * ga[j] + be[j]);
-    store8_bf16(y + row * C + c, v);
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = rs[j] * ga[j];
+      sh[j] = be[j] - mu[j] * sc[j];
+    }
+  }
+  const long long step = (long long)gridDim.y * 4;
+  for (long long r0 = (long long)blockIdx.y * 4 + rl; r0 < M; r0 += BN_U * step) {
+    uint4 raw[BN_U];
+#pragma unroll
+    for (int u = 0; u < BN_U; ++u) {
+      const long long r = r0 + u * step;
+      raw[u] = r < M ? *reinterpret_cast<const uint4*>(x + r * C + c) : make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < BN_U; ++u) {
+      const long long r = r0 + u * step;
+      if (r < M) {
+        const uint32_t w4[4] = {raw[u].x, raw[u].y, raw[u].z, raw[u].w};
+        float v[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float2 p2 = unpack_bf16x2(w4[q]);
+          v[2 * q] = swishf_(fmaf(p2.x, sc[2 * q], sh[2 * q]));
+          v[2 * q + 1] = swishf_(fmaf(p2.y, sc[2 * q + 1], sh[2 * q + 1]));
+        }
+        store8_bf16(y + r * C + c, v);
+      }
+    }
   }
 }
 
@@ -298,29 +336,55 @@ __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __r
                                                                  const float* __restrict__ sums2, long long M, int C,
                                                                  bf16* __restrict__ dx, float* __restrict__ dgamma,
                                                                  float* __restrict__ dbeta) {
-  const int gpr = C >> 3;
-  const float invn = 1.f / (float)M;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < M * gpr; i += (long long)gridDim.x * blockDim.x) {
-    const long long row = i / gpr;
-    const int c = (int)(i - row * gpr) * 8;
-    float d[8], v[8], mu[8], rs[8], ga[8], be[8], s1[8], s2[8], o[8];
-    load8_bf16(dy + row * C + c, d);
-    load8_bf16(x + row * C + c, v);
+  const int cg = blockIdx.x * 64 + (threadIdx.x & 63), rl = threadIdx.x >> 6;
+  if (cg * 8 < C) {
+    const int c = cg * 8;
+    const float invn = 1.f / (float)M;
+    float mu[8], rs[8], ga[8], be[8], k1[8], k2[8];
     load8_f32(mean_rstd + c, mu);
     load8_f32(mean_rstd + C + c, rs);
     load8_f32(gamma + c, ga);
     load8_f32(beta + c, be);
-    load8_f32(sums2 + c, s1);
-    load8_f32(sums2 + C + c, s2);
+    load8_f32(sums2 + c, k1);
+    load8_f32(sums2 + C + c, k2);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float xh = (v[j] - mu[j]) * rs[j];
-      const float dz = d[j] * swish_gradf_(ga[j] * xh + be[j]);
-      o[j] = ga[j] * rs[j] * (dz - s1[j] * invn - xh * s2[j] * invn);
+      k1[j] *= invn;
+      k2[j] *= invn;
     }
-    store8_bf16(dx + row * C + c, o);
+    const long long step = (long long)gridDim.y * 4;
+    for (long long r0 = (long long)blockIdx.y * 4 + rl; r0 < M; r0 += BN_U * step) {
+      uint4 rd[BN_U], rx[BN_U];
+#pragma unroll
+      for (int u = 0; u < BN_U; ++u) {
+        const long long r = r0 + u * step;
+        rd[u] = r < M ? *reinterpret_cast<const uint4*>(dy + r * C + c) : make_uint4(0u, 0u, 0u, 0u);
+        rx[u] = r < M ? *reinterpret_cast<const uint4*>(x + r * C + c) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < BN_U; ++u) {
+        const long long r = r0 + u * step;
+        if (r < M) {
+          const uint32_t wd[4] = {rd[u].x, rd[u].y, rd[u].z, rd[u].w}, wx[4] = {rx[u].x, rx[u].y, rx[u].z, rx[u].w};
+          float o[8];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 d2 = unpack_bf16x2(wd[q]), x2 = unpack_bf16x2(wx[q]);
+            const float dd[2] = {d2.x, d2.y}, xx[2] = {x2.x, x2.y};
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              const int j = 2 * q + h;
+              const float xh = (xx[h] - mu[j]) * rs[j];
+              const float dz = dd[h] * swish_gradf_(fmaf(ga[j], xh, be[j]));
+              o[j] = ga[j] * rs[j] * (dz - k1[j] - xh * k2[j]);
+            }
+          }
+          store8_bf16(dx + r * C + c, o);
+        }
+      }
+    }
   }
-  if (blockIdx.x == 0) {
+  if (blockIdx.x == 0 && blockIdx.y == 0) {
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
       dbeta[c] += sums2[c];
       dgamma[c] += sums2[C + c];
@@ -368,7 +432,7 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                                 \
     int gy = (2 * b2_num_sms() + ctiles - 1) / ctiles;                                                                       \
     if (gy > units) gy = units;                                                                                              \
-    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 1)) * sizeof(float);                               \
+    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 2)) * sizeof(float);                               \
     auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
     static bool cfg = false;                                                                                                 \
     if (!cfg) {                                                                                                              \
@@ -405,7 +469,13 @@ extern "C" int b200slu_bn_swish_fwd(const void* x, const float* mean_rstd, const
   B2_CHECK_ARG(M > 0 && C % 8 == 0, "bn_swish_fwd: C %% 8 == 0");
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_CONVMOD, st, 0, 4.0 * M * C);
-  bn_swish_fwd_kernel<<<b2_grid_for(M * (C >> 3), 256), 256, 0, st>>>((const bf16*)x, mean_rstd, gamma, beta, M, C, (bf16*)y);
+  {
+    dim3 grid((C + 511) / 512, 1);
+    const long long gy = (M + 4 * BN_U - 1) / (4 * BN_U);
+    const long long cap = (8LL * b2_num_sms() + grid.x - 1) / grid.x;
+    grid.y = (unsigned)(gy < cap ? gy : cap);
+    bn_swish_fwd_kernel<<<grid, 256, 0, st>>>((const bf16*)x, mean_rstd, gamma, beta, M, C, (bf16*)y);
+  }
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -423,9 +493,14 @@ extern "C" int b200slu_bn_swish_bwd(const void* dy, const void* x, const float* 
   bn_swish_bwd_reduce_kernel<<<grid, 512, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, (int)M, C,
                                                    sums2_zeroed);
   B2_LAUNCH_CHECK();
-  bn_swish_bwd_apply_kernel<<<b2_grid_for(M * (C >> 3), 256), 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma,
-                                                                            beta, sums2_zeroed, M, C, (bf16*)dx, dgamma_accum,
-                                                                            dbeta_accum);
+  {
+    dim3 ga((C + 511) / 512, 1);
+    const long long gya = (M + 4 * BN_U - 1) / (4 * BN_U);
+    const long long capa = (4LL * b2_num_sms() + ga.x - 1) / ga.x;
+    ga.y = (unsigned)(gya < capa ? gya : capa);
+    bn_swish_bwd_apply_kernel<<<ga, 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, sums2_zeroed, M, C,
+                                                  (bf16*)dx, dgamma_accum, dbeta_accum);
+  }
   B2_LAUNCH_CHECK();
   return 0;
 }
