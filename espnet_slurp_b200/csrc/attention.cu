@@ -1,0 +1,499 @@
+// Fused relative-position multi-head attention for short sequences (keys <= 192, d_k = 64), forward.
+//
+// Replaces, in one kernel per layer, the chain the reference runs as separate torch ops
+// (espnet/nets/pytorch_backend/transformer/attention.py): matrix_ac = (q+u) k^T and matrix_bd = (q+v) p^T (:297-302),
+// rel_shift (:240-263), (ac + bd) / sqrt(d_k) (:304-306), masked softmax + dropout (forward_attention :78-91) and
+// attn . v (:93-95).  The same kernel with relpos_mode = NONE is MultiHeadedAttention.forward (:98-114) of the decoder
+// (causal self-attention, cross-attention over the encoder memory).
+//
+// One CTA = one (utterance, head, 128-query tile).  All operands of the tile arrive by TMA (SWIZZLE_128B); scores live
+// in tensor memory only:
+//   TMEM columns [0, TKP)          ac  = QU[128 x 64] . K[TKP x 64]^T                       (tcgen05.mma, M = 128)
+//   TMEM columns [TKP, TKP + WIN)  bd  = QV[128 x 64] . Pwin[WIN x 64]^T, WIN = TKP + 128: the window of relative
+//                                  positions rows i0 .. i0+127 can reach; P row c0 + n with c0 = T-1-i0-127
+// rel_shift is index arithmetic on that window: out[i0+r, j] = bd[r, 127 - r + j].  A TMEM lane (= query row) is read
+// by the thread of the same number, tcgen05.ld gives every lane of a warp the same columns, so the per-row offset is
+// applied by a round trip through a private shared-memory row (16-byte stores, scalar loads at the shifted offset:
+// bank-conflict-free with a 52-float row stride).  8 warps: lane quadrant = warp % 4, column half = warp / 4; three
+// passes over the warp's columns (max, exp + sum, normalise) keep the scores in TMEM between passes (tcgen05.st), so a
+// thread never holds more than one 16-column chunk.  The normalised, dropped-out probabilities are written (a) to HBM
+// (bf16, head-major [H,B,Tq,ld_p], saved for the backward) and (b) into shared memory as the K-major A operand of the
+// second contraction O = P . V (V is the MN-major B operand, exactly as TMA delivered it).
+// Shared memory is recycled between phases (Q/K/P-window are dead once the score MMAs retire), which keeps a T = 155
+// tile at 110 KB: two CTAs per SM, so one CTA's TMA loads and TMEM allocation wait overlap the other's compute.
+#include <stdlib.h>
+
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace {
+
+constexpr int DK = 64;        // head dimension (one 128-byte swizzle span of bf16)
+constexpr int QT = 128;       // query rows per CTA = TMEM lanes
+constexpr int CH = 16;        // score columns per softmax chunk
+constexpr int RING_LD = 84;   // floats per private shift-ring row: 64 window columns, 16 mirrored ones (reads never wrap), 4 pad
+constexpr int NCH = 6;        // softmax chunks per warp (half a row of at most 192 keys)
+constexpr int MAX_TK = 192;   // ac (TKP) + bd (TKP + 128) columns must fit the 512 TMEM columns
+constexpr int NTHREADS = 256;
+
+// one full 32-byte sector per thread (sm_100 256-bit store)
+__device__ __forceinline__ void stg256(void* p, const uint32_t (&v)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+               "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+struct AttnArgs {
+  int B, H, Tq, Tk, TKP, WIN, rel, causal;
+  float scale_log2e;
+  const int* lens;
+  bf16 *p, *pd, *ctx;
+  long long ld_p, ldctx;
+  uint32_t off_k, off_p, off_v, off_bar, tmem_cols;
+  B2Dropout drop;
+  long long* dbg;  // tuning only (B200SLU_ATTN_DEBUG=1): per-CTA phase time stamps
+};
+
+__global__ void __launch_bounds__(NTHREADS, 2)
+relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_constant__ CUtensorMap map_qv,
+                   const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                   const __grid_constant__ CUtensorMap map_pos, const AttnArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  if (sbase & 1023u) __trap();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nqt = (a.Tq + QT - 1) / QT;
+  const int qt = blockIdx.x % nqt, hb = blockIdx.x / nqt, h = hb % a.H, b = hb / a.H;
+  const int i0 = qt * QT;
+  const int TKP = a.TKP, WIN = a.WIN;
+  const uint32_t bar_qk = sbase + a.off_bar, bar_v = bar_qk + 8, bar_s = bar_qk + 16, bar_o = bar_qk + 24;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + a.off_bar + 32);
+  float* rowstat = reinterpret_cast<float*>(smem + a.off_bar + 64);  // [2 halves][128 rows] max, then the same for sums
+  const uint32_t s_qu = sbase, s_qv = sbase + QT * 128, s_k = sbase + a.off_k, s_p = sbase + a.off_p, s_v = sbase + a.off_v;
+
+  long long ts[8];
+  ts[0] = clock64();
+  b2_pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qu) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    if (a.rel) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qv) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_pos) : "memory");
+    }
+    mbar_init(bar_qk, 1);
+    mbar_init(bar_v, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // every operand of the tile is requested before this CTA queues for tensor memory
+    b2_pdl_wait();
+    mbar_expect_tx(bar_qk, (uint32_t)(QT * 128 * (a.rel ? 2 : 1) + TKP * 128 + (a.rel ? WIN * 128 : 0)));
+    tma_load_3d(s_qu, &map_qu, bar_qk, h * DK, i0, b);
+    tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
+    if (a.rel) {
+      tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
+      const int c0 = a.Tq - 1 - i0 - (QT - 1);  // may be negative: out-of-range rows are zero-filled
+      tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
+      tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
+    }
+    mbar_expect_tx(bar_v, (uint32_t)(TKP * 128));
+    tma_load_3d(s_v, &map_v, bar_v, h * DK, 0, b);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(a.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // global scalars of the softmax (valid length, dropout key): fetched here so their latency hides behind the TMA loads
+  b2_pdl_wait();
+  const int len_b = a.lens != nullptr ? min(a.lens[b], a.Tk) : a.Tk;
+  B2DropKey dk = {0ull, 0u, 1.f};
+  const bool dropping = a.drop.p > 0.f;
+  if (dropping) dk = dropout_key(a.drop);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  ts[1] = clock64();
+
+  // ---------------------------------------------------------------- scores: ac (and bd) into tensor memory
+  if (threadIdx.x == 0) {
+    mbar_wait(bar_qk, 0);
+    tcgen05_fence_after();
+    const uint32_t id_ac = make_idesc(TKP, 0, 0, QT);
+#pragma unroll
+    for (int kk = 0; kk < DK / 16; ++kk)
+      umma_bf16(tmem_base, make_smem_desc(s_qu + kk * 32, 16, 1024), make_smem_desc(s_k + kk * 32, 16, 1024), id_ac, kk != 0);
+    if (a.rel) {
+      const uint32_t id_bd = make_idesc(WIN / 2, 0, 0, QT);
+      for (int half = 0; half < 2; ++half) {
+#pragma unroll
+        for (int kk = 0; kk < DK / 16; ++kk)
+          umma_bf16(tmem_base + TKP + half * (WIN / 2), make_smem_desc(s_qv + kk * 32, 16, 1024),
+                    make_smem_desc(s_p + half * (WIN / 2) * 128 + kk * 32, 16, 1024), id_bd, kk != 0);
+      }
+    }
+    umma_commit(bar_s);
+  }
+  mbar_wait(bar_s, 0);
+  tcgen05_fence_after();
+  ts[2] = clock64();
+
+  // ---------------------------------------------------------------- softmax: ONE pass over tensor memory
+  // TMEM -> register reads run at 64 B/clk/SM (16 B/clk per scheduler), so every score column is read exactly once
+  // (+ 31 window columns per warp for the shift).  A thread keeps its half row as e = exp2(s - m_c) per 16-column
+  // chunk (m_c = the chunk's own maximum), packed fp16x2 (e <= 1; the final bf16 rounding of p is 4x coarser); the
+  // chunk references are reconciled when the row maximum and sum are known.
+  const int q = warp & 3, hs = warp >> 2;
+  const int r = q * 32 + lane, i = i0 + r;
+  const bool row_ok = i < a.Tq;
+  const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+  const int nch = TKP / CH, n0 = (nch + 1) / 2;
+  const int cbeg = hs ? n0 : 0, nmine = hs ? nch - n0 : n0;  // this warp's chunks: [cbeg, cbeg + nmine), nmine <= NCH
+  const int jbeg = cbeg * CH;
+  const int nvalid = a.causal ? min(len_b, i + 1) : len_b;
+  // shift ring: 64 window columns per thread; positions 64..79 mirror 0..15 so that the 16 lane-shifted scalar loads of a
+  // chunk are base + immediate (no wrap); the 84-float row pitch keeps 16-byte stores and shifted loads conflict-free
+  const uint32_t ring = sbase + (uint32_t)(warp * 32 + lane) * (RING_LD * 4);
+  const float* ring_g = reinterpret_cast<const float*>(smem) + (warp * 32 + lane) * RING_LD;
+  const int nb = 96 - 32 * q + jbeg;  // window column of ring position 0: row r, key jbeg + x reads position 31 - lane + x
+  const float kap = a.scale_log2e;
+
+  uint32_t E[NCH][CH / 2];
+  float mc[NCH], sc[NCH];
+  uint32_t ta[16], tb[16];
+  if (nmine > 0) {
+    if (a.rel) {
+      tmem_ld16(tlane + TKP + nb, ta);
+      tmem_ld16(tlane + TKP + nb + 16, tb);
+      tmem_ld_wait();
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        sts128(ring + t * 16, ta[4 * t], ta[4 * t + 1], ta[4 * t + 2], ta[4 * t + 3]);
+        sts128(ring + 64 + t * 16, tb[4 * t], tb[4 * t + 1], tb[4 * t + 2], tb[4 * t + 3]);
+      }
+      tmem_ld16(tlane + TKP + nb + 32, tb);
+    }
+    tmem_ld16(tlane + jbeg, ta);
+  }
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    mc[c] = -INFINITY;
+    sc[c] = 0.f;
+#pragma unroll
+    for (int e = 0; e < CH / 2; ++e) E[c][e] = 0u;
+    if (c < nmine) {
+      const int j0 = jbeg + c * CH;
+      float sv[CH];
+      tmem_ld_wait();
+#pragma unroll
+      for (int jj = 0; jj < CH; ++jj) sv[jj] = __uint_as_float(ta[jj]);
+      if (a.rel) {
+        const uint32_t wr = ring + (uint32_t)(((32 + 16 * c) & 63) * 4);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          sts128(wr + t * 16, tb[4 * t], tb[4 * t + 1], tb[4 * t + 2], tb[4 * t + 3]);
+          if ((c & 3) == 2) sts128(wr + 256 + t * 16, tb[4 * t], tb[4 * t + 1], tb[4 * t + 2], tb[4 * t + 3]);
+        }
+      }
+      if (c + 1 < nmine) {  // next chunk's TMEM reads fly while this one is processed
+        if (a.rel) tmem_ld16(tlane + TKP + nb + 48 + 16 * c, tb);
+        tmem_ld16(tlane + j0 + CH, ta);
+      }
+      if (a.rel) {
+        const float* rd = ring_g + ((31 - lane + 16 * c) & 63);
+#pragma unroll
+        for (int jj = 0; jj < CH; ++jj) sv[jj] += rd[jj];
+      }
+      // scores stay raw (unscaled) until the exponent: e = 2^(kap * s - kap * m) is one FFMA + one MUFU per element
+      if (j0 + CH > nvalid) {  // only chunks that straddle the valid length pay for masking
+#pragma unroll
+        for (int jj = 0; jj < CH; ++jj) sv[jj] = (j0 + jj < nvalid) ? sv[jj] : -INFINITY;
+      }
+      float m = -INFINITY;
+#pragma unroll
+      for (int jj = 0; jj < CH; ++jj) m = fmaxf(m, sv[jj]);
+      m *= kap;  // kap > 0
+      mc[c] = m;
+      const float mneg = (m == -INFINITY) ? 0.f : -m;
+      float sum = 0.f;
+#pragma unroll
+      for (int jj = 0; jj < CH; jj += 2) {
+        const float e0 = ex2_approx(fmaf(sv[jj], kap, mneg)), e1 = ex2_approx(fmaf(sv[jj + 1], kap, mneg));
+        sum += e0 + e1;
+        const __half2 hv = __floats2half2_rn(e0, e1);
+        E[c][jj >> 1] = *reinterpret_cast<const uint32_t*>(&hv);
+      }
+      sc[c] = sum;
+    }
+  }
+  float mw = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) mw = fmaxf(mw, mc[c]);
+  float sw = 0.f;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) sw += (mc[c] == -INFINITY) ? 0.f : sc[c] * exp2f(mc[c] - mw);
+  rowstat[hs * QT + r] = mw;
+  rowstat[2 * QT + hs * QT + r] = sw;
+  tcgen05_fence_before();
+  __syncthreads();  // also: every warp is done with its shift ring, which the P operand below overwrites
+  ts[3] = clock64();
+  const float mo = rowstat[(hs ^ 1) * QT + r], so = rowstat[2 * QT + (hs ^ 1) * QT + r];
+  const float mrow = fmaxf(mw, mo);
+  float tot = 0.f;
+  if (mw != -INFINITY) tot += sw * exp2f(mw - mrow);
+  if (mo != -INFINITY) tot += so * exp2f(mo - mrow);
+  const float inv = tot > 0.f ? 1.f / tot : 0.f;
+  ts[4] = clock64();
+
+  // p = e * exp2(m_c - m) / sum -> HBM (bf16, one 32-byte sector per thread and chunk); dropout(p) -> K-major A operand
+  const long long rg = ((long long)h * a.B + b) * a.Tq + i;  // row of the head-major [H,B,Tq,ld_p] tensors
+  bf16* prow = a.p + rg * a.ld_p;
+  bf16* pdrow = a.pd != nullptr ? a.pd + rg * a.ld_p : nullptr;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    if (c < nmine) {
+      const int j0 = jbeg + c * CH;
+      const float f = (mc[c] == -INFINITY) ? 0.f : exp2f(mc[c] - mrow) * inv;
+      float v[CH];
+#pragma unroll
+      for (int e = 0; e < CH / 2; ++e) {
+        const float2 ev = __half22float2(*reinterpret_cast<const __half2*>(&E[c][e]));
+        v[2 * e] = ev.x * f;
+        v[2 * e + 1] = ev.y * f;
+      }
+      uint32_t pk[CH / 2];
+#pragma unroll
+      for (int e = 0; e < CH / 2; ++e) pk[e] = pack_bf16x2(v[2 * e], v[2 * e + 1]);
+      const bool full = row_ok && j0 + CH <= a.ld_p, wide = (a.ld_p & 15) == 0;  // row pitch a multiple of 32 bytes
+      auto store16 = [&](bf16* dst, const uint32_t (&w)[CH / 2]) {
+        if (full && wide) {
+          stg256(dst, w);
+        } else if (row_ok && j0 < a.ld_p) {
+          *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+          if (full) *reinterpret_cast<uint4*>(dst + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+        }
+      };
+      store16(prow + j0, pk);
+      if (dropping) {
+        // the A operand is p with the dropped lanes zeroed; the 1 / (1 - rate) factor is applied to the context rows
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          uint32_t w[4];
+          dropout_lanes8(dk, (unsigned long long)(rg * a.ld_p + j0 + g * 8) >> 3, w);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t mlo = (w[e] & 0xffffu) >= dk.thr ? 0x0000ffffu : 0u, mhi = (w[e] >> 16) >= dk.thr ? 0xffff0000u : 0u;
+            pk[g * 4 + e] &= (mlo | mhi);
+          }
+        }
+        if (pdrow != nullptr) {  // only for the unfused backward: dropout(p) with its scale, as b200slu_softmax_fwd writes it
+          uint32_t pq[CH / 2];
+#pragma unroll
+          for (int e = 0; e < CH / 2; ++e) {
+            const float2 x = unpack_bf16x2(pk[e]);
+            pq[e] = pack_bf16x2(x.x * dk.inv, x.y * dk.inv);
+          }
+          store16(pdrow + j0, pq);
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        const int jc = j0 + g * 8;
+        const uint32_t chunk = (uint32_t)((jc & 63) >> 3);
+        sts128(sbase + (uint32_t)(jc >> 6) * (QT * 128) + (uint32_t)r * 128u + ((chunk ^ (uint32_t)(r & 7)) << 4), pk[g * 4],
+               pk[g * 4 + 1], pk[g * 4 + 2], pk[g * 4 + 3]);
+      }
+    }
+  }
+  fence_async_smem();
+  tcgen05_fence_before();
+  __syncthreads();
+
+  ts[5] = clock64();
+  // ---------------------------------------------------------------- context: O = P . V
+  const uint32_t t_o = tmem_base + TKP;  // the bd window is dead
+  if (threadIdx.x == 0) {
+    mbar_wait(bar_v, 0);
+    tcgen05_fence_after();
+    const uint32_t id_o = make_idesc(DK, 0, 1, QT);
+    for (int ks = 0; ks < TKP / 16; ++ks)
+      umma_bf16(t_o, make_smem_desc(sbase + (uint32_t)(ks >> 2) * (QT * 128) + (ks & 3) * 32, 16, 1024),
+                make_smem_desc(s_v + ks * 2048, 64 * DK * 2, 1024), id_o, ks != 0);
+    umma_commit(bar_o);
+  }
+  mbar_wait(bar_o, 0);
+  tcgen05_fence_after();
+  ts[6] = clock64();
+  {
+    uint32_t o[32];
+    tmem_ld32(tlane + TKP + hs * 32, o);
+    tmem_ld_wait();
+    if (row_ok) {
+      bf16* dst = a.ctx + ((long long)b * a.Tq + i) * a.ldctx + h * DK + hs * 32;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(o[g * 8 + e]) * dk.inv;
+        store8_bf16(dst + g * 8, v);
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (a.dbg != nullptr && threadIdx.x == 0 && blockIdx.x < 512) {
+    ts[7] = clock64();
+    for (int t = 0; t < 8; ++t) a.dbg[blockIdx.x * 8 + t] = ts[t];
+  }
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols) : "memory");
+  }
+}
+
+// ----------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// bf16 [n2, n1, cols] (row stride ld, slab stride s2, elements); box {64, box_rows, 1}; SWIZZLE_128B; zero fill out of range
+int make_map3(CUtensorMap* m, const void* base, long long cols, long long n1, long long ld, long long n2, long long s2,
+              int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (enc == nullptr) {
+    b200slu_set_error("cuTensorMapEncodeTiled driver entry point unavailable");
+    return B200SLU_ECUDA;
+  }
+  if (n2 <= 1) {
+    n2 = 1;
+    s2 = ld * n1;
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)n1, (cuuint64_t)n2};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)s2 * 2};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b200slu_set_error("relattn: cuTensorMapEncodeTiled failed (%d): cols=%lld n1=%lld ld=%lld n2=%lld s2=%lld box_rows=%d base=%p",
+                      (int)r, cols, n1, ld, n2, s2, box_rows, base);
+    return B200SLU_ECUDA;
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200slu_relattn_supported(int Tq, int Tk, int dk, int relpos_mode) {
+  if (dk != DK || Tq < 1 || Tk < 1 || Tk > MAX_TK) return 0;
+  if (relpos_mode == B200SLU_RELPOS_LATEST) return Tq == Tk;
+  return relpos_mode == B200SLU_RELPOS_NONE;
+}
+
+extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
+                                   const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk,
+                                   int relpos_mode, int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx,
+                                   long long ldctx, float drop_p, unsigned long long seed, unsigned int site, void* stream) {
+  B2_CHECK_ARG(B > 0 && H > 0, "relattn_fwd: empty problem");
+  B2_CHECK_ARG(b200slu_relattn_supported(Tq, Tk, DK, relpos_mode),
+               "relattn_fwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)",
+               MAX_TK, Tq, Tk, relpos_mode);
+  const bool rel = relpos_mode == B200SLU_RELPOS_LATEST;
+  B2_CHECK_ARG(qu != nullptr && k != nullptr && v != nullptr && p != nullptr && ctx != nullptr, "relattn_fwd: null operand");
+  B2_CHECK_ARG(!rel || (qv != nullptr && pos != nullptr), "relattn_fwd: rel-pos mode needs q_v and the projected positions");
+  B2_CHECK_ARG(drop_p > 0.f || p_drop == p || p_drop == nullptr, "relattn_fwd: without dropout p_drop must alias p (or be NULL)");
+  B2_CHECK_ARG(ldq % 8 == 0 && ldkv % 8 == 0 && ldctx % 8 == 0 && ld_p % 8 == 0 && ld_p >= Tk && (!rel || ldpos % 8 == 0),
+               "relattn_fwd: row strides must be multiples of 8 elements, ld_p >= Tk");
+  B2_CHECK_ARG(((uintptr_t)qu % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 && ((uintptr_t)ctx % 16) == 0 &&
+                   ((uintptr_t)p % 32) == 0 && ((uintptr_t)p_drop % 32) == 0 && (!rel || (((uintptr_t)qv % 16) == 0 && ((uintptr_t)pos % 16) == 0)),
+               "relattn_fwd: operands must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  AttnArgs a{};
+  a.B = B; a.H = H; a.Tq = Tq; a.Tk = Tk;
+  a.TKP = (Tk + 15) / 16 * 16;
+  a.WIN = a.TKP + QT;
+  a.rel = rel; a.causal = causal;
+  a.scale_log2e = scale * 1.4426950408889634f;
+  a.lens = key_lens;
+  a.p = (bf16*)p; a.pd = (p_drop != p) ? (bf16*)p_drop : nullptr; a.ctx = (bf16*)ctx;
+  a.ld_p = ld_p; a.ldctx = ldctx;
+  a.off_k = 2 * QT * 128;
+  a.off_p = a.off_k + a.TKP * 128;
+  a.off_v = a.off_p + (rel ? a.WIN * 128 : 0);
+  const uint32_t recycled = rel ? (uint32_t)(NTHREADS * RING_LD * 4) : 0u;            // scratch rows of pass 1
+  const uint32_t pm = (uint32_t)((a.TKP + 63) / 64) * (QT * 128);                      // A operand of P.V
+  const uint32_t need = (recycled > pm ? recycled : pm);
+  if (a.off_v < need) a.off_v = (need + 1023u) / 1024u * 1024u;
+  a.off_bar = a.off_v + a.TKP * 128;
+  const int cols = rel ? a.TKP + a.WIN : a.TKP + DK;
+  a.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
+  a.drop = b2_make_drop(drop_p, seed, site);
+  const size_t smem = (size_t)a.off_bar + 64 + 4 * QT * sizeof(float);
+
+  CUtensorMap mqu, mqv, mk, mv, mp;
+  const int d = H * DK;
+  B2_TRY(make_map3(&mqu, qu, d, Tq, ldq, B, (long long)Tq * ldq, QT));
+  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  if (rel) {
+    B2_TRY(make_map3(&mqv, qv, d, Tq, ldq, B, (long long)Tq * ldq, QT));
+    // projected positions [2T-1, d], shared by all utterances: rank 2 (encoded as rank 3 with one slab)
+    B2_TRY(make_map3(&mp, pos, d, 2 * Tq - 1, ldpos, 1, 0, a.WIN / 2));
+  } else {
+    mqv = mqu;
+    mp = mk;
+  }
+  static bool configured = false;
+  if (!configured) {
+    B2_CUDA(cudaFuncSetAttribute(relattn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    configured = true;
+  }
+  const int nqt = (Tq + QT - 1) / QT;
+  const double tiles = (double)B * H;
+  B2_SCOPE(FAM_ATTN, st, tiles * (4.0 * Tq * Tk * DK + (rel ? 2.0 * Tq * (2.0 * Tq - 1) * DK : 0.0)),
+           tiles * (2.0 * DK * (2.0 * Tq + 2.0 * Tk) + 2.0 * Tq * Tk * (drop_p > 0.f ? 2.0 : 1.0)));
+  static const bool dbg = getenv("B200SLU_ATTN_DEBUG") != nullptr;
+  static long long* dbg_buf = nullptr;
+  if (dbg) {
+    if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 512 * 8 * sizeof(long long)));
+    B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 512 * 8 * sizeof(long long), st));
+    a.dbg = dbg_buf;
+  }
+  B2_CUDA(b2_launch(relattn_fwd_kernel, dim3((unsigned)(B * H * nqt)), dim3(NTHREADS), smem, st, mqu, mqv, mk, mv, mp, a));
+  if (dbg) {
+    static long long h[512 * 8];
+    B2_CUDA(cudaStreamSynchronize(st));
+    B2_CUDA(cudaMemcpy(h, dbg_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    double acc[7] = {0};
+    int n = 0;
+    for (int c = 0; c < 512 && c < B * H * nqt; ++c, ++n)
+      for (int t = 0; t < 7; ++t) acc[t] += (double)(h[c * 8 + t + 1] - h[c * 8 + t]);
+    fprintf(stderr, "[relattn dbg] Tq=%d Tk=%d rel=%d smem=%zu tmem=%u | mean cycles over %d CTAs: alloc+sync %.0f, loads+score MMA %.0f, pass1 %.0f, "
+            "pass2 %.0f, pass3 %.0f, PV MMA %.0f, epilogue %.0f\n", Tq, Tk, (int)rel, smem, a.tmem_cols, n, acc[0] / n, acc[1] / n, acc[2] / n,
+            acc[3] / n, acc[4] / n, acc[5] / n, acc[6] / n);
+  }
+  return 0;
+}

@@ -254,6 +254,29 @@ def softmax_bwd(dpd, p, Tk: int, mode: str, scale: float, ld_bd: int = 0, drop: 
     return dac, dbd
 
 
+# ---- fused attention (scores -> rel_shift -> softmax -> dropout -> context) --------------------------------------
+def relattn_supported(Tq: int, Tk: int, dk: int, mode: str) -> bool:
+    return bool(_lib.lib().b200slu_relattn_supported(Tq, Tk, dk, RELPOS[mode]))
+
+
+def relattn_fwd(qu, qv, k, v, pos, key_lens, B: int, Tq: int, Tk: int, H: int, mode: str, causal: bool, scale: float,
+                drop: Drop = None, want_pd: bool = True):
+    """One kernel for attention.py:281-308 / :98-114.  qu, qv [B*Tq, H*64] (qv, pos only for mode "latest"), k, v
+    [B*Tk, H*64] (column slices of wider buffers are fine) -> (p, p_drop) bf16 [H,B,Tq,round8(Tk)], ctx bf16 [B*Tq, H*64]."""
+    d = k.shape[1]
+    ld = round8(Tk)
+    p = torch.empty(H, B, Tq, ld, device=k.device, dtype=torch.bfloat16)
+    dp, seed, site = _drop(drop)
+    pd = (torch.empty_like(p) if want_pd else None) if dp > 0.0 else p  # the fused backward regenerates dropout(p) from p
+    ctx = torch.empty(B * Tq, d, device=k.device, dtype=torch.bfloat16)
+    assert qu.stride(0) == (qv.stride(0) if qv is not None else qu.stride(0)) and k.stride(0) == v.stride(0)
+    check(_lib.lib().b200slu_relattn_fwd(ptr(qu), ptr(qv), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(pos),
+                                         pos.stride(0) if pos is not None else 0, ptr(key_lens), B, H, Tq, Tk, RELPOS[mode],
+                                         int(causal), scale, ptr(p), ptr(pd), ld, ptr(ctx), ctx.stride(0), dp, seed, site,
+                                         stream_ptr()), "relattn_fwd")
+    return p, pd, ctx
+
+
 # ---- conv module --------------------------------------------------------------------------------------------------
 def glu_dwconv_fwd(pw1, w, bias, B: int, T: int, K: int):
     Cc = pw1.shape[1] // 2

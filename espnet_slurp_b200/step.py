@@ -148,14 +148,18 @@ def relmha_fwd(x, pos16, klens, P, W, p: str, norm: str, cfg: EncCfg, B: int, T:
     qu, qv = K.pos_bias_fwd(q, P[a + ".pos_bias_u"].reshape(-1), P[a + ".pos_bias_v"].reshape(-1))
     pp = K.gemm(pos16, W[a + ".linear_pos.weight"])
     Pn = pos16.shape[0]
-    ac = K.attn_f1(qu, k, B, T, T, H)
-    bd = K.attn_f1(qv, pp, B, T, Pn, H, y_bcast=True)
     da, do = ctx.drop(cfg.att_dropout), ctx.drop(cfg.dropout)
     scale = 1.0 / math.sqrt(d // H)
-    pr, pd = K.softmax_fwd(ac, bd, klens, T, cfg.rel_pos_type, False, scale, drop=da)
-    c = K.attn_f2(pd, v, B, T, T, H)
+    if K.relattn_supported(T, T, d // H, cfg.rel_pos_type):
+        # short utterances: scores, rel_shift, softmax, dropout and context in one tcgen05 kernel (scores never leave TMEM)
+        pr, pd, c = K.relattn_fwd(qu, qv, k, v, pp, klens, B, T, T, H, cfg.rel_pos_type, False, scale, drop=da)
+    else:
+        ac = K.attn_f1(qu, k, B, T, T, H)
+        bd = K.attn_f1(qv, pp, B, T, Pn, H, y_bcast=True)
+        pr, pd = K.softmax_fwd(ac, bd, klens, T, cfg.rel_pos_type, False, scale, drop=da)
+        c = K.attn_f2(pd, v, B, T, T, H)
     y = K.gemm(c, W[a + ".linear_out.weight"], bias=P[a + ".linear_out.bias"], residual=x, drop=do, out_dtype=F32)
-    return y, (x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, bd.shape[-1])
+    return y, (x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, K.round8(Pn))
 
 
 def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int):
@@ -324,11 +328,14 @@ def _mha_fwd(xq16, kv_src16, q_w: str, kv_w: str, P, W, a: str, klens, B, Tq, Tk
         kv = K.gemm(kv_src16, W[a + ".linear_kv.weight"], bias=P[a + ".linear_kv.bias"])
         k, v = kv[:, :d], kv[:, d:]
         proj = (q, kv)
-    ac = K.attn_f1(q, k, B, Tq, Tk, H)
     da = ctx.drop(p_att)
     scale = 1.0 / math.sqrt(d // H)
-    pr, pd = K.softmax_fwd(ac, None, klens, Tk, "none", causal, scale, drop=da)
-    c = K.attn_f2(pd, v, B, Tq, Tk, H)
+    if K.relattn_supported(Tq, Tk, d // H, "none"):
+        pr, pd, c = K.relattn_fwd(q, None, k, v, None, klens, B, Tq, Tk, H, "none", causal, scale, drop=da)
+    else:
+        ac = K.attn_f1(q, k, B, Tq, Tk, H)
+        pr, pd = K.softmax_fwd(ac, None, klens, Tk, "none", causal, scale, drop=da)
+        c = K.attn_f2(pd, v, B, Tq, Tk, H)
     return c, (proj, pr, pd, da, scale)
 
 

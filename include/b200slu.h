@@ -161,6 +161,19 @@ int b200slu_softmax_fwd(const float* ac, long long ld_ac, const float* bd, long 
 int b200slu_softmax_bwd(const float* dp_drop, const void* p, long long ld_p, int H, int B, int Tq, int Tk, int relpos_mode,
                         float scale, void* d_ac, void* d_bd, long long ld_bd, float drop_p, unsigned long long seed,
                         unsigned int site, void* stream);
+/* ---- K1/K10 fused: scores -> rel_shift -> masked softmax -> dropout -> context in ONE kernel (tcgen05 / TMEM / TMA) ----
+ * RelPositionMultiHeadedAttention.forward attention.py:281-308 (relpos_mode LATEST: q_u = q + pos_bias_u, q_v = q + pos_bias_v,
+ * pos = linear_pos(pos_emb) [2T-1, H*64]) and MultiHeadedAttention.forward :98-114 (relpos_mode NONE: q_u = q; q_v, pos
+ * unused; causal = decoder self-attention).  Rows of q_u/q_v (stride ldq) and k/v (stride ldkv) are (utterance, frame),
+ * heads are 64-column slices.  Outputs: p / p_drop bf16 head-major [H,B,Tq,ld_p] (saved for the backward; p_drop must
+ * alias p iff drop_p == 0; the dropout decisions are those of b200slu_softmax_fwd / _bwd) and the merged-head context
+ * bf16 [B*Tq, H*64] (row stride ldctx).  b200slu_relattn_supported tells whether a shape runs here (d_k = 64, keys <= 192,
+ * LATEST with Tq == Tk, or NONE); other shapes use the unfused GEMM + softmax entry points above. */
+int b200slu_relattn_supported(int Tq, int Tk, int dk, int relpos_mode);
+int b200slu_relattn_fwd(const void* q_u, const void* q_v, long long ldq, const void* k, const void* v, long long ldkv,
+                        const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk, int relpos_mode,
+                        int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx, long long ldctx, float drop_p,
+                        unsigned long long seed, unsigned int site, void* stream);
 /* rel_shift source index (bit-exact index test): returns row * 65536 + col + 1 of the un-shifted matrix that lands at
  * out[i, j], or 0 for the literal zero of the legacy variant. */
 long long b200slu_rel_shift_index(int i, int j, int T, int mode);

@@ -233,6 +233,18 @@ def softmax_bwd(dpd, p, Tk, mode, scale, ld_bd=0, drop=None):
     return dac, dbd
 
 
+def relattn_supported(Tq, Tk, dk, mode):
+    return dk == 64 and Tk <= 192 and ((mode == "latest" and Tq == Tk) or mode in (None, "none"))
+
+
+def relattn_fwd(qu, qv, k, v, pos, key_lens, B, Tq, Tk, H, mode, causal, scale, drop=None):
+    """the fused kernel = the unfused chain (scores stay fp32 on chip, as in attn_f1's fp32 outputs)"""
+    ac = attn_f1(qu, k, B, Tq, Tk, H)
+    bd = attn_f1(qv, pos, B, Tq, pos.shape[0], H, y_bcast=True) if mode == "latest" else None
+    p, pd = softmax_fwd(ac, bd, key_lens, Tk, mode, causal, scale, drop=drop)
+    return p, pd, attn_f2(pd, v, B, Tq, Tk, H)
+
+
 def glu_dwconv_fwd(pw1, w, bias, B, T, K):
     C = pw1.shape[1] // 2
     x = pw1.float().reshape(B, T, 2 * C)

@@ -179,6 +179,45 @@ def test_softmax_relshift(mode, T):
         close(dbd, wdbd, 1e-2, "softmax dbd")
 
 
+@pytest.mark.parametrize("mode,causal,Tq,Tk", [("latest", False, 155, 155), ("latest", False, 124, 124), ("latest", False, 7, 7),
+                                               ("latest", False, 192, 192), ("latest", False, 129, 129), ("latest", False, 33, 33),
+                                               ("none", True, 21, 21), ("none", False, 21, 155), ("none", False, 140, 99),
+                                               ("none", True, 150, 150)])
+def test_fused_attention_fwd(mode, causal, Tq, Tk):
+    """the fused tcgen05 kernel against the statement of the unfused chain, and against the unfused CUDA chain"""
+    H, B, dk = 4, 3, 64
+    d = H * dk
+    assert K().relattn_supported(Tq, Tk, dk, mode)
+    qkv = (rnd(B * Tq, 3 * d, seed=1) * 0.7).to(BF)
+    kv = (rnd(B * Tk, 2 * d, seed=2) * 0.7).to(BF)
+    qv = (rnd(B * Tq, d, seed=3) * 0.7).to(BF)
+    Pn = 2 * Tq - 1
+    pos = (rnd(Pn, d, seed=4) * 0.7).to(BF) if mode == "latest" else None
+    lens = torch.tensor([Tk, max(1, Tk - 3), max(1, Tk // 2)], dtype=torch.int32)
+    qu = qkv[:, :d]
+    k, v = kv[:, :d], kv[:, d:]
+    qkv_c, kv_c = qkv.cuda(), kv.cuda()
+    args_c = (qkv_c[:, :d].contiguous() if mode == "latest" else qkv_c[:, :d], qv.cuda() if mode == "latest" else None, kv_c[:, :d], kv_c[:, d:],
+              pos.cuda() if pos is not None else None, lens.cuda(), B, Tq, Tk, H, mode, causal, 0.125)
+    p, pd, ctx = K().relattn_fwd(*args_c)
+    wp, _, wctx = E.relattn_fwd(qu, qv if mode == "latest" else None, k, v, pos, lens, B, Tq, Tk, H, mode, causal, 0.125)
+    assert p.data_ptr() == pd.data_ptr()
+    close(p[..., :Tk], wp[..., :Tk], 1e-2, "fused p")
+    close(ctx, wctx, 1e-2, "fused ctx")
+    for bi in range(B):  # masked keys get probability exactly 0
+        assert p[:, bi, :, int(lens[bi]):Tk].abs().max().item() == 0 if int(lens[bi]) < Tk else True
+    # dropout: the decisions are those of the unfused softmax kernel (the unfused backward regenerates them)
+    drop = (0.1, 1234, 7)
+    p2, pd2, ctx2 = K().relattn_fwd(*args_c, drop=drop)
+    ac = K().attn_f1(args_c[0], args_c[2], B, Tq, Tk, H)
+    bd = K().attn_f1(args_c[1], args_c[4], B, Tq, Pn, H, y_bcast=True) if mode == "latest" else None
+    up, upd = K().softmax_fwd(ac, bd, args_c[5], Tk, mode, causal, 0.125, drop=drop)
+    close(p2[..., :Tk], up[..., :Tk], 1e-2, "fused p vs unfused")
+    assert ((pd2[..., :Tk] == 0) == (upd[..., :Tk] == 0)).float().mean().item() > 0.999
+    close(pd2[..., :Tk], upd[..., :Tk], 2e-2, "fused p_drop vs unfused")
+    close(ctx2, K().attn_f2(upd, args_c[3], B, Tq, Tk, H), 2e-2, "fused ctx (dropout) vs unfused")
+
+
 @pytest.mark.parametrize("T", [1, 2, 3, 7, 16, 33, 64])
 def test_rel_shift_index_bit_exact(T, golden_dir):
     import os
