@@ -62,102 +62,26 @@ struct AttnArgs {
   long long* dbg;  // tuning only (B200SLU_ATTN_DEBUG=1): per-CTA phase time stamps
 };
 
-__global__ void __launch_bounds__(NTHREADS, 2)
-relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_constant__ CUtensorMap map_qv,
-                   const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
-                   const __grid_constant__ CUtensorMap map_pos, const AttnArgs a) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  const uint32_t sbase = smem_u32(smem);
-  if (sbase & 1023u) __trap();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nqt = (a.Tq + QT - 1) / QT;
-  const int qt = blockIdx.x % nqt, hb = blockIdx.x / nqt, h = hb % a.H, b = hb / a.H;
-  const int i0 = qt * QT;
-  const int TKP = a.TKP, WIN = a.WIN;
-  const uint32_t bar_qk = sbase + a.off_bar, bar_v = bar_qk + 8, bar_s = bar_qk + 16, bar_o = bar_qk + 24;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + a.off_bar + 32);
-  float* rowstat = reinterpret_cast<float*>(smem + a.off_bar + 64);  // [2 halves][128 rows] max, then the same for sums
-  const uint32_t s_qu = sbase, s_qv = sbase + QT * 128, s_k = sbase + a.off_k, s_p = sbase + a.off_p, s_v = sbase + a.off_v;
+// group barrier: the 256 threads of one tile (barrier 0 = the whole CTA in the one-tile kernel)
+__device__ __forceinline__ void group_sync(int bar_id) { asm volatile("bar.sync %0, 256;" ::"r"(bar_id) : "memory"); }
 
-  long long ts[8];
-  ts[0] = clock64();
-  b2_pdl_launch_dependents();
-  if (threadIdx.x == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qu) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
-    if (a.rel) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qv) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_pos) : "memory");
-    }
-    mbar_init(bar_qk, 1);
-    mbar_init(bar_v, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    // every operand of the tile is requested before this CTA queues for tensor memory
-    b2_pdl_wait();
-    mbar_expect_tx(bar_qk, (uint32_t)(QT * 128 * (a.rel ? 2 : 1) + TKP * 128 + (a.rel ? WIN * 128 : 0)));
-    tma_load_3d(s_qu, &map_qu, bar_qk, h * DK, i0, b);
-    tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
-    if (a.rel) {
-      tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
-      const int c0 = a.Tq - 1 - i0 - (QT - 1);  // may be negative: out-of-range rows are zero-filled
-      tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
-      tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
-    }
-    mbar_expect_tx(bar_v, (uint32_t)(TKP * 128));
-    tma_load_3d(s_v, &map_v, bar_v, h * DK, 0, b);
-  }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(a.tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  // global scalars of the softmax (valid length, dropout key): fetched here so their latency hides behind the TMA loads
-  b2_pdl_wait();
-  const int len_b = a.lens != nullptr ? min(a.lens[b], a.Tk) : a.Tk;
-  B2DropKey dk = {0ull, 0u, 1.f};
-  const bool dropping = a.drop.p > 0.f;
-  if (dropping) dk = dropout_key(a.drop);
-  tcgen05_fence_before();
-  __syncthreads();
-  tcgen05_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  ts[1] = clock64();
-
-  // ---------------------------------------------------------------- scores: ac (and bd) into tensor memory
-  if (threadIdx.x == 0) {
-    mbar_wait(bar_qk, 0);
-    tcgen05_fence_after();
-    const uint32_t id_ac = make_idesc(TKP, 0, 0, QT);
-#pragma unroll
-    for (int kk = 0; kk < DK / 16; ++kk)
-      umma_bf16(tmem_base, make_smem_desc(s_qu + kk * 32, 16, 1024), make_smem_desc(s_k + kk * 32, 16, 1024), id_ac, kk != 0);
-    if (a.rel) {
-      const uint32_t id_bd = make_idesc(WIN / 2, 0, 0, QT);
-      for (int half = 0; half < 2; ++half) {
-#pragma unroll
-        for (int kk = 0; kk < DK / 16; ++kk)
-          umma_bf16(tmem_base + TKP + half * (WIN / 2), make_smem_desc(s_qv + kk * 32, 16, 1024),
-                    make_smem_desc(s_p + half * (WIN / 2) * 128 + kk * 32, 16, 1024), id_bd, kk != 0);
-      }
-    }
-    umma_commit(bar_s);
-  }
-  mbar_wait(bar_s, 0);
-  tcgen05_fence_after();
-  ts[2] = clock64();
-
+// Softmax of one 128-query tile whose scores sit in tensor memory at t_s (ac at column 0, the bd window at column TKP):
+// leaves P in HBM and the (dropped-out) K-major A operand of P.V at the start of the tile's shared-memory region.
+__device__ __forceinline__ void softmax_tile(const AttnArgs& a, uint8_t* smem, uint32_t sbase, int tid, int bar_id, uint32_t t_s,
+                                             float* rowstat, int i0, int h, int b, int len_b, const B2DropKey& dk,
+                                             uint32_t s_release) {
   // ---------------------------------------------------------------- softmax: ONE pass over tensor memory
   // TMEM -> register reads run at 64 B/clk/SM (16 B/clk per scheduler), so every score column is read exactly once
   // (+ 31 window columns per warp for the shift).  A thread keeps its half row as e = exp2(s - m_c) per 16-column
   // chunk (m_c = the chunk's own maximum), packed fp16x2 (e <= 1; the final bf16 rounding of p is 4x coarser); the
   // chunk references are reconciled when the row maximum and sum are known.
+  const int warp = tid >> 5, lane = tid & 31;  // warp within the group of 8
+  const int TKP = a.TKP;
+  const bool dropping = a.drop.p > 0.f;
   const int q = warp & 3, hs = warp >> 2;
   const int r = q * 32 + lane, i = i0 + r;
   const bool row_ok = i < a.Tq;
-  const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+  const uint32_t tlane = t_s + ((uint32_t)(q * 32) << 16);
   const int nch = TKP / CH, n0 = (nch + 1) / 2;
   const int cbeg = hs ? n0 : 0, nmine = hs ? nch - n0 : n0;  // this warp's chunks: [cbeg, cbeg + nmine), nmine <= NCH
   const int jbeg = cbeg * CH;
@@ -246,15 +170,14 @@ relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_cons
   rowstat[hs * QT + r] = mw;
   rowstat[2 * QT + hs * QT + r] = sw;
   tcgen05_fence_before();
-  __syncthreads();  // also: every warp is done with its shift ring, which the P operand below overwrites
-  ts[3] = clock64();
+  group_sync(bar_id);  // also: every warp is done with its shift ring, which the P operand below overwrites
+  if (s_release != 0u && tid == 0) mbar_arrive(s_release);  // the score columns may be overwritten (two-group kernel)
   const float mo = rowstat[(hs ^ 1) * QT + r], so = rowstat[2 * QT + (hs ^ 1) * QT + r];
   const float mrow = fmaxf(mw, mo);
   float tot = 0.f;
   if (mw != -INFINITY) tot += sw * exp2f(mw - mrow);
   if (mo != -INFINITY) tot += so * exp2f(mo - mrow);
   const float inv = tot > 0.f ? 1.f / tot : 0.f;
-  ts[4] = clock64();
 
   // p = e * exp2(m_c - m) / sum -> HBM (bf16, one 32-byte sector per thread and chunk); dropout(p) -> K-major A operand
   const long long rg = ((long long)h * a.B + b) * a.Tq + i;  // row of the head-major [H,B,Tq,ld_p] tensors
@@ -318,8 +241,103 @@ relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_cons
   }
   fence_async_smem();
   tcgen05_fence_before();
-  __syncthreads();
+  group_sync(bar_id);
 
+}
+
+__global__ void __launch_bounds__(NTHREADS, 2)
+relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_constant__ CUtensorMap map_qv,
+                   const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                   const __grid_constant__ CUtensorMap map_pos, const AttnArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  if (sbase & 1023u) __trap();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nqt = (a.Tq + QT - 1) / QT;
+  const int qt = blockIdx.x % nqt, hb = blockIdx.x / nqt, h = hb % a.H, b = hb / a.H;
+  const int i0 = qt * QT;
+  const int TKP = a.TKP, WIN = a.WIN;
+  const uint32_t bar_qk = sbase + a.off_bar, bar_v = bar_qk + 8, bar_s = bar_qk + 16, bar_o = bar_qk + 24;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + a.off_bar + 32);
+  float* rowstat = reinterpret_cast<float*>(smem + a.off_bar + 64);  // [2 halves][128 rows] max, then the same for sums
+  const uint32_t s_qu = sbase, s_qv = sbase + QT * 128, s_k = sbase + a.off_k, s_p = sbase + a.off_p, s_v = sbase + a.off_v;
+
+  long long ts[8];
+  ts[0] = clock64();
+  b2_pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qu) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    if (a.rel) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qv) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_pos) : "memory");
+    }
+    mbar_init(bar_qk, 1);
+    mbar_init(bar_v, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // every operand of the tile is requested before this CTA queues for tensor memory
+    b2_pdl_wait();
+    mbar_expect_tx(bar_qk, (uint32_t)(QT * 128 * (a.rel ? 2 : 1) + TKP * 128 + (a.rel ? WIN * 128 : 0)));
+    tma_load_3d(s_qu, &map_qu, bar_qk, h * DK, i0, b);
+    tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
+    if (a.rel) {
+      tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
+      const int c0 = a.Tq - 1 - i0 - (QT - 1);  // may be negative: out-of-range rows are zero-filled
+      tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
+      tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
+    }
+    mbar_expect_tx(bar_v, (uint32_t)(TKP * 128));
+    tma_load_3d(s_v, &map_v, bar_v, h * DK, 0, b);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(a.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // global scalars of the softmax (valid length, dropout key): fetched here so their latency hides behind the TMA loads
+  b2_pdl_wait();
+  const int len_b = a.lens != nullptr ? min(a.lens[b], a.Tk) : a.Tk;
+  B2DropKey dk = {0ull, 0u, 1.f};
+  const bool dropping = a.drop.p > 0.f;
+  if (dropping) dk = dropout_key(a.drop);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  ts[1] = clock64();
+
+  // ---------------------------------------------------------------- scores: ac (and bd) into tensor memory
+  if (threadIdx.x == 0) {
+    mbar_wait(bar_qk, 0);
+    tcgen05_fence_after();
+    const uint32_t id_ac = make_idesc(TKP, 0, 0, QT);
+#pragma unroll
+    for (int kk = 0; kk < DK / 16; ++kk)
+      umma_bf16(tmem_base, make_smem_desc(s_qu + kk * 32, 16, 1024), make_smem_desc(s_k + kk * 32, 16, 1024), id_ac, kk != 0);
+    if (a.rel) {
+      const uint32_t id_bd = make_idesc(WIN / 2, 0, 0, QT);
+      for (int half = 0; half < 2; ++half) {
+#pragma unroll
+        for (int kk = 0; kk < DK / 16; ++kk)
+          umma_bf16(tmem_base + TKP + half * (WIN / 2), make_smem_desc(s_qv + kk * 32, 16, 1024),
+                    make_smem_desc(s_p + half * (WIN / 2) * 128 + kk * 32, 16, 1024), id_bd, kk != 0);
+      }
+    }
+    umma_commit(bar_s);
+  }
+  mbar_wait(bar_s, 0);
+  tcgen05_fence_after();
+  ts[2] = clock64();
+
+  softmax_tile(a, smem, sbase, threadIdx.x, 0, tmem_base, rowstat, i0, h, b, len_b, dk, 0u);
+  const int q = warp & 3, hs = warp >> 2;
+  const int r = q * 32 + lane, i = i0 + r;
+  const bool row_ok = i < a.Tq;
+  const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+  ts[3] = ts[4] = clock64();
   ts[5] = clock64();
   // ---------------------------------------------------------------- context: O = P . V
   const uint32_t t_o = tmem_base + TKP;  // the bd window is dead
@@ -359,6 +377,159 @@ relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_cons
   if (warp == 1) {
     tcgen05_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(a.tmem_cols) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Two tiles per SM in flight.  The one-tile kernel above lets two CTAs share an SM, but its 448 score columns make tensor
+// memory exclusive, so the CTAs take turns and every phase runs as a latency chain of 8 warps.  Here ONE persistent CTA
+// of 16 warps owns all 512 columns and runs two groups of 8 warps, each with its own shared-memory region, on alternate
+// tiles.  Only two things are shared and handed back and forth through mbarriers: the score columns [0, 448) (from the
+// score MMAs until the softmax pass has read them) and the context columns [448, 512) (from the P.V MMAs until the
+// epilogue has read them).  A group's finalise / P.V / epilogue therefore overlaps the other group's loads / score MMAs /
+// softmax pass.
+constexpr int PIPE_O_COL = 448;
+constexpr int PIPE_CTL_BYTES = 128 + 2 * 4 * QT * 4;
+
+__global__ void __launch_bounds__(2 * NTHREADS, 1)
+relattn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_constant__ CUtensorMap map_qv,
+                        const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                        const __grid_constant__ CUtensorMap map_pos, const AttnArgs a, int num_tiles) {
+  extern __shared__ __align__(1024) uint8_t smem_all[];
+  const uint32_t sall = smem_u32(smem_all);
+  if (sall & 1023u) __trap();
+  const int g = threadIdx.x >> 8, tid = threadIdx.x & 255, warp = tid >> 5, lane = tid & 31;
+  const uint32_t region = a.off_bar;  // one tile's operands (the one-tile kernel's layout), a multiple of 1024 bytes
+  uint8_t* smem = smem_all + (size_t)g * region;
+  const uint32_t sbase = sall + g * region, ctl = sall + 2 * region;
+  const uint32_t bar_qk = ctl + g * 32, bar_v = bar_qk + 8, bar_s = bar_qk + 16, bar_o = bar_qk + 24;
+  const uint32_t s_free = ctl + 64, o_free = ctl + 80;  // [2] each: "group g may use the score / context columns"
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_all + 2 * (size_t)region + 96);
+  float* rowstat = reinterpret_cast<float*>(smem_all + 2 * (size_t)region + 128) + g * 4 * QT;
+  const int TKP = a.TKP, WIN = a.WIN;
+  const uint32_t s_qu = sbase, s_qv = sbase + QT * 128, s_k = sbase + a.off_k, s_p = sbase + a.off_p, s_v = sbase + a.off_v;
+  const int nqt = (a.Tq + QT - 1) / QT;
+
+  b2_pdl_launch_dependents();
+  if (threadIdx.x == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qu) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    if (a.rel) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qv) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_pos) : "memory");
+    }
+    for (int i = 0; i < 12; ++i) mbar_init(ctl + i * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_arrive(s_free);  // group 0 goes first
+    mbar_arrive(o_free);
+  }
+  if ((threadIdx.x >> 5) == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  b2_pdl_wait();
+  B2DropKey dk = {0ull, 0u, 1.f};
+  if (a.drop.p > 0.f) dk = dropout_key(a.drop);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t t_s = tmem_base, t_o = tmem_base + PIPE_O_COL;
+
+  const int n_c = (int)blockIdx.x < num_tiles ? (num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;  // this CTA's tiles
+  const int n_iter = (n_c + 1) / 2;
+  const int q = warp & 3, hs = warp >> 2;
+  int kdone = 0;  // tiles this group has run: parity of its own barriers
+  for (int it = 0; it < n_iter; ++it) {
+    const int j = 2 * it + g;
+    const uint32_t tokpar = (uint32_t)(it & 1);
+    if (j >= n_c) {  // odd tile count: keep the hand-over going
+      if (tid == 0) {
+        mbar_wait(s_free + g * 8, tokpar);
+        mbar_arrive(s_free + (g ^ 1) * 8);
+        mbar_wait(o_free + g * 8, tokpar);
+        mbar_arrive(o_free + (g ^ 1) * 8);
+      }
+      continue;
+    }
+    const int tile = (int)blockIdx.x + j * (int)gridDim.x;
+    const int qt = tile % nqt, hb = tile / nqt, h = hb % a.H, b = hb / a.H;
+    const int i0 = qt * QT;
+    const uint32_t par = (uint32_t)(kdone & 1);
+    if (tid == 0) {
+      mbar_expect_tx(bar_qk, (uint32_t)(QT * 128 * (a.rel ? 2 : 1) + TKP * 128 + (a.rel ? WIN * 128 : 0)));
+      tma_load_3d(s_qu, &map_qu, bar_qk, h * DK, i0, b);
+      tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
+      if (a.rel) {
+        tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
+        const int c0 = a.Tq - 1 - i0 - (QT - 1);
+        tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
+        tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
+      }
+      mbar_expect_tx(bar_v, (uint32_t)(TKP * 128));
+      tma_load_3d(s_v, &map_v, bar_v, h * DK, 0, b);
+    }
+    const int len_b = a.lens != nullptr ? min(a.lens[b], a.Tk) : a.Tk;
+    if (tid == 0) {
+      mbar_wait(bar_qk, par);
+      mbar_wait(s_free + g * 8, tokpar);  // the other group's softmax pass has read its scores
+      tcgen05_fence_after();
+      const uint32_t id_ac = make_idesc(TKP, 0, 0, QT);
+#pragma unroll
+      for (int kk = 0; kk < DK / 16; ++kk)
+        umma_bf16(t_s, make_smem_desc(s_qu + kk * 32, 16, 1024), make_smem_desc(s_k + kk * 32, 16, 1024), id_ac, kk != 0);
+      if (a.rel) {
+        const uint32_t id_bd = make_idesc(WIN / 2, 0, 0, QT);
+        for (int half = 0; half < 2; ++half) {
+#pragma unroll
+          for (int kk = 0; kk < DK / 16; ++kk)
+            umma_bf16(t_s + TKP + half * (WIN / 2), make_smem_desc(s_qv + kk * 32, 16, 1024),
+                      make_smem_desc(s_p + half * (WIN / 2) * 128 + kk * 32, 16, 1024), id_bd, kk != 0);
+        }
+      }
+      umma_commit(bar_s);
+    }
+    mbar_wait(bar_s, par);
+    tcgen05_fence_after();
+    softmax_tile(a, smem, sbase, tid, 1 + g, t_s, rowstat, i0, h, b, len_b, dk, s_free + (g ^ 1) * 8);
+    if (tid == 0) {
+      mbar_wait(bar_v, par);
+      mbar_wait(o_free + g * 8, tokpar);  // the other group's epilogue has read its context rows
+      tcgen05_fence_after();
+      const uint32_t id_o = make_idesc(DK, 0, 1, QT);
+      for (int ks = 0; ks < TKP / 16; ++ks)
+        umma_bf16(t_o, make_smem_desc(sbase + (uint32_t)(ks >> 2) * (QT * 128) + (ks & 3) * 32, 16, 1024),
+                  make_smem_desc(s_v + ks * 2048, 64 * DK * 2, 1024), id_o, ks != 0);
+      umma_commit(bar_o);
+    }
+    mbar_wait(bar_o, par);
+    tcgen05_fence_after();
+    uint32_t o[32];
+    tmem_ld32(t_o + ((uint32_t)(q * 32) << 16) + hs * 32, o);
+    tmem_ld_wait();
+    tcgen05_fence_before();
+    fence_async_smem();  // this tile's ring / P operand writes are ordered before the next tile's TMA loads into the same bytes
+    group_sync(1 + g);
+    if (tid == 0) mbar_arrive(o_free + (g ^ 1) * 8);
+    const int i = i0 + q * 32 + lane;
+    if (i < a.Tq) {
+      bf16* dst = a.ctx + ((long long)b * a.Tq + i) * a.ldctx + h * DK + hs * 32;
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(o[gq * 8 + e]) * dk.inv;
+        store8_bf16(dst + gq * 8, v);
+      }
+    }
+    ++kdone;
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if ((threadIdx.x >> 5) == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
   }
 }
 
@@ -469,6 +640,7 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
   static bool configured = false;
   if (!configured) {
     B2_CUDA(cudaFuncSetAttribute(relattn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B2_CUDA(cudaFuncSetAttribute(relattn_fwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     configured = true;
   }
   const int nqt = (Tq + QT - 1) / QT;
@@ -481,6 +653,17 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
     if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 512 * 8 * sizeof(long long)));
     B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 512 * 8 * sizeof(long long), st));
     a.dbg = dbg_buf;
+  }
+  static const int force_pipe = getenv("B200SLU_ATTN_PIPE") ? atoi(getenv("B200SLU_ATTN_PIPE")) : -1;  // tuning: 0 / 1
+  const size_t smem_pipe = 2 * (size_t)a.off_bar + PIPE_CTL_BYTES;
+  const int num_tiles = B * H * nqt;
+  // plain mode needs <= 256 columns: two one-tile CTAs already run side by side on an SM (measured 74 vs 78 us)
+  if (!dbg && force_pipe != 0 && (rel || force_pipe == 1) && smem_pipe <= 232448 && (!rel || a.TKP + a.WIN <= PIPE_O_COL)) {
+    const int sms = b2_num_sms();
+    const int grid = (num_tiles + 1) / 2 < sms ? (num_tiles + 1) / 2 : sms;
+    B2_CUDA(b2_launch(relattn_fwd_pipe_kernel, dim3((unsigned)grid), dim3(2 * NTHREADS), smem_pipe, st, mqu, mqv, mk, mv, mp, a,
+                      num_tiles));
+    return 0;
   }
   B2_CUDA(b2_launch(relattn_fwd_kernel, dim3((unsigned)(B * H * nqt)), dim3(NTHREADS), smem, st, mqu, mqv, mk, mv, mp, a));
   if (dbg) {
