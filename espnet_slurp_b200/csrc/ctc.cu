@@ -19,6 +19,7 @@
 //                                   dependence on the total likelihood), scattered into a shared-memory
 //                                   row and fused with softmax: grad = scale * (softmax - occ).
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -115,103 +116,114 @@ __device__ __forceinline__ float warp_max_fast(float x) {
   return __int_as_float(i);
 }
 
-template <int C, int D>  // C states per lane (S <= 32*C); D frames of emission prefetch
-__global__ void __launch_bounds__(64) ctc_lattice_kernel(const float* __restrict__ em, int T, int Smax,
-                                                         const int* __restrict__ hlens, const int* __restrict__ labels, int Lmax,
-                                                         const int* __restrict__ llens, int blank, float* __restrict__ alpha,
-                                                         float* __restrict__ beta, float* __restrict__ nll) {
-  const int b = blockIdx.x, lane = threadIdx.x & 31, dir = threadIdx.x >> 5;  // dir 0 = alpha, 1 = beta
-  const int Tb = hlens[b], L = llens[b], S = 2 * L + 1;
-  const int* lab = labels + (long long)b * Lmax;
-  const float* eb = em + (long long)b * T * Smax;
-  float* out = (dir == 0 ? alpha : beta) + (long long)b * T * Smax;
-  if (Tb <= 0 || Tb > T || L > Lmax || S > 32 * C) {
-    if (dir == 0 && lane == 0) nll[b] = INFINITY;  // infeasible -> zeroed by the caller-visible flag path
-    return;
-  }
+// One direction of the recursion (DIR 0 = alpha, forward in time; 1 = beta, backward) for one utterance, run by one warp.
+// The recursion is a single-warp latency chain, so what a frame costs is its instruction count: the direction is a
+// template parameter (no per-frame branches), the main loop runs whole groups of D frames without bounds checks (the
+// prefetch of frame n + D clamps its frame number instead of predicating the load), the < D tail frames use the
+// emissions already held in registers, and dead states carry an emission of -1e30 so they need no select.
+template <int C, int D, int DIR, bool PEEL>  // C states per lane (S <= 32*C); D frames of emission prefetch
+__device__ __forceinline__ void lattice_run(const float* __restrict__ eb, int Smax, int Tb, int S, const int* __restrict__ lab,
+                                            int lane, float* __restrict__ out, float* __restrict__ nll) {
   const int s0 = lane * C;
   // skip-arc permission of the state a transition ENTERS: alpha uses skip[s] (s-2 -> s); beta uses skip[s+2]
-  bool skip[C];
+  bool skip[C], live[C];
 #pragma unroll
   for (int i = 0; i < C; ++i) {
-    const int s = dir == 0 ? s0 + i : s0 + i + 2;
+    const int s = DIR == 0 ? s0 + i : s0 + i + 2;
     skip[i] = (s < S) && (s & 1) && s > 1 && (lab[s >> 1] != lab[(s >> 1) - 1]);
+    live[i] = s0 + i < S;
   }
+  const int t_first = DIR == 0 ? 0 : Tb - 1;
+  const int step = DIR == 0 ? 1 : -1;
+  const float* const e0 = eb + s0;  // + frame * Smax
+  float* op = out + (long long)t_first * Smax + s0;
+  const long long ostep = DIR == 0 ? Smax : -Smax;
   float a[C];
   float e[D][C];  // emissions of the next D frames: the loads are D frames ahead of their use (L2 latency off the chain)
   double offset = 0.0;
-  const int t_first = dir == 0 ? 0 : Tb - 1;
-  const int step = dir == 0 ? 1 : -1;
 #pragma unroll
   for (int i = 0; i < C; ++i) {
     const int s = s0 + i;
-    const bool init = dir == 0 ? (s < 2) : (s >= S - 2);
-    a[i] = (s < S && init) ? eb[(long long)t_first * Smax + s] : NEG_BIG;
+    const bool init = DIR == 0 ? (s < 2) : (s >= S - 2);
+    a[i] = (live[i] && init) ? e0[(long long)t_first * Smax + i] : NEG_BIG;
   }
+  auto load_frame = [&](int n, float (&dst)[C]) {  // emissions of the n-th frame of the walk (clamped to the last one)
+    const float* src = e0 + (t_first + min(n, Tb - 1) * step) * Smax;
 #pragma unroll
-  for (int j = 0; j < D; ++j) {
-    const int nn = 1 + j;
+    for (int i = 0; i < C; ++i) dst[i] = live[i] ? src[i] : NEG_BIG;
+  };
 #pragma unroll
-    for (int i = 0; i < C; ++i)
-      e[j][i] = (nn < Tb && s0 + i < S) ? eb[(long long)(t_first + nn * step) * Smax + s0 + i] : 0.f;
-  }
+  for (int j = 0; j < D; ++j) load_frame(1 + j, e[j]);
   // renormalise the row by its maximum (one redux instruction) and store it
-  auto renorm_store = [&](int t) {
-    float m = NEG_BIG;
+  auto renorm_store = [&]() {
+    float m = a[0];
 #pragma unroll
-    for (int i = 0; i < C; ++i) m = fmaxf(m, a[i]);
+    for (int i = 1; i < C; ++i) m = fmaxf(m, a[i]);
     m = warp_max_fast(m);
     offset += (double)m;  // an impossible row (m ~ -1e30) drives the total below -1e29: reported as infeasible
 #pragma unroll
     for (int i = 0; i < C; ++i) a[i] = fmaxf(a[i] - m, NEG_BIG);
 #pragma unroll
     for (int i = 0; i < C; ++i)
-      if (s0 + i < S) out[(long long)t * Smax + s0 + i] = a[i];
+      if (live[i]) op[i] = a[i];
   };
-  renorm_store(t_first);
-  for (int n0 = 1; n0 < Tb; n0 += D) {
+  const bool edge = DIR == 0 ? lane == 0 : lane == 31;
+  const bool edge2 = DIR == 0 ? lane == 1 : lane == 30;  // C == 1: the second neighbour comes from two lanes away
+  auto frame = [&](const float (&em)[C]) {
+    // neighbours across the chunk boundary -- alpha: states s0-1, s0-2 ; beta: states s0+C, s0+C+1
+    float p1, p2;
+    if (DIR == 0) {
+      p1 = __shfl_up_sync(0xffffffffu, a[C - 1], 1);
+      p2 = C >= 2 ? __shfl_up_sync(0xffffffffu, a[C >= 2 ? C - 2 : 0], 1) : __shfl_up_sync(0xffffffffu, a[0], 2);
+    } else {
+      p1 = __shfl_down_sync(0xffffffffu, a[0], 1);
+      p2 = C >= 2 ? __shfl_down_sync(0xffffffffu, a[C >= 2 ? 1 : 0], 1) : __shfl_down_sync(0xffffffffu, a[0], 2);
+    }
+    p1 = edge ? NEG_BIG : p1;
+    p2 = (edge || (C < 2 && edge2)) ? NEG_BIG : p2;
+    if (DIR == 0) {
 #pragma unroll
-    for (int j = 0; j < D; ++j) {
-      const int n = n0 + j;
-      if (n >= Tb) break;
-      const int t = t_first + n * step;
-      // neighbours across the chunk boundary
-      float p1, p2;  // alpha: states s0-1, s0-2 ; beta: states s0+C, s0+C+1
-      if (dir == 0) {
-        p1 = __shfl_up_sync(0xffffffffu, a[C - 1], 1);
-        p2 = C >= 2 ? __shfl_up_sync(0xffffffffu, a[C >= 2 ? C - 2 : 0], 1) : __shfl_up_sync(0xffffffffu, a[0], 2);
-        if (lane == 0) p1 = p2 = NEG_BIG;
-        if (C < 2 && lane == 1) p2 = NEG_BIG;
-#pragma unroll
-        for (int i = C - 1; i >= 0; --i) {
-          const float m1 = i >= 1 ? a[i >= 1 ? i - 1 : 0] : p1;
-          const float m2 = i >= 2 ? a[i >= 2 ? i - 2 : 0] : (i == 1 ? p1 : p2);
-          const float v = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG);
-          a[i] = (s0 + i < S) ? v + e[j][i] : NEG_BIG;
-        }
-      } else {
-        p1 = __shfl_down_sync(0xffffffffu, a[0], 1);
-        p2 = C >= 2 ? __shfl_down_sync(0xffffffffu, a[C >= 2 ? 1 : 0], 1) : __shfl_down_sync(0xffffffffu, a[0], 2);
-        if (lane == 31) p1 = p2 = NEG_BIG;
-        if (C < 2 && lane == 30) p2 = NEG_BIG;
-#pragma unroll
-        for (int i = 0; i < C; ++i) {
-          const float m1 = i + 1 < C ? a[i + 1 < C ? i + 1 : 0] : p1;
-          const float m2 = i + 2 < C ? a[i + 2 < C ? i + 2 : 0] : (i + 2 == C ? p1 : p2);
-          const float v = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG);
-          a[i] = (s0 + i < S) ? v + e[j][i] : NEG_BIG;
-        }
+      for (int i = C - 1; i >= 0; --i) {
+        const float m1 = i >= 1 ? a[i >= 1 ? i - 1 : 0] : p1;
+        const float m2 = i >= 2 ? a[i >= 2 ? i - 2 : 0] : (i == 1 ? p1 : p2);
+        a[i] = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG) + em[i];
       }
-      // refill this slot with the emissions of frame n + D
-      const int nf = n + D;
-      if (nf < Tb) {
+    } else {
 #pragma unroll
-        for (int i = 0; i < C; ++i) e[j][i] = (s0 + i < S) ? eb[(long long)(t_first + nf * step) * Smax + s0 + i] : 0.f;
+      for (int i = 0; i < C; ++i) {
+        const float m1 = i + 1 < C ? a[i + 1 < C ? i + 1 : 0] : p1;
+        const float m2 = i + 2 < C ? a[i + 2 < C ? i + 2 : 0] : (i + 2 == C ? p1 : p2);
+        a[i] = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG) + em[i];
       }
-      renorm_store(t);
+    }
+  };
+  renorm_store();
+  int n = 1;
+  if (PEEL) {
+    for (; n + D <= Tb; n += D) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        frame(e[j]);
+        load_frame(n + j + D, e[j]);  // refill this slot with the emissions of frame n + j + D
+        op += ostep;
+        renorm_store();
+      }
     }
   }
-  if (dir == 0) {
+  // PEEL: the last Tb - n < D frames.  Otherwise (many states per lane: the frame body is ~500 instructions and a second
+  // copy of it does not pay) the whole walk, with the per-frame bound check.
+  for (; n < Tb; n += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      if (n + j < Tb) {
+        frame(e[j]);
+        load_frame(n + j + D, e[j]);
+        op += ostep;
+        renorm_store();
+      }
+    }
+  }
+  if (DIR == 0) {
     // log-likelihood = offsets + lse(alpha~(S-1), alpha~(S-2)) at the last frame
     float fin = NEG_BIG;
 #pragma unroll
@@ -223,9 +235,187 @@ __global__ void __launch_bounds__(64) ctc_lattice_kernel(const float* __restrict
     sum = warp_sum(sum);
     if (lane == 0) {
       const double ll2 = offset + (double)mx + log2((double)sum);  // log2 of the sequence likelihood
-      nll[b] = (ll2 < -1.0e29) ? INFINITY : (float)(-ll2 * 0.6931471805599453);  // +inf when infeasible (zero_infinity later)
+      *nll = (ll2 < -1.0e29) ? INFINITY : (float)(-ll2 * 0.6931471805599453);  // +inf when infeasible (zero_infinity later)
     }
   }
+}
+
+template <int C, int D>
+__global__ void __launch_bounds__(64) ctc_lattice_kernel(const float* __restrict__ em, int T, int Smax,
+                                                         const int* __restrict__ hlens, const int* __restrict__ labels, int Lmax,
+                                                         const int* __restrict__ llens, int blank, float* __restrict__ alpha,
+                                                         float* __restrict__ beta, float* __restrict__ nll) {
+  const int b = blockIdx.x, lane = threadIdx.x & 31, dir = threadIdx.x >> 5;  // dir 0 = alpha, 1 = beta
+  const int Tb = hlens[b], L = llens[b], S = 2 * L + 1;
+  const int* lab = labels + (long long)b * Lmax;
+  const float* eb = em + (long long)b * T * Smax;
+  if (Tb <= 0 || Tb > T || L > Lmax || S > 32 * C) {
+    if (dir == 0 && lane == 0) nll[b] = INFINITY;  // infeasible -> zeroed by the caller-visible flag path
+    return;
+  }
+  if (dir == 0) lattice_run<C, D, 0, (C <= 8)>(eb, Smax, Tb, S, lab, lane, alpha + (long long)b * T * Smax, nll + b);
+  else lattice_run<C, D, 1, (C <= 8)>(eb, Smax, Tb, S, lab, lane, beta + (long long)b * T * Smax, nll + b);
+}
+
+// Long label sequences (S > 128 states): W warps per direction share the lattice (C states per lane, 32 * W * C >= S), so
+// the per-frame chain is C = 4..5 states long instead of 8..20.  A frame costs ONE named barrier: every warp publishes
+// its un-normalised boundary states and its row maximum, and after the barrier each warp reads all W maxima (the row
+// normaliser is global, so every warp subtracts the same value) and its neighbour's boundary states for the next frame
+// (slots double-buffered by frame parity).
+template <int C, int D, int DIR, int W>
+__device__ __forceinline__ void lattice_run_mw(const float* __restrict__ eb, int Smax, int Tb, int S, const int* __restrict__ lab,
+                                               int w, int lane, float* __restrict__ out, float* __restrict__ nll,
+                                               float (*slot)[W][4] /* [2 parities][W][4] */, int bar_id) {
+  static_assert(C >= 2, "multi-warp lattice: at least two states per lane");
+  const int s0 = (w * 32 + lane) * C;
+  bool skip[C], live[C];
+#pragma unroll
+  for (int i = 0; i < C; ++i) {
+    const int s = DIR == 0 ? s0 + i : s0 + i + 2;
+    skip[i] = (s < S) && (s & 1) && s > 1 && (lab[s >> 1] != lab[(s >> 1) - 1]);
+    live[i] = s0 + i < S;
+  }
+  const int t_first = DIR == 0 ? 0 : Tb - 1;
+  const int step = DIR == 0 ? 1 : -1;
+  const float* const e0 = eb + s0;
+  float* op = out + (long long)t_first * Smax + s0;
+  const long long ostep = DIR == 0 ? Smax : -Smax;
+  float a[C], e[D][C];
+  double offset = 0.0;
+#pragma unroll
+  for (int i = 0; i < C; ++i) {
+    const int s = s0 + i;
+    const bool init = DIR == 0 ? (s < 2) : (s >= S - 2);
+    a[i] = (live[i] && init) ? e0[(long long)t_first * Smax + i] : NEG_BIG;
+  }
+  auto load_frame = [&](int n, float (&dst)[C]) {
+    const float* src = e0 + (t_first + min(n, Tb - 1) * step) * Smax;
+#pragma unroll
+    for (int i = 0; i < C; ++i) dst[i] = live[i] ? src[i] : NEG_BIG;
+  };
+#pragma unroll
+  for (int j = 0; j < D; ++j) load_frame(1 + j, e[j]);
+  const int wn = DIR == 0 ? w - 1 : w + 1;                 // the warp whose boundary states this warp's edge lane needs
+  const bool has_nb = DIR == 0 ? w > 0 : w < W - 1;
+  const bool edge = DIR == 0 ? lane == 0 : lane == 31;
+  const bool pub = DIR == 0 ? lane == 31 : lane == 0;      // the lane that owns the states the next warp needs
+  float nb1 = NEG_BIG, nb2 = NEG_BIG;                       // neighbour warp's boundary states of the previous frame, normalised
+  int par = 0;
+  auto publish_renorm_store = [&]() {
+    float m = a[0];
+#pragma unroll
+    for (int i = 1; i < C; ++i) m = fmaxf(m, a[i]);
+    m = warp_max_fast(m);
+    if (pub) {
+      slot[par][w][0] = DIR == 0 ? a[C - 1] : a[0];
+      slot[par][w][1] = DIR == 0 ? a[C - 2] : a[1];
+      slot[par][w][2] = m;
+    }
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(W * 32) : "memory");
+    float mg = slot[par][0][2];
+#pragma unroll
+    for (int v = 1; v < W; ++v) mg = fmaxf(mg, slot[par][v][2]);
+    if (has_nb) {
+      nb1 = fmaxf(slot[par][wn][0] - mg, NEG_BIG);
+      nb2 = fmaxf(slot[par][wn][1] - mg, NEG_BIG);
+    }
+    offset += (double)mg;
+#pragma unroll
+    for (int i = 0; i < C; ++i) a[i] = fmaxf(a[i] - mg, NEG_BIG);
+#pragma unroll
+    for (int i = 0; i < C; ++i)
+      if (live[i]) op[i] = a[i];
+    par ^= 1;
+  };
+  auto frame = [&](const float (&em)[C]) {
+    float p1, p2;
+    if (DIR == 0) {
+      p1 = __shfl_up_sync(0xffffffffu, a[C - 1], 1);
+      p2 = __shfl_up_sync(0xffffffffu, a[C - 2], 1);
+    } else {
+      p1 = __shfl_down_sync(0xffffffffu, a[0], 1);
+      p2 = __shfl_down_sync(0xffffffffu, a[1], 1);
+    }
+    p1 = edge ? nb1 : p1;
+    p2 = edge ? nb2 : p2;
+    if (DIR == 0) {
+#pragma unroll
+      for (int i = C - 1; i >= 0; --i) {
+        const float m1 = i >= 1 ? a[i >= 1 ? i - 1 : 0] : p1;
+        const float m2 = i >= 2 ? a[i >= 2 ? i - 2 : 0] : (i == 1 ? p1 : p2);
+        a[i] = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG) + em[i];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < C; ++i) {
+        const float m1 = i + 1 < C ? a[i + 1 < C ? i + 1 : 0] : p1;
+        const float m2 = i + 2 < C ? a[i + 2 < C ? i + 2 : 0] : (i + 2 == C ? p1 : p2);
+        a[i] = lse3(a[i], m1, skip[i] ? m2 : NEG_BIG) + em[i];
+      }
+    }
+  };
+  publish_renorm_store();
+  int n = 1;
+  for (; n + D <= Tb; n += D) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      frame(e[j]);
+      load_frame(n + j + D, e[j]);
+      op += ostep;
+      publish_renorm_store();
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < D; ++j) {  // Tb is the same for every warp of the utterance: the barrier count stays matched
+    if (n + j < Tb) {
+      frame(e[j]);
+      op += ostep;
+      publish_renorm_store();
+    }
+  }
+  if (DIR == 0) {
+    float fin = NEG_BIG;
+#pragma unroll
+    for (int i = 0; i < C; ++i)
+      if (s0 + i == S - 1 || s0 + i == S - 2) fin = lse2(fin, a[i]);
+    const float mx = warp_max(fin);
+    float sum = ex2_(fin - mx);
+    sum = warp_sum(sum);
+    if (lane == 0) {  // `par` is the buffer nobody reads any more
+      slot[par][w][0] = mx;
+      slot[par][w][1] = sum;
+    }
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(W * 32) : "memory");
+    if (w == 0 && lane == 0) {
+      float M = slot[par][0][0];
+#pragma unroll
+      for (int v = 1; v < W; ++v) M = fmaxf(M, slot[par][v][0]);
+      float tot = 0.f;
+#pragma unroll
+      for (int v = 0; v < W; ++v) tot += slot[par][v][1] * ex2_(slot[par][v][0] - M);
+      const double ll2 = offset + (double)M + log2((double)tot);
+      *nll = (ll2 < -1.0e29) ? INFINITY : (float)(-ll2 * 0.6931471805599453);
+    }
+  }
+}
+
+template <int C, int D, int W>
+__global__ void __launch_bounds__(64 * W) ctc_lattice_mw_kernel(const float* __restrict__ em, int T, int Smax,
+                                                                const int* __restrict__ hlens, const int* __restrict__ labels,
+                                                                int Lmax, const int* __restrict__ llens, int blank,
+                                                                float* __restrict__ alpha, float* __restrict__ beta,
+                                                                float* __restrict__ nll) {
+  __shared__ float slot[2][2][W][4];  // [direction][frame parity][warp][boundary 1, boundary 2, row max, -]
+  const int b = blockIdx.x, lane = threadIdx.x & 31, wi = threadIdx.x >> 5, dir = wi / W, w = wi % W;
+  const int Tb = hlens[b], L = llens[b], S = 2 * L + 1;
+  const int* lab = labels + (long long)b * Lmax;
+  const float* eb = em + (long long)b * T * Smax;
+  if (Tb <= 0 || Tb > T || L > Lmax || S > 32 * W * C) {
+    if (threadIdx.x == 0) nll[b] = INFINITY;
+    return;
+  }
+  if (dir == 0) lattice_run_mw<C, D, 0, W>(eb, Smax, Tb, S, lab, w, lane, alpha + (long long)b * T * Smax, nll + b, slot[0], 1);
+  else lattice_run_mw<C, D, 1, W>(eb, Smax, Tb, S, lab, w, lane, beta + (long long)b * T * Smax, nll + b, slot[1], 2);
 }
 
 // nll_raw (+inf if infeasible) -> loss (0 if infeasible) + feasibility flag; loss_sum = sum_b loss_b (one block)
@@ -343,14 +533,34 @@ extern "C" int b200slu_ctc_fwd(const float* logits, long long ldv, int B, int T,
   ctc_prep_kernel<<<dim3(T, B), 256, 0, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, lse, em,
                                               Smax);
   B2_LAUNCH_CHECK();
-#define LAT(C)                                                                                                              \
-  ctc_lattice_kernel<C, (C <= 8 ? 4 : 2)><<<B, 64, 0, st>>>(em, T, Smax, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, alpha, beta, \
-                                          nll_raw)
-  if (Smax <= 64) LAT(2);
-  else if (Smax <= 128) LAT(4);
-  else if (Smax <= 256) LAT(8);
-  else LAT(20);
+  // D = frames of emission prefetch: the recursion is a latency chain (~170 cycles per frame at C = 2), the emission
+  // rows come from L2 / HBM (~1000-2500 cycles away once the logits have streamed through L2), so D * frame time has
+  // to cover that latency.
+  static const int force_d = getenv("B200SLU_CTC_D") ? atoi(getenv("B200SLU_CTC_D")) : 0;  // tuning experiments only
+#define LAT2(C, D)                                                                                                          \
+  ctc_lattice_kernel<C, D><<<B, 64, 0, st>>>(em, T, Smax, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, alpha, beta, \
+                                             nll_raw)
+#define LAT(C, DDEF)                                   \
+  do {                                                 \
+    const int d_ = force_d > 0 ? force_d : DDEF;       \
+    if (d_ >= 16 && C <= 4) LAT2(C, 16);               \
+    else if (d_ >= 8 && C <= 8) LAT2(C, 8);            \
+    else if (d_ >= 4) LAT2(C, 4);                      \
+    else LAT2(C, 2);                                   \
+  } while (0)
+  static const int no_mw = getenv("B200SLU_CTC_NO_MW") != nullptr;  // tuning experiments only
+#define LATMW(C, D, W)                                                                                                       \
+  ctc_lattice_mw_kernel<C, D, W><<<B, 64 * W, 0, st>>>(em, T, Smax, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, alpha, \
+                                                       beta, nll_raw)
+  if (Smax <= 64) LAT(2, 16);
+  else if (Smax <= 128) LAT(4, 8);
+  else if (no_mw && Smax <= 256) LAT(8, 4);
+  else if (no_mw) LAT(20, 2);
+  else if (Smax <= 256) LATMW(4, 8, 2);
+  else LATMW(5, 8, 4);
+#undef LATMW
 #undef LAT
+#undef LAT2
   B2_LAUNCH_CHECK();
   ctc_finish_kernel<<<1, 256, 0, st>>>(nll_raw, B, loss_per_utt, feasible, loss_sum);
   B2_LAUNCH_CHECK();

@@ -53,7 +53,9 @@ def torch_ctc(logits, hlens, labels, llens, dtype):
 @pytest.mark.parametrize("B,T,V,Lmax,kw", [
     (3, 17, 7, 4, {}), (2, 10, 10, 5, {}), (8, 124, 600, 20, {}), (4, 60, 50, 30, {"infeasible": True}),
     (4, 300, 100, 60, {}), (4, 500, 64, 120, {}), (3, 700, 40, 300, {}), (5, 90, 33, 12, {"empty": True}),
-    (6, 468, 5000, 60, {})])
+    (6, 468, 5000, 60, {}),
+    # label sequences long enough for the multi-warp lattice (2 and 4 warps per direction), with the edge cases again
+    (4, 400, 50, 100, {"infeasible": True}), (4, 450, 30, 200, {"empty": True}), (3, 330, 21, 160, {})])
 def test_ctc_vs_torch_fp64(B, T, V, Lmax, kw):
     logits, hlens, labels, llens = ctc_case(B, T, V, Lmax, seed=B * T + V, **kw)
     ldv = E.round8(V)
