@@ -50,7 +50,7 @@ struct EpiArgs {
 // load-constant / test / branch decisions per feature does not fit into (measured: 840 cycles per slice).
 enum : uint32_t {
   EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
-  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_GENERIC = 1u << 31
+  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_GENERIC = 1u << 31
 };
 // Epilogue warps: 2 per TMEM lane quadrant for the register-heavy epilogues (168 registers each).
 // 16 warps (4 per quadrant, 64 columns each) halve the epilogue time of the light epilogues (bias-only: 6500 -> 3300
@@ -86,7 +86,7 @@ struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = (BN / CG) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int NUM_BARS = 2 * STAGES + 4;
+  static constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * EW;  // ring full / empty, accumulator full / empty, residual boxes per epilogue warp
   // output staging for the TMA stores: per epilogue warp STGB boxes of 32 rows x 128 B (SWIZZLE_128B), 1024-B aligned
   static constexpr int STG_OFF = STAGES * STAGE_BYTES;
   static constexpr int STG_BYTES = EW * STGB * 4096;
@@ -185,7 +185,7 @@ __device__ __forceinline__ void epi_prefetch(uint32_t rt_flags, const EpiRow& er
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
       if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) p.x[g] = *reinterpret_cast<const uint4*>(er.aux + col0 + g * 8);
-      if (F & EF_RES) load8_f32(er.res + col0 + g * 8, p.r[g]);
+      if ((F & EF_RES) && !(F & EF_RES_TMA)) load8_f32(er.res + col0 + g * 8, p.r[g]);
     }
   }
 }
@@ -208,13 +208,19 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
     const int c = col0 + g * 8;
     float w[8], d[8], b[8] = {}, x[8] = {}, r[8] = {};
     if (F & EF_BIAS) load8_f32(bias_s + g * 8, b);
+    if (F & EF_RES_TMA) {
+      // the residual box was TMA-loaded into the very staging box the results go to: same lane, same 16-byte chunks
+      const uint32_t ch = (uint32_t)((sl & 1) * 4 + g * 2);
+      lds128(stg_out + rowoff + ((ch ^ sw) << 4), r[0], r[1], r[2], r[3]);
+      lds128(stg_out + rowoff + (((ch + 1) ^ sw) << 4), r[4], r[5], r[6], r[7]);
+    }
     if (whole) {
       if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) {
         const float2 x0 = unpack_bf16x2(pre.x[g].x), x1 = unpack_bf16x2(pre.x[g].y), x2 = unpack_bf16x2(pre.x[g].z),
                      x3 = unpack_bf16x2(pre.x[g].w);
         x[0] = x0.x; x[1] = x0.y; x[2] = x1.x; x[3] = x1.y; x[4] = x2.x; x[5] = x2.y; x[6] = x3.x; x[7] = x3.y;
       }
-      if (F & EF_RES) {
+      if ((F & EF_RES) && !(F & EF_RES_TMA)) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) r[j] = pre.r[g][j];
       }
@@ -223,7 +229,7 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
       for (int j = 0; j < 8; ++j) {
         const bool ok = c + j < N;
         if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) x[j] = ok ? __bfloat162float(er.aux[c + j]) : 0.f;
-        if (F & EF_RES) r[j] = ok ? er.res[c + j] : 0.f;
+        if ((F & EF_RES) && !(F & EF_RES_TMA)) r[j] = ok ? er.res[c + j] : 0.f;
       }
     }
 #pragma unroll
@@ -267,6 +273,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const uint32_t bar_empty = bar_full + STAGES * 8;
   const uint32_t bar_acc_full = bar_empty + STAGES * 8;   // [2]
   const uint32_t bar_acc_empty = bar_acc_full + 16;       // [2]
+  const uint32_t bar_res = bar_acc_empty + 16;            // [epilogue warps][2]: residual box landed in staging buffer b
   uint32_t* tmem_slot = (uint32_t*)(smem + L::BAR_OFF + L::NUM_BARS * 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -278,11 +285,12 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_c) : "memory");
-    if (((EF & EF_GENERIC) ? ep.flags : EF) & EF_DACT) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_d) : "memory");
+    if (((EF & EF_GENERIC) ? ep.flags : EF) & (EF_DACT | EF_RES_TMA)) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_d) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(bar_full + s * 8, 1);
       mbar_init(bar_empty + s * 8, 1);
     }
+    for (int b = 0; b < 2 * epi_warps(EF, BN, CG); ++b) mbar_init(bar_res + b * 8, 1);
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar_acc_full + b * 8, 1);
       mbar_init(bar_acc_empty + b * 8, epi_warps(EF, BN, CG) * CG);  // CG = 2: both CTAs' epilogue warps release the leader
@@ -458,6 +466,19 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const int c = lane_grp * 32 + lane;
         if (c < WCOLS) bias_base[(t & 1) * BN + c] = (colw + c < N) ? bias[colw + c] : 0.f;
       }
+      // Residual through TMA (EF_RES_TMA): a row-per-lane 16-byte global load touches 32 cache lines per instruction and
+      // the L1 tag stage made the residual read of a 128 x 256 fp32 tile cost more than the tile's MMAs.  The residual box
+      // of a 32-column pair is bulk-loaded into the staging box its results will leave from (pair p of this warp: buffer
+      // p & 1, barrier phase (p >> 1) & 1), one pair ahead of its use; the first pair of a tile before the accumulator wait.
+      constexpr bool RT = !(EFC & EF_GENERIC) && (EFC & EF_RES_TMA) != 0;
+      static_assert(!RT || (STGB == 2 && (EFC & EF_F32) && !(EFC & (EF_DACT | EF_ACC))), "TMA residual: fp32 output, two staging boxes");
+      const uint32_t rbar = bar_res + ew * 16;
+      if (RT && lane == 0) {
+        bulk_wait_read<1>();  // the store that last read this buffer (two pairs ago) is done with it
+        const uint32_t bsel = nflush & 1u;
+        mbar_expect_tx(rbar + bsel * 8, 4096);
+        tma_load_4d(bsel ? stg1 : stg0, &map_d, rbar + bsel * 8, colw, row0, 0, 0);
+      }
       EpiPre pa, pb;
       if (!(EFC & EF_GENERIC) && row_ok) epi_prefetch<EFC>(rtf, er, colw, N, pa);
       if (((EFC & EF_GENERIC) || (EFC & EF_BIAS)) && has_bias) asm volatile("bar.sync %0, 128;" ::"r"(1 + cgrp) : "memory");
@@ -480,7 +501,15 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const bool box_end = (F & EF_F32) ? true : ((cp & 1) == 1);
         const uint32_t so = (two_out || STGB == 1) ? stg0 : ((nflush & 1) ? stg1 : stg0);
         long long q0 = rec ? clock64() : 0;
-        if (box_start) {
+        if (RT) {
+          if (lane == 0 && cp + 1 < NPAIR) {  // next pair's residual -> the other buffer, once its last store has read it
+            bulk_wait_read<0>();
+            const uint32_t bn = (nflush + 1u) & 1u;
+            mbar_expect_tx(rbar + bn * 8, 4096);
+            tma_load_4d(bn ? stg1 : stg0, &map_d, rbar + bn * 8, c2c, row0, 0, 0);
+          }
+          mbar_wait(rbar + (nflush & 1u) * 8, (nflush >> 1) & 1u);
+        } else if (box_start) {
           // the bulk store that last read this staging box must have finished reading it
           if (lane == 0) {
             if (two_out || STGB == 1) bulk_wait_read<0>();
@@ -697,6 +726,11 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     if (ep.res != nullptr) f |= EF_RES;
     if (ep.out_f32) f |= EF_F32;
     if (ep.accumulate) f |= EF_ACC;
+    // residual boxes through TMA (specialised fp32-output kernels only): whole 32-column boxes, 16-byte aligned rows
+    static const bool res_tma_off = getenv("B200SLU_GEMM_RES_TMA") && atoi(getenv("B200SLU_GEMM_RES_TMA")) == 0;  // tuning only
+    if ((f & EF_RES) && (f & EF_F32) && !(f & (EF_ACC | EF_DACT)) && nbatch == 1 && N % 32 == 0 && ep.ldres % 4 == 0 &&
+        ((uintptr_t)ep.res % 16) == 0 && !res_tma_off)
+      f |= EF_RES_TMA;
     ep.flags = f;
   }
   B2_CHECK_ARG(e == nullptr || e->act == B200SLU_ACT_NONE || e->act == B200SLU_ACT_SWISH || e->act == B200SLU_ACT_RELU,
@@ -762,6 +796,12 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   }
   const int kb_per = (num_kb + splits - 1) / splits;
   splits = (num_kb + kb_per - 1) / kb_per;
+  if (ep.flags & EF_RES_TMA) {  // only the specialised kernels below implement it; anything else keeps the register path
+    const uint32_t base = ep.flags & ~EF_RES_TMA;
+    const bool ok = bn == 256 && !g->trans_a && (ep.debug & ~16) == 0 &&
+                    ((!g->trans_b && base == (EF_BIAS | EF_DROP | EF_RES | EF_F32)) || (g->trans_b && base == (EF_RES | EF_F32)));
+    if (!ok) ep.flags = base;
+  }
 
   CUtensorMap ma, mb;
   const double flops = 2.0 * M * N * (double)K * nbatch;
@@ -780,6 +820,8 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
                   ep.out_f32 ? 4 : 2));
   if (ep.pre_out != nullptr)
     B2_TRY(make_map(&md, ep.pre_out, M, N, g->ldc, 1, 0, 1, 0, 64, 32, 2));
+  else if (ep.flags & EF_RES_TMA)
+    B2_TRY(make_map(&md, ep.res, M, N, ep.ldres, 1, 0, 1, 0, 32, 32, 4));  // residual boxes share the second-output slot
   else
     md = mc;
   // Specialised epilogues for the hot GEMMs of the train step; anything else runs the generic kernel.
@@ -799,6 +841,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
         B2_CASE(256, 3, false, false, EF_BIAS | EF_SWISH | EF_DACT | EF_DROP);
         B2_CASE(256, 3, false, false, EF_BIAS | EF_RELU | EF_DACT | EF_DROP);
         B2_CASE(256, 3, false, false, EF_BIAS | EF_DROP | EF_RES | EF_F32);
+        B2_CASE(256, 3, false, false, EF_BIAS | EF_DROP | EF_RES | EF_F32 | EF_RES_TMA);
         B2_CASE(256, 3, false, false, EF_BIAS | EF_RELU);
         B2_CASE(256, 3, false, false, EF_BIAS | EF_F32);
         B2_CASE(256, 3, false, false, EF_BIAS | EF_DROP | EF_F32);
@@ -813,6 +856,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
         B2_CASE(256, 3, false, true, EF_AUX_MUL);
         B2_CASE(256, 3, false, true, EF_AUX_RELU);
         B2_CASE(256, 3, false, true, EF_RES | EF_F32);
+        B2_CASE(256, 3, false, true, EF_RES | EF_F32 | EF_RES_TMA);
         B2_CASE(256, 3, false, true, EF_F32);
       }
       B2_L(256, 3, false, true, EF_GENERIC);
