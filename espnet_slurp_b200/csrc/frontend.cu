@@ -118,6 +118,7 @@ __global__ void __launch_bounds__(256) specaug_mvn_kernel(const float* __restric
   const int fl = threadIdx.x / F, f = threadIdx.x - fl * F;
   const bool active = fl < nfl;
   const int c = center != nullptr ? center[b] : -1, wp = center != nullptr ? warped[b] : 0;
+  const bool keep_pad = center == nullptr && !do_mvn;
   bool fdrop = false;
   if (active)
     for (int k = 0; k < nf; ++k) {
@@ -128,7 +129,9 @@ __global__ void __launch_bounds__(256) specaug_mvn_kernel(const float* __restric
   if (active) {
     for (int t = fl; t < T; t += nfl) {
       float v = 0.f;
-      if (t < len) {
+      // without a warp stage (center == nullptr) and without the MVN the reference never touches the padding except through
+      // the masks, which run over the padded axes; TimeWarp re-pads with 0 and UtteranceMVN zeroes the padding itself
+      if (t < len || keep_pad) {
         if (c >= 0) v = t < wp ? warp_sample(xb, F, f, 0, c, wp, t) : warp_sample(xb, F, f, c, len - c, len - wp, t - wp);
         else v = xb[(long long)t * F + f];
         bool drop = fdrop;
@@ -157,7 +160,47 @@ __global__ void __launch_bounds__(256) specaug_mvn_kernel(const float* __restric
   }
 }
 
+// GlobalMVN (espnet2/layers/global_mvn.py:66-94): y = (x - mean[f]) on the valid frames, 0 on the padding, then / std[f].
+// One thread per 4 contiguous bins (F % 4 == 0: 16-byte accesses), grid-stride over (utterance, frame) rows.
+__global__ void __launch_bounds__(256) global_mvn_kernel(const float* __restrict__ x, int B, int T, int F,
+                                                         const int* __restrict__ lens, const float* __restrict__ mean,
+                                                         const float* __restrict__ inv_std, float* __restrict__ y) {
+  const int f4 = F >> 2;
+  const long long n = (long long)B * T * f4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int fq = (int)(i % f4);
+    const long long row = i / f4;
+    const int t = (int)(row % T), b = (int)(row / T);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t < lens[b]) {
+      v = *reinterpret_cast<const float4*>(x + row * F + fq * 4);
+      if (mean != nullptr) {
+        const float4 m = *reinterpret_cast<const float4*>(mean + fq * 4);
+        v.x -= m.x; v.y -= m.y; v.z -= m.z; v.w -= m.w;
+      }
+      if (inv_std != nullptr) {
+        const float4 s = *reinterpret_cast<const float4*>(inv_std + fq * 4);
+        v.x *= s.x; v.y *= s.y; v.z *= s.z; v.w *= s.w;
+      }
+    }
+    *reinterpret_cast<float4*>(y + row * F + fq * 4) = v;
+  }
+}
+
 }  // namespace
+
+extern "C" int b200slu_global_mvn_fwd(const float* x, int B, int T, int F, const int* lens, const float* mean, const float* inv_std,
+                                      float* y, void* stream) {
+  B2_CHECK_ARG(B > 0 && T > 0 && F > 0 && F % 4 == 0, "global_mvn: need F %% 4 == 0 (F=%d)", F);
+  B2_CHECK_ARG(((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0 && (mean == nullptr || ((uintptr_t)mean % 16) == 0) &&
+                   (inv_std == nullptr || ((uintptr_t)inv_std % 16) == 0),
+               "global_mvn: operands must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_FRONTEND, st, 0, 8.0 * B * T * F);
+  global_mvn_kernel<<<b2_grid_for((long long)B * T * (F / 4), 256, 8), 256, 0, st>>>(x, B, T, F, lens, mean, inv_std, y);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int b200slu_logmel_fwd(const float* wav, long long ldw, int B, int N, const int* lens, const float* melmat, int n_fft,
                                   int hop, int n_mels, float* feats, int* feat_lens, void* stream) {

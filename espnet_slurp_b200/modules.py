@@ -11,6 +11,7 @@ initialisation and error behaviour, and runs on the B200 kernels of ``libb200slu
     DefaultFrontend    espnet2/asr/frontend/default.py:18-131              DefaultFrontend
     SpecAug            espnet2/asr/specaug/specaug.py:12-96                SpecAug
     UtteranceMVN       espnet2/layers/utterance_mvn.py:9-88                UtteranceMVN
+    GlobalMVN          espnet2/layers/global_mvn.py:13-94                  GlobalMVN
     ESPnetASRModel     espnet2/asr/espnet_model.py:39-297                  ESPnetASRModel (whole step fused: one
                                                                            forward+backward pass over the kernels)
 
@@ -185,17 +186,30 @@ class SpecAug(nn.Module):
         if apply_time_mask and time_mask_width_range is not None and time_mask_width_ratio_range is not None:
             raise ValueError('Either one of "time_mask_width_range" or "time_mask_width_ratio_range" can be used')
         _unsupported(apply_time_warp and time_warp_mode != "bicubic", "time_warp_mode != bicubic")
-        _unsupported(apply_time_mask and time_mask_width_range is None, "time_mask_width_ratio_range masks")
+        if apply_time_mask and time_mask_width_range is None and time_mask_width_ratio_range is None:
+            raise ValueError('Either one of "time_mask_width_range" or "time_mask_width_ratio_range" should be used.')
         self.W = time_warp_window if apply_time_warp else None
         self.F = _range(freq_mask_width_range) if apply_freq_mask else None
-        self.Tm = _range(time_mask_width_range) if apply_time_mask else None
+        self.Tm = _range(time_mask_width_range) if apply_time_mask and time_mask_width_range is not None else None
+        # MaskAlongAxisVariableMaxWidth (mask_along_axis.py:132-204): the width range follows the padded length
+        self.Tratio = None
+        if apply_time_mask and time_mask_width_range is None:
+            r = time_mask_width_ratio_range
+            r = (0.0, float(r)) if isinstance(r, float) else (float(r[0]), float(r[1]))
+            if not r[1] > r[0]:
+                raise ValueError(f"time_mask_width_ratio_range must be increasing: {r}")
+            self.Tratio = r
         self.n_f, self.n_t = num_freq_mask, num_time_mask
 
     def forward(self, x: torch.Tensor, x_lengths: Optional[torch.Tensor] = None):
         _need_cuda(x, "SpecAug")
         B, T, Fd = x.shape
         lens = x_lengths if x_lengths is not None else torch.full((B,), T, dtype=torch.long)
-        d = specaug_draws(lens.cpu(), T, Fd, self.W, self.F, self.n_f, self.Tm, self.n_t)
+        Tm = self.Tm
+        if self.Tratio is not None:  # mask_along_axis.py:187-203: no mask at all when the range is empty
+            lo, hi = max(0, math.floor(T * self.Tratio[0])), min(T, math.floor(T * self.Tratio[1]))
+            Tm = (lo, hi) if hi > lo else None
+        d = specaug_draws(lens.cpu(), T, Fd, self.W, self.F, self.n_f, Tm, self.n_t)
         dev = {k: (v.to(x.device) if v is not None else None) for k, v in d.items()}
         y = S.K.specaug_mvn(x.float().contiguous(), lens.to(device=x.device, dtype=torch.int32), dev["center"], dev["warped"],
                             dev["fmask"], dev["tmask"], do_mvn=False)
@@ -218,6 +232,42 @@ class UtteranceMVN(nn.Module):
         B, T, _ = x.shape
         lens = ilens if ilens is not None else torch.full((B,), T, dtype=torch.long)
         y = S.K.specaug_mvn(x.float().contiguous(), lens.to(device=x.device, dtype=torch.int32), do_mvn=True)
+        return y, ilens
+
+
+class GlobalMVN(nn.Module):
+    """Global mean / variance normalisation from a statistics file, global_mvn.py:13-94 (asr.sh default feats_normalize).
+    Same keywords; the Kaldi-style .npy and the {count, sum, sum_square} .npz statistics are both read (:41-53)."""
+
+    def __init__(self, stats_file, norm_means: bool = True, norm_vars: bool = True, eps: float = 1.0e-20):
+        super().__init__()
+        import numpy as np
+
+        self.norm_means, self.norm_vars, self.eps, self.stats_file = norm_means, norm_vars, eps, str(stats_file)
+        stats = np.load(self.stats_file)
+        if isinstance(stats, np.ndarray):
+            count = stats[0].flatten()[-1]
+            mean = stats[0, :-1] / count
+            var = stats[1, :-1] / count - mean * mean
+        else:
+            count = stats["count"]
+            mean = stats["sum"] / count
+            var = stats["sum_square"] / count - mean * mean
+        std = np.sqrt(np.maximum(var, eps))
+        self.register_buffer("mean", torch.from_numpy(np.asarray(mean)))
+        self.register_buffer("std", torch.from_numpy(np.asarray(std)))
+
+    def extra_repr(self):
+        return f"stats_file={self.stats_file}, norm_means={self.norm_means}, norm_vars={self.norm_vars}"
+
+    def forward(self, x: torch.Tensor, ilens: Optional[torch.Tensor] = None):
+        _need_cuda(x, "GlobalMVN")
+        B, T, F = x.shape
+        _unsupported(F % 4 != 0, "GlobalMVN with a feature dimension that is not a multiple of 4")
+        lens = ilens if ilens is not None else torch.full((B,), T, dtype=torch.long)
+        mean = self.mean.to(device=x.device, dtype=torch.float32).contiguous() if self.norm_means else None
+        inv_std = (1.0 / self.std.to(device=x.device, dtype=torch.float32)).contiguous() if self.norm_vars else None
+        y = S.K.global_mvn(x.float().contiguous(), lens.to(device=x.device, dtype=torch.int32), mean, inv_std)
         return y, ilens
 
 

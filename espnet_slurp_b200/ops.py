@@ -417,6 +417,15 @@ def specaug_mvn(x, lens, center=None, warped=None, fmask=None, tmask=None, do_mv
     return y
 
 
+def global_mvn(x, lens, mean=None, inv_std=None):
+    """GlobalMVN (global_mvn.py:66-94): (x - mean) * inv_std on the valid frames, 0 on the padding."""
+    B, T, F = x.shape
+    y = torch.empty_like(x)
+    check(_lib.lib().b200slu_global_mvn_fwd(ptr(x), B, T, F, ptr(lens), ptr(mean), ptr(inv_std), ptr(y), stream_ptr()),
+          "global_mvn")
+    return y
+
+
 def rel_shift_index(i: int, j: int, T: int, mode: str) -> int:
     return _lib.lib().b200slu_rel_shift_index(i, j, T, RELPOS[mode])
 

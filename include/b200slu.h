@@ -226,6 +226,11 @@ int b200slu_specaug_mvn_fwd(const float* x, int B, int T, int F, const int* lens
                             const int* freq_masks, int n_freq_masks, const int* time_masks, int n_time_masks, int do_mvn,
                             float* y, void* stream);
 
+/* N4 (next row): GlobalMVN, espnet2/layers/global_mvn.py:66-94 -- y = (x - mean[f]) / std[f] on the valid frames, 0 on the
+ * padding; mean / inv_std = NULL skip that half (norm_means / norm_vars = False).  F % 4 == 0. */
+int b200slu_global_mvn_fwd(const float* x, int B, int T, int F, const int* lens, const float* mean, const float* inv_std,
+                           float* y, void* stream);
+
 /* ---- N1: fused optimizer step over the flat buffers (espnet2/train/trainer.py:640-690: clip_grad_norm_ 2-norm,
  * non-finite skip, torch.optim.Adam; lr from WarmupLR espnet2/schedulers/warmup_lr.py:43-50) ----------------
  * state3 (device, 3 doubles): [0] sum of squares, [1] gradient norm, [2] 1 if the update was applied. */

@@ -7,6 +7,7 @@ Fixture shapes follow the reference's own tests.
 """
 from __future__ import annotations
 
+import math
 import os
 import warnings
 
@@ -232,6 +233,51 @@ def gen_frontend():
     np.savez_compressed(os.path.join(OUT, "frontend.npz"), **_np(out))
 
 
+def gen_norm_variants():
+    """N4 rows: GlobalMVN (global_mvn.py, both statistics file formats) and SpecAug with time_mask_width_ratio_range
+    (MaskAlongAxisVariableMaxWidth, the LibriSpeech conformer YAMLs) with the reference's RNG stream replayed."""
+    ref_shim.install()
+    import tempfile
+    from espnet2.asr.specaug.specaug import SpecAug
+    from espnet2.layers.global_mvn import GlobalMVN
+
+    g = torch.Generator().manual_seed(41)
+    B, T, Fq = 3, 50, 80
+    x = torch.randn(B, T, Fq, generator=g) * 2 + 1
+    lens = torch.tensor([50, 33, 41])
+    count = 1234.0
+    ssum = torch.randn(Fq, generator=g).double() * count
+    ssq = (torch.rand(Fq, generator=g).double() * 3 + 0.5) * count + ssum * ssum / count
+    out = {"x": x, "lens": lens, "count": np.array(count), "sum": ssum, "sum_square": ssq}
+    with tempfile.TemporaryDirectory() as td:
+        npz = os.path.join(td, "feats_stats.npz")
+        np.savez(npz, count=np.array(count), sum=ssum.numpy(), sum_square=ssq.numpy())
+        kaldi = np.zeros((2, Fq + 1))
+        kaldi[0, :-1], kaldi[0, -1], kaldi[1, :-1] = ssum.numpy(), count, ssq.numpy()
+        npy = os.path.join(td, "cmvn.npy")
+        np.save(npy, kaldi)
+        for nm, nv in ((True, True), (True, False), (False, True)):
+            y, _ = GlobalMVN(npz, norm_means=nm, norm_vars=nv)(x.clone(), lens)
+            out[f"y_{int(nm)}{int(nv)}"] = y
+        mk = GlobalMVN(npy)
+        out["y_kaldi"], _ = mk(x.clone(), lens)
+        out["mean"], out["std"] = mk.mean, mk.std
+    # SpecAug, ratio-range time masks (train_asr_conformer10_hop_length160.yaml:62-76 style), no time warp
+    sa = SpecAug(apply_time_warp=False, apply_freq_mask=True, freq_mask_width_range=(0, 27), num_freq_mask=2,
+                 apply_time_mask=True, time_mask_width_ratio_range=(0.0, 0.2), num_time_mask=3)
+    xs = torch.randn(B, T, Fq, generator=g)
+    torch.manual_seed(43)
+    ys, _ = sa(xs.clone(), lens)
+    torch.manual_seed(43)
+    f_len = torch.randint(0, 27, (B, 2))
+    f_pos = torch.randint(0, max(1, Fq - int(f_len.max())), (B, 2))
+    hi = math.floor(T * 0.2)
+    t_len = torch.randint(0, hi, (B, 3))
+    t_pos = torch.randint(0, max(1, T - int(t_len.max())), (B, 3))
+    out.update({"sa_x": xs, "sa_y": ys, "f_len": f_len, "f_pos": f_pos, "t_len": t_len, "t_pos": t_pos})
+    np.savez_compressed(os.path.join(OUT, "norm_variants.npz"), **_np(out))
+
+
 def main():
     warnings.filterwarnings("ignore")
     os.makedirs(OUT, exist_ok=True)
@@ -239,6 +285,7 @@ def main():
     gen_ctc()
     gen_specaug()
     gen_frontend()
+    gen_norm_variants()
     gen_bn_running()
     gen_e2e("latest", "e2e_latest.npz")
     gen_e2e("legacy", "e2e_legacy.npz")

@@ -240,21 +240,24 @@ def spec_augment(feats: torch.Tensor, lens: torch.Tensor, draws: dict, window: i
     """SpecAug.forward (espnet2/asr/specaug/specaug.py:89-96) with the RNG draws
     supplied: draws = {center (B,), warped (B,), f_len (B,nf), f_pos (B,nf),
     t_len (B,nt), t_pos (B,nt)}; center < 0 means "no warp for this utterance"
-    (time_warp.py:24-25: t - W <= W).
+    (time_warp.py:24-25: t - W <= W); center None means the warp stage is off.
 
     TimeWarp (time_warp.py:65-88) runs per utterance on the UNPADDED slice and
     re-pads with 0; mask_along_axis (mask_along_axis.py:8-68) zeroes
     [pos, pos+len) along freq then along the padded time axis.
     """
     B, T, Fq = feats.shape
-    out = torch.zeros_like(feats)
-    for b in range(B):
-        L = int(lens[b])
-        xb = feats[b, :L]
-        c, w = int(draws["center"][b]), int(draws["warped"][b])
-        if c >= 0:
-            xb = time_warp_one(xb, c, w)
-        out[b, :L] = xb
+    if draws.get("center") is None:  # apply_time_warp=False: no per-utterance slicing, the padding passes through
+        out = feats.clone()
+    else:
+        out = torch.zeros_like(feats)
+        for b in range(B):
+            L = int(lens[b])
+            xb = feats[b, :L]
+            c, w = int(draws["center"][b]), int(draws["warped"][b])
+            if c >= 0:
+                xb = time_warp_one(xb, c, w)
+            out[b, :L] = xb
     ar_f = torch.arange(Fq)[None, None, :]
     fm = ((draws["f_pos"][:, :, None] <= ar_f) & (ar_f < (draws["f_pos"] + draws["f_len"])[:, :, None])).any(1)
     out = out.masked_fill(fm[:, None, :], 0.0)
@@ -270,6 +273,25 @@ def utterance_mvn(x: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
     x = x.masked_fill(pad_mask(lens, x.shape[1])[:, :, None], 0.0)
     mean = x.sum(1, keepdim=True) / lens.to(x.dtype)[:, None, None]
     return x - mean
+
+
+def global_mvn(x: torch.Tensor, lens: torch.Tensor, mean: torch.Tensor, std: torch.Tensor, norm_means: bool = True,
+               norm_vars: bool = True) -> torch.Tensor:
+    """espnet2/layers/global_mvn.py:66-94: subtract the global mean, zero the padding, divide by the global std."""
+    if norm_means:
+        x = x - mean
+    x = x.masked_fill(pad_mask(lens, x.shape[1])[:, :, None], 0.0)
+    if norm_vars:
+        x = x / std
+    return x
+
+
+def variable_time_mask_range(T: int, ratio_range) -> Optional[Tuple[int, int]]:
+    """MaskAlongAxisVariableMaxWidth.forward, espnet2/layers/mask_along_axis.py:187-203: the width range of the time
+    masks follows the padded length; None when the range is empty (no mask is drawn then)."""
+    lo = max(0, math.floor(T * ratio_range[0]))
+    hi = min(T, math.floor(T * ratio_range[1]))
+    return (lo, hi) if hi > lo else None
 
 
 # --------------------------------------------------------------------------- #

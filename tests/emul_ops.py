@@ -383,13 +383,20 @@ def specaug_mvn(x, lens, center=None, warped=None, fmask=None, tmask=None, do_mv
     if center is not None or fmask is not None or tmask is not None:
         z = torch.zeros(B, 0, dtype=torch.long)
         draws = {
-            "center": center.long() if center is not None else torch.full((B,), -1),
-            "warped": warped.long() if warped is not None else torch.zeros(B, dtype=torch.long),
+            "center": center.long() if center is not None else None,
+            "warped": warped.long() if warped is not None else None,
             "f_pos": fmask[..., 0].long() if fmask is not None else z, "f_len": fmask[..., 1].long() if fmask is not None else z,
             "t_pos": tmask[..., 0].long() if tmask is not None else z, "t_len": tmask[..., 1].long() if tmask is not None else z,
         }
         y = om.spec_augment(x, lens.long(), draws)
     return om.utterance_mvn(y, lens.long()) if do_mvn else y
+
+
+def global_mvn(x, lens, mean=None, inv_std=None):
+    valid = (torch.arange(x.shape[1])[None, :] < lens[:, None].long())[:, :, None]
+    y = x - mean if mean is not None else x.clone()
+    y = torch.where(valid, y, torch.zeros_like(y))
+    return y * inv_std if inv_std is not None else y
 
 
 def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, state3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,

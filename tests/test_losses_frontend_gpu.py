@@ -174,3 +174,29 @@ def test_specaug_replay_golden(golden_dir):
                          fm.cuda(), tm.cuda(), do_mvn=True)
     want = om.utterance_mvn(torch.tensor(z["y"]), lens.long())
     np.testing.assert_allclose(y2.cpu().numpy(), want.numpy(), rtol=1e-4, atol=2e-5)
+
+
+def test_global_mvn_and_ratio_masks_golden(golden_dir):
+    """GlobalMVN kernel and the mask-only SpecAug path (no warp stage: the padding passes through) against outputs of the
+    unmodified reference (tests/golden/norm_variants.npz)."""
+    z = np.load(os.path.join(golden_dir, "norm_variants.npz"))
+    x, lens = torch.tensor(z["x"]).cuda(), torch.tensor(z["lens"]).int().cuda()
+    mean, istd = torch.tensor(z["mean"]).float().cuda(), (1.0 / torch.tensor(z["std"]).float()).cuda()
+    for key, m, s in (("y_11", mean, istd), ("y_10", mean, None), ("y_01", None, istd)):
+        y = K().global_mvn(x, lens, m, s)
+        np.testing.assert_allclose(y.cpu().numpy(), z[key], rtol=1e-5, atol=2e-6)
+    fm = torch.stack([torch.tensor(z["f_pos"]), torch.tensor(z["f_len"])], -1).int().contiguous().cuda()
+    tm = torch.stack([torch.tensor(z["t_pos"]), torch.tensor(z["t_len"])], -1).int().contiguous().cuda()
+    sx = torch.tensor(z["sa_x"]).cuda()
+    y = K().specaug_mvn(sx, lens, None, None, fm, tm, do_mvn=False)
+    assert np.array_equal(y.cpu().numpy(), z["sa_y"])
+    y2 = K().specaug_mvn(sx, lens, None, None, fm, tm, do_mvn=True)
+    want = om.utterance_mvn(torch.tensor(z["sa_y"]), lens.long().cpu())
+    np.testing.assert_allclose(y2.cpu().numpy(), want.numpy(), rtol=1e-4, atol=2e-5)
+    # ragged larger case against the emulation: F = 80, T not a multiple of anything
+    g = torch.Generator().manual_seed(5)
+    xb = torch.randn(7, 203, 80, generator=g)
+    lb = torch.tensor([203, 1, 77, 150, 202, 64, 9]).int()
+    mb, sb = torch.randn(80, generator=g), torch.rand(80, generator=g) + 0.5
+    yb = K().global_mvn(xb.cuda(), lb.cuda(), mb.cuda(), sb.cuda())
+    np.testing.assert_allclose(yb.cpu().numpy(), E.global_mvn(xb, lb, mb, sb).numpy(), rtol=1e-6, atol=1e-6)

@@ -187,6 +187,35 @@ def test_espnet_asr_model_from_waveform():
     assert torch.isfinite(le).all()
 
 
+def test_global_mvn_and_ratio_specaug_modules(golden_dir, tmp_path):
+    """GlobalMVN / SpecAug(time_mask_width_ratio_range) drop-ins against outputs of the unmodified reference."""
+    import os
+    import numpy as np
+    m = M()
+    g = np.load(os.path.join(golden_dir, "norm_variants.npz"))
+    x, lens = torch.tensor(g["x"]).cuda(), torch.tensor(g["lens"]).cuda()
+    npz = str(tmp_path / "feats_stats.npz")
+    np.savez(npz, count=g["count"], sum=g["sum"], sum_square=g["sum_square"])
+    kaldi = np.zeros((2, g["sum"].shape[0] + 1))
+    kaldi[0, :-1], kaldi[0, -1], kaldi[1, :-1] = g["sum"], float(g["count"]), g["sum_square"]
+    npy = str(tmp_path / "cmvn.npy")
+    np.save(npy, kaldi)
+    for nm, nv in ((True, True), (True, False), (False, True)):
+        y, yl = m.GlobalMVN(npz, norm_means=nm, norm_vars=nv)(x, lens)
+        assert yl is lens
+        np.testing.assert_allclose(y.cpu().numpy(), g[f"y_{int(nm)}{int(nv)}"], rtol=1e-5, atol=2e-6)
+    y, _ = m.GlobalMVN(npy)(x, lens)
+    np.testing.assert_allclose(y.cpu().numpy(), g["y_kaldi"], rtol=1e-5, atol=2e-6)
+    # the module draws in the reference's order: same seed, same masks, same output
+    sa = m.SpecAug(apply_time_warp=False, apply_freq_mask=True, freq_mask_width_range=(0, 27), num_freq_mask=2,
+                   apply_time_mask=True, time_mask_width_ratio_range=(0.0, 0.2), num_time_mask=3)
+    torch.manual_seed(43)
+    ys, _ = sa(torch.tensor(g["sa_x"]).cuda(), lens)
+    np.testing.assert_allclose(ys.cpu().numpy(), g["sa_y"], rtol=1e-6, atol=1e-7)
+    with pytest.raises(ValueError):
+        m.SpecAug(apply_time_mask=True, time_mask_width_range=None, time_mask_width_ratio_range=None)
+
+
 def test_specaug_and_mvn_modules():
     m = M()
     torch.manual_seed(0)

@@ -95,6 +95,27 @@ def test_specaug_replay():
     np.testing.assert_allclose(y.numpy(), g["y"], rtol=1e-5, atol=1e-5)
 
 
+def test_global_mvn_and_ratio_time_masks():
+    """N4 rows against the unmodified reference: GlobalMVN (both statistics formats, the three norm settings) and
+    SpecAug with time_mask_width_ratio_range (draws replayed)."""
+    g = load("norm_variants.npz")
+    x, lens = torch.tensor(g["x"]), torch.tensor(g["lens"])
+    mean, std = torch.tensor(g["mean"]).float(), torch.tensor(g["std"]).float()
+    cnt = float(g["count"])
+    np.testing.assert_allclose(mean.numpy(), g["sum"] / cnt, rtol=1e-6)
+    np.testing.assert_allclose(std.numpy(), np.sqrt(np.maximum(g["sum_square"] / cnt - (g["sum"] / cnt) ** 2, 1e-20)), rtol=1e-6)
+    for nm, nv in ((True, True), (True, False), (False, True)):
+        y = om.global_mvn(x, lens, mean, std, nm, nv)
+        np.testing.assert_allclose(y.numpy(), g[f"y_{int(nm)}{int(nv)}"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(g["y_kaldi"], g["y_11"], rtol=1e-6, atol=1e-7)
+    T = g["sa_x"].shape[1]
+    assert om.variable_time_mask_range(T, (0.0, 0.2)) == (0, 10)
+    assert om.variable_time_mask_range(4, (0.0, 0.2)) is None
+    draws = {k: torch.tensor(g[k]) for k in ("f_len", "f_pos", "t_len", "t_pos")}
+    y = om.spec_augment(torch.tensor(g["sa_x"]), lens, draws)
+    np.testing.assert_allclose(y.numpy(), g["sa_y"], rtol=1e-6, atol=1e-7)
+
+
 def test_encoder_and_bn_running_stats():
     g = load("encoder_bn.npz")
     sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/")}
