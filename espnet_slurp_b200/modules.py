@@ -23,7 +23,8 @@ eager fallback, and a module on a non-CUDA device raises at the first call.
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional, Sequence, Tuple, Union
+import weakref
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
 
 import torch
 import torch.nn as nn
@@ -84,6 +85,21 @@ class _Packed(nn.Module):
             self.__dict__["_pp"] = pp
         return pp
 
+    def _infer_pack(self) -> ParamPack:
+        """Pack for the no-grad scoring entry points (encode / forward_one_step / log_softmax ...): a sub-module that sits
+        inside an ESPnetASRModel reads the MODEL's flat buffers (same names), so a decoding loop that alternates
+        model.encode(), decoder.batch_score() and ctc.log_softmax() never re-packs the parameters."""
+        owner = self.__dict__.get("_owner")
+        owner = owner() if owner is not None else None
+        if owner is not None and not any(sub is self for sub in (owner.encoder, owner.decoder, owner.ctc)):
+            owner = None  # a copy of the sub-module that still carries the original model's link
+        pp = (owner if owner is not None else self)._pack()
+        pp.refresh()
+        return pp
+
+    def __getstate__(self):  # pickling / deepcopy: the flat buffers and the owner link are rebuilt on first use
+        return {k: v for k, v in self.__dict__.items() if k not in ("_pp", "_owner")}
+
     def _bn_buffers(self) -> Dict[str, torch.Tensor]:
         return {self._prefix + n: b for n, b in self.named_buffers()}
 
@@ -121,18 +137,19 @@ class DefaultFrontend(nn.Module):
         self.fs, self.n_fft, self.hop_length, self.n_mels = fs, n_fft, hop_length, n_mels
         fmin = 0.0 if fmin is None else fmin
         fmax = fs / 2 if fmax is None else fmax
-        self.register_buffer("melmat", melbank.mel_matrix(fs, n_fft, n_mels, float(fmin), float(fmax)).float(),
-                             persistent=False)
+        # the reference keeps the filterbank in its state_dict as "frontend.logmel.melmat" (log_mel.py:52), (n_freq, n_mels)
+        self.logmel = nn.Module()
+        self.logmel.register_buffer("melmat", melbank.mel_matrix(fs, n_fft, n_mels, float(fmin), float(fmax)).float())
 
     def output_size(self) -> int:
         return self.n_mels
 
     def forward(self, input: torch.Tensor, input_lengths: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
         _need_cuda(input, "DefaultFrontend")
-        if self.melmat.device != input.device:
-            self.melmat = self.melmat.to(input.device)
+        if self.logmel.melmat.device != input.device:
+            self.logmel.melmat = self.logmel.melmat.to(input.device)
         feats, flens = S.K.logmel(input.float().contiguous(), input_lengths.to(device=input.device, dtype=torch.int32),
-                                  self.melmat, self.n_fft, self.hop_length)
+                                  self.logmel.melmat, self.n_fft, self.hop_length)
         return feats, flens.to(torch.long)
 
 
@@ -576,6 +593,55 @@ class TransformerDecoder(_Packed):
         x = _DecoderFn.apply(self, hs_pad, hlens, ys_in_pad, ys_in_lens, *self.parameters())
         return x, ys_in_lens.to(hs_pad.device)
 
+    # ---- incremental scoring (next row N2): BatchScorerInterface as asr_inference.py / batch_beam_search.py use it ----
+    def forward_one_step(self, tgt: torch.Tensor, tgt_mask: torch.Tensor, memory: torch.Tensor,
+                         cache: List[torch.Tensor] = None) -> Tuple[torch.Tensor, List[torch.Tensor]]:
+        """transformer_decoder.py:147-184.  tgt int64 (batch, maxlen_out) prefix, memory (batch, maxlen_in, feat) without
+        a mask; returns (log-probs of the next token (batch, vocab), per-layer outputs (batch, maxlen_out, size)).
+
+        The reference's cache only spares the query side of the earlier positions: keys / values of the whole prefix and
+        of the whole memory are projected again at every step (decoder_layer.py:84-123), and the memory projection
+        (maxlen_in rows) dominates.  Here the prefix is re-run causally through the same kernels as the training
+        forward (dropout off), which yields the identical rows (the invariant of test/test_transformer_decode.py) for
+        the same dominant cost; `cache` is checked for shape and otherwise not needed."""
+        _need_cuda(memory, "TransformerDecoder")
+        B, L = tgt.shape
+        T, d = memory.shape[1], memory.shape[2]
+        n_layers = len(self.decoders)
+        if cache is not None:
+            assert len(cache) == n_layers and all(c.shape == (B, L - 1, d) for c in cache), \
+                ([tuple(c.shape) for c in cache], (B, L - 1, d))
+        dev = memory.device
+        with torch.no_grad():
+            pp = self._infer_pack()
+            mem16 = S.K.cast_bf16(memory.float().contiguous().view(B * T, d))
+            mlens = torch.full((B,), T, device=dev, dtype=torch.int32)
+            ylens = torch.full((B,), L, device=dev, dtype=torch.int32)
+            logits, saved = S.decoder_fwd(mem16, mlens, _i32(tgt, dev).contiguous(), ylens, pp.P, pp.W, self._cfg,
+                                          S.StepCtx(seed=0, training=False), B, T, p="decoder")
+            layers, x_last = saved[2], saved[3]
+            # a layer's output is the next layer's saved input
+            outs = [layers[n + 1][0] for n in range(n_layers - 1)] + [x_last]
+            new_cache = [o.view(B, L, d) for o in outs]
+            V = self._cfg.vocab
+            y = torch.log_softmax(logits.view(B, L, -1)[:, -1, :V], dim=-1)
+        return y, new_cache
+
+    def score(self, ys: torch.Tensor, state, x: torch.Tensor):
+        """transformer_decoder.py:186-192: one hypothesis (ys (ylen,), x (xlen, feat))."""
+        logp, state = self.forward_one_step(ys.unsqueeze(0), None, x.unsqueeze(0), cache=state)
+        return logp.squeeze(0), state
+
+    def batch_score(self, ys: torch.Tensor, states: List[Any], xs: torch.Tensor) -> Tuple[torch.Tensor, List[Any]]:
+        """transformer_decoder.py:194-229: states[b][layer] (ylen-1, size) <-> batch layout [layer] (n_batch, ylen-1, size)."""
+        n_batch, n_layers = len(ys), len(self.decoders)
+        if states[0] is None:
+            batch_state = None
+        else:
+            batch_state = [torch.stack([states[b][i] for b in range(n_batch)]) for i in range(n_layers)]
+        logp, states = self.forward_one_step(ys, None, xs, cache=batch_state)
+        return logp, [[states[i][b] for i in range(n_layers)] for b in range(n_batch)]
+
 
 class CTC(_Packed):
     """ctc.py:9-127: ctc_lo projection + log_softmax + CTC loss (sum / batch, zero_infinity)."""
@@ -601,8 +667,7 @@ class CTC(_Packed):
         return _CTCFn.apply(self, hs_pad, hlens, ys_pad, ys_lens, *self.parameters())
 
     def _logits(self, hs_pad):
-        pp = self._pack()
-        pp.refresh()
+        pp = self._infer_pack()
         B, T, d = hs_pad.shape
         V = self._odim
         out = torch.empty(B * T, S.K.round8(V), device=hs_pad.device, dtype=torch.float32)
@@ -655,6 +720,33 @@ class ESPnetASRModel(_Packed):
         self.extract_feats_in_collect_stats = extract_feats_in_collect_stats
         self._cfg = S.ModelCfg(enc=encoder._cfg, dec=decoder._cfg, vocab=vocab_size, ctc_weight=ctc_weight, lsm_weight=lsm_weight)
         self._names = [n for n, _ in self.named_parameters()]
+        self._link_owner()
+
+    def _link_owner(self):
+        for sub in (self.encoder, self.decoder, self.ctc):  # weak: no module cycle
+            sub.__dict__["_owner"] = weakref.ref(self)
+
+    # espnet_model.py:319-377 (the entry asr_inference.py uses): frontend -> [SpecAug when training] -> normalize -> encoder
+    def encode(self, speech: torch.Tensor, speech_lengths: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        _need_cuda(speech, "ESPnetASRModel")
+        self._link_owner()  # (again after a deepcopy / unpickle)
+        feats, flens = self._extract_feats(speech, speech_lengths)
+        if self.specaug is not None and self.training:
+            feats, flens = self.specaug(feats, flens)
+        if self.normalize is not None:
+            feats, flens = self.normalize(feats, flens)
+        short, limit = check_short_utt(self.encoder.embed, feats.size(1))
+        if short:
+            raise TooShortUttError(f"has {feats.size(1)} frames and is too short for subsampling "
+                                   f"(it needs more than {limit} frames), return empty results", feats.size(1), limit)
+        B = feats.shape[0]
+        with torch.no_grad():
+            pp = self._infer_pack()
+            enc, _, olens, _ = S.encoder_fwd(feats.float().contiguous(), _i32(flens, feats.device), pp.P, pp.W, self._cfg.enc,
+                                             self._ctx(), p="encoder", bn_buffers=self._bn_buffers())
+        encoder_out, encoder_out_lens = enc.view(B, -1, self._cfg.enc.d), olens.to(torch.long)
+        assert encoder_out.size(0) == speech.size(0), (encoder_out.size(), speech.size(0))
+        return encoder_out, encoder_out_lens
 
     # espnet_model.py:379-396
     def _extract_feats(self, speech, speech_lengths):

@@ -278,6 +278,52 @@ def gen_norm_variants():
     np.savez_compressed(os.path.join(OUT, "norm_variants.npz"), **_np(out))
 
 
+def gen_decode():
+    """Next-row N2: eval-mode encode() (BN running statistics), CTC.log_softmax / argmax and the decoder's incremental
+    scoring interface (batch_score over a growing prefix with the per-layer cache; score for one hypothesis)."""
+    torch.manual_seed(7)
+    m = ref_shim.build_reference_model(TINY_V, TINY_ENC, TINY_DEC)
+    randomize_(m, 8)
+    g = torch.Generator().manual_seed(9)
+    with torch.no_grad():
+        for n, b in m.named_buffers():
+            if n.endswith("running_mean"):
+                b.copy_(0.2 * torch.randn(b.shape, generator=g))
+            elif n.endswith("running_var"):
+                b.copy_(0.5 + torch.rand(b.shape, generator=g))
+    m.eval()
+    wav, lens, _, _ = tiny_batch(seed=10)
+    with torch.no_grad():
+        enc_out, enc_lens = m.encode(wav, lens)
+        ctc_logp = m.ctc.log_softmax(enc_out)
+        ctc_arg = m.ctc.argmax(enc_out)
+        x = enc_out[0, : int(enc_lens[0])]
+        n_hyp, L = 3, 5
+        ys = torch.randint(2, TINY_V - 1, (n_hyp, L), generator=g)
+        ys[:, 0] = TINY_V - 1  # sos
+        xs = x.unsqueeze(0).expand(n_hyp, -1, -1)
+        states = [None] * n_hyp
+        logps = []
+        for l in range(1, L + 1):
+            logp, states = m.decoder.batch_score(ys[:, :l], states, xs)
+            logps.append(logp)
+        cache = torch.stack([torch.stack([states[b][i] for b in range(n_hyp)]) for i in range(len(m.decoder.decoders))])
+        st, one = None, []
+        for l in range(1, 4):
+            lp, st = m.decoder.score(ys[1, :l], st, x)
+            one.append(lp)
+        # the full (teacher-forced) forward gives the same rows: transformer_decoder.py:92-145
+        full, _ = m.decoder(xs, torch.full((n_hyp,), xs.shape[1]), ys, torch.full((n_hyp,), L))
+    out = {"wav": wav, "lens": lens, "enc_out": enc_out, "enc_lens": enc_lens, "ctc_logp": ctc_logp, "ctc_argmax": ctc_arg,
+           "ys": ys, "logp_steps": torch.stack(logps), "cache": cache, "logp_one": torch.stack(one),
+           "full_logp": torch.log_softmax(full, dim=-1)}
+    for k, v in m.state_dict().items():
+        out["sd/" + k] = v
+    np.savez_compressed(os.path.join(OUT, "decode.npz"), **_np(out))
+    print("decode.npz", tuple(enc_out.shape), float(torch.stack(logps).abs().max()),
+          float((torch.stack(logps)[-1] - torch.log_softmax(full, -1)[:, -1]).abs().max()))
+
+
 def main():
     warnings.filterwarnings("ignore")
     os.makedirs(OUT, exist_ok=True)
@@ -286,6 +332,7 @@ def main():
     gen_specaug()
     gen_frontend()
     gen_norm_variants()
+    gen_decode()
     gen_bn_running()
     gen_e2e("latest", "e2e_latest.npz")
     gen_e2e("legacy", "e2e_legacy.npz")

@@ -440,20 +440,20 @@ def conv_module(x, sd: SD, p: str, kernel: int, training: bool = True, bn_stats_
     return y @ sd[p + ".pointwise_conv2.weight"][:, :, 0].t() + sd[p + ".pointwise_conv2.bias"]
 
 
-def conformer_block(x, pos_emb, key_valid, sd: SD, p: str, cfg: EncCfg, bn_stats_out=None):
+def conformer_block(x, pos_emb, key_valid, sd: SD, p: str, cfg: EncCfg, bn_stats_out=None, training: bool = True):
     """EncoderLayer.forward (espnet/nets/pytorch_backend/conformer/encoder_layer.py:76-157),
-    pre-LN macaron, dropout = 0."""
+    pre-LN macaron, dropout = 0; training=False: BatchNorm uses its running statistics."""
     x = x + 0.5 * ffn(layer_norm(x, sd, p + ".norm_ff_macaron"), sd, p + ".feed_forward_macaron", swish)
     x = x + rel_pos_mhsa(layer_norm(x, sd, p + ".norm_mha"), pos_emb, key_valid, sd, p + ".self_attn",
                          cfg.heads, cfg.rel_pos_type)
-    x = x + conv_module(layer_norm(x, sd, p + ".norm_conv"), sd, p + ".conv_module", cfg.kernel,
+    x = x + conv_module(layer_norm(x, sd, p + ".norm_conv"), sd, p + ".conv_module", cfg.kernel, training=training,
                         bn_stats_out=bn_stats_out)
     x = x + 0.5 * ffn(layer_norm(x, sd, p + ".norm_ff"), sd, p + ".feed_forward", swish)
     return layer_norm(x, sd, p + ".norm_final")
 
 
 def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_stats_out=None,
-                      return_blocks: bool = False):
+                      return_blocks: bool = False, training: bool = True):
     """ConformerEncoder.forward (espnet2/asr/encoder/conformer_encoder.py:292-368)."""
     T_in = feats.shape[1]
     x = conv2d_subsample(feats, sd, p + ".embed") * math.sqrt(cfg.d)  # embedding.py:239
@@ -466,7 +466,7 @@ def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_
         pos_emb = legacy_pos_table(T, cfg.d, dtype=x.dtype)
     outs = []
     for n in range(cfg.blocks):
-        x = conformer_block(x, pos_emb, key_valid, sd, f"{p}.encoders.{n}", cfg, bn_stats_out)
+        x = conformer_block(x, pos_emb, key_valid, sd, f"{p}.encoders.{n}", cfg, bn_stats_out, training)
         if return_blocks:
             outs.append(x)
     x = layer_norm(x, sd, p + ".after_norm")
@@ -598,6 +598,34 @@ def transformer_decoder(memory, mem_lens, ys_in, ys_in_lens, sd: SD, cfg: DecCfg
         x = x + ffn(layer_norm(x, sd, q + ".norm3"), sd, q + ".feed_forward", F.relu)
     x = layer_norm(x, sd, p + ".after_norm")
     return linear(x, sd, p + ".output_layer")
+
+
+def decoder_forward_one_step(tgt, memory, sd: SD, cfg: DecCfg, cache=None, p: str = "decoder"):
+    """BaseTransformerDecoder.forward_one_step (espnet2/asr/decoder/transformer_decoder.py:147-184) with the cache branch
+    of DecoderLayer.forward (decoder_layer.py:84-134): only the LAST prefix position is a query; keys/values are recomputed
+    over the whole prefix (layer input = previous layer's cache + its new row) and over the memory (memory_mask None);
+    each layer's new row is appended to its cache.  Returns (log-probs of the next token (B, V), new cache list)."""
+    B, L = tgt.shape
+    x = sd[p + ".embed.0.weight"][tgt] * math.sqrt(cfg.d) + abs_pos_table(L, cfg.d, memory.dtype)
+    tgt_valid = torch.ones(B, L, dtype=torch.bool)
+    mem_valid = torch.ones(B, memory.shape[1], dtype=torch.bool)
+    new_cache = []
+    for n in range(cfg.blocks):
+        q = f"{p}.decoders.{n}"
+        c = None if cache is None else cache[n]
+        h = layer_norm(x, sd, q + ".norm1")
+        if c is None:
+            y = x + mha(h, h, tgt_valid, sd, q + ".self_attn", cfg.heads, causal=True)
+        else:
+            assert c.shape == (B, L - 1, cfg.d), (c.shape, (B, L - 1, cfg.d))
+            # the subsequent mask's last row lets the newest position see the whole prefix: no causal mask needed
+            y = x[:, -1:] + mha(h[:, -1:], h, tgt_valid, sd, q + ".self_attn", cfg.heads)
+        y = y + mha(layer_norm(y, sd, q + ".norm2"), memory, mem_valid, sd, q + ".src_attn", cfg.heads)
+        y = y + ffn(layer_norm(y, sd, q + ".norm3"), sd, q + ".feed_forward", F.relu)
+        x = y if c is None else torch.cat([c, y], dim=1)
+        new_cache.append(x)
+    y = layer_norm(x[:, -1], sd, p + ".after_norm")
+    return torch.log_softmax(linear(y, sd, p + ".output_layer"), dim=-1), new_cache
 
 
 def label_smoothing_loss(logits, target, smoothing: float, ignore: int = -1):

@@ -34,6 +34,7 @@ SIGS = {
     "SpecAug": "apply_time_warp time_warp_window time_warp_mode apply_freq_mask freq_mask_width_range num_freq_mask "
                "apply_time_mask time_mask_width_range time_mask_width_ratio_range num_time_mask",
     "UtteranceMVN": "norm_means norm_vars eps",
+    "GlobalMVN": "stats_file norm_means norm_vars eps",
 }
 
 
@@ -46,7 +47,8 @@ def test_constructor_keywords_match_reference(name):
         path = {"ConformerEncoder": "espnet2/asr/encoder/conformer_encoder.py", "TransformerDecoder":
                 "espnet2/asr/decoder/transformer_decoder.py", "CTC": "espnet2/asr/ctc.py", "ESPnetASRModel":
                 "espnet2/asr/espnet_model.py", "DefaultFrontend": "espnet2/asr/frontend/default.py", "SpecAug":
-                "espnet2/asr/specaug/specaug.py", "UtteranceMVN": "espnet2/layers/utterance_mvn.py"}[name]
+                "espnet2/asr/specaug/specaug.py", "UtteranceMVN": "espnet2/layers/utterance_mvn.py",
+                "GlobalMVN": "espnet2/layers/global_mvn.py"}[name]
         import ast
         tree = ast.parse(open(os.path.join(ref_root, path)).read())
         cls = [n for n in ast.walk(tree) if isinstance(n, ast.ClassDef) and n.name == name][-1]
@@ -63,6 +65,7 @@ def test_state_dict_names_and_shapes():
                              None, dec, ctc, None, ctc_weight=0.3, lsm_weight=0.1)
     want = make_sd(om.EncCfg(80, 64, 4, 128, 2, 7, "latest"), om.DecCfg(30, 64, 4, 128, 2), 30)
     got = {k: tuple(v.shape) for k, v in model.state_dict().items()}
+    assert got.pop("frontend.logmel.melmat") == (257, 80)  # log_mel.py:52
     params = {k: v for k, v in got.items() if not k.endswith(("running_mean", "running_var", "num_batches_tracked"))}
     assert params == {k: tuple(v.shape) for k, v in want.items()}
     bn = sorted(k for k in got if k not in params)
@@ -113,3 +116,26 @@ def test_specaug_draws_follow_reference_ranges():
     f, t = d["fmask"], d["tmask"]
     assert f.shape == (3, 2, 2) and int(f[..., 1].max()) < 30 and int((f[..., 0] + f[..., 1]).max()) <= 80 + 30
     assert t.shape == (3, 2, 2) and int(t[..., 1].max()) < 40
+
+
+def test_reference_checkpoint_loads_strictly():
+    """A state_dict saved by the unmodified reference model (tests/golden/decode.npz, frontend + BatchNorm buffers
+    included) loads with strict=True, and the filterbank buffer equals the reference's librosa table."""
+    import numpy as np
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "decode.npz"))
+    sd = {k[3:]: torch.tensor(z[k]) for k in z.files if k.startswith("sd/")}
+    V = 20
+    enc = m.ConformerEncoder(80, 16, 2, 32, 2, macaron_style=True, rel_pos_type="latest", cnn_module_kernel=7)
+    dec = m.TransformerDecoder(V, 16, 2, 32, 2)
+    fe = m.DefaultFrontend()
+    assert torch.equal(fe.logmel.melmat, sd["frontend.logmel.melmat"])
+    model = m.ESPnetASRModel(V, ["<blank>", "<unk>"] + [f"t{i}" for i in range(V - 3)] + ["<sos/eos>"], fe,
+                             m.SpecAug(time_mask_width_range=(0, 40)), m.UtteranceMVN(), None, enc, None, dec, m.CTC(V, 16), None)
+    res = model.load_state_dict(sd, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert sorted(model.state_dict()) == sorted(sd)
+    import copy
+    import pickle
+    clone = copy.deepcopy(model)  # the owner links / flat buffers are rebuilt lazily, never copied or pickled
+    assert "_owner" not in clone.decoder.__dict__ and model.decoder.__dict__["_owner"]() is model
+    pickle.loads(pickle.dumps(model))

@@ -187,6 +187,77 @@ def test_espnet_asr_model_from_waveform():
     assert torch.isfinite(le).all()
 
 
+def test_encode_and_incremental_scoring_golden(golden_dir):
+    """Next-row N2 against the unmodified reference (tests/golden/decode.npz): eval-mode ESPnetASRModel.encode from raw
+    waveforms (BatchNorm running statistics), CTC.log_softmax / argmax, TransformerDecoder.batch_score over a growing
+    prefix with the per-layer state lists, score for one hypothesis; bf16 tolerances as in tests/test_step_gpu.py."""
+    import os
+    m = M()
+    z = np.load(os.path.join(golden_dir, "decode.npz"))
+    g = {k: z[k] for k in z.files}
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/")}
+    V = 20
+    enc = m.ConformerEncoder(80, 16, 2, 32, 2, 0.1, 0.1, 0.1, macaron_style=True, rel_pos_type="latest", cnn_module_kernel=7)
+    dec = m.TransformerDecoder(V, 16, 2, 32, 2, 0.1, 0.1)
+    ctc = m.CTC(V, 16)
+    tokens = ["<blank>", "<unk>"] + [f"t{i}" for i in range(V - 3)] + ["<sos/eos>"]
+    model = m.ESPnetASRModel(V, tokens, m.DefaultFrontend(), m.SpecAug(time_mask_width_range=(0, 40)), m.UtteranceMVN(), None, enc,
+                             None, dec, ctc, None)
+    model.load_state_dict(sd)
+    model = model.cuda().eval()
+    enc_out, enc_lens = model.encode(torch.tensor(g["wav"]).cuda(), torch.tensor(g["lens"]).cuda())
+    assert enc_lens.dtype == torch.long and enc_lens.tolist() == g["enc_lens"].tolist()
+    assert tuple(enc_out.shape) == g["enc_out"].shape
+    for b, L in enumerate(g["enc_lens"]):  # rows past the length are padding the reference does not define either
+        err = np.abs(enc_out[b, :L].cpu().numpy() - g["enc_out"][b, :L]).max()
+        assert err < 0.06 * max(1.0, np.abs(g["enc_out"][b, :L]).max()), err
+    want = torch.tensor(g["enc_out"]).cuda()
+    lp = model.ctc.log_softmax(want)
+    np.testing.assert_allclose(lp.cpu().numpy(), g["ctc_logp"], atol=0.05)
+    am = model.ctc.argmax(want).cpu().numpy()
+    # bf16 logits may flip near-ties: the chosen class must be within the tolerance of the best one
+    ref_lp = torch.tensor(g["ctc_logp"])
+    chosen = ref_lp.gather(2, torch.tensor(am)[..., None])[..., 0]
+    assert float((ref_lp.max(2).values - chosen).max()) < 0.05
+    assert (am == g["ctc_argmax"]).mean() > 0.9
+    # the model's flat buffers serve the sub-modules' scoring calls: no second pack
+    assert "_pp" not in model.decoder.__dict__ and "_pp" not in model.ctc.__dict__
+
+    ys = torch.tensor(g["ys"]).cuda()
+    x = want[0, : int(g["enc_lens"][0])]
+    xs = x.unsqueeze(0).expand(ys.shape[0], -1, -1)
+    states = [None] * ys.shape[0]
+    for l in range(1, ys.shape[1] + 1):
+        logp, states = model.decoder.batch_score(ys[:, :l], states, xs)
+        assert logp.shape == (ys.shape[0], V) and len(states) == ys.shape[0] and len(states[0]) == 2
+        assert states[0][0].shape == (l, 16)
+        np.testing.assert_allclose(logp.cpu().numpy(), g["logp_steps"][l - 1], atol=0.06)
+        np.testing.assert_allclose(logp.exp().sum(-1).cpu().numpy(), 1.0, rtol=1e-4)
+    cache = torch.stack([torch.stack([states[b][i] for b in range(ys.shape[0])]) for i in range(2)])
+    err = (cache.cpu() - torch.tensor(g["cache"])).abs().max().item()
+    assert err < 0.06 * max(1.0, float(np.abs(g["cache"]).max())), err
+    st = None
+    for l in range(1, 4):
+        lp1, st = model.decoder.score(ys[1, :l], st, x)
+        assert lp1.shape == (V,)
+        np.testing.assert_allclose(lp1.cpu().numpy(), g["logp_one"][l - 1], atol=0.06)
+    # a cache of the wrong length is refused rather than ignored
+    with pytest.raises(AssertionError):
+        model.decoder.forward_one_step(ys[:, :3], None, xs, cache=[torch.zeros(3, 1, 16).cuda()] * 2)
+    # stand-alone decoder (not inside a model) packs its own parameters
+    dec2 = m.TransformerDecoder(V, 16, 2, 32, 2).cuda().eval()
+    _load(dec2, {k: v.cuda() for k, v in sd.items()}, "decoder.")
+    lp2, _ = dec2.forward_one_step(ys, None, xs)
+    np.testing.assert_allclose(lp2.cpu().numpy(), g["logp_steps"][-1], atol=0.06)
+    # training mode keeps working after the scoring calls (same flat buffers)
+    model.train()
+    _, _, text, tl = _batch(V=V)
+    loss, _, _ = model(torch.tensor(g["wav"]).cuda(), torch.tensor(g["lens"]).cuda(), text[:, :4].clamp(max=V - 2).cuda(),
+                       torch.tensor([4, 4, 4]).cuda())
+    loss.backward()
+    assert torch.isfinite(loss).all() and all(p.grad is not None for p in model.decoder.parameters())
+
+
 def test_global_mvn_and_ratio_specaug_modules(golden_dir, tmp_path):
     """GlobalMVN / SpecAug(time_mask_width_ratio_range) drop-ins against outputs of the unmodified reference."""
     import os

@@ -131,6 +131,40 @@ def test_encoder_and_bn_running_stats():
         np.testing.assert_allclose(rv.numpy(), g["after/" + p + ".norm.running_var"], rtol=1e-4, atol=1e-6)
 
 
+def test_eval_encode_and_incremental_decoding():
+    """Next-row N2: eval-mode encode (BN running statistics), CTC log_softmax / argmax, and the decoder's cached
+    one-step scoring against batch_score / score of the unmodified reference (tests/golden/decode.npz)."""
+    g = load("decode.npz")
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/")}
+    cfg = tiny_cfg("latest")
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    lens = torch.tensor(g["lens"])
+    feats, flens = om.frontend_logmel(torch.tensor(g["wav"]), lens, mel)
+    enc, olens = om.conformer_encoder(om.utterance_mvn(feats, flens), flens, sd, cfg.enc, training=False)
+    assert olens.tolist() == g["enc_lens"].tolist()
+    np.testing.assert_allclose(enc.numpy(), g["enc_out"], rtol=1e-4, atol=2e-5)
+    logp = torch.log_softmax(om.linear(torch.tensor(g["enc_out"]), sd, "ctc.ctc_lo"), dim=2)
+    np.testing.assert_allclose(logp.numpy(), g["ctc_logp"], rtol=1e-5, atol=1e-5)
+    assert np.array_equal(logp.argmax(2).numpy(), g["ctc_argmax"])
+    ys = torch.tensor(g["ys"])
+    x = torch.tensor(g["enc_out"])[0, : int(g["enc_lens"][0])]
+    xs = x.unsqueeze(0).expand(ys.shape[0], -1, -1)
+    cache = None
+    for l in range(1, ys.shape[1] + 1):
+        lp, cache = om.decoder_forward_one_step(ys[:, :l], xs, sd, cfg.dec, cache)
+        np.testing.assert_allclose(lp.numpy(), g["logp_steps"][l - 1], rtol=1e-4, atol=1e-5)
+        # test/espnet2/asr/decoder/test_transformer_decoder.py / test/test_transformer_decode.py invariant:
+        # the cached step equals the un-cached one and the teacher-forced forward's row l-1
+        lp0, _ = om.decoder_forward_one_step(ys[:, :l], xs, sd, cfg.dec, None)
+        np.testing.assert_allclose(lp0.numpy(), lp.numpy(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(lp.numpy(), g["full_logp"][:, l - 1], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(torch.stack(cache).numpy(), g["cache"], rtol=1e-4, atol=1e-5)
+    st = None
+    for l in range(1, 4):
+        lp, st = om.decoder_forward_one_step(ys[1:2, :l], x[None], sd, cfg.dec, st)
+        np.testing.assert_allclose(lp[0].numpy(), g["logp_one"][l - 1], rtol=1e-4, atol=1e-5)
+
+
 @pytest.mark.parametrize("rel", ["latest", "legacy"])
 def test_whole_step_loss_and_grads(rel):
     g = load(f"e2e_{rel}.npz")
