@@ -63,7 +63,7 @@ _SIGNATURES = {
     "b200slu_gemm_bf16": [_I, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P],
     "b200slu_gemm_bf16_ex": [_P, _P, _P],
     "b200slu_layernorm_fwd": [_P, _P, _P, _I, _I, _F, _P, _P, _P, _P],
-    "b200slu_layernorm_bwd": [_P, _I, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _U64, _U32, _P],
+    "b200slu_layernorm_bwd": [_P, _I, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _F, _U64, _U32, _P],
     "b200slu_cast_bf16": [_P, _P, _L, _F, _F, _U64, _U32, _P],
     "b200slu_cast_colsum_bf16": [_P, _P, _I, _I, _F, _F, _U64, _U32, _P, _P],
     "b200slu_colsum_bf16": [_P, _I, _I, _L, _P, _P],

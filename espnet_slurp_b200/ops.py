@@ -167,14 +167,16 @@ def layernorm_fwd(x, gamma, beta, eps: float = 1e-12, want_bf16: bool = True, wa
 
 
 def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g: bool = False, g_alpha: float = 1.0,
-                  g_drop: Drop = None):
+                  g_drop: Drop = None, g_colsum_out=None):
+    """dx (+ dx_add) and, with want_g, g16 = bf16(g_alpha * dropout(dx)) whose column sums accumulate into g_colsum_out."""
     M, D = x.shape
     dx = torch.empty(M, D, device=x.device, dtype=torch.float32)
     g16 = torch.empty(M, D, device=x.device, dtype=torch.bfloat16) if want_g else None
+    assert g_colsum_out is None or want_g
     p, seed, site = _drop(g_drop)
     check(_lib.lib().b200slu_layernorm_bwd(ptr(dy), int(dy.dtype == torch.float32), ptr(x), ptr(gamma), ptr(stats),
-                                           ptr(dx_add), M, D, ptr(dx), ptr(dgamma), ptr(dbeta), ptr(g16), g_alpha, p, seed,
-                                           site, stream_ptr()), "layernorm_bwd")
+                                           ptr(dx_add), M, D, ptr(dx), ptr(dgamma), ptr(dbeta), ptr(g16), g_alpha,
+                                           ptr(g_colsum_out), p, seed, site, stream_ptr()), "layernorm_bwd")
     return dx, g16
 
 

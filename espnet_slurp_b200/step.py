@@ -124,16 +124,39 @@ def ffn_fwd(x, P, W, pre: str, norm: str, act: str, scale: float, p_drop: float,
     return y, (x, ln, st, hpre, h, d1, d2, pre, norm, act, scale)
 
 
-def ffn_bwd(dy, saved, P, W, G):
+# Backward of "x + dropout(branch(LN(x)))": a branch starts from g = bf16(alpha * dropout(dy)) plus the bias gradient of its
+# last Linear (column sums of g).  The LayerNorm backward that PRODUCES dy can emit both in the same pass (layernorm.cu),
+# so each *_bwd takes an optional ready-made ``g`` and the ``nxt`` head (alpha, drop, bias-gradient tensor) of the branch
+# that will consume its dx, and returns (dx, g for that branch or None).
+def _head_g(dy, g, head):
+    if g is not None:
+        return g
+    alpha, drop, bias_grad = head
+    return K.cast_bf16(dy, alpha=alpha, drop=drop, colsum_out=bias_grad)
+
+
+def _ln_bwd(dln, x, P, G, norm: str, st, dx_add, nxt):
+    if nxt is None:
+        return K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dx_add)
+    alpha, drop, bias_grad = nxt
+    return K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dx_add, want_g=True,
+                           g_alpha=alpha, g_drop=drop, g_colsum_out=bias_grad)
+
+
+def ffn_head(saved, G):
+    pre, scale, d2 = saved[7], saved[10], saved[6]
+    return scale, d2, G[pre + ".w_2.bias"]
+
+
+def ffn_bwd(dy, saved, P, W, G, g=None, nxt=None):
     x, ln, st, hpre, h, d1, d2, pre, norm, act, scale = saved
-    g = K.cast_bf16(dy, alpha=scale, drop=d2, colsum_out=G[pre + ".w_2.bias"])
+    g = _head_g(dy, g, (scale, d2, G[pre + ".w_2.bias"]))
     K.gemm(g, h, trans=True, out=G[pre + ".w_2.weight"], accumulate=True)
     dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad="mul")  # hpre = act' * dropout mask
     K.colsum(dh, G[pre + ".w_1.bias"])
     K.gemm(dh, ln, trans=True, out=G[pre + ".w_1.weight"], accumulate=True)
     dln = K.gemm(dh, W[pre + ".w_1.weight"], trans_b=True)
-    dx, _ = K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dy)
-    return dx
+    return _ln_bwd(dln, x, P, G, norm, st, dy, nxt)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -162,12 +185,16 @@ def relmha_fwd(x, pos16, klens, P, W, p: str, norm: str, cfg: EncCfg, B: int, T:
     return y, (x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, K.round8(Pn))
 
 
-def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int):
+def relmha_head(saved, G, p: str):
+    return 1.0, saved[11], G[p + ".self_attn.linear_out.bias"]
+
+
+def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int, g=None, nxt=None):
     x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, ld_bd = saved
     d, H = cfg.d, cfg.heads
     a = p + ".self_attn"
     k, v = qkv[:, d:2 * d], qkv[:, 2 * d:]
-    g = K.cast_bf16(dy, alpha=1.0, drop=do, colsum_out=G[a + ".linear_out.bias"])
+    g = _head_g(dy, g, (1.0, do, G[a + ".linear_out.bias"]))
     K.gemm(g, c, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
@@ -184,8 +211,7 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
     K.colsum(dqkv, G[a + ".linear_qkv.bias"])
     K.gemm(dqkv, ln, trans=True, out=G[a + ".linear_qkv.weight"], accumulate=True)
     dln = K.gemm(dqkv, W[a + ".linear_qkv.weight"], trans_b=True)
-    dx, _ = K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dy)
-    return dx
+    return _ln_bwd(dln, x, P, G, norm, st, dy, nxt)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -214,10 +240,14 @@ def convmod_fwd(x, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: St
     return y, (x, ln, st, pw1, dw, mr, bs, do)
 
 
-def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int):
+def convmod_head(saved, G, p: str):
+    return 1.0, saved[7], G[p + ".conv_module.pointwise_conv2.bias"]
+
+
+def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int, g=None, nxt=None):
     x, ln, st, pw1, dw, mr, bs, do = saved
     cm = p + ".conv_module"
-    g = K.cast_bf16(dy, alpha=1.0, drop=do, colsum_out=G[cm + ".pointwise_conv2.bias"])
+    g = _head_g(dy, g, (1.0, do, G[cm + ".pointwise_conv2.bias"]))
     K.gemm(g, bs, trans=True, out=G[cm + ".pointwise_conv2.weight"], accumulate=True)
     dbs = K.gemm(g, W[cm + ".pointwise_conv2.weight"], trans_b=True)
     ddw = K.bn_swish_bwd(dbs, dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"], G[cm + ".norm.weight"],
@@ -228,8 +258,7 @@ def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: i
     K.colsum(dpw1, G[cm + ".pointwise_conv1.bias"])
     K.gemm(dpw1, ln, trans=True, out=G[cm + ".pointwise_conv1.weight"], accumulate=True)
     dln = K.gemm(dpw1, W[cm + ".pointwise_conv1.weight"], trans_b=True)
-    dx, _ = K.layernorm_bwd(dln, x, P[norm + ".weight"], st, G[norm + ".weight"], G[norm + ".bias"], dx_add=dy)
-    return dx
+    return _ln_bwd(dln, x, P, G, norm, st, dy, nxt)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -244,15 +273,14 @@ def enc_layer_fwd(x, pos16, klens, P, W, p: str, cfg: EncCfg, B: int, T: int, ct
     return y, (s1, s2, s3, s4, x, st)
 
 
-def enc_layer_bwd(dy, saved, pos16, P, W, G, p: str, cfg: EncCfg, B: int, T: int):
+def enc_layer_bwd(dy, saved, pos16, P, W, G, p: str, cfg: EncCfg, B: int, T: int, nxt=None):
+    """Returns (dx, g): g is the ready-made branch gradient for the head ``nxt`` of whatever consumes dx (or None)."""
     s1, s2, s3, s4, x4, st = saved
-    n = p + ".norm_final"
-    dx, _ = K.layernorm_bwd(dy, x4, P[n + ".weight"], st, G[n + ".weight"], G[n + ".bias"])
-    dx = ffn_bwd(dx, s4, P, W, G)
-    dx = convmod_bwd(dx, s3, P, W, G, p, p + ".norm_conv", cfg, B, T)
-    dx = relmha_bwd(dx, s2, pos16, P, W, G, p, p + ".norm_mha", cfg, B, T)
-    dx = ffn_bwd(dx, s1, P, W, G)
-    return dx
+    dx, g = _ln_bwd(dy, x4, P, G, p + ".norm_final", st, None, ffn_head(s4, G))
+    dx, g = ffn_bwd(dx, s4, P, W, G, g, convmod_head(s3, G, p))
+    dx, g = convmod_bwd(dx, s3, P, W, G, p, p + ".norm_conv", cfg, B, T, g, relmha_head(s2, G, p))
+    dx, g = relmha_bwd(dx, s2, pos16, P, W, G, p, p + ".norm_mha", cfg, B, T, g, ffn_head(s1, G))
+    return ffn_bwd(dx, s1, P, W, G, g, nxt)
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -294,13 +322,16 @@ def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=
     feats, h1, h2v, dpos, pos16, layers, xl, st, col, B, T = saved
     e = p + ".embed"
     dx, _ = K.layernorm_bwd(denc, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
+    embed_head = (math.sqrt(cfg.d), dpos, G[e + ".out.0.bias"])
+    g = None
     for n in reversed(range(cfg.blocks)):
-        dx = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T)
+        # block 0 hands its dx to the embedding's output Linear, the others to the previous block's norm_final (fp32 only)
+        dx, g = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T, embed_head if n == 0 else None)
         layers[n] = None  # free the block's activations as we go
         if on_ready is not None:
             on_ready("enc%d" % n)
     C_ = h1.shape[-1]
-    g = K.cast_bf16(dx, alpha=math.sqrt(cfg.d), drop=dpos, colsum_out=G[e + ".out.0.bias"])
+    g = _head_g(dx, g, embed_head)
     K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
     dh2 = K.gemm(g, W[e + ".out.0.weight"], trans_b=True, act_grad_input=h2v, act_grad="relu").view(-1, C_)
     K.colsum(dh2, G[e + ".conv.2.bias"])
@@ -358,16 +389,16 @@ def dec_layer_fwd(x, mem16, ylens, mlens, P, W, p: str, cfg: DecCfg, B: int, L: 
     return x3, (x, ln1, st1, c1, sa, do1, x1, ln2, st2, c2, ca, do2, sf)
 
 
-def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, L: int, T: int):
-    """Returns dx; accumulates the memory gradient into dmem (f32 [B*T, d], in place via the GEMM residual input)."""
+def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, L: int, T: int, g=None, nxt=None):
+    """Returns (dx, g for the head ``nxt``); accumulates the memory gradient into dmem (f32 [B*T, d], in place via the GEMM
+    residual input)."""
     x, ln1, st1, c1, sa, do1, x1, ln2, st2, c2, ca, do2, sf = saved
     d, H = cfg.d, cfg.heads
-    dx2 = ffn_bwd(dy, sf, P, W, G)
-    # ---- source attention
     a = p + ".src_attn"
+    dx2, g = ffn_bwd(dy, sf, P, W, G, g, (1.0, do2, G[a + ".linear_out.bias"]))
+    # ---- source attention
     (q, kv), pr, pd, da, scale = ca
     k, v = kv[:, :d], kv[:, d:]
-    g = K.cast_bf16(dx2, alpha=1.0, drop=do2, colsum_out=G[a + ".linear_out.bias"])
     K.gemm(g, c2, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dkv = torch.empty_like(kv)
@@ -382,12 +413,11 @@ def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, 
     K.colsum(dq, G[a + ".linear_q.bias"])
     K.gemm(dq, ln2, trans=True, out=G[a + ".linear_q.weight"], accumulate=True)
     dln2 = K.gemm(dq, W[a + ".linear_q.weight"], trans_b=True)
-    dx1, _ = K.layernorm_bwd(dln2, x1, P[p + ".norm2.weight"], st2, G[p + ".norm2.weight"], G[p + ".norm2.bias"], dx_add=dx2)
-    # ---- self attention
     a = p + ".self_attn"
+    dx1, g = _ln_bwd(dln2, x1, P, G, p + ".norm2", st2, dx2, (1.0, do1, G[a + ".linear_out.bias"]))
+    # ---- self attention
     (qkv,), pr, pd, da, scale = sa
     q, k, v = qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:]
-    g = K.cast_bf16(dx1, alpha=1.0, drop=do1, colsum_out=G[a + ".linear_out.bias"])
     K.gemm(g, c1, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
@@ -399,8 +429,7 @@ def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, 
     K.colsum(dqkv, G[a + ".linear_qkv.bias"])
     K.gemm(dqkv, ln1, trans=True, out=G[a + ".linear_qkv.weight"], accumulate=True)
     dln1 = K.gemm(dqkv, W[a + ".linear_qkv.weight"], trans_b=True)
-    dx, _ = K.layernorm_bwd(dln1, x, P[p + ".norm1.weight"], st1, G[p + ".norm1.weight"], G[p + ".norm1.bias"], dx_add=dx1)
-    return dx
+    return _ln_bwd(dln1, x, P, G, p + ".norm1", st1, dx1, nxt)
 
 
 def decoder_fwd(mem16, mlens, ys_in, ys_in_lens, P, W, cfg: DecCfg, ctx: StepCtx, B: int, T: int, p: str = "decoder"):
@@ -428,9 +457,10 @@ def decoder_bwd(dlogits16, dmem, saved, mem16, P, W, G, cfg: DecCfg, B: int, T: 
     K.colsum(dlogits16, G[p + ".output_layer.bias"], n=V)
     K.gemm(gl, ln, trans=True, out=G[p + ".output_layer.weight"], accumulate=True)
     dln = K.gemm(gl, W[p + ".output_layer.weight"], trans_b=True)
-    dx, _ = K.layernorm_bwd(dln, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
+    dx, g = _ln_bwd(dln, xl, P, G, p + ".after_norm", st, None, ffn_head(layers[-1][12], G))
     for n in reversed(range(cfg.blocks)):
-        dx = dec_layer_bwd(dx, dmem, layers[n], mem16, P, W, G, f"{p}.decoders.{n}", cfg, B, L, T)
+        nxt = ffn_head(layers[n - 1][12], G) if n > 0 else None  # the block below starts its backward with its FFN branch
+        dx, g = dec_layer_bwd(dx, dmem, layers[n], mem16, P, W, G, f"{p}.decoders.{n}", cfg, B, L, T, g, nxt)
         layers[n] = None
     K.embed_bwd(dx, tok, math.sqrt(cfg.d), G[p + ".embed.0.weight"], drop=de)
 

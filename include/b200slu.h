@@ -123,10 +123,12 @@ int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epil
 int b200slu_layernorm_fwd(const float* x, const float* gamma, const float* beta, int M, int D, float eps, void* y_bf16,
                           float* y_f32, float* stats, void* stream);
 /* dx = LN'(dy) (+ dx_add); dgamma/dbeta accumulated; optional g_bf16 = bf16(g_alpha * dropout(dx)),
- * the branch gradient the next dgrad GEMM consumes (encoder_layer.py:101,129,138,144). */
+ * the branch gradient the next dgrad GEMM consumes (encoder_layer.py:101,129,138,144), and with it optionally
+ * g_colsum_accum[D] += column sums of g_alpha * dropout(dx): the bias gradient of that branch's last Linear. */
 int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float* x, const float* gamma, const float* stats,
                           const float* dx_add, int M, int D, float* dx, float* dgamma_accum, float* dbeta_accum, void* g_bf16,
-                          float g_alpha, float drop_p, unsigned long long seed, unsigned int site, void* stream);
+                          float g_alpha, float* g_colsum_accum, float drop_p, unsigned long long seed, unsigned int site,
+                          void* stream);
 
 /* ---- small helpers around the GEMMs ---------------------------------------------------------- */
 /* y = bf16(alpha * dropout(x)) (weight casts; embedding.py:244 dropout on pos_emb) */

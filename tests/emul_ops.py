@@ -131,7 +131,7 @@ def layernorm_fwd(x, gamma, beta, eps=1e-12, want_bf16=True, want_f32=False):
     return (_r(y) if want_bf16 else None), (y if want_f32 else None), torch.cat([mean, rstd], 1)
 
 
-def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g=False, g_alpha=1.0, g_drop=None):
+def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g=False, g_alpha=1.0, g_drop=None, g_colsum_out=None):
     _nodrop(g_drop)
     dy = dy.float()
     mean, rstd = stats[:, 0:1], stats[:, 1:2]
@@ -142,6 +142,8 @@ def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g=False,
         dx = dx + dx_add
     dgamma += (dy * xh).sum(0)
     dbeta += dy.sum(0)
+    if g_colsum_out is not None:
+        g_colsum_out += (dx * g_alpha).float().sum(0)
     return dx, (_r(dx * g_alpha) if want_g else None)
 
 

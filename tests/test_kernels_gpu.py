@@ -98,6 +98,17 @@ def test_layernorm(M, D):
         close(g16, wg16, 1e-2, "ln g16")
         close(dg, wg, 1e-4, "ln dgamma")
         close(db, wb, 1e-4, "ln dbeta")
+        # fused branch head: g16 with dropout + its column sums (accumulated) must equal the separate cast_colsum pass
+        drop = (0.1, 77, 5)
+        cs, dg2, db2 = torch.ones(D, device="cuda"), torch.zeros(D, device="cuda"), torch.zeros(D, device="cuda")
+        dx2, g2 = K().layernorm_bwd(dy.cuda(), x.cuda(), ga.cuda(), st, dg2, db2, dx_add=add.cuda(), want_g=True, g_alpha=0.5,
+                                    g_drop=drop, g_colsum_out=cs)
+        assert torch.equal(dx2, dx)
+        cs_ref = torch.ones(D, device="cuda")
+        g_ref = K().cast_bf16(dx, alpha=0.5, drop=drop, colsum_out=cs_ref)
+        assert torch.equal(g2, g_ref)
+        close(cs, cs_ref, 1e-4, "ln g colsum")
+        close(dg2, wg, 1e-4, "ln dgamma (fused head)")
 
 
 # ---------------------------------------------------------------------------------------------- small helpers
