@@ -6,6 +6,8 @@
 // transposes (:67, :79) disappear.  Memory-bound; shared-memory staging of a (TT + K - 1) x 64 halo
 // tile, 16-byte vector loads, per-channel statistics reduced in shared memory then one atomic per
 // channel per block.  Algorithmic bytes per position (bf16): fwd pass A 2*(2C) + 2*C, pass B 2*C + 2*C.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -17,26 +19,48 @@ constexpr int KMAX = 31;  // cnn_module_kernel upper bound (SLURP/LibriSpeech: 3
 // KT = compile-time kernel size (31 for every recipe; 0 = run-time K <= KMAX for the small test fixtures): with KT the
 // tap loops carry no run-time predicates (they were 70 % of the instructions of the first version).
 
-// stage glu(pw1) for frames [t0 - pad, t0 + TT + pad) x channels [c0, c0 + CC) into smem (0 outside [0, T))
-template <int TT>
-__device__ __forceinline__ void stage_glu(const bf16* __restrict__ pw1, int b, int T, int C, int t0, int c0, int K,
-                                          float (*sm)[CC]) {
-  const int pad = (K - 1) / 2, nf = TT + K - 1;
-  for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
+// Stage glu(pw1) -- and for the backward d_dw -- for frames [t0 - pad, t0 + TT + pad) x channels [c0, c0 + CC) into
+// shared memory as fp32 (0 outside [0, T)).  All of a thread's 16-byte loads are issued before the first one is used:
+// a tile costs one memory round trip, not one per item (the staging loop used to be a third of the backward's time).
+template <int TT, bool BWD>
+__device__ __forceinline__ void stage_tiles(const bf16* __restrict__ pw1, const bf16* __restrict__ d_dw, int b, int T, int C,
+                                            int t0, int c0, int K, float (*sg)[CC], float (*sd)[CC]) {
+  constexpr int U = ((TT + KMAX - 1) * (CC / 8) + 255) / 256;  // items per thread of a 256-thread block
+  const int pad = (K - 1) / 2, nitems = (TT + K - 1) * (CC / 8);
+  uint4 ra[U], rg[U], rd[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int it = threadIdx.x + u * 256;
     const int f = it / (CC / 8), cg = it - f * (CC / 8);
     const int t = t0 - pad + f, c = c0 + cg * 8;
-    float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (t >= 0 && t < T && c < C) {
-      float a[8], gt[8];
+    ra[u] = rg[u] = rd[u] = make_uint4(0u, 0u, 0u, 0u);
+    if (it < nitems && t >= 0 && t < T && c < C) {
       const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
-      load8_bf16(row + c, a);
-      load8_bf16(row + C + c, gt);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) g[j] = a[j] * sigmoidf_(gt[j]);
+      ra[u] = *reinterpret_cast<const uint4*>(row + c);
+      rg[u] = *reinterpret_cast<const uint4*>(row + C + c);
+      if (BWD) rd[u] = *reinterpret_cast<const uint4*>(d_dw + ((long long)b * T + t) * C + c);
     }
-    float4* dst = reinterpret_cast<float4*>(&sm[f][cg * 8]);
-    dst[0] = make_float4(g[0], g[1], g[2], g[3]);
-    dst[1] = make_float4(g[4], g[5], g[6], g[7]);
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int it = threadIdx.x + u * 256;
+    if (it < nitems) {
+      const int f = it / (CC / 8), cg = it - f * (CC / 8);
+      float a[8], gt[8], g[8];
+      unpack8_bf16(ra[u], a);
+      unpack8_bf16(rg[u], gt);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) g[q] = a[q] * sigmoidf_(gt[q]);  // 0 * sigmoid(0) = 0 outside the utterance
+      float4* dst = reinterpret_cast<float4*>(&sg[f][cg * 8]);
+      dst[0] = make_float4(g[0], g[1], g[2], g[3]);
+      dst[1] = make_float4(g[4], g[5], g[6], g[7]);
+      if (BWD) {
+        unpack8_bf16(rd[u], g);
+        float4* dd = reinterpret_cast<float4*>(&sd[f][cg * 8]);
+        dd[0] = make_float4(g[0], g[1], g[2], g[3]);
+        dd[1] = make_float4(g[4], g[5], g[6], g[7]);
+      }
+    }
   }
 }
 
@@ -67,7 +91,7 @@ __global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict_
   for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
   const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
   __syncthreads();  // previous tile fully consumed
-  stage_glu<TT>(pw1, b, T, C, t0, c0, K, sm);
+  stage_tiles<TT, false>(pw1, nullptr, b, T, C, t0, c0, K, sm, nullptr);
   __syncthreads();
   if (c < C) {
 #pragma unroll 1
@@ -119,35 +143,33 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
   float (*sd)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + (TT + KMAX - 1) * CC);      // d_dw halo tile
   // dW partial (+ dbias); rows padded to an odd stride so that the 32 channels of a warp hit 32 different banks
   float (*swg)[KMAX + 2] = reinterpret_cast<float (*)[KMAX + 2]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);
+  // reversed taps [KMAX][CC]: swr[m][ch] = w[ch][K-1-m] (0 for m >= K); re-read per tile so that the staging phase has the
+  // whole register file for its loads in flight
+  float (*swr)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + 2 * (TT + KMAX - 1) * CC + CC * (KMAX + 2));
   const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
-  const int pad = (K - 1) / 2, nf = TT + K - 1;
+  const int pad = (K - 1) / 2;
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;
   const int c = c0 + cl;
   const int ntt = (T + TT - 1) / TT;
-  float wrev[KMAX], acc[KMAX];  // wrev[m] = w[K-1-m]: keeps every register-array index a compile-time constant
-#pragma unroll
-  for (int k = 0; k < KMAX; ++k) {
-    wrev[k] = (c < C && k < K) ? w[c * K + (K - 1 - k)] : 0.f;
-    acc[k] = 0.f;
-  }
-  float accb = 0.f;
   for (int it = threadIdx.x; it < CC * (KMAX + 2); it += blockDim.x) (&swg[0][0])[it] = 0.f;
+  for (int it = threadIdx.x; it < KMAX * CC; it += blockDim.x) {
+    const int m = it / CC, ch = it - m * CC;
+    swr[m][ch] = (c0 + ch < C && m < K) ? w[(c0 + ch) * K + (K - 1 - m)] : 0.f;
+  }
   for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
     const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
-    __syncthreads();  // previous tile fully consumed
-    stage_glu<TT>(pw1, b, T, C, t0, c0, K, sg);
-    for (int it = threadIdx.x; it < nf * (CC / 8); it += blockDim.x) {
-      const int f = it / (CC / 8), cg = it - f * (CC / 8);
-      const int t = t0 - pad + f, cc = c0 + cg * 8;
-      float g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-      if (t >= 0 && t < T && cc < C) load8_bf16(d_dw + ((long long)b * T + t) * C + cc, g);
-      float4* dst = reinterpret_cast<float4*>(&sd[f][cg * 8]);
-      dst[0] = make_float4(g[0], g[1], g[2], g[3]);
-      dst[1] = make_float4(g[4], g[5], g[6], g[7]);
-    }
+    __syncthreads();  // previous tile fully consumed (and, the first time, swg / swr written)
+    stage_tiles<TT, true>(pw1, d_dw, b, T, C, t0, c0, K, sg, sd);
     __syncthreads();
     if (c < C) {
+     float wrev[KMAX], acc[KMAX];  // wrev[m] = w[K-1-m]: keeps every register-array index a compile-time constant
+#pragma unroll
+     for (int k = 0; k < KMAX; ++k) {
+       wrev[k] = swr[k][cl];
+       acc[k] = 0.f;
+     }
+     float accb = 0.f;
 #pragma unroll 1
      for (int sub = 0; sub < TT / (4 * FR); ++sub) {
       const int f0 = sub * 4 * FR + fr * FR;
@@ -198,13 +220,12 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
         }
       }
      }
-    }
-  }
-  if (c < C) {
+     // this tile's weight / bias gradient partials join the block's (4 frame lanes per address)
 #pragma unroll
-    for (int k = 0; k < KMAX; ++k)
-      if (k < K) atomicAdd(&swg[cl][k], acc[k]);
-    atomicAdd(&swg[cl][KMAX], accb);
+     for (int k = 0; k < KMAX; ++k)
+       if (k < K) atomicAdd(&swg[cl][k], acc[k]);
+     atomicAdd(&swg[cl][KMAX], accb);
+    }
   }
   __syncthreads();
   for (int it = threadIdx.x; it < CC * K; it += blockDim.x) {
@@ -392,6 +413,16 @@ __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __r
   }
 }
 
+// Frames per tile for K = 31: every tile stages TT + 30 frames and pays two block barriers, so pick the tile length that
+// stages the fewest frames for this T (T = 124: one 128-frame tile, 158 staged, instead of two 96-frame tiles, 252).
+int dw_tile_frames(int T) {
+  static const int forced = getenv("B200SLU_DW_TT") ? atoi(getenv("B200SLU_DW_TT")) : 0;  // tuning only
+  if (forced == 32 || forced == 96 || forced == 128) return forced;
+  if (T <= 64) return 32;
+  const int c96 = ((T + 95) / 96) * (96 + 30), c128 = ((T + 127) / 128) * (128 + 30);
+  return c128 <= c96 ? 128 : 96;
+}
+
 }  // namespace
 
 extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const float* bias, int B, int T, int C, int K, void* out,
@@ -411,7 +442,9 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
                                                                   bn_sums);                                           \
   } while (0)
   if (K == 31) {
-    if (T > 64) B2_FWD(96, 31);
+    const int tt = dw_tile_frames(T);
+    if (tt == 128) B2_FWD(128, 31);
+    else if (tt == 96) B2_FWD(96, 31);
     else B2_FWD(32, 31);
   } else {
     B2_FWD(32, 0);
@@ -432,7 +465,7 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                                 \
     int gy = (2 * b2_num_sms() + ctiles - 1) / ctiles;                                                                       \
     if (gy > units) gy = units;                                                                                              \
-    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 2)) * sizeof(float);                               \
+    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 2) + KMAX * CC) * sizeof(float);                               \
     auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
     static bool cfg = false;                                                                                                 \
     if (!cfg) {                                                                                                              \
@@ -443,7 +476,9 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
                                               dbias_accum);                                                                  \
   } while (0)
   if (K == 31) {
-    if (T > 64) B2_BWD(96, 31);
+    const int tt = dw_tile_frames(T);
+    if (tt == 128) B2_BWD(128, 31);
+    else if (tt == 96) B2_BWD(96, 31);
     else B2_BWD(32, 31);
   } else {
     B2_BWD(32, 0);

@@ -9,7 +9,7 @@ from espnet_slurp_b200 import ops
 
 torch.manual_seed(0)
 dev = "cuda"
-B, T, d, F, H, K = 128, 155, 512, 2048, 8, 31
+B, T, d, F, H, K = 128, int(os.environ.get("MB_T", 155)), 512, 2048, 8, 31
 M = B * T
 ROT = 6
 peak = 6500.0
