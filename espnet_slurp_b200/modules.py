@@ -393,19 +393,23 @@ class _EncoderFn(torch.autograd.Function):
         B = xs.shape[0]
         bn = mod._bn_buffers()
         enc, _, olens, saved = S.encoder_fwd(xs.float().contiguous(), _i32(ilens, xs.device), pp.P, pp.W, mod._cfg, mod._ctx(),
-                                             p="encoder", bn_buffers=bn)
+                                             p="encoder", bn_buffers=bn, want_inter_f32=True)
         ctx.mod, ctx.saved = mod, saved
         olens = olens.to(torch.long)
         ctx.mark_non_differentiable(olens)
-        return enc.view(B, -1, mod._cfg.d), olens
+        d = mod._cfg.d
+        # intermediate-CTC taps (fp32, after_norm'ed) are further differentiable outputs, in block order
+        return (enc.view(B, -1, d), olens, *[tap[4].view(B, -1, d) for tap in saved[11]])
 
     @staticmethod
-    def backward(ctx, denc, _dolens):
+    def backward(ctx, denc, _dolens, *dtaps):
         mod = ctx.mod
         pp = mod._pp
         pp.zero_grad()
         d = mod._cfg.d
-        S.encoder_bwd(denc.float().contiguous().view(-1, d), ctx.saved, pp.P, pp.W, pp.G, mod._cfg, p="encoder")
+        dinter = {tap[0]: g.float().contiguous().view(-1, d) for tap, g in zip(ctx.saved[11], dtaps) if g is not None}
+        denc = denc.float().contiguous().view(-1, d) if denc is not None else torch.zeros_like(ctx.saved[6])
+        S.encoder_bwd(denc, ctx.saved, pp.P, pp.W, pp.G, mod._cfg, p="encoder", dinter=dinter)
         ctx.saved = None
         return (None, None, None, *_grads_out(pp, mod._names, 1.0))
 
@@ -449,17 +453,15 @@ class _CTCFn(torch.autograd.Function):
         # the loss and its gradients (w.r.t. the encoder output and ctc_lo) come out of one pass over the lattice
         loss, denc = S.ctc_head(enc16, _i32(hlens, hs.device), _i32(ys_pad, hs.device), _i32(ys_lens, hs.device), pp.P, pp.W,
                                 pp.G, mod._odim, B, T, 1.0, p="ctc", want_grad=True)
-        ctx.mod, ctx.denc, ctx.dims = mod, denc, (B, T, d)
-        ctx.gen = mod._gen = mod.__dict__.get("_gen", 0) + 1
+        # ctc_lo's gradients are copied out of the shared buffers now (1.2 MB at V = 600): the reference calls the same CTC
+        # module once per intermediate-CTC tap before any backward (espnet_model.py:230-232)
+        ctx.denc, ctx.dims, ctx.pgrads = denc, (B, T, d), _grads_out(pp, mod._names, 1.0)
         return loss.reshape(())
 
     @staticmethod
     def backward(ctx, g):
-        mod = ctx.mod
-        if ctx.gen != mod._gen:
-            raise RuntimeError("CTC: a later forward() overwrote this call's gradient buffers; call backward() first")
         B, T, d = ctx.dims
-        return (None, (ctx.denc * g).view(B, T, d), None, None, None, *_grads_out(mod._pp, mod._names, g))
+        return (None, (ctx.denc * g).view(B, T, d), None, None, None, *[p * g for p in ctx.pgrads])
 
 
 class _ModelFn(torch.autograd.Function):
@@ -479,9 +481,11 @@ class _ModelFn(torch.autograd.Function):
                                       want_grad=want)
         ctx.model = model
         ctx.gen = model._gen = model.__dict__.get("_gen", 0) + 1
-        for k in ("loss_ctc", "loss_att", "acc"):
-            ctx.mark_non_differentiable(out[k])
-        return out["loss"].reshape(()), out["loss_ctc"].reshape(()), out["loss_att"].reshape(()), out["acc"].reshape(())
+        ic = [out[f"loss_interctc_layer{i}"].reshape(()) for i in (model._cfg.enc.interctc_layer_idx if model._cfg.interctc_weight
+                                                                   != 0.0 else ())]
+        ret = (out["loss"].reshape(()), out["loss_ctc"].reshape(()), out["loss_att"].reshape(()), out["acc"].reshape(()), *ic)
+        ctx.mark_non_differentiable(*ret[1:])
+        return ret
 
     @staticmethod
     def backward(ctx, g, *_):
@@ -530,7 +534,9 @@ class ConformerEncoder(_Packed):
             raise ValueError("pos_enc_layer_type and selfattention_layer_type must both be legacy or both be latest")
         _unsupported(activation_type != "swish", f"activation_type={activation_type!r}")
         _unsupported(zero_triu, "zero_triu")
-        _unsupported(len(interctc_layer_idx) > 0 or interctc_use_conditioning, "intermediate CTC")
+        _unsupported(interctc_use_conditioning, "self-conditioned intermediate CTC (interctc_use_conditioning)")
+        if len(interctc_layer_idx) > 0:
+            assert 0 < min(interctc_layer_idx) and max(interctc_layer_idx) < num_blocks  # conformer_encoder.py:284-285
         sd = stochastic_depth_rate
         _unsupported((any(sd) if isinstance(sd, (list, tuple)) else sd != 0.0) or layer_drop_rate != 0.0,
                      "stochastic depth / layer drop")
@@ -545,7 +551,7 @@ class ConformerEncoder(_Packed):
         self.conditioning_layer = None
         self._cfg = S.EncCfg(input_size, output_size, attention_heads, linear_units, num_blocks, cnn_module_kernel,
                              "latest" if pos_enc_layer_type == "rel_pos" else "legacy", dropout_rate, positional_dropout_rate,
-                             attention_dropout_rate)
+                             attention_dropout_rate, tuple(sorted(set(int(i) for i in interctc_layer_idx))))
         self._names = [self._prefix + n for n, _ in self.named_parameters()]
 
     def output_size(self) -> int:
@@ -558,7 +564,9 @@ class ConformerEncoder(_Packed):
         if short:  # conformer_encoder.py:320-327
             raise TooShortUttError(f"has {xs_pad.size(1)} frames and is too short for subsampling "
                                    f"(it needs more than {limit} frames), return empty results", xs_pad.size(1), limit)
-        xs, olens = _EncoderFn.apply(self, xs_pad, ilens, *self.parameters())
+        xs, olens, *taps = _EncoderFn.apply(self, xs_pad, ilens, *self.parameters())
+        if taps:  # conformer_encoder.py:366-367
+            return (xs, list(zip(self._cfg.interctc_layer_idx, taps))), olens, None
         return xs, olens, None
 
 
@@ -702,8 +710,7 @@ class ESPnetASRModel(_Packed):
         _unsupported(preencoder is not None or postencoder is not None or joint_network is not None,
                      "pre/post-encoders and transducer joint networks")
         _unsupported(ctc_weight in (0.0, 1.0), "pure attention (ctc_weight 0) or pure CTC (ctc_weight 1) training")
-        _unsupported(interctc_weight != 0.0 or length_normalized_loss or lang_token_id != -1,
-                     "interctc / length-normalised loss / language tokens")
+        _unsupported(length_normalized_loss or lang_token_id != -1, "length-normalised loss / language tokens")
         _unsupported(not isinstance(encoder, ConformerEncoder) or not isinstance(decoder, TransformerDecoder) or
                      not isinstance(ctc, CTC), "mixing reference encoder/decoder/ctc modules into the fused model")
         token_list = list(token_list)
@@ -712,13 +719,16 @@ class ESPnetASRModel(_Packed):
         self.sos = token_list.index(sym_sos) if sym_sos in token_list else vocab_size - 1
         self.eos = token_list.index(sym_eos) if sym_eos in token_list else vocab_size - 1
         _unsupported(self.sos != vocab_size - 1 or self.eos != vocab_size - 1, "sos/eos other than the last token")
-        self.vocab_size, self.ignore_id, self.ctc_weight, self.interctc_weight = vocab_size, ignore_id, ctc_weight, 0.0
+        self.vocab_size, self.ignore_id, self.ctc_weight = vocab_size, ignore_id, ctc_weight
+        self.interctc_weight = interctc_weight
         self.token_list = token_list
         self.frontend, self.specaug, self.normalize = frontend, specaug, normalize
         self.preencoder = self.postencoder = None
         self.encoder, self.decoder, self.ctc = encoder, decoder, ctc
         self.extract_feats_in_collect_stats = extract_feats_in_collect_stats
-        self._cfg = S.ModelCfg(enc=encoder._cfg, dec=decoder._cfg, vocab=vocab_size, ctc_weight=ctc_weight, lsm_weight=lsm_weight)
+        # intermediate CTC (espnet_model.py:223-245) needs both the weight and taps in the encoder; either alone is a no-op
+        self._cfg = S.ModelCfg(enc=encoder._cfg, dec=decoder._cfg, vocab=vocab_size, ctc_weight=ctc_weight, lsm_weight=lsm_weight,
+                               interctc_weight=interctc_weight if encoder._cfg.interctc_layer_idx else 0.0)
         self._names = [n for n, _ in self.named_parameters()]
         self._link_owner()
 
@@ -778,9 +788,12 @@ class ESPnetASRModel(_Packed):
             raise TooShortUttError(f"has {feats.size(1)} frames and is too short for subsampling "
                                    f"(it needs more than {limit} frames), return empty results", feats.size(1), limit)
         want = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
-        loss, loss_ctc, loss_att, acc = _ModelFn.apply(self, want, feats.float().contiguous(), flens, text, text_lengths,
-                                                       *self.parameters())
-        stats = dict(loss_ctc=loss_ctc.detach()[None], cer_ctc=None, loss_att=loss_att.detach()[None], acc=acc.detach()[None],
-                     cer=None, wer=None, loss=loss.detach()[None])
+        loss, loss_ctc, loss_att, acc, *ic = _ModelFn.apply(self, want, feats.float().contiguous(), flens, text, text_lengths,
+                                                            *self.parameters())
+        stats = dict(loss_ctc=loss_ctc.detach()[None], cer_ctc=None)
+        for idx, l in zip(self._cfg.enc.interctc_layer_idx, ic):  # espnet_model.py:236-239
+            stats[f"loss_interctc_layer{idx}"] = l.detach()[None]
+            stats[f"cer_interctc_layer{idx}"] = None
+        stats.update(loss_att=loss_att.detach()[None], acc=acc.detach()[None], cer=None, wer=None, loss=loss.detach()[None])
         weight = torch.tensor([batch_size], dtype=torch.long, device=loss.device)
         return loss[None], stats, weight

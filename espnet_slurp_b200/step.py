@@ -47,6 +47,7 @@ class EncCfg:
     dropout: float = 0.1
     pos_dropout: float = 0.1
     att_dropout: float = 0.1
+    interctc_layer_idx: tuple = ()  # 1-based block indices whose (after_norm'ed) output also feeds the CTC (:336-347)
 
 
 @dataclass
@@ -286,8 +287,10 @@ def enc_layer_bwd(dy, saved, pos16, P, W, G, p: str, cfg: EncCfg, B: int, T: int
 # ------------------------------------------------------------------------------------------------------------------
 # encoder: Conv2dSubsampling + rel-pos encoding + N blocks + after_norm
 # ------------------------------------------------------------------------------------------------------------------
-def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder", bn_buffers=None):
-    """feats f32 [B, T_in, idim], flens int32 [B] (device).  Returns (enc f32 [B*T, d], enc16 bf16, olens int32, saved)."""
+def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder", bn_buffers=None,
+                want_inter_f32: bool = False):
+    """feats f32 [B, T_in, idim], flens int32 [B] (device).  Returns (enc f32 [B*T, d], enc16 bf16, olens int32, saved).
+    saved[11] lists the intermediate-CTC taps (block idx, block output, LN stats, bf16 tap, fp32 tap or None)."""
     B, Tin, _ = feats.shape
     e = p + ".embed"
     C_ = P[e + ".conv.0.weight"].shape[0]
@@ -308,23 +311,35 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     dpe = ctx.drop(cfg.pos_dropout)
     pos16 = K.cast_bf16(pos_table(cfg.rel_pos_type, T if cfg.rel_pos_type == "latest" else Pn, cfg.d, feats.device), drop=dpe)
     olens = torch.clamp((flens + 3) // 4, max=T).to(torch.int32)  # mask[:, :, :-2:2][:, :, :-2:2] (subsampling.py:87)
-    layers = []
+    layers, inter = [], []
     for n in range(cfg.blocks):
         x, s = enc_layer_fwd(x, pos16, olens, P, W, f"{p}.encoders.{n}", cfg, B, T, ctx, bn_buffers)
         layers.append(s)
+        if n + 1 in cfg.interctc_layer_idx:
+            # intermediate CTC tap: the block output through after_norm (conformer_encoder.py:339-347)
+            i16, i32, sti = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"], want_bf16=True,
+                                            want_f32=want_inter_f32)
+            inter.append((n + 1, x, sti, i16, i32))
     enc16, enc, st = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"], want_bf16=True, want_f32=True)
-    return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, col, B, T)
+    return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, col, B, T, inter)
 
 
-def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=None):
+def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=None, dinter=None):
     """denc f32 [B*T, d]: gradient w.r.t. the encoder output.  Accumulates every encoder parameter gradient into G.
-    on_ready("enc<n>") is called when block n's parameter gradients are final (data-parallel bucket hook)."""
-    feats, h1, h2v, dpos, pos16, layers, xl, st, col, B, T = saved
+    on_ready("enc<n>") is called when block n's parameter gradients are final (data-parallel bucket hook).
+    dinter = {block idx: f32 [B*T, d] gradient w.r.t. that intermediate-CTC tap} (missing / None = no gradient)."""
+    feats, h1, h2v, dpos, pos16, layers, xl, st, col, B, T, inter = saved
+    taps = {idx: (xi, sti) for idx, xi, sti, _, _ in inter}
     e = p + ".embed"
     dx, _ = K.layernorm_bwd(denc, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
     embed_head = (math.sqrt(cfg.d), dpos, G[e + ".out.0.bias"])
     g = None
     for n in reversed(range(cfg.blocks)):
+        if dinter is not None and dinter.get(n + 1) is not None:
+            # the tap's after_norm backward joins the gradient of block n's output (one pass: dx = LN'(dtap) + dx)
+            xi, sti = taps[n + 1]
+            dx, _ = K.layernorm_bwd(dinter[n + 1], xi, P[p + ".after_norm.weight"], sti, G[p + ".after_norm.weight"],
+                                    G[p + ".after_norm.bias"], dx_add=dx)
         # block 0 hands its dx to the embedding's output Linear, the others to the previous block's norm_final (fp32 only)
         dx, g = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T, embed_head if n == 0 else None)
         layers[n] = None  # free the block's activations as we go
@@ -507,6 +522,7 @@ class ModelCfg:
     n_fft: int = 512
     hop: int = 128
     n_mels: int = 80
+    interctc_weight: float = 0.0  # espnet_model.py:223-245; the taps are cfg.enc.interctc_layer_idx
 
 
 def add_sos_eos(text, text_lens, sos: int, eos: int, ignore: int = -1):
@@ -530,11 +546,20 @@ def train_step_from_feats(feats, flens, text, text_lens, P, W, G, cfg: ModelCfg,
     B = feats.shape[0]
     V = cfg.vocab
     enc, enc16, olens, s_enc = encoder_fwd(feats, flens, P, W, cfg.enc, ctx, bn_buffers=bn_buffers)
-    T = s_enc[-1]
+    T, inter = s_enc[10], s_enc[11]
     wc, wa = cfg.ctc_weight * grad_scale, (1.0 - cfg.ctc_weight) * grad_scale
-    text = text.to(torch.int32)
+    text = text.to(torch.int32).contiguous()
     tl = text_lens.to(torch.int32)
-    loss_ctc, denc = ctc_head(enc16, olens, text.contiguous(), tl, P, W, G, V, B, T, wc, want_grad=want_grad)
+    # intermediate CTC (espnet_model.py:223-245): same CTC module, same targets, losses averaged over the taps and mixed
+    # into the CTC term with interctc_weight; every head writes its own, already weighted, input gradient
+    iw = cfg.interctc_weight if inter else 0.0
+    loss_ctc, denc = ctc_head(enc16, olens, text, tl, P, W, G, V, B, T, wc * (1.0 - iw), want_grad=want_grad)
+    stats_ic, dinter, loss_ic = {}, {}, None
+    if iw != 0.0:
+        for idx, _, _, i16, _ in inter:
+            l, dinter[idx] = ctc_head(i16, olens, text, tl, P, W, G, V, B, T, wc * iw / len(inter), want_grad=want_grad)
+            stats_ic[f"loss_interctc_layer{idx}"] = l
+            loss_ic = l if loss_ic is None else loss_ic + l
     ys_in, ys_out = add_sos_eos(text, tl, V - 1, V - 1)
     ylens = (tl + 1).to(torch.int32)
     logits, s_dec = decoder_fwd(enc16, olens, ys_in, ylens, P, W, cfg.dec, ctx, B, T)
@@ -544,9 +569,11 @@ def train_step_from_feats(feats, flens, text, text_lens, P, W, G, cfg: ModelCfg,
         del s_dec
         if on_ready is not None:
             on_ready("heads")  # decoder + CTC head gradients are final
-        encoder_bwd(denc, s_enc, P, W, G, cfg.enc, on_ready=on_ready)
-    loss = cfg.ctc_weight * loss_ctc + (1.0 - cfg.ctc_weight) * loss_att
-    return {"loss": loss, "loss_ctc": loss_ctc, "loss_att": loss_att, "acc": acc}
+        encoder_bwd(denc, s_enc, P, W, G, cfg.enc, on_ready=on_ready, dinter=dinter)
+    # stats["loss_ctc"] is the final block's CTC loss alone (espnet_model.py:217, recorded before the mix)
+    mixed = loss_ctc if loss_ic is None else (1.0 - iw) * loss_ctc + iw * (loss_ic / len(inter))
+    loss = cfg.ctc_weight * mixed + (1.0 - cfg.ctc_weight) * loss_att
+    return {"loss": loss, "loss_ctc": loss_ctc, "loss_att": loss_att, "acc": acc, **stats_ic}
 
 
 def frontend_fwd(speech, speech_lens, melmat, cfg: ModelCfg, draws: Optional[dict] = None):

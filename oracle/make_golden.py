@@ -54,13 +54,16 @@ def tiny_batch(seed=0, B=3, N=6000, V=TINY_V):
     return wav, lens, text, tl
 
 
-def gen_e2e(rel_pos_type: str, name: str):
-    """Whole train step from raw waveform: loss, stats, encoder output, all grads."""
+def gen_e2e(rel_pos_type: str, name: str, interctc=None):
+    """Whole train step from raw waveform: loss, stats, encoder output, all grads.  interctc = (weight, [block idx])
+    adds intermediate CTC losses (next-row N4; 3 blocks so that two of them can carry one)."""
     torch.manual_seed(1)
     enc_conf = dict(TINY_ENC, rel_pos_type=rel_pos_type)
     if rel_pos_type == "legacy":
         enc_conf.update(pos_enc_layer_type="rel_pos", selfattention_layer_type="rel_selfattn")
-    m = ref_shim.build_reference_model(TINY_V, enc_conf, TINY_DEC)
+    if interctc is not None:
+        enc_conf.update(num_blocks=3, interctc_layer_idx=list(interctc[1]))
+    m = ref_shim.build_reference_model(TINY_V, enc_conf, TINY_DEC, interctc_weight=interctc[0] if interctc else 0.0)
     randomize_(m, 2)
     m.train()
     wav, lens, text, tl = tiny_batch()
@@ -70,9 +73,14 @@ def gen_e2e(rel_pos_type: str, name: str):
         feats, flens = m._extract_feats(wav, lens)
         feats_n, _ = m.normalize(feats.clone(), flens)
         enc_out, enc_lens, _ = m.encoder(feats_n, flens)  # note: BN running stats updated twice
+        if isinstance(enc_out, tuple):
+            enc_out = enc_out[0]
     out = {"wav": wav, "lens": lens, "text": text, "text_lens": tl, "loss": loss.detach(),
            "loss_ctc": stats["loss_ctc"], "loss_att": stats["loss_att"], "acc": stats["acc"],
            "feats": feats, "feat_lens": flens, "enc_out": enc_out, "enc_lens": enc_lens}
+    for k, v in stats.items():
+        if k.startswith("loss_interctc"):
+            out[k] = v
     for k, v in m.state_dict().items():
         if "running_" in k or "num_batches" in k:
             continue
@@ -336,6 +344,7 @@ def main():
     gen_bn_running()
     gen_e2e("latest", "e2e_latest.npz")
     gen_e2e("legacy", "e2e_legacy.npz")
+    gen_e2e("latest", "e2e_interctc.npz", interctc=(0.4, [1, 2]))
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -60,6 +60,8 @@ class ModelCfg:
     hop: int = 128
     n_mels: int = 80
     fs: int = 16000
+    interctc_weight: float = 0.0
+    interctc_layer_idx: tuple = ()  # 1-based block indices (conformer_encoder.py:283-285)
 
 
 # --------------------------------------------------------------------------- #
@@ -655,16 +657,26 @@ def th_accuracy(logits, target, ignore: int = -1) -> float:
 def asr_forward_from_feats(feats, feat_lens, text, text_lens, sd: SD, cfg: ModelCfg):
     """ESPnetASRModel.forward from the encoder input on
     (espnet2/asr/espnet_model.py:202-297): returns (loss, stats)."""
-    enc, olens = conformer_encoder(feats, feat_lens, sd, cfg.enc)
+    enc, olens, blocks = conformer_encoder(feats, feat_lens, sd, cfg.enc, return_blocks=True)
     loss_ctc = ctc_branch(enc, olens, text, text_lens, sd)
+    stats_ic = {"loss_ctc": loss_ctc.detach()}  # espnet_model.py:217: recorded before the intermediate losses are mixed in
+    if cfg.interctc_weight != 0.0 and cfg.interctc_layer_idx:
+        # intermediate CTC (conformer_encoder.py:336-347: the block output goes through after_norm; espnet_model.py:223-245:
+        # the same CTC module scores it against the same targets, the losses are averaged and mixed into loss_ctc)
+        loss_ic = 0.0
+        for idx in cfg.interctc_layer_idx:
+            l = ctc_branch(layer_norm(blocks[idx - 1], sd, "encoder.after_norm"), olens, text, text_lens, sd)
+            stats_ic[f"loss_interctc_layer{idx}"] = l.detach()
+            loss_ic = loss_ic + l
+        loss_ic = loss_ic / len(cfg.interctc_layer_idx)
+        loss_ctc = (1 - cfg.interctc_weight) * loss_ctc + cfg.interctc_weight * loss_ic
     sos = eos = cfg.vocab - 1  # espnet_model.py:75-82
     ys_in, ys_out = add_sos_eos(text, text_lens, sos, eos)
     dec = transformer_decoder(enc, olens, ys_in, text_lens + 1, sd, cfg.dec)
     loss_att = label_smoothing_loss(dec, ys_out, cfg.lsm_weight)
     acc = th_accuracy(dec, ys_out)
     loss = cfg.ctc_weight * loss_ctc + (1 - cfg.ctc_weight) * loss_att  # espnet_model.py:284
-    return loss, {"loss_ctc": loss_ctc.detach(), "loss_att": loss_att.detach(), "acc": acc,
-                  "loss": loss.detach()}
+    return loss, {"loss_att": loss_att.detach(), "acc": acc, "loss": loss.detach(), **stats_ic}
 
 
 def asr_forward(speech, speech_lens, text, text_lens, sd: SD, cfg: ModelCfg, melmat, draws=None):

@@ -147,7 +147,7 @@ def install():
 
 
 def build_reference_model(vocab: int, enc_conf: dict, dec_conf: dict, ctc_weight=0.3, lsm_weight=0.1,
-                          frontend=True, specaug_conf=None):
+                          frontend=True, specaug_conf=None, interctc_weight=0.0):
     """The reference's ESPnetASRModel, assembled as espnet2/tasks/asr.py:439-562 does."""
     install()
     from espnet2.asr.ctc import CTC
@@ -168,7 +168,7 @@ def build_reference_model(vocab: int, enc_conf: dict, dec_conf: dict, ctc_weight
         vocab_size=vocab, token_list=token_list, frontend=fe,
         specaug=SpecAug(**specaug_conf) if specaug_conf else None,
         normalize=UtteranceMVN() if frontend else None, preencoder=None, encoder=enc, postencoder=None,
-        decoder=dec, ctc=ctc, joint_network=None, ctc_weight=ctc_weight, lsm_weight=lsm_weight,
+        decoder=dec, ctc=ctc, joint_network=None, ctc_weight=ctc_weight, interctc_weight=interctc_weight, lsm_weight=lsm_weight,
         length_normalized_loss=False, report_cer=False, report_wer=False,
     )
     return model

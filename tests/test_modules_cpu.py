@@ -85,7 +85,10 @@ def test_unsupported_options_raise():
     with pytest.raises(NotImplementedError):
         m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, input_layer="linear")
     with pytest.raises(NotImplementedError):
-        m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, interctc_layer_idx=[1])
+        m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, interctc_layer_idx=[1], interctc_use_conditioning=True)
+    with pytest.raises(AssertionError):  # conformer_encoder.py:284-285: taps must lie strictly inside the stack
+        m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, interctc_layer_idx=[2])
+    assert m.ConformerEncoder(80, 64, 4, 128, 3, macaron_style=True, interctc_layer_idx=[2, 1])._cfg.interctc_layer_idx == (1, 2)
     with pytest.raises(NotImplementedError):
         m.TransformerDecoder(30, 64, concat_after=True)
     with pytest.raises(NotImplementedError):

@@ -258,6 +258,64 @@ def test_encode_and_incremental_scoring_golden(golden_dir):
     assert torch.isfinite(loss).all() and all(p.grad is not None for p in model.decoder.parameters())
 
 
+def test_intermediate_ctc_modules_golden(golden_dir):
+    """Next-row N4 at the module level against the unmodified reference (tests/golden/e2e_interctc.npz): the fused model with
+    interctc_weight, and the stand-alone encoder returning ((out, [(idx, tap), ...]), olens, None) with gradients
+    flowing back through the taps."""
+    import os
+    m = M()
+    z = np.load(os.path.join(golden_dir, "e2e_interctc.npz"))
+    g = {k: z[k] for k in z.files}
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/")}
+    V = 20
+
+    def build():
+        enc = m.ConformerEncoder(80, 16, 2, 32, 3, 0.0, 0.0, 0.0, macaron_style=True, rel_pos_type="latest", cnn_module_kernel=7,
+                                 interctc_layer_idx=[1, 2])
+        dec = m.TransformerDecoder(V, 16, 2, 32, 2, 0.0, 0.0)
+        tokens = ["<blank>", "<unk>"] + [f"t{i}" for i in range(V - 3)] + ["<sos/eos>"]
+        model = m.ESPnetASRModel(V, tokens, m.DefaultFrontend(), None, m.UtteranceMVN(), None, enc, None, dec, m.CTC(V, 16), None,
+                                 ctc_weight=0.3, interctc_weight=0.4, lsm_weight=0.1)
+        _load(model, sd, "")
+        return model.cuda()
+
+    model = build()
+    wav, lens = torch.tensor(g["wav"]).cuda(), torch.tensor(g["lens"]).cuda()
+    text, tl = torch.tensor(g["text"]).cuda(), torch.tensor(g["text_lens"]).cuda()
+    loss, stats, _ = model(wav, lens, text, tl)
+    loss.backward()
+    for k in ("loss", "loss_ctc", "loss_att", "loss_interctc_layer1", "loss_interctc_layer2"):
+        np.testing.assert_allclose(stats[k].item(), g[k].item(), rtol=2e-2, err_msg=k)
+    assert stats["cer_interctc_layer1"] is None and list(stats).index("loss_interctc_layer1") < list(stats).index("loss_att")
+    want = {k[5:]: v for k, v in g.items() if k.startswith("grad/")}
+    rows = grad_report(_grads(model, ""), want)
+    assert rows[0][0] < 0.10, rows[:6]
+
+    # module by module, composed the way the reference's ESPnetASRModel.forward does (espnet_model.py:202-245)
+    model2 = build()
+    feats, flens = model2.normalize(*model2.frontend(wav, lens))
+    (enc_out, taps), olens, _ = model2.encoder(feats, flens)
+    assert [i for i, _ in taps] == [1, 2] and taps[0][1].shape == enc_out.shape
+    l_ctc = model2.ctc(enc_out, olens, text, tl)
+    l_ic = sum(model2.ctc(t, olens, text, tl) for _, t in taps) / len(taps)
+    np.testing.assert_allclose(l_ctc.item(), g["loss_ctc"].item(), rtol=2e-2)
+    np.testing.assert_allclose(l_ic.item(), 0.5 * (g["loss_interctc_layer1"].item() + g["loss_interctc_layer2"].item()), rtol=2e-2)
+    ((1 - 0.4) * l_ctc + 0.4 * l_ic).backward()
+    # encoder gradients of the CTC terms alone: compare with the oracle's autograd on the same expression
+    osd = {k: v.clone().requires_grad_(v.dtype == torch.float32) for k, v in sd.items()}
+    ocfg = om.ModelCfg(enc=om.EncCfg(80, 16, 2, 32, 3, 7, "latest"), dec=om.DecCfg(20, 16, 2, 32, 2), vocab=V)
+    of, ofl = om.frontend_logmel(torch.tensor(g["wav"]), torch.tensor(g["lens"]), torch.from_numpy(om.slaney_mel_matrix()))
+    oenc, oolens, blocks = om.conformer_encoder(om.utterance_mvn(of, ofl), ofl, osd, ocfg.enc, return_blocks=True)
+    ot, otl = torch.tensor(g["text"]), torch.tensor(g["text_lens"])
+    o_ic = sum(om.ctc_branch(om.layer_norm(blocks[i - 1], osd, "encoder.after_norm"), oolens, ot, otl, osd) for i in (1, 2)) / 2
+    (0.6 * om.ctc_branch(oenc, oolens, ot, otl, osd) + 0.4 * o_ic).backward()
+    want2 = {k: (v.grad.numpy() if v.grad is not None else np.zeros(tuple(v.shape), np.float32)) for k, v in osd.items()
+             if k.startswith(("encoder.", "ctc.")) and v.dtype == torch.float32}
+    got2 = {k: v for k, v in _grads(model2, "").items() if k in want2}
+    rows = grad_report(got2, want2)
+    assert rows[0][0] < 0.10, rows[:6]
+
+
 def test_global_mvn_and_ratio_specaug_modules(golden_dir, tmp_path):
     """GlobalMVN / SpecAug(time_mask_width_ratio_range) drop-ins against outputs of the unmodified reference."""
     import os

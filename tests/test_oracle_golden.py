@@ -188,3 +188,26 @@ def test_whole_step_loss_and_grads(rel):
         scale = max(np.abs(v).max(), 1e-3)
         worst = max(worst, float(np.abs(got.numpy() - v).max() / scale))
     assert worst < 2e-3, worst
+
+
+def test_intermediate_ctc_step():
+    """Next-row N4: intermediate CTC on blocks 1 and 2 of 3 (interctc_weight 0.4), loss, per-block stats and every
+    gradient against the unmodified reference (tests/golden/e2e_interctc.npz)."""
+    g = load("e2e_interctc.npz")
+    sd = {k[3:]: torch.tensor(v).requires_grad_(v.dtype == np.float32) for k, v in g.items() if k.startswith("sd/")}
+    cfg = om.ModelCfg(enc=om.EncCfg(80, 16, 2, 32, 3, 7, "latest"), dec=om.DecCfg(20, 16, 2, 32, 2), vocab=20,
+                      interctc_weight=0.4, interctc_layer_idx=(1, 2))
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    loss, stats = om.asr_forward(torch.tensor(g["wav"]), torch.tensor(g["lens"]), torch.tensor(g["text"]),
+                                 torch.tensor(g["text_lens"]), sd, cfg, mel)
+    for k in ("loss_ctc", "loss_att", "loss_interctc_layer1", "loss_interctc_layer2"):
+        np.testing.assert_allclose(float(stats[k]), g[k].item(), rtol=2e-5)
+    np.testing.assert_allclose(loss.item(), g["loss"].item(), rtol=2e-5)
+    loss.backward()
+    worst = 0.0
+    for k, v in g.items():
+        if k.startswith("grad/"):
+            got = sd[k[5:]].grad
+            got = torch.zeros_like(sd[k[5:]]) if got is None else got
+            worst = max(worst, float(np.abs(got.numpy() - v).max() / max(np.abs(v).max(), 1e-3)))
+    assert worst < 2e-3, worst
