@@ -170,35 +170,20 @@ def cpu_step_time(args, cfg, n_steps, warmup, batch, min_seconds=0.0):
 
 # ----------------------------------------------------------------------------------------------------- GPU arm
 class Trainer:
-    """One rank of the data-parallel train step (mirrors espnet2/train/trainer.py:464-720 for one iteration)."""
+    """Synthetic batches around espnet_slurp_b200.trainer.TrainStep -- the package's public train-step API (forward,
+    backward, gradient all-reduce, clip + Adam; one CUDA graph per batch shape).  See trainer.py for the step itself."""
 
     def __init__(self, args, cfg, rank, world):
-        from espnet_slurp_b200 import ops, params as bparams, step as bstep
-        from espnet_slurp_b200.melbank import mel_matrix
-        self.ops, self.bstep, self.cfg, self.args, self.rank, self.world = ops, bstep, cfg, args, rank, world
+        from espnet_slurp_b200.trainer import TrainStep
+        self.cfg, self.args, self.rank, self.world = cfg, args, rank, world
         dev = torch.device("cuda", torch.cuda.current_device())
-        self.dev = dev
-        self.pack = bparams.ParamPack({k: v.to(dev) for k, v in make_state_dict(cfg).items()})
-        n = self.pack.total
-        self.m = torch.zeros(n, device=dev)
-        self.v = torch.zeros(n, device=dev)
-        self.state = torch.zeros(3, device=dev, dtype=torch.float64)
-        self.mel = mel_matrix(device=dev)
-        self.bn = {}
-        for nblk in range(cfg.enc.blocks):
-            p = f"encoder.encoders.{nblk}.conv_module.norm."
-            self.bn[p + "running_mean"] = torch.zeros(cfg.enc.d, device=dev)
-            self.bn[p + "running_var"] = torch.ones(cfg.enc.d, device=dev)
-            self.bn[p + "num_batches_tracked"] = torch.zeros(1, device=dev, dtype=torch.long)
-        self.step_no = 0
-        from espnet_slurp_b200.dist import GradReducer
         # --dp-mode: "graph" = step body replayed as one CUDA graph, then the gradient all-reduce (437 MB, ~0.9 ms at
         # N = 2), then clip + Adam: 28.4 ms/step measured at N = 2;  "eager_overlap" = eager launches with the bucketed
         # all-reduce overlapped with the backward: 31.1 ms/step (the launch overhead costs more than the overlap saves).
         # Capturing the NCCL calls inside the graph hung on this stack (torch 2.11 / NCCL 2.28.9) and is not offered.
-        self.reducer = GradReducer(self.pack, world, overlap=(args.dp_mode != "graph"))
-        # gradient buckets for the overlapped all-reduce: decoder + ctc first (their backward finishes first),
-        # then encoder blocks last-to-first, then the embedding front
+        # Graph capture is driven explicitly below (eager_steps_before_capture is never reached) so that the launches of
+        # one eager step can be counted first.
+        self.ts = TrainStep(cfg, make_state_dict(cfg), rank, world, dp_mode=args.dp_mode, use_graph=False)
         self.host_batches, self.dev_batches = [], []
         gen = torch.Generator().manual_seed(99 + rank)
         for i in range(4):
@@ -211,68 +196,20 @@ class Trainer:
             self.dev_batches.append({k: v.to(dev) for k, v in hb.items()})
         self.audio_sec = [float(hb["lens"].sum()) / FS for hb in self.host_batches]
         self.h2d_bytes = sum(v.numel() * v.element_size() for v in self.host_batches[0].values())
-        self.loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
 
-    def lr(self, base=1e-3, warmup=25000):
-        s = self.step_no
-        return base * warmup ** 0.5 * min(s ** -0.5, s * warmup ** -1.5)  # warmup_lr.py:43-50
-
-    # ---- the step body: only device-resident inputs (self.inp, the 24-byte step params), no host values -> capturable
-    def body(self, overlap=False):
-        bstep, pack, cfg, b = self.bstep, self.pack, self.cfg, self.inp
-        pack.refresh()
-        pack.zero_grad()
-        self.reducer.begin()
-        draws = {k: b[k] for k in ("center", "warped", "fmask", "tmask")}
-        feats, flens = bstep.frontend_fwd(b["wav"], b["lens"], self.mel, cfg, draws)
-        # trainer.py:594-606: loss is the batch-weighted mean over ranks, DDP averages -> net scale 1/world on summed grads
-        out = bstep.train_step_from_feats(feats, flens, b["text"], b["tl"], pack.P, pack.W, pack.G, cfg,
-                                          bstep.StepCtx(1000003 * (self.rank + 1), True), bn_buffers=self.bn,
-                                          on_ready=self.reducer.ready if (overlap and self.world > 1) else None)
-        pack.finalize_grads()
-        self.res = torch.cat([out["loss"], out["loss_ctc"], out["loss_att"], out["acc"]])
-
-    def tail(self):
-        self.reducer.finish()   # issues whatever buckets are still pending ("front"), then joins the side stream
-        self.ops.adam_step(self.pack.flat32, self.pack.gflat, self.m, self.v, 0.0, 0, self.state,
-                           grad_inv_scale=1.0 / self.world, max_norm=5.0)
-
-    def setup_static(self):
-        import numpy as np
-        self.inp = {k: torch.empty_like(v) for k, v in self.dev_batches[0].items()}
-        self.sp_host = torch.zeros(64, 24, dtype=torch.uint8).pin_memory()
-        self.sp_np = self.sp_host.numpy().view(np.dtype([("seed", "<u8"), ("lr", "<f4"), ("bc1", "<f4"), ("bc2", "<f4"), ("pad", "<f4")]))
-        self.sp_dev = torch.zeros(24, dtype=torch.uint8, device=self.dev)
-        self.ops.set_step_params(self.sp_dev)
-        self.graph = None
+    @property
+    def loss_host(self):
+        return self.ts.loss_host
 
     def capture(self):
-        """Whole step (cast -> front-end -> fwd -> bwd [-> Adam when single-GPU]) as ONE CUDA graph."""
-        g = torch.cuda.CUDAGraph()
-        self.graph_has_tail = self.world == 1
-        with torch.cuda.graph(g):
-            self.body(overlap=False)
-            if self.graph_has_tail:
-                self.tail()
-        self.graph = g
+        self.ts.capture()
+
+    def drop_graphs(self):
+        self.ts.drop_graphs()
 
     def step(self, i, e2e=False):
-        self.step_no += 1
-        slot = self.step_no % 64
-        self.sp_np[slot] = (self.step_no * 0x9E3779B97F4A7C15 % (1 << 64), self.lr(), 1 - 0.9 ** self.step_no, 1 - 0.999 ** self.step_no, 0.0)
-        self.sp_dev.copy_(self.sp_host[slot], non_blocking=True)
-        src = self.host_batches[i % 4] if e2e else self.dev_batches[i % 4]
-        for k, v in src.items():
-            self.inp[k].copy_(v, non_blocking=True)
-        if self.graph is not None:
-            self.graph.replay()
-            if not self.graph_has_tail:
-                self.tail()
-        else:
-            self.body(overlap=self.args.dp_mode != "graph")
-            self.tail()
-        if e2e:
-            self.loss_host.copy_(self.res, non_blocking=True)
+        # e2e: inputs come from pinned HOST memory (H2D inside the timed region) and the losses are read back (D2H)
+        self.ts((self.host_batches if e2e else self.dev_batches)[i % 4], fetch_loss=e2e)
 
 
 def run_ours(args):
@@ -307,7 +244,6 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return ms.item(), last
 
-    tr.setup_static()
     for i in range(2):
         tr.step(i)  # eager: one-time kernel attribute / driver-entry-point setup happens outside any capture
     torch.cuda.synchronize()
@@ -339,7 +275,7 @@ def run_ours(args):
         lib.b200slu_prof_reset()
         lib.b200slu_prof_enable_timing(1)
         nprof = 2
-        tr.graph = None  # eager launches so that every kernel can be bracketed by events
+        tr.drop_graphs()  # eager launches so that every kernel can be bracketed by events
         for i in range(nprof):
             tr.step(i)
         torch.cuda.synchronize()

@@ -1,0 +1,177 @@
+"""One rank of the data-parallel train step, replayed from CUDA graphs kept per batch shape.
+
+Mirrors one iteration of the reference's training loop -- espnet2/train/trainer.py:464-720: forward, backward, gradient
+all-reduce (DDP averages over ranks), grad-norm clipping at 5.0, the non-finite-norm skip, Adam, WarmupLR
+(espnet2/schedulers/warmup_lr.py:43-50) -- over the kernels of this package:
+
+    step = TrainStep(cfg, state_dict, rank, world)
+    loss4 = step(batch)        # batch: dict of tensors, pinned host or device:
+                               #   wav f32 [B, N], lens i32 [B], text i32 [B, Lmax], tl i32 [B]
+                               #   and optionally the SpecAug draws center / warped i32 [B], fmask / tmask i32 [B, n, 2]
+                               #   (modules.specaug_draws makes them in the reference's RNG order)
+
+Nothing in a step depends on a host value: lengths, targets and SpecAug draws are device tensors, the dropout seed, the
+learning rate and Adam's bias corrections are read by the kernels from a 24-byte device record refreshed per step
+(ops.set_step_params).  A step is therefore capturable as ONE CUDA graph per input shape.  Batches of the reference's
+samplers come in a handful of padded shapes (length-bucketed batching: `batch_type: folded / numel`, sorted by length), so
+the graphs are cached per shape ("length buckets") with least-recently-used eviction: the first step of a new shape runs
+eagerly (one-time kernel attribute setup), the next one is captured, later ones replay.  With more than one rank the
+gradient all-reduce and the optimizer run after the replay (NCCL calls inside a capture hung on this stack, see
+bench.py), or, with dp_mode="eager_overlap", the step runs eagerly with the bucketed all-reduce overlapping the backward.
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import ops, params as bparams, step as bstep
+from .dist import GradReducer
+from .melbank import mel_matrix
+
+_DRAW_KEYS = ("center", "warped", "fmask", "tmask")
+
+
+class _Bucket:
+    """Static input buffers, result buffer and (once captured) the CUDA graph of one batch shape."""
+
+    def __init__(self, batch: Dict[str, torch.Tensor], dev):
+        self.inp = {k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in batch.items()}
+        self.res: Optional[torch.Tensor] = None
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.eager_steps = 0
+
+
+class TrainStep:
+    def __init__(self, cfg: bstep.ModelCfg, state_dict: Dict[str, torch.Tensor], rank: int = 0, world: int = 1,
+                 dp_mode: str = "graph", use_graph: bool = True, lr: float = 1e-3, warmup_steps: int = 25000,
+                 max_norm: float = 5.0, max_buckets: int = 4, eager_steps_before_capture: int = 1):
+        assert dp_mode in ("graph", "eager_overlap"), dp_mode
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.cfg, self.rank, self.world, self.dev, self.dp_mode = cfg, rank, world, dev, dp_mode
+        self.use_graph = use_graph and not (world > 1 and dp_mode == "eager_overlap")
+        self.base_lr, self.warmup_steps, self.max_norm = lr, warmup_steps, max_norm
+        self.max_buckets, self.eager_before = max_buckets, eager_steps_before_capture
+        self.pack = bparams.ParamPack({k: v.to(dev) for k, v in state_dict.items() if v.dtype == torch.float32
+                                       and "running_" not in k and not k.endswith("melmat")})
+        n = self.pack.total
+        self.m = torch.zeros(n, device=dev)       # Adam moments over the flat fp32 parameter buffer
+        self.v = torch.zeros(n, device=dev)
+        self.state = torch.zeros(3, device=dev, dtype=torch.float64)  # (sum of squares, grad norm, update-applied flag)
+        self.mel = mel_matrix(device=dev)
+        self.bn: Dict[str, torch.Tensor] = {}
+        for nblk in range(cfg.enc.blocks):
+            p = f"encoder.encoders.{nblk}.conv_module.norm."
+            rm, rv, nb = state_dict.get(p + "running_mean"), state_dict.get(p + "running_var"), state_dict.get(p + "num_batches_tracked")
+            self.bn[p + "running_mean"] = rm.to(dev).float().clone() if rm is not None else torch.zeros(cfg.enc.d, device=dev)
+            self.bn[p + "running_var"] = rv.to(dev).float().clone() if rv is not None else torch.ones(cfg.enc.d, device=dev)
+            self.bn[p + "num_batches_tracked"] = nb.to(dev).long().reshape(1).clone() if nb is not None else \
+                torch.zeros(1, device=dev, dtype=torch.long)
+        self.step_no = 0
+        self.reducer = GradReducer(self.pack, world, overlap=(dp_mode != "graph"))
+        self.buckets: "OrderedDict[tuple, _Bucket]" = OrderedDict()
+        # per-step device record {u64 dropout seed; f32 lr, bias correction 1, bias correction 2, pad}: a ring of pinned
+        # host slots so that the asynchronous copy of step s is never overwritten by the host preparing step s + 1
+        self.sp_host = torch.zeros(64, 24, dtype=torch.uint8).pin_memory()
+        self.sp_np = self.sp_host.numpy().view(np.dtype([("seed", "<u8"), ("lr", "<f4"), ("bc1", "<f4"), ("bc2", "<f4"),
+                                                         ("pad", "<f4")]))
+        self.sp_dev = torch.zeros(24, dtype=torch.uint8, device=dev)
+        ops.set_step_params(self.sp_dev)
+        self.loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+        self.last: Optional[_Bucket] = None
+
+    # warmup_lr.py:43-50
+    def lr(self) -> float:
+        s, w = self.step_no, self.warmup_steps
+        return self.base_lr * w ** 0.5 * min(s ** -0.5, s * w ** -1.5)
+
+    # ---- the step body: only device-resident inputs (the bucket's static buffers, the 24-byte record) -> capturable
+    def _body(self, b: _Bucket, overlap: bool):
+        pack, cfg, inp = self.pack, self.cfg, b.inp
+        pack.refresh()
+        pack.zero_grad()
+        self.reducer.begin()
+        draws = {k: inp[k] for k in _DRAW_KEYS if k in inp}
+        feats, flens = bstep.frontend_fwd(inp["wav"], inp["lens"], self.mel, cfg, draws)
+        # trainer.py:594-606: the loss is the batch-weighted mean over ranks and DDP averages the gradients: the summed
+        # gradients are scaled by 1 / world inside the optimizer kernel
+        out = bstep.train_step_from_feats(feats, flens, inp["text"], inp["tl"], pack.P, pack.W, pack.G, cfg,
+                                          bstep.StepCtx(1000003 * (self.rank + 1), True), bn_buffers=self.bn,
+                                          on_ready=self.reducer.ready if (overlap and self.world > 1) else None)
+        pack.finalize_grads()
+        b.res = torch.cat([out["loss"], out["loss_ctc"], out["loss_att"], out["acc"]])
+
+    def _tail(self):
+        self.reducer.finish()  # issues whatever gradient buckets are still pending, then joins the side stream
+        # lr = 0 / step = 0: the kernel reads lr and the bias corrections from the device record (capturable)
+        ops.adam_step(self.pack.flat32, self.pack.gflat, self.m, self.v, 0.0, 0, self.state, grad_inv_scale=1.0 / self.world,
+                      max_norm=self.max_norm)
+
+    def capture(self, b: Optional[_Bucket] = None):
+        """Record the whole step of this bucket (weight cast -> front-end -> forward -> backward [-> clip + Adam when
+        single-GPU]) as ONE CUDA graph.  Called automatically by __call__; public for benchmarks that want control."""
+        b = b if b is not None else self.last
+        ops.set_step_params(self.sp_dev)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        self.graph_has_tail = self.world == 1
+        with torch.cuda.graph(g):
+            self._body(b, overlap=False)
+            if self.graph_has_tail:
+                self._tail()
+        b.graph = g
+
+    def drop_graphs(self):
+        """Back to eager launches (profiling passes bracket every kernel with events)."""
+        for b in self.buckets.values():
+            b.graph = None
+        self.use_graph = False
+
+    def _bucket(self, batch: Dict[str, torch.Tensor]) -> _Bucket:
+        key = tuple((k, tuple(v.shape), v.dtype) for k, v in sorted(batch.items()))
+        b = self.buckets.get(key)
+        if b is None:
+            while len(self.buckets) >= self.max_buckets:  # least recently used shape goes, with its graph's memory pool
+                self.buckets.popitem(last=False)
+            b = self.buckets[key] = _Bucket(batch, self.dev)
+        else:
+            self.buckets.move_to_end(key)
+        return b
+
+    def __call__(self, batch: Dict[str, torch.Tensor], fetch_loss: bool = False) -> torch.Tensor:
+        """One optimizer step on ``batch``.  Returns the device tensor (loss, loss_ctc, loss_att, acc); with fetch_loss it
+        is also copied (asynchronously) into the pinned ``self.loss_host``.  No host synchronisation."""
+        for k in ("wav", "lens", "text", "tl"):
+            assert k in batch, f"TrainStep: batch lacks {k!r}"
+        b = self.last = self._bucket(batch)
+        ops.set_step_params(self.sp_dev)  # host-side registration, handed to the kernels as an argument (baked into a graph
+        self.step_no += 1                 # at capture): re-registered per call so that several TrainSteps can coexist
+        slot = self.step_no % 64
+        self.sp_np[slot] = (self.step_no * 0x9E3779B97F4A7C15 % (1 << 64), self.lr(), 1 - 0.9 ** self.step_no,
+                            1 - 0.999 ** self.step_no, 0.0)
+        self.sp_dev.copy_(self.sp_host[slot], non_blocking=True)
+        for k, v in batch.items():
+            b.inp[k].copy_(v, non_blocking=True)
+        if b.graph is not None:
+            b.graph.replay()
+            if not self.graph_has_tail:
+                self._tail()
+            res = b.res
+        else:
+            self._body(b, overlap=self.dp_mode != "graph")
+            self._tail()
+            res = b.res  # this step's result; a capture below re-points b.res at the graph's own output buffer
+            b.eager_steps += 1
+            if self.use_graph and b.eager_steps >= self.eager_before:
+                self.capture(b)
+        if fetch_loss:
+            self.loss_host.copy_(res, non_blocking=True)
+        return res
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        """Parameters in the reference's layout and names, plus the BatchNorm buffers (loadable by the reference model)."""
+        out = {n: self.pack.P[n].detach().clone() for n in self.pack.names}
+        out.update({k: v.clone() for k, v in self.bn.items()})
+        return out

@@ -1,0 +1,114 @@
+"""espnet_slurp_b200.trainer.TrainStep on the GPU: CUDA graphs cached per batch shape must give the same
+losses and parameters as eager launches, the optimizer must follow torch.optim.Adam + clip_grad_norm_ + WarmupLR
+(trainer.py:640-690, warmup_lr.py:43-50) on the oracle's gradients, and the shape cache must evict least-recently-used."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model as om
+from test_step_gpu import make_sd
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg():
+    from espnet_slurp_b200 import step as bstep
+    enc = bstep.EncCfg(80, 64, 4, 128, 2, 7, "latest", 0.0, 0.0, 0.0)
+    dec = bstep.DecCfg(30, 64, 4, 128, 1, 0.0, 0.0, 0.0, 0.0)
+    return bstep.ModelCfg(enc=enc, dec=dec, vocab=30), om.ModelCfg(enc=om.EncCfg(80, 64, 4, 128, 2, 7, "latest"),
+                                                                 dec=om.DecCfg(30, 64, 4, 128, 1), vocab=30)
+
+
+def _batch(B, N, L, seed):
+    g = torch.Generator().manual_seed(seed)
+    lens = torch.randint(N * 3 // 5, N + 1, (B,), generator=g)
+    lens[0] = N
+    wav = torch.randn(B, N, generator=g) * 0.1
+    for b in range(B):
+        wav[b, lens[b]:] = 0
+    tl = torch.randint(2, L + 1, (B,), generator=g)
+    text = torch.randint(2, 28, (B, L), generator=g)
+    text = torch.where(torch.arange(L)[None] < tl[:, None], text, torch.full_like(text, -1))
+    return {"wav": wav, "lens": lens.int(), "text": text.int(), "tl": tl.int()}
+
+
+def test_graph_buckets_match_eager_and_evict():
+    from espnet_slurp_b200.trainer import TrainStep
+    cfg, ocfg = _cfg()
+    sd = make_sd(ocfg.enc, ocfg.dec, 30, seed=3)
+    eager = TrainStep(cfg, sd, use_graph=False, lr=2e-3, warmup_steps=4)
+    graph = TrainStep(cfg, sd, use_graph=True, lr=2e-3, warmup_steps=4, max_buckets=2)
+    shapes = [(3, 8000, 5), (2, 12000, 7)]
+    batches = [_batch(*shapes[i % 2], seed=10 + i) for i in range(8)]
+    for i, b in enumerate(batches):
+        le = eager({k: v.cuda() for k, v in b.items()}).clone()
+        lg = graph({k: v.pin_memory() for k, v in b.items()}, fetch_loss=True).clone()  # host inputs, like the e2e path
+        torch.cuda.synchronize()
+        # same kernels, same inputs; only the order of the floating-point atomics differs from run to run
+        np.testing.assert_allclose(lg.cpu().numpy(), le.cpu().numpy(), rtol=1e-2, atol=1e-4, err_msg=f"step {i}")
+        np.testing.assert_allclose(graph.loss_host.numpy(), lg.cpu().numpy(), rtol=0, atol=0)
+    assert len(graph.buckets) == 2 and all(b.graph is not None for b in graph.buckets.values())
+    assert all(b.eager_steps == 1 for b in graph.buckets.values())  # one eager step per shape, replays afterwards
+    pe, pg = eager.state_dict(), graph.state_dict()
+    # both took the same 8 Adam steps; the summation order of the atomics differs between runs and Adam amplifies noise on
+    # near-zero gradients (a mathematically zero one -- the softmax-shift-invariant linear_k.bias, the depthwise bias in
+    # front of BatchNorm -- becomes +-lr noise): compare the total update, those two families left out
+    ue, ug = [], []
+    for k in pe:
+        if k.endswith(("linear_k.bias", "depthwise_conv.bias")) or "running_" in k or "num_batches" in k:
+            continue
+        ue.append((pe[k].cpu().float() - sd[k]).flatten())
+        ug.append((pg[k].cpu().float() - sd[k]).flatten())
+    ue, ug = torch.cat(ue), torch.cat(ug)
+    cos = float(torch.dot(ue, ug) / (ue.norm() * ug.norm()))
+    assert cos > 0.97 and abs(float(ug.norm() / ue.norm()) - 1) < 0.05, (cos, float(ug.norm() / ue.norm()))
+    assert float(eager.bn["encoder.encoders.0.conv_module.norm.num_batches_tracked"]) == 8
+    assert eager.step_no == graph.step_no == 8 and float(graph.state[2]) == 1.0  # last update applied (finite norm)
+    # a third shape evicts the least recently used one
+    first_key = next(iter(graph.buckets))
+    graph({k: v.cuda() for k, v in _batch(2, 9000, 4, seed=99).items()})
+    assert len(graph.buckets) == 2 and first_key not in graph.buckets
+
+
+def test_optimizer_follows_reference_recipe():
+    """Two steps from the same start: clip_grad_norm_(5.0) + Adam(lr from WarmupLR) applied to the oracle's fp32 gradients."""
+    from espnet_slurp_b200.trainer import TrainStep
+    cfg, ocfg = _cfg()
+    sd = make_sd(ocfg.enc, ocfg.dec, 30, seed=4)
+    ts = TrainStep(cfg, sd, use_graph=False, lr=1e-3, warmup_steps=10)
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    opt = torch.optim.Adam(list(osd.values()), lr=1e-3)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    for i in range(2):
+        b = _batch(3, 8000, 5, seed=20 + i)
+        loss4 = ts({k: v.cuda() for k, v in b.items()})
+        step = i + 1
+        for gp in opt.param_groups:
+            gp["lr"] = 1e-3 * 10 ** 0.5 * min(step ** -0.5, step * 10 ** -1.5)
+        opt.zero_grad()
+        oloss, _ = om.asr_forward(b["wav"], b["lens"].long(), b["text"].long(), b["tl"].long(), osd, ocfg, mel)
+        oloss.backward()
+        torch.nn.utils.clip_grad_norm_(list(osd.values()), 5.0)
+        opt.step()
+        np.testing.assert_allclose(loss4[0].item(), oloss.item(), rtol=2e-2)
+    got = ts.state_dict()
+    # Adam's first steps move every weight by ~lr whatever the gradient's scale: compare sign and size of the UPDATES where
+    # the reference's update is not negligible (parameters with a mathematically zero gradient get +-lr noise here, from
+    # bf16 rounding, and ~0 in the fp32 oracle, where eps dominates)
+    agree = total = 0
+    ur, ug = [], []
+    for k, v in osd.items():
+        if k.endswith(("linear_k.bias", "depthwise_conv.bias")):
+            continue
+        du_ref = (v.detach() - sd[k]).flatten()
+        du_got = (got[k].cpu() - sd[k]).flatten()
+        big = du_ref.abs() > 0.5 * du_ref.abs().max()
+        agree += int((torch.sign(du_ref[big]) == torch.sign(du_got[big])).sum())
+        total += int(big.sum())
+        ur.append(du_ref)
+        ug.append(du_got)
+    ur, ug = torch.cat(ur), torch.cat(ug)
+    assert agree / total > 0.97, (agree, total)
+    assert float(ug.abs().max()) <= 1.05 * float(ur.abs().max()), (float(ug.abs().max()), float(ur.abs().max()))
+    cos = float(torch.dot(ur, ug) / (ur.norm() * ug.norm()))
+    assert cos > 0.9, cos
