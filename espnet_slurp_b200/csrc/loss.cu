@@ -113,7 +113,72 @@ __global__ void lsm_finish_kernel(const float* __restrict__ loss_rows, const int
   }
 }
 
+// Posterior over the vocabulary for self-conditioned intermediate CTC (conformer_encoder.py:350-351, ctc.py:99-107):
+// p = softmax(logits[:, :V]) written as bf16 (the A operand of the conditioning Linear), padding columns [V, ldp) = 0.
+// One warp per row: V = 600 is 19 elements per lane, the row is read twice (max, then exp + sum) from L1/L2.
+__global__ void __launch_bounds__(256) vocab_softmax_fwd_kernel(const float* __restrict__ x, long long ldx, long long R, int V,
+                                                                bf16* __restrict__ p, long long ldp) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= R) return;
+  const float* xr = x + row * ldx;
+  float m = -INFINITY;
+  for (int j = lane; j < V; j += 32) m = fmaxf(m, xr[j]);
+  m = warp_max(m);
+  float s = 0.f;
+  for (int j = lane; j < V; j += 32) s += __expf(xr[j] - m);
+  const float inv = 1.f / warp_sum(s);
+  bf16* pr = p + row * ldp;
+  for (int j = lane; j < ldp; j += 32) pr[j] = __float2bfloat16(j < V ? __expf(xr[j] - m) * inv : 0.f);
+}
+
+// dlogits = p * (dp - sum_j p_j dp_j) (+ add): softmax backward over the vocabulary, bf16 in, bf16 out, padding columns 0.
+__global__ void __launch_bounds__(256) vocab_softmax_bwd_kernel(const bf16* __restrict__ p, long long ldp,
+                                                                const bf16* __restrict__ dp, long long lddp, long long R, int V,
+                                                                const bf16* __restrict__ add, long long ldadd,
+                                                                bf16* __restrict__ dx, long long lddx) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= R) return;
+  const bf16 *pr = p + row * ldp, *dr = dp + row * lddp;
+  float dot = 0.f;
+  for (int j = lane; j < V; j += 32) dot += __bfloat162float(pr[j]) * __bfloat162float(dr[j]);
+  dot = warp_sum(dot);
+  bf16* o = dx + row * lddx;
+  for (int j = lane; j < lddx; j += 32) {
+    float v = 0.f;
+    if (j < V) {
+      v = __bfloat162float(pr[j]) * (__bfloat162float(dr[j]) - dot);
+      if (add != nullptr) v += __bfloat162float(add[row * ldadd + j]);
+    }
+    o[j] = __float2bfloat16(v);
+  }
+}
+
 }  // namespace
+
+extern "C" int b200slu_vocab_softmax_fwd(const float* logits, long long ldv, long long R, int V, void* probs_bf16, long long ldp,
+                                         void* stream) {
+  B2_CHECK_ARG(R > 0 && V > 0 && ldv >= V && ldp >= V, "vocab_softmax_fwd: bad shape R=%lld V=%d", R, V);
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_LOSS, st, 0, (double)R * V * 6.0);
+  vocab_softmax_fwd_kernel<<<(unsigned)((R + 7) / 8), 256, 0, st>>>(logits, ldv, R, V, (bf16*)probs_bf16, ldp);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_vocab_softmax_bwd(const void* probs_bf16, long long ldp, const void* dprobs_bf16, long long lddp,
+                                         long long R, int V, const void* add_bf16, long long ldadd, void* dlogits_bf16,
+                                         long long ldd, void* stream) {
+  B2_CHECK_ARG(R > 0 && V > 0 && ldp >= V && lddp >= V && ldd >= V && (add_bf16 == nullptr || ldadd >= V),
+               "vocab_softmax_bwd: bad shape R=%lld V=%d", R, V);
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_LOSS, st, 0, (double)R * V * (6.0 + (add_bf16 ? 2.0 : 0.0)));
+  vocab_softmax_bwd_kernel<<<(unsigned)((R + 7) / 8), 256, 0, st>>>((const bf16*)probs_bf16, ldp, (const bf16*)dprobs_bf16, lddp,
+                                                                     R, V, (const bf16*)add_bf16, ldadd, (bf16*)dlogits_bf16, ldd);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" long long b200slu_lsm_workspace_size(long long R) { return R * 8; }
 

@@ -534,7 +534,6 @@ class ConformerEncoder(_Packed):
             raise ValueError("pos_enc_layer_type and selfattention_layer_type must both be legacy or both be latest")
         _unsupported(activation_type != "swish", f"activation_type={activation_type!r}")
         _unsupported(zero_triu, "zero_triu")
-        _unsupported(interctc_use_conditioning, "self-conditioned intermediate CTC (interctc_use_conditioning)")
         if len(interctc_layer_idx) > 0:
             assert 0 < min(interctc_layer_idx) and max(interctc_layer_idx) < num_blocks  # conformer_encoder.py:284-285
         sd = stochastic_depth_rate
@@ -551,7 +550,8 @@ class ConformerEncoder(_Packed):
         self.conditioning_layer = None
         self._cfg = S.EncCfg(input_size, output_size, attention_heads, linear_units, num_blocks, cnn_module_kernel,
                              "latest" if pos_enc_layer_type == "rel_pos" else "legacy", dropout_rate, positional_dropout_rate,
-                             attention_dropout_rate, tuple(sorted(set(int(i) for i in interctc_layer_idx))))
+                             attention_dropout_rate, tuple(sorted(set(int(i) for i in interctc_layer_idx))),
+                             bool(interctc_use_conditioning))
         self._names = [self._prefix + n for n, _ in self.named_parameters()]
 
     def output_size(self) -> int:
@@ -560,6 +560,10 @@ class ConformerEncoder(_Packed):
     def forward(self, xs_pad: torch.Tensor, ilens: torch.Tensor, prev_states: torch.Tensor = None, ctc=None
                 ) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
         _need_cuda(xs_pad, "ConformerEncoder")
+        # self-conditioning reads the CTC projection inside the encoder: available in the fused ESPnetASRModel / TrainStep
+        # (one parameter pack), not through this stand-alone forward
+        _unsupported(self.interctc_use_conditioning and len(self.interctc_layer_idx) > 0,
+                     "a stand-alone ConformerEncoder.forward with interctc_use_conditioning (use ESPnetASRModel)")
         short, limit = check_short_utt(self.embed, xs_pad.size(1))
         if short:  # conformer_encoder.py:320-327
             raise TooShortUttError(f"has {xs_pad.size(1)} frames and is too short for subsampling "
@@ -725,6 +729,13 @@ class ESPnetASRModel(_Packed):
         self.frontend, self.specaug, self.normalize = frontend, specaug, normalize
         self.preencoder = self.postencoder = None
         self.encoder, self.decoder, self.ctc = encoder, decoder, ctc
+        if not hasattr(self.encoder, "interctc_use_conditioning"):
+            self.encoder.interctc_use_conditioning = False
+        if self.encoder.interctc_use_conditioning:  # espnet_model.py:96-101
+            _unsupported(vocab_size % 8 != 0, "self-conditioned intermediate CTC with a vocabulary size that is not a multiple "
+                                              "of 8 (the posterior is a GEMM operand)")
+            self.encoder.conditioning_layer = nn.Linear(vocab_size, self.encoder.output_size())
+            self.encoder._cfg.vocab = vocab_size
         self.extract_feats_in_collect_stats = extract_feats_in_collect_stats
         # intermediate CTC (espnet_model.py:223-245) needs both the weight and taps in the encoder; either alone is a no-op
         self._cfg = S.ModelCfg(enc=encoder._cfg, dec=decoder._cfg, vocab=vocab_size, ctc_weight=ctc_weight, lsm_weight=lsm_weight,

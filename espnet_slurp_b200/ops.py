@@ -395,6 +395,25 @@ def lsm_loss(logits, V: int, targets, smoothing: float, grad_scale: float, ignor
     return stats, g32, g16
 
 
+def vocab_softmax_fwd(logits, V: int):
+    """softmax over the first V columns of f32 [R, ld]: bf16 [R, round8(V)], padding columns zero."""
+    R, ldv = logits.shape
+    out = torch.empty(R, round8(V), device=logits.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_vocab_softmax_fwd(ptr(logits), ldv, R, V, ptr(out), out.shape[1], stream_ptr()), "vocab_softmax_fwd")
+    return out
+
+
+def vocab_softmax_bwd(sm, dsm, V: int, add=None):
+    """dlogits = sm * (dsm - <sm, dsm>) (+ add), bf16 [R, round8(V)]."""
+    R = sm.shape[0]
+    assert sm.dtype == dsm.dtype == torch.bfloat16 and sm.stride(1) == 1 and dsm.stride(1) == 1
+    out = torch.empty(R, round8(V), device=sm.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_vocab_softmax_bwd(ptr(sm), sm.stride(0), ptr(dsm), dsm.stride(0), R, V, ptr(add),
+                                               add.stride(0) if add is not None else 0, ptr(out), out.shape[1], stream_ptr()),
+          "vocab_softmax_bwd")
+    return out
+
+
 # ---- front-end ----------------------------------------------------------------------------------------------------
 def logmel(wav, lens, melmat, n_fft: int = 512, hop: int = 128):
     B, N = wav.shape

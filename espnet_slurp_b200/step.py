@@ -48,6 +48,8 @@ class EncCfg:
     pos_dropout: float = 0.1
     att_dropout: float = 0.1
     interctc_layer_idx: tuple = ()  # 1-based block indices whose (after_norm'ed) output also feeds the CTC (:336-347)
+    interctc_use_conditioning: bool = False  # feed the CTC posterior of every tap back into the stream (:350-358)
+    vocab: int = 0  # CTC output size (only the self-conditioning path needs it inside the encoder)
 
 
 @dataclass
@@ -319,7 +321,21 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
             # intermediate CTC tap: the block output through after_norm (conformer_encoder.py:339-347)
             i16, i32, sti = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"], want_bf16=True,
                                             want_f32=want_inter_f32)
-            inter.append((n + 1, x, sti, i16, i32))
+            cond = None
+            if cfg.interctc_use_conditioning:
+                # x += conditioning_layer(softmax(ctc_lo(tap))): the tap's CTC logits are computed here and handed to the
+                # CTC head later; the posterior is kept (bf16) for the backward
+                V = cfg.vocab
+                lg = torch.empty(x.shape[0], K.round8(V), device=x.device, dtype=F32)
+                K.gemm(i16, W["ctc.ctc_lo.weight"], bias=P["ctc.ctc_lo.bias"], out=lg)
+                sm = K.vocab_softmax_fwd(lg, V)
+                x_tap = x
+                x = K.gemm(sm[:, :V], W[p + ".conditioning_layer.weight"], bias=P[p + ".conditioning_layer.bias"], residual=x,
+                           out_dtype=F32)
+                cond = (lg, sm)
+                inter.append((n + 1, x_tap, sti, i16, i32, cond))
+                continue
+            inter.append((n + 1, x, sti, i16, i32, cond))
     enc16, enc, st = K.layernorm_fwd(x, P[p + ".after_norm.weight"], P[p + ".after_norm.bias"], want_bf16=True, want_f32=True)
     return enc, enc16, olens, (feats, h1, h2v, dpos, pos16, layers, x, st, col, B, T, inter)
 
@@ -329,16 +345,32 @@ def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=
     on_ready("enc<n>") is called when block n's parameter gradients are final (data-parallel bucket hook).
     dinter = {block idx: f32 [B*T, d] gradient w.r.t. that intermediate-CTC tap} (missing / None = no gradient)."""
     feats, h1, h2v, dpos, pos16, layers, xl, st, col, B, T, inter = saved
-    taps = {idx: (xi, sti) for idx, xi, sti, _, _ in inter}
+    taps = {t[0]: t for t in inter}
     e = p + ".embed"
     dx, _ = K.layernorm_bwd(denc, xl, P[p + ".after_norm.weight"], st, G[p + ".after_norm.weight"], G[p + ".after_norm.bias"])
     embed_head = (math.sqrt(cfg.d), dpos, G[e + ".out.0.bias"])
     g = None
     for n in reversed(range(cfg.blocks)):
-        if dinter is not None and dinter.get(n + 1) is not None:
+        tap = taps.get(n + 1)
+        dtap = dinter.get(n + 1) if dinter is not None else None
+        if tap is not None and tap[5] is not None:
+            # self-conditioning backward: dx is the gradient of x + cond(softmax(ctc_lo(tap))); the posterior's gradient
+            # goes through the softmax and ctc_lo into the tap, next to the CTC loss's own gradient (dtap)
+            V = cfg.vocab
+            _, i16, (_, sm) = tap[1], tap[3], tap[5]
+            c = p + ".conditioning_layer"
+            g = K.cast_bf16(dx, colsum_out=G[c + ".bias"])
+            K.gemm(g, sm[:, :V], trans=True, out=G[c + ".weight"], accumulate=True)
+            dsm = K.gemm(g, W[c + ".weight"], trans_b=True)
+            dlg = K.vocab_softmax_bwd(sm, dsm, V)
+            gl = dlg[:, :V]
+            K.colsum(dlg, G["ctc.ctc_lo.bias"], n=V)
+            K.gemm(gl, i16, trans=True, out=G["ctc.ctc_lo.weight"], accumulate=True)
+            dcond = K.gemm(gl, W["ctc.ctc_lo.weight"], trans_b=True, out_dtype=F32)
+            dtap = dcond if dtap is None else dtap + dcond
+        if tap is not None and dtap is not None:
             # the tap's after_norm backward joins the gradient of block n's output (one pass: dx = LN'(dtap) + dx)
-            xi, sti = taps[n + 1]
-            dx, _ = K.layernorm_bwd(dinter[n + 1], xi, P[p + ".after_norm.weight"], sti, G[p + ".after_norm.weight"],
+            dx, _ = K.layernorm_bwd(dtap, tap[1], P[p + ".after_norm.weight"], tap[2], G[p + ".after_norm.weight"],
                                     G[p + ".after_norm.bias"], dx_add=dx)
         # block 0 hands its dx to the embedding's output Linear, the others to the previous block's norm_final (fp32 only)
         dx, g = enc_layer_bwd(dx, layers[n], pos16, P, W, G, f"{p}.encoders.{n}", cfg, B, T, embed_head if n == 0 else None)
@@ -484,11 +516,13 @@ def decoder_bwd(dlogits16, dmem, saved, mem16, P, W, G, cfg: DecCfg, B: int, T: 
 # heads: CTC and label-smoothing attention loss (each computes its own input gradient in the same pass)
 # ------------------------------------------------------------------------------------------------------------------
 def ctc_head(enc16, olens, labels, label_lens, P, W, G, V: int, B: int, T: int, weight: float, p: str = "ctc",
-             want_grad: bool = True):
+             want_grad: bool = True, logits=None):
     """CTC.forward (espnet2/asr/ctc.py:72-97) + its backward.  Returns (loss_ctc scalar tensor = sum/B, denc f32 or None).
-    ``weight`` = d(total loss)/d(loss_ctc); the gradient written is already scaled by it."""
-    logits = torch.empty(B * T, K.round8(V), device=enc16.device, dtype=F32)
-    K.gemm(enc16, W[p + ".ctc_lo.weight"], bias=P[p + ".ctc_lo.bias"], out=logits)
+    ``weight`` = d(total loss)/d(loss_ctc); the gradient written is already scaled by it.  ``logits``: ctc_lo(enc16) when
+    the caller has it already (self-conditioned taps)."""
+    if logits is None:
+        logits = torch.empty(B * T, K.round8(V), device=enc16.device, dtype=F32)
+        K.gemm(enc16, W[p + ".ctc_lo.weight"], bias=P[p + ".ctc_lo.bias"], out=logits)
     l3 = logits.view(B, T, -1)
     _, loss_sum, ws = K.ctc_fwd(l3, V, olens, labels, label_lens, blank=0)
     loss = loss_sum / B
@@ -556,8 +590,9 @@ def train_step_from_feats(feats, flens, text, text_lens, P, W, G, cfg: ModelCfg,
     loss_ctc, denc = ctc_head(enc16, olens, text, tl, P, W, G, V, B, T, wc * (1.0 - iw), want_grad=want_grad)
     stats_ic, dinter, loss_ic = {}, {}, None
     if iw != 0.0:
-        for idx, _, _, i16, _ in inter:
-            l, dinter[idx] = ctc_head(i16, olens, text, tl, P, W, G, V, B, T, wc * iw / len(inter), want_grad=want_grad)
+        for idx, _, _, i16, _, cond in inter:
+            l, dinter[idx] = ctc_head(i16, olens, text, tl, P, W, G, V, B, T, wc * iw / len(inter), want_grad=want_grad,
+                                      logits=cond[0] if cond is not None else None)
             stats_ic[f"loss_interctc_layer{idx}"] = l
             loss_ic = l if loss_ic is None else loss_ic + l
     ys_in, ys_out = add_sos_eos(text, tl, V - 1, V - 1)

@@ -219,6 +219,14 @@ int b200slu_lsm_loss_fwd_bwd(const float* logits, long long ldv, long long R, in
                              float smoothing, float grad_scale, void* workspace, float* stats3, float* grad_f32, void* grad_bf16,
                              long long ldg, void* stream);
 
+/* Self-conditioned intermediate CTC (espnet2/asr/encoder/conformer_encoder.py:350-358, espnet2/asr/ctc.py:99-107):
+ * probs = softmax(logits[:, :V]) as bf16 [R, ldp] (columns >= V zero), and its backward
+ * dlogits = probs * (dprobs - <probs, dprobs>) (+ add), bf16 [R, ldd]. */
+int b200slu_vocab_softmax_fwd(const float* logits, long long ldv, long long R, int V, void* probs_bf16, long long ldp,
+                              void* stream);
+int b200slu_vocab_softmax_bwd(const void* probs_bf16, long long ldp, const void* dprobs_bf16, long long lddp, long long R, int V,
+                              const void* add_bf16, long long ldadd, void* dlogits_bf16, long long ldd, void* stream);
+
 /* ---- K7/K8: front-end (default.py:82-117, stft.py:83-170, log_mel.py:62-79; specaug.py:89-96,
  * time_warp.py:9-46, mask_along_axis.py:8-68, utterance_mvn.py:45-88) ------------------------------ */
 int b200slu_logmel_fwd(const float* wav, long long ldw, int B, int N, const int* lens, const float* melmat, int n_fft, int hop,

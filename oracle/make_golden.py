@@ -54,7 +54,7 @@ def tiny_batch(seed=0, B=3, N=6000, V=TINY_V):
     return wav, lens, text, tl
 
 
-def gen_e2e(rel_pos_type: str, name: str, interctc=None):
+def gen_e2e(rel_pos_type: str, name: str, interctc=None, cond=False, V=TINY_V):
     """Whole train step from raw waveform: loss, stats, encoder output, all grads.  interctc = (weight, [block idx])
     adds intermediate CTC losses (next-row N4; 3 blocks so that two of them can carry one)."""
     torch.manual_seed(1)
@@ -62,17 +62,18 @@ def gen_e2e(rel_pos_type: str, name: str, interctc=None):
     if rel_pos_type == "legacy":
         enc_conf.update(pos_enc_layer_type="rel_pos", selfattention_layer_type="rel_selfattn")
     if interctc is not None:
-        enc_conf.update(num_blocks=3, interctc_layer_idx=list(interctc[1]))
-    m = ref_shim.build_reference_model(TINY_V, enc_conf, TINY_DEC, interctc_weight=interctc[0] if interctc else 0.0)
+        enc_conf.update(num_blocks=3, interctc_layer_idx=list(interctc[1]), interctc_use_conditioning=cond)
+    m = ref_shim.build_reference_model(V, enc_conf, TINY_DEC, interctc_weight=interctc[0] if interctc else 0.0)
     randomize_(m, 2)
     m.train()
-    wav, lens, text, tl = tiny_batch()
+    wav, lens, text, tl = tiny_batch(V=V)
     loss, stats, _ = m(wav, lens, text.clone(), tl)
     loss.backward()
     with torch.no_grad():
         feats, flens = m._extract_feats(wav, lens)
         feats_n, _ = m.normalize(feats.clone(), flens)
-        enc_out, enc_lens, _ = m.encoder(feats_n, flens)  # note: BN running stats updated twice
+        # note: BN running stats updated twice
+        enc_out, enc_lens, _ = m.encoder(feats_n, flens, ctc=m.ctc) if cond else m.encoder(feats_n, flens)
         if isinstance(enc_out, tuple):
             enc_out = enc_out[0]
     out = {"wav": wav, "lens": lens, "text": text, "text_lens": tl, "loss": loss.detach(),
@@ -345,6 +346,7 @@ def main():
     gen_e2e("latest", "e2e_latest.npz")
     gen_e2e("legacy", "e2e_legacy.npz")
     gen_e2e("latest", "e2e_interctc.npz", interctc=(0.4, [1, 2]))
+    gen_e2e("latest", "e2e_selfcond.npz", interctc=(0.4, [1, 2]), cond=True, V=24)  # V % 8 == 0: a GEMM K dimension
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

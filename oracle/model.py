@@ -62,6 +62,7 @@ class ModelCfg:
     fs: int = 16000
     interctc_weight: float = 0.0
     interctc_layer_idx: tuple = ()  # 1-based block indices (conformer_encoder.py:283-285)
+    interctc_use_conditioning: bool = False
 
 
 # --------------------------------------------------------------------------- #
@@ -455,8 +456,11 @@ def conformer_block(x, pos_emb, key_valid, sd: SD, p: str, cfg: EncCfg, bn_stats
 
 
 def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_stats_out=None,
-                      return_blocks: bool = False, training: bool = True):
-    """ConformerEncoder.forward (espnet2/asr/encoder/conformer_encoder.py:292-368)."""
+                      return_blocks: bool = False, training: bool = True, cond_idx=()):
+    """ConformerEncoder.forward (espnet2/asr/encoder/conformer_encoder.py:292-368).  cond_idx: 1-based block indices
+    after which the CTC posterior of the (after_norm'ed) block output is fed back, self-conditioning :350-358:
+    x += conditioning_layer(softmax(ctc_lo(after_norm(x)))); the returned blocks are the outputs BEFORE that addition,
+    which is what the intermediate CTC losses see (:339-347)."""
     T_in = feats.shape[1]
     x = conv2d_subsample(feats, sd, p + ".embed") * math.sqrt(cfg.d)  # embedding.py:239
     T = x.shape[1]
@@ -471,6 +475,9 @@ def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_
         x = conformer_block(x, pos_emb, key_valid, sd, f"{p}.encoders.{n}", cfg, bn_stats_out, training)
         if return_blocks:
             outs.append(x)
+        if n + 1 in cond_idx:
+            post = torch.softmax(linear(layer_norm(x, sd, p + ".after_norm"), sd, "ctc.ctc_lo"), dim=-1)
+            x = x + linear(post, sd, p + ".conditioning_layer")
     x = layer_norm(x, sd, p + ".after_norm")
     if return_blocks:
         return x, olens, outs
@@ -657,7 +664,8 @@ def th_accuracy(logits, target, ignore: int = -1) -> float:
 def asr_forward_from_feats(feats, feat_lens, text, text_lens, sd: SD, cfg: ModelCfg):
     """ESPnetASRModel.forward from the encoder input on
     (espnet2/asr/espnet_model.py:202-297): returns (loss, stats)."""
-    enc, olens, blocks = conformer_encoder(feats, feat_lens, sd, cfg.enc, return_blocks=True)
+    enc, olens, blocks = conformer_encoder(feats, feat_lens, sd, cfg.enc, return_blocks=True,
+                                           cond_idx=cfg.interctc_layer_idx if cfg.interctc_use_conditioning else ())
     loss_ctc = ctc_branch(enc, olens, text, text_lens, sd)
     stats_ic = {"loss_ctc": loss_ctc.detach()}  # espnet_model.py:217: recorded before the intermediate losses are mixed in
     if cfg.interctc_weight != 0.0 and cfg.interctc_layer_idx:

@@ -401,6 +401,23 @@ def global_mvn(x, lens, mean=None, inv_std=None):
     return y * inv_std if inv_std is not None else y
 
 
+def vocab_softmax_fwd(logits, V):
+    """softmax over the first V columns of f32 [M, ld]; bf16-rounded [M, ld] with zero padding columns."""
+    out = torch.zeros_like(logits)
+    out[:, :V] = torch.softmax(logits[:, :V].float(), dim=-1)
+    return _r(out)
+
+
+def vocab_softmax_bwd(sm, dsm, V, add=None):
+    """dlogits = sm * (dsm - sum(sm * dsm)) (+ add) over the first V columns; padding columns 0."""
+    s, d = sm[:, :V].float(), dsm[:, :V].float()
+    out = torch.zeros(sm.shape[0], sm.shape[1])
+    out[:, :V] = s * (d - (s * d).sum(-1, keepdim=True))
+    if add is not None:
+        out[:, :V] += add[:, :V].float()
+    return _r(out)
+
+
 def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, state3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
               grad_inv_scale=1.0, max_norm=5.0):
     g = grads * grad_inv_scale

@@ -296,3 +296,20 @@ def test_subsampling(B, Tin, F, C):
     E.conv1_bwd(dh1.cpu(), x, wdw, wdb)
     close(dw, wdw, 1e-3, "conv1 dw")
     close(db, wdb, 1e-3, "conv1 db")
+
+
+def test_vocab_softmax_fwd_bwd():
+    """Posterior for self-conditioned intermediate CTC and its backward, against the emulation (V = 600 and a ragged V)."""
+    for R, V in ((777, 600), (65, 24), (33, 50)):
+        ld = ((V + 7) // 8) * 8
+        x = rnd(R, ld, seed=R) * 3
+        p = K().vocab_softmax_fwd(x.cuda(), V)
+        want = E.vocab_softmax_fwd(x, V)
+        assert p.shape == (R, ld) and float(p[:, V:].float().abs().sum()) == 0.0
+        close(p, want, 1e-2, "vocab softmax")
+        dp, add = rnd(R, ld, seed=R + 1).to(BF), rnd(R, ld, seed=R + 2).to(BF)
+        for a in (None, add):
+            d = K().vocab_softmax_bwd(p, dp.cuda(), V, add=a.cuda() if a is not None else None)
+            wd = E.vocab_softmax_bwd(p.cpu(), dp, V, add=a)
+            assert float(d[:, V:].float().abs().sum()) == 0.0
+            close(d, wd, 2e-2, "vocab softmax bwd")

@@ -84,8 +84,10 @@ def test_unsupported_options_raise():
         m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=False)
     with pytest.raises(NotImplementedError):
         m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, input_layer="linear")
-    with pytest.raises(NotImplementedError):
-        m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, interctc_layer_idx=[1], interctc_use_conditioning=True)
+    enc_sc = m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, interctc_layer_idx=[1], interctc_use_conditioning=True)
+    assert enc_sc._cfg.interctc_use_conditioning and enc_sc.conditioning_layer is None  # the model creates it (:96-101)
+    with pytest.raises(NotImplementedError):  # stochastic depth: the reference's own EncoderLayer takes no such argument
+        m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, stochastic_depth_rate=0.1)
     with pytest.raises(AssertionError):  # conformer_encoder.py:284-285: taps must lie strictly inside the stack
         m.ConformerEncoder(80, 64, 4, 128, 2, macaron_style=True, interctc_layer_idx=[2])
     assert m.ConformerEncoder(80, 64, 4, 128, 3, macaron_style=True, interctc_layer_idx=[2, 1])._cfg.interctc_layer_idx == (1, 2)

@@ -316,6 +316,41 @@ def test_intermediate_ctc_modules_golden(golden_dir):
     assert rows[0][0] < 0.10, rows[:6]
 
 
+def test_self_conditioned_model_golden(golden_dir):
+    """ESPnetASRModel with interctc_use_conditioning: the model creates encoder.conditioning_layer like the reference
+    (espnet_model.py:96-101), the reference's state_dict loads, loss / stats / gradients follow tests/golden/e2e_selfcond.npz."""
+    import os
+    m = M()
+    z = np.load(os.path.join(golden_dir, "e2e_selfcond.npz"))
+    g = {k: z[k] for k in z.files}
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/")}
+    V = 24
+    enc = m.ConformerEncoder(80, 16, 2, 32, 3, 0.0, 0.0, 0.0, macaron_style=True, rel_pos_type="latest", cnn_module_kernel=7,
+                             interctc_layer_idx=[1, 2], interctc_use_conditioning=True)
+    dec = m.TransformerDecoder(V, 16, 2, 32, 2, 0.0, 0.0)
+    tokens = ["<blank>", "<unk>"] + [f"t{i}" for i in range(V - 3)] + ["<sos/eos>"]
+    model = m.ESPnetASRModel(V, tokens, m.DefaultFrontend(), None, m.UtteranceMVN(), None, enc, None, dec, m.CTC(V, 16), None,
+                             ctc_weight=0.3, interctc_weight=0.4, lsm_weight=0.1)
+    assert tuple(model.encoder.conditioning_layer.weight.shape) == (16, V)
+    assert set(sd) <= set(model.state_dict())
+    _load(model, sd, "")
+    model = model.cuda()
+    loss, stats, _ = model(torch.tensor(g["wav"]).cuda(), torch.tensor(g["lens"]).cuda(), torch.tensor(g["text"]).cuda(),
+                           torch.tensor(g["text_lens"]).cuda())
+    loss.backward()
+    for k in ("loss", "loss_ctc", "loss_att", "loss_interctc_layer1", "loss_interctc_layer2"):
+        np.testing.assert_allclose(stats[k].item(), g[k].item(), rtol=2e-2, err_msg=k)
+    rows = grad_report(_grads(model, ""), {k[5:]: v for k, v in g.items() if k.startswith("grad/")})
+    assert rows[0][0] < 0.10, rows[:6]
+    with pytest.raises(NotImplementedError):
+        model.encoder(torch.zeros(1, 40, 80).cuda(), torch.tensor([40]).cuda())
+    with pytest.raises(NotImplementedError):  # vocabulary must be a multiple of 8 for the posterior GEMM
+        m.ESPnetASRModel(20, tokens[:20], None, None, None, None,
+                         m.ConformerEncoder(80, 16, 2, 32, 3, macaron_style=True, rel_pos_type="latest", cnn_module_kernel=7,
+                                            interctc_layer_idx=[1], interctc_use_conditioning=True),
+                         None, m.TransformerDecoder(20, 16, 2, 32, 1), m.CTC(20, 16), None, ctc_weight=0.3)
+
+
 def test_global_mvn_and_ratio_specaug_modules(golden_dir, tmp_path):
     """GlobalMVN / SpecAug(time_mask_width_ratio_range) drop-ins against outputs of the unmodified reference."""
     import os

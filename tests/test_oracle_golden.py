@@ -211,3 +211,28 @@ def test_intermediate_ctc_step():
             got = torch.zeros_like(sd[k[5:]]) if got is None else got
             worst = max(worst, float(np.abs(got.numpy() - v).max() / max(np.abs(v).max(), 1e-3)))
     assert worst < 2e-3, worst
+
+
+def test_self_conditioned_intermediate_ctc_step():
+    """Self-conditioned intermediate CTC (conformer_encoder.py:350-358, interctc_use_conditioning): the CTC posterior of
+    blocks 1 and 2 is fed back through encoder.conditioning_layer; loss, stats and every gradient against the unmodified
+    reference (tests/golden/e2e_selfcond.npz, V = 24)."""
+    g = load("e2e_selfcond.npz")
+    sd = {k[3:]: torch.tensor(v).requires_grad_(v.dtype == np.float32) for k, v in g.items() if k.startswith("sd/")}
+    assert sd["encoder.conditioning_layer.weight"].shape == (16, 24)
+    cfg = om.ModelCfg(enc=om.EncCfg(80, 16, 2, 32, 3, 7, "latest"), dec=om.DecCfg(24, 16, 2, 32, 2), vocab=24,
+                      interctc_weight=0.4, interctc_layer_idx=(1, 2), interctc_use_conditioning=True)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    loss, stats = om.asr_forward(torch.tensor(g["wav"]), torch.tensor(g["lens"]), torch.tensor(g["text"]),
+                                 torch.tensor(g["text_lens"]), sd, cfg, mel)
+    for k in ("loss_ctc", "loss_att", "loss_interctc_layer1", "loss_interctc_layer2"):
+        np.testing.assert_allclose(float(stats[k]), g[k].item(), rtol=2e-5)
+    np.testing.assert_allclose(loss.item(), g["loss"].item(), rtol=2e-5)
+    loss.backward()
+    worst = 0.0
+    for k, v in g.items():
+        if k.startswith("grad/"):
+            got = sd[k[5:]].grad
+            got = torch.zeros_like(sd[k[5:]]) if got is None else got
+            worst = max(worst, float(np.abs(got.numpy() - v).max() / max(np.abs(v).max(), 1e-3)))
+    assert worst < 2e-3, worst

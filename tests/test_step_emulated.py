@@ -98,6 +98,35 @@ def test_emulated_step_with_intermediate_ctc(emulated):
     assert "loss_interctc_layer1" not in out0
 
 
+def test_emulated_step_with_self_conditioning(emulated):
+    """Self-conditioned intermediate CTC (interctc_use_conditioning) against the unmodified reference, V = 24."""
+    z = np.load(os.path.join(GOLDEN, "e2e_selfcond.npz"))
+    g = {k: z[k] for k in z.files}
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/") and v.dtype == np.float32}
+    pack = bparams.ParamPack(sd, lowp=torch.float32)
+    pack.refresh()
+    pack.zero_grad()
+    enc = bstep.EncCfg(80, 16, 2, 32, 3, 7, "latest", 0.0, 0.0, 0.0, interctc_layer_idx=(1, 2), interctc_use_conditioning=True,
+                       vocab=24)
+    dec = bstep.DecCfg(24, 16, 2, 32, 2, 0.0, 0.0, 0.0, 0.0)
+    cfg = bstep.ModelCfg(enc=enc, dec=dec, vocab=24, interctc_weight=0.4)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    feats, flens = bstep.frontend_fwd(torch.tensor(g["wav"]), torch.tensor(g["lens"]), mel, cfg)
+    out = bstep.train_step_from_feats(feats, flens, torch.tensor(g["text"]), torch.tensor(g["text_lens"]), pack.P, pack.W,
+                                      pack.G, cfg, bstep.StepCtx(0, True))
+    pack.finalize_grads()
+    for k in ("loss", "loss_ctc", "loss_att", "loss_interctc_layer1", "loss_interctc_layer2"):
+        np.testing.assert_allclose(out[k].item(), g[k].item(), rtol=5e-5, err_msg=k)
+    worst, worst_name = 0.0, ""
+    for k, v in g.items():
+        if k.startswith("grad/"):
+            got = pack.grads()[k[5:]].numpy()
+            err = float(np.abs(got - v).max() / max(np.abs(v).max(), 1e-3))
+            if err > worst:
+                worst, worst_name = err, k
+    assert worst < 3e-3, (worst, worst_name)
+
+
 def test_add_sos_eos_matches_oracle():
     text = torch.tensor([[5, 6, 7, 8], [3, 4, -1, -1], [9, 2, 11, -1]])
     tl = torch.tensor([4, 2, 3])

@@ -99,6 +99,32 @@ def test_step_with_intermediate_ctc_vs_reference_golden():
     assert rows[0][0] < 0.10, rows[:6]
 
 
+def test_step_with_self_conditioning_vs_reference_golden():
+    """Self-conditioned intermediate CTC (interctc_use_conditioning), tests/golden/e2e_selfcond.npz (V = 24)."""
+    bparams, bstep = mods()
+    z = np.load(os.path.join(GOLDEN, "e2e_selfcond.npz"))
+    g = {k: z[k] for k in z.files}
+    sd = {k[3:]: torch.tensor(v).cuda() for k, v in g.items() if k.startswith("sd/") and v.dtype == np.float32}
+    pack = bparams.ParamPack(sd)
+    pack.refresh()
+    pack.zero_grad()
+    enc = bstep.EncCfg(80, 16, 2, 32, 3, 7, "latest", 0.0, 0.0, 0.0, interctc_layer_idx=(1, 2), interctc_use_conditioning=True,
+                       vocab=24)
+    dec = bstep.DecCfg(24, 16, 2, 32, 2, 0.0, 0.0, 0.0, 0.0)
+    cfg = bstep.ModelCfg(enc=enc, dec=dec, vocab=24, interctc_weight=0.4)
+    mel = torch.from_numpy(om.slaney_mel_matrix()).cuda()
+    feats, flens = bstep.frontend_fwd(torch.tensor(g["wav"]).cuda(), torch.tensor(g["lens"]).cuda(), mel, cfg)
+    out = bstep.train_step_from_feats(feats, flens, torch.tensor(g["text"]).cuda(), torch.tensor(g["text_lens"]).cuda(),
+                                      pack.P, pack.W, pack.G, cfg, bstep.StepCtx(0, True))
+    pack.finalize_grads()
+    torch.cuda.synchronize()
+    for k in ("loss", "loss_ctc", "loss_att", "loss_interctc_layer1", "loss_interctc_layer2"):
+        np.testing.assert_allclose(out[k].item(), g[k].item(), rtol=2e-2, err_msg=k)
+    rows = grad_report(pack.grads(), {k[5:]: v for k, v in g.items() if k.startswith("grad/")})
+    print("worst grads:", rows[:6])
+    assert rows[0][0] < 0.10, rows[:6]
+
+
 def make_sd(enc, dec, V, seed=0):
     """Random-init parameters under the reference's state_dict names/shapes."""
     g = torch.Generator().manual_seed(seed)
