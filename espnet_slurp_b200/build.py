@@ -51,11 +51,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
                 f.write(r.stderr)
     objs = [os.path.join(OBJ, os.path.basename(s)[:-3] + ".o") for s in srcs]
     if force or jobs or _stale(LIB, objs):
-        r = subprocess.run([NVCC, "-shared", "-o", LIB] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"],
+        tmp = LIB + ".tmp%d" % os.getpid()  # link next to the target, then rename: readers never see a partial library
+        r = subprocess.run([NVCC, "-shared", "-o", tmp] + objs + ["-lcudart_static", "-lpthread", "-ldl", "-lrt"],
                            capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError("link failed")
+        os.replace(tmp, LIB)
     return LIB
 
 

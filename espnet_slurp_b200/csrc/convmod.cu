@@ -51,14 +51,19 @@ __device__ __forceinline__ void stage_tiles(const bf16* __restrict__ pw1, const 
       unpack8_bf16(rg[u], gt);
 #pragma unroll
       for (int q = 0; q < 8; ++q) g[q] = a[q] * sigmoidf_(gt[q]);  // 0 * sigmoid(0) = 0 outside the utterance
+      // a quarter-warp stores 8 x 16 B at a 32-byte stride: lanes cg 4..7 write their upper half first so that each
+      // store instruction touches 32 distinct banks (ncu showed a 2-way conflict on these stores)
+      const int h = (cg >> 2) & 1;
       float4* dst = reinterpret_cast<float4*>(&sg[f][cg * 8]);
-      dst[0] = make_float4(g[0], g[1], g[2], g[3]);
-      dst[1] = make_float4(g[4], g[5], g[6], g[7]);
+      const float4 lo = make_float4(g[0], g[1], g[2], g[3]), hi = make_float4(g[4], g[5], g[6], g[7]);
+      dst[h] = h ? hi : lo;
+      dst[h ^ 1] = h ? lo : hi;
       if (BWD) {
         unpack8_bf16(rd[u], g);
         float4* dd = reinterpret_cast<float4*>(&sd[f][cg * 8]);
-        dd[0] = make_float4(g[0], g[1], g[2], g[3]);
-        dd[1] = make_float4(g[4], g[5], g[6], g[7]);
+        const float4 dlo = make_float4(g[0], g[1], g[2], g[3]), dhi = make_float4(g[4], g[5], g[6], g[7]);
+        dd[h] = h ? dhi : dlo;
+        dd[h ^ 1] = h ? dlo : dhi;
       }
     }
   }
