@@ -16,7 +16,8 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libb200slu.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", 
-         "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-Xptxas", "-v"]
+         "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default", "-Xptxas", "-v"] + \
+    os.environ.get("B200SLU_NVCC_EXTRA", "").split()  # tuning experiments only (e.g. -DB200SLU_EPI_F32X2=0)
 
 
 def _stale(target, deps):
