@@ -218,9 +218,12 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
+    # stdout carries exactly one JSON line: anything libraries write to fd 1 while the job runs (NCCL prints its version
+    # banner there from C, whatever NCCL_DEBUG_FILE says) is sent to stderr; fd 1 is restored just before the line
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own banner / debug output (NCCL_DEBUG=VERSION|INFO) goes to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from espnet_slurp_b200 import _lib
     lib = _lib.lib()
@@ -337,6 +340,8 @@ def run_ours(args):
                                 "sample": f"1 warm-up + {nt} timed fwd+bwd steps ({nt * sec:.1f} s of CPU work) of the same model on "
                                           f"{args.cpu_batch} utterances per step ({audio_cpu:.1f} audio-s), oracle/model.py fp32 "
                                           f"on {cores} torch threads, {sec:.2f} s/step"}
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
