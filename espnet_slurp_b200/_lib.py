@@ -94,6 +94,8 @@ _SIGNATURES = {
     "b200slu_logmel_fwd": [_P, _L, _I, _I, _P, _P, _I, _I, _I, _P, _P, _P],
     "b200slu_set_step_params": [_P],
     "b200slu_adam_step": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _I, _F, _F, _P, _P],
+    "b200slu_lsm_static_max_rows": [],
+    "b200slu_lsm_loss_fwd_bwd_static": [_P, _L, _L, _I, _P, _I, _F, _F, _P, _P, _P, _L, _P],
     "b200slu_vocab_softmax_fwd": [_P, _L, _L, _I, _P, _L, _P],
     "b200slu_vocab_softmax_bwd": [_P, _L, _P, _L, _L, _I, _P, _L, _P, _L, _P],
     "b200slu_global_mvn_fwd": [_P, _I, _I, _I, _P, _P, _P, _P, _P],
@@ -108,6 +110,7 @@ _RESTYPES = {
     "b200slu_ctc_workspace_size": C.c_longlong,
     "b200slu_conv1_bwd_workspace_size": C.c_longlong,
     "b200slu_lsm_workspace_size": C.c_longlong,
+    "b200slu_lsm_static_max_rows": C.c_longlong,
     "b200slu_rel_shift_index": C.c_longlong,
 }
 EXPORTS = tuple(_SIGNATURES)

@@ -198,3 +198,55 @@ extern "C" int b200slu_lsm_loss_fwd_bwd(const float* logits, long long ldv, long
   B2_LAUNCH_CHECK();
   return 0;
 }
+
+// ----------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of b200slu_lsm_loss_fwd_bwd for callers that cannot allocate (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The per-row scratch (loss + "correct" flag, 8 bytes per row) lives in a file-scope device array of
+// B200SLU_LSM_STATIC_MAX_ROWS rows = 256 KB, held by every GPU that loads the library until the process exits.
+//  * In host code `g_lsm_static_scratch` is only a host-side stand-in for the symbol, not a device address: its device
+//    address is looked up with cudaGetSymbolAddress once per device (that device current) and handed to the kernels.
+//  * Every call on a device shares the array.  Both kernels touch rows [0, R) only and lsm_kernel writes each of those
+//    rows before lsm_finish_kernel reads it, so nothing has to start at zero and stale contents of an earlier call are
+//    never read.  Calls that overlap on the GPU (different streams, or graphs replayed concurrently) race on it.
+//  * Calls no cudaMalloc / cudaFree / allocating library routine, and leaves the (optional, event-creating) profiling
+//    scope out.
+// ----------------------------------------------------------------------------------------------------------------
+#define B200SLU_LSM_STATIC_MAX_ROWS 32768
+static __device__ __align__(256) unsigned char g_lsm_static_scratch[(size_t)B200SLU_LSM_STATIC_MAX_ROWS * 8];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_lsm_static_ptr[kMaxDevices] = {};  // device address of the array, per device ordinal (0 = not looked up yet)
+}  // namespace
+
+extern "C" long long b200slu_lsm_static_max_rows(void) { return B200SLU_LSM_STATIC_MAX_ROWS; }
+
+extern "C" int b200slu_lsm_loss_fwd_bwd_static(const float* logits, long long ldv, long long R, int V, const int* targets,
+                                               int ignore_id, float smoothing, float grad_scale, float* stats3, float* grad_f32,
+                                               void* grad_bf16, long long ldg, void* stream) {
+  B2_CHECK_ARG(R > 0 && V > 1 && ldv >= V, "lsm_loss_static: bad shape R=%lld V=%d", R, V);
+  B2_CHECK_ARG(R <= B200SLU_LSM_STATIC_MAX_ROWS,
+               "lsm_loss_static: R=%lld rows exceed the static scratch of %d rows; use b200slu_lsm_loss_fwd_bwd with a "
+               "caller-provided workspace",
+               R, B200SLU_LSM_STATIC_MAX_ROWS);
+  B2_CHECK_ARG((grad_f32 == nullptr && grad_bf16 == nullptr) || ldg >= V, "lsm_loss_static: ldg < V");
+  int dev = -1;
+  B2_CUDA(cudaGetDevice(&dev));
+  B2_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "lsm_loss_static: device ordinal %d out of range", dev);
+  void* ws = __atomic_load_n(&g_lsm_static_ptr[dev], __ATOMIC_ACQUIRE);
+  if (ws == nullptr) {  // set-up, once per device, with that device current (racing threads look up the same address)
+    B2_CUDA(cudaGetSymbolAddress(&ws, g_lsm_static_scratch));
+    B2_CHECK_ARG(ws != nullptr, "lsm_loss_static: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&g_lsm_static_ptr[dev], ws, __ATOMIC_RELEASE);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  float* loss_rows = (float*)ws;
+  int* correct_rows = (int*)(loss_rows + R);
+  lsm_kernel<<<(unsigned)R, 256, 0, st>>>(logits, ldv, V, targets, ignore_id, smoothing, grad_scale, loss_rows, correct_rows,
+                                          grad_f32, (bf16*)grad_bf16, (grad_f32 || grad_bf16) ? ldg : 0);
+  B2_LAUNCH_CHECK();
+  lsm_finish_kernel<<<1, 256, 0, st>>>(loss_rows, correct_rows, R, stats3);
+  B2_LAUNCH_CHECK();
+  return 0;
+}

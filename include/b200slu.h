@@ -219,6 +219,16 @@ int b200slu_lsm_loss_fwd_bwd(const float* logits, long long ldv, long long R, in
                              float smoothing, float grad_scale, void* workspace, float* stats3, float* grad_f32, void* grad_bf16,
                              long long ldg, void* stream);
 
+/* Allocation-free variant of b200slu_lsm_loss_fwd_bwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments minus the workspace: the per-row scratch is a static device array of b200slu_lsm_static_max_rows()
+ * (32768) rows = 256 KB per GPU; more rows -> B200SLU_EINVAL with a message.  Allocates nothing.  All calls on a device
+ * share the array: calls that overlap on the GPU (different streams) race. */
+long long b200slu_lsm_static_max_rows(void);
+int b200slu_lsm_loss_fwd_bwd_static(const float* logits, long long ldv, long long R, int V, const int* targets, int ignore_id,
+                                    float smoothing, float grad_scale, float* stats3, float* grad_f32, void* grad_bf16,
+                                    long long ldg, void* stream);
+
 /* Self-conditioned intermediate CTC (espnet2/asr/encoder/conformer_encoder.py:350-358, espnet2/asr/ctc.py:99-107):
  * probs = softmax(logits[:, :V]) as bf16 [R, ldp] (columns >= V zero), and its backward
  * dlogits = probs * (dprobs - <probs, dprobs>) (+ add), bf16 [R, ldd]. */
