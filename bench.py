@@ -96,8 +96,7 @@ def build_cfg(args):
 
 def make_state_dict(cfg, seed=0):
     """Random-init weights of the architecture under the reference's state_dict names (no checkpoints offline)."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from test_step_gpu import make_sd
+    from espnet_slurp_b200.testing import make_sd
     return make_sd(cfg.enc, cfg.dec, cfg.vocab, seed=seed)
 
 

@@ -60,6 +60,7 @@ _SIGNATURES = {
     "b200slu_prof_family_name": [_I],
     "b200slu_prof_get": [_I, C.POINTER(C.c_double)],
     "b200slu_prof_total_launches": [],
+    "b200slu_dropout_mask": [_F, _U64, _U32, _L, _P, _P],
     "b200slu_gemm_bf16": [_I, _I, _I, _I, _P, _L, _P, _L, _P, _L, _P, _P],
     "b200slu_gemm_bf16_ex": [_P, _P, _P],
     "b200slu_layernorm_fwd": [_P, _P, _P, _I, _I, _F, _P, _P, _P, _P],

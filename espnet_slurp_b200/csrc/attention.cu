@@ -637,20 +637,21 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
     mqv = mqu;
     mp = mk;
   }
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;  // per device
+  if (!b2_device_done(configured)) {
     B2_CUDA(cudaFuncSetAttribute(relattn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     B2_CUDA(cudaFuncSetAttribute(relattn_fwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    configured = true;
+    b2_device_mark(configured);
   }
   const int nqt = (Tq + QT - 1) / QT;
   const double tiles = (double)B * H;
   B2_SCOPE(FAM_ATTN, st, tiles * (4.0 * Tq * Tk * DK + (rel ? 2.0 * Tq * (2.0 * Tq - 1) * DK : 0.0)),
            tiles * (2.0 * DK * (2.0 * Tq + 2.0 * Tk) + 2.0 * Tq * Tk * (drop_p > 0.f ? 2.0 : 1.0)));
   static const bool dbg = getenv("B200SLU_ATTN_DEBUG") != nullptr;
-  static long long* dbg_buf = nullptr;
+  long long* dbg_buf = nullptr;
   if (dbg) {
-    if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 512 * 8 * sizeof(long long)));
+    dbg_buf = b2_debug_scratch();
+    B2_CHECK_ARG(dbg_buf != nullptr, "relattn: debug scratch unavailable");
     B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 512 * 8 * sizeof(long long), st));
     a.dbg = dbg_buf;
   }

@@ -74,6 +74,13 @@ struct B2ProfScope {
 #define B2_SCOPE(fam, st, flops, bytes) B2ProfScope prof_scope_((fam), (st), (double)(flops), (double)(bytes))
 
 int b2_num_sms();
+// Per-device one-time set-up (cudaFuncSetAttribute, symbol addresses): `mask` holds one bit per device ordinal.  Two
+// threads racing through the same set-up both run it (harmless); the bit is set only after the set-up succeeded.
+int b2_current_device();
+static inline bool b2_device_done(const unsigned long long& mask) { return (mask >> (b2_current_device() & 63)) & 1ull; }
+static inline void b2_device_mark(unsigned long long& mask) { mask |= 1ull << (b2_current_device() & 63); }
+// Debug scratch (tuning printouts only): a static device array, so that even the debug paths never allocate.
+long long* b2_debug_scratch();  // 4096 long longs per device, or nullptr on error
 
 // ---------------------------------------------------------------------------
 // device helpers

@@ -472,10 +472,10 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
     if (gy > units) gy = units;                                                                                              \
     const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 2) + KMAX * CC) * sizeof(float);                               \
     auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
-    static bool cfg = false;                                                                                                 \
-    if (!cfg) {                                                                                                              \
+    static unsigned long long cfg = 0;                                                                                                 \
+    if (!b2_device_done(cfg)) {                                                                                                              \
       B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                           \
-      cfg = true;                                                                                                            \
+      b2_device_mark(cfg);                                                                                                            \
     }                                                                                                                        \
     kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,  \
                                               dbias_accum);                                                                  \

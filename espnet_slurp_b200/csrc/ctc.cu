@@ -581,10 +581,10 @@ extern "C" int b200slu_ctc_bwd(const float* logits, long long ldv, int B, int T,
   const long long n = (long long)B * T * Smax;
   const float *em = ws, *alpha = ws + n, *beta = ws + 2 * n, *lse = ws + 3 * n;
   const int* feasible = (const int*)(ws + ws_floats(B, T, Lmax));
-  static bool cfg = false;
-  if (!cfg) {
+  static unsigned long long cfg = 0;
+  if (!b2_device_done(cfg)) {
     B2_CUDA(cudaFuncSetAttribute(ctc_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    cfg = true;
+    b2_device_mark(cfg);
   }
   B2_SCOPE(FAM_CTC, st, 0, (double)B * T * V * (4.0 + (grad_f32 ? 4.0 : 0.0) + (grad_bf16 ? 2.0 : 0.0)) + 12.0 * n);
   const bool vec4 = ldv % 4 == 0 && ldg % 4 == 0 && ((uintptr_t)logits % 16) == 0 &&

@@ -193,6 +193,19 @@ __global__ void __launch_bounds__(256) embed_bwd_kernel(const float* __restrict_
   }
 }
 
+// keep[e] = 1 iff element e (flat index) of dropout site (seed, site) is kept: the decisions every kernel of the
+// library derives from dropout_keep8 / dropout_mul8 / dropout_lanes8 (parity tests replay them in the CPU oracle)
+__global__ void __launch_bounds__(256) dropout_mask_kernel(uint8_t* __restrict__ keep, long long n, B2Dropout drop) {
+  const long long ng = (n + 7) >> 3;
+  const B2DropKey dk = dropout_key(drop);
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ng; g += (long long)gridDim.x * blockDim.x) {
+    const uint32_t m = dropout_keep8(dk, (unsigned long long)g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (g * 8 + j < n) keep[g * 8 + j] = (uint8_t)((m >> j) & 1u);
+  }
+}
+
 int colsum_blocks_per_sm() {
   static const int v = getenv("B200SLU_COLSUM_BPS") ? atoi(getenv("B200SLU_COLSUM_BPS")) : 2;  // tuning knob
   return v > 0 ? v : 2;
@@ -207,6 +220,16 @@ extern "C" int b200slu_cast_bf16(const float* x, void* y, long long n, float alp
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * n);
   cast_kernel<<<b2_grid_for(n >> 3, 256), 256, 0, st>>>(x, (bf16*)y, n, alpha, b2_make_drop(drop_p, seed, site));
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_dropout_mask(float drop_p, unsigned long long seed, unsigned int site, long long n, unsigned char* keep,
+                                    void* stream) {
+  B2_CHECK_ARG(n > 0 && keep != nullptr && drop_p >= 0.f && drop_p < 1.f, "dropout_mask: n > 0, 0 <= p < 1");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 1.0 * n);
+  dropout_mask_kernel<<<b2_grid_for((n + 7) >> 3, 256), 256, 0, st>>>(keep, n, b2_make_drop(drop_p, seed, site));
   B2_LAUNCH_CHECK();
   return 0;
 }

@@ -620,10 +620,10 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
            int kb_per, const EpiArgs& ep, cudaStream_t st) {
   using L = SmemLayout<BN, STAGES, stg_bufs(EF, BN, CG), CG, epi_warps(EF, BN, CG)>;
   auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF, CG>;
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;  // per device
+  if (!b2_device_done(configured)) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    configured = true;
+    b2_device_mark(configured);
   }
   const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BM * CG - 1) / (BM * CG);
   const long long units = (long long)tiles_n * tiles_m * splits * nbatch;
@@ -631,9 +631,10 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
   const int slots = b2_num_sms() / CG;  // CTAs (CG = 1) or CTA pairs (CG = 2: one pair per TPC)
   const int grid = (units < slots ? (int)units : slots) * CG;
   EpiArgs epl = ep;
-  static long long* dbg_buf = nullptr;
+  long long* dbg_buf = nullptr;
   if (ep.debug & 16) {
-    if (dbg_buf == nullptr) B2_CUDA(cudaMalloc(&dbg_buf, 12 * sizeof(long long)));
+    dbg_buf = b2_debug_scratch();
+    B2_CHECK_ARG(dbg_buf != nullptr, "gemm: debug scratch unavailable");
     B2_CUDA(cudaMemsetAsync(dbg_buf, 0, 12 * sizeof(long long), st));
     epl.dbg_out = dbg_buf;
   }

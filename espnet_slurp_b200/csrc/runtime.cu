@@ -18,21 +18,37 @@ void b200slu_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-static const B2StepParams* g_step_params = nullptr;
-const B2StepParams* b2_step_params() { return g_step_params; }
+int b2_current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+// One registration slot per device ordinal: the pointer is device memory of THAT device (two devices driven from one
+// process each keep their own; a kernel launched on device d only ever sees d's slot).
+static const B2StepParams* g_step_params[64] = {};
+const B2StepParams* b2_step_params() { return g_step_params[b2_current_device() & 63]; }
 extern "C" int b200slu_set_step_params(const void* dev_ptr) {
-  g_step_params = (const B2StepParams*)dev_ptr;
+  g_step_params[b2_current_device() & 63] = (const B2StepParams*)dev_ptr;
   return 0;
 }
 
 int b2_num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  static int n[64] = {};
+  const int dev = b2_current_device();
+  int& v = n[dev & 63];
+  if (v == 0) {
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
   }
-  return n;
+  return v;
+}
+
+static __device__ __align__(256) long long g_debug_scratch[4096];
+long long* b2_debug_scratch() {
+  static long long* ptrs[64] = {};
+  long long*& p = ptrs[b2_current_device() & 63];
+  if (p == nullptr && cudaGetSymbolAddress((void**)&p, g_debug_scratch) != cudaSuccess) p = nullptr;
+  return p;
 }
 
 namespace {

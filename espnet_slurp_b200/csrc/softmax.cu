@@ -420,10 +420,10 @@ extern "C" int b200slu_softmax_bwd(const float* dp_drop, const void* p, long lon
 #undef SM_BR
 #define SM_B(NG)                                                                                                  \
   do {                                                                                                            \
-    static bool cfg = false;                                                                                      \
-    if (!cfg) {                                                                                                   \
+    static unsigned long long cfg = 0;                                                                                      \
+    if (!b2_device_done(cfg)) {                                                                                                   \
       B2_CUDA(cudaFuncSetAttribute(softmax_bwd_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536)); \
-      cfg = true;                                                                                                 \
+      b2_device_mark(cfg);                                                                                                 \
     }                                                                                                             \
     softmax_bwd_kernel<NG><<<grid, threads, smem, st>>>(dp_drop, (const bf16*)p, a, (bf16*)d_ac, (bf16*)d_bd, drop); \
   } while (0)

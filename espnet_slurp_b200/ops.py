@@ -451,6 +451,14 @@ def rel_shift_index(i: int, j: int, T: int, mode: str) -> int:
     return _lib.lib().b200slu_rel_shift_index(i, j, T, RELPOS[mode])
 
 
+def dropout_mask(drop: Drop, n: int, device="cuda"):
+    """uint8 [n]: 1 where flat element e of the dropout site ``drop`` = (p, seed, site) is kept (parity tests)."""
+    p, seed, site = _drop(drop)
+    keep = torch.empty(n, device=device, dtype=torch.uint8)
+    check(_lib.lib().b200slu_dropout_mask(p, seed, site, n, ptr(keep), stream_ptr()), "dropout_mask")
+    return keep
+
+
 # ---- optimizer ----------------------------------------------------------------------------------------------------
 def adam_step(params, grads, exp_avg, exp_avg_sq, lr: float, step: int, state3, betas=(0.9, 0.999), eps: float = 1e-8,
               weight_decay: float = 0.0, grad_inv_scale: float = 1.0, max_norm: float = 5.0):

@@ -72,11 +72,15 @@ class StepCtx:
         self.seed = int(seed)
         self.training = training
         self._site = 0
+        self.sites: Dict[str, tuple] = {}  # tag (the reference module that owns the Dropout) -> (p, site)
 
-    def drop(self, p: float):
+    def drop(self, p: float, tag: Optional[str] = None):
         """Allocate a site; returns the (p, seed, site) triple or None when dropout is inactive."""
         self._site += 1
-        if not self.training or p <= 0.0:
+        active = self.training and p > 0.0
+        if tag is not None:
+            self.sites[tag] = (float(p) if active else 0.0, self._site)
+        if not active:
             return None
         return (float(p), self.seed, self._site)
 
@@ -121,7 +125,7 @@ def subsampled_len(t_in: int) -> int:
 # ------------------------------------------------------------------------------------------------------------------
 def ffn_fwd(x, P, W, pre: str, norm: str, act: str, scale: float, p_drop: float, ctx: StepCtx):
     ln, _, st = K.layernorm_fwd(x, P[norm + ".weight"], P[norm + ".bias"])
-    d1, d2 = ctx.drop(p_drop), ctx.drop(p_drop)
+    d1, d2 = ctx.drop(p_drop, pre + ".inner"), ctx.drop(p_drop, pre + ".outer")
     h, hpre = K.gemm(ln, W[pre + ".w_1.weight"], bias=P[pre + ".w_1.bias"], act=act, act_grad_out=True, drop=d1)
     y = K.gemm(h, W[pre + ".w_2.weight"], bias=P[pre + ".w_2.bias"], alpha=scale, residual=x, drop=d2, out_dtype=F32)
     return y, (x, ln, st, hpre, h, d1, d2, pre, norm, act, scale)
@@ -174,7 +178,7 @@ def relmha_fwd(x, pos16, klens, P, W, p: str, norm: str, cfg: EncCfg, B: int, T:
     qu, qv = K.pos_bias_fwd(q, P[a + ".pos_bias_u"].reshape(-1), P[a + ".pos_bias_v"].reshape(-1))
     pp = K.gemm(pos16, W[a + ".linear_pos.weight"])
     Pn = pos16.shape[0]
-    da, do = ctx.drop(cfg.att_dropout), ctx.drop(cfg.dropout)
+    da, do = ctx.drop(cfg.att_dropout, a + ".att"), ctx.drop(cfg.dropout, a + ".out")
     scale = 1.0 / math.sqrt(d // H)
     if K.relattn_supported(T, T, d // H, cfg.rel_pos_type):
         # short utterances: scores, rel_shift, softmax, dropout and context in one tcgen05 kernel (scores never leave TMEM)
@@ -237,7 +241,7 @@ def convmod_fwd(x, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: St
     else:
         mr = K.bn_finalize(sums, B * T, 1e-5, 0.1, rm, rv, nb)
     bs = K.bn_swish_fwd(dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"])
-    do = ctx.drop(cfg.dropout)
+    do = ctx.drop(cfg.dropout, cm + ".out")
     y = K.gemm(bs, W[cm + ".pointwise_conv2.weight"], bias=P[cm + ".pointwise_conv2.bias"], residual=x, drop=do,
                out_dtype=F32)
     return y, (x, ln, st, pw1, dw, mr, bs, do)
@@ -306,11 +310,11 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     if col.numel() * 2 > KEEP_IM2COL_BYTES:
         col = None
     h2v = h2.view(B * T, F2 * C_)
-    dpos = ctx.drop(cfg.pos_dropout)
+    dpos = ctx.drop(cfg.pos_dropout, e + ".x")
     x = K.gemm(h2v, W[e + ".out.0.weight"], bias=P[e + ".out.0.bias"], alpha=math.sqrt(cfg.d), drop=dpos, out_dtype=F32)
     # RelPositionalEncoding: table rows + dropout (embedding.py:228-244 / 156-170)
     Pn = 2 * T - 1 if cfg.rel_pos_type == "latest" else T
-    dpe = ctx.drop(cfg.pos_dropout)
+    dpe = ctx.drop(cfg.pos_dropout, e + ".pos")
     pos16 = K.cast_bf16(pos_table(cfg.rel_pos_type, T if cfg.rel_pos_type == "latest" else Pn, cfg.d, feats.device), drop=dpe)
     olens = torch.clamp((flens + 3) // 4, max=T).to(torch.int32)  # mask[:, :, :-2:2][:, :, :-2:2] (subsampling.py:87)
     layers, inter = [], []
@@ -406,7 +410,7 @@ def _mha_fwd(xq16, kv_src16, q_w: str, kv_w: str, P, W, a: str, klens, B, Tq, Tk
         kv = K.gemm(kv_src16, W[a + ".linear_kv.weight"], bias=P[a + ".linear_kv.bias"])
         k, v = kv[:, :d], kv[:, d:]
         proj = (q, kv)
-    da = ctx.drop(p_att)
+    da = ctx.drop(p_att, a + ".att")
     scale = 1.0 / math.sqrt(d // H)
     if K.relattn_supported(Tq, Tk, d // H, "none"):
         pr, pd, c = K.relattn_fwd(q, None, k, v, None, klens, B, Tq, Tk, H, "none", causal, scale, drop=da)
@@ -422,13 +426,13 @@ def dec_layer_fwd(x, mem16, ylens, mlens, P, W, p: str, cfg: DecCfg, B: int, L: 
     # masked self-attention (decoder_layer.py:88-110)
     ln1, _, st1 = K.layernorm_fwd(x, P[p + ".norm1.weight"], P[p + ".norm1.bias"])
     c1, sa = _mha_fwd(ln1, None, "", "", P, W, p + ".self_attn", ylens, B, L, L, H, d, True, cfg.self_att_dropout, ctx, True)
-    do1 = ctx.drop(cfg.dropout)
+    do1 = ctx.drop(cfg.dropout, p + ".self_attn.out")
     x1 = K.gemm(c1, W[p + ".self_attn.linear_out.weight"], bias=P[p + ".self_attn.linear_out.bias"], residual=x, drop=do1,
                 out_dtype=F32)
     # source attention over the encoder memory (decoder_layer.py:112-123)
     ln2, _, st2 = K.layernorm_fwd(x1, P[p + ".norm2.weight"], P[p + ".norm2.bias"])
     c2, ca = _mha_fwd(ln2, mem16, "", "", P, W, p + ".src_attn", mlens, B, L, T, H, d, False, cfg.src_att_dropout, ctx, False)
-    do2 = ctx.drop(cfg.dropout)
+    do2 = ctx.drop(cfg.dropout, p + ".src_attn.out")
     x2 = K.gemm(c2, W[p + ".src_attn.linear_out.weight"], bias=P[p + ".src_attn.linear_out.bias"], residual=x1, drop=do2,
                 out_dtype=F32)
     # feed-forward, ReLU (decoder_layer.py:125-131)
@@ -483,7 +487,7 @@ def decoder_fwd(mem16, mlens, ys_in, ys_in_lens, P, W, cfg: DecCfg, ctx: StepCtx
     """mem16 bf16 [B*T, d]; ys_in int32 [B, L]; returns (logits f32 [B*L, round8(V)] (columns >= V unspecified), saved)."""
     L = ys_in.shape[1]
     tok = ys_in.reshape(-1)
-    de = ctx.drop(cfg.pos_dropout)
+    de = ctx.drop(cfg.pos_dropout, p + ".embed")
     x = K.embed_fwd(P[p + ".embed.0.weight"], tok, pos_table("abs", L, cfg.d, mem16.device), L, math.sqrt(cfg.d), drop=de)
     layers = []
     for n in range(cfg.blocks):

@@ -58,6 +58,15 @@ long long b200slu_prof_total_launches(void);
  * copy.  NULL unregisters.  Process-global (one training process per GPU, abs_task.py:1049-1070). */
 int b200slu_set_step_params(const void* dev_ptr);
 
+/* Dropout decisions of one site, exported for the parity tests (the reference draws torch's Philox stream, which no
+ * other implementation can reproduce; the tests replay THESE decisions in the CPU oracle at every torch.nn.Dropout
+ * of encoder_layer.py:97-149, attention.py:91, positionwise_feed_forward.py:32, embedding.py:94,244,
+ * decoder_layer.py:88-131).  keep[e] = 1 iff flat element e of site (seed, site) is kept; kept elements are scaled
+ * by 1/(1-p).  Element index of a site: row * N + column of the [M,N] tensor the dropout acts on (N = logical width;
+ * attention probabilities: ((h*B + b)*Tq + i) * round8(Tk) + j).  Honours the registered device seed like every kernel. */
+int b200slu_dropout_mask(float drop_p, unsigned long long seed, unsigned int site, long long n, unsigned char* keep,
+                         void* stream);
+
 /* ---- K2: GEMM with fused epilogue ------------------------------------------------------
  * Replaces the nn.Linear / Conv1d(k=1) / im2col-Conv2d GEMMs:
  *   espnet/nets/pytorch_backend/transformer/attention.py:33-36,232 (linear_q/k/v/out/pos)
@@ -223,7 +232,8 @@ int b200slu_lsm_loss_fwd_bwd(const float* logits, long long ldv, long long R, in
  * operators for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  * Same arguments minus the workspace: the per-row scratch is a static device array of b200slu_lsm_static_max_rows()
  * (32768) rows = 256 KB per GPU; more rows -> B200SLU_EINVAL with a message.  Allocates nothing.  All calls on a device
- * share the array: calls that overlap on the GPU (different streams) race. */
+ * share the array: calls that overlap on the GPU (different streams) race.  The first call on a device looks the
+ * array's address up (cudaGetSymbolAddress): make that call outside a graph capture. */
 long long b200slu_lsm_static_max_rows(void);
 int b200slu_lsm_loss_fwd_bwd_static(const float* logits, long long ldv, long long R, int V, const int* targets, int ignore_id,
                                     float smoothing, float grad_scale, float* stats3, float* grad_f32, void* grad_bf16,

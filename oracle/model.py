@@ -355,9 +355,17 @@ def conv2d_subsample(x: torch.Tensor, sd: SD, p: str) -> torch.Tensor:
     return linear(h, sd, p + ".out.0")
 
 
-def mha_core(q, k, v, key_valid, extra_scores=None, causal=False):
+def _d(drop, x, tag: str):
+    """One torch.nn.Dropout call site of the reference.  ``drop`` is None (p = 0, the configuration of the frozen goldens)
+    or a callable (x, tag) -> x * keep / (1 - p) that replays given keep decisions: torch's own Philox stream cannot be
+    reproduced by another implementation, so dropout parity is checked with the decisions as an INPUT (the tests feed
+    the CUDA path's exported decisions, b200slu_dropout_mask).  Tags name the module that owns the Dropout."""
+    return x if drop is None else drop(x, tag)
+
+
+def mha_core(q, k, v, key_valid, extra_scores=None, causal=False, drop=None, tag: str = ""):
     """forward_attention (attention.py:64-96): scores already scaled; masked with
-    finfo.min, softmax, masked entries re-zeroed, @ v, heads merged."""
+    finfo.min, softmax, masked entries re-zeroed, dropout (:91), @ v, heads merged."""
     B, H, Tq, dk = q.shape
     Tk = k.shape[2]
     scores = q @ k.transpose(-2, -1)
@@ -370,11 +378,11 @@ def mha_core(q, k, v, key_valid, extra_scores=None, causal=False):
         valid = valid & tri[None, None]
     scores = scores.masked_fill(~valid, torch.finfo(scores.dtype).min)
     attn = torch.softmax(scores, dim=-1).masked_fill(~valid, 0.0)
-    ctx = attn @ v
+    ctx = _d(drop, attn, tag + ".att") @ v
     return ctx.transpose(1, 2).reshape(B, Tq, H * dk)
 
 
-def rel_pos_mhsa(x, pos_emb, key_valid, sd: SD, p: str, H: int, mode: str = "latest"):
+def rel_pos_mhsa(x, pos_emb, key_valid, sd: SD, p: str, H: int, mode: str = "latest", drop=None):
     """RelPositionMultiHeadedAttention.forward (attention.py:265-308) /
     LegacyRelPositionMultiHeadedAttention.forward (attention.py:167-209).
     rel_shift is applied through the integer index maps above instead of the
@@ -397,11 +405,11 @@ def rel_pos_mhsa(x, pos_emb, key_valid, sd: SD, p: str, H: int, mode: str = "lat
         row_t = torch.from_numpy(row)
         col_t = torch.from_numpy(np.maximum(col, 0))
         bd = bd[:, :, row_t, col_t].masked_fill(zero[None, None], 0.0)
-    ctx = mha_core(qu, k, v, key_valid, extra_scores=bd)
+    ctx = mha_core(qu, k, v, key_valid, extra_scores=bd, drop=drop, tag=p)
     return linear(ctx, sd, p + ".linear_out")
 
 
-def mha(xq, xkv, key_valid, sd: SD, p: str, H: int, causal: bool = False):
+def mha(xq, xkv, key_valid, sd: SD, p: str, H: int, causal: bool = False, drop=None):
     """MultiHeadedAttention.forward (attention.py:98-114)."""
     B, Tq, d = xq.shape
     Tk = xkv.shape[1]
@@ -409,12 +417,12 @@ def mha(xq, xkv, key_valid, sd: SD, p: str, H: int, causal: bool = False):
     q = linear(xq, sd, p + ".linear_q").view(B, Tq, H, dk).transpose(1, 2)
     k = linear(xkv, sd, p + ".linear_k").view(B, Tk, H, dk).transpose(1, 2)
     v = linear(xkv, sd, p + ".linear_v").view(B, Tk, H, dk).transpose(1, 2)
-    return linear(mha_core(q, k, v, key_valid, causal=causal), sd, p + ".linear_out")
+    return linear(mha_core(q, k, v, key_valid, causal=causal, drop=drop, tag=p), sd, p + ".linear_out")
 
 
-def ffn(x, sd: SD, p: str, act):
-    """PositionwiseFeedForward.forward (positionwise_feed_forward.py:30-32)."""
-    return linear(act(linear(x, sd, p + ".w_1")), sd, p + ".w_2")
+def ffn(x, sd: SD, p: str, act, drop=None):
+    """PositionwiseFeedForward.forward (positionwise_feed_forward.py:30-32): w_2(dropout(act(w_1(x))))."""
+    return linear(_d(drop, act(linear(x, sd, p + ".w_1")), p + ".inner"), sd, p + ".w_2")
 
 
 def conv_module(x, sd: SD, p: str, kernel: int, training: bool = True, bn_stats_out: Optional[dict] = None):
@@ -443,26 +451,29 @@ def conv_module(x, sd: SD, p: str, kernel: int, training: bool = True, bn_stats_
     return y @ sd[p + ".pointwise_conv2.weight"][:, :, 0].t() + sd[p + ".pointwise_conv2.bias"]
 
 
-def conformer_block(x, pos_emb, key_valid, sd: SD, p: str, cfg: EncCfg, bn_stats_out=None, training: bool = True):
+def conformer_block(x, pos_emb, key_valid, sd: SD, p: str, cfg: EncCfg, bn_stats_out=None, training: bool = True, drop=None):
     """EncoderLayer.forward (espnet/nets/pytorch_backend/conformer/encoder_layer.py:76-157),
-    pre-LN macaron, dropout = 0; training=False: BatchNorm uses its running statistics."""
-    x = x + 0.5 * ffn(layer_norm(x, sd, p + ".norm_ff_macaron"), sd, p + ".feed_forward_macaron", swish)
-    x = x + rel_pos_mhsa(layer_norm(x, sd, p + ".norm_mha"), pos_emb, key_valid, sd, p + ".self_attn",
-                         cfg.heads, cfg.rel_pos_type)
-    x = x + conv_module(layer_norm(x, sd, p + ".norm_conv"), sd, p + ".conv_module", cfg.kernel, training=training,
-                        bn_stats_out=bn_stats_out)
-    x = x + 0.5 * ffn(layer_norm(x, sd, p + ".norm_ff"), sd, p + ".feed_forward", swish)
+    pre-LN macaron; every branch is ``residual + scale * dropout(branch)`` (:101,129,138,144), dropout replayed through
+    ``drop`` (see _d; None = p 0); training=False: BatchNorm uses its running statistics."""
+    x = x + 0.5 * _d(drop, ffn(layer_norm(x, sd, p + ".norm_ff_macaron"), sd, p + ".feed_forward_macaron", swish, drop),
+                     p + ".feed_forward_macaron.outer")
+    x = x + _d(drop, rel_pos_mhsa(layer_norm(x, sd, p + ".norm_mha"), pos_emb, key_valid, sd, p + ".self_attn",
+                                  cfg.heads, cfg.rel_pos_type, drop), p + ".self_attn.out")
+    x = x + _d(drop, conv_module(layer_norm(x, sd, p + ".norm_conv"), sd, p + ".conv_module", cfg.kernel, training=training,
+                                 bn_stats_out=bn_stats_out), p + ".conv_module.out")
+    x = x + 0.5 * _d(drop, ffn(layer_norm(x, sd, p + ".norm_ff"), sd, p + ".feed_forward", swish, drop),
+                     p + ".feed_forward.outer")
     return layer_norm(x, sd, p + ".norm_final")
 
 
 def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_stats_out=None,
-                      return_blocks: bool = False, training: bool = True, cond_idx=()):
+                      return_blocks: bool = False, training: bool = True, cond_idx=(), drop=None):
     """ConformerEncoder.forward (espnet2/asr/encoder/conformer_encoder.py:292-368).  cond_idx: 1-based block indices
     after which the CTC posterior of the (after_norm'ed) block output is fed back, self-conditioning :350-358:
     x += conditioning_layer(softmax(ctc_lo(after_norm(x)))); the returned blocks are the outputs BEFORE that addition,
     which is what the intermediate CTC losses see (:339-347)."""
     T_in = feats.shape[1]
-    x = conv2d_subsample(feats, sd, p + ".embed") * math.sqrt(cfg.d)  # embedding.py:239
+    x = _d(drop, conv2d_subsample(feats, sd, p + ".embed") * math.sqrt(cfg.d), p + ".embed.x")  # embedding.py:239,244
     T = x.shape[1]
     olens = subsampled_lens(ilens, T_in)
     key_valid = ~pad_mask(olens, T)
@@ -470,9 +481,10 @@ def conformer_encoder(feats, ilens, sd: SD, cfg: EncCfg, p: str = "encoder", bn_
         pos_emb = rel_pos_table(T, cfg.d, x.dtype)
     else:
         pos_emb = legacy_pos_table(T, cfg.d, dtype=x.dtype)
+    pos_emb = _d(drop, pos_emb, p + ".embed.pos")  # embedding.py:244 / :170: dropout on the positional table too
     outs = []
     for n in range(cfg.blocks):
-        x = conformer_block(x, pos_emb, key_valid, sd, f"{p}.encoders.{n}", cfg, bn_stats_out, training)
+        x = conformer_block(x, pos_emb, key_valid, sd, f"{p}.encoders.{n}", cfg, bn_stats_out, training, drop)
         if return_blocks:
             outs.append(x)
         if n + 1 in cond_idx:
@@ -592,19 +604,20 @@ def add_sos_eos(text, text_lens, sos: int, eos: int, ignore: int = -1):
     return ys_in, ys_out
 
 
-def transformer_decoder(memory, mem_lens, ys_in, ys_in_lens, sd: SD, cfg: DecCfg, p: str = "decoder"):
+def transformer_decoder(memory, mem_lens, ys_in, ys_in_lens, sd: SD, cfg: DecCfg, p: str = "decoder", drop=None):
     """TransformerDecoder.forward (espnet2/asr/decoder/transformer_decoder.py:92-145) with
     DecoderLayer.forward (espnet/nets/pytorch_backend/transformer/decoder_layer.py:63-134)."""
     B, L = ys_in.shape
-    x = sd[p + ".embed.0.weight"][ys_in] * math.sqrt(cfg.d) + abs_pos_table(L, cfg.d, memory.dtype)
+    x = _d(drop, sd[p + ".embed.0.weight"][ys_in] * math.sqrt(cfg.d) + abs_pos_table(L, cfg.d, memory.dtype), p + ".embed")
     tgt_valid = ~pad_mask(ys_in_lens, L)
     mem_valid = ~pad_mask(mem_lens, memory.shape[1])
     for n in range(cfg.blocks):
         q = f"{p}.decoders.{n}"
         h = layer_norm(x, sd, q + ".norm1")
-        x = x + mha(h, h, tgt_valid, sd, q + ".self_attn", cfg.heads, causal=True)
-        x = x + mha(layer_norm(x, sd, q + ".norm2"), memory, mem_valid, sd, q + ".src_attn", cfg.heads)
-        x = x + ffn(layer_norm(x, sd, q + ".norm3"), sd, q + ".feed_forward", F.relu)
+        x = x + _d(drop, mha(h, h, tgt_valid, sd, q + ".self_attn", cfg.heads, causal=True, drop=drop), q + ".self_attn.out")
+        x = x + _d(drop, mha(layer_norm(x, sd, q + ".norm2"), memory, mem_valid, sd, q + ".src_attn", cfg.heads, drop=drop),
+                   q + ".src_attn.out")
+        x = x + _d(drop, ffn(layer_norm(x, sd, q + ".norm3"), sd, q + ".feed_forward", F.relu, drop), q + ".feed_forward.outer")
     x = layer_norm(x, sd, p + ".after_norm")
     return linear(x, sd, p + ".output_layer")
 
@@ -661,11 +674,12 @@ def th_accuracy(logits, target, ignore: int = -1) -> float:
 # --------------------------------------------------------------------------- #
 # whole step
 # --------------------------------------------------------------------------- #
-def asr_forward_from_feats(feats, feat_lens, text, text_lens, sd: SD, cfg: ModelCfg):
+def asr_forward_from_feats(feats, feat_lens, text, text_lens, sd: SD, cfg: ModelCfg, drop=None):
     """ESPnetASRModel.forward from the encoder input on
     (espnet2/asr/espnet_model.py:202-297): returns (loss, stats)."""
     enc, olens, blocks = conformer_encoder(feats, feat_lens, sd, cfg.enc, return_blocks=True,
-                                           cond_idx=cfg.interctc_layer_idx if cfg.interctc_use_conditioning else ())
+                                           cond_idx=cfg.interctc_layer_idx if cfg.interctc_use_conditioning else (),
+                                           drop=drop)
     loss_ctc = ctc_branch(enc, olens, text, text_lens, sd)
     stats_ic = {"loss_ctc": loss_ctc.detach()}  # espnet_model.py:217: recorded before the intermediate losses are mixed in
     if cfg.interctc_weight != 0.0 and cfg.interctc_layer_idx:
@@ -680,7 +694,7 @@ def asr_forward_from_feats(feats, feat_lens, text, text_lens, sd: SD, cfg: Model
         loss_ctc = (1 - cfg.interctc_weight) * loss_ctc + cfg.interctc_weight * loss_ic
     sos = eos = cfg.vocab - 1  # espnet_model.py:75-82
     ys_in, ys_out = add_sos_eos(text, text_lens, sos, eos)
-    dec = transformer_decoder(enc, olens, ys_in, text_lens + 1, sd, cfg.dec)
+    dec = transformer_decoder(enc, olens, ys_in, text_lens + 1, sd, cfg.dec, drop=drop)
     loss_att = label_smoothing_loss(dec, ys_out, cfg.lsm_weight)
     acc = th_accuracy(dec, ys_out)
     loss = cfg.ctc_weight * loss_ctc + (1 - cfg.ctc_weight) * loss_att  # espnet_model.py:284

@@ -3,7 +3,8 @@
 Two uses: (1) on the GPU each CUDA kernel is compared with its function here on the same inputs;
 (2) on the CPU the step orchestration (``espnet_slurp_b200.step``: forward + hand-written backward) runs
 over these functions instead of the kernels and is compared with autograd over ``oracle/model.py``, which
-checks every backward formula and every buffer layout without a GPU.  Dropout is not emulated (p must be 0).
+checks every backward formula and every buffer layout without a GPU.  Dropout is emulated with the library's own
+counter-based decisions (tests/dropout_ref.py restates the hash; element index conventions as in the kernels).
 ``exact=True`` keeps everything in fp32 (no bf16 rounding) for tight checks of the formulas.
 """
 from __future__ import annotations
@@ -30,8 +31,12 @@ def round8(n):
     return (n + 7) // 8 * 8
 
 
-def _nodrop(drop):
-    assert drop is None or drop[0] <= 0.0, "dropout is not emulated"
+def _mul(drop, shape):
+    """keep / (1 - p) multipliers of a dropout site over a row-major tensor of ``shape`` (None when inactive)."""
+    if drop is None or drop[0] <= 0.0:
+        return None
+    import dropout_ref
+    return dropout_ref.multiplier(drop, tuple(shape))
 
 
 def _act(y, act):
@@ -56,8 +61,8 @@ def _act_grad(x, act):
 def gemm(a, b, *, trans=False, trans_a=None, trans_b=None, bias=None, act=None, alpha=1.0, residual=None,
          act_grad_input=None, act_grad=None, act_grad_out=False, out_dtype=None, out=None, accumulate=False, drop=None,
          dropout_p=0.0, seed=0, site=0):
-    _nodrop(drop)
-    assert dropout_p == 0.0
+    if drop is None and dropout_p > 0.0:
+        drop = (dropout_p, seed, site)
     ta = trans if trans_a is None else trans_a
     tb = trans if trans_b is None else trans_b
     A = a.float().t() if ta else a.float()
@@ -67,8 +72,15 @@ def gemm(a, b, *, trans=False, trans_a=None, trans_b=None, bias=None, act=None, 
     if bias is not None:
         y = y + bias[:N]
     pre_act_out = act_grad_out
-    pre = _r(_act_grad(y, act)) if pre_act_out is not False and pre_act_out is not None else None
-    y = _act(y, act) * alpha
+    m = _mul(drop, y.shape)  # element index row * N + column (gemm_sm100.cu epilogue)
+    pre = None
+    if pre_act_out is not False and pre_act_out is not None:
+        pre = _act_grad(y, act)
+        pre = _r(pre * m if m is not None else pre)  # the saved derivative carries the element's dropout multiplier
+    y = _act(y, act)
+    if m is not None:
+        y = y * m
+    y = y * alpha
     if act_grad_input is not None:
         y = y * _act_grad(act_grad_input.float(), act_grad)
     if residual is not None:
@@ -132,7 +144,6 @@ def layernorm_fwd(x, gamma, beta, eps=1e-12, want_bf16=True, want_f32=False):
 
 
 def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g=False, g_alpha=1.0, g_drop=None, g_colsum_out=None):
-    _nodrop(g_drop)
     dy = dy.float()
     mean, rstd = stats[:, 0:1], stats[:, 1:2]
     xh = (x - mean) * rstd
@@ -142,16 +153,19 @@ def layernorm_bwd(dy, x, gamma, stats, dgamma, dbeta, dx_add=None, want_g=False,
         dx = dx + dx_add
     dgamma += (dy * xh).sum(0)
     dbeta += dy.sum(0)
+    m = _mul(g_drop, dx.shape)
+    gd = dx * g_alpha if m is None else dx * m * g_alpha
     if g_colsum_out is not None:
-        g_colsum_out += (dx * g_alpha).float().sum(0)
-    return dx, (_r(dx * g_alpha) if want_g else None)
+        g_colsum_out += gd.float().sum(0)
+    return dx, (_r(gd) if want_g else None)
 
 
 def cast_bf16(x, alpha=1.0, drop=None, out=None, colsum_out=None):
-    _nodrop(drop)
-    y = _r(x * alpha)
+    m = _mul(drop, x.shape)
+    xd = x * alpha if m is None else x * m * alpha
+    y = _r(xd)
     if colsum_out is not None:
-        colsum_out += (x * alpha).float().sum(0)
+        colsum_out += xd.float().sum(0)
     if out is not None:
         out.copy_(y.to(out.dtype))
         return out
@@ -175,15 +189,16 @@ def pos_bias_bwd(dqu, dqv, dq_out, du, dv):
 
 
 def embed_fwd(emb, tokens, pe, L, scale, drop=None):
-    _nodrop(drop)
     R = tokens.numel()
     pos = torch.arange(R) % L
-    return emb[tokens.long()] * scale + pe[pos]
+    x = emb[tokens.long()] * scale + pe[pos]
+    m = _mul(drop, x.shape)
+    return x if m is None else x * m
 
 
 def embed_bwd(dx, tokens, scale, demb, drop=None):
-    _nodrop(drop)
-    demb.index_add_(0, tokens.long(), dx * scale)
+    m = _mul(drop, dx.shape)
+    demb.index_add_(0, tokens.long(), (dx if m is None else dx * m) * scale)
 
 
 def _shift(bd, T, mode):
@@ -199,7 +214,6 @@ def _shift(bd, T, mode):
 
 
 def softmax_fwd(ac, bd, key_lens, Tk, mode, causal, scale, drop=None):
-    _nodrop(drop)
     H, B, Tq, ld = ac.shape
     s = ac[..., :Tk].clone()
     if mode in ("latest", "legacy"):
@@ -215,14 +229,17 @@ def softmax_fwd(ac, bd, key_lens, Tk, mode, causal, scale, drop=None):
     p = torch.nan_to_num(p, nan=0.0)
     out = torch.zeros(H, B, Tq, ld, dtype=_lowp())
     out[..., :Tk] = p.to(out.dtype)
-    return out, out
+    m = _mul(drop, out.shape)  # element index over the padded head-major tensor (softmax.cu / attention.cu)
+    if m is None:
+        return out, out
+    return out, _r(out.float() * m)
 
 
 def softmax_bwd(dpd, p, Tk, mode, scale, ld_bd=0, drop=None):
-    _nodrop(drop)
     H, B, Tq, ld = p.shape
     pf = p.float()[..., :Tk]
-    dp = dpd[..., :Tk]
+    m = _mul(drop, p.shape)
+    dp = dpd[..., :Tk] if m is None else dpd[..., :Tk] * m[..., :Tk]
     ds = pf * (dp - (dp * pf).sum(-1, keepdim=True)) * scale
     dac = torch.zeros(H, B, Tq, ld, dtype=_lowp())
     dac[..., :Tk] = ds.to(dac.dtype)

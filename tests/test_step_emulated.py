@@ -152,3 +152,58 @@ def test_param_pack_fusions_are_views():
     pack.G["decoder.decoders.0.self_attn.linear_qkv.weight"][d:2 * d] += 1.0
     assert torch.all(pack.grads()["decoder.decoders.0.self_attn.linear_k.weight"] == 1.0)
     assert torch.all(pack.grads()["decoder.decoders.0.self_attn.linear_q.weight"] == 0.0)
+
+
+@pytest.mark.parametrize("rel", ["latest", "legacy"])
+def test_emulated_step_with_dropout_matches_oracle_with_replayed_masks(emulated, rel):
+    """Dropout ON at every site (encoder 0.1 / 0.1 / 0.1, decoder incl. the self / source attention dropouts the SLURP
+    recipes leave at 0): the step's forward and hand-written backward must use the SAME decisions at every site, which
+    the oracle replays through its Dropout hooks (tests/dropout_ref.py).  A site or element-index mismatch between a
+    forward and its backward gives finite, plausible, wrong gradients -- this is the test that sees it."""
+    import dropout_ref
+    z = np.load(os.path.join(GOLDEN, f"e2e_{rel}.npz"))
+    g = {k: z[k] for k in z.files}
+    sd = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/") and v.dtype == np.float32}
+    pack = bparams.ParamPack(sd, lowp=torch.float32)
+    pack.refresh()
+    pack.zero_grad()
+    enc = bstep.EncCfg(80, 16, 2, 32, 2, 7, rel, 0.1, 0.1, 0.1)
+    dec = bstep.DecCfg(20, 16, 2, 32, 2, 0.1, 0.1, 0.1, 0.1)
+    cfg = bstep.ModelCfg(enc=enc, dec=dec, vocab=20)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    feats, flens = bstep.frontend_fwd(torch.tensor(g["wav"]), torch.tensor(g["lens"]), mel, cfg)
+    seed = 77
+    ctx = bstep.StepCtx(seed, True)
+    text, tl = torch.tensor(g["text"]), torch.tensor(g["text_lens"])
+    out = bstep.train_step_from_feats(feats, flens, text, tl, pack.P, pack.W, pack.G, cfg, ctx)
+    pack.finalize_grads()
+    assert len(ctx.sites) == 2 + 2 * 7 + 1 + 2 * 6 and all(p == 0.1 for p, _ in ctx.sites.values())
+    assert len({s for _, s in ctx.sites.values()}) == len(ctx.sites)  # one site id per Dropout module
+    replay = dropout_ref.DropReplay(ctx.sites, seed)
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    ocfg = om.ModelCfg(enc=om.EncCfg(80, 16, 2, 32, 2, 7, rel), dec=om.DecCfg(20, 16, 2, 32, 2), vocab=20)
+    oloss, ostats = om.asr_forward_from_feats(feats, flens.long(), text, tl, osd, ocfg, drop=replay)
+    oloss.backward()
+    assert replay.used == set(ctx.sites)  # every Dropout of the reference graph has its site in the step, and vice versa
+    np.testing.assert_allclose(out["loss"].item(), oloss.item(), rtol=5e-5)
+    np.testing.assert_allclose(out["loss_att"].item(), ostats["loss_att"].item(), rtol=5e-5)
+    # dropout really changed the result (the goldens are p = 0)
+    assert abs(out["loss"].item() - g["loss"].item()) > 1e-3 * abs(g["loss"].item())
+    worst, worst_name = 0.0, ""
+    for k, v in osd.items():
+        want = v.grad.numpy() if v.grad is not None else np.zeros(tuple(v.shape), np.float32)
+        got = pack.grads()[k].numpy()
+        err = float(np.abs(got - want).max() / max(np.abs(want).max(), 1e-3))
+        if err > worst:
+            worst, worst_name = err, k
+    assert worst < 3e-3, (worst, worst_name)
+
+
+def test_dropout_ref_keep_rate_and_determinism():
+    import dropout_ref
+    a = dropout_ref.keep_mask(0.1, 5, 3, 100003)
+    assert np.array_equal(a, dropout_ref.keep_mask(0.1, 5, 3, 100003))
+    assert abs(a.mean() - 0.9) < 5e-3
+    assert not np.array_equal(a, dropout_ref.keep_mask(0.1, 5, 4, 100003))
+    assert not np.array_equal(a, dropout_ref.keep_mask(0.1, 6, 3, 100003))
+    assert dropout_ref.keep_mask(0.0, 1, 1, 64).all()
