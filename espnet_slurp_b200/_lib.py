@@ -88,6 +88,7 @@ _SIGNATURES = {
     "b200slu_im2col3x3s2": [_P, _I, _I, _I, _I, _P, _P],
     "b200slu_col2im3x3s2_relu": [_P, _P, _I, _I, _I, _I, _P, _P],
     "b200slu_ctc_workspace_size": [_I, _I, _I],
+    "b200slu_ctc_lattice_states": [_P, _I, _P, _I, _I, _P, _P, _P],
     "b200slu_ctc_fwd": [_P, _L, _I, _I, _I, _P, _P, _I, _P, _I, _P, _P, _P, _P],
     "b200slu_ctc_bwd": [_P, _L, _I, _I, _I, _P, _P, _I, _P, _I, _P, _F, _P, _P, _L, _P],
     "b200slu_lsm_workspace_size": [_L],

@@ -285,7 +285,9 @@ relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_cons
     tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
     if (a.rel) {
       tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
-      const int c0 = a.Tq - 1 - i0 - (QT - 1);  // may be negative: out-of-range rows are zero-filled
+      // first position row the tile can reach = source column of (last query row of the tile, key 0); may be negative:
+      // out-of-range rows are zero-filled
+      const int c0 = b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col;
       tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
       tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
     }
@@ -463,7 +465,7 @@ relattn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid
       tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
       if (a.rel) {
         tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
-        const int c0 = a.Tq - 1 - i0 - (QT - 1);
+        const int c0 = b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col;
         tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
         tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
       }

@@ -120,6 +120,22 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
 }
 
 // ---------------------------------------------------------------------------
+// rel_shift as an index map (attention.py:240-263 latest, :145-165 legacy): element (i, j) of the shifted T x T matrix
+// is element (row, col) of the un-shifted matrix_bd; row < 0 = the literal zero the legacy variant inserts at j = i + 1.
+// ONE definition for the host index entry (b200slu_rel_shift_index), softmax.cu (forward gather and the base column
+// of the backward scatter) and attention.cu (base of the position window a query tile can reach).
+// ---------------------------------------------------------------------------
+struct B2ShiftSrc {
+  int row, col;
+};
+__host__ __device__ __forceinline__ B2ShiftSrc b2_rel_shift_src(int i, int j, int T, int mode) {
+  if (mode == B200SLU_RELPOS_LATEST) return B2ShiftSrc{i, T - 1 - i + j};
+  if (j <= i) return B2ShiftSrc{i, T - 1 - i + j};  // legacy, lower triangle: same map as latest
+  if (j == i + 1) return B2ShiftSrc{-1, 0};
+  return B2ShiftSrc{i + 1, j - i - 2};
+}
+
+// ---------------------------------------------------------------------------
 // counter-based dropout: splitmix64 keyed by (seed, site); two evaluations yield
 // 128 random bits = 8 x 16-bit lanes -> keep decisions for 8 consecutive
 // elements (element index = 8*group + lane).  Recomputed, never stored.

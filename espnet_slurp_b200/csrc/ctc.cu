@@ -51,6 +51,22 @@ __device__ __forceinline__ float lse3(float a, float b, float c) {  // log2 doma
 }
 
 __device__ __forceinline__ int ext_label(const int* __restrict__ lab, int s, int blank) { return (s & 1) ? lab[s >> 1] : blank; }
+// skip arc s-2 -> s allowed iff s is a label state past the first one whose label differs from the previous label
+// (gtn_ctc.py:26-36); the only definition: both lattice kernels and the export below call it
+__device__ __forceinline__ bool ctc_skip_into(const int* __restrict__ lab, int s, int S) {
+  return (s < S) && (s & 1) && s > 1 && (lab[s >> 1] != lab[(s >> 1) - 1]);
+}
+// the lattice as the device code sees it, for the bit-exact test against gtn_ctc.py:26-36
+__global__ void ctc_lattice_states_kernel(const int* __restrict__ labels, int Lmax, const int* __restrict__ llens, int blank,
+                                          int Smax, int* __restrict__ ext_out, unsigned char* __restrict__ skip_out) {
+  const int b = blockIdx.x;
+  const int* lab = labels + (long long)b * Lmax;
+  const int S = 2 * llens[b] + 1;
+  for (int s = threadIdx.x; s < Smax; s += blockDim.x) {
+    ext_out[(long long)b * Smax + s] = s < S ? ext_label(lab, s, blank) : -1;
+    skip_out[(long long)b * Smax + s] = ctc_skip_into(lab, s, S) ? 1 : 0;
+  }
+}
 
 // ---- 1. prep: one block per (b, t) ------------------------------------------------------------
 __global__ void __launch_bounds__(256) ctc_prep_kernel(const float* __restrict__ logits, long long ldv, int T, int V,
@@ -130,7 +146,7 @@ __device__ __forceinline__ void lattice_run(const float* __restrict__ eb, int Sm
 #pragma unroll
   for (int i = 0; i < C; ++i) {
     const int s = DIR == 0 ? s0 + i : s0 + i + 2;
-    skip[i] = (s < S) && (s & 1) && s > 1 && (lab[s >> 1] != lab[(s >> 1) - 1]);
+    skip[i] = ctc_skip_into(lab, s, S);
     live[i] = s0 + i < S;
   }
   const int t_first = DIR == 0 ? 0 : Tb - 1;
@@ -272,7 +288,7 @@ __device__ __forceinline__ void lattice_run_mw(const float* __restrict__ eb, int
 #pragma unroll
   for (int i = 0; i < C; ++i) {
     const int s = DIR == 0 ? s0 + i : s0 + i + 2;
-    skip[i] = (s < S) && (s & 1) && s > 1 && (lab[s >> 1] != lab[(s >> 1) - 1]);
+    skip[i] = ctc_skip_into(lab, s, S);
     live[i] = s0 + i < S;
   }
   const int t_first = DIR == 0 ? 0 : Tb - 1;
@@ -511,6 +527,15 @@ long long ws_floats(int B, int T, int Lmax) {
 }
 
 }  // namespace
+
+extern "C" int b200slu_ctc_lattice_states(const int* labels, int Lmax, const int* label_lens, int B, int blank, int* ext_out,
+                                          unsigned char* skip_out, void* stream) {
+  B2_CHECK_ARG(B > 0 && Lmax >= 0 && ext_out != nullptr && skip_out != nullptr, "ctc_lattice_states: bad arguments");
+  ctc_lattice_states_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(labels, Lmax > 0 ? Lmax : 1, label_lens, blank, 2 * Lmax + 1,
+                                                                 ext_out, skip_out);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" long long b200slu_ctc_workspace_size(int B, int T, int Lmax) { return ws_floats(B, T, Lmax) * 4 + (long long)B * 4; }
 

@@ -137,13 +137,9 @@ long long b200slu_prof_total_launches(void) {
 // same arithmetic softmax.cu applies on the device.  Used by the bit-exact index tests.
 extern "C" long long b200slu_rel_shift_index(int i, int j, int T, int mode) {
   if (i < 0 || j < 0 || i >= T || j >= T) return -1;
-  if (mode == B200SLU_RELPOS_LATEST) return (long long)i * 65536 + (T - 1 - i + j) + 1;
-  if (mode == B200SLU_RELPOS_LEGACY) {
-    if (j <= i) return (long long)i * 65536 + (T - 1 - i + j) + 1;
-    if (j == i + 1) return 0;
-    return (long long)(i + 1) * 65536 + (j - i - 2) + 1;
-  }
-  return -1;
+  if (mode != B200SLU_RELPOS_LATEST && mode != B200SLU_RELPOS_LEGACY) return -1;
+  const B2ShiftSrc src = b2_rel_shift_src(i, j, T, mode);  // the function the kernels call (common.cuh)
+  return src.row < 0 ? 0 : (long long)src.row * 65536 + src.col + 1;
 }
 
 bool b2_pdl_enabled() {

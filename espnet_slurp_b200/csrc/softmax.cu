@@ -24,13 +24,9 @@ struct SmArgs {
 
 __device__ __forceinline__ float bd_term(const float* __restrict__ bd, long long hb, int i, int j, int T, long long ld_bd,
                                          int mode) {
-  if (mode == B200SLU_RELPOS_LATEST) return bd[(hb * T + i) * ld_bd + (T - 1 - i + j)];
-  if (mode == B200SLU_RELPOS_LEGACY) {
-    if (j <= i) return bd[(hb * T + i) * ld_bd + (T - 1 - i + j)];
-    if (j == i + 1) return 0.f;
-    return bd[(hb * T + i + 1) * ld_bd + (j - i - 2)];
-  }
-  return 0.f;
+  if (mode == B200SLU_RELPOS_NONE) return 0.f;
+  const B2ShiftSrc src = b2_rel_shift_src(i, j, T, mode);
+  return src.row < 0 ? 0.f : bd[(hb * T + src.row) * ld_bd + src.col];
 }
 
 template <int NG>
@@ -143,13 +139,13 @@ __global__ void __launch_bounds__(256) softmax_bwd_kernel(const float* __restric
       __syncwarp();
       bf16* own = dbd + (hb * T + i) * a.ld_bd;
       if (a.mode == B200SLU_RELPOS_LATEST) {
-        const int lo = T - 1 - i;  // column of j = 0
+        const int lo = b2_rel_shift_src(i, 0, T, B200SLU_RELPOS_LATEST).col;  // column of j = 0
         for (int n = lane; n < a.ld_bd; n += 32) {
           const int j = n - lo;
           own[n] = __float2bfloat16((j >= 0 && j < T) ? row_sm[j] : 0.f);
         }
       } else {  // legacy
-        const int lo = T - 1 - i;
+        const int lo = b2_rel_shift_src(i, 0, T, B200SLU_RELPOS_LATEST).col;
         for (int n = lane; n < a.ld_bd; n += 32) {
           if (n >= lo && n < T) own[n] = __float2bfloat16(row_sm[n - lo]);           // j = n - lo <= i
           else if (n >= T || i == 0) own[n] = __float2bfloat16(0.f);               // padding / never-read part of row 0
@@ -202,7 +198,10 @@ __global__ void __launch_bounds__(256) softmax_fwd_rows_kernel(const float* __re
       nvalid = min(nvalid, a.Tk);
       if (a.causal) nvalid = min(nvalid, i + 1);
     }
-    const float* bdr = (a.mode == B200SLU_RELPOS_LATEST) ? bd + (hb * a.Tq + i) * a.ld_bd + (a.Tq - 1 - i) : nullptr;
+    // latest: the source of (i, j) is (i, src(i, 0).col + j): one contiguous run per row
+    const float* bdr = (a.mode == B200SLU_RELPOS_LATEST)
+                           ? bd + (hb * a.Tq + i) * a.ld_bd + b2_rel_shift_src(i, 0, a.Tq, B200SLU_RELPOS_LATEST).col
+                           : nullptr;
     float s[NGL][8];
     float mx = -INFINITY;
 #pragma unroll
@@ -324,7 +323,7 @@ __global__ void __launch_bounds__(256) softmax_bwd_rows_kernel(const float* __re
         const long long hb = r / a.Tq;
         const int i = (int)(r - hb * a.Tq);
         bf16* own = dbd + (hb * T + i) * a.ld_bd;
-        const int lo = T - 1 - i;
+        const int lo = b2_rel_shift_src(i, 0, T, B200SLU_RELPOS_LATEST).col;
         for (int gq = l; gq < (int)(a.ld_bd >> 3); gq += LPR) {
           float o[8];
 #pragma unroll

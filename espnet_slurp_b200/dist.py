@@ -41,8 +41,12 @@ def loss_weight(batch_size: int, device, group=None) -> float:
 class GradReducer:
     """Bucketed all-reduce of the flat gradient buffer, overlapped with the backward."""
 
-    def __init__(self, pack, world: Optional[int] = None, group=None, bucket_bytes: int = 64 << 20, overlap: bool = True):
+    def __init__(self, pack, world: Optional[int] = None, group=None, bucket_bytes: int = 64 << 20, overlap: bool = True,
+                 late_prefixes: Sequence[str] = ()):
+        """late_prefixes: parameter-name prefixes whose gradients keep changing after their usual stage (self-conditioned
+        intermediate CTC: the encoder backward adds to ctc.ctc_lo after "heads"); they go into the last bucket."""
         self.pack, self.group = pack, group
+        self.late_prefixes = tuple(late_prefixes)
         self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.overlap = overlap
         self.cuda = pack.gflat.is_cuda
@@ -67,6 +71,8 @@ class GradReducer:
             s[0], s[1] = min(s[0], lo), max(s[1], hi)
 
         for n in pk.names:
+            if any(n.startswith(lp) for lp in self.late_prefixes):
+                continue  # left uncovered here -> part of the "front" remainder below
             if n.startswith("decoder.") or n.startswith("ctc."):
                 add("heads", n)
             elif n.startswith("encoder.encoders."):

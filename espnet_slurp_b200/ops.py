@@ -369,6 +369,16 @@ def ctc_fwd(logits, V: int, hlens, labels, label_lens, blank: int = 0):
     return loss, loss_sum, ws
 
 
+def ctc_lattice_states(labels, label_lens, blank: int = 0):
+    """(ext int32 [B, 2*Lmax+1], skip uint8): the lattice as the device code builds it (bit-exact test)."""
+    B, Lmax = labels.shape
+    ext = torch.empty(B, 2 * Lmax + 1, device=labels.device, dtype=torch.int32)
+    skip = torch.empty(B, 2 * Lmax + 1, device=labels.device, dtype=torch.uint8)
+    check(_lib.lib().b200slu_ctc_lattice_states(ptr(labels), Lmax, ptr(label_lens), B, blank, ptr(ext), ptr(skip), stream_ptr()),
+          "ctc_lattice_states")
+    return ext, skip
+
+
 def ctc_bwd(logits, V: int, hlens, labels, label_lens, ws, scale: float, blank: int = 0, want_f32: bool = False,
             want_bf16: bool = True):
     B, T, ldv = logits.shape

@@ -15,9 +15,18 @@ learning rate and Adam's bias corrections are read by the kernels from a 24-byte
 (ops.set_step_params).  A step is therefore capturable as ONE CUDA graph per input shape.  Batches of the reference's
 samplers come in a handful of padded shapes (length-bucketed batching: `batch_type: folded / numel`, sorted by length), so
 the graphs are cached per shape ("length buckets") with least-recently-used eviction: the first step of a new shape runs
-eagerly (one-time kernel attribute setup), the next one is captured, later ones replay.  With more than one rank the
-gradient all-reduce and the optimizer run after the replay (NCCL calls inside a capture hung on this stack, see
-bench.py), or, with dp_mode="eager_overlap", the step runs eagerly with the bucketed all-reduce overlapping the backward.
+eagerly (one-time kernel attribute setup), the next one is captured, later ones replay.
+
+More than one rank (the reference's DDP overlaps its bucketed all-reduce with the backward, trainer.py:221-236):
+  dp_mode="graph" (default)   the step is captured as a CHAIN of graphs that share one memory pool, cut where a gradient
+                              bucket of dist.GradReducer becomes final (decoder + CTC head, then every few encoder blocks,
+                              last to first).  Between two replays the host issues that bucket's NCCL all-reduce on the
+                              communication stream, so it runs under the next segment's kernels; only the small front
+                              bucket (subsampling convs) is reduced after the last segment.  NCCL calls stay outside any
+                              capture (capturing them hung on this stack).
+  dp_mode="graph_serial"      one graph, then ONE all-reduce of the whole 437 MB gradient buffer, then clip + Adam
+                              (round 1's measured mode: 0.94 ms exposed at 8 GPUs).
+  dp_mode="eager_overlap"     eager launches with the bucketed all-reduce overlapping the backward.
 """
 from __future__ import annotations
 
@@ -40,7 +49,7 @@ class _Bucket:
     def __init__(self, batch: Dict[str, torch.Tensor], dev):
         self.inp = {k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in batch.items()}
         self.res: Optional[torch.Tensor] = None
-        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.graph = None  # once captured: list of (CUDAGraph, stage whose gradient bucket is final after it or None)
         self.eager_steps = 0
 
 
@@ -48,7 +57,7 @@ class TrainStep:
     def __init__(self, cfg: bstep.ModelCfg, state_dict: Dict[str, torch.Tensor], rank: int = 0, world: int = 1,
                  dp_mode: str = "graph", use_graph: bool = True, lr: float = 1e-3, warmup_steps: int = 25000,
                  max_norm: float = 5.0, max_buckets: int = 4, eager_steps_before_capture: int = 1):
-        assert dp_mode in ("graph", "eager_overlap"), dp_mode
+        assert dp_mode in ("graph", "graph_serial", "eager_overlap"), dp_mode
         dev = torch.device("cuda", torch.cuda.current_device())
         self.cfg, self.rank, self.world, self.dev, self.dp_mode = cfg, rank, world, dev, dp_mode
         self.use_graph = use_graph and not (world > 1 and dp_mode == "eager_overlap")
@@ -70,15 +79,20 @@ class TrainStep:
             self.bn[p + "num_batches_tracked"] = nb.to(dev).long().reshape(1).clone() if nb is not None else \
                 torch.zeros(1, device=dev, dtype=torch.long)
         self.step_no = 0
-        self.reducer = GradReducer(self.pack, world, overlap=(dp_mode != "graph"))
+        # with self-conditioning the encoder backward still adds to ctc.ctc_lo's gradient after the heads are done
+        # (step.encoder_bwd): those parameters then belong to the last bucket, not to "heads"
+        late = ("ctc.",) if cfg.enc.interctc_use_conditioning else ()
+        self.reducer = GradReducer(self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
         self.buckets: "OrderedDict[tuple, _Bucket]" = OrderedDict()
         # per-step device record {u64 dropout seed; f32 lr, bias correction 1, bias correction 2, pad}: a ring of pinned
         # host slots so that the asynchronous copy of step s is never overwritten by the host preparing step s + 1
         self.sp_host = torch.zeros(64, 24, dtype=torch.uint8).pin_memory()
         self.sp_np = self.sp_host.numpy().view(np.dtype([("seed", "<u8"), ("lr", "<f4"), ("bc1", "<f4"), ("bc2", "<f4"),
                                                          ("pad", "<f4")]))
+        self.sp_events: list = [None] * 64  # per slot: "the H2D copy out of this slot has executed"
         self.sp_dev = torch.zeros(24, dtype=torch.uint8, device=dev)
         ops.set_step_params(self.sp_dev)
+        self._closed = False
         self.loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
         self.last: Optional[_Bucket] = None
 
@@ -87,19 +101,34 @@ class TrainStep:
         s, w = self.step_no, self.warmup_steps
         return self.base_lr * w ** 0.5 * min(s ** -0.5, s * w ** -1.5)
 
+    def close(self):
+        """Unregister this step's device record from the library (the kernels of OTHER users of the library -- the drop-in
+        modules with dropout on -- would otherwise keep reading a pointer that goes back to the allocator with this
+        object).  Called by __del__; idempotent."""
+        if not self._closed:
+            self._closed = True
+            try:
+                with torch.cuda.device(self.dev):
+                    ops.set_step_params(None)
+            except Exception:  # interpreter shutdown: the library may be gone already
+                pass
+
+    def __del__(self):
+        self.close()
+
     # ---- the step body: only device-resident inputs (the bucket's static buffers, the 24-byte record) -> capturable
-    def _body(self, b: _Bucket, overlap: bool):
+    def _body(self, b: _Bucket, overlap: bool, on_ready=None):
         pack, cfg, inp = self.pack, self.cfg, b.inp
         pack.refresh()
         pack.zero_grad()
-        self.reducer.begin()
         draws = {k: inp[k] for k in _DRAW_KEYS if k in inp}
         feats, flens = bstep.frontend_fwd(inp["wav"], inp["lens"], self.mel, cfg, draws)
         # trainer.py:594-606: the loss is the batch-weighted mean over ranks and DDP averages the gradients: the summed
         # gradients are scaled by 1 / world inside the optimizer kernel
         out = bstep.train_step_from_feats(feats, flens, inp["text"], inp["tl"], pack.P, pack.W, pack.G, cfg,
                                           bstep.StepCtx(1000003 * (self.rank + 1), True), bn_buffers=self.bn,
-                                          on_ready=self.reducer.ready if (overlap and self.world > 1) else None)
+                                          on_ready=on_ready if on_ready is not None else
+                                          (self.reducer.ready if (overlap and self.world > 1) else None))
         pack.finalize_grads()
         b.res = torch.cat([out["loss"], out["loss_ctc"], out["loss_att"], out["acc"]])
 
@@ -115,13 +144,46 @@ class TrainStep:
         b = b if b is not None else self.last
         ops.set_step_params(self.sp_dev)
         torch.cuda.synchronize()
-        g = torch.cuda.CUDAGraph()
         self.graph_has_tail = self.world == 1
-        with torch.cuda.graph(g):
-            self._body(b, overlap=False)
-            if self.graph_has_tail:
-                self._tail()
-        b.graph = g
+        cuts = self._cut_stages()
+        if not cuts:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._body(b, overlap=False)
+                if self.graph_has_tail:
+                    self._tail()
+            b.graph = [(g, None)]
+            return
+        # a chain of graphs sharing one memory pool, replayed in capture order; a cut sits where step.py reports a
+        # gradient bucket final (on_ready), so the host can issue that bucket's all-reduce between two replays
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        chain, cur = [], [torch.cuda.CUDAGraph()]
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+
+        def cut(stage):
+            if stage in cuts:
+                cur[0].capture_end()
+                chain.append((cur[0], stage))
+                cur[0] = torch.cuda.CUDAGraph()
+                cur[0].capture_begin(pool=chain[0][0].pool())
+
+        with torch.cuda.stream(side):
+            cur[0].capture_begin()
+            self._body(b, overlap=False, on_ready=cut)
+            cur[0].capture_end()
+            chain.append((cur[0], None))
+        torch.cuda.current_stream().wait_stream(side)
+        b.graph = chain
+
+    def _cut_stages(self):
+        """Stages after which the captured step is cut (dp_mode "graph", more than one rank): every bucket of the reducer's
+        plan except the last one, which is reduced after the last segment anyway."""
+        if self.world == 1 or self.dp_mode != "graph":
+            return set(getattr(self, "force_cuts", ()))  # tests cut a single-GPU step to check the chain replays identically
+        return {s for s, _, _ in self.reducer.stages if s != "front"}
 
     def drop_graphs(self):
         """Back to eager launches (profiling passes bracket every kernel with events)."""
@@ -149,13 +211,22 @@ class TrainStep:
         ops.set_step_params(self.sp_dev)  # host-side registration, handed to the kernels as an argument (baked into a graph
         self.step_no += 1                 # at capture): re-registered per call so that several TrainSteps can coexist
         slot = self.step_no % 64
+        if self.sp_events[slot] is not None:
+            self.sp_events[slot].synchronize()  # the host never runs more than 64 steps ahead of the copies out of the ring
         self.sp_np[slot] = (self.step_no * 0x9E3779B97F4A7C15 % (1 << 64), self.lr(), 1 - 0.9 ** self.step_no,
                             1 - 0.999 ** self.step_no, 0.0)
         self.sp_dev.copy_(self.sp_host[slot], non_blocking=True)
+        if self.sp_events[slot] is None:
+            self.sp_events[slot] = torch.cuda.Event()
+        self.sp_events[slot].record()
         for k, v in batch.items():
             b.inp[k].copy_(v, non_blocking=True)
+        self.reducer.begin()
         if b.graph is not None:
-            b.graph.replay()
+            for g, stage in b.graph:
+                g.replay()
+                if stage is not None:
+                    self.reducer.ready(stage)  # this bucket's all-reduce runs under the next segment
             if not self.graph_has_tail:
                 self._tail()
             res = b.res

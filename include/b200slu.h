@@ -215,6 +215,11 @@ int b200slu_col2im3x3s2_relu(const void* dcol, const void* h1, int B, int T1, in
 /* ---- K6: CTC (espnet2/asr/ctc.py:52-63,82-95; lattice espnet/nets/pytorch_backend/gtn_ctc.py:26-36) -----
  * logits f32 [B,T,ldv] (log_softmax fused); labels int32 [B,Lmax]; all lengths int32 on the device. */
 long long b200slu_ctc_workspace_size(int B, int T, int Lmax);
+/* The blank-extended lattice exactly as the device code builds it (bit-exact test against gtn_ctc.py:26-36):
+ * ext_out int32 [B, 2*Lmax+1] = label of state s (-1 past the utterance's 2L+1 states), skip_out u8 = 1 iff the arc
+ * s-2 -> s exists. */
+int b200slu_ctc_lattice_states(const int* labels, int Lmax, const int* label_lens, int B, int blank, int* ext_out,
+                               unsigned char* skip_out, void* stream);
 int b200slu_ctc_fwd(const float* logits, long long ldv, int B, int T, int V, const int* hlens, const int* labels, int Lmax,
                     const int* label_lens, int blank, void* workspace, float* loss_per_utt, float* loss_sum, void* stream);
 int b200slu_ctc_bwd(const float* logits, long long ldv, int B, int T, int V, const int* hlens, const int* labels, int Lmax,

@@ -24,12 +24,16 @@ def _free_port():
     return p
 
 
-def _problem():
-    from test_step_gpu import make_sd
+def _problem(cond=False):
+    from espnet_slurp_b200.testing import make_sd
     from oracle import model as om
-    enc, dec, V = om.EncCfg(80, 16, 2, 32, 2, 7, "latest"), om.DecCfg(20, 16, 2, 32, 1), 20
+    V = 24 if cond else 20  # the conditioning Linear wants V % 8 == 0
+    enc, dec = om.EncCfg(80, 16, 2, 32, 2, 7, "latest"), om.DecCfg(V, 16, 2, 32, 1)
     sd = make_sd(enc, dec, V, seed=2)
     g = torch.Generator().manual_seed(4)
+    if cond:
+        sd["encoder.conditioning_layer.weight"] = torch.randn(16, V, generator=g) / V ** 0.5
+        sd["encoder.conditioning_layer.bias"] = torch.randn(16, generator=g) * 0.1
     B, Tin = 5, 64
     feats = torch.randn(B, Tin, 80, generator=g)
     flens = torch.tensor([64, 60, 55, 48, 40])
@@ -37,10 +41,13 @@ def _problem():
     text = torch.full((B, 5), -1, dtype=torch.long)
     for b in range(B):
         text[b, : tl[b]] = torch.randint(1, V - 1, (int(tl[b]),), generator=g)
-    return om.ModelCfg(enc=enc, dec=dec, vocab=V), sd, feats, flens, text, tl
+    ocfg = om.ModelCfg(enc=enc, dec=dec, vocab=V)
+    if cond:
+        ocfg.interctc_weight, ocfg.interctc_layer_idx, ocfg.interctc_use_conditioning = 0.4, (1,), True
+    return ocfg, sd, feats, flens, text, tl
 
 
-def _worker(rank, world, port, overlap, out_dir):
+def _worker(rank, world, port, overlap, out_dir, cond=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -50,14 +57,20 @@ def _worker(rank, world, port, overlap, out_dir):
         from espnet_slurp_b200 import step as bstep
         bstep.K = emul_ops
         emul_ops.exact = True
-        ocfg, sd, feats, flens, text, tl = _problem()
-        cfg = bstep.ModelCfg(enc=bstep.EncCfg(80, 16, 2, 32, 2, 7, "latest", 0.0, 0.0, 0.0),
-                             dec=bstep.DecCfg(20, 16, 2, 32, 1, 0.0, 0.0, 0.0, 0.0), vocab=20)
+        ocfg, sd, feats, flens, text, tl = _problem(cond)
+        V = ocfg.vocab
+        cfg = bstep.ModelCfg(enc=bstep.EncCfg(80, 16, 2, 32, 2, 7, "latest", 0.0, 0.0, 0.0,
+                                              interctc_layer_idx=(1,) if cond else (), interctc_use_conditioning=cond, vocab=V),
+                             dec=bstep.DecCfg(V, 16, 2, 32, 1, 0.0, 0.0, 0.0, 0.0), vocab=V,
+                             interctc_weight=0.4 if cond else 0.0)
         idx = bdist.shard_batch(list(range(feats.shape[0])), rank, world)
         pack = bparams.ParamPack(sd, lowp=torch.float32)
         pack.refresh()
         pack.zero_grad()
-        red = bdist.GradReducer(pack, world, bucket_bytes=4096, overlap=overlap)
+        # self-conditioning: the encoder backward still adds to ctc.ctc_lo's gradient after "heads" is reported final, so
+        # those parameters must ride in the last bucket (what trainer.TrainStep asks for) -- an all-reduce issued at "heads"
+        # would race with / miss those contributions
+        red = bdist.GradReducer(pack, world, bucket_bytes=4096, overlap=overlap, late_prefixes=("ctc.",) if cond else ())
         stages = [s for s, _, _ in red.stages]
         assert stages[0] == "heads" and stages[-1] == "front" and any(s.startswith("enc") for s in stages)
         cover = torch.zeros(pack.total)
@@ -83,13 +96,13 @@ def _worker(rank, world, port, overlap, out_dir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("overlap", [True, False])
-def test_two_rank_gradients_follow_reference_ddp(tmp_path, overlap):
+@pytest.mark.parametrize("overlap,cond", [(True, False), (False, False), (True, True)])
+def test_two_rank_gradients_follow_reference_ddp(tmp_path, overlap, cond):
     from oracle import model as om
     world, port = 2, _free_port()
-    mp.spawn(_worker, args=(world, port, overlap, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, overlap, str(tmp_path), cond), nprocs=world, join=True)
     r0, r1 = np.load(tmp_path / "rank0.npz"), np.load(tmp_path / "rank1.npz")
-    ocfg, sd, feats, flens, text, tl = _problem()
+    ocfg, sd, feats, flens, text, tl = _problem(cond)
     # reference semantics: every rank runs its shard (BatchNorm over the shard only), loss weights B_r * world / sum B,
     # DDP averages the gradients
     want = {k: np.zeros(v.shape, np.float32) for k, v in sd.items()}

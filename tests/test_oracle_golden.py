@@ -236,3 +236,27 @@ def test_self_conditioned_intermediate_ctc_step():
             got = torch.zeros_like(sd[k[5:]]) if got is None else got
             worst = max(worst, float(np.abs(got.numpy() - v).max() / max(np.abs(v).max(), 1e-3)))
     assert worst < 2e-3, worst
+
+
+def test_library_ops_switch_agrees_with_the_spelled_out_arithmetic(monkeypatch):
+    """oracle.LIBRARY_OPS = True routes LayerNorm / Linear / depthwise conv / BatchNorm / GLU / STFT / bicubic resize through
+    the torch library ops the reference's modules call (bench.py's same-box eager-PyTorch leg); same loss and gradients."""
+    g = load("e2e_latest.npz")
+    sd0 = {k[3:]: torch.tensor(v) for k, v in g.items() if k.startswith("sd/") and v.dtype == np.float32}
+    cfg = om.ModelCfg(enc=om.EncCfg(80, 16, 2, 32, 2, 7, "latest"), dec=om.DecCfg(20, 16, 2, 32, 2), vocab=20)
+    mel = torch.from_numpy(om.slaney_mel_matrix())
+    wav, lens = torch.tensor(g["wav"]), torch.tensor(g["lens"])
+    draws = {"center": torch.tensor([20, 30, -1][: wav.shape[0]]), "warped": torch.tensor([22, 27, 0][: wav.shape[0]]),
+             "f_pos": torch.tensor([[3, 40]] * wav.shape[0]), "f_len": torch.tensor([[5, 9]] * wav.shape[0]),
+             "t_pos": torch.tensor([[2, 30]] * wav.shape[0]), "t_len": torch.tensor([[4, 7]] * wav.shape[0])}
+    res = []
+    for flag in (False, True):
+        monkeypatch.setattr(om, "LIBRARY_OPS", flag)
+        sd = {k: v.clone().requires_grad_(True) for k, v in sd0.items()}
+        loss, _ = om.asr_forward(wav, lens, torch.tensor(g["text"]), torch.tensor(g["text_lens"]), sd, cfg, mel, draws=draws)
+        loss.backward()
+        res.append((loss.item(), {k: v.grad.clone() for k, v in sd.items() if v.grad is not None}))
+    np.testing.assert_allclose(res[0][0], res[1][0], rtol=2e-5)
+    gmax = max(v.abs().max().item() for v in res[0][1].values())
+    for k, v in res[0][1].items():  # (gradients that are mathematically zero -- BatchNorm cancels the depthwise bias -- are noise)
+        assert (res[1][1][k] - v).abs().max() <= 2e-4 * max(v.abs().max().item(), 1e-3 * gmax), k

@@ -112,3 +112,52 @@ def test_optimizer_follows_reference_recipe():
     assert float(ug.abs().max()) <= 1.05 * float(ur.abs().max()), (float(ug.abs().max()), float(ur.abs().max()))
     cos = float(torch.dot(ur, ug) / (ur.norm() * ug.norm()))
     assert cos > 0.9, cos
+
+
+def test_chained_graph_segments_replay_like_one_graph():
+    """dp_mode "graph" with more than one rank cuts the captured step into a chain of graphs (shared memory pool) so that
+    gradient buckets can be all-reduced between replays.  On one GPU the same chain (cuts forced after the heads and after
+    encoder block 1) must reproduce the eager step: same losses, same parameters after several optimizer steps."""
+    from espnet_slurp_b200.trainer import TrainStep
+    cfg, ocfg = _cfg()
+    sd = make_sd(ocfg.enc, ocfg.dec, 30, seed=5)
+    eager = TrainStep(cfg, sd, use_graph=False, lr=2e-3, warmup_steps=4)
+    chain = TrainStep(cfg, sd, use_graph=True, lr=2e-3, warmup_steps=4)
+    chain.force_cuts = ("heads", "enc1")
+    batches = [_batch(3, 8000, 5, seed=20 + i) for i in range(6)]
+    for i, b in enumerate(batches):
+        le = eager({k: v.cuda() for k, v in b.items()}).clone()
+        lc = chain({k: v.cuda() for k, v in b.items()}).clone()
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(lc.cpu().numpy(), le.cpu().numpy(), rtol=1e-2, atol=1e-4, err_msg=f"step {i}")
+    bk = next(iter(chain.buckets.values()))
+    assert [st for _, st in bk.graph] == ["heads", "enc1", None]  # three segments, replayed in capture order
+    pe, pc = eager.state_dict(), chain.state_dict()
+    ue, uc = [], []
+    for k in pe:
+        if k.endswith(("linear_k.bias", "depthwise_conv.bias")) or "running_" in k or "num_batches" in k:
+            continue
+        ue.append((pe[k].cpu().float() - sd[k]).flatten())
+        uc.append((pc[k].cpu().float() - sd[k]).flatten())
+    ue, uc = torch.cat(ue), torch.cat(uc)
+    cos = float(torch.dot(ue, uc) / (ue.norm() * uc.norm()))
+    assert cos > 0.97 and abs(float(uc.norm() / ue.norm()) - 1) < 0.05, (cos, float(uc.norm() / ue.norm()))
+
+
+def test_close_unregisters_the_device_record():
+    """A TrainStep registers its 24-byte device record with the library; close() / __del__ must unregister it so that later
+    users of the library (drop-in modules with dropout on) never read a pointer that went back to the allocator."""
+    from espnet_slurp_b200 import ops
+    from espnet_slurp_b200.trainer import TrainStep
+    import dropout_ref
+    cfg, ocfg = _cfg()
+    ts = TrainStep(cfg, make_sd(ocfg.enc, ocfg.dec, 30, seed=5), use_graph=False)
+    ts.sp_np[0] = (12345, 0.0, 0.0, 0.0, 0.0)
+    ts.sp_dev.copy_(ts.sp_host[0])
+    got = ops.dropout_mask((0.1, 7, 3), 4096).cpu().numpy()
+    assert np.array_equal(got, dropout_ref.keep_mask(0.1, 7, 3, 4096, dev_seed=12345))
+    del ts
+    import gc
+    gc.collect()
+    got = ops.dropout_mask((0.1, 7, 3), 4096).cpu().numpy()
+    assert np.array_equal(got, dropout_ref.keep_mask(0.1, 7, 3, 4096))
