@@ -535,6 +535,287 @@ relattn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Backward, keys <= 192: ONE kernel per layer for everything between the gradient of the context and the gradients
+// of q_u / k / v (reference: autograd through attention.py:78-95 and the two matmuls of :297-302 / :111-113):
+//
+//   dPd = dO . V^T                    tcgen05, 128 queries x TKP keys into tensor memory           (never leaves the SM)
+//   dS  = p (m dPd - delta) scale     delta_i = <dO_i, O_i> (= sum_j dP_ij p_ij, the flash-attention identity), m = the
+//                                     element's dropout multiplier regenerated from (seed, site, index)
+//   dQ_u = dS . K     dK += dS^T . Q_u     dV += (m p)^T . dO          tcgen05 out of shared memory
+//
+// p (bf16, what the forward saved) arrives by TMA straight into the shared-memory tile that becomes the A operand of
+// the dV contraction: the threads turn it into dropout(p) IN PLACE and write dS into a second tile; both tiles are
+// SWIZZLE_128B [128 query rows x 64 keys] blocks, read K-major (A = dS for dQ_u) and MN-major (A = dS^T / pd^T for
+// dK / dV) through the UMMA descriptors -- no transposed copy exists anywhere.  dP, dS, dropout(p) and (rel-pos modes)
+// d(matrix_bd) never touch HBM.  One CTA owns one (utterance, head) at a time and walks its query tiles, so dK / dV
+// accumulate in tensor memory across the tiles; thread = TMEM lane = query row (or key row in the dK / dV epilogue).
+// Rel-pos (latest): dS is also what d(matrix_bd) is made of -- the un-shift and the two position contractions
+// (dQ_v = d(bd) . P, dP = d(bd)^T . Q_v) are stage 2; until then the kernel hands dS out (bf16, shifted layout).
+constexpr int BWD_DK_COL = 192;   // dK: two key tiles x 64 columns
+constexpr int BWD_DV_COL = 320;   // dV: two key tiles x 64 columns
+constexpr int BLK = QT * 128;     // bytes of one [128 rows x 64 bf16] swizzled block
+
+struct AttnBwdArgs {
+  int B, H, Tq, Tk, TKP;
+  float scale;
+  const bf16* ctx;  // forward output O, merged heads [B*Tq, ldctx]
+  long long ldctx;
+  bf16 *dq, *dk, *dv, *dac;
+  long long lddq, lddkv, ld_p;
+  uint32_t off_pd, off_ds, off_k, off_v, off_do, off_qu, off_bar;
+  B2Dropout drop;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_constant__ CUtensorMap map_qu,
+                   const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
+                   const __grid_constant__ CUtensorMap map_p, const AttnBwdArgs a, int num_units) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  if (sbase & 1023u) __trap();
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t s_pd = sbase + a.off_pd, s_ds = sbase + a.off_ds, s_k = sbase + a.off_k, s_v = sbase + a.off_v,
+                 s_do = sbase + a.off_do, s_qu = sbase + a.off_qu;
+  const uint32_t bar_kv = sbase + a.off_bar, bar_q = bar_kv + 8, bar_s = bar_kv + 16, bar_c = bar_kv + 24;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + a.off_bar + 32);
+  float* rowstat = reinterpret_cast<float*>(smem + a.off_bar + 64);  // [2 halves][128 rows] partial delta
+  const int TKP = a.TKP, nblk = (TKP + 63) / 64, nkt = (TKP + QT - 1) / QT;
+  const int nqt = (a.Tq + QT - 1) / QT;
+
+  b2_pdl_launch_dependents();
+  if (tid == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_do) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qu) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_p) : "memory");
+    for (int i = 0; i < 4; ++i) mbar_init(bar_kv + i * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  b2_pdl_wait();
+  B2DropKey dk = {0ull, 0u, 1.f};
+  const bool dropping = a.drop.p > 0.f;
+  if (dropping) dk = dropout_key(a.drop);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int q = warp & 3, hs = warp >> 2;
+  const int r = q * 32 + lane;
+  const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
+  const int nch = TKP / CH, n0 = (nch + 1) / 2;
+  const int cbeg = hs ? n0 : 0, nmine = hs ? nch - n0 : n0;
+  uint32_t n_kv = 0, n_q = 0;  // completed load / MMA rounds: barrier parities (the same in every thread)
+
+  for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+    const int h = unit % a.H, b = unit / a.H;
+    if (tid == 0) {
+      mbar_expect_tx(bar_kv, (uint32_t)(2 * TKP * 128));
+      tma_load_3d(s_k, &map_k, bar_kv, h * DK, 0, b);
+      tma_load_3d(s_v, &map_v, bar_kv, h * DK, 0, b);
+    }
+    for (int qt = 0; qt < nqt; ++qt) {
+      const int i0 = qt * QT, i = i0 + r;
+      const bool row_ok = i < a.Tq;
+      const uint32_t par = n_q & 1u;
+      if (tid == 0) {
+        mbar_expect_tx(bar_q, (uint32_t)(2 * BLK + nblk * BLK));
+        tma_load_3d(s_do, &map_do, bar_q, h * DK, i0, b);
+        tma_load_3d(s_qu, &map_qu, bar_q, h * DK, i0, b);
+        for (int kb = 0; kb < nblk; ++kb) tma_load_3d(s_pd + kb * BLK, &map_p, bar_q, kb * 64, i0, h * a.B + b);
+      }
+      // this thread's half (32 columns) of its row of the forward output, for delta
+      uint4 cx[4];
+      if (row_ok) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.ctx + ((long long)b * a.Tq + i) * a.ldctx + h * DK + hs * 32);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) cx[t] = __ldg(src + t);
+      } else {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) cx[t] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      if (tid == 0) {
+        if (qt == 0) mbar_wait(bar_kv, n_kv & 1u);
+        mbar_wait(bar_q, par);
+        tcgen05_fence_after();
+        const uint32_t id_s = make_idesc(TKP, 0, 0, QT);
+#pragma unroll
+        for (int kk = 0; kk < DK / 16; ++kk)
+          umma_bf16(tmem_base, make_smem_desc(s_do + kk * 32, 16, 1024), make_smem_desc(s_v + kk * 32, 16, 1024), id_s, kk != 0);
+        umma_commit(bar_s);
+      }
+      mbar_wait(bar_q, par);
+      float dpart = 0.f;
+      {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const uint32_t chunk = (uint32_t)(hs * 4 + t);
+          float d0, d1, d2, d3;
+          lds128(s_do + (uint32_t)r * 128u + ((chunk ^ (uint32_t)(r & 7)) << 4), d0, d1, d2, d3);
+          const uint32_t dw[4] = {__float_as_uint(d0), __float_as_uint(d1), __float_as_uint(d2), __float_as_uint(d3)};
+          const uint32_t cw[4] = {cx[t].x, cx[t].y, cx[t].z, cx[t].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 x = unpack_bf16x2(dw[e]), y = unpack_bf16x2(cw[e]);
+            dpart = fmaf(x.x, y.x, dpart);
+            dpart = fmaf(x.y, y.y, dpart);
+          }
+        }
+      }
+      rowstat[hs * QT + r] = dpart;
+      group_sync(0);
+      const float delta = rowstat[r] + rowstat[QT + r];
+      mbar_wait(bar_s, par);
+      tcgen05_fence_after();
+
+      // ------------------------------------------------------------ dS and dropout(p), 16 keys at a time
+      const long long rg = ((long long)h * a.B + b) * a.Tq + i;
+      bf16* dacrow = a.dac != nullptr ? a.dac + rg * a.ld_p : nullptr;
+      const float sc = a.scale;
+      uint32_t ta[16], tb[16];
+      if (nmine > 0) tmem_ld16(tlane + cbeg * CH, ta);
+#pragma unroll 1
+      for (int c = 0; c < nmine; c += 2) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int cc = c + half;
+          if (cc < nmine) {
+            const int j0 = (cbeg + cc) * CH;
+            tmem_ld_wait();
+            if (cc + 1 < nmine) tmem_ld16(tlane + j0 + CH, half ? ta : tb);
+            const uint32_t(&dp)[16] = half ? tb : ta;
+            const uint32_t blk = (uint32_t)(j0 >> 6) * BLK + (uint32_t)r * 128u;
+            const uint32_t ch0 = (uint32_t)((j0 & 63) >> 3);
+            const uint32_t ad0 = blk + (((ch0) ^ (uint32_t)(r & 7)) << 4), ad1 = blk + (((ch0 + 1u) ^ (uint32_t)(r & 7)) << 4);
+            float p0, p1, p2, p3, p4, p5, p6, p7;
+            lds128(s_pd + ad0, p0, p1, p2, p3);
+            lds128(s_pd + ad1, p4, p5, p6, p7);
+            const uint32_t pw[8] = {__float_as_uint(p0), __float_as_uint(p1), __float_as_uint(p2), __float_as_uint(p3),
+                                    __float_as_uint(p4), __float_as_uint(p5), __float_as_uint(p6), __float_as_uint(p7)};
+            float mul[16];
+            if (dropping) {
+#pragma unroll
+              for (int g = 0; g < 2; ++g) {
+                float m8[8];
+                dropout_mul8(dk, (unsigned long long)(rg * a.ld_p + j0 + g * 8) >> 3, dk.inv, m8);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) mul[g * 8 + e] = m8[e];
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 16; ++e) mul[e] = 1.f;
+            }
+            uint32_t pdw[8], dsw[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float2 pv = unpack_bf16x2(pw[e]);
+              const float g0 = __uint_as_float(dp[2 * e]), g1 = __uint_as_float(dp[2 * e + 1]);
+              const float m0 = mul[2 * e], m1 = mul[2 * e + 1];
+              pdw[e] = pack_bf16x2(pv.x * m0, pv.y * m1);
+              // p == 0 (masked key, padded row) gives exactly 0 whatever the accumulator holds there
+              const float s0 = pv.x != 0.f ? pv.x * (fmaf(g0, m0, -delta)) * sc : 0.f;
+              const float s1 = pv.y != 0.f ? pv.y * (fmaf(g1, m1, -delta)) * sc : 0.f;
+              dsw[e] = pack_bf16x2(s0, s1);
+            }
+            sts128(s_pd + ad0, pdw[0], pdw[1], pdw[2], pdw[3]);
+            sts128(s_pd + ad1, pdw[4], pdw[5], pdw[6], pdw[7]);
+            sts128(s_ds + ad0, dsw[0], dsw[1], dsw[2], dsw[3]);
+            sts128(s_ds + ad1, dsw[4], dsw[5], dsw[6], dsw[7]);
+            if (dacrow != nullptr && row_ok && j0 < a.ld_p) {
+              if (j0 + CH <= a.ld_p && (a.ld_p & 15) == 0) {
+                stg256(dacrow + j0, dsw);
+              } else {
+                *reinterpret_cast<uint4*>(dacrow + j0) = make_uint4(dsw[0], dsw[1], dsw[2], dsw[3]);
+                if (j0 + CH <= a.ld_p) *reinterpret_cast<uint4*>(dacrow + j0 + 8) = make_uint4(dsw[4], dsw[5], dsw[6], dsw[7]);
+              }
+            }
+          }
+        }
+      }
+      fence_async_smem();
+      tcgen05_fence_before();
+      group_sync(0);
+
+      // ------------------------------------------------------------ dQ_u, dK, dV
+      if (tid == 0) {
+        tcgen05_fence_after();
+        const uint32_t id_q = make_idesc(DK, 0, 1, QT);  // A = dS (K-major), B = K rows as MN-major
+        for (int ks = 0; ks < TKP / 16; ++ks)
+          umma_bf16(tmem_base, make_smem_desc(s_ds + (uint32_t)(ks >> 2) * BLK + (ks & 3) * 32, 16, 1024),
+                    make_smem_desc(s_k + ks * 2048, 64 * DK * 2, 1024), id_q, ks != 0);
+        const uint32_t id_t = make_idesc(DK, 1, 1, QT);  // A = dS^T / pd^T (MN-major), B = Q_u / dO rows (MN-major)
+        for (int m = 0; m < nkt; ++m) {
+#pragma unroll
+          for (int kk = 0; kk < QT / 16; ++kk) {
+            const uint32_t acc = (qt != 0 || kk != 0) ? 1u : 0u;
+            umma_bf16(tmem_base + BWD_DK_COL + m * DK, make_smem_desc(s_ds + (uint32_t)m * 2 * BLK + kk * 2048, BLK, 1024),
+                      make_smem_desc(s_qu + kk * 2048, 64 * DK * 2, 1024), id_t, acc);
+            umma_bf16(tmem_base + BWD_DV_COL + m * DK, make_smem_desc(s_pd + (uint32_t)m * 2 * BLK + kk * 2048, BLK, 1024),
+                      make_smem_desc(s_do + kk * 2048, 64 * DK * 2, 1024), id_t, acc);
+          }
+        }
+        umma_commit(bar_c);
+      }
+      mbar_wait(bar_c, par);
+      tcgen05_fence_after();
+      {
+        uint32_t o[32];
+        tmem_ld32(tlane + hs * 32, o);
+        tmem_ld_wait();
+        if (row_ok) {
+          bf16* dst = a.dq + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(o[g * 8 + e]);
+            store8_bf16(dst + g * 8, v);
+          }
+        }
+      }
+      if (qt == nqt - 1) {
+        for (int m = 0; m < nkt; ++m) {
+          const int j = m * QT + r;
+          uint32_t ok_[32], ov_[32];
+          tmem_ld32(tlane + BWD_DK_COL + m * DK + hs * 32, ok_);
+          tmem_ld32(tlane + BWD_DV_COL + m * DK + hs * 32, ov_);
+          tmem_ld_wait();
+          if (j < a.Tk) {
+            const long long row = ((long long)b * a.Tk + j) * a.lddkv + h * DK + hs * 32;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              float v[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(ok_[g * 8 + e]);
+              store8_bf16(a.dk + row + g * 8, v);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(ov_[g * 8 + e]);
+              store8_bf16(a.dv + row + g * 8, v);
+            }
+          }
+        }
+      }
+      ++n_q;
+      tcgen05_fence_before();
+      fence_async_smem();  // this tile's generic writes to the p / dS tiles are ordered before the next TMA loads into them
+      group_sync(0);
+    }
+    ++n_kv;
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
 // ----------------------------------------------------------------------------- host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -681,5 +962,73 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
             "pass2 %.0f, pass3 %.0f, PV MMA %.0f, epilogue %.0f\n", Tq, Tk, (int)rel, smem, a.tmem_cols, n, acc[0] / n, acc[1] / n, acc[2] / n,
             acc[3] / n, acc[4] / n, acc[5] / n, acc[6] / n);
   }
+  return 0;
+}
+
+extern "C" int b200slu_relattn_bwd_supported(int Tq, int Tk, int dk, int relpos_mode) {
+  if (dk != DK || Tq < 1 || Tk < 1 || Tk > MAX_TK) return 0;
+  if (relpos_mode == B200SLU_RELPOS_LATEST) return Tq == Tk;
+  return relpos_mode == B200SLU_RELPOS_NONE;
+}
+
+extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
+                                   long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H,
+                                   int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
+                                   void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
+                                   unsigned int site, void* stream) {
+  B2_CHECK_ARG(B > 0 && H > 0, "relattn_bwd: empty problem");
+  B2_CHECK_ARG(b200slu_relattn_bwd_supported(Tq, Tk, DK, relpos_mode),
+               "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
+               Tq, Tk, relpos_mode);
+  B2_CHECK_ARG(d_ctx && q_u && k && v && p && ctx && dq_u && dk_out && dv_out, "relattn_bwd: null operand");
+  B2_CHECK_ARG(lddo % 8 == 0 && ldq % 8 == 0 && ldkv % 8 == 0 && ldctx % 8 == 0 && lddq % 8 == 0 && lddkv % 8 == 0 && ld_p % 8 == 0 &&
+                   ld_p >= Tk,
+               "relattn_bwd: row strides must be multiples of 8 elements, ld_p >= Tk");
+  B2_CHECK_ARG(((uintptr_t)d_ctx % 16) == 0 && ((uintptr_t)q_u % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 &&
+                   ((uintptr_t)p % 16) == 0 && ((uintptr_t)ctx % 16) == 0 && ((uintptr_t)dq_u % 16) == 0 &&
+                   ((uintptr_t)dk_out % 16) == 0 && ((uintptr_t)dv_out % 16) == 0 && ((uintptr_t)d_ac % 32) == 0,
+               "relattn_bwd: operands must be 16-byte aligned (d_ac: 32)");
+  cudaStream_t st = (cudaStream_t)stream;
+  AttnBwdArgs a{};
+  a.B = B; a.H = H; a.Tq = Tq; a.Tk = Tk;
+  a.TKP = (Tk + 15) / 16 * 16;
+  a.scale = scale;
+  a.ctx = (const bf16*)ctx; a.ldctx = ldctx;
+  a.dq = (bf16*)dq_u; a.dk = (bf16*)dk_out; a.dv = (bf16*)dv_out; a.dac = (bf16*)d_ac;
+  a.lddq = lddq; a.lddkv = lddkv; a.ld_p = ld_p;
+  // the two A-operand tiles first: an M = 128 contraction over the second key tile reads two 64-key blocks, of which only
+  // the first may exist (keys <= 192): the bytes behind it belong to the next region (never faulting, never stored)
+  const uint32_t nblk = (uint32_t)(a.TKP + 63) / 64;
+  a.off_pd = 0;
+  a.off_ds = a.off_pd + nblk * BLK;
+  a.off_k = a.off_ds + nblk * BLK;
+  a.off_v = a.off_k + (uint32_t)(a.TKP * 128 + 1023) / 1024 * 1024;
+  a.off_do = a.off_v + (uint32_t)(a.TKP * 128 + 1023) / 1024 * 1024;
+  a.off_qu = a.off_do + BLK;
+  a.off_bar = a.off_qu + BLK;
+  a.drop = b2_make_drop(drop_p, seed, site);
+  size_t smem = (size_t)a.off_bar + 64 + 2 * QT * sizeof(float);
+  const size_t reach = (size_t)a.off_ds + ((size_t)(a.TKP + QT - 1) / QT) * 2 * BLK;  // what the widest MN-major read touches
+  if (smem < reach) smem = reach;
+  B2_CHECK_ARG(smem <= 232448, "relattn_bwd: shared memory %zu", smem);
+
+  CUtensorMap mdo, mqu, mk, mv, mp;
+  const int d = H * DK;
+  B2_TRY(make_map3(&mdo, d_ctx, d, Tq, lddo, B, (long long)Tq * lddo, QT));
+  B2_TRY(make_map3(&mqu, q_u, d, Tq, ldq, B, (long long)Tq * ldq, QT));
+  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  B2_TRY(make_map3(&mp, p, ld_p, Tq, ld_p, (long long)H * B, (long long)Tq * ld_p, QT));
+  static unsigned long long configured = 0;  // per device
+  if (!b2_device_done(configured)) {
+    B2_CUDA(cudaFuncSetAttribute(relattn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    b2_device_mark(configured);
+  }
+  const int units = B * H, sms = b2_num_sms();
+  B2_SCOPE(FAM_ATTN, st, (double)units * 8.0 * Tq * Tk * DK,
+           (double)units * (2.0 * DK * (3.0 * Tq + 2.0 * Tk) + 2.0 * Tq * Tk + 2.0 * DK * (Tq + 2.0 * Tk) +
+                            (d_ac ? 2.0 * Tq * Tk : 0.0)));
+  B2_CUDA(b2_launch(relattn_bwd_kernel, dim3((unsigned)(units < sms ? units : sms)), dim3(NTHREADS), smem, st, mdo, mqu, mk, mv, mp, a,
+                    units));
   return 0;
 }

@@ -353,6 +353,28 @@ int check(const SmArgs& a) {
   return 0;
 }
 
+// d(matrix_bd) (un-shifted layout) from d(scores) (shifted layout): the rel_shift scatter alone (latest mode), for
+// callers that already hold d(scores) -- dbd[i, n] = ds[i, n - src(i, 0).col] inside the band, 0 outside.
+__global__ void __launch_bounds__(256) rel_unshift_kernel(const bf16* __restrict__ ds, long long ld_p, long long rows, int T,
+                                                          bf16* __restrict__ dbd, long long ld_bd) {
+  const int gpr = (int)(ld_bd >> 3);
+  const long long total = rows * gpr;
+  for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (long long)gridDim.x * blockDim.x) {
+    const long long r = w / gpr;
+    const int g = (int)(w - r * gpr);
+    const int i = (int)(r % T);
+    const int lo = b2_rel_shift_src(i, 0, T, B200SLU_RELPOS_LATEST).col;
+    const bf16* src = ds + r * ld_p;
+    float o[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int j = g * 8 + e - lo;
+      o[e] = (j >= 0 && j < T) ? __bfloat162float(src[j]) : 0.f;
+    }
+    store8_bf16(dbd + r * ld_bd + g * 8, o);
+  }
+}
+
 }  // namespace
 
 extern "C" int b200slu_softmax_fwd(const float* ac, long long ld_ac, const float* bd, long long ld_bd, const int* key_lens, int H,
@@ -431,6 +453,18 @@ extern "C" int b200slu_softmax_bwd(const float* dp_drop, const void* p, long lon
   else if (ld_p <= 1024) SM_B(4);
   else SM_B(8);
 #undef SM_B
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_rel_unshift(const void* d_scores, long long ld_p, int H, int B, int T, int relpos_mode, void* d_bd,
+                                   long long ld_bd, void* stream) {
+  B2_CHECK_ARG(relpos_mode == B200SLU_RELPOS_LATEST, "rel_unshift: latest mode only");
+  B2_CHECK_ARG(H > 0 && B > 0 && T > 0 && ld_p >= T && ld_bd >= 2 * T - 1 && ld_bd % 8 == 0, "rel_unshift: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long rows = (long long)H * B * T;
+  B2_SCOPE(FAM_ATTN, st, 0, (double)rows * (2.0 * T + 2.0 * ld_bd));
+  rel_unshift_kernel<<<b2_grid_for(rows * (ld_bd >> 3), 256, 8), 256, 0, st>>>((const bf16*)d_scores, ld_p, rows, T, (bf16*)d_bd, ld_bd);
   B2_LAUNCH_CHECK();
   return 0;
 }

@@ -279,6 +279,34 @@ def relattn_fwd(qu, qv, k, v, pos, key_lens, B: int, Tq: int, Tk: int, H: int, m
     return p, pd, ctx
 
 
+def relattn_bwd_supported(Tq: int, Tk: int, dk: int, mode: str) -> bool:
+    return bool(_lib.lib().b200slu_relattn_bwd_supported(Tq, Tk, dk, RELPOS[mode]))
+
+
+def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: str, scale: float, dq, dk, dv,
+                drop: Drop = None, want_dac: bool = False):
+    """One kernel for the backward of the attention core (autograd through attention.py:78-95, :297-302 / :111-113).
+    dctx, qu, ctx [B*Tq, H*64], k, v [B*Tk, H*64], p bf16 [H,B,Tq,round8(Tk)] (as saved by the forward); writes dq
+    [B*Tq, H*64], dk, dv [B*Tk, H*64] (views with their own row strides are fine).  want_dac: also return dS (bf16,
+    shifted layout [H,B,Tq,round8(Tk)]) for the rel-pos position terms."""
+    ld = p.shape[-1]
+    dac = torch.empty_like(p) if want_dac else None
+    dp, seed, site = _drop(drop)
+    assert k.stride(0) == v.stride(0) and dk.stride(0) == dv.stride(0)
+    check(_lib.lib().b200slu_relattn_bwd(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
+                                         ptr(ctx), ctx.stride(0), B, H, Tq, Tk, RELPOS[mode], scale, ptr(dq), dq.stride(0),
+                                         ptr(dk), ptr(dv), dk.stride(0), ptr(dac), dp, seed, site, stream_ptr()), "relattn_bwd")
+    return dac
+
+
+def rel_unshift(dac, T: int, mode: str, ld_bd: int):
+    """d(matrix_bd) (un-shifted, bf16 [H,B,T,ld_bd]) from d(scores) (shifted layout)."""
+    H, B, Tq, ld = dac.shape
+    dbd = torch.empty(H, B, Tq, ld_bd, device=dac.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_rel_unshift(ptr(dac), ld, H, B, T, RELPOS[mode], ptr(dbd), ld_bd, stream_ptr()), "rel_unshift")
+    return dbd
+
+
 # ---- conv module --------------------------------------------------------------------------------------------------
 def glu_dwconv_fwd(pw1, w, bias, B: int, T: int, K: int):
     Cc = pw1.shape[1] // 2

@@ -180,16 +180,19 @@ def relmha_fwd(x, pos16, klens, P, W, p: str, norm: str, cfg: EncCfg, B: int, T:
     Pn = pos16.shape[0]
     da, do = ctx.drop(cfg.att_dropout, a + ".att"), ctx.drop(cfg.dropout, a + ".out")
     scale = 1.0 / math.sqrt(d // H)
+    fb = False
     if K.relattn_supported(T, T, d // H, cfg.rel_pos_type):
-        # short utterances: scores, rel_shift, softmax, dropout and context in one tcgen05 kernel (scores never leave TMEM)
-        pr, pd, c = K.relattn_fwd(qu, qv, k, v, pp, klens, B, T, T, H, cfg.rel_pos_type, False, scale, drop=da)
+        # short utterances: scores, rel_shift, softmax, dropout and context in one tcgen05 kernel (scores never leave TMEM);
+        # the fused backward regenerates dropout(p) from p, so only p is saved
+        fb = ctx.training and K.relattn_bwd_supported(T, T, d // H, cfg.rel_pos_type)
+        pr, pd, c = K.relattn_fwd(qu, qv, k, v, pp, klens, B, T, T, H, cfg.rel_pos_type, False, scale, drop=da, want_pd=not fb)
     else:
         ac = K.attn_f1(qu, k, B, T, T, H)
         bd = K.attn_f1(qv, pp, B, T, Pn, H, y_bcast=True)
         pr, pd = K.softmax_fwd(ac, bd, klens, T, cfg.rel_pos_type, False, scale, drop=da)
         c = K.attn_f2(pd, v, B, T, T, H)
     y = K.gemm(c, W[a + ".linear_out.weight"], bias=P[a + ".linear_out.bias"], residual=x, drop=do, out_dtype=F32)
-    return y, (x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, K.round8(Pn))
+    return y, (x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, K.round8(Pn), fb)
 
 
 def relmha_head(saved, G, p: str):
@@ -197,7 +200,7 @@ def relmha_head(saved, G, p: str):
 
 
 def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: int, g=None, nxt=None):
-    x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, ld_bd = saved
+    x, ln, st, qkv, qu, qv, pp, pr, pd, c, da, do, scale, Pn, ld_bd, fb = saved
     d, H = cfg.d, cfg.heads
     a = p + ".self_attn"
     k, v = qkv[:, d:2 * d], qkv[:, 2 * d:]
@@ -205,11 +208,18 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
     K.gemm(g, c, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
-    dpd = K.attn_f1(dc, v, B, T, T, H)
-    K.attn_f3(pd, dc, B, T, T, H, out=dqkv[:, 2 * d:])
-    dac, dbd = K.softmax_bwd(dpd, pr, T, cfg.rel_pos_type, scale, ld_bd=ld_bd, drop=da)
-    dqu = K.attn_f2(dac, k, B, T, T, H)
-    K.attn_f3(dac, qu, B, T, T, H, out=dqkv[:, d:2 * d])
+    if fb:
+        # fused backward (keys <= 192): dP, dS and dropout(p) stay on the SM; dq_u, dk, dv come out of one kernel
+        dqu = torch.empty(B * T, d, device=x.device, dtype=dc.dtype)
+        dac = K.relattn_bwd(dc, qu, k, v, pr, c, B, T, T, H, cfg.rel_pos_type, scale, dqu, dqkv[:, d:2 * d], dqkv[:, 2 * d:],
+                            drop=da, want_dac=True)
+        dbd = K.rel_unshift(dac, T, cfg.rel_pos_type, ld_bd)
+    else:
+        dpd = K.attn_f1(dc, v, B, T, T, H)
+        K.attn_f3(pd, dc, B, T, T, H, out=dqkv[:, 2 * d:])
+        dac, dbd = K.softmax_bwd(dpd, pr, T, cfg.rel_pos_type, scale, ld_bd=ld_bd, drop=da)
+        dqu = K.attn_f2(dac, k, B, T, T, H)
+        K.attn_f3(dac, qu, B, T, T, H, out=dqkv[:, d:2 * d])
     dqv = K.attn_f2(dbd, pp, B, T, Pn, H, y_bcast=True)
     dpp = torch.zeros(Pn, d, device=x.device, dtype=F32)
     K.attn_f4(dbd, qv, B, T, Pn, H, dpp)
@@ -412,13 +422,15 @@ def _mha_fwd(xq16, kv_src16, q_w: str, kv_w: str, P, W, a: str, klens, B, Tq, Tk
         proj = (q, kv)
     da = ctx.drop(p_att, a + ".att")
     scale = 1.0 / math.sqrt(d // H)
+    fb = False
     if K.relattn_supported(Tq, Tk, d // H, "none"):
-        pr, pd, c = K.relattn_fwd(q, None, k, v, None, klens, B, Tq, Tk, H, "none", causal, scale, drop=da)
+        fb = ctx.training and K.relattn_bwd_supported(Tq, Tk, d // H, "none")
+        pr, pd, c = K.relattn_fwd(q, None, k, v, None, klens, B, Tq, Tk, H, "none", causal, scale, drop=da, want_pd=not fb)
     else:
         ac = K.attn_f1(q, k, B, Tq, Tk, H)
         pr, pd = K.softmax_fwd(ac, None, klens, Tk, "none", causal, scale, drop=da)
         c = K.attn_f2(pd, v, B, Tq, Tk, H)
-    return c, (proj, pr, pd, da, scale)
+    return c, (proj, pr, pd, da, scale, fb)
 
 
 def dec_layer_fwd(x, mem16, ylens, mlens, P, W, p: str, cfg: DecCfg, B: int, L: int, T: int, ctx: StepCtx):
@@ -448,16 +460,20 @@ def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, 
     a = p + ".src_attn"
     dx2, g = ffn_bwd(dy, sf, P, W, G, g, (1.0, do2, G[a + ".linear_out.bias"]))
     # ---- source attention
-    (q, kv), pr, pd, da, scale = ca
+    (q, kv), pr, pd, da, scale, fb = ca
     k, v = kv[:, :d], kv[:, d:]
     K.gemm(g, c2, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dkv = torch.empty_like(kv)
-    dpd = K.attn_f1(dc, v, B, L, T, H)
-    K.attn_f3(pd, dc, B, L, T, H, out=dkv[:, d:])
-    dac, _ = K.softmax_bwd(dpd, pr, T, "none", scale, drop=da)
-    dq = K.attn_f2(dac, k, B, L, T, H)
-    K.attn_f3(dac, q, B, L, T, H, out=dkv[:, :d])
+    if fb:
+        dq = torch.empty_like(q)
+        K.relattn_bwd(dc, q, k, v, pr, c2, B, L, T, H, "none", scale, dq, dkv[:, :d], dkv[:, d:], drop=da)
+    else:
+        dpd = K.attn_f1(dc, v, B, L, T, H)
+        K.attn_f3(pd, dc, B, L, T, H, out=dkv[:, d:])
+        dac, _ = K.softmax_bwd(dpd, pr, T, "none", scale, drop=da)
+        dq = K.attn_f2(dac, k, B, L, T, H)
+        K.attn_f3(dac, q, B, L, T, H, out=dkv[:, :d])
     K.colsum(dkv, G[a + ".linear_kv.bias"])
     K.gemm(dkv, mem16, trans=True, out=G[a + ".linear_kv.weight"], accumulate=True)
     K.gemm(dkv, W[a + ".linear_kv.weight"], trans_b=True, residual=dmem, out=dmem)
@@ -467,16 +483,19 @@ def dec_layer_bwd(dy, dmem, saved, mem16, P, W, G, p: str, cfg: DecCfg, B: int, 
     a = p + ".self_attn"
     dx1, g = _ln_bwd(dln2, x1, P, G, p + ".norm2", st2, dx2, (1.0, do1, G[a + ".linear_out.bias"]))
     # ---- self attention
-    (qkv,), pr, pd, da, scale = sa
+    (qkv,), pr, pd, da, scale, fb = sa
     q, k, v = qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:]
     K.gemm(g, c1, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
-    dpd = K.attn_f1(dc, v, B, L, L, H)
-    K.attn_f3(pd, dc, B, L, L, H, out=dqkv[:, 2 * d:])
-    dac, _ = K.softmax_bwd(dpd, pr, L, "none", scale, drop=da)
-    K.attn_f2(dac, k, B, L, L, H, out=dqkv[:, :d])
-    K.attn_f3(dac, q, B, L, L, H, out=dqkv[:, d:2 * d])
+    if fb:
+        K.relattn_bwd(dc, q, k, v, pr, c1, B, L, L, H, "none", scale, dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:], drop=da)
+    else:
+        dpd = K.attn_f1(dc, v, B, L, L, H)
+        K.attn_f3(pd, dc, B, L, L, H, out=dqkv[:, 2 * d:])
+        dac, _ = K.softmax_bwd(dpd, pr, L, "none", scale, drop=da)
+        K.attn_f2(dac, k, B, L, L, H, out=dqkv[:, :d])
+        K.attn_f3(dac, q, B, L, L, H, out=dqkv[:, d:2 * d])
     K.colsum(dqkv, G[a + ".linear_qkv.bias"])
     K.gemm(dqkv, ln1, trans=True, out=G[a + ".linear_qkv.weight"], accumulate=True)
     dln1 = K.gemm(dqkv, W[a + ".linear_qkv.weight"], trans_b=True)

@@ -157,6 +157,7 @@ class TrainStep:
         # a chain of graphs sharing one memory pool, replayed in capture order; a cut sits where step.py reports a
         # gradient bucket final (on_ready), so the host can issue that bucket's all-reduce between two replays
         import gc
+        self.graph_has_tail = False  # clip + Adam follow the last segment eagerly (after the last bucket's all-reduce)
         gc.collect()
         torch.cuda.empty_cache()
         chain, cur = [], [torch.cuda.CUDAGraph()]

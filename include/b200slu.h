@@ -185,6 +185,21 @@ int b200slu_relattn_fwd(const void* q_u, const void* q_v, long long ldq, const v
                         const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk, int relpos_mode,
                         int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx, long long ldctx, float drop_p,
                         unsigned long long seed, unsigned int site, void* stream);
+/* Backward of the same, keys <= 192 (b200slu_relattn_bwd_supported): autograd through attention.py:78-95 and the
+ * matmuls of :297-302 / :111-113 in ONE kernel -- dP = dO . v^T and dS = p (m dP - <dO, O>) scale stay on the SM
+ * (tensor memory / shared memory), dq_u = dS . k, dk = dS^T . q_u, dv = dropout(p)^T . dO are written as bf16 rows
+ * (utterance, frame) x head slices like their forward counterparts.  d_ctx = gradient of the merged-head context,
+ * p = the probabilities the forward saved, ctx = the forward's context output.  d_ac (optional, bf16 [H,B,Tq,ld_p]):
+ * dS in the shifted layout, for the rel-pos position terms (b200slu_rel_unshift + the batched GEMMs). */
+int b200slu_relattn_bwd_supported(int Tq, int Tk, int dk, int relpos_mode);
+int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
+                        long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H, int Tq,
+                        int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk, void* dv, long long lddkv,
+                        void* d_ac, float drop_p, unsigned long long seed, unsigned int site, void* stream);
+/* d(matrix_bd) [H,B,T,ld_bd] (un-shifted) from d(scores) [H,B,T,ld_p] (shifted): the scatter of rel_shift's backward
+ * (attention.py:240-263), latest mode. */
+int b200slu_rel_unshift(const void* d_scores, long long ld_p, int H, int B, int T, int relpos_mode, void* d_bd, long long ld_bd,
+                        void* stream);
 /* rel_shift source index (bit-exact index test): returns row * 65536 + col + 1 of the un-shifted matrix that lands at
  * out[i, j], or 0 for the literal zero of the legacy variant. */
 long long b200slu_rel_shift_index(int i, int j, int T, int mode);

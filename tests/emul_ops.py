@@ -256,12 +256,45 @@ def relattn_supported(Tq, Tk, dk, mode):
     return dk == 64 and Tk <= 192 and ((mode == "latest" and Tq == Tk) or mode in (None, "none"))
 
 
-def relattn_fwd(qu, qv, k, v, pos, key_lens, B, Tq, Tk, H, mode, causal, scale, drop=None):
+def relattn_fwd(qu, qv, k, v, pos, key_lens, B, Tq, Tk, H, mode, causal, scale, drop=None, want_pd=True):
     """the fused kernel = the unfused chain (scores stay fp32 on chip, as in attn_f1's fp32 outputs)"""
     ac = attn_f1(qu, k, B, Tq, Tk, H)
     bd = attn_f1(qv, pos, B, Tq, pos.shape[0], H, y_bcast=True) if mode == "latest" else None
     p, pd = softmax_fwd(ac, bd, key_lens, Tk, mode, causal, scale, drop=drop)
-    return p, pd, attn_f2(pd, v, B, Tq, Tk, H)
+    ctx = attn_f2(pd, v, B, Tq, Tk, H)
+    if not want_pd and pd is not p:
+        pd = None
+    return p, pd, ctx
+
+
+def relattn_bwd_supported(Tq, Tk, dk, mode):
+    return relattn_supported(Tq, Tk, dk, mode)
+
+
+def relattn_bwd(dctx, qu, k, v, p, ctx, B, Tq, Tk, H, mode, scale, dq, dk, dv, drop=None, want_dac=False):
+    """the fused backward = the unfused chain: dPd = dO v^T, dS = p (m dPd - <dO, O>) scale, dq = dS k, dk = dS^T q, dv = pd^T dO"""
+    dpd = attn_f1(dctx, v, B, Tq, Tk, H)
+    m = _mul(drop, p.shape)
+    pf = p.float()
+    pd = pf if m is None else pf * m
+    Hd = dctx.shape[1]
+    dkh = Hd // H
+    delta = (dctx.float() * ctx.float()).reshape(B, Tq, H, dkh).sum(-1).permute(2, 0, 1)[..., None]  # [H,B,Tq,1]
+    dP = dpd if m is None else dpd * m
+    ds = torch.zeros_like(pf)
+    ds[..., :Tk] = (pf * (dP - delta) * scale)[..., :Tk]
+    ds = _r(ds)
+    attn_f2(ds, k, B, Tq, Tk, H, out=dq)
+    attn_f3(ds, qu, B, Tq, Tk, H, out=dk)
+    attn_f3(_r(pd), dctx, B, Tq, Tk, H, out=dv)
+    return ds if want_dac else None
+
+
+def rel_unshift(dac, T, mode, ld_bd):
+    H, B, Tq, ld = dac.shape
+    bd = torch.zeros(H, B, T, ld_bd, requires_grad=True)
+    (_shift(bd, T, mode) * dac.float()[..., :T]).sum().backward()
+    return _r(bd.grad)
 
 
 def glu_dwconv_fwd(pw1, w, bias, B, T, K):

@@ -229,6 +229,48 @@ def test_fused_attention_fwd(mode, causal, Tq, Tk):
     close(ctx2, K().attn_f2(upd, args_c[3], B, Tq, Tk, H), 2e-2, "fused ctx (dropout) vs unfused")
 
 
+@pytest.mark.parametrize("drop", [None, (0.1, 4321, 9)])
+@pytest.mark.parametrize("mode,Tq,Tk", [("latest", 124, 124), ("latest", 155, 155), ("latest", 192, 192), ("latest", 129, 129),
+                                        ("latest", 33, 33), ("latest", 64, 64), ("none", 21, 21), ("none", 21, 155),
+                                        ("none", 140, 99), ("none", 5, 190), ("none", 150, 150)])
+def test_fused_attention_bwd(mode, Tq, Tk, drop):
+    """the fused tcgen05 backward (dP, dS, dropout(p) on the SM) against the statement of the unfused chain, fed the
+    probabilities and context the fused forward produced"""
+    H, B, dk = 4, 3, 64
+    d = H * dk
+    if not K().relattn_bwd_supported(Tq, Tk, dk, mode):
+        pytest.skip("shape not on the fused backward")
+    qkv = (rnd(B * Tq, 3 * d, seed=1) * 0.7).to(BF)
+    kv = (rnd(B * Tk, 2 * d, seed=2) * 0.7).to(BF)
+    qv = (rnd(B * Tq, d, seed=3) * 0.7).to(BF)
+    pos = (rnd(2 * Tq - 1, d, seed=4) * 0.7).to(BF) if mode == "latest" else None
+    lens = torch.tensor([Tk, max(1, Tk - 3), max(1, Tk // 2)], dtype=torch.int32)
+    dctx = (rnd(B * Tq, d, seed=5)).to(BF)
+    qkv_c, kv_c = qkv.cuda(), kv.cuda()
+    qu_c = qkv_c[:, :d].contiguous() if mode == "latest" else qkv_c[:, :d]
+    p, _, ctx = K().relattn_fwd(qu_c, qv.cuda() if mode == "latest" else None, kv_c[:, :d], kv_c[:, d:],
+                                pos.cuda() if pos is not None else None, lens.cuda(), B, Tq, Tk, H, mode, False, 0.125, drop=drop,
+                                want_pd=False)
+    dq = torch.full((B * Tq, 3 * d), 7.0, device="cuda", dtype=BF)   # written through strided views, like dqkv in the step
+    dkv = torch.full((B * Tk, 2 * d), 7.0, device="cuda", dtype=BF)
+    dac = K().relattn_bwd(dctx.cuda(), qu_c, kv_c[:, :d], kv_c[:, d:], p, ctx, B, Tq, Tk, H, mode, 0.125, dq[:, d:2 * d], dkv[:, :d],
+                          dkv[:, d:], drop=drop, want_dac=True)
+    torch.cuda.synchronize()
+    wdq, wdk, wdv = torch.zeros(B * Tq, d), torch.zeros(B * Tk, d), torch.zeros(B * Tk, d)
+    wdac = E.relattn_bwd(dctx, qkv[:, :d], kv[:, :d], kv[:, d:], p.float().cpu(), ctx.float().cpu(), B, Tq, Tk, H, mode, 0.125, wdq,
+                         wdk, wdv, drop=drop, want_dac=True)
+    close(dac[..., :Tk], wdac[..., :Tk], 2e-2, "dS")
+    close(dq[:, d:2 * d], wdq, 2e-2, "dq_u")
+    close(dkv[:, :d], wdk, 2e-2, "dk")
+    close(dkv[:, d:], wdv, 2e-2, "dv")
+    assert (dq[:, :d] == 7.0).all() and (dq[:, 2 * d:] == 7.0).all()  # neighbours of the strided outputs untouched
+    if mode == "latest":
+        Pn = 2 * Tq - 1
+        dbd = K().rel_unshift(dac, Tq, mode, E.round8(Pn))
+        wdbd = E.rel_unshift(dac.float().cpu(), Tq, mode, E.round8(Pn))
+        assert torch.equal(dbd.float().cpu()[..., :Pn], wdbd[..., :Pn])
+
+
 @pytest.mark.parametrize("T", [1, 2, 3, 7, 16, 33, 64])
 def test_rel_shift_index_bit_exact(T, golden_dir):
     import os

@@ -207,3 +207,50 @@ def test_dropout_ref_keep_rate_and_determinism():
     assert not np.array_equal(a, dropout_ref.keep_mask(0.1, 5, 4, 100003))
     assert not np.array_equal(a, dropout_ref.keep_mask(0.1, 6, 3, 100003))
     assert dropout_ref.keep_mask(0.0, 1, 1, 64).all()
+
+
+@pytest.mark.parametrize("p_drop", [0.0, 0.1])
+def test_emulated_step_on_the_fused_attention_formulation(emulated, p_drop):
+    """d_k = 64 routes the step through the FUSED attention forward / backward entry points (relattn_fwd / relattn_bwd:
+    delta = <dO, O>, dropout(p) regenerated from p, dq_u / dk / dv from dS): the formulation the CUDA kernels implement,
+    checked here against autograd over the oracle (with the dropout decisions replayed)."""
+    import dropout_ref
+    from espnet_slurp_b200.testing import make_sd
+    enc = bstep.EncCfg(80, 128, 2, 64, 2, 7, "latest", p_drop, p_drop, p_drop)
+    dec = bstep.DecCfg(20, 128, 2, 64, 1, p_drop, p_drop, p_drop, p_drop)
+    cfg = bstep.ModelCfg(enc=enc, dec=dec, vocab=20)
+    ocfg = om.ModelCfg(enc=om.EncCfg(80, 128, 2, 64, 2, 7, "latest"), dec=om.DecCfg(20, 128, 2, 64, 1), vocab=20)
+    sd = make_sd(ocfg.enc, ocfg.dec, 20, seed=11)
+    g = torch.Generator().manual_seed(3)
+    B, Tin = 3, 70
+    feats = torch.randn(B, Tin, 80, generator=g)
+    flens = torch.tensor([70, 61, 44])
+    tl = torch.tensor([5, 2, 4])
+    text = torch.full((B, 5), -1, dtype=torch.long)
+    for b in range(B):
+        text[b, : tl[b]] = torch.randint(1, 18, (int(tl[b]),), generator=g)
+    calls = []
+    orig = emul_ops.relattn_bwd
+    emul_ops.relattn_bwd = lambda *a, **k: (calls.append(1), orig(*a, **k))[1]
+    try:
+        pack = bparams.ParamPack(sd, lowp=torch.float32)
+        pack.refresh()
+        pack.zero_grad()
+        ctx = bstep.StepCtx(5, True)
+        out = bstep.train_step_from_feats(feats, flens.int(), text, tl, pack.P, pack.W, pack.G, cfg, ctx)
+        pack.finalize_grads()
+    finally:
+        emul_ops.relattn_bwd = orig
+    assert len(calls) == 2 + 2  # two encoder blocks, decoder self- and source-attention
+    osd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    replay = dropout_ref.DropReplay(ctx.sites, 5) if p_drop > 0 else None
+    oloss, _ = om.asr_forward_from_feats(feats, flens, text, tl, osd, ocfg, drop=replay)
+    oloss.backward()
+    np.testing.assert_allclose(out["loss"].item(), oloss.item(), rtol=5e-5)
+    worst, worst_name = 0.0, ""
+    for k, v in osd.items():
+        want = v.grad.numpy() if v.grad is not None else np.zeros(tuple(v.shape), np.float32)
+        err = float(np.abs(pack.grads()[k].numpy() - want).max() / max(np.abs(want).max(), 1e-3))
+        if err > worst:
+            worst, worst_name = err, k
+    assert worst < 3e-3, (worst, worst_name)
