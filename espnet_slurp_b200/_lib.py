@@ -78,7 +78,7 @@ _SIGNATURES = {
     "b200slu_relattn_fwd": [_P, _P, _L, _P, _P, _L, _P, _L, _P, _I, _I, _I, _I, _I, _I, _F, _P, _P, _L, _P, _L, _F, _U64, _U32, _P],
     "b200slu_relattn_bwd_supported": [_I, _I, _I, _I],
     "b200slu_relattn_bwd": [_P, _L, _P, _L, _P, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _F, _P, _L, _P, _P, _L, _P, _F, _U64, _U32,
-                            _P],
+                            _P, _P, _L, _P, _P, _L, _P],
     "b200slu_rel_unshift": [_P, _L, _I, _I, _I, _I, _P, _L, _P],
     "b200slu_rel_shift_index": [_I, _I, _I, _I],
     "b200slu_glu_dwconv_fwd": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P],

@@ -550,10 +550,16 @@ relattn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid
 // dK / dV) through the UMMA descriptors -- no transposed copy exists anywhere.  dP, dS, dropout(p) and (rel-pos modes)
 // d(matrix_bd) never touch HBM.  One CTA owns one (utterance, head) at a time and walks its query tiles, so dK / dV
 // accumulate in tensor memory across the tiles; thread = TMEM lane = query row (or key row in the dK / dV epilogue).
-// Rel-pos (latest): dS is also what d(matrix_bd) is made of -- the un-shift and the two position contractions
-// (dQ_v = d(bd) . P, dP = d(bd)^T . Q_v) are stage 2; until then the kernel hands dS out (bf16, shifted layout).
+// Rel-pos (latest): d(matrix_bd) is dS un-shifted, d(bd)[r, 127 - r + j] = dS[r, j] in the coordinates of the position
+// window the query tile can reach (the forward's window).  Once dQ_u / dK / dV are issued the threads rebuild dS as that
+// SKEWED tile [128 x WIN] over the dead operand tiles: a row moves right by s = 127 - r elements = (s / 8) 16-byte
+// units (placement) + (s % 8) elements (a funnel shift over two neighbouring units in registers: two select levels for
+// the 4-byte part, one PRMT for the odd element).  The same tile is then the K-major A operand of
+// dQ_v = d(bd) . P_window and the MN-major A operand of dP_window = d(bd)^T . Q_v; dP rows go to the fp32 gradient of
+// the projected positions with vector reductions (red.global.add.v4.f32).  Nothing of shape T x T is written to HBM.
 constexpr int BWD_DK_COL = 192;   // dK: two key tiles x 64 columns
 constexpr int BWD_DV_COL = 320;   // dV: two key tiles x 64 columns
+constexpr int BWD_DQV_COL = 448;  // dQ_v (rel-pos); d(pos) tiles reuse columns [0, 192) once dQ_u has been read out
 constexpr int BLK = QT * 128;     // bytes of one [128 rows x 64 bf16] swizzled block
 
 struct AttnBwdArgs {
@@ -563,22 +569,32 @@ struct AttnBwdArgs {
   long long ldctx;
   bf16 *dq, *dk, *dv, *dac;
   long long lddq, lddkv, ld_p;
-  uint32_t off_pd, off_ds, off_k, off_v, off_do, off_qu, off_bar;
+  bf16* dqv;        // rel-pos: gradient of q_v, rows like dq
+  float* dpos;      // rel-pos: fp32 gradient of the projected positions [2T-1, lddpos], accumulated
+  long long lddpos;
+  int WIN;
+  uint32_t off_pd, off_ds, off_k, off_v, off_do, off_qu, off_pos, off_stg, off_bar;
   B2Dropout drop;
+  long long* dbg;  // tuning only (B200SLU_ATTN_BWD_DEBUG): CTA 0's cycles per phase, summed over its query tiles
+  int dbgflags;    // tuning only (B200SLU_ATTN_BWD_FLAGS): 1 = no d(pos) reduce, 2 = no load prefetch
 };
 
+template <bool REL>
 __global__ void __launch_bounds__(NTHREADS, 1)
 relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_constant__ CUtensorMap map_qu,
                    const __grid_constant__ CUtensorMap map_k, const __grid_constant__ CUtensorMap map_v,
-                   const __grid_constant__ CUtensorMap map_p, const AttnBwdArgs a, int num_units) {
+                   const __grid_constant__ CUtensorMap map_p, const __grid_constant__ CUtensorMap map_qv,
+                   const __grid_constant__ CUtensorMap map_pos, const AttnBwdArgs a, int num_units) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = smem_u32(smem);
   if (sbase & 1023u) __trap();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t s_pd = sbase + a.off_pd, s_ds = sbase + a.off_ds, s_k = sbase + a.off_k, s_v = sbase + a.off_v,
                  s_do = sbase + a.off_do, s_qu = sbase + a.off_qu;
+  const uint32_t s_pos = sbase + a.off_pos, s_qv = s_k, s_dbd = sbase;  // Q_v lands where K was; the skewed tile over pd / dO / Q_u / V
   const uint32_t bar_kv = sbase + a.off_bar, bar_q = bar_kv + 8, bar_s = bar_kv + 16, bar_c = bar_kv + 24;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + a.off_bar + 32);
+  const uint32_t bar_qv = bar_kv + 32, bar_c2 = bar_kv + 40;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + a.off_bar + 48);
   float* rowstat = reinterpret_cast<float*>(smem + a.off_bar + 64);  // [2 halves][128 rows] partial delta
   const int TKP = a.TKP, nblk = (TKP + 63) / 64, nkt = (TKP + QT - 1) / QT;
   const int nqt = (a.Tq + QT - 1) / QT;
@@ -590,7 +606,11 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_p) : "memory");
-    for (int i = 0; i < 4; ++i) mbar_init(bar_kv + i * 8, 1);
+    if (REL) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_qv) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_pos) : "memory");
+    }
+    for (int i = 0; i < 6; ++i) mbar_init(bar_kv + i * 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -611,25 +631,53 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
   const uint32_t tlane = tmem_base + ((uint32_t)(q * 32) << 16);
   const int nch = TKP / CH, n0 = (nch + 1) / 2;
   const int cbeg = hs ? n0 : 0, nmine = hs ? nch - n0 : n0;
-  uint32_t n_kv = 0, n_q = 0;  // completed load / MMA rounds: barrier parities (the same in every thread)
+  uint32_t n_q = 0;  // completed query tiles: the parity of every barrier (each completes once per tile)
+  long long acc_t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const bool rec = a.dbg != nullptr && blockIdx.x == 0 && tid == 32;
+#define BWD_STAMP(k_)                     \
+  if (rec) {                              \
+    const long long now_ = clock64();     \
+    acc_t[k_] += now_ - t_prev;           \
+    t_prev = now_;                        \
+  }
+  long long t_prev = rec ? clock64() : 0;
+
+  // All operand loads of one query tile (thread 0).  K and V come per tile too: their regions are recycled (Q_v lands on K,
+  // the skewed tile on V).  Issued one tile AHEAD, as soon as the last MMA that reads those regions has completed, so the
+  // load latency hides behind the previous tile's read-out.
+  auto issue_loads = [&](int unit_, int qt_) {
+    const int h_ = unit_ % a.H, b_ = unit_ / a.H, i0_ = qt_ * QT;
+    mbar_expect_tx(bar_kv, (uint32_t)(2 * TKP * 128));
+    tma_load_3d(s_k, &map_k, bar_kv, h_ * DK, 0, b_);
+    tma_load_3d(s_v, &map_v, bar_kv, h_ * DK, 0, b_);
+    mbar_expect_tx(bar_q, (uint32_t)(2 * BLK + nblk * BLK + (REL ? a.WIN * 128 : 0)));
+    tma_load_3d(s_do, &map_do, bar_q, h_ * DK, i0_, b_);
+    tma_load_3d(s_qu, &map_qu, bar_q, h_ * DK, i0_, b_);
+    for (int kb = 0; kb < nblk; ++kb) tma_load_3d(s_pd + kb * BLK, &map_p, bar_q, kb * 64, i0_, h_ * a.B + b_);
+    if (REL) {
+      const int c0_ = b2_rel_shift_src(i0_ + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col;
+      tma_load_3d(s_pos, &map_pos, bar_q, h_ * DK, c0_, 0);
+      tma_load_3d(s_pos + (a.WIN / 2) * 128, &map_pos, bar_q, h_ * DK, c0_ + a.WIN / 2, 0);
+    }
+  };
+  auto issue_next = [&](int unit_, int qt_) {
+    if (a.dbgflags & 2) return;
+    if (qt_ + 1 < nqt) issue_loads(unit_, qt_ + 1);
+    else if (unit_ + (int)gridDim.x < num_units) issue_loads(unit_ + (int)gridDim.x, 0);
+  };
+  if (tid == 0 && (int)blockIdx.x < num_units) issue_loads(blockIdx.x, 0);
+  const uint32_t s_stg = sbase + a.off_stg;
 
   for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
     const int h = unit % a.H, b = unit / a.H;
-    if (tid == 0) {
-      mbar_expect_tx(bar_kv, (uint32_t)(2 * TKP * 128));
-      tma_load_3d(s_k, &map_k, bar_kv, h * DK, 0, b);
-      tma_load_3d(s_v, &map_v, bar_kv, h * DK, 0, b);
-    }
     for (int qt = 0; qt < nqt; ++qt) {
       const int i0 = qt * QT, i = i0 + r;
       const bool row_ok = i < a.Tq;
+      const bool warp_live = i0 + q * 32 < a.Tq;  // warp-uniform: any valid query row in this warp's 32 lanes
       const uint32_t par = n_q & 1u;
-      if (tid == 0) {
-        mbar_expect_tx(bar_q, (uint32_t)(2 * BLK + nblk * BLK));
-        tma_load_3d(s_do, &map_do, bar_q, h * DK, i0, b);
-        tma_load_3d(s_qu, &map_qu, bar_q, h * DK, i0, b);
-        for (int kb = 0; kb < nblk; ++kb) tma_load_3d(s_pd + kb * BLK, &map_p, bar_q, kb * 64, i0, h * a.B + b);
-      }
+      if ((a.dbgflags & 2) && tid == 0 && !(unit == (int)blockIdx.x && qt == 0)) issue_loads(unit, qt);
+      // first position row of the window this tile reaches (the forward's window); may be negative: zero-filled
+      const int c0 = REL ? b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col : 0;
       // this thread's half (32 columns) of its row of the forward output, for delta
       uint4 cx[4];
       if (row_ok) {
@@ -641,7 +689,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
         for (int t = 0; t < 4; ++t) cx[t] = make_uint4(0u, 0u, 0u, 0u);
       }
       if (tid == 0) {
-        if (qt == 0) mbar_wait(bar_kv, n_kv & 1u);
+        mbar_wait(bar_kv, par);
         mbar_wait(bar_q, par);
         tcgen05_fence_after();
         const uint32_t id_s = make_idesc(TKP, 0, 0, QT);
@@ -651,6 +699,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
         umma_commit(bar_s);
       }
       mbar_wait(bar_q, par);
+      BWD_STAMP(0)
       float dpart = 0.f;
       {
 #pragma unroll
@@ -673,15 +722,26 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
       const float delta = rowstat[r] + rowstat[QT + r];
       mbar_wait(bar_s, par);
       tcgen05_fence_after();
+      BWD_STAMP(1)
 
       // ------------------------------------------------------------ dS and dropout(p), 16 keys at a time
       const long long rg = ((long long)h * a.B + b) * a.Tq + i;
       bf16* dacrow = a.dac != nullptr ? a.dac + rg * a.ld_p : nullptr;
       const float sc = a.scale;
       uint32_t ta[16], tb[16];
-      if (nmine > 0) tmem_ld16(tlane + cbeg * CH, ta);
+      if (!warp_live) {
+        // no valid query row in this warp (tail tile): p arrived as zeros (TMA fill), so dropout(p) is in place already;
+        // dS = 0
+        for (int cc = 0; cc < nmine; ++cc) {
+          const int j0 = (cbeg + cc) * CH;
+          const uint32_t blk = (uint32_t)(j0 >> 6) * BLK + (uint32_t)r * 128u, ch0 = (uint32_t)((j0 & 63) >> 3);
+          sts128(s_ds + blk + (((ch0) ^ (uint32_t)(r & 7)) << 4), 0u, 0u, 0u, 0u);
+          sts128(s_ds + blk + (((ch0 + 1u) ^ (uint32_t)(r & 7)) << 4), 0u, 0u, 0u, 0u);
+        }
+      }
+      if (warp_live && nmine > 0) tmem_ld16(tlane + cbeg * CH, ta);
 #pragma unroll 1
-      for (int c = 0; c < nmine; c += 2) {
+      for (int c = 0; warp_live && c < nmine; c += 2) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           const int cc = c + half;
@@ -741,6 +801,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
       fence_async_smem();
       tcgen05_fence_before();
       group_sync(0);
+      BWD_STAMP(2)
 
       // ------------------------------------------------------------ dQ_u, dK, dV
       if (tid == 0) {
@@ -764,22 +825,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
       }
       mbar_wait(bar_c, par);
       tcgen05_fence_after();
-      {
-        uint32_t o[32];
-        tmem_ld32(tlane + hs * 32, o);
-        tmem_ld_wait();
-        if (row_ok) {
-          bf16* dst = a.dq + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float v[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(o[g * 8 + e]);
-            store8_bf16(dst + g * 8, v);
-          }
-        }
-      }
-      if (qt == nqt - 1) {
+      auto drain_dkv = [&]() {
         for (int m = 0; m < nkt; ++m) {
           const int j = m * QT + r;
           uint32_t ok_[32], ov_[32];
@@ -800,14 +846,157 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
             }
           }
         }
+      };
+      BWD_STAMP(3)
+      if (REL && tid == 0) {  // K is dead: Q_v (B operand of the d(pos) contraction) takes its place while the tile is skewed
+        mbar_expect_tx(bar_qv, (uint32_t)BLK);
+        tma_load_3d(s_qv, &map_qv, bar_qv, h * DK, i0, b);
       }
+      if (!REL && tid == 0) issue_next(unit, qt);  // every operand region is dead: the next tile's loads fly during the read-out
+      {
+        uint32_t o[32];
+        tmem_ld32(tlane + hs * 32, o);
+        tmem_ld_wait();
+        if (row_ok) {
+          bf16* dst = a.dq + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(o[g * 8 + e]);
+            store8_bf16(dst + g * 8, v);
+          }
+        }
+      }
+      if (REL) {
+        // ---------------------------------------------------------- d(bd): dS skewed into window coordinates
+        const int WU = a.WIN >> 3, NU = TKP >> 3;   // 16-byte units per window row / per dS row
+        const int sft = QT - 1 - r, ua = sft >> 3, bw = (sft >> 1) & 3;
+        const uint32_t psel = (sft & 1) ? 0x5432u : 0x7654u;
+        const bool s1 = bw & 1, s2 = bw & 2;
+        const int ubeg = hs ? WU / 2 : 0, uend = hs ? WU : WU / 2;
+        const uint32_t rsw = (uint32_t)(r & 7), rbase = (uint32_t)r * 128u;
+        auto load_unit = [&](int k, uint32_t (&w)[4]) {
+          if (k >= 0 && k < NU) {
+            float f0, f1, f2, f3;
+            lds128(s_ds + (uint32_t)(k >> 3) * BLK + rbase + ((((uint32_t)k & 7u) ^ rsw) << 4), f0, f1, f2, f3);
+            w[0] = __float_as_uint(f0); w[1] = __float_as_uint(f1); w[2] = __float_as_uint(f2); w[3] = __float_as_uint(f3);
+          } else {
+            w[0] = w[1] = w[2] = w[3] = 0u;
+          }
+        };
+        if (!warp_live) {
+          for (int u = ubeg; u < uend; ++u)
+            sts128(s_dbd + (uint32_t)(u >> 3) * BLK + rbase + ((((uint32_t)u & 7u) ^ rsw) << 4), 0u, 0u, 0u, 0u);
+        }
+        uint32_t y[8];
+        if (warp_live) {
+          uint32_t t4[4];
+          load_unit(ubeg - ua - 1, t4);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) y[4 + e] = t4[e];
+        }
+#pragma unroll 2
+        for (int u = ubeg; warp_live && u < uend; ++u) {
+          uint32_t t4[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) y[e] = y[4 + e];
+          load_unit(u - ua, t4);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) y[4 + e] = t4[e];
+          uint32_t w1[7], z[5];
+#pragma unroll
+          for (int e = 0; e < 7; ++e) w1[e] = s1 ? y[e] : y[e + 1];
+#pragma unroll
+          for (int e = 0; e < 5; ++e) z[e] = s2 ? w1[e] : w1[e + 2];
+          sts128(s_dbd + (uint32_t)(u >> 3) * BLK + rbase + ((((uint32_t)u & 7u) ^ rsw) << 4), __byte_perm(z[0], z[1], psel),
+                 __byte_perm(z[1], z[2], psel), __byte_perm(z[2], z[3], psel), __byte_perm(z[3], z[4], psel));
+        }
+        fence_async_smem();
+        tcgen05_fence_before();
+        group_sync(0);
+        BWD_STAMP(4)
+        const int nmt = (a.WIN + QT - 1) / QT;
+        if (tid == 0) {
+          mbar_wait(bar_qv, par);
+          tcgen05_fence_after();
+          const uint32_t id_q = make_idesc(DK, 0, 1, QT);  // dQ_v = d(bd) . P_window
+          for (int ks = 0; ks < a.WIN / 16; ++ks)
+            umma_bf16(tmem_base + BWD_DQV_COL, make_smem_desc(s_dbd + (uint32_t)(ks >> 2) * BLK + (ks & 3) * 32, 16, 1024),
+                      make_smem_desc(s_pos + ks * 2048, 64 * DK * 2, 1024), id_q, ks != 0);
+          const uint32_t id_t = make_idesc(DK, 1, 1, QT);  // dP_window = d(bd)^T . Q_v
+          for (int m = 0; m < nmt; ++m) {
+#pragma unroll
+            for (int kk = 0; kk < QT / 16; ++kk)
+              umma_bf16(tmem_base + m * DK, make_smem_desc(s_dbd + (uint32_t)m * 2 * BLK + kk * 2048, BLK, 1024),
+                        make_smem_desc(s_qv + kk * 2048, 64 * DK * 2, 1024), id_t, kk != 0);
+          }
+          umma_commit(bar_c2);
+        }
+        if (qt == nqt - 1) drain_dkv();  // final since the first MMA batch: read out under the second one
+        mbar_wait(bar_c2, par);
+        tcgen05_fence_after();
+        if (tid == 0) issue_next(unit, qt);  // every operand region is dead: the next tile's loads fly during the read-out
+        BWD_STAMP(5)
+        {
+          uint32_t o[32];
+          tmem_ld32(tlane + BWD_DQV_COL + hs * 32, o);
+          tmem_ld_wait();
+          if (row_ok) {
+            bf16* dst = a.dqv + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              float v[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(o[g * 8 + e]);
+              store8_bf16(dst + g * 8, v);
+            }
+          }
+        }
+        // d(pos): a warp's [32 window rows x 32 floats] slice goes through a private 4 KB staging patch (128-byte rows,
+        // 16-byte chunks XORed with the row like every tile here), then leaves with 8 lanes per row: one reduction
+        // instruction covers four whole 128-byte lines instead of 32 scattered 16-byte pieces (row-per-lane
+        // red.global.add.v4 measured 6200 cycles per tile).  Only a __syncwarp between the two halves.
+        const int rows_here = min(QT, a.Tq - i0);
+        const int wlo = QT - rows_here, whi = QT - 1 + a.Tk;  // window rows [wlo, whi) can be non-zero
+        const uint32_t patch = s_stg + (uint32_t)warp * 4096u;
+        for (int m = 0; m < nmt; ++m) {
+          const int w0 = m * QT + q * 32;  // first window row of this warp's slice
+          if (w0 >= whi || w0 + 32 <= wlo) continue;  // warp-uniform: nothing of the band in this slice
+          uint32_t o[32];
+          tmem_ld32(tlane + m * DK + hs * 32, o);
+          tmem_ld_wait();
+          __syncwarp();  // the previous slice has been read out of the patch
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            sts128(patch + (uint32_t)lane * 128u + ((((uint32_t)g) ^ (uint32_t)(lane & 7)) << 4), o[g * 4], o[g * 4 + 1], o[g * 4 + 2],
+                   o[g * 4 + 3]);
+          __syncwarp();
+          const int ch = lane & 7;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3), w = w0 + rr, n = c0 + w;
+            float f0, f1, f2, f3;
+            lds128(patch + (uint32_t)rr * 128u + ((((uint32_t)ch) ^ (uint32_t)(rr & 7)) << 4), f0, f1, f2, f3);
+            if (w >= wlo && w < whi && n >= 0 && n < 2 * a.Tq - 1)
+              atomicAdd(reinterpret_cast<float4*>(a.dpos + (long long)n * a.lddpos + h * DK + hs * 32 + ch * 4),
+                        make_float4(f0, f1, f2, f3));
+          }
+        }
+      }
+      if (!REL && qt == nqt - 1) drain_dkv();
       ++n_q;
       tcgen05_fence_before();
       fence_async_smem();  // this tile's generic writes to the p / dS tiles are ordered before the next TMA loads into them
       group_sync(0);
+      BWD_STAMP(6)
     }
-    ++n_kv;
   }
+  if (rec) {
+    for (int t = 0; t < 7; ++t) a.dbg[t] = acc_t[t];
+    a.dbg[7] = (long long)n_q;
+  }
+#undef BWD_STAMP
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -975,60 +1164,103 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
                                    long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H,
                                    int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
                                    void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
-                                   unsigned int site, void* stream) {
+                                   unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
+                                   float* dpos_accum, long long lddpos, void* stream) {
   B2_CHECK_ARG(B > 0 && H > 0, "relattn_bwd: empty problem");
   B2_CHECK_ARG(b200slu_relattn_bwd_supported(Tq, Tk, DK, relpos_mode),
                "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
                Tq, Tk, relpos_mode);
+  const bool rel = relpos_mode == B200SLU_RELPOS_LATEST;
   B2_CHECK_ARG(d_ctx && q_u && k && v && p && ctx && dq_u && dk_out && dv_out, "relattn_bwd: null operand");
+  B2_CHECK_ARG(!rel || (q_v && pos && dq_v && dpos_accum), "relattn_bwd: rel-pos mode needs q_v, pos, dq_v and dpos_accum");
   B2_CHECK_ARG(lddo % 8 == 0 && ldq % 8 == 0 && ldkv % 8 == 0 && ldctx % 8 == 0 && lddq % 8 == 0 && lddkv % 8 == 0 && ld_p % 8 == 0 &&
-                   ld_p >= Tk,
+                   ld_p >= Tk && (!rel || (ldpos % 8 == 0 && lddpos % 4 == 0)),
                "relattn_bwd: row strides must be multiples of 8 elements, ld_p >= Tk");
   B2_CHECK_ARG(((uintptr_t)d_ctx % 16) == 0 && ((uintptr_t)q_u % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 &&
                    ((uintptr_t)p % 16) == 0 && ((uintptr_t)ctx % 16) == 0 && ((uintptr_t)dq_u % 16) == 0 &&
-                   ((uintptr_t)dk_out % 16) == 0 && ((uintptr_t)dv_out % 16) == 0 && ((uintptr_t)d_ac % 32) == 0,
+                   ((uintptr_t)dk_out % 16) == 0 && ((uintptr_t)dv_out % 16) == 0 && ((uintptr_t)d_ac % 32) == 0 &&
+                   (!rel || (((uintptr_t)q_v % 16) == 0 && ((uintptr_t)pos % 16) == 0 && ((uintptr_t)dq_v % 16) == 0 &&
+                             ((uintptr_t)dpos_accum % 16) == 0)),
                "relattn_bwd: operands must be 16-byte aligned (d_ac: 32)");
   cudaStream_t st = (cudaStream_t)stream;
   AttnBwdArgs a{};
   a.B = B; a.H = H; a.Tq = Tq; a.Tk = Tk;
   a.TKP = (Tk + 15) / 16 * 16;
+  a.WIN = a.TKP + QT;
   a.scale = scale;
   a.ctx = (const bf16*)ctx; a.ldctx = ldctx;
   a.dq = (bf16*)dq_u; a.dk = (bf16*)dk_out; a.dv = (bf16*)dv_out; a.dac = (bf16*)d_ac;
   a.lddq = lddq; a.lddkv = lddkv; a.ld_p = ld_p;
-  // the two A-operand tiles first: an M = 128 contraction over the second key tile reads two 64-key blocks, of which only
-  // the first may exist (keys <= 192): the bytes behind it belong to the next region (never faulting, never stored)
-  const uint32_t nblk = (uint32_t)(a.TKP + 63) / 64;
+  a.dqv = (bf16*)dq_v; a.dpos = dpos_accum; a.lddpos = lddpos;
+  // [pd tile | dO | Q_u | V] [dS tile] [K, later Q_v] [position window].  The first group is dead once dQ_u / dK / dV are
+  // issued: the skewed d(bd) tile is built over it (dS, its source, stays).  An M = 128 MN-major read over the last key /
+  // window tile may run past the blocks that exist into the next region: never faulting (bounded below), never stored.
+  const uint32_t nblk = (uint32_t)(a.TKP + 63) / 64, vpad = (uint32_t)(a.TKP * 128 + 1023) / 1024 * 1024;
   a.off_pd = 0;
-  a.off_ds = a.off_pd + nblk * BLK;
-  a.off_k = a.off_ds + nblk * BLK;
-  a.off_v = a.off_k + (uint32_t)(a.TKP * 128 + 1023) / 1024 * 1024;
-  a.off_do = a.off_v + (uint32_t)(a.TKP * 128 + 1023) / 1024 * 1024;
+  a.off_do = nblk * BLK;
   a.off_qu = a.off_do + BLK;
-  a.off_bar = a.off_qu + BLK;
+  a.off_v = a.off_qu + BLK;
+  a.off_ds = a.off_v + vpad;
+  a.off_k = a.off_ds + nblk * BLK;
+  a.off_pos = a.off_k + (rel ? (vpad > (uint32_t)BLK ? vpad : (uint32_t)BLK) : vpad);
+  a.off_stg = a.off_pos + (rel ? (uint32_t)(a.WIN * 128 + 1023) / 1024 * 1024 : 0u);
+  // d(pos) staging (8 warps x 4 KB): the dS tile is dead by then and, from three key blocks on, large enough to host it
+  a.off_bar = a.off_stg;
+  if (rel) {
+    if (nblk >= 3) a.off_stg = a.off_ds;
+    else a.off_bar = a.off_stg + 2 * BLK;
+  }
   a.drop = b2_make_drop(drop_p, seed, site);
   size_t smem = (size_t)a.off_bar + 64 + 2 * QT * sizeof(float);
-  const size_t reach = (size_t)a.off_ds + ((size_t)(a.TKP + QT - 1) / QT) * 2 * BLK;  // what the widest MN-major read touches
+  const size_t nkt = (size_t)(a.TKP + QT - 1) / QT, nmt = (size_t)(a.WIN + QT - 1) / QT;
+  size_t reach = (size_t)a.off_ds + nkt * 2 * BLK;  // what the widest MN-major reads touch
+  if (rel && nmt * 2 * BLK > reach) reach = nmt * 2 * BLK;
   if (smem < reach) smem = reach;
   B2_CHECK_ARG(smem <= 232448, "relattn_bwd: shared memory %zu", smem);
+  B2_CHECK_ARG(!rel || (size_t)((a.WIN + 63) / 64) * BLK <= a.off_ds, "relattn_bwd: skewed tile overlaps its source");
 
-  CUtensorMap mdo, mqu, mk, mv, mp;
+  CUtensorMap mdo, mqu, mk, mv, mp, mqv, mpos;
   const int d = H * DK;
   B2_TRY(make_map3(&mdo, d_ctx, d, Tq, lddo, B, (long long)Tq * lddo, QT));
   B2_TRY(make_map3(&mqu, q_u, d, Tq, ldq, B, (long long)Tq * ldq, QT));
   B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
   B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
   B2_TRY(make_map3(&mp, p, ld_p, Tq, ld_p, (long long)H * B, (long long)Tq * ld_p, QT));
+  if (rel) {
+    B2_TRY(make_map3(&mqv, q_v, d, Tq, ldq, B, (long long)Tq * ldq, QT));
+    B2_TRY(make_map3(&mpos, pos, d, 2 * Tq - 1, ldpos, 1, 0, a.WIN / 2));
+  } else {
+    mqv = mqu;
+    mpos = mk;
+  }
   static unsigned long long configured = 0;  // per device
   if (!b2_device_done(configured)) {
-    B2_CUDA(cudaFuncSetAttribute(relattn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B2_CUDA(cudaFuncSetAttribute(relattn_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B2_CUDA(cudaFuncSetAttribute(relattn_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     b2_device_mark(configured);
   }
   const int units = B * H, sms = b2_num_sms();
-  B2_SCOPE(FAM_ATTN, st, (double)units * 8.0 * Tq * Tk * DK,
+  B2_SCOPE(FAM_ATTN, st, (double)units * (8.0 * Tq * Tk * DK + (rel ? 4.0 * Tq * (2.0 * Tq - 1) * DK : 0.0)),
            (double)units * (2.0 * DK * (3.0 * Tq + 2.0 * Tk) + 2.0 * Tq * Tk + 2.0 * DK * (Tq + 2.0 * Tk) +
-                            (d_ac ? 2.0 * Tq * Tk : 0.0)));
-  B2_CUDA(b2_launch(relattn_bwd_kernel, dim3((unsigned)(units < sms ? units : sms)), dim3(NTHREADS), smem, st, mdo, mqu, mk, mv, mp, a,
-                    units));
+                            (rel ? 2.0 * DK * 2.0 * Tq : 0.0) + (d_ac ? 2.0 * Tq * Tk : 0.0)));
+  const dim3 grid((unsigned)(units < sms ? units : sms));
+  static const bool dbg = getenv("B200SLU_ATTN_BWD_DEBUG") != nullptr && atoi(getenv("B200SLU_ATTN_BWD_DEBUG")) != 0;
+  if (dbg) {
+    a.dbg = b2_debug_scratch();
+    B2_CHECK_ARG(a.dbg != nullptr, "relattn_bwd: debug scratch unavailable");
+  }
+  static const int dbgflags = getenv("B200SLU_ATTN_BWD_FLAGS") ? atoi(getenv("B200SLU_ATTN_BWD_FLAGS")) : 0;
+  a.dbgflags = dbgflags;
+  if (rel) B2_CUDA(b2_launch(relattn_bwd_kernel<true>, grid, dim3(NTHREADS), smem, st, mdo, mqu, mk, mv, mp, mqv, mpos, a, units));
+  else B2_CUDA(b2_launch(relattn_bwd_kernel<false>, grid, dim3(NTHREADS), smem, st, mdo, mqu, mk, mv, mp, mqv, mpos, a, units));
+  if (dbg) {
+    long long hbuf[8];
+    B2_CUDA(cudaStreamSynchronize(st));
+    B2_CUDA(cudaMemcpy(hbuf, a.dbg, sizeof(hbuf), cudaMemcpyDeviceToHost));
+    const double n = hbuf[7] > 0 ? (double)hbuf[7] : 1.0;
+    fprintf(stderr, "[relattn_bwd dbg] Tq=%d Tk=%d rel=%d smem=%zu | CTA 0, %lld query tiles, mean cycles per tile: loads %.0f, dP MMA %.0f, "
+            "dS pass %.0f, dQu/dK/dV MMA %.0f, dQu drain + skew %.0f, dQv/dPos MMA %.0f, drains %.0f\n", Tq, Tk, (int)rel, smem, hbuf[7],
+            hbuf[0] / n, hbuf[1] / n, hbuf[2] / n, hbuf[3] / n, hbuf[4] / n, hbuf[5] / n, hbuf[6] / n);
+  }
   return 0;
 }

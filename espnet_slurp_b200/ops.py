@@ -284,18 +284,23 @@ def relattn_bwd_supported(Tq: int, Tk: int, dk: int, mode: str) -> bool:
 
 
 def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: str, scale: float, dq, dk, dv,
-                drop: Drop = None, want_dac: bool = False):
-    """One kernel for the backward of the attention core (autograd through attention.py:78-95, :297-302 / :111-113).
-    dctx, qu, ctx [B*Tq, H*64], k, v [B*Tk, H*64], p bf16 [H,B,Tq,round8(Tk)] (as saved by the forward); writes dq
-    [B*Tq, H*64], dk, dv [B*Tk, H*64] (views with their own row strides are fine).  want_dac: also return dS (bf16,
-    shifted layout [H,B,Tq,round8(Tk)]) for the rel-pos position terms."""
+                drop: Drop = None, want_dac: bool = False, qv=None, pos=None, dqv=None, dpos=None):
+    """One kernel for the backward of the attention core (autograd through attention.py:78-95, :297-302 / :111-113, rel_shift
+    :240-263).  dctx, qu, ctx [B*Tq, H*64], k, v [B*Tk, H*64], p bf16 [H,B,Tq,round8(Tk)] (as saved by the forward); writes
+    dq [B*Tq, H*64], dk, dv [B*Tk, H*64] (views with their own row strides are fine).  Mode "latest": qv, pos (projected
+    positions [2T-1, H*64]) in, dqv (row stride of dq) out, dpos (f32 [2T-1, H*64]) ACCUMULATED.  want_dac: also return dS
+    (bf16, shifted layout [H,B,Tq,round8(Tk)])."""
     ld = p.shape[-1]
     dac = torch.empty_like(p) if want_dac else None
     dp, seed, site = _drop(drop)
     assert k.stride(0) == v.stride(0) and dk.stride(0) == dv.stride(0)
+    if RELPOS[mode]:
+        assert qv.stride(0) == qu.stride(0) and dqv.stride(0) == dq.stride(0) and dpos.dtype == torch.float32
     check(_lib.lib().b200slu_relattn_bwd(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
                                          ptr(ctx), ctx.stride(0), B, H, Tq, Tk, RELPOS[mode], scale, ptr(dq), dq.stride(0),
-                                         ptr(dk), ptr(dv), dk.stride(0), ptr(dac), dp, seed, site, stream_ptr()), "relattn_bwd")
+                                         ptr(dk), ptr(dv), dk.stride(0), ptr(dac), dp, seed, site, ptr(qv), ptr(pos),
+                                         pos.stride(0) if pos is not None else 0, ptr(dqv), ptr(dpos),
+                                         dpos.stride(0) if dpos is not None else 0, stream_ptr()), "relattn_bwd")
     return dac
 
 

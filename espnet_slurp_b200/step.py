@@ -208,21 +208,22 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
     K.gemm(g, c, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
+    dpp = torch.zeros(Pn, d, device=x.device, dtype=F32)
     if fb:
-        # fused backward (keys <= 192): dP, dS and dropout(p) stay on the SM; dq_u, dk, dv come out of one kernel
+        # fused backward (keys <= 192): dP, dS, dropout(p) and d(matrix_bd) stay on the SM; dq_u, dq_v, dk, dv and the
+        # gradient of the projected positions come out of ONE kernel
         dqu = torch.empty(B * T, d, device=x.device, dtype=dc.dtype)
-        dac = K.relattn_bwd(dc, qu, k, v, pr, c, B, T, T, H, cfg.rel_pos_type, scale, dqu, dqkv[:, d:2 * d], dqkv[:, 2 * d:],
-                            drop=da, want_dac=True)
-        dbd = K.rel_unshift(dac, T, cfg.rel_pos_type, ld_bd)
+        dqv = torch.empty_like(dqu)
+        K.relattn_bwd(dc, qu, k, v, pr, c, B, T, T, H, cfg.rel_pos_type, scale, dqu, dqkv[:, d:2 * d], dqkv[:, 2 * d:], drop=da,
+                      qv=qv, pos=pp, dqv=dqv, dpos=dpp)
     else:
         dpd = K.attn_f1(dc, v, B, T, T, H)
         K.attn_f3(pd, dc, B, T, T, H, out=dqkv[:, 2 * d:])
         dac, dbd = K.softmax_bwd(dpd, pr, T, cfg.rel_pos_type, scale, ld_bd=ld_bd, drop=da)
         dqu = K.attn_f2(dac, k, B, T, T, H)
         K.attn_f3(dac, qu, B, T, T, H, out=dqkv[:, d:2 * d])
-    dqv = K.attn_f2(dbd, pp, B, T, Pn, H, y_bcast=True)
-    dpp = torch.zeros(Pn, d, device=x.device, dtype=F32)
-    K.attn_f4(dbd, qv, B, T, Pn, H, dpp)
+        dqv = K.attn_f2(dbd, pp, B, T, Pn, H, y_bcast=True)
+        K.attn_f4(dbd, qv, B, T, Pn, H, dpp)
     K.gemm(K.cast_bf16(dpp), pos16, trans=True, out=G[a + ".linear_pos.weight"], accumulate=True)
     K.pos_bias_bwd(dqu, dqv, dqkv[:, :d], G[a + ".pos_bias_u"].reshape(-1), G[a + ".pos_bias_v"].reshape(-1))
     K.colsum(dqkv, G[a + ".linear_qkv.bias"])

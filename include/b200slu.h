@@ -185,17 +185,20 @@ int b200slu_relattn_fwd(const void* q_u, const void* q_v, long long ldq, const v
                         const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk, int relpos_mode,
                         int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx, long long ldctx, float drop_p,
                         unsigned long long seed, unsigned int site, void* stream);
-/* Backward of the same, keys <= 192 (b200slu_relattn_bwd_supported): autograd through attention.py:78-95 and the
- * matmuls of :297-302 / :111-113 in ONE kernel -- dP = dO . v^T and dS = p (m dP - <dO, O>) scale stay on the SM
- * (tensor memory / shared memory), dq_u = dS . k, dk = dS^T . q_u, dv = dropout(p)^T . dO are written as bf16 rows
- * (utterance, frame) x head slices like their forward counterparts.  d_ctx = gradient of the merged-head context,
- * p = the probabilities the forward saved, ctx = the forward's context output.  d_ac (optional, bf16 [H,B,Tq,ld_p]):
- * dS in the shifted layout, for the rel-pos position terms (b200slu_rel_unshift + the batched GEMMs). */
+/* Backward of the same, keys <= 192 (b200slu_relattn_bwd_supported): autograd through attention.py:78-95, the matmuls of
+ * :297-302 / :111-113 and rel_shift (:240-263) in ONE kernel -- dP = dO . v^T, dS = p (m dP - <dO, O>) scale, dropout(p)
+ * and d(matrix_bd) (dS skewed back into position-window coordinates) stay on the SM (tensor memory / shared memory);
+ * dq_u = dS . k, dk = dS^T . q_u, dv = dropout(p)^T . dO and, in rel-pos mode, dq_v = d(bd) . pos are written as bf16
+ * rows (utterance, frame) x head slices like their forward counterparts; dpos_accum (fp32 [2T-1, lddpos], gradient of the
+ * projected positions, summed over utterances) is ACCUMULATED.  d_ctx = gradient of the merged-head context, p = the
+ * probabilities the forward saved, ctx = the forward's context output.  d_ac (optional, bf16 [H,B,Tq,ld_p]) receives dS.
+ * q_v / pos / dq_v / dpos_accum: rel-pos mode only (NULL otherwise); dq_v shares dq_u's row stride. */
 int b200slu_relattn_bwd_supported(int Tq, int Tk, int dk, int relpos_mode);
 int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
                         long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H, int Tq,
                         int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk, void* dv, long long lddkv,
-                        void* d_ac, float drop_p, unsigned long long seed, unsigned int site, void* stream);
+                        void* d_ac, float drop_p, unsigned long long seed, unsigned int site, const void* q_v, const void* pos,
+                        long long ldpos, void* dq_v, float* dpos_accum, long long lddpos, void* stream);
 /* d(matrix_bd) [H,B,T,ld_bd] (un-shifted) from d(scores) [H,B,T,ld_p] (shifted): the scatter of rel_shift's backward
  * (attention.py:240-263), latest mode. */
 int b200slu_rel_unshift(const void* d_scores, long long ld_p, int H, int B, int T, int relpos_mode, void* d_bd, long long ld_bd,

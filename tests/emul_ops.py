@@ -271,8 +271,10 @@ def relattn_bwd_supported(Tq, Tk, dk, mode):
     return relattn_supported(Tq, Tk, dk, mode)
 
 
-def relattn_bwd(dctx, qu, k, v, p, ctx, B, Tq, Tk, H, mode, scale, dq, dk, dv, drop=None, want_dac=False):
-    """the fused backward = the unfused chain: dPd = dO v^T, dS = p (m dPd - <dO, O>) scale, dq = dS k, dk = dS^T q, dv = pd^T dO"""
+def relattn_bwd(dctx, qu, k, v, p, ctx, B, Tq, Tk, H, mode, scale, dq, dk, dv, drop=None, want_dac=False, qv=None, pos=None,
+                dqv=None, dpos=None):
+    """the fused backward = the unfused chain: dPd = dO v^T, dS = p (m dPd - <dO, O>) scale, dq = dS k, dk = dS^T q, dv = pd^T dO,
+    and in rel-pos mode d(bd) = unshift(dS), dq_v = d(bd) pos, dpos += d(bd)^T q_v"""
     dpd = attn_f1(dctx, v, B, Tq, Tk, H)
     m = _mul(drop, p.shape)
     pf = p.float()
@@ -287,6 +289,11 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B, Tq, Tk, H, mode, scale, dq, dk, dv, d
     attn_f2(ds, k, B, Tq, Tk, H, out=dq)
     attn_f3(ds, qu, B, Tq, Tk, H, out=dk)
     attn_f3(_r(pd), dctx, B, Tq, Tk, H, out=dv)
+    if mode == "latest":
+        Pn = pos.shape[0]
+        dbd = rel_unshift(ds, Tq, mode, round8(Pn))
+        attn_f2(dbd, pos, B, Tq, Pn, H, out=dqv, y_bcast=True)
+        attn_f4(dbd, qv, B, Tq, Pn, H, dpos)
     return ds if want_dac else None
 
 

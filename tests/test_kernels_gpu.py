@@ -253,19 +253,27 @@ def test_fused_attention_bwd(mode, Tq, Tk, drop):
                                 want_pd=False)
     dq = torch.full((B * Tq, 3 * d), 7.0, device="cuda", dtype=BF)   # written through strided views, like dqkv in the step
     dkv = torch.full((B * Tk, 2 * d), 7.0, device="cuda", dtype=BF)
+    rel = mode == "latest"
+    Pn = 2 * Tq - 1
+    dqv = torch.full((B * Tq, 3 * d), 7.0, device="cuda", dtype=BF) if rel else None
+    dpos = torch.ones(Pn, d, device="cuda") if rel else None   # accumulated into
     dac = K().relattn_bwd(dctx.cuda(), qu_c, kv_c[:, :d], kv_c[:, d:], p, ctx, B, Tq, Tk, H, mode, 0.125, dq[:, d:2 * d], dkv[:, :d],
-                          dkv[:, d:], drop=drop, want_dac=True)
+                          dkv[:, d:], drop=drop, want_dac=True, qv=qv.cuda() if rel else None, pos=pos.cuda() if rel else None,
+                          dqv=dqv[:, d:2 * d] if rel else None, dpos=dpos)
     torch.cuda.synchronize()
     wdq, wdk, wdv = torch.zeros(B * Tq, d), torch.zeros(B * Tk, d), torch.zeros(B * Tk, d)
+    wdqv, wdpos = (torch.zeros(B * Tq, d), torch.ones(Pn, d)) if rel else (None, None)
     wdac = E.relattn_bwd(dctx, qkv[:, :d], kv[:, :d], kv[:, d:], p.float().cpu(), ctx.float().cpu(), B, Tq, Tk, H, mode, 0.125, wdq,
-                         wdk, wdv, drop=drop, want_dac=True)
+                         wdk, wdv, drop=drop, want_dac=True, qv=qv if rel else None, pos=pos, dqv=wdqv, dpos=wdpos)
     close(dac[..., :Tk], wdac[..., :Tk], 2e-2, "dS")
     close(dq[:, d:2 * d], wdq, 2e-2, "dq_u")
     close(dkv[:, :d], wdk, 2e-2, "dk")
     close(dkv[:, d:], wdv, 2e-2, "dv")
     assert (dq[:, :d] == 7.0).all() and (dq[:, 2 * d:] == 7.0).all()  # neighbours of the strided outputs untouched
-    if mode == "latest":
-        Pn = 2 * Tq - 1
+    if rel:
+        close(dqv[:, d:2 * d], wdqv, 2e-2, "dq_v")
+        close(dpos, wdpos, 2e-2, "d(projected positions)")
+        assert (dqv[:, :d] == 7.0).all() and (dqv[:, 2 * d:] == 7.0).all()
         dbd = K().rel_unshift(dac, Tq, mode, E.round8(Pn))
         wdbd = E.rel_unshift(dac.float().cpu(), Tq, mode, E.round8(Pn))
         assert torch.equal(dbd.float().cpu()[..., :Pn], wdbd[..., :Pn])

@@ -45,7 +45,9 @@ def test_graph_buckets_match_eager_and_evict():
         lg = graph({k: v.pin_memory() for k, v in b.items()}, fetch_loss=True).clone()  # host inputs, like the e2e path
         torch.cuda.synchronize()
         # same kernels, same inputs; only the order of the floating-point atomics differs from run to run
-        np.testing.assert_allclose(lg.cpu().numpy(), le.cpu().numpy(), rtol=1e-2, atol=1e-4, err_msg=f"step {i}")
+        # (losses; the accuracy is an argmax count over ~10 tokens: one near-tie flips it by 1 / #tokens)
+        np.testing.assert_allclose(lg.cpu().numpy()[:3], le.cpu().numpy()[:3], rtol=1e-2, atol=1e-4, err_msg=f"step {i}")
+        assert abs(float(lg[3]) - float(le[3])) <= 0.15
         np.testing.assert_allclose(graph.loss_host.numpy(), lg.cpu().numpy(), rtol=0, atol=0)
     assert len(graph.buckets) == 2 and all(b.graph is not None for b in graph.buckets.values())
     assert all(b.eager_steps == 1 for b in graph.buckets.values())  # one eager step per shape, replays afterwards
@@ -129,7 +131,8 @@ def test_chained_graph_segments_replay_like_one_graph():
         le = eager({k: v.cuda() for k, v in b.items()}).clone()
         lc = chain({k: v.cuda() for k, v in b.items()}).clone()
         torch.cuda.synchronize()
-        np.testing.assert_allclose(lc.cpu().numpy(), le.cpu().numpy(), rtol=1e-2, atol=1e-4, err_msg=f"step {i}")
+        np.testing.assert_allclose(lc.cpu().numpy()[:3], le.cpu().numpy()[:3], rtol=1e-2, atol=1e-4, err_msg=f"step {i}")
+        assert abs(float(lc[3]) - float(le[3])) <= 0.15
     bk = next(iter(chain.buckets.values()))
     assert [st for _, st in bk.graph] == ["heads", "enc1", None]  # three segments, replayed in capture order
     pe, pc = eager.state_dict(), chain.state_dict()

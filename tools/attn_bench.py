@@ -61,26 +61,31 @@ def main():
     flops = B * H * (4.0 * T * T * 64 + (2.0 * T * Pn * 64 if rel else 0))
     tf, tu = timeit(fused), timeit(unfused)
     print(f"fwd  B={B} T={T} H={H} mode={a.mode} drop={a.drop}: fused {tf:.1f} us ({flops / tf * 1e-6:.0f} TFLOP/s)  unfused chain {tu:.1f} us")
-    if a.bwd and hasattr(K, "relattn_bwd"):
-        pr, pd, c = fused()
+    if a.bwd:
+        pr, pd, c = K.relattn_fwd(qu, qv if rel else None, k, v, pos if rel else None, lens, B, T, T, H, a.mode, False, 0.125,
+                                  drop=drop, want_pd=True)
         dc = torch.randn(B * T, d, device=dev, generator=g).bfloat16()
         dqkv = torch.empty_like(qkv)
+        dqu, dqv = torch.empty(B * T, d, device=dev, dtype=torch.bfloat16), torch.empty(B * T, d, device=dev, dtype=torch.bfloat16)
+        dpp = torch.zeros(Pn, d, device=dev)
 
         def fused_b():
-            return K.relattn_bwd(dc, qu, qv if rel else None, k, v, pos if rel else None, pr, lens, B, T, T, H, a.mode, False,
-                                 0.125, dqkv, drop=drop)
+            return K.relattn_bwd(dc, qu, k, v, pr, c, B, T, T, H, a.mode, 0.125, dqu, dqkv[:, d:2 * d], dqkv[:, 2 * d:], drop=drop,
+                                 qv=qv if rel else None, pos=pos if rel else None, dqv=dqv if rel else None, dpos=dpp if rel else None)
 
         def unfused_b():
             dpd = K.attn_f1(dc, v, B, T, T, H)
             K.attn_f3(pd, dc, B, T, T, H, out=dqkv[:, 2 * d:])
             dac, dbd = K.softmax_bwd(dpd, pr, T, a.mode, 0.125, ld_bd=K.round8(Pn), drop=drop)
-            dqu = K.attn_f2(dac, k, B, T, T, H)
+            K.attn_f2(dac, k, B, T, T, H, out=dqu)
             K.attn_f3(dac, qu, B, T, T, H, out=dqkv[:, d:2 * d])
             if rel:
-                K.attn_f2(dbd, pos, B, T, Pn, H, y_bcast=True)
-            return dqu
+                K.attn_f2(dbd, pos, B, T, Pn, H, y_bcast=True, out=dqv)
+                K.attn_f4(dbd, qv, B, T, Pn, H, dpp)
 
-        print(f"bwd: fused {timeit(fused_b):.1f} us  unfused chain {timeit(unfused_b):.1f} us")
+        bflops = B * H * (8.0 * T * T * 64 + (4.0 * T * Pn * 64 if rel else 0))
+        tb, tub = timeit(fused_b), timeit(unfused_b)
+        print(f"bwd  B={B} T={T} H={H} mode={a.mode} drop={a.drop}: fused {tb:.1f} us ({bflops / tb * 1e-6:.0f} TFLOP/s)  unfused chain {tub:.1f} us")
 
 
 if __name__ == "__main__":
