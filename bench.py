@@ -312,6 +312,8 @@ class Trainer:
         # Graph capture is driven explicitly below (eager_steps_before_capture is never reached) so that the launches of
         # one eager step can be counted first.
         self.ts = TrainStep(cfg, make_state_dict(cfg), rank, world, dp_mode=args.dp_mode, use_graph=False)
+        if os.environ.get("B200SLU_BENCH_FORCE_CUTS"):  # tuning: the chain-of-graphs capture on one GPU (cost of the cuts alone)
+            self.ts.force_cuts = tuple(s for s, _, _ in self.ts.reducer.stages if s != "front")
         self.host_batches, self.dev_batches, self.flens, self.done = [], [], [], []
         self.gen = torch.Generator().manual_seed(99 + rank)
         for i in range(4):

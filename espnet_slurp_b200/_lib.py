@@ -103,6 +103,7 @@ _SIGNATURES = {
     "b200slu_lsm_static_max_rows": [],
     "b200slu_lsm_loss_fwd_bwd_static": [_P, _L, _L, _I, _P, _I, _F, _F, _P, _P, _P, _L, _P],
     "b200slu_vocab_softmax_fwd": [_P, _L, _L, _I, _P, _L, _P],
+    "b200slu_vocab_log_softmax_fwd": [_P, _L, _L, _I, _P, _L, _P],
     "b200slu_vocab_softmax_bwd": [_P, _L, _P, _L, _L, _I, _P, _L, _P, _L, _P],
     "b200slu_global_mvn_fwd": [_P, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200slu_specaug_mvn_fwd": [_P, _I, _I, _I, _P, _P, _P, _P, _I, _P, _I, _I, _P, _P],

@@ -132,6 +132,24 @@ __global__ void __launch_bounds__(256) vocab_softmax_fwd_kernel(const float* __r
   for (int j = lane; j < ldp; j += 32) pr[j] = __float2bfloat16(j < V ? __expf(xr[j] - m) * inv : 0.f);
 }
 
+// y = log_softmax(logits[:, :V]) in fp32 (decoding: transformer_decoder.py:181, ctc.py:109-117).  One warp per row, exact
+// logf / expf (the scores feed a beam search that compares hypotheses).
+__global__ void __launch_bounds__(256) vocab_log_softmax_kernel(const float* __restrict__ x, long long ldx, long long R, int V,
+                                                                float* __restrict__ y, long long ldy) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= R) return;
+  const float* xr = x + row * ldx;
+  float m = -INFINITY;
+  for (int j = lane; j < V; j += 32) m = fmaxf(m, xr[j]);
+  m = warp_max(m);
+  float s = 0.f;
+  for (int j = lane; j < V; j += 32) s += expf(xr[j] - m);
+  const float lse = m + logf(warp_sum(s));
+  float* yr = y + row * ldy;
+  for (int j = lane; j < V; j += 32) yr[j] = xr[j] - lse;
+}
+
 // dlogits = p * (dp - sum_j p_j dp_j) (+ add): softmax backward over the vocabulary, bf16 in, bf16 out, padding columns 0.
 __global__ void __launch_bounds__(256) vocab_softmax_bwd_kernel(const bf16* __restrict__ p, long long ldp,
                                                                 const bf16* __restrict__ dp, long long lddp, long long R, int V,
@@ -163,6 +181,16 @@ extern "C" int b200slu_vocab_softmax_fwd(const float* logits, long long ldv, lon
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_LOSS, st, 0, (double)R * V * 6.0);
   vocab_softmax_fwd_kernel<<<(unsigned)((R + 7) / 8), 256, 0, st>>>(logits, ldv, R, V, (bf16*)probs_bf16, ldp);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_vocab_log_softmax_fwd(const float* logits, long long ldv, long long R, int V, float* out, long long ldo,
+                                             void* stream) {
+  B2_CHECK_ARG(R > 0 && V > 0 && ldv >= V && ldo >= V && out != nullptr, "vocab_log_softmax_fwd: bad shape R=%lld V=%d", R, V);
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_LOSS, st, 0, (double)R * V * 8.0);
+  vocab_log_softmax_kernel<<<(unsigned)((R + 7) / 8), 256, 0, st>>>(logits, ldv, R, V, out, ldo);
   B2_LAUNCH_CHECK();
   return 0;
 }

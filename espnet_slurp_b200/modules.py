@@ -93,8 +93,14 @@ class _Packed(nn.Module):
         owner = owner() if owner is not None else None
         if owner is not None and not any(sub is self for sub in (owner.encoder, owner.decoder, owner.ctc)):
             owner = None  # a copy of the sub-module that still carries the original model's link
-        pp = (owner if owner is not None else self)._pack()
-        pp.refresh()
+        holder = owner if owner is not None else self
+        pp = holder._pack()
+        # the bf16 copies are refreshed only when a parameter changed since the last scoring call (a decoding loop calls
+        # this once per hypothesis step: re-casting 109 M parameters each time would dominate it)
+        ver = sum(int(p._version) for p in holder.parameters()) + 7919 * id(pp)
+        if holder.__dict__.get("_infer_ver") != ver:
+            pp.refresh()
+            holder.__dict__["_infer_ver"] = ver
         return pp
 
     def __getstate__(self):  # pickling / deepcopy: the flat buffers and the owner link are rebuilt on first use
@@ -611,11 +617,14 @@ class TransformerDecoder(_Packed):
         """transformer_decoder.py:147-184.  tgt int64 (batch, maxlen_out) prefix, memory (batch, maxlen_in, feat) without
         a mask; returns (log-probs of the next token (batch, vocab), per-layer outputs (batch, maxlen_out, size)).
 
-        The reference's cache only spares the query side of the earlier positions: keys / values of the whole prefix and
-        of the whole memory are projected again at every step (decoder_layer.py:84-123), and the memory projection
-        (maxlen_in rows) dominates.  Here the prefix is re-run causally through the same kernels as the training
-        forward (dropout off), which yields the identical rows (the invariant of test/test_transformer_decode.py) for
-        the same dominant cost; `cache` is checked for shape and otherwise not needed."""
+        With ``cache`` (per layer, the outputs of the earlier positions, decoder_layer.py:84-98) only the LAST position is a
+        query: one row per hypothesis goes through the projections, both attentions, the FFN and the output layer, the
+        layer's output row is appended to its cache.  Keys / values of the prefix are projected from the cached layer
+        inputs like the reference does (:100-110); the keys / values of the MEMORY -- maxlen_in rows per layer, which the
+        reference projects again at every step (:112-123) and which dominate its cost -- are projected once per memory
+        tensor and kept (`_mem_kv`).  Without a cache (first step, or a caller that passes none) the whole prefix runs
+        causally through the training kernels with dropout off; both give the same rows (the invariant of
+        test/test_transformer_decode.py)."""
         _need_cuda(memory, "TransformerDecoder")
         B, L = tgt.shape
         T, d = memory.shape[1], memory.shape[2]
@@ -624,6 +633,8 @@ class TransformerDecoder(_Packed):
             assert len(cache) == n_layers and all(c.shape == (B, L - 1, d) for c in cache), \
                 ([tuple(c.shape) for c in cache], (B, L - 1, d))
         dev = memory.device
+        if cache is not None and L > 1:
+            return self._one_step_cached(tgt, memory, cache)
         with torch.no_grad():
             pp = self._infer_pack()
             mem16 = S.K.cast_bf16(memory.float().contiguous().view(B * T, d))
@@ -636,7 +647,80 @@ class TransformerDecoder(_Packed):
             outs = [layers[n + 1][0] for n in range(n_layers - 1)] + [x_last]
             new_cache = [o.view(B, L, d) for o in outs]
             V = self._cfg.vocab
-            y = torch.log_softmax(logits.view(B, L, -1)[:, -1, :V], dim=-1)
+            y = S.K.vocab_log_softmax(logits.view(B, L, -1)[:, -1].contiguous(), V)
+        return y, new_cache
+
+    def _attend(self, q, k, v, lens, B: int, Tq: int, Tk: int):
+        """softmax(q k^T / sqrt(d_k)) v over the first lens[b] keys (attention.py:98-114), no dropout: the fused kernel
+        when the keys fit it, else the batched contractions + softmax kernel."""
+        K, cfg = S.K, self._cfg
+        H, scale = cfg.heads, 1.0 / math.sqrt(cfg.d // cfg.heads)
+        if K.relattn_supported(Tq, Tk, cfg.d // H, "none"):
+            return K.relattn_fwd(q, None, k, v, None, lens, B, Tq, Tk, H, "none", False, scale)[2]
+        ac = K.attn_f1(q, k, B, Tq, Tk, H)
+        pr, _ = K.softmax_fwd(ac, None, lens, Tk, "none", False, scale)
+        return K.attn_f2(pr, v, B, Tq, Tk, H)
+
+    def _memory_kv(self, memory: torch.Tensor, pp):
+        """Per layer, linear_k / linear_v of the encoder memory (bf16 [B*T, 2d]); computed once per memory tensor."""
+        key = (memory.data_ptr(), tuple(memory.shape), tuple(memory.stride()), int(memory._version), id(pp),
+               self.__dict__.get("_infer_ver"))
+        memo = self.__dict__.get("_mem_kv")
+        if memo is None or memo[0] != key:
+            B, T, d = memory.shape
+            mem16 = S.K.cast_bf16(memory.float().contiguous().view(B * T, d))
+            kvs = []
+            for n in range(len(self.decoders)):
+                a = f"decoder.decoders.{n}.src_attn"
+                kvs.append(S.K.gemm(mem16, pp.W[a + ".linear_kv.weight"], bias=pp.P[a + ".linear_kv.bias"]))
+            memo = self.__dict__["_mem_kv"] = (key, kvs)
+        return memo[1]
+
+    def _one_step_cached(self, tgt: torch.Tensor, memory: torch.Tensor, cache: List[torch.Tensor]):
+        K, cfg = S.K, self._cfg
+        B, L = tgt.shape
+        T, d = memory.shape[1], memory.shape[2]
+        dev = memory.device
+        with torch.no_grad():
+            pp = self._infer_pack()
+            P, W = pp.P, pp.W
+            mkv = self._memory_kv(memory, pp)
+            mlens = torch.full((B,), T, device=dev, dtype=torch.int32)
+            ylens = torch.full((B,), L, device=dev, dtype=torch.int32)
+            # the embedded prefix (transformer_decoder.py:166, embedding.py:82-94): layer 0's input; a gather, no cache needed
+            x_emb = K.embed_fwd(P["decoder.embed.0.weight"], _i32(tgt, dev).contiguous().view(-1), S.pos_table("abs", L, d, dev), L,
+                                math.sqrt(d))                                           # [B*L, d]
+            x_new = x_emb.view(B, L, d)[:, -1].contiguous()                            # [B, d]
+            new_cache = []
+            for n in range(len(self.decoders)):
+                p = f"decoder.decoders.{n}"
+                # this layer's input over the whole prefix: the embedded prefix for layer 0, else the previous layer's cached
+                # outputs + its new row (exactly what new_cache[n - 1] holds)
+                x_full = x_emb if n == 0 else new_cache[n - 1].view(B * L, d)
+                ln1, _, _ = K.layernorm_fwd(x_full, P[p + ".norm1.weight"], P[p + ".norm1.bias"])
+                wq = W[p + ".self_attn.linear_qkv.weight"]
+                bq = P[p + ".self_attn.linear_qkv.bias"]
+                kv = K.gemm(ln1, wq[d:], bias=bq[d:])                                   # prefix keys / values [B*L, 2d]
+                q = K.gemm(ln1.view(B, L, d)[:, -1], wq[:d], bias=bq[:d])              # the last position is the only query
+                c1 = self._attend(q, kv[:, :d], kv[:, d:], ylens, B, 1, L)
+                x1 = K.gemm(c1, W[p + ".self_attn.linear_out.weight"], bias=P[p + ".self_attn.linear_out.bias"],
+                            residual=x_new, out_dtype=torch.float32)
+                ln2, _, _ = K.layernorm_fwd(x1, P[p + ".norm2.weight"], P[p + ".norm2.bias"])
+                q2 = K.gemm(ln2, W[p + ".src_attn.linear_q.weight"], bias=P[p + ".src_attn.linear_q.bias"])
+                c2 = self._attend(q2, mkv[n][:, :d], mkv[n][:, d:], mlens, B, 1, T)
+                x2 = K.gemm(c2, W[p + ".src_attn.linear_out.weight"], bias=P[p + ".src_attn.linear_out.bias"], residual=x1,
+                            out_dtype=torch.float32)
+                ln3, _, _ = K.layernorm_fwd(x2, P[p + ".norm3.weight"], P[p + ".norm3.bias"])
+                hdn = K.gemm(ln3, W[p + ".feed_forward.w_1.weight"], bias=P[p + ".feed_forward.w_1.bias"], act="relu")
+                x3 = K.gemm(hdn, W[p + ".feed_forward.w_2.weight"], bias=P[p + ".feed_forward.w_2.bias"], residual=x2,
+                            out_dtype=torch.float32)
+                new_cache.append(torch.cat([cache[n].to(torch.float32), x3.view(B, 1, d)], 1))
+                x_new = x3
+            lnf, _, _ = K.layernorm_fwd(x_new, P["decoder.after_norm.weight"], P["decoder.after_norm.bias"])
+            V = cfg.vocab
+            logits = torch.empty(B, K.round8(V), device=dev, dtype=torch.float32)
+            K.gemm(lnf, W["decoder.output_layer.weight"], bias=P["decoder.output_layer.bias"], out=logits)
+            y = K.vocab_log_softmax(logits, V)
         return y, new_cache
 
     def score(self, ys: torch.Tensor, state, x: torch.Tensor):
@@ -685,16 +769,21 @@ class CTC(_Packed):
         out = torch.empty(B * T, S.K.round8(V), device=hs_pad.device, dtype=torch.float32)
         S.K.gemm(S.K.cast_bf16(hs_pad.float().contiguous().view(B * T, d)), pp.W["ctc.ctc_lo.weight"],
                  bias=pp.P["ctc.ctc_lo.bias"], out=out)
-        return out[:, :V].reshape(B, T, V)
+        return out
 
     def softmax(self, hs_pad):
-        return torch.softmax(self._logits(hs_pad), dim=2)
+        return self.log_softmax(hs_pad).exp()
 
     def log_softmax(self, hs_pad):
-        return torch.log_softmax(self._logits(hs_pad), dim=2)
+        """ctc.py:109-117 on the fp32 log-softmax kernel (no torch op on the scoring path)."""
+        B, T, _ = hs_pad.shape
+        with torch.no_grad():
+            return S.K.vocab_log_softmax(self._logits(hs_pad), self._odim).view(B, T, self._odim)
 
     def argmax(self, hs_pad):
-        return torch.argmax(self._logits(hs_pad), dim=2)
+        B, T, _ = hs_pad.shape
+        with torch.no_grad():
+            return torch.argmax(self._logits(hs_pad)[:, :self._odim], dim=1).view(B, T)
 
 
 class ESPnetASRModel(_Packed):

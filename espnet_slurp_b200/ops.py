@@ -446,6 +446,14 @@ def vocab_softmax_fwd(logits, V: int):
     return out
 
 
+def vocab_log_softmax(logits, V: int):
+    """log_softmax over the first V columns of f32 [R, ld] -> f32 [R, V]."""
+    R, ldv = logits.shape
+    out = torch.empty(R, V, device=logits.device, dtype=torch.float32)
+    check(_lib.lib().b200slu_vocab_log_softmax_fwd(ptr(logits), ldv, R, V, ptr(out), V, stream_ptr()), "vocab_log_softmax")
+    return out
+
+
 def vocab_softmax_bwd(sm, dsm, V: int, add=None):
     """dlogits = sm * (dsm - <sm, dsm>) (+ add), bf16 [R, round8(V)]."""
     R = sm.shape[0]

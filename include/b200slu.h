@@ -267,6 +267,9 @@ int b200slu_lsm_loss_fwd_bwd_static(const float* logits, long long ldv, long lon
  * dlogits = probs * (dprobs - <probs, dprobs>) (+ add), bf16 [R, ldd]. */
 int b200slu_vocab_softmax_fwd(const float* logits, long long ldv, long long R, int V, void* probs_bf16, long long ldp,
                               void* stream);
+/* N2 (decoding): out = log_softmax(logits[:, :V]) in fp32 -- the scores of TransformerDecoder.forward_one_step
+ * (espnet2/asr/decoder/transformer_decoder.py:181) and CTC.log_softmax (espnet2/asr/ctc.py:109-117). */
+int b200slu_vocab_log_softmax_fwd(const float* logits, long long ldv, long long R, int V, float* out, long long ldo, void* stream);
 int b200slu_vocab_softmax_bwd(const void* probs_bf16, long long ldp, const void* dprobs_bf16, long long lddp, long long R, int V,
                               const void* add_bf16, long long ldadd, void* dlogits_bf16, long long ldd, void* stream);
 

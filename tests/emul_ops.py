@@ -465,6 +465,10 @@ def vocab_softmax_fwd(logits, V):
     return _r(out)
 
 
+def vocab_log_softmax(logits, V):
+    return torch.log_softmax(logits[:, :V].float(), dim=-1)
+
+
 def vocab_softmax_bwd(sm, dsm, V, add=None):
     """dlogits = sm * (dsm - sum(sm * dsm)) (+ add) over the first V columns; padding columns 0."""
     s, d = sm[:, :V].float(), dsm[:, :V].float()

@@ -392,3 +392,32 @@ def test_specaug_and_mvn_modules():
     z, _ = m.UtteranceMVN()(x, lens)
     for b in range(4):
         assert z[b, : int(lens[b])].mean(0).abs().max().item() < 1e-4
+
+
+def test_cached_one_step_matches_prefix_rerun_at_real_sizes():
+    """N2: forward_one_step with the per-layer cache (last position is the only query, memory keys / values projected once)
+    against the uncached prefix re-run and against the oracle's cached step, d = 512 / 8 heads (the fused attention kernel
+    with one query row), beam of 5 hypotheses over a 155-frame memory, 7 steps."""
+    m = M()
+    V, d, H, F, NB = 60, 512, 8, 2048, 2
+    ocfg = om.DecCfg(V, d, H, F, NB)
+    sd = make_sd(om.EncCfg(80, d, H, F, 0, 15, "latest"), ocfg, V, seed=9)
+    dec = m.TransformerDecoder(V, d, H, F, NB).cuda().eval()
+    _load(dec, {k: v.cuda() for k, v in sd.items()}, "decoder.")
+    g = torch.Generator().manual_seed(1)
+    nb, T, L = 5, 155, 7
+    mem = torch.randn(1, T, d, generator=g).cuda().expand(nb, -1, -1)
+    ys = torch.randint(1, V - 1, (nb, L), generator=g).cuda()
+    cache, ocache = None, None
+    osd = {k: v for k, v in sd.items() if k.startswith("decoder.")}
+    for l in range(1, L + 1):
+        lp, cache = dec.forward_one_step(ys[:, :l], None, mem, cache=cache)
+        lp_full, cache_full = dec.forward_one_step(ys[:, :l], None, mem, cache=None)
+        olp, ocache = om.decoder_forward_one_step(ys[:, :l].cpu(), mem.cpu().contiguous(), osd, ocfg, cache=ocache)
+        assert lp.dtype == torch.float32 and lp.shape == (nb, V)
+        np.testing.assert_allclose(lp.cpu().numpy(), lp_full.cpu().numpy(), atol=0.05)
+        np.testing.assert_allclose(lp.cpu().numpy(), olp.numpy(), atol=0.08)
+        for a, b in zip(cache, cache_full):
+            assert a.shape == (nb, l, d)
+            assert (a - b).abs().max().item() < 0.05 * max(1.0, b.abs().max().item())
+    assert "_mem_kv" in dec.__dict__  # the memory projections were computed once and reused
