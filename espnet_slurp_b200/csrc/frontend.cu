@@ -13,6 +13,7 @@
 // zero the padding, mean over valid frames, subtract from ALL frames).  The random draws stay on the
 // host (same torch RNG calls, same order as the reference, Appendix A.15) and arrive as small arrays.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -75,6 +76,119 @@ __global__ void __launch_bounds__(256) logmel_kernel(const float* __restrict__ w
     float acc = 0.f;
     for (int k = 0; k < nbins; ++k) acc += re[k] * melmat[k * n_mels + m];
     out[m] = logf(fmaxf(acc, 1e-10f));
+  }
+}
+
+// Warp-per-frame form of the same computation (n_fft <= 1024): the block-per-frame kernel above spends its time in
+// 9 block-wide barriers per frame, 256 sincospi per frame and a dense 257 x 80 mel product run by 80 threads (0.83 ms
+// for 80 k frames = 0.018 of the HBM roofline its bytes would allow).  Here a block of 8 warps computes the window, the
+// twiddles and, per mel filter, the range of FFT bins with non-zero weight ONCE; then every warp walks its own frames:
+// framing + window into its private shared-memory buffers (bit-reversed), radix-2 stages separated by __syncwarp only,
+// power spectrum, and the mel product over the non-zero range of each filter (Slaney filters overlap two neighbours:
+// ~6 bins per filter instead of 257; exact for any mel matrix, zero weights contribute exactly 0).
+constexpr int LM_WARPS = 8;
+// Shared memory is the bound of an in-place radix-2 FFT (10 shared accesses per butterfly), so the real input is
+// transformed as ONE complex FFT of half the length (z[n] = x[2n] + i x[2n+1]; X[k] = E[k] + e^{-2 pi i k/N} O[k] with
+// E, O from Z[k] and conj(Z[M-k])), and the twiddles of every stage sit contiguously (stage s reads entries
+// half-1 .. 2 half-2: consecutive lanes, consecutive words, instead of a stride that folds 32 lanes onto 2 banks).
+__global__ void __launch_bounds__(LM_WARPS * 32) logmel_warp_kernel(const float* __restrict__ wav, long long ldw, int N,
+                                                                    const int* __restrict__ lens,
+                                                                    const float* __restrict__ melmat, int n_fft, int log2n,
+                                                                    int hop, int n_mels, int T, int B,
+                                                                    float* __restrict__ feats, int* __restrict__ flens) {
+  extern __shared__ float sm[];
+  const int M = n_fft / 2, log2m = log2n - 1, nbins = M + 1, pad = n_fft / 2;
+  float* win = sm;                   // [n_fft]
+  float* twc = win + n_fft;          // [M] per-stage twiddles of the M-point FFT (M - 1 used): cos
+  float* tws = twc + M;              // [M] -sin
+  float* pc = tws + M;               // [M + 1] cos(2 pi k / n_fft)   (split of the real transform)
+  float* ps = pc + (M + 1);          // [M + 1] -sin(2 pi k / n_fft)
+  int* klo = reinterpret_cast<int*>(ps + (M + 1));     // [n_mels] first bin with a non-zero weight
+  int* khi = klo + n_mels;                             // [n_mels] one past the last
+  float* bufs = reinterpret_cast<float*>(khi + n_mels);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* re = bufs + (size_t)warp * (2 * M + nbins + 3);
+  float* im = re + M;
+  float* pw = im + M;                // [M + 1] power spectrum
+  for (int i = threadIdx.x; i < n_fft; i += blockDim.x) win[i] = 0.5f - 0.5f * cospif(2.f * (float)i / (float)n_fft);
+  for (int e = threadIdx.x; e < M - 1; e += blockDim.x) {
+    // entry e belongs to the stage with half = 2^floor(log2(e + 1)), position pos = e - (half - 1): W = exp(-pi i pos / half)
+    const int half = 1 << (31 - __clz(e + 1)), pos = e - (half - 1);
+    float sn, c;
+    sincospif(-(float)pos / (float)half, &sn, &c);
+    twc[e] = c;
+    tws[e] = sn;
+  }
+  for (int k = threadIdx.x; k <= M; k += blockDim.x) {
+    float sn, c;
+    sincospif(-2.f * (float)k / (float)n_fft, &sn, &c);
+    pc[k] = c;
+    ps[k] = sn;
+  }
+  for (int m = threadIdx.x; m < n_mels; m += blockDim.x) {
+    int lo = nbins, hi = 0;
+    for (int k = 0; k < nbins; ++k)
+      if (melmat[k * n_mels + m] != 0.f) {
+        lo = min(lo, k);
+        hi = k + 1;
+      }
+    klo[m] = lo;
+    khi[m] = hi;
+  }
+  if (blockIdx.x == 0 && flens != nullptr)
+    for (int b = threadIdx.x; b < B; b += blockDim.x) flens[b] = (lens[b] + 2 * pad - n_fft) / hop + 1;
+  __syncthreads();
+  const long long frames = (long long)B * T, wstride = (long long)gridDim.x * LM_WARPS;
+  for (long long f = (long long)blockIdx.x * LM_WARPS + warp; f < frames; f += wstride) {
+    const int b = (int)(f / T), t = (int)(f - (long long)b * T);
+    const int olen = (lens[b] + 2 * pad - n_fft) / hop + 1;
+    float* out = feats + f * n_mels;
+    if (t >= olen) {
+      for (int m = lane; m < n_mels; m += 32) out[m] = 0.f;
+      continue;
+    }
+    const float* w = wav + (long long)b * ldw;
+    const int n0 = t * hop - pad;
+    for (int i = lane; i < n_fft; i += 32) {
+      int n = n0 + i;
+      if (n < 0) n = -n;                    // reflect (no edge repeat), over the padded batch width N
+      if (n >= N) n = 2 * (N - 1) - n;
+      const int rev = (int)(__brev((unsigned)(i >> 1)) >> (32 - log2m));
+      ((i & 1) ? im : re)[rev] = w[n] * win[i];
+    }
+    __syncwarp();
+    for (int s = 1; s <= log2m; ++s) {
+      const int half = 1 << (s - 1);
+      const float *tc = twc + (half - 1), *ts = tws + (half - 1);
+      for (int j = lane; j < M / 2; j += 32) {
+        const int grp = j >> (s - 1), pos = j & (half - 1);
+        const int i0 = (grp << s) + pos, i1 = i0 + half;
+        const float c = tc[pos], sn = ts[pos];
+        const float xr = re[i1] * c - im[i1] * sn, xi = re[i1] * sn + im[i1] * c;
+        const float ur = re[i0], ui = im[i0];
+        re[i0] = ur + xr;
+        im[i0] = ui + xi;
+        re[i1] = ur - xr;
+        im[i1] = ui - xi;
+      }
+      __syncwarp();
+    }
+    for (int k = lane; k <= M; k += 32) {
+      const int ka = k & (M - 1), kb = (M - k) & (M - 1);
+      const float zr = re[ka], zi = im[ka], cr = re[kb], ci = -im[kb];   // Z[k], conj(Z[M - k])
+      const float er = 0.5f * (zr + cr), ei = 0.5f * (zi + ci);          // E = (Z + Zc) / 2
+      const float dr = 0.5f * (zr - cr), di = 0.5f * (zi - ci);          // (Z - Zc) / 2 ;  O = -i * that = (di, -dr)
+      const float orr = di, oi = -dr;
+      const float xr = er + pc[k] * orr - ps[k] * oi, xi = ei + pc[k] * oi + ps[k] * orr;
+      pw[k] = xr * xr + xi * xi;
+    }
+    __syncwarp();
+    for (int m = lane; m < n_mels; m += 32) {
+      float acc = 0.f;
+      for (int k = klo[m]; k < khi[m]; ++k) acc += pw[k] * melmat[k * n_mels + m];
+      out[m] = logf(fmaxf(acc, 1e-10f));
+    }
+    __syncwarp();  // the buffers are rewritten by the next frame
   }
 }
 
@@ -211,9 +325,26 @@ extern "C" int b200slu_logmel_fwd(const float* wav, long long ldw, int B, int N,
                "logmel: need power-of-two 4 <= n_fft <= 4096 and N > n_fft/2 (N=%d n_fft=%d)", N, n_fft);
   const int T = N / hop + 1;
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t smem = (size_t)3 * n_fft * sizeof(float);
   B2_SCOPE(FAM_FRONTEND, st, (double)B * T * (5.0 * n_fft * log2n + 2.0 * (n_fft / 2 + 1) * n_mels),
            4.0 * B * N + 4.0 * B * T * n_mels);
+  static const bool old_kernel = getenv("B200SLU_LOGMEL_BLOCK") != nullptr;  // tuning: the block-per-frame kernel
+  if (n_fft <= 1024 && !old_kernel) {
+    const size_t smw = (size_t)(3 * n_fft + 2 + 2 * n_mels + LM_WARPS * (n_fft + n_fft / 2 + 4)) * sizeof(float);
+    const long long frames = (long long)B * T;
+    long long blocks = (frames + LM_WARPS - 1) / LM_WARPS;
+    const long long cap = (long long)b2_num_sms() * (smw <= 48 * 1024 ? 4 : 2);
+    if (blocks > cap) blocks = cap;
+    static unsigned long long cfg = 0;
+    if (smw > 48 * 1024 && !b2_device_done(cfg)) {
+      B2_CUDA(cudaFuncSetAttribute(logmel_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      b2_device_mark(cfg);
+    }
+    logmel_warp_kernel<<<(unsigned)blocks, LM_WARPS * 32, smw, st>>>(wav, ldw, N, lens, melmat, n_fft, log2n, hop, n_mels, T, B, feats,
+                                                                     feat_lens);
+    B2_LAUNCH_CHECK();
+    return 0;
+  }
+  const size_t smem = (size_t)3 * n_fft * sizeof(float);
   logmel_kernel<<<dim3(T, B), 256, smem, st>>>(wav, ldw, N, lens, melmat, n_fft, log2n, hop, n_mels, T, feats, feat_lens);
   B2_LAUNCH_CHECK();
   return 0;
