@@ -91,6 +91,10 @@ _SIGNATURES = {
     "b200slu_conv1_bwd": [_P, _P, _I, _I, _I, _I, _P, _P, _P, _L, _P],
     "b200slu_im2col3x3s2": [_P, _I, _I, _I, _I, _P, _P],
     "b200slu_col2im3x3s2_relu": [_P, _P, _I, _I, _I, _I, _P, _P],
+    "b200slu_conv2_implicit_supported": [_I, _I, _I, _I],
+    "b200slu_conv2_fwd": [_P, _I, _I, _I, _I, _P, _P, _P, _P],
+    "b200slu_conv2_wgrad": [_P, _P, _I, _I, _I, _I, _P, _P],
+    "b200slu_conv2_dgrad_relu": [_P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200slu_ctc_workspace_size": [_I, _I, _I],
     "b200slu_ctc_lattice_states": [_P, _I, _P, _I, _I, _P, _P, _P],
     "b200slu_ctc_fwd": [_P, _L, _I, _I, _I, _P, _P, _I, _P, _I, _P, _P, _P, _P],
@@ -100,6 +104,7 @@ _SIGNATURES = {
     "b200slu_logmel_fwd": [_P, _L, _I, _I, _P, _P, _I, _I, _I, _P, _P, _P],
     "b200slu_set_step_params": [_P],
     "b200slu_adam_step": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _I, _F, _F, _P, _P],
+    "b200slu_adam_step_sched": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _F, _F, _F, _P, _P],
     "b200slu_lsm_static_max_rows": [],
     "b200slu_lsm_loss_fwd_bwd_static": [_P, _L, _L, _I, _P, _I, _F, _F, _P, _P, _P, _L, _P],
     "b200slu_vocab_softmax_fwd": [_P, _L, _L, _I, _P, _L, _P],

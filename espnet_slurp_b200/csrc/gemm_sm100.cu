@@ -27,6 +27,20 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle span
 
+// Implicit-GEMM view of Conv2dSubsampling's second convolution (subsampling.py:56-65: 3x3, stride 2, C -> C channels):
+// one operand's k-blocks (CONV = 1: A, rows = pixels) or column boxes (CONV = 2: B, wgrad) come from a TMA im2col map over
+// the channels-last activation instead of a materialised [pixels, 9 C] matrix.
+struct ConvArgs {
+  int pw, ph;          // pixel grid (per image, w fastest) the GEMM's pixel dimension enumerates
+  int mult;            // tensor-coordinate step between neighbouring pixels (the map's traversal stride)
+  int base_w, base_h;  // tensor coordinates of pixel (0, 0) (the map's lower corner)
+  int cb, C;           // channel blocks of 64 per tap; channels (= columns per tap of the [C, 9 C] weight matrix)
+  unsigned char off_w[9], off_h[9], wtap[9];  // per tap of THIS GEMM: im2col offsets and the weight matrix's tap index
+  // scatter epilogue (dgrad parity classes): pixel (n, hq, wq) of the GEMM is pixel (n, hq*o_mult + o_h0, wq*o_mult + o_w0)
+  // of the [*, OH, OW, C] output; the same position of `aux` gates it (ReLU mask)
+  int o_mult, o_w0, o_h0, OW, OH;
+};
+
 struct EpiArgs {
   const float* bias;
   const float* res;
@@ -43,6 +57,7 @@ struct EpiArgs {
               // 16 = CTA 0 records phase cycle counts into dbg_out (printed by the host after a synchronize)
   long long* dbg_out;
   B2Dropout drop;
+  ConvArgs cv;
 };
 
 // Epilogue feature bits.  A kernel instantiated with EF != EF_GENERIC has its epilogue resolved at compile time: the
@@ -50,7 +65,7 @@ struct EpiArgs {
 // load-constant / test / branch decisions per feature does not fit into (measured: 840 cycles per slice).
 enum : uint32_t {
   EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
-  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_GENERIC = 1u << 31
+  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_SCATTER = 8192u, EF_GENERIC = 1u << 31
 };
 // Epilogue warps: 2 per TMEM lane quadrant for the register-heavy epilogues (168 registers each).
 // 16 warps (4 per quadrant, 64 columns each) halve the epilogue time of the light epilogues (bias-only: 6500 -> 3300
@@ -255,7 +270,7 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
 }
 
 // Persistent: grid = min(#work units, #SMs); unit u = (batch, tile, k-split), tiles n-fastest.
-template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG>
+template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG, int CONV = 0>
 __global__ void __launch_bounds__(num_threads(EF, BN, CG), 1)
 gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_d, int M, int N, int K, int tiles_n, int tiles_per_batch, int batch_inner, int splits, int kb_per_split,
@@ -327,6 +342,14 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         const int kb0 = sp * kb_per_split;
         const int nkb = min(kb_per_split, num_kb_total - kb0);
         const int abi = bi * ep.a_bc_inner, abo = bo * ep.a_bc_outer, bbi = bi * ep.b_bc_inner, bbo = bo * ep.b_bc_outer;
+        int pn0 = 0, pw0 = 0, ph0 = 0;  // CONV = 1: base pixel of this CTA's 128 rows, in tensor coordinates
+        if (CONV == 1) {
+          const int arow = tile_m * TM + (int)cta_rank * BM, per = ep.cv.pw * ep.cv.ph;
+          pn0 = arow / per;
+          const int r2 = arow - pn0 * per, hq = r2 / ep.cv.pw;
+          ph0 = ep.cv.base_h + hq * ep.cv.mult;
+          pw0 = ep.cv.base_w + (r2 - hq * ep.cv.pw) * ep.cv.mult;
+        }
         for (int kb = 0; kb < nkb; ++kb, ++i) {
           const int s = i % STAGES, it = i / STAGES;
           const bool rec = (ep.debug & 16) && blockIdx.x == 0;
@@ -349,6 +372,39 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             if (CG == 2) tma_load_4d_pair(dst, m, fb, c0, c1, c2, c3);
             else tma_load_4d(dst, m, fb, c0, c1, c2, c3);
           };
+          auto load_px = [&](uint32_t dst, const CUtensorMap* m, int c, int w, int h, int n, int tap) {
+            if (CG == 2) tma_load_im2col_4d_pair(dst, m, fb, c, w, h, n, ep.cv.off_w[tap], ep.cv.off_h[tap]);
+            else tma_load_im2col_4d(dst, m, fb, c, w, h, n, ep.cv.off_w[tap], ep.cv.off_h[tap]);
+          };
+          if (CONV == 1) {
+            // k-block = (tap, 64 channels): 128 pixels x 64 channels of the activation, shifted by the tap; the weight
+            // operand's coordinates follow the tap (forward: k = (tap, cin) as stored; dgrad: column block (tap, cin))
+            static_assert(CONV != 1 || !TA, "im2col A operand is K-major");
+            const int kbg = kb0 + kb, tj = kbg / ep.cv.cb, c0 = (kbg - tj * ep.cv.cb) * 64;
+            load_px(sa, &map_a, c0, pw0, ph0, pn0, tj);
+            const int wt = (int)ep.cv.wtap[tj] * ep.cv.C;
+            if (!TB) {
+              load(sb, &map_b, wt + c0, brow, 0, 0);
+            } else {
+#pragma unroll
+              for (int b = 0; b < BNL / 64; ++b) load(sb + b * (64 * BK * 2), &map_b, brow + b * 64 + wt, c0, 0, 0);
+            }
+            continue;
+          }
+          if (CONV == 2) {
+            // wgrad: k = pixels.  A = dy^T as usual; B's 64-column boxes are (tap, 64 channels) of 64 consecutive pixels
+            static_assert(CONV != 2 || (TA && TB), "im2col B operand is MN-major");
+#pragma unroll
+            for (int a = 0; a < BM / 64; ++a) load(sa + a * (64 * BK * 2), &map_a, arow + a * 64, k, 0, 0);
+            const int per = ep.cv.pw * ep.cv.ph, pn = k / per, r2 = k - pn * per, hq = r2 / ep.cv.pw;
+            const int ph = ep.cv.base_h + hq * ep.cv.mult, pw = ep.cv.base_w + (r2 - hq * ep.cv.pw) * ep.cv.mult;
+#pragma unroll
+            for (int b = 0; b < BNL / 64; ++b) {
+              const int ncol = brow + b * 64, tj = ncol / ep.cv.C;
+              load_px(sb + b * (64 * BK * 2), &map_b, ncol - tj * ep.cv.C, pw, ph, pn, tj);
+            }
+            continue;
+          }
           if (!TA) {
             load(sa, &map_a, k, arow, abi, abo);   // box {64 k, 128 rows}
           } else {
@@ -455,6 +511,11 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       er.res = ep.res + (long long)row * ep.ldres;
       er.aux = ep.aux + (long long)row * ep.ldaux;
       er.e0 = (unsigned long long)row * (unsigned long long)N;
+      int spix = -1;  // EF_SCATTER: output pixel of this lane's row
+      if (!(EFC & EF_GENERIC) && (EFC & EF_SCATTER) && row_ok) {
+        const int per = ep.cv.pw * ep.cv.ph, pn = row / per, r2 = row - pn * per, hq = r2 / ep.cv.pw, wq = r2 - hq * ep.cv.pw;
+        spix = (pn * ep.cv.OH + hq * ep.cv.o_mult + ep.cv.o_h0) * ep.cv.OW + wq * ep.cv.o_mult + ep.cv.o_w0;
+      }
       // this warp's bias slice -> shared memory and the first slice's operands -> registers, both before the wait
       // for the accumulator so their latency hides behind the MMAs of the tile
       // The four warps of a column half share one bias slice (tile parity selects the buffer; the named barrier
@@ -509,7 +570,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             tma_load_4d(bn ? stg1 : stg0, &map_d, rbar + bn * 8, c2c, row0, 0, 0);
           }
           mbar_wait(rbar + (nflush & 1u) * 8, (nflush >> 1) & 1u);
-        } else if (box_start) {
+        } else if (box_start && !(!(EFC & EF_GENERIC) && (EFC & EF_SCATTER))) {
           // the bulk store that last read this staging box must have finished reading it
           if (lane == 0) {
             if (two_out || STGB == 1) bulk_wait_read<0>();
@@ -534,7 +595,45 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32 + 16, pb, rb, c1c, N, sl1, lane, so, stg1);
         }
         if (rec) { const long long q1 = clock64(); ep.dbg_out[10] += q1 - q0; q0 = q1; }
-        if (box_end && !(debug & 1)) {
+        if (!(EFC & EF_GENERIC) && (EFC & EF_SCATTER)) {
+          if (box_end) {
+            // the 32 x 64 box leaves row by row: 8 lanes move one row's 128 bytes (4 rows per pass), each row to the pixel its
+            // lane computed above, gated by the ReLU mask read from the same position of `aux`
+            __syncwarp();
+            const int bcol = c0c - 32 + (lane & 7) * 8;
+            const bf16* __restrict__ mask = ep.aux;
+            bf16* __restrict__ outp = reinterpret_cast<bf16*>(ep.out);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint4 hv[4];
+              long long off[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const int rr = (h * 4 + q) * 4 + (lane >> 3);
+                const int px = __shfl_sync(0xffffffffu, spix, rr);
+                off[q] = px >= 0 && bcol < N ? (long long)px * ep.ldc + bcol : -1;
+                if (off[q] >= 0) hv[q] = *reinterpret_cast<const uint4*>(mask + off[q]);
+              }
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const int rr = (h * 4 + q) * 4 + (lane >> 3);
+                uint32_t v[4];
+                lds128u(so + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4), v[0], v[1], v[2], v[3]);
+                if (off[q] >= 0) {
+                  const uint32_t m4[4] = {hv[q].x, hv[q].y, hv[q].z, hv[q].w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const float2 hh = unpack_bf16x2(m4[e]);
+                    if (!(hh.x > 0.f)) v[e] &= 0xffff0000u;
+                    if (!(hh.y > 0.f)) v[e] &= 0x0000ffffu;
+                  }
+                  *reinterpret_cast<uint4*>(outp + off[q]) = make_uint4(v[0], v[1], v[2], v[3]);
+                }
+              }
+            }
+            __syncwarp();  // the box is rewritten by the next slices
+          }
+        } else if (box_end && !(debug & 1)) {
           fence_async_smem();  // generic-proxy writes of every lane -> visible to the async proxy
           __syncwarp();
           const int bcol = (F & EF_F32) ? c0c : c0c - 32;  // first column of the box
@@ -615,11 +714,11 @@ int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, l
   return 0;
 }
 
-template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG>
+template <int BN, int STAGES, bool TA, bool TB, uint32_t EF, int CG, int CONV = 0>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, const CUtensorMap& md, int M, int N, int K, int nbatch, int batch_inner, int splits,
            int kb_per, const EpiArgs& ep, cudaStream_t st) {
   using L = SmemLayout<BN, STAGES, stg_bufs(EF, BN, CG), CG, epi_warps(EF, BN, CG)>;
-  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF, CG>;
+  auto kern = gemm_bf16_tcgen05<BN, STAGES, TA, TB, EF, CG, CONV>;
   static unsigned long long configured = 0;  // per device
   if (!b2_device_done(configured)) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -892,6 +991,183 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
 #undef B2_CASE
 #undef B2_L
 #undef B2_ARGS
+}
+
+// ----------------------------------------------------------------------------- conv.2 as implicit GEMM
+namespace {
+
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// im2col map over a channels-last bf16 tensor [Nimg, H, W, C]: base pixels run over [lower, dim - 1 + upper] per axis in
+// steps of `stride`; a load moves `pixels` consecutive base pixels x 64 channels.
+int make_im2col_map(CUtensorMap* m, const void* base, int Nimg, int H, int W, int C, int lower_w, int lower_h, int upper_w,
+                    int upper_h, int stride, int pixels) {
+  static EncodeIm2colFn enc = nullptr;
+  if (enc == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      enc = (EncodeIm2colFn)p;
+  }
+  if (enc == nullptr) {
+    b200slu_set_error("cuTensorMapEncodeIm2col driver entry point unavailable");
+    return B200SLU_ECUDA;
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Nimg};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {lower_w, lower_h}, upper[2] = {upper_w, upper_h};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper, 64,
+                   (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b200slu_set_error("cuTensorMapEncodeIm2col failed (%d): N=%d H=%d W=%d C=%d corners (%d,%d)/(%d,%d) stride %d", (int)r, Nimg, H,
+                      W, C, lower_w, lower_h, upper_w, upper_h, stride);
+    return B200SLU_ECUDA;
+  }
+  // Drivers up to CUDA 13.1 encode im2col maps of tensors smaller than 128 KB with a flag the hardware path then trips
+  // over (same correction as CUTLASS' make_im2col_tma_copy_desc applies).
+  int drv = 0;
+  if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 && (long long)Nimg * H * W * C * 2 < 131072)
+    reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+  return 0;
+}
+
+struct Conv2Geom {
+  int B, T1, F1, C, T2, F2;
+  long long M;  // output pixels
+};
+
+int conv2_geom(int B, int T1, int F1, int C, Conv2Geom* g) {
+  B2_CHECK_ARG(B > 0 && T1 >= 3 && F1 >= 3 && C > 0 && C % 256 == 0 && C <= 4096, "conv2: B > 0, T1, F1 >= 3, C a multiple of 256 (got B=%d T1=%d F1=%d C=%d)",
+               B, T1, F1, C);
+  g->B = B; g->T1 = T1; g->F1 = F1; g->C = C;
+  g->T2 = (T1 - 3) / 2 + 1;
+  g->F2 = (F1 - 3) / 2 + 1;
+  g->M = (long long)B * g->T2 * g->F2;
+  B2_CHECK_ARG((long long)B * T1 * F1 < (1LL << 30) && T1 < 32768 && F1 < 32768, "conv2: tensor too large for 32-bit pixel indices");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200slu_conv2_implicit_supported(int B, int T1, int F1, int C) {
+  return B > 0 && T1 >= 3 && F1 >= 3 && C > 0 && C % 256 == 0 && C <= 4096 && (long long)B * T1 * F1 < (1LL << 30) && T1 < 32768 &&
+         F1 < 32768;
+}
+
+// h2[(b,t,f), co] = relu(bias[co] + sum_{kt,kf,ci} h1[b, 2t+kt, 2f+kf, ci] * w[co, (kt*3+kf)*C + ci])
+extern "C" int b200slu_conv2_fwd(const void* h1, int B, int T1, int F1, int C, const void* w, const float* bias, void* h2,
+                                 void* stream) {
+  Conv2Geom g;
+  B2_TRY(conv2_geom(B, T1, F1, C, &g));
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CHECK_ARG(((uintptr_t)h1 % 16) == 0 && ((uintptr_t)w % 16) == 0 && ((uintptr_t)h2 % 16) == 0 && ((uintptr_t)bias % 16) == 0,
+               "conv2_fwd: 16-byte aligned operands");
+  const int M = (int)g.M, N = C, K = 9 * C;
+  CUtensorMap ma, mb, mc;
+  B2_TRY(make_im2col_map(&ma, h1, B, T1, F1, C, 0, 0, -2, -2, 2, BM));
+  B2_TRY(make_map(&mb, w, N, K, K, 1, 0, 1, 0, BK, 128));
+  B2_TRY(make_map(&mc, h2, M, N, N, 1, 0, 1, 0, 64, 32, 2));
+  EpiArgs ep{};
+  ep.out = h2; ep.ldc = N; ep.alpha = 1.f; ep.bias = bias; ep.act = B200SLU_ACT_RELU;
+  ep.flags = EF_BIAS | EF_RELU;
+  ep.cv.pw = g.F2; ep.cv.ph = g.T2; ep.cv.mult = 2; ep.cv.base_w = 0; ep.cv.base_h = 0; ep.cv.cb = C / 64; ep.cv.C = C;
+  for (int t = 0; t < 9; ++t) {
+    ep.cv.off_h[t] = (unsigned char)(t / 3);
+    ep.cv.off_w[t] = (unsigned char)(t % 3);
+    ep.cv.wtap[t] = (unsigned char)t;
+  }
+  B2_SCOPE(FAM_GEMM, st, 2.0 * M * N * (double)K, 2.0 * ((double)B * T1 * F1 * C + (double)N * K + (double)M * N));
+  constexpr uint32_t EF = EF_BIAS | EF_RELU;
+  return launch<256, num_stages<256, 2>(EF), false, false, EF, 2, 1>(ma, mb, mc, mc, M, N, K, 1, 1, 1, K / BK, ep, st);
+}
+
+// dw[co, (kt*3+kf)*C + ci] += sum_{b,t,f} dh2[(b,t,f), co] * h1[b, 2t+kt, 2f+kf, ci]      (fp32, accumulated)
+extern "C" int b200slu_conv2_wgrad(const void* dh2, const void* h1, int B, int T1, int F1, int C, float* dw_accum, void* stream) {
+  Conv2Geom g;
+  B2_TRY(conv2_geom(B, T1, F1, C, &g));
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CHECK_ARG(((uintptr_t)h1 % 16) == 0 && ((uintptr_t)dh2 % 16) == 0 && ((uintptr_t)dw_accum % 16) == 0,
+               "conv2_wgrad: 16-byte aligned operands");
+  const int M = C, N = 9 * C, K = (int)g.M;
+  CUtensorMap ma, mb, mc;
+  B2_TRY(make_map(&ma, dh2, K, M, C, 1, 0, 1, 0, 64, BK));
+  B2_TRY(make_im2col_map(&mb, h1, B, T1, F1, C, 0, 0, -2, -2, 2, BK));
+  B2_TRY(make_map(&mc, dw_accum, M, N, N, 1, 0, 1, 0, 32, 32, 4));
+  EpiArgs ep{};
+  ep.out = dw_accum; ep.ldc = N; ep.alpha = 1.f; ep.out_f32 = 1; ep.accumulate = 1;
+  ep.flags = EF_F32 | EF_ACC;
+  ep.cv.pw = g.F2; ep.cv.ph = g.T2; ep.cv.mult = 2; ep.cv.base_w = 0; ep.cv.base_h = 0; ep.cv.cb = C / 64; ep.cv.C = C;
+  for (int t = 0; t < 9; ++t) {
+    ep.cv.off_h[t] = (unsigned char)(t / 3);
+    ep.cv.off_w[t] = (unsigned char)(t % 3);
+    ep.cv.wtap[t] = (unsigned char)t;
+  }
+  // split K (= pixels) so that the (C/256) x (9C/256) pair tiles fill the machine
+  const int num_kb = (K + BK - 1) / BK;
+  const long long tiles = (long long)((M + 255) / 256) * (N / 256), slots = b2_num_sms() / 2;
+  int splits = 1;
+  double best = 1e300;
+  for (int sp = 1; sp <= 64 && sp <= max(1, num_kb / 4); ++sp) {
+    const int kbs = (num_kb + sp - 1) / sp;
+    const double cost = (double)((tiles * sp + slots - 1) / slots) * (kbs * 1.05 + 4.0);
+    if (cost < best * 0.999) {
+      best = cost;
+      splits = sp;
+    }
+  }
+  const int kb_per = (num_kb + splits - 1) / splits;
+  splits = (num_kb + kb_per - 1) / kb_per;
+  B2_SCOPE(FAM_GEMM, st, 2.0 * M * N * (double)K, 2.0 * ((double)B * T1 * F1 * C + (double)M * K) + 4.0 * M * N);
+  constexpr uint32_t EF = EF_F32 | EF_ACC;
+  return launch<256, num_stages<256, 2>(EF), true, true, EF, 2, 2>(ma, mb, mc, mc, M, N, K, 1, 1, splits, kb_per, ep, st);
+}
+
+// dh1[b, r, g, ci] = (h1[b, r, g, ci] > 0) * sum over taps with 2t+kt = r, 2f+kf = g of dh2[(b,t,f), co] * w[co, (kt*3+kf)*C + ci]
+// Gather form, one GEMM per parity class (r & 1, g & 1): 4 / 2 / 2 / 1 taps, no scatter-add and no [pixels, 9 C] matrix.
+extern "C" int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const void* h1, int B, int T1, int F1, int C, void* dh1,
+                                        void* stream) {
+  Conv2Geom g;
+  B2_TRY(conv2_geom(B, T1, F1, C, &g));
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CHECK_ARG(((uintptr_t)h1 % 16) == 0 && ((uintptr_t)dh2 % 16) == 0 && ((uintptr_t)w % 16) == 0 && ((uintptr_t)dh1 % 16) == 0,
+               "conv2_dgrad: 16-byte aligned operands");
+  CUtensorMap mb, mc;
+  B2_TRY(make_map(&mb, w, C, 9 * C, 9 * C, 1, 0, 1, 0, 64, BK));  // [K = co, N = (tap, ci)], N contiguous
+  B2_TRY(make_map(&mc, dh1, (long long)B * T1 * F1, C, C, 1, 0, 1, 0, 64, 32, 2));  // not stored through (scatter epilogue)
+  constexpr uint32_t EF = EF_SCATTER;
+  for (int cls = 0; cls < 4; ++cls) {
+    const int pt = cls >> 1, pf = cls & 1;
+    const int Hc = (T1 - pt + 1) / 2, Wc = (F1 - pf + 1) / 2;  // pixels r = 2a + pt < T1, g = 2b + pf < F1
+    if (Hc <= 0 || Wc <= 0) continue;
+    const int lh = pt == 0 ? -1 : 0, lw = pf == 0 ? -1 : 0;
+    CUtensorMap ma;
+    B2_TRY(make_im2col_map(&ma, dh2, B, g.T2, g.F2, C, lw, lh, Wc - g.F2 + lw, Hc - g.T2 + lh, 1, BM));
+    EpiArgs ep{};
+    ep.out = dh1; ep.ldc = C; ep.alpha = 1.f; ep.aux = (const bf16*)h1; ep.ldaux = C;
+    ep.flags = EF;
+    ep.cv.pw = Wc; ep.cv.ph = Hc; ep.cv.mult = 1; ep.cv.base_w = lw; ep.cv.base_h = lh; ep.cv.cb = C / 64; ep.cv.C = C;
+    ep.cv.o_mult = 2; ep.cv.o_w0 = pf; ep.cv.o_h0 = pt; ep.cv.OW = F1; ep.cv.OH = T1;
+    // taps of the class: kt in {0, 2} (pt = 0: source row a - kt/2 = base row + (1 - kt/2)) or {1} (source row a)
+    int nt = 0;
+    for (int it = 0; it < (pt == 0 ? 2 : 1); ++it)
+      for (int jf = 0; jf < (pf == 0 ? 2 : 1); ++jf) {
+        const int kt = pt == 0 ? 2 * it : 1, kf = pf == 0 ? 2 * jf : 1;
+        ep.cv.off_h[nt] = (unsigned char)(pt == 0 ? 1 - it : 0);
+        ep.cv.off_w[nt] = (unsigned char)(pf == 0 ? 1 - jf : 0);
+        ep.cv.wtap[nt] = (unsigned char)(kt * 3 + kf);
+        ++nt;
+      }
+    const long long Mc = (long long)B * Hc * Wc;
+    const int K = nt * C;
+    B2_SCOPE(FAM_GEMM, st, 2.0 * Mc * C * (double)K, 2.0 * ((double)B * g.T2 * g.F2 * C + (double)C * K + 2.0 * Mc * C));
+    B2_TRY((launch<256, num_stages<256, 2>(EF), false, true, EF, 2, 1>(ma, mb, mc, mc, (int)Mc, C, K, 1, 1, 1, K / BK, ep, st)));
+  }
+  return 0;
 }
 
 extern "C" int b200slu_gemm_bf16_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* epilogue, void* stream) {

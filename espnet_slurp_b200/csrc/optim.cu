@@ -35,11 +35,20 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    float* __restrict__ v, long long n, float lr, float beta1, float beta2,
                                                    float eps, float weight_decay, float bc1, float bc2, float inv_scale,
                                                    float max_norm, double* __restrict__ state,
-                                                   const B2StepParams* __restrict__ sp) {
+                                                   const B2StepParams* __restrict__ sp, float warmup) {
   if (sp != nullptr) {  // per-step values live on the device (CUDA-graph replay): lr, 1 - beta1^t, 1 - beta2^t
     lr = sp->lr;
     bc1 = sp->bc1;
     bc2 = sp->bc2;
+  }
+  if (warmup > 0.f) {
+    // scheduled form: t = applied updates so far + 1 lives on the device (state[3]); a skipped (non-finite) step advances
+    // neither Adam's step count nor WarmupLR, like the reference (trainer.py:651-690, warmup_lr.py:43-50: lr is the
+    // `lr` argument here = base_lr)
+    const double t = state[3] + 1.0;
+    lr = (float)((double)lr * sqrt((double)warmup) * fmin(1.0 / sqrt(t), t / ((double)warmup * sqrt((double)warmup))));
+    bc1 = (float)(1.0 - pow((double)beta1, t));
+    bc2 = (float)(1.0 - pow((double)beta2, t));
   }
   const double ss = state[0];
   const float norm = (float)sqrt(ss);
@@ -65,6 +74,11 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// after the update: count it (state[3]) when it was applied
+__global__ void adam_advance_kernel(double* __restrict__ state) {
+  if (state[2] == 1.0) state[3] += 1.0;
+}
+
 }  // namespace
 
 // state: 3 doubles on the device (zeroed here).  grad_inv_scale multiplies every gradient first (e.g. 1/accum_grad).
@@ -82,7 +96,28 @@ extern "C" int b200slu_adam_step(float* params, const float* grads, float* exp_a
   const float bc1 = step >= 1 ? 1.f - powf(beta1, (float)step) : 1.f, bc2 = step >= 1 ? 1.f - powf(beta2, (float)step) : 1.f;
   adam_kernel<<<b2_grid_for(n, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
                                                       bc1, bc2, grad_inv_scale, max_norm, state3,
-                                                      step >= 1 ? nullptr : b2_step_params());
+                                                      step >= 1 ? nullptr : b2_step_params(), 0.f);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+// Scheduled form: the step count lives on the device.  state4 = {sum of squares, grad norm, applied flag (as above; zeroed
+// here), number of APPLIED updates so far (persistent: the caller zeroes it once)}.  lr_t = base_lr * warmup^0.5 *
+// min(t^-0.5, t * warmup^-1.5) and the bias corrections use t = state4[3] + 1; a non-finite gradient norm skips the update
+// AND leaves t unchanged.  Nothing depends on a host value, so the call is capturable in a CUDA graph as is.
+extern "C" int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n,
+                                       float base_lr, float warmup_steps, float beta1, float beta2, float eps, float weight_decay,
+                                       float grad_inv_scale, float max_norm, double* state4, void* stream) {
+  B2_CHECK_ARG(n > 0 && warmup_steps > 0.f && ((uintptr_t)grads % 16) == 0, "adam_step_sched: n > 0, warmup_steps > 0, aligned grads");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_CUDA(cudaMemsetAsync(state4, 0, 3 * sizeof(double), st));
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 32.0 * n);
+  sumsq_kernel<<<b2_grid_for(n >> 2, 256, 4), 256, 0, st>>>(grads, n, grad_inv_scale, state4);
+  B2_LAUNCH_CHECK();
+  adam_kernel<<<b2_grid_for(n, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, base_lr, beta1, beta2, eps,
+                                                      weight_decay, 1.f, 1.f, grad_inv_scale, max_norm, state4, nullptr, warmup_steps);
+  B2_LAUNCH_CHECK();
+  adam_advance_kernel<<<1, 1, 0, st>>>(state4);
   B2_LAUNCH_CHECK();
   return 0;
 }

@@ -12,6 +12,7 @@ Conventions shared with the step orchestration (``espnet_slurp_b200.step``):
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -389,6 +390,33 @@ def col2im_relu(dcol, h1):
     return dh1
 
 
+def conv2_implicit_supported(B: int, T1: int, F1: int, C: int) -> bool:
+    if os.environ.get("B200SLU_CONV2_IMPLICIT", "1") == "0":  # A/B measurements against the im2col + GEMM path
+        return False
+    return bool(_lib.lib().b200slu_conv2_implicit_supported(B, T1, F1, C))
+
+
+def conv2_fwd(h1, w16, bias):
+    """relu(conv.2(h1) + bias) as an implicit GEMM: h1 bf16 [B,T1,F1,C], w16 bf16 [C, 9C] -> bf16 [B*T2*F2, C]."""
+    B, T1, F1, Cc = h1.shape
+    T2, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
+    h2 = torch.empty(B * T2 * F2, Cc, device=h1.device, dtype=torch.bfloat16)
+    check(_lib.lib().b200slu_conv2_fwd(ptr(h1), B, T1, F1, Cc, ptr(w16), ptr(bias), ptr(h2), stream_ptr()), "conv2_fwd")
+    return h2
+
+
+def conv2_wgrad(dh2, h1, dw_accum):
+    B, T1, F1, Cc = h1.shape
+    check(_lib.lib().b200slu_conv2_wgrad(ptr(dh2), ptr(h1), B, T1, F1, Cc, ptr(dw_accum), stream_ptr()), "conv2_wgrad")
+
+
+def conv2_dgrad_relu(dh2, w16, h1):
+    B, T1, F1, Cc = h1.shape
+    dh1 = torch.empty_like(h1)
+    check(_lib.lib().b200slu_conv2_dgrad_relu(ptr(dh2), ptr(w16), ptr(h1), B, T1, F1, Cc, ptr(dh1), stream_ptr()), "conv2_dgrad")
+    return dh1
+
+
 # ---- losses -------------------------------------------------------------------------------------------------------
 def ctc_fwd(logits, V: int, hlens, labels, label_lens, blank: int = 0):
     """logits f32 [B,T,ldv]; returns (loss_per_utt [B], loss_sum [1], workspace)."""
@@ -517,6 +545,15 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, lr: float, step: int, state3, 
     check(_lib.lib().b200slu_adam_step(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), lr, betas[0],
                                        betas[1], eps, weight_decay, step, grad_inv_scale, max_norm, ptr(state3), stream_ptr()),
           "adam_step")
+
+
+def adam_step_sched(params, grads, exp_avg, exp_avg_sq, base_lr: float, warmup_steps: float, state4, betas=(0.9, 0.999),
+                    eps: float = 1e-8, weight_decay: float = 0.0, grad_inv_scale: float = 1.0, max_norm: float = 5.0):
+    """clip + Adam + WarmupLR with the step count on the device: state4 = float64[4] (sumsq, grad norm, applied flag, number of
+    applied updates so far -- persistent).  A non-finite gradient norm skips the update and does not advance the schedule."""
+    check(_lib.lib().b200slu_adam_step_sched(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), base_lr,
+                                             float(warmup_steps), betas[0], betas[1], eps, weight_decay, grad_inv_scale, max_norm,
+                                             ptr(state4), stream_ptr()), "adam_step_sched")
 
 
 def set_step_params(dev_tensor):

@@ -314,12 +314,17 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     h1 = K.conv1_fwd(feats, P[e + ".conv.0.weight"].reshape(C_, 9), P[e + ".conv.0.bias"])
     _, T1, F1, _ = h1.shape
     T, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
-    col = K.im2col(h1)
-    h2 = K.gemm(col, W[e + ".conv.2.weight"], bias=P[e + ".conv.2.bias"], act="relu")
-    # the im2col matrix (9x the conv.0 output: 27 MB per utterance of 5 s) is kept for the wgrad GEMM while it fits
-    # comfortably (<= 8 GB of the 180 GB), else dropped here and rebuilt in the backward
-    if col.numel() * 2 > KEEP_IM2COL_BYTES:
-        col = None
+    if K.conv2_implicit_supported(B, T1, F1, C_):
+        # implicit GEMM: the operand loads walk h1 through TMA im2col maps, no [pixels, 9 C] matrix anywhere
+        col = "implicit"
+        h2 = K.conv2_fwd(h1, W[e + ".conv.2.weight"], P[e + ".conv.2.bias"])
+    else:
+        col = K.im2col(h1)
+        h2 = K.gemm(col, W[e + ".conv.2.weight"], bias=P[e + ".conv.2.bias"], act="relu")
+        # the im2col matrix (9x the conv.0 output: 27 MB per utterance of 5 s) is kept for the wgrad GEMM while it fits
+        # comfortably (<= 8 GB of the 180 GB), else dropped here and rebuilt in the backward
+        if col.numel() * 2 > KEEP_IM2COL_BYTES:
+            col = None
     h2v = h2.view(B * T, F2 * C_)
     dpos = ctx.drop(cfg.pos_dropout, e + ".x")
     x = K.gemm(h2v, W[e + ".out.0.weight"], bias=P[e + ".out.0.bias"], alpha=math.sqrt(cfg.d), drop=dpos, out_dtype=F32)
@@ -397,13 +402,17 @@ def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=
     K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
     dh2 = K.gemm(g, W[e + ".out.0.weight"], trans_b=True, act_grad_input=h2v, act_grad="relu").view(-1, C_)
     K.colsum(dh2, G[e + ".conv.2.bias"])
-    if col is None:
-        col = K.im2col(h1)
-    K.gemm(dh2, col, trans=True, out=G[e + ".conv.2.weight"], accumulate=True)
-    del col
-    dcol = K.gemm(dh2, W[e + ".conv.2.weight"], trans_b=True)
-    dh1 = K.col2im_relu(dcol, h1)
-    del dcol
+    if isinstance(col, str):
+        K.conv2_wgrad(dh2, h1, G[e + ".conv.2.weight"])
+        dh1 = K.conv2_dgrad_relu(dh2, W[e + ".conv.2.weight"], h1)
+    else:
+        if col is None:
+            col = K.im2col(h1)
+        K.gemm(dh2, col, trans=True, out=G[e + ".conv.2.weight"], accumulate=True)
+        del col
+        dcol = K.gemm(dh2, W[e + ".conv.2.weight"], trans_b=True)
+        dh1 = K.col2im_relu(dcol, h1)
+        del dcol
     K.conv1_bwd(dh1, feats, G[e + ".conv.0.weight"].reshape(C_, 9), G[e + ".conv.0.bias"])
 
 

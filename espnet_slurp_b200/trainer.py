@@ -68,7 +68,8 @@ class TrainStep:
         n = self.pack.total
         self.m = torch.zeros(n, device=dev)       # Adam moments over the flat fp32 parameter buffer
         self.v = torch.zeros(n, device=dev)
-        self.state = torch.zeros(3, device=dev, dtype=torch.float64)  # (sum of squares, grad norm, update-applied flag)
+        # (sum of squares, grad norm, update-applied flag, number of applied updates): the schedule's step lives on the device
+        self.state = torch.zeros(4, device=dev, dtype=torch.float64)
         self.mel = mel_matrix(device=dev)
         self.bn: Dict[str, torch.Tensor] = {}
         for nblk in range(cfg.enc.blocks):
@@ -134,9 +135,10 @@ class TrainStep:
 
     def _tail(self):
         self.reducer.finish()  # issues whatever gradient buckets are still pending, then joins the side stream
-        # lr = 0 / step = 0: the kernel reads lr and the bias corrections from the device record (capturable)
-        ops.adam_step(self.pack.flat32, self.pack.gflat, self.m, self.v, 0.0, 0, self.state, grad_inv_scale=1.0 / self.world,
-                      max_norm=self.max_norm)
+        # WarmupLR and Adam's bias corrections are evaluated in the kernel from the device-side count of APPLIED updates: a
+        # step skipped for a non-finite gradient norm advances neither (trainer.py:651-690), and nothing here is a host value
+        ops.adam_step_sched(self.pack.flat32, self.pack.gflat, self.m, self.v, self.base_lr, self.warmup_steps, self.state,
+                            grad_inv_scale=1.0 / self.world, max_norm=self.max_norm)
 
     def capture(self, b: Optional[_Bucket] = None):
         """Record the whole step of this bucket (weight cast -> front-end -> forward -> backward [-> clip + Adam when
@@ -241,6 +243,27 @@ class TrainStep:
         if fetch_loss:
             self.loss_host.copy_(res, non_blocking=True)
         return res
+
+    def optimizer_state_dict(self) -> Dict[str, Dict[str, torch.Tensor]]:
+        """Adam's state per parameter NAME in torch.optim.Adam's vocabulary (step, exp_avg, exp_avg_sq, reference shapes): what
+        the reference checkpoints under `optimizers` once mapped onto its parameter order (`names` below gives ours)."""
+        step = self.state[3:4].to(torch.float32).clone()
+        out = {}
+        for n in self.pack.names:
+            o, num = self.pack.offs[n], int(np.prod(self.pack.shapes[n], dtype=np.int64))
+            out[n] = {"step": step.clone(), "exp_avg": self.m[o:o + num].view(self.pack.shapes[n]).clone(),
+                      "exp_avg_sq": self.v[o:o + num].view(self.pack.shapes[n]).clone()}
+        return out
+
+    def load_optimizer_state_dict(self, sd: Dict[str, Dict[str, torch.Tensor]]):
+        steps = set()
+        for n, st in sd.items():
+            o, num = self.pack.offs[n], int(np.prod(self.pack.shapes[n], dtype=np.int64))
+            self.m[o:o + num].copy_(st["exp_avg"].reshape(-1))
+            self.v[o:o + num].copy_(st["exp_avg_sq"].reshape(-1))
+            steps.add(float(st["step"]))
+        assert len(steps) == 1, "one optimizer step count for all parameters"
+        self.state[3] = steps.pop()
 
     def state_dict(self) -> Dict[str, torch.Tensor]:
         """Parameters in the reference's layout and names, plus the BatchNorm buffers (loadable by the reference model)."""

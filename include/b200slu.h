@@ -229,6 +229,18 @@ int b200slu_conv1_bwd(const void* dh1, const float* x, int B, int Tin, int F, in
                       void* workspace, long long workspace_bytes, void* stream);
 int b200slu_im2col3x3s2(const void* h1, int B, int T1, int F1, int C, void* col, void* stream);
 int b200slu_col2im3x3s2_relu(const void* dcol, const void* h1, int B, int T1, int F1, int C, void* dh1, void* stream);
+/* The same convolution (subsampling.py:56-65, conv.2: 3x3, stride 2, C -> C) as implicit GEMMs: the [pixels, 9 C] matrix is
+ * never written; the tensor-core GEMM's operand loads walk h1 (or dh2) through TMA im2col maps.  h1 bf16 [B,T1,F1,C]
+ * channels-last; w bf16 [C, 9 C] with k = (kt*3+kf)*C + ci; h2 / dh2 bf16 [B*T2*F2, C], T2 = (T1-3)/2+1, F2 = (F1-3)/2+1.
+ *   fwd:    h2 = relu(conv(h1) + bias)
+ *   wgrad:  dw_accum (fp32 [C, 9 C]) += dh2^T * im2col(h1)
+ *   dgrad:  dh1 = (h1 > 0) * conv_transpose(dh2, w), one gather GEMM per output parity class (4 / 2 / 2 / 1 taps)
+ * Needs C % 256 == 0 (b200slu_conv2_implicit_supported); callers keep the im2col + GEMM path otherwise. */
+int b200slu_conv2_implicit_supported(int B, int T1, int F1, int C);
+int b200slu_conv2_fwd(const void* h1, int B, int T1, int F1, int C, const void* w, const float* bias, void* h2, void* stream);
+int b200slu_conv2_wgrad(const void* dh2, const void* h1, int B, int T1, int F1, int C, float* dw_accum, void* stream);
+int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const void* h1, int B, int T1, int F1, int C, void* dh1,
+                             void* stream);
 
 /* ---- K6: CTC (espnet2/asr/ctc.py:52-63,82-95; lattice espnet/nets/pytorch_backend/gtn_ctc.py:26-36) -----
  * logits f32 [B,T,ldv] (log_softmax fused); labels int32 [B,Lmax]; all lengths int32 on the device. */
@@ -293,6 +305,14 @@ int b200slu_global_mvn_fwd(const float* x, int B, int T, int F, const int* lens,
 int b200slu_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
                       float beta2, float eps, float weight_decay, int step, float grad_inv_scale, float max_norm,
                       double* state3, void* stream);
+
+/* The same with the schedule on the device: state4[3] counts the APPLIED updates (persistent, zeroed once by the caller);
+ * lr_t = base_lr * warmup^0.5 * min(t^-0.5, t * warmup^-1.5) (WarmupLR) and Adam's bias corrections use t = state4[3] + 1.
+ * A non-finite gradient norm skips the update and leaves t unchanged, as trainer.py:651-690 skips optimizer.step() and
+ * scheduler.step() together. */
+int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float base_lr,
+                            float warmup_steps, float beta1, float beta2, float eps, float weight_decay, float grad_inv_scale,
+                            float max_norm, double* state4, void* stream);
 
 #ifdef __cplusplus
 }

@@ -389,6 +389,29 @@ def col2im_relu(dcol, h1):
     return _r(out * (h1.float() > 0))
 
 
+def conv2_implicit_supported(B, T1, F1, C):
+    return C % 256 == 0
+
+
+def conv2_fwd(h1, w16, bias):
+    return gemm(im2col(h1), w16, bias=bias, act="relu")
+
+
+def conv2_wgrad(dh2, h1, dw_accum):
+    gemm(dh2, im2col(h1), trans=True, out=dw_accum, accumulate=True)
+
+
+def conv2_dgrad_relu(dh2, w16, h1):
+    B, T1, F1, C = h1.shape
+    T2, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
+    d = (dh2.float() @ w16.float()).reshape(B, T2, F2, 3, 3, C)   # one rounding, after the sum over taps
+    out = torch.zeros(B, T1, F1, C)
+    for kh in range(3):
+        for kw in range(3):
+            out[:, kh:kh + 2 * T2 - 1:2, kw:kw + 2 * F2 - 1:2, :] += d[:, :, :, kh, kw, :]
+    return _r(out * (h1.float() > 0))
+
+
 def _ctc_inputs(logits, V, hlens, labels, label_lens):
     B, T, _ = logits.shape
     lp = logits[..., :V].detach().clone().requires_grad_(True)
@@ -477,6 +500,16 @@ def vocab_softmax_bwd(sm, dsm, V, add=None):
     if add is not None:
         out[:, :V] += add[:, :V].float()
     return _r(out)
+
+
+def adam_step_sched(params, grads, exp_avg, exp_avg_sq, base_lr, warmup_steps, state4, betas=(0.9, 0.999), eps=1e-8,
+                    weight_decay=0.0, grad_inv_scale=1.0, max_norm=5.0):
+    t = float(state4[3]) + 1.0
+    w = float(warmup_steps)
+    lr = base_lr * w ** 0.5 * min(t ** -0.5, t * w ** -1.5)
+    adam_step(params, grads, exp_avg, exp_avg_sq, lr, t, state4, betas, eps, weight_decay, grad_inv_scale, max_norm)
+    if float(state4[2]) == 1.0:
+        state4[3] += 1.0
 
 
 def adam_step(params, grads, exp_avg, exp_avg_sq, lr, step, state3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,

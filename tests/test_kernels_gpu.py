@@ -330,6 +330,37 @@ def test_conv_module_middle(B, T, C, Kk):
 
 
 # ---------------------------------------------------------------------------------------------- subsampling
+@pytest.mark.parametrize("B,T1,F1,C", [(2, 23, 39, 256), (3, 24, 40, 256), (1, 7, 5, 256), (2, 3, 3, 256), (4, 50, 39, 512),
+                                       (5, 312, 39, 256)])
+def test_conv2_implicit_gemms_bit_exact(B, T1, F1, C):
+    """conv.2 forward / wgrad / dgrad as implicit GEMMs (TMA im2col operand loads, parity-class gather for dgrad) on
+    small-integer data, where every sum is exact in fp32 and representable in bf16: the results must EQUAL the explicit
+    im2col statement -- any wrong pixel, tap, channel or parity class shows as a changed integer."""
+    g = torch.Generator().manual_seed(B * 1000 + T1 * 10 + F1 + C)
+    T2, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
+    def sparse(shape, vals, p):
+        idx = torch.randint(0, len(vals), shape, generator=g)
+        keep = torch.rand(shape, generator=g) < p
+        return (torch.tensor(vals, dtype=torch.float32)[idx] * keep).to(BF)
+    h1 = sparse((B, T1, F1, C), [1.0, 2.0], 0.15)
+    w = sparse((C, 9 * C), [-1.0, 1.0], 0.3)
+    bias = torch.randint(-3, 4, (C,), generator=g).float()
+    dh2 = sparse((B * T2 * F2, C), [-1.0, 1.0, 2.0], 0.1)
+    col = E.im2col(h1).float()
+    want_h2 = torch.relu(col @ w.float().t() + bias)
+    assert want_h2.max() < 256
+    h2 = K().conv2_fwd(h1.cuda(), w.cuda(), bias.cuda())
+    assert torch.equal(h2.float().cpu(), want_h2), ("fwd", (h2.float().cpu() - want_h2).abs().max())
+    dw = torch.full((C, 9 * C), 3.0, device="cuda")
+    K().conv2_wgrad(dh2.cuda(), h1.cuda(), dw)
+    want_dw = 3.0 + dh2.float().t() @ col
+    assert torch.equal(dw.cpu(), want_dw), ("wgrad", (dw.cpu() - want_dw).abs().max())
+    want_dh1 = E.conv2_dgrad_relu(dh2, w, h1).float()
+    assert want_dh1.abs().max() < 256
+    dh1 = K().conv2_dgrad_relu(dh2.cuda(), w.cuda(), h1.cuda())
+    assert torch.equal(dh1.float().cpu(), want_dh1), ("dgrad", (dh1.float().cpu() - want_dh1).abs().max())
+
+
 @pytest.mark.parametrize("B,Tin,F,C", [(2, 47, 80, 16), (3, 101, 80, 512), (2, 30, 20, 64)])
 def test_subsampling(B, Tin, F, C):
     x, w, b = rnd(B, Tin, F, seed=1), rnd(C, 9, seed=2) * 0.3, rnd(C, seed=3) * 0.1

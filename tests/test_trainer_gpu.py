@@ -164,3 +164,57 @@ def test_close_unregisters_the_device_record():
     gc.collect()
     got = ops.dropout_mask((0.1, 7, 3), 4096).cpu().numpy()
     assert np.array_equal(got, dropout_ref.keep_mask(0.1, 7, 3, 4096))
+
+
+def test_skipped_step_does_not_advance_schedule_and_state_exports():
+    """b200slu_adam_step_sched vs torch.optim.Adam + WarmupLR driven the way trainer.py:651-690 drives them: a step whose
+    gradient norm is not finite skips optimizer.step() AND scheduler.step(), so the next applied update still uses t = k+1."""
+    from espnet_slurp_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    n, base_lr, warm = 4096, 2e-3, 3.0
+    p0 = torch.randn(n, generator=g)
+    ref = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([ref], lr=base_lr)
+    p = p0.cuda()
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    st = torch.zeros(4, device="cuda", dtype=torch.float64)
+    applied = 0
+    for i in range(6):
+        grad = torch.randn(n, generator=g) * (10.0 if i == 1 else 0.01)   # step 1 gets clipped
+        if i in (2, 4):
+            grad[17] = float("inf") if i == 2 else float("nan")
+        before = p.clone()
+        ops.adam_step_sched(p, grad.cuda(), m, v, base_lr, warm, st, max_norm=5.0)
+        if i in (2, 4):
+            assert st[2].item() == 0.0 and st[3].item() == applied and torch.equal(p, before)
+            continue
+        applied += 1
+        assert st[2].item() == 1.0 and st[3].item() == applied
+        for gp in opt.param_groups:
+            gp["lr"] = base_lr * warm ** 0.5 * min(applied ** -0.5, applied * warm ** -1.5)
+        ref.grad = grad.clone()
+        torch.nn.utils.clip_grad_norm_([ref], 5.0)
+        opt.step()
+        torch.testing.assert_close(p.cpu(), ref.detach(), rtol=2e-5, atol=2e-6)
+    sto = opt.state[ref]
+    assert float(sto["step"]) == applied
+    torch.testing.assert_close(m.cpu(), sto["exp_avg"], rtol=1e-4, atol=1e-8)
+    torch.testing.assert_close(v.cpu(), sto["exp_avg_sq"], rtol=1e-4, atol=1e-10)
+
+    # the trainer exports that state per parameter name in torch.optim.Adam's vocabulary, and takes it back
+    from espnet_slurp_b200.trainer import TrainStep
+    cfg, ocfg = _cfg()
+    sd = make_sd(ocfg.enc, ocfg.dec, 30, seed=6)
+    a = TrainStep(cfg, sd, use_graph=False, lr=1e-3, warmup_steps=10)
+    for i in range(2):
+        a({k: t.cuda() for k, t in _batch(2, 6000, 4, seed=40 + i).items()})
+    osd = a.optimizer_state_dict()
+    assert set(osd) == set(sd) and all(float(s["step"]) == 2 and s["exp_avg"].shape == sd[k].shape for k, s in osd.items())
+    b = TrainStep(cfg, a.state_dict(), use_graph=False, lr=1e-3, warmup_steps=10)
+    b.load_optimizer_state_dict(osd)
+    nb = {k: t.cuda() for k, t in _batch(2, 6000, 4, seed=50).items()}
+    b.step_no = a.step_no            # same dropout / SpecAug stream position (all rates are 0 here)
+    la, lb = a(nb), b(nb)
+    assert torch.equal(la, lb)
+    sa, sb = a.state_dict(), b.state_dict()
+    assert all(torch.equal(sa[k], sb[k]) for k in sd)
