@@ -95,6 +95,8 @@ _SIGNATURES = {
     "b200slu_conv2_fwd": [_P, _I, _I, _I, _I, _P, _P, _P, _P],
     "b200slu_conv2_wgrad": [_P, _P, _I, _I, _I, _I, _P, _P],
     "b200slu_conv2_dgrad_relu": [_P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "b200slu_conv1_fwd_bits": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P],
+    "b200slu_relu_bits": [_P, _L, _I, _P, _P],
     "b200slu_ctc_workspace_size": [_I, _I, _I],
     "b200slu_ctc_lattice_states": [_P, _I, _P, _I, _I, _P, _P, _P],
     "b200slu_ctc_fwd": [_P, _L, _I, _I, _I, _P, _P, _I, _P, _I, _P, _P, _P, _P],

@@ -110,6 +110,16 @@ __device__ __forceinline__ float swish_gradf_(float x) {
   return s * (1.f + x * (1.f - s));
 }
 
+// two independent IEEE fp32 FMAs in one instruction (FFMA2): d = a * b + c per component
+__device__ __forceinline__ float2 b2_fma2(float2 a, float2 b, float2 c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)),
+        "l"(*reinterpret_cast<unsigned long long*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);

@@ -214,7 +214,8 @@ __device__ __forceinline__ void epi_prefetch(uint32_t rt_flags, const EpiRow& er
 template <uint32_t EF>
 __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs& ep, const B2DropKey& dk, const EpiRow& er,
                                                float alpha, const float* bias_s, const EpiPre& pre, const uint32_t (&acc)[16],
-                                               int col0, int N, int sl, int lane, uint32_t stg_out, uint32_t stg_d) {
+                                               int col0, int N, int sl, int lane, uint32_t stg_out, uint32_t stg_d,
+                                               uint32_t keep16 = 0xffffu) {
   const uint32_t F = (EF & EF_GENERIC) ? rt_flags : EF;
   const uint32_t rowoff = (uint32_t)lane * 128u, sw = (uint32_t)(lane & 7);
   const bool whole = col0 + 16 <= N;
@@ -250,6 +251,10 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
 #pragma unroll
     for (int j = 0; j < 8; ++j) w[j] = __uint_as_float(acc[g * 8 + j]);
     epi_math8<EF>(rt_flags, ep, dk, alpha, er.e0, c, w, b, x, r, d);
+    if (F & EF_SCATTER) {  // ReLU gate of the layer below, one bit per column
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = ((keep16 >> (g * 8 + j)) & 1u) ? w[j] : 0.f;
+    }
     if (F & EF_DACT) {
       const uint32_t ch = (uint32_t)((sl & 3) * 2 + g);
       sts128(stg_d + rowoff + ((ch ^ sw) << 4), pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]),
@@ -337,18 +342,36 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       for (int u = first_unit; u < num_units; u += unit_step) {
         const int batch = u / units_per_batch, r = u - batch * units_per_batch;
         const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
-        const int tile = r / splits, sp = r - tile * splits;
+        // CONV = 2 orders its units k-chunk-major: the tiles running at any moment then read the same pixels (through
+        // different taps) and L2 serves all but the first
+        const int tile = CONV == 2 ? r % tiles_per_batch : r / splits, sp = CONV == 2 ? r / tiles_per_batch : r - tile * splits;
         const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
         const int kb0 = sp * kb_per_split;
         const int nkb = min(kb_per_split, num_kb_total - kb0);
         const int abi = bi * ep.a_bc_inner, abo = bo * ep.a_bc_outer, bbi = bi * ep.b_bc_inner, bbo = bo * ep.b_bc_outer;
-        int pn0 = 0, pw0 = 0, ph0 = 0;  // CONV = 1: base pixel of this CTA's 128 rows, in tensor coordinates
-        if (CONV == 1) {
-          const int arow = tile_m * TM + (int)cta_rank * BM, per = ep.cv.pw * ep.cv.ph;
-          pn0 = arow / per;
-          const int r2 = arow - pn0 * per, hq = r2 / ep.cv.pw;
-          ph0 = ep.cv.base_h + hq * ep.cv.mult;
-          pw0 = ep.cv.base_w + (r2 - hq * ep.cv.pw) * ep.cv.mult;
+        // CONV: everything that needs an integer division is worked out once per unit; the k-block loop only steps
+        // counters.  (One lane issues all loads of the CTA: four divisions per k-block made it the slowest stage of the
+        // pipeline -- 960 cycles per k-block against 512 of MMA.)
+        int pn0 = 0, pwq = 0, phq = 0;  // pixel (image, row, column in the pixel grid): CONV = 1 this CTA's first row, CONV = 2 the k-block's first pixel
+        int tj = 0, cbi = 0;            // CONV = 1: tap and channel block of the k-block
+        int btap[BN / CG / 64], bch[BN / CG / 64];  // CONV = 2: tap and first channel of this CTA's 64-column boxes of B
+        if (CONV != 0) {
+          const int p0 = CONV == 1 ? tile_m * TM + (int)cta_rank * BM : kb0 * BK, per = ep.cv.pw * ep.cv.ph;
+          pn0 = p0 / per;
+          const int r2 = p0 - pn0 * per;
+          phq = r2 / ep.cv.pw;
+          pwq = r2 - phq * ep.cv.pw;
+          if (CONV == 1) {
+            tj = kb0 / ep.cv.cb;
+            cbi = kb0 - tj * ep.cv.cb;
+          } else {
+#pragma unroll
+            for (int b = 0; b < BN / CG / 64; ++b) {
+              const int ncol = tile_n * BN + (int)cta_rank * (BN / CG) + b * 64;
+              btap[b] = ncol / ep.cv.C;
+              bch[b] = ncol - btap[b] * ep.cv.C;
+            }
+          }
         }
         for (int kb = 0; kb < nkb; ++kb, ++i) {
           const int s = i % STAGES, it = i / STAGES;
@@ -380,14 +403,18 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             // k-block = (tap, 64 channels): 128 pixels x 64 channels of the activation, shifted by the tap; the weight
             // operand's coordinates follow the tap (forward: k = (tap, cin) as stored; dgrad: column block (tap, cin))
             static_assert(CONV != 1 || !TA, "im2col A operand is K-major");
-            const int kbg = kb0 + kb, tj = kbg / ep.cv.cb, c0 = (kbg - tj * ep.cv.cb) * 64;
-            load_px(sa, &map_a, c0, pw0, ph0, pn0, tj);
+            const int c0 = cbi * 64;
+            load_px(sa, &map_a, c0, ep.cv.base_w + pwq * ep.cv.mult, ep.cv.base_h + phq * ep.cv.mult, pn0, tj);
             const int wt = (int)ep.cv.wtap[tj] * ep.cv.C;
             if (!TB) {
               load(sb, &map_b, wt + c0, brow, 0, 0);
             } else {
 #pragma unroll
               for (int b = 0; b < BNL / 64; ++b) load(sb + b * (64 * BK * 2), &map_b, brow + b * 64 + wt, c0, 0, 0);
+            }
+            if (++cbi == ep.cv.cb) {
+              cbi = 0;
+              ++tj;
             }
             continue;
           }
@@ -396,12 +423,16 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             static_assert(CONV != 2 || (TA && TB), "im2col B operand is MN-major");
 #pragma unroll
             for (int a = 0; a < BM / 64; ++a) load(sa + a * (64 * BK * 2), &map_a, arow + a * 64, k, 0, 0);
-            const int per = ep.cv.pw * ep.cv.ph, pn = k / per, r2 = k - pn * per, hq = r2 / ep.cv.pw;
-            const int ph = ep.cv.base_h + hq * ep.cv.mult, pw = ep.cv.base_w + (r2 - hq * ep.cv.pw) * ep.cv.mult;
+            const int ph = ep.cv.base_h + phq * ep.cv.mult, pw = ep.cv.base_w + pwq * ep.cv.mult;
 #pragma unroll
-            for (int b = 0; b < BNL / 64; ++b) {
-              const int ncol = brow + b * 64, tj = ncol / ep.cv.C;
-              load_px(sb + b * (64 * BK * 2), &map_b, ncol - tj * ep.cv.C, pw, ph, pn, tj);
+            for (int b = 0; b < BNL / 64; ++b) load_px(sb + b * (64 * BK * 2), &map_b, bch[b], pw, ph, pn0, btap[b]);
+            pwq += BK;  // the next k-block starts 64 pixels on
+            while (pwq >= ep.cv.pw) {
+              pwq -= ep.cv.pw;
+              if (++phq == ep.cv.ph) {
+                phq = 0;
+                ++pn0;
+              }
             }
             continue;
           }
@@ -432,7 +463,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       long long w_full = 0, w_acc = 0, t_begin = rec ? clock64() : 0;
       for (int u = first_unit; u < num_units; u += unit_step, ++t) {
         const int r = u % units_per_batch;
-        const int sp = r % splits;
+        const int sp = CONV == 2 ? r / tiles_per_batch : r % splits;
         const int kb0 = sp * kb_per_split;
         const int nkb = min(kb_per_split, num_kb_total - kb0);
         const int buf = t & 1;
@@ -496,7 +527,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
     for (int u = first_unit; u < num_units; u += unit_step, ++t) {
       const int batch = u / units_per_batch, r = u - batch * units_per_batch;
       const int bo = batch / batch_inner, bi = batch - bo * batch_inner;
-      const int tile = r / splits, sp = r - tile * splits;
+      const int tile = CONV == 2 ? r % tiles_per_batch : r / splits, sp = CONV == 2 ? r / tiles_per_batch : r - tile * splits;
       const int tile_m = tile / tiles_n, tile_n = tile - tile_m * tiles_n;
       const int buf = t & 1;
       const int row0 = tile_m * TM + (int)cta_rank * BM + lane_grp * 32, row = row0 + lane;
@@ -540,6 +571,14 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         mbar_expect_tx(rbar + bsel * 8, 4096);
         tma_load_4d(bsel ? stg1 : stg0, &map_d, rbar + bsel * 8, colw, row0, 0, 0);
       }
+      // EF_SCATTER: this lane's ReLU bits for the warp's 128 columns (one 16-byte load per tile), requested before the
+      // accumulator wait.  (Reading the mask as bf16 rows of h1 -- 64 KB per tile in flight per SM -- stalled the epilogue
+      // warps at load issue for as long as the tile's arithmetic took.)
+      constexpr bool SC = !(EFC & EF_GENERIC) && (EFC & EF_SCATTER) != 0;
+      static_assert(!SC || WCOLS == 128, "scatter epilogue: 128 columns = 4 mask words per warp");
+      uint4 keep = make_uint4(0u, 0u, 0u, 0u);
+      if (SC && spix >= 0 && colw < N)
+        keep = ld_nc_u4(reinterpret_cast<const uint32_t*>(ep.aux) + (long long)spix * (ep.ldaux >> 5) + (colw >> 5));
       EpiPre pa, pb;
       if (!(EFC & EF_GENERIC) && row_ok) epi_prefetch<EFC>(rtf, er, colw, N, pa);
       if (((EFC & EF_GENERIC) || (EFC & EF_BIAS)) && has_bias) asm volatile("bar.sync %0, 128;" ::"r"(1 + cgrp) : "memory");
@@ -570,7 +609,7 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             tma_load_4d(bn ? stg1 : stg0, &map_d, rbar + bn * 8, c2c, row0, 0, 0);
           }
           mbar_wait(rbar + (nflush & 1u) * 8, (nflush >> 1) & 1u);
-        } else if (box_start && !(!(EFC & EF_GENERIC) && (EFC & EF_SCATTER))) {
+        } else if (box_start && !(!(EFC & EF_GENERIC) && (EFC & EF_SCATTER) != 0)) {
           // the bulk store that last read this staging box must have finished reading it
           if (lane == 0) {
             if (two_out || STGB == 1) bulk_wait_read<0>();
@@ -585,51 +624,32 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         if (row_ok && c0c < N && !(debug & 2)) {
           if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c0c, N, pa);
           else if (c1c < N) epi_prefetch<EFC>(rtf, er, c1c, N, pb);
-          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32, pa, ra, c0c, N, sl0, lane, so, stg1);
+          const uint32_t kw = SC ? (cp == 0 ? keep.x : cp == 1 ? keep.y : cp == 2 ? keep.z : keep.w) : 0u;
+          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32, pa, ra, c0c, N, sl0, lane, so, stg1, kw & 0xffffu);
         }
         tmem_ld_wait();
         if (cp + 1 < NPAIR) tmem_ld16(tbase + cp * 32 + 32, ra);
         if (row_ok && c1c < N && !(debug & 2)) {
           if (EFC & EF_GENERIC) epi_prefetch<EFC>(rtf, er, c1c, N, pb);
           else if (cp + 1 < NPAIR && c2c < N) epi_prefetch<EFC>(rtf, er, c2c, N, pa);
-          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32 + 16, pb, rb, c1c, N, sl1, lane, so, stg1);
+          const uint32_t kw = SC ? (cp == 0 ? keep.x : cp == 1 ? keep.y : cp == 2 ? keep.z : keep.w) : 0u;
+          epilogue_slice<EFC>(rtf, ep, dk, er, alpha, bias_s + cp * 32 + 16, pb, rb, c1c, N, sl1, lane, so, stg1, kw >> 16);
         }
         if (rec) { const long long q1 = clock64(); ep.dbg_out[10] += q1 - q0; q0 = q1; }
-        if (!(EFC & EF_GENERIC) && (EFC & EF_SCATTER)) {
+        if (SC) {
           if (box_end) {
             // the 32 x 64 box leaves row by row: 8 lanes move one row's 128 bytes (4 rows per pass), each row to the pixel its
-            // lane computed above, gated by the ReLU mask read from the same position of `aux`
+            // lane computed above
             __syncwarp();
             const int bcol = c0c - 32 + (lane & 7) * 8;
-            const bf16* __restrict__ mask = ep.aux;
             bf16* __restrict__ outp = reinterpret_cast<bf16*>(ep.out);
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              uint4 hv[4];
-              long long off[4];
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const int rr = (h * 4 + q) * 4 + (lane >> 3);
-                const int px = __shfl_sync(0xffffffffu, spix, rr);
-                off[q] = px >= 0 && bcol < N ? (long long)px * ep.ldc + bcol : -1;
-                if (off[q] >= 0) hv[q] = *reinterpret_cast<const uint4*>(mask + off[q]);
-              }
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const int rr = (h * 4 + q) * 4 + (lane >> 3);
-                uint32_t v[4];
-                lds128u(so + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4), v[0], v[1], v[2], v[3]);
-                if (off[q] >= 0) {
-                  const uint32_t m4[4] = {hv[q].x, hv[q].y, hv[q].z, hv[q].w};
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    const float2 hh = unpack_bf16x2(m4[e]);
-                    if (!(hh.x > 0.f)) v[e] &= 0xffff0000u;
-                    if (!(hh.y > 0.f)) v[e] &= 0x0000ffffu;
-                  }
-                  *reinterpret_cast<uint4*>(outp + off[q]) = make_uint4(v[0], v[1], v[2], v[3]);
-                }
-              }
+            for (int q = 0; q < 8; ++q) {
+              const int rr = q * 4 + (lane >> 3);
+              const int px = __shfl_sync(0xffffffffu, spix, rr);
+              uint32_t v[4];
+              lds128u(so + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4), v[0], v[1], v[2], v[3]);
+              if (px >= 0 && bcol < N) *reinterpret_cast<uint4*>(outp + (long long)px * ep.ldc + bcol) = make_uint4(v[0], v[1], v[2], v[3]);
             }
             __syncwarp();  // the box is rewritten by the next slices
           }
@@ -763,16 +783,21 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc, 
     B2_CUDA(cudaStreamSynchronize(st));
     B2_CUDA(cudaMemcpy(h, dbg_buf, sizeof(h), cudaMemcpyDeviceToHost));
     fprintf(stderr,
-            "[gemm dbg] M=%d N=%d K=%d BN=%d CG=%d TA=%d TB=%d splits=%d grid=%d | CTA0: tiles=%lld kblocks=%lld mma_loop=%lld cyc "
+            "[gemm dbg] M=%d N=%d K=%d BN=%d CG=%d TA=%d TB=%d splits=%d grid=%d conv=%d | CTA0: tiles=%lld kblocks=%lld mma_loop=%lld cyc "
             "(wait operands %lld, wait accumulator %lld) | epi warp0: wait acc %lld, busy %lld [staging free %lld, tmem wait %lld, "
-            "slices %lld, flush %lld] | producer wait stage %lld | EF=%u\n",
-            M, N, K, BN, CG, (int)TA, (int)TB, splits, grid, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[8], h[9], h[10], h[11], h[7],
-            (unsigned)EF);
+            "slices %lld, flush %lld] | producer wait stage %lld | EF=%u CONV=%d\n",
+            M, N, K, BN, CG, (int)TA, (int)TB, splits, grid, CONV, h[4], h[3], h[0], h[1], h[2], h[5], h[6], h[8], h[9], h[10], h[11], h[7],
+            (unsigned)EF, CONV);
   }
   return 0;
 }
 
 }  // namespace
+
+static int gemm_debug_env() {
+  static const int dbg = getenv("B200SLU_GEMM_DEBUG") ? atoi(getenv("B200SLU_GEMM_DEBUG")) : 0;
+  return dbg;
+}
 
 // Internal C++ entry (used by the C ABI below).
 int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_t st) {
@@ -810,8 +835,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     ep.out_f32 = e->out_f32;
     ep.accumulate = e->accumulate;
     ep.drop = b2_make_drop(e->dropout_p, e->dropout_seed, e->dropout_site);
-    static const int dbg = getenv("B200SLU_GEMM_DEBUG") ? atoi(getenv("B200SLU_GEMM_DEBUG")) : 0;
-    ep.debug = dbg;
+    ep.debug = gemm_debug_env();
   }
   {
     uint32_t f = 0;
@@ -1022,7 +1046,8 @@ int make_im2col_map(CUtensorMap* m, const void* base, int Nimg, int H, int W, in
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper, 64,
                    (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     b200slu_set_error("cuTensorMapEncodeIm2col failed (%d): N=%d H=%d W=%d C=%d corners (%d,%d)/(%d,%d) stride %d", (int)r, Nimg, H,
                       W, C, lower_w, lower_h, upper_w, upper_h, stride);
@@ -1075,6 +1100,7 @@ extern "C" int b200slu_conv2_fwd(const void* h1, int B, int T1, int F1, int C, c
   EpiArgs ep{};
   ep.out = h2; ep.ldc = N; ep.alpha = 1.f; ep.bias = bias; ep.act = B200SLU_ACT_RELU;
   ep.flags = EF_BIAS | EF_RELU;
+  ep.debug = gemm_debug_env() & 16;
   ep.cv.pw = g.F2; ep.cv.ph = g.T2; ep.cv.mult = 2; ep.cv.base_w = 0; ep.cv.base_h = 0; ep.cv.cb = C / 64; ep.cv.C = C;
   for (int t = 0; t < 9; ++t) {
     ep.cv.off_h[t] = (unsigned char)(t / 3);
@@ -1101,13 +1127,16 @@ extern "C" int b200slu_conv2_wgrad(const void* dh2, const void* h1, int B, int T
   EpiArgs ep{};
   ep.out = dw_accum; ep.ldc = N; ep.alpha = 1.f; ep.out_f32 = 1; ep.accumulate = 1;
   ep.flags = EF_F32 | EF_ACC;
+  ep.debug = gemm_debug_env() & 16;
   ep.cv.pw = g.F2; ep.cv.ph = g.T2; ep.cv.mult = 2; ep.cv.base_w = 0; ep.cv.base_h = 0; ep.cv.cb = C / 64; ep.cv.C = C;
   for (int t = 0; t < 9; ++t) {
     ep.cv.off_h[t] = (unsigned char)(t / 3);
     ep.cv.off_w[t] = (unsigned char)(t % 3);
     ep.cv.wtap[t] = (unsigned char)t;
   }
-  // split K (= pixels) so that the (C/256) x (9C/256) pair tiles fill the machine
+  // split K (= pixels) so that the (C/256) x (9C/256) pair tiles fill the machine in one wave; the units run split-major,
+  // so the tiles in flight read the same pixels through different taps.  (Short k-chunks, tried for L2 locality, only add
+  // reduce-add epilogues: 1551 us with 48-block chunks against 1451 us.)
   const int num_kb = (K + BK - 1) / BK;
   const long long tiles = (long long)((M + 255) / 256) * (N / 256), slots = b2_num_sms() / 2;
   int splits = 1;
@@ -1129,12 +1158,12 @@ extern "C" int b200slu_conv2_wgrad(const void* dh2, const void* h1, int B, int T
 
 // dh1[b, r, g, ci] = (h1[b, r, g, ci] > 0) * sum over taps with 2t+kt = r, 2f+kf = g of dh2[(b,t,f), co] * w[co, (kt*3+kf)*C + ci]
 // Gather form, one GEMM per parity class (r & 1, g & 1): 4 / 2 / 2 / 1 taps, no scatter-add and no [pixels, 9 C] matrix.
-extern "C" int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const void* h1, int B, int T1, int F1, int C, void* dh1,
-                                        void* stream) {
+extern "C" int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const unsigned int* relu_bits, int B, int T1, int F1, int C,
+                                        void* dh1, void* stream) {
   Conv2Geom g;
   B2_TRY(conv2_geom(B, T1, F1, C, &g));
   cudaStream_t st = (cudaStream_t)stream;
-  B2_CHECK_ARG(((uintptr_t)h1 % 16) == 0 && ((uintptr_t)dh2 % 16) == 0 && ((uintptr_t)w % 16) == 0 && ((uintptr_t)dh1 % 16) == 0,
+  B2_CHECK_ARG(((uintptr_t)relu_bits % 16) == 0 && ((uintptr_t)dh2 % 16) == 0 && ((uintptr_t)w % 16) == 0 && ((uintptr_t)dh1 % 16) == 0,
                "conv2_dgrad: 16-byte aligned operands");
   CUtensorMap mb, mc;
   B2_TRY(make_map(&mb, w, C, 9 * C, 9 * C, 1, 0, 1, 0, 64, BK));  // [K = co, N = (tap, ci)], N contiguous
@@ -1148,8 +1177,9 @@ extern "C" int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const vo
     CUtensorMap ma;
     B2_TRY(make_im2col_map(&ma, dh2, B, g.T2, g.F2, C, lw, lh, Wc - g.F2 + lw, Hc - g.T2 + lh, 1, BM));
     EpiArgs ep{};
-    ep.out = dh1; ep.ldc = C; ep.alpha = 1.f; ep.aux = (const bf16*)h1; ep.ldaux = C;
+    ep.out = dh1; ep.ldc = C; ep.alpha = 1.f; ep.aux = (const bf16*)relu_bits; ep.ldaux = C;  // bit rows, C bits each
     ep.flags = EF;
+    ep.debug = gemm_debug_env() & 16;
     ep.cv.pw = Wc; ep.cv.ph = Hc; ep.cv.mult = 1; ep.cv.base_w = lw; ep.cv.base_h = lh; ep.cv.cb = C / 64; ep.cv.C = C;
     ep.cv.o_mult = 2; ep.cv.o_w0 = pf; ep.cv.o_h0 = pt; ep.cv.OW = F1; ep.cv.OH = T1;
     // taps of the class: kt in {0, 2} (pt = 0: source row a - kt/2 = base row + (1 - kt/2)) or {1} (source row a)

@@ -13,10 +13,10 @@ namespace {
 // x [B, Tin, F] f32 -> h1 [B, T1, F1, C] bf16 ;  grid (ceil(T1 / TR1), B).  Each thread keeps the 9 taps + bias of its
 // 8 channels in registers and walks the output pixels of TR1 rows; the 2*TR1+1 input rows sit in shared memory
 // (broadcast reads), every store is one 16-byte vector and a warp writes 512 contiguous bytes.
-constexpr int TR1 = 8;
+constexpr int TR1 = 16;
 __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                         const float* __restrict__ bias, int Tin, int F, int C, int T1, int F1,
-                                                        bf16* __restrict__ h1) {
+                                                        bf16* __restrict__ h1, uint32_t* __restrict__ relu_bits) {
   extern __shared__ float sx[];  // [2*TR1+1][F]
   const int tb = blockIdx.x * TR1, b = blockIdx.y;
   const int nt = min(TR1, T1 - tb), nrows = 2 * nt + 1;
@@ -25,28 +25,74 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
   const int ncg = C >> 3;
   const int npl = blockDim.x / ncg;  // position lanes (4 for C = 512)
   for (int cg = threadIdx.x % ncg, pl = threadIdx.x / ncg; pl < npl && cg < ncg; cg += ncg) {
-    float wr[9][8], bs[8];
+    // The kernel is issue-bound (72 FMAs per 16 bytes stored): the taps run as packed FFMA2 (fma.rn.f32x2, two
+    // IEEE FMAs per instruction -- same rounding as the scalar form), channel pairs (2j, 2j+1) per register pair.
+    float2 wr[9][4], bs[4];
+    {
+      // this thread's 8 x 9 taps are 72 consecutive floats of w: 18 vector loads instead of 72 strided scalar ones
+      float wf[72];
+      const float4* wsrc = reinterpret_cast<const float4*>(w + cg * 72);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      bs[j] = bias[cg * 8 + j];
+      for (int q = 0; q < 18; ++q) {
+        const float4 v = wsrc[q];
+        wf[4 * q] = v.x; wf[4 * q + 1] = v.y; wf[4 * q + 2] = v.z; wf[4 * q + 3] = v.w;
+      }
+      const float4 b0 = *reinterpret_cast<const float4*>(bias + cg * 8), b1 = *reinterpret_cast<const float4*>(bias + cg * 8 + 4);
+      bs[0] = make_float2(b0.x, b0.y); bs[1] = make_float2(b0.z, b0.w); bs[2] = make_float2(b1.x, b1.y); bs[3] = make_float2(b1.z, b1.w);
 #pragma unroll
-      for (int k = 0; k < 9; ++k) wr[k][j] = w[(cg * 8 + j) * 9 + k];
+      for (int j = 0; j < 4; ++j) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) wr[k][j] = make_float2(wf[(2 * j) * 9 + k], wf[(2 * j + 1) * 9 + k]);
+      }
     }
     for (int p = pl; p < nt * F1; p += npl) {
       const int tl = p / F1, f = p - tl * F1;
-      float acc[8];
+      float2 acc2[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = bs[j];
+      for (int j = 0; j < 4; ++j) acc2[j] = bs[j];
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
         const float xv = sx[(2 * tl + k / 3) * F + 2 * f + (k % 3)];
+        const float2 xx = make_float2(xv, xv);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += xv * wr[k][j];
+        for (int j = 0; j < 4; ++j) acc2[j] = b2_fma2(xx, wr[k][j], acc2[j]);
       }
+      uint32_t pk[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
-      store8_bf16(h1 + (((long long)b * T1 + tb + tl) * F1 + f) * C + cg * 8, acc);
+      for (int j = 0; j < 4; ++j) pk[j] = pack_bf16x2(fmaxf(acc2[j].x, 0.f), fmaxf(acc2[j].y, 0.f));
+      const long long pix = ((long long)b * T1 + tb + tl) * F1 + f;
+      *reinterpret_cast<uint4*>(h1 + pix * C + cg * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      if (relu_bits != nullptr) {
+        // bit c of the pixel's C-bit row = (h1[c] > 0): what conv.2's dgrad needs of h1, at 1/16 of the bytes.  Taken
+        // from the stored bf16 pairs (non-negative after the ReLU, so > 0 <=> != 0): adding 0x7fff to a half sets its top
+        // bit iff it is nonzero and cannot carry into the neighbour.
+        uint32_t x = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x |= ((pk[j] + 0x7fff7fffu) & 0x80008000u) >> (15 - 2 * j);  // halves of pair j -> bits 2j, 2j+16
+        // one byte per lane: a warp's 32 bytes are contiguous (little-endian words: byte cg % 4 of word cg / 4)
+        reinterpret_cast<unsigned char*>(relu_bits)[pix * (C >> 3) + cg] = (unsigned char)((x | (x >> 15)) & 0xffu);
+      }
     }
+  }
+}
+
+// bits[p][c / 32] bit (c % 32) = (h1[p][c] > 0), for callers that hold only h1
+__global__ void __launch_bounds__(256) relu_bits_kernel(const bf16* __restrict__ h1, long long words, uint32_t* __restrict__ bits) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (long long)gridDim.x * blockDim.x) {
+    const uint4* src = reinterpret_cast<const uint4*>(h1 + i * 32);
+    uint32_t m = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint4 v = src[q];
+      const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f2 = unpack_bf16x2(w4[e]);
+        m |= (f2.x > 0.f ? 1u : 0u) << (q * 8 + e * 2);
+        m |= (f2.y > 0.f ? 1u : 0u) << (q * 8 + e * 2 + 1);
+      }
+    }
+    bits[i] = m;
   }
 }
 
@@ -178,15 +224,32 @@ __global__ void __launch_bounds__(256) col2im_relu_kernel(const bf16* __restrict
 
 }  // namespace
 
+extern "C" int b200slu_conv1_fwd_bits(const float* x, const float* w, const float* bias, int B, int Tin, int F, int C, void* h1,
+                                      unsigned int* relu_bits, void* stream);
 extern "C" int b200slu_conv1_fwd(const float* x, const float* w, const float* bias, int B, int Tin, int F, int C, void* h1,
                                  void* stream) {
+  return b200slu_conv1_fwd_bits(x, w, bias, B, Tin, F, C, h1, nullptr, stream);
+}
+
+extern "C" int b200slu_relu_bits(const void* h1, long long pixels, int C, unsigned int* relu_bits, void* stream) {
+  B2_CHECK_ARG(pixels > 0 && C > 0 && C % 32 == 0 && ((uintptr_t)h1 % 16) == 0, "relu_bits: C %% 32 == 0, aligned input");
+  const long long words = pixels * (C / 32);
+  relu_bits_kernel<<<b2_grid_for(words, 256, 8), 256, 0, (cudaStream_t)stream>>>((const bf16*)h1, words, relu_bits);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_conv1_fwd_bits(const float* x, const float* w, const float* bias, int B, int Tin, int F, int C, void* h1,
+                                      unsigned int* relu_bits, void* stream) {
   B2_CHECK_ARG(B > 0 && Tin >= 3 && F >= 3 && C % 8 == 0 && B <= 65535, "conv1_fwd: bad shape B=%d Tin=%d F=%d C=%d", B, Tin, F, C);
   const int T1 = (Tin - 3) / 2 + 1, F1 = (F - 3) / 2 + 1;
   cudaStream_t st = (cudaStream_t)stream;
   const size_t smem = (size_t)(2 * TR1 + 1) * F * sizeof(float);
   B2_CHECK_ARG(smem <= 48 * 1024 && C <= 2048, "conv1_fwd: F or C too large");
+  B2_CHECK_ARG(((uintptr_t)w % 16) == 0 && ((uintptr_t)bias % 16) == 0 && ((uintptr_t)h1 % 16) == 0, "conv1_fwd: 16-byte aligned w, bias, h1");
   B2_SCOPE(FAM_SUBSAMPLE, st, 18.0 * B * T1 * F1 * C, 4.0 * B * Tin * F + 2.0 * B * T1 * F1 * C);
-  conv1_fwd_kernel<<<dim3((T1 + TR1 - 1) / TR1, B), 256, smem, st>>>(x, w, bias, Tin, F, C, T1, F1, (bf16*)h1);
+  B2_CHECK_ARG(relu_bits == nullptr || C % 32 == 0, "conv1_fwd: the ReLU bit rows need C %% 32 == 0");
+  conv1_fwd_kernel<<<dim3((T1 + TR1 - 1) / TR1, B), 256, smem, st>>>(x, w, bias, Tin, F, C, T1, F1, (bf16*)h1, relu_bits);
   B2_LAUNCH_CHECK();
   return 0;
 }

@@ -357,13 +357,27 @@ def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta):
 
 
 # ---- subsampling --------------------------------------------------------------------------------------------------
-def conv1_fwd(x, w, bias):
+def conv1_fwd(x, w, bias, want_bits: bool = False):
+    """relu(conv.0(x) + bias) -> bf16 [B,T1,F1,C]; want_bits: also the (h1 > 0) bit rows int32 [B*T1*F1, C/32] that
+    conv2_dgrad_relu reads instead of h1 (C % 256 == 0)."""
     B, Tin, F = x.shape
     Cc = w.shape[0]
     T1, F1 = (Tin - 3) // 2 + 1, (F - 3) // 2 + 1
     h1 = torch.empty(B, T1, F1, Cc, device=x.device, dtype=torch.bfloat16)
-    check(_lib.lib().b200slu_conv1_fwd(ptr(x), ptr(w), ptr(bias), B, Tin, F, Cc, ptr(h1), stream_ptr()), "conv1_fwd")
-    return h1
+    if not want_bits:
+        check(_lib.lib().b200slu_conv1_fwd(ptr(x), ptr(w), ptr(bias), B, Tin, F, Cc, ptr(h1), stream_ptr()), "conv1_fwd")
+        return h1
+    bits = torch.empty(B * T1 * F1, Cc // 32, device=x.device, dtype=torch.int32)
+    check(_lib.lib().b200slu_conv1_fwd_bits(ptr(x), ptr(w), ptr(bias), B, Tin, F, Cc, ptr(h1), ptr(bits), stream_ptr()), "conv1_fwd")
+    return h1, bits
+
+
+def relu_bits(h1):
+    Cc = h1.shape[-1]
+    pixels = h1.numel() // Cc
+    bits = torch.empty(pixels, Cc // 32, device=h1.device, dtype=torch.int32)
+    check(_lib.lib().b200slu_relu_bits(ptr(h1), pixels, Cc, ptr(bits), stream_ptr()), "relu_bits")
+    return bits
 
 
 def conv1_bwd(dh1, x, dw, db):
@@ -410,10 +424,14 @@ def conv2_wgrad(dh2, h1, dw_accum):
     check(_lib.lib().b200slu_conv2_wgrad(ptr(dh2), ptr(h1), B, T1, F1, Cc, ptr(dw_accum), stream_ptr()), "conv2_wgrad")
 
 
-def conv2_dgrad_relu(dh2, w16, h1):
+def conv2_dgrad_relu(dh2, w16, h1, bits=None):
+    """dh1 = (h1 > 0) * conv_transpose(dh2, w): `bits` = the (h1 > 0) rows from conv1_fwd(want_bits=True), derived from h1 here
+    when the caller has none."""
     B, T1, F1, Cc = h1.shape
+    if bits is None:
+        bits = relu_bits(h1)
     dh1 = torch.empty_like(h1)
-    check(_lib.lib().b200slu_conv2_dgrad_relu(ptr(dh2), ptr(w16), ptr(h1), B, T1, F1, Cc, ptr(dh1), stream_ptr()), "conv2_dgrad")
+    check(_lib.lib().b200slu_conv2_dgrad_relu(ptr(dh2), ptr(w16), ptr(bits), B, T1, F1, Cc, ptr(dh1), stream_ptr()), "conv2_dgrad")
     return dh1
 
 

@@ -311,12 +311,16 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     B, Tin, _ = feats.shape
     e = p + ".embed"
     C_ = P[e + ".conv.0.weight"].shape[0]
-    h1 = K.conv1_fwd(feats, P[e + ".conv.0.weight"].reshape(C_, 9), P[e + ".conv.0.bias"])
+    Tin_, F_ = feats.shape[1], feats.shape[2]
+    implicit = K.conv2_implicit_supported(B, (Tin_ - 3) // 2 + 1, (F_ - 3) // 2 + 1, C_)
+    h1 = K.conv1_fwd(feats, P[e + ".conv.0.weight"].reshape(C_, 9), P[e + ".conv.0.bias"], want_bits=implicit)
+    h1, h1_bits = h1 if implicit else (h1, None)
     _, T1, F1, _ = h1.shape
     T, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
-    if K.conv2_implicit_supported(B, T1, F1, C_):
-        # implicit GEMM: the operand loads walk h1 through TMA im2col maps, no [pixels, 9 C] matrix anywhere
-        col = "implicit"
+    if implicit:
+        # implicit GEMM: the operand loads walk h1 through TMA im2col maps, no [pixels, 9 C] matrix anywhere; the backward
+        # gets h1's ReLU mask as bit rows
+        col = h1_bits
         h2 = K.conv2_fwd(h1, W[e + ".conv.2.weight"], P[e + ".conv.2.bias"])
     else:
         col = K.im2col(h1)
@@ -402,9 +406,9 @@ def encoder_bwd(denc, saved, P, W, G, cfg: EncCfg, p: str = "encoder", on_ready=
     K.gemm(g, h2v, trans=True, out=G[e + ".out.0.weight"], accumulate=True)
     dh2 = K.gemm(g, W[e + ".out.0.weight"], trans_b=True, act_grad_input=h2v, act_grad="relu").view(-1, C_)
     K.colsum(dh2, G[e + ".conv.2.bias"])
-    if isinstance(col, str):
+    if col is not None and col.dtype == torch.int32:
         K.conv2_wgrad(dh2, h1, G[e + ".conv.2.weight"])
-        dh1 = K.conv2_dgrad_relu(dh2, W[e + ".conv.2.weight"], h1)
+        dh1 = K.conv2_dgrad_relu(dh2, W[e + ".conv.2.weight"], h1, bits=col)
     else:
         if col is None:
             col = K.im2col(h1)

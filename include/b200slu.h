@@ -234,13 +234,19 @@ int b200slu_col2im3x3s2_relu(const void* dcol, const void* h1, int B, int T1, in
  * channels-last; w bf16 [C, 9 C] with k = (kt*3+kf)*C + ci; h2 / dh2 bf16 [B*T2*F2, C], T2 = (T1-3)/2+1, F2 = (F1-3)/2+1.
  *   fwd:    h2 = relu(conv(h1) + bias)
  *   wgrad:  dw_accum (fp32 [C, 9 C]) += dh2^T * im2col(h1)
- *   dgrad:  dh1 = (h1 > 0) * conv_transpose(dh2, w), one gather GEMM per output parity class (4 / 2 / 2 / 1 taps)
+ *   dgrad:  dh1 = relu_bits * conv_transpose(dh2, w), one gather GEMM per output parity class (4 / 2 / 2 / 1 taps)
  * Needs C % 256 == 0 (b200slu_conv2_implicit_supported); callers keep the im2col + GEMM path otherwise. */
 int b200slu_conv2_implicit_supported(int B, int T1, int F1, int C);
 int b200slu_conv2_fwd(const void* h1, int B, int T1, int F1, int C, const void* w, const float* bias, void* h2, void* stream);
 int b200slu_conv2_wgrad(const void* dh2, const void* h1, int B, int T1, int F1, int C, float* dw_accum, void* stream);
-int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const void* h1, int B, int T1, int F1, int C, void* dh1,
-                             void* stream);
+int b200slu_conv2_dgrad_relu(const void* dh2, const void* w, const unsigned int* relu_bits, int B, int T1, int F1, int C,
+                             void* dh1, void* stream);
+/* relu_bits: u32 [B*T1*F1, C/32], bit (c % 32) of word c / 32 of a pixel's row = (h1[pixel][c] > 0) -- all dgrad needs of
+ * h1, at 1/16 of its bytes.  b200slu_conv1_fwd_bits writes it next to h1 (C % 256 == 0); b200slu_relu_bits derives it from
+ * an h1 the caller already holds. */
+int b200slu_conv1_fwd_bits(const float* x, const float* w, const float* bias, int B, int Tin, int F, int C, void* h1,
+                           unsigned int* relu_bits, void* stream);
+int b200slu_relu_bits(const void* h1, long long pixels, int C, unsigned int* relu_bits, void* stream);
 
 /* ---- K6: CTC (espnet2/asr/ctc.py:52-63,82-95; lattice espnet/nets/pytorch_backend/gtn_ctc.py:26-36) -----
  * logits f32 [B,T,ldv] (log_softmax fused); labels int32 [B,Lmax]; all lengths int32 on the device. */

@@ -352,10 +352,19 @@ def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta):
     return _r(gamma * mean_rstd[C:] * (dz - dz.mean(0) - xh * (dz * xh).mean(0)))
 
 
-def conv1_fwd(x, w, bias):
+def conv1_fwd(x, w, bias, want_bits=False):
     C = w.shape[0]
     y = torch.relu(F.conv2d(x[:, None], w.reshape(C, 1, 3, 3), bias, stride=2))  # [B,C,T1,F1]
-    return _r(y.permute(0, 2, 3, 1).contiguous())
+    h1 = _r(y.permute(0, 2, 3, 1).contiguous())
+    return (h1, relu_bits(h1)) if want_bits else h1
+
+
+def relu_bits(h1):
+    """int32 [pixels, C/32]: bit (c % 32) of word c // 32 = (h1[pixel, c] > 0)."""
+    C = h1.shape[-1]
+    b = (h1.float().reshape(-1, C // 32, 32) > 0).to(torch.int64)
+    v = (b << torch.arange(32)).sum(-1)
+    return torch.where(v >= 2 ** 31, v - 2 ** 32, v).to(torch.int32)
 
 
 def conv1_bwd(dh1, x, dw, db):
@@ -401,7 +410,7 @@ def conv2_wgrad(dh2, h1, dw_accum):
     gemm(dh2, im2col(h1), trans=True, out=dw_accum, accumulate=True)
 
 
-def conv2_dgrad_relu(dh2, w16, h1):
+def conv2_dgrad_relu(dh2, w16, h1, bits=None):
     B, T1, F1, C = h1.shape
     T2, F2 = (T1 - 3) // 2 + 1, (F1 - 3) // 2 + 1
     d = (dh2.float() @ w16.float()).reshape(B, T2, F2, 3, 3, C)   # one rounding, after the sum over taps

@@ -366,6 +366,11 @@ def test_subsampling(B, Tin, F, C):
     x, w, b = rnd(B, Tin, F, seed=1), rnd(C, 9, seed=2) * 0.3, rnd(C, seed=3) * 0.1
     h1 = K().conv1_fwd(x.cuda(), w.cuda(), b.cuda())
     close(h1, E.conv1_fwd(x, w, b), 1e-2, "conv1")
+    if C % 256 == 0:  # the (h1 > 0) bit rows conv.2's dgrad reads: next to h1 from the same kernel, or derived from h1
+        h1b, bits = K().conv1_fwd(x.cuda(), w.cuda(), b.cuda(), want_bits=True)
+        assert torch.equal(h1b, h1)
+        assert torch.equal(bits.cpu(), E.relu_bits(h1.cpu()))
+        assert torch.equal(K().relu_bits(h1), bits)
     col = K().im2col(h1)
     assert torch.equal(col.cpu(), E.im2col(h1.cpu()))
     dcol = rnd(*col.shape, seed=4).to(BF)

