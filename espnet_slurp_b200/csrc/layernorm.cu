@@ -11,6 +11,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace {
 
@@ -197,6 +198,175 @@ __global__ void __launch_bounds__(NG <= 2 ? 384 : 256, 1) ln_bwd_kernel(const vo
   }
 }
 
+// The same backward with the row loads decoupled from the arithmetic: every warp owns a ring of NBUF row slots in shared
+// memory (x | dy | dx_add of one row each), filled by 1-D bulk copies that complete on the slot's mbarrier, issued NBUF rows
+// ahead.  The register-only version above has each warp wait out a full HBM round trip per row with 12 warps per SM --
+// about 30 KB in flight per SM against the ~45 KB that 6.5 TB/s x 1 us of latency asks for (measured 0.61 of the HBM
+// peak); here 12 warps x NBUF x 5 KB are in flight whatever the arithmetic is doing.  D <= 512.
+constexpr int LNP_WARPS = 12;
+template <int NG, bool DY_F32, bool GSUM>
+__global__ void __launch_bounds__(LNP_WARPS * 32, 1) ln_bwd_pipe_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
+                                                     const float* __restrict__ gamma, const float* __restrict__ stats,
+                                                     const float* __restrict__ dx_add, int M, int D, float* __restrict__ dx,
+                                                     float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                     bf16* __restrict__ g16, float g_alpha, B2Dropout drop,
+                                                     float* __restrict__ gsum, int nbuf) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  float* sm = reinterpret_cast<float*>(smraw);  // [3][D] block partials, then the barriers, then the row slots
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ngroups = D >> 3;
+  const uint32_t bx = (uint32_t)D * 4u, bdy = (uint32_t)D * (DY_F32 ? 4u : 2u), badd = dx_add != nullptr ? (uint32_t)D * 4u : 0u;
+  const uint32_t slot = bx + bdy + badd;
+  const uint32_t bar0 = smem_u32(smraw) + 3u * D * 4u + (uint32_t)(warp * nbuf) * 8u;
+  const uint32_t ring_off = (3u * D * 4u + (uint32_t)(LNP_WARPS * nbuf) * 8u + 127u) & ~127u;
+  const uint32_t buf0 = ring_off + (uint32_t)(warp * nbuf) * slot;  // byte offset of this warp's first slot
+  for (int i = threadIdx.x; i < 3 * D; i += blockDim.x) sm[i] = 0.f;
+  if (lane == 0) {
+    for (int b = 0; b < nbuf; ++b) mbar_init(bar0 + b * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const long long W = (long long)gridDim.x * LNP_WARPS, gw = (long long)blockIdx.x * LNP_WARPS + warp;
+  const uint32_t sbase = smem_u32(smraw);
+  auto issue = [&](long long row, int b) {  // one lane
+    const uint32_t bar = bar0 + b * 8, dst = sbase + buf0 + (uint32_t)b * slot;
+    mbar_expect_tx(bar, slot);
+    bulk_g2s(dst, x + row * D, bx, bar);
+    bulk_g2s(dst + bx, reinterpret_cast<const unsigned char*>(dy_) + row * (long long)bdy, bdy, bar);
+    if (badd) bulk_g2s(dst + bx + bdy, dx_add + row * D, badd, bar);
+  };
+  if (lane == 0) {
+    for (int b = 0; b < nbuf; ++b)
+      if (gw + b * W < M) issue(gw + b * W, b);
+  }
+  float ga[NG][8];
+#pragma unroll
+  for (int i = 0; i < NG; ++i) {
+    const int g = lane + 32 * i;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ga[i][j] = 0.f;
+    if (g < ngroups) load8_f32(gamma + g * 8, ga[i]);
+  }
+  float dg[NG][8], db[NG][8], dc[GSUM ? NG : 1][8];
+#pragma unroll
+  for (int i = 0; i < NG; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f;
+#pragma unroll
+  for (int i = 0; i < (GSUM ? NG : 1); ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dc[i][j] = 0.f;
+
+  float2 st_next = gw < M ? *reinterpret_cast<const float2*>(stats + gw * 2) : make_float2(0.f, 0.f);
+  int b = 0;
+  uint32_t ph = 0;
+  for (long long row = gw; row < M; row += W) {
+    const float mean = st_next.x, rstd = st_next.y;
+    if (row + W < M) st_next = *reinterpret_cast<const float2*>(stats + (row + W) * 2);  // one row ahead of its use
+    mbar_wait(bar0 + b * 8, ph);
+    const unsigned char* sl = smraw + buf0 + (uint32_t)b * slot;
+    float xh[NG][8], dyg[NG][8], addv[NG][8];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        float xv[8], dyv[8];
+        load8_f32(reinterpret_cast<const float*>(sl) + g * 8, xv);
+        if (DY_F32)
+          load8_f32(reinterpret_cast<const float*>(sl + bx) + g * 8, dyv);
+        else
+          load8_bf16(reinterpret_cast<const bf16*>(sl + bx) + g * 8, dyv);
+        if (badd) load8_f32(reinterpret_cast<const float*>(sl + bx + bdy) + g * 8, addv[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] = (xv[j] - mean) * rstd;
+          dyg[i][j] = dyv[j] * ga[i][j];
+          c1 += dyg[i][j];
+          c2 += dyg[i][j] * xh[i][j];
+          dg[i][j] += dyv[j] * xh[i][j];
+          db[i][j] += dyv[j];
+        }
+      }
+    }
+    __syncwarp();  // every lane has read the slot: refill it with the row NBUF rows on
+    if (lane == 0 && row + (long long)nbuf * W < M) issue(row + (long long)nbuf * W, b);
+    if (++b == nbuf) {
+      b = 0;
+      ph ^= 1u;
+    }
+    c1 = warp_sum(c1) / (float)D;
+    c2 = warp_sum(c2) / (float)D;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (dyg[i][j] - c1 - xh[i][j] * c2);
+        if (badd) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += addv[i][j];
+        }
+        store8_f32(dx + row * D + g * 8, o);
+        if (g16 != nullptr) {
+          dropout8(drop, (unsigned long long)row * D + g * 8, o);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] *= g_alpha;
+          if (GSUM) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dc[i][j] += o[j];
+          }
+          store8_bf16(g16 + row * D + g * 8, o);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NG; ++i) {
+    const int g = lane + 32 * i;
+    if (g < ngroups) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&sm[g * 8 + j], dg[i][j]);
+        atomicAdd(&sm[D + g * 8 + j], db[i][j]);
+        if (GSUM) atomicAdd(&sm[2 * D + g * 8 + j], dc[i][j]);
+      }
+    }
+  }
+  __syncthreads();
+  const bool vec4 = (((uintptr_t)dgamma | (uintptr_t)dbeta | (GSUM ? (uintptr_t)gsum : 0)) & 15) == 0 && (D & 3) == 0;
+  if (vec4) {
+    for (int i = threadIdx.x; i < D / 4; i += blockDim.x) {
+      atomicAdd(reinterpret_cast<float4*>(dgamma) + i, reinterpret_cast<const float4*>(sm)[i]);
+      atomicAdd(reinterpret_cast<float4*>(dbeta) + i, reinterpret_cast<const float4*>(sm + D)[i]);
+      if (GSUM) atomicAdd(reinterpret_cast<float4*>(gsum) + i, reinterpret_cast<const float4*>(sm + 2 * D)[i]);
+    }
+  } else {
+    for (int i = threadIdx.x; i < D; i += blockDim.x) {
+      atomicAdd(dgamma + i, sm[i]);
+      atomicAdd(dbeta + i, sm[D + i]);
+      if (GSUM) atomicAdd(gsum + i, sm[2 * D + i]);
+    }
+  }
+}
+
+template <int NG, bool F32, bool GS>
+int launch_ln_bwd_pipe(const void* dy, const float* x, const float* gamma, const float* stats, const float* dx_add, int M, int D,
+                       float* dx, float* dgamma, float* dbeta, bf16* g16, float g_alpha, B2Dropout drop, float* gsum, int nbuf,
+                       size_t smem, cudaStream_t st) {
+  auto kern = ln_bwd_pipe_kernel<NG, F32, GS>;
+  static unsigned long long configured = 0;  // per device
+  if (!b2_device_done(configured)) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+    b2_device_mark(configured);
+  }
+  const long long warps = M;
+  const int grid = (int)min((long long)b2_num_sms(), (warps + LNP_WARPS - 1) / LNP_WARPS);
+  kern<<<grid, LNP_WARPS * 32, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta, g16, g_alpha, drop, gsum, nbuf);
+  return 0;
+}
+
 }  // namespace
 
 extern "C" int b200slu_layernorm_fwd(const float* x, const float* gamma, const float* beta, int M, int D, float eps,
@@ -232,6 +402,36 @@ extern "C" int b200slu_layernorm_bwd(const void* dy, int dy_is_f32, const float*
   const size_t smem = (g_colsum_accum ? 3 : 2) * (size_t)D * sizeof(float);
   B2_SCOPE(FAM_LN, st, 0,
            (double)M * D * ((dy_is_f32 ? 4.0 : 2.0) + 4.0 + 4.0 + (dx_add ? 4.0 : 0.0) + (g_bf16 ? 2.0 : 0.0)));
+  // rows through a shared-memory ring (D <= 512, aligned rows): see ln_bwd_pipe_kernel
+  static const bool pipe_off = getenv("B200SLU_LN_PIPE") && atoi(getenv("B200SLU_LN_PIPE")) == 0;  // tuning / A-B only
+  if (!pipe_off && D <= 512 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)dy % 16) == 0 && ((uintptr_t)dx_add % 16) == 0) {
+    const size_t slot = (size_t)D * (4 + (dy_is_f32 ? 4 : 2) + (dx_add ? 4 : 0));
+    const size_t fixed = 3 * (size_t)D * 4 + 1024;
+    int nbuf = (int)((232448 - fixed) / (LNP_WARPS * slot));
+    if (nbuf > 4) nbuf = 4;
+    if (nbuf >= 2) {
+      const size_t psmem = ((3 * (size_t)D * 4 + (size_t)LNP_WARPS * nbuf * 8 + 127) & ~(size_t)127) + (size_t)LNP_WARPS * nbuf * slot;
+#define LN_P(NG, F32, GS)                                                                                                  \
+  B2_TRY((launch_ln_bwd_pipe<NG, F32, GS>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta, (bf16*)g_bf16, g_alpha, drop, \
+                                          g_colsum_accum, nbuf, psmem, st)))
+#define LN_PP(NG)                                        \
+  do {                                                   \
+    if (dy_is_f32) {                                     \
+      if (g_colsum_accum) LN_P(NG, true, true);          \
+      else LN_P(NG, true, false);                        \
+    } else {                                             \
+      if (g_colsum_accum) LN_P(NG, false, true);         \
+      else LN_P(NG, false, false);                       \
+    }                                                    \
+  } while (0)
+      if (D <= 256) LN_PP(1);
+      else LN_PP(2);
+#undef LN_PP
+#undef LN_P
+      B2_LAUNCH_CHECK();
+      return 0;
+    }
+  }
 #define LN_B3(NG, F32, GS)                                                                                                \
   ln_bwd_kernel<NG, F32, GS><<<grid, threads, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta, (bf16*)g_bf16, \
                                                           g_alpha, drop, g_colsum_accum)

@@ -54,6 +54,12 @@ __device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+// 1-D bulk copy global -> shared (16-byte aligned addresses, size a multiple of 16), completion counted on an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
 // im2col mode (tensor map from cuTensorMapEncodeIm2col over a [N, H, W, C] tensor): loads `pixelsPerColumn` consecutive
 // pixels of the map's bounding box starting at base pixel (w, h, n), walking w then h then n in steps of the map's
 // traversal strides, `channelsPerPixel` channels from c; (off_w, off_h) is the filter tap added to every pixel.  The box
