@@ -57,6 +57,11 @@ struct AttnArgs {
   const int* lens;
   bf16 *p, *pd, *ctx;
   long long ld_p, ldctx;
+  // key chunk of a longer key axis (b200slu_relattn_fwd_chunk): this launch sees keys [key_off, key_off + Tk) of every
+  // utterance.  key_off shifts the rel-pos window, the valid length and the dropout counter; p already points at column
+  // key_off (p_cols = columns left in the row); lse2 receives log2 of each row's partition sum over the chunk.
+  int key_off, p_cols;
+  float* lse2;
   uint32_t off_k, off_p, off_v, off_bar, tmem_cols;
   B2Dropout drop;
   long long* dbg;  // tuning only (B200SLU_ATTN_DEBUG=1): per-CTA phase time stamps
@@ -85,7 +90,7 @@ __device__ __forceinline__ void softmax_tile(const AttnArgs& a, uint8_t* smem, u
   const int nch = TKP / CH, n0 = (nch + 1) / 2;
   const int cbeg = hs ? n0 : 0, nmine = hs ? nch - n0 : n0;  // this warp's chunks: [cbeg, cbeg + nmine), nmine <= NCH
   const int jbeg = cbeg * CH;
-  const int nvalid = a.causal ? min(len_b, i + 1) : len_b;
+  const int nvalid = a.causal ? min(len_b, i + 1 - a.key_off) : len_b;
   // shift ring: 64 window columns per thread; positions 64..79 mirror 0..15 so that the 16 lane-shifted scalar loads of a
   // chunk are base + immediate (no wrap); the 84-float row pitch keeps 16-byte stores and shifted loads conflict-free
   const uint32_t ring = sbase + (uint32_t)(warp * 32 + lane) * (RING_LD * 4);
@@ -178,6 +183,10 @@ __device__ __forceinline__ void softmax_tile(const AttnArgs& a, uint8_t* smem, u
   if (mw != -INFINITY) tot += sw * exp2f(mw - mrow);
   if (mo != -INFINITY) tot += so * exp2f(mo - mrow);
   const float inv = tot > 0.f ? 1.f / tot : 0.f;
+  // chunked keys: log2 of the row's partition sum over THIS chunk (-inf when no key of the chunk is valid), from which the
+  // combine pass rescales p and the context rows to the softmax over all chunks
+  if (a.lse2 != nullptr && hs == 0 && row_ok)
+    a.lse2[((long long)h * a.B + b) * a.Tq + i] = tot > 0.f ? mrow + log2f(tot) : -INFINITY;
 
   // p = e * exp2(m_c - m) / sum -> HBM (bf16, one 32-byte sector per thread and chunk); dropout(p) -> K-major A operand
   const long long rg = ((long long)h * a.B + b) * a.Tq + i;  // row of the head-major [H,B,Tq,ld_p] tensors
@@ -198,11 +207,11 @@ __device__ __forceinline__ void softmax_tile(const AttnArgs& a, uint8_t* smem, u
       uint32_t pk[CH / 2];
 #pragma unroll
       for (int e = 0; e < CH / 2; ++e) pk[e] = pack_bf16x2(v[2 * e], v[2 * e + 1]);
-      const bool full = row_ok && j0 + CH <= a.ld_p, wide = (a.ld_p & 15) == 0;  // row pitch a multiple of 32 bytes
+      const bool full = row_ok && j0 + CH <= a.p_cols, wide = (a.ld_p & 15) == 0;  // row pitch a multiple of 32 bytes
       auto store16 = [&](bf16* dst, const uint32_t (&w)[CH / 2]) {
         if (full && wide) {
           stg256(dst, w);
-        } else if (row_ok && j0 < a.ld_p) {
+        } else if (row_ok && j0 < a.p_cols) {
           *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
           if (full) *reinterpret_cast<uint4*>(dst + 8) = make_uint4(w[4], w[5], w[6], w[7]);
         }
@@ -213,7 +222,7 @@ __device__ __forceinline__ void softmax_tile(const AttnArgs& a, uint8_t* smem, u
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
           uint32_t w[4];
-          dropout_lanes8(dk, (unsigned long long)(rg * a.ld_p + j0 + g * 8) >> 3, w);
+          dropout_lanes8(dk, (unsigned long long)(rg * a.ld_p + a.key_off + j0 + g * 8) >> 3, w);
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const uint32_t mlo = (w[e] & 0xffffu) >= dk.thr ? 0x0000ffffu : 0u, mhi = (w[e] >> 16) >= dk.thr ? 0xffff0000u : 0u;
@@ -287,7 +296,7 @@ relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_cons
       tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
       // first position row the tile can reach = source column of (last query row of the tile, key 0); may be negative:
       // out-of-range rows are zero-filled
-      const int c0 = b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col;
+      const int c0 = b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + a.key_off;
       tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
       tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
     }
@@ -301,7 +310,7 @@ relattn_fwd_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid_cons
   }
   // global scalars of the softmax (valid length, dropout key): fetched here so their latency hides behind the TMA loads
   b2_pdl_wait();
-  const int len_b = a.lens != nullptr ? min(a.lens[b], a.Tk) : a.Tk;
+  const int len_b = a.lens != nullptr ? max(0, min(a.lens[b] - a.key_off, a.Tk)) : a.Tk;
   B2DropKey dk = {0ull, 0u, 1.f};
   const bool dropping = a.drop.p > 0.f;
   if (dropping) dk = dropout_key(a.drop);
@@ -465,14 +474,14 @@ relattn_fwd_pipe_kernel(const __grid_constant__ CUtensorMap map_qu, const __grid
       tma_load_3d(s_k, &map_k, bar_qk, h * DK, 0, b);
       if (a.rel) {
         tma_load_3d(s_qv, &map_qv, bar_qk, h * DK, i0, b);
-        const int c0 = b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col;
+        const int c0 = b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + a.key_off;
         tma_load_3d(s_p, &map_pos, bar_qk, h * DK, c0, 0);
         tma_load_3d(s_p + (WIN / 2) * 128, &map_pos, bar_qk, h * DK, c0 + WIN / 2, 0);
       }
       mbar_expect_tx(bar_v, (uint32_t)(TKP * 128));
       tma_load_3d(s_v, &map_v, bar_v, h * DK, 0, b);
     }
-    const int len_b = a.lens != nullptr ? min(a.lens[b], a.Tk) : a.Tk;
+    const int len_b = a.lens != nullptr ? max(0, min(a.lens[b] - a.key_off, a.Tk)) : a.Tk;
     if (tid == 0) {
       mbar_wait(bar_qk, par);
       mbar_wait(s_free + g * 8, tokpar);  // the other group's softmax pass has read its scores
@@ -577,6 +586,9 @@ struct AttnBwdArgs {
   B2Dropout drop;
   long long* dbg;  // tuning only (B200SLU_ATTN_BWD_DEBUG): CTA 0's cycles per phase, summed over its query tiles
   int dbgflags;    // tuning only (B200SLU_ATTN_BWD_FLAGS): 1 = no d(pos) reduce, 2 = no load prefetch
+  // key chunk of a longer key axis (b200slu_relattn_bwd_chunk): keys [key_off, key_off + Tk) of kv_rows per utterance;
+  // k, v, dk, dv and p already point at key / column key_off.  key_off shifts the rel-pos window and the dropout counter.
+  int key_off, kv_rows;
 };
 
 template <bool REL>
@@ -655,7 +667,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
     tma_load_3d(s_qu, &map_qu, bar_q, h_ * DK, i0_, b_);
     for (int kb = 0; kb < nblk; ++kb) tma_load_3d(s_pd + kb * BLK, &map_p, bar_q, kb * 64, i0_, h_ * a.B + b_);
     if (REL) {
-      const int c0_ = b2_rel_shift_src(i0_ + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col;
+      const int c0_ = b2_rel_shift_src(i0_ + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + a.key_off;
       tma_load_3d(s_pos, &map_pos, bar_q, h_ * DK, c0_, 0);
       tma_load_3d(s_pos + (a.WIN / 2) * 128, &map_pos, bar_q, h_ * DK, c0_ + a.WIN / 2, 0);
     }
@@ -677,7 +689,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
       const uint32_t par = n_q & 1u;
       if ((a.dbgflags & 2) && tid == 0 && !(unit == (int)blockIdx.x && qt == 0)) issue_loads(unit, qt);
       // first position row of the window this tile reaches (the forward's window); may be negative: zero-filled
-      const int c0 = REL ? b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col : 0;
+      const int c0 = REL ? b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + a.key_off : 0;
       // this thread's half (32 columns) of its row of the forward output, for delta
       uint4 cx[4];
       if (row_ok) {
@@ -763,7 +775,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
 #pragma unroll
               for (int g = 0; g < 2; ++g) {
                 float m8[8];
-                dropout_mul8(dk, (unsigned long long)(rg * a.ld_p + j0 + g * 8) >> 3, dk.inv, m8);
+                dropout_mul8(dk, (unsigned long long)(rg * a.ld_p + a.key_off + j0 + g * 8) >> 3, dk.inv, m8);
 #pragma unroll
                 for (int e = 0; e < 8; ++e) mul[g * 8 + e] = m8[e];
               }
@@ -833,7 +845,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
           tmem_ld32(tlane + BWD_DV_COL + m * DK + hs * 32, ov_);
           tmem_ld_wait();
           if (j < a.Tk) {
-            const long long row = ((long long)b * a.Tk + j) * a.lddkv + h * DK + hs * 32;
+            const long long row = ((long long)b * a.kv_rows + j) * a.lddkv + h * DK + hs * 32;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               float v[8];
@@ -1056,20 +1068,29 @@ extern "C" int b200slu_relattn_supported(int Tq, int Tk, int dk, int relpos_mode
   return relpos_mode == B200SLU_RELPOS_NONE;
 }
 
-extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
-                                   const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk,
-                                   int relpos_mode, int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx,
-                                   long long ldctx, float drop_p, unsigned long long seed, unsigned int site, void* stream) {
+extern "C" int b200slu_relattn_chunk_supported(int Tq, int Tk_chunk, int dk, int relpos_mode) {
+  return dk == DK && Tq >= 1 && Tk_chunk >= 1 && Tk_chunk <= MAX_TK &&
+         (relpos_mode == B200SLU_RELPOS_LATEST || relpos_mode == B200SLU_RELPOS_NONE);
+}
+
+// chunk form: keys [key_off, key_off + Tk) of kv_rows keys per utterance; k, v, p, p_drop point at key / column key_off
+static int relattn_fwd_impl(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
+                            const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk,
+                            int relpos_mode, int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx,
+                            long long ldctx, float drop_p, unsigned long long seed, unsigned int site, int key_off, int kv_rows,
+                            float* lse2, void* stream) {
   B2_CHECK_ARG(B > 0 && H > 0, "relattn_fwd: empty problem");
-  B2_CHECK_ARG(b200slu_relattn_supported(Tq, Tk, DK, relpos_mode),
-               "relattn_fwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)",
-               MAX_TK, Tq, Tk, relpos_mode);
+  B2_CHECK_ARG(b200slu_relattn_chunk_supported(Tq, Tk, DK, relpos_mode) && key_off >= 0 && key_off % 16 == 0 &&
+                   kv_rows >= key_off + Tk && ld_p >= key_off + Tk,
+               "relattn_fwd: supports d_k = 64, <= %d keys per launch, rel-pos mode latest or none, key_off %% 16 == 0 (got Tq=%d "
+               "Tk=%d mode=%d key_off=%d kv_rows=%d)", MAX_TK, Tq, Tk, relpos_mode, key_off, kv_rows);
   const bool rel = relpos_mode == B200SLU_RELPOS_LATEST;
   B2_CHECK_ARG(qu != nullptr && k != nullptr && v != nullptr && p != nullptr && ctx != nullptr, "relattn_fwd: null operand");
   B2_CHECK_ARG(!rel || (qv != nullptr && pos != nullptr), "relattn_fwd: rel-pos mode needs q_v and the projected positions");
   B2_CHECK_ARG(drop_p > 0.f || p_drop == p || p_drop == nullptr, "relattn_fwd: without dropout p_drop must alias p (or be NULL)");
   B2_CHECK_ARG(ldq % 8 == 0 && ldkv % 8 == 0 && ldctx % 8 == 0 && ld_p % 8 == 0 && ld_p >= Tk && (!rel || ldpos % 8 == 0),
                "relattn_fwd: row strides must be multiples of 8 elements, ld_p >= Tk");
+  B2_CHECK_ARG(relpos_mode != B200SLU_RELPOS_LATEST || kv_rows == Tq, "relattn_fwd: rel-pos mode attends over the queries' own axis");
   B2_CHECK_ARG(((uintptr_t)qu % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 && ((uintptr_t)ctx % 16) == 0 &&
                    ((uintptr_t)p % 32) == 0 && ((uintptr_t)p_drop % 32) == 0 && (!rel || (((uintptr_t)qv % 16) == 0 && ((uintptr_t)pos % 16) == 0)),
                "relattn_fwd: operands must be 16-byte aligned");
@@ -1083,6 +1104,7 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
   a.lens = key_lens;
   a.p = (bf16*)p; a.pd = (p_drop != p) ? (bf16*)p_drop : nullptr; a.ctx = (bf16*)ctx;
   a.ld_p = ld_p; a.ldctx = ldctx;
+  a.key_off = key_off; a.p_cols = (int)(ld_p - key_off); a.lse2 = lse2;
   a.off_k = 2 * QT * 128;
   a.off_p = a.off_k + a.TKP * 128;
   a.off_v = a.off_p + (rel ? a.WIN * 128 : 0);
@@ -1099,8 +1121,8 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
   CUtensorMap mqu, mqv, mk, mv, mp;
   const int d = H * DK;
   B2_TRY(make_map3(&mqu, qu, d, Tq, ldq, B, (long long)Tq * ldq, QT));
-  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
-  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)kv_rows * ldkv, a.TKP));
+  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)kv_rows * ldkv, a.TKP));
   if (rel) {
     B2_TRY(make_map3(&mqv, qv, d, Tq, ldq, B, (long long)Tq * ldq, QT));
     // projected positions [2T-1, d], shared by all utterances: rank 2 (encoded as rank 3 with one slab)
@@ -1154,22 +1176,45 @@ extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq
   return 0;
 }
 
+extern "C" int b200slu_relattn_fwd(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
+                                   const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk,
+                                   int relpos_mode, int causal, float scale, void* p, void* p_drop, long long ld_p, void* ctx,
+                                   long long ldctx, float drop_p, unsigned long long seed, unsigned int site, void* stream) {
+  B2_CHECK_ARG(b200slu_relattn_supported(Tq, Tk, DK, relpos_mode),
+               "relattn_fwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)",
+               MAX_TK, Tq, Tk, relpos_mode);
+  return relattn_fwd_impl(qu, qv, ldq, k, v, ldkv, pos, ldpos, key_lens, B, H, Tq, Tk, relpos_mode, causal, scale, p, p_drop, ld_p,
+                          ctx, ldctx, drop_p, seed, site, 0, Tk, nullptr, stream);
+}
+
+extern "C" int b200slu_relattn_fwd_chunk(const void* qu, const void* qv, long long ldq, const void* k, const void* v,
+                                         long long ldkv, const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq,
+                                         int Tk_chunk, int relpos_mode, int causal, float scale, void* p, long long ld_p,
+                                         void* ctx_chunk, long long ldctx, float drop_p, unsigned long long seed, unsigned int site,
+                                         int key_off, int kv_rows, float* lse2, void* stream) {
+  B2_CHECK_ARG(lse2 != nullptr, "relattn_fwd_chunk: lse2 output required");
+  return relattn_fwd_impl(qu, qv, ldq, k, v, ldkv, pos, ldpos, key_lens, B, H, Tq, Tk_chunk, relpos_mode, causal, scale, p, p, ld_p,
+                          ctx_chunk, ldctx, drop_p, seed, site, key_off, kv_rows, lse2, stream);
+}
+
 extern "C" int b200slu_relattn_bwd_supported(int Tq, int Tk, int dk, int relpos_mode) {
   if (dk != DK || Tq < 1 || Tk < 1 || Tk > MAX_TK) return 0;
   if (relpos_mode == B200SLU_RELPOS_LATEST) return Tq == Tk;
   return relpos_mode == B200SLU_RELPOS_NONE;
 }
 
-extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
-                                   long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H,
-                                   int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
-                                   void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
-                                   unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
-                                   float* dpos_accum, long long lddpos, void* stream) {
+static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
+                            long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H,
+                            int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
+                            void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
+                            unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
+                            float* dpos_accum, long long lddpos, int key_off, int kv_rows, void* stream) {
   B2_CHECK_ARG(B > 0 && H > 0, "relattn_bwd: empty problem");
-  B2_CHECK_ARG(b200slu_relattn_bwd_supported(Tq, Tk, DK, relpos_mode),
-               "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
-               Tq, Tk, relpos_mode);
+  B2_CHECK_ARG(b200slu_relattn_chunk_supported(Tq, Tk, DK, relpos_mode) && key_off >= 0 && key_off % 16 == 0 &&
+                   kv_rows >= key_off + Tk && ld_p >= key_off + Tk && (key_off == 0 || d_ac == nullptr),
+               "relattn_bwd: supports d_k = 64, <= %d keys per launch, rel-pos mode latest or none, key_off %% 16 == 0 (got Tq=%d "
+               "Tk=%d mode=%d key_off=%d kv_rows=%d)", MAX_TK, Tq, Tk, relpos_mode, key_off, kv_rows);
+  B2_CHECK_ARG(relpos_mode != B200SLU_RELPOS_LATEST || kv_rows == Tq, "relattn_bwd: rel-pos mode attends over the queries' own axis");
   const bool rel = relpos_mode == B200SLU_RELPOS_LATEST;
   B2_CHECK_ARG(d_ctx && q_u && k && v && p && ctx && dq_u && dk_out && dv_out, "relattn_bwd: null operand");
   B2_CHECK_ARG(!rel || (q_v && pos && dq_v && dpos_accum), "relattn_bwd: rel-pos mode needs q_v, pos, dq_v and dpos_accum");
@@ -1192,6 +1237,7 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
   a.dq = (bf16*)dq_u; a.dk = (bf16*)dk_out; a.dv = (bf16*)dv_out; a.dac = (bf16*)d_ac;
   a.lddq = lddq; a.lddkv = lddkv; a.ld_p = ld_p;
   a.dqv = (bf16*)dq_v; a.dpos = dpos_accum; a.lddpos = lddpos;
+  a.key_off = key_off; a.kv_rows = kv_rows;
   // [pd tile | dO | Q_u | V] [dS tile] [K, later Q_v] [position window].  The first group is dead once dQ_u / dK / dV are
   // issued: the skewed d(bd) tile is built over it (dS, its source, stays).  An M = 128 MN-major read over the last key /
   // window tile may run past the blocks that exist into the next region: never faulting (bounded below), never stored.
@@ -1223,9 +1269,9 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
   const int d = H * DK;
   B2_TRY(make_map3(&mdo, d_ctx, d, Tq, lddo, B, (long long)Tq * lddo, QT));
   B2_TRY(make_map3(&mqu, q_u, d, Tq, ldq, B, (long long)Tq * ldq, QT));
-  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
-  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
-  B2_TRY(make_map3(&mp, p, ld_p, Tq, ld_p, (long long)H * B, (long long)Tq * ld_p, QT));
+  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)kv_rows * ldkv, a.TKP));
+  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)kv_rows * ldkv, a.TKP));
+  B2_TRY(make_map3(&mp, p, ld_p - key_off, Tq, ld_p, (long long)H * B, (long long)Tq * ld_p, QT));
   if (rel) {
     B2_TRY(make_map3(&mqv, q_v, d, Tq, ldq, B, (long long)Tq * ldq, QT));
     B2_TRY(make_map3(&mpos, pos, d, 2 * Tq - 1, ldpos, 1, 0, a.WIN / 2));
@@ -1262,5 +1308,145 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
             "dS pass %.0f, dQu/dK/dV MMA %.0f, dQu drain + skew %.0f, dQv/dPos MMA %.0f, drains %.0f\n", Tq, Tk, (int)rel, smem, hbuf[7],
             hbuf[0] / n, hbuf[1] / n, hbuf[2] / n, hbuf[3] / n, hbuf[4] / n, hbuf[5] / n, hbuf[6] / n);
   }
+  return 0;
+}
+
+extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
+                                   long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H,
+                                   int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
+                                   void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
+                                   unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
+                                   float* dpos_accum, long long lddpos, void* stream) {
+  B2_CHECK_ARG(b200slu_relattn_bwd_supported(Tq, Tk, DK, relpos_mode),
+               "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
+               Tq, Tk, relpos_mode);
+  return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u, lddq, dk_out,
+                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, 0, Tk, stream);
+}
+
+extern "C" int b200slu_relattn_bwd_chunk(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k,
+                                         const void* v, long long ldkv, const void* p, long long ld_p, const void* ctx,
+                                         long long ldctx, int B, int H, int Tq, int Tk_chunk, int relpos_mode, float scale,
+                                         void* dq_u_chunk, long long lddq, void* dk_out, void* dv_out, long long lddkv, float drop_p,
+                                         unsigned long long seed, unsigned int site, const void* q_v, const void* pos,
+                                         long long ldpos, void* dq_v_chunk, float* dpos_accum, long long lddpos, int key_off,
+                                         int kv_rows, void* stream) {
+  return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk_chunk, relpos_mode, scale, dq_u_chunk,
+                          lddq, dk_out, dv_out, lddkv, nullptr, drop_p, seed, site, q_v, pos, ldpos, dq_v_chunk, dpos_accum, lddpos,
+                          key_off, kv_rows, stream);
+}
+
+// ----------------------------------------------------------------------------- key chunks -> one softmax
+namespace {
+
+constexpr int MAX_CHUNKS = 16;
+
+// One warp per (head, utterance, query) row.  alpha_c = 2^(lse2_c - LSE2) with LSE2 = log2 sum_c 2^lse2_c rescales what each
+// chunk launch normalised over its own keys: p[row, chunk c's columns] *= alpha_c in place (bf16), ctx = sum_c alpha_c ctx_c.
+__global__ void __launch_bounds__(256) relattn_combine_kernel(bf16* __restrict__ p, long long ld_p, int Tk, int chunk_keys, int nchunk,
+                                                              const float* __restrict__ lse2, long long rows,
+                                                              const bf16* __restrict__ ctx_chunks, long long chunk_stride,
+                                                              long long ldctx, bf16* __restrict__ ctx, long long ldout, int B, int H,
+                                                              int Tq) {
+  const int lane = threadIdx.x & 31;
+  for (long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows;
+       row += (long long)gridDim.x * (blockDim.x >> 5)) {
+    float al[MAX_CHUNKS];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < MAX_CHUNKS; ++c) {
+      al[c] = c < nchunk ? lse2[(long long)c * rows + row] : -INFINITY;
+      mx = fmaxf(mx, al[c]);
+    }
+    float tot = 0.f;
+#pragma unroll
+    for (int c = 0; c < MAX_CHUNKS; ++c) {
+      al[c] = (al[c] == -INFINITY) ? 0.f : exp2f(al[c] - mx);
+      tot += al[c];
+    }
+    const float inv = tot > 0.f ? 1.f / tot : 0.f;
+#pragma unroll
+    for (int c = 0; c < MAX_CHUNKS; ++c) al[c] *= inv;
+    // p row: groups of 8 columns; a group never straddles a chunk (chunk_keys % 8 == 0)
+    bf16* pr = p + row * ld_p;
+    for (int g = lane; g * 8 < Tk; g += 32) {
+      const int c = (g * 8) / chunk_keys;
+      float v[8], a = 0.f;
+#pragma unroll
+      for (int cc = 0; cc < MAX_CHUNKS; ++cc) a = cc == c ? al[cc] : a;
+      load8_bf16(pr + g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] *= a;
+      store8_bf16(pr + g * 8, v);
+    }
+    // context: row = (h, b, i) -> [b * Tq + i, h * 64 .. +64), 8 lanes x 8 channels
+    const long long hb = row / Tq;
+    const int i = (int)(row - hb * Tq), h = (int)(hb / B), b = (int)(hb - (long long)h * B);
+    if (lane < 8) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const long long off = ((long long)b * Tq + i) * ldctx + h * 64 + lane * 8;
+#pragma unroll
+      for (int c = 0; c < MAX_CHUNKS; ++c) {
+        if (c < nchunk && al[c] != 0.f) {
+          float v[8];
+          load8_bf16(ctx_chunks + (long long)c * chunk_stride + off, v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += al[c] * v[j];
+        }
+      }
+      store8_bf16(ctx + ((long long)b * Tq + i) * ldout + h * 64 + lane * 8, acc);
+    }
+  }
+}
+
+// dst[r, :] = sum_c src[c][r, :] (fp32 sum, bf16 in and out), rows of `cols` columns (cols % 8 == 0)
+__global__ void __launch_bounds__(256) sum_chunks_kernel(const bf16* __restrict__ src, long long chunk_stride, long long ld_src,
+                                                         int nchunk, long long rows, int cols, bf16* __restrict__ dst,
+                                                         long long ld_dst) {
+  const int gpr = cols >> 3;
+  const long long total = rows * gpr;
+  for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (long long)gridDim.x * blockDim.x) {
+    const long long r = it / gpr;
+    const int g = (int)(it - r * gpr);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < nchunk; ++c) {
+      float v[8];
+      load8_bf16(src + (long long)c * chunk_stride + r * ld_src + g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+    store8_bf16(dst + r * ld_dst + g * 8, acc);
+  }
+}
+
+}  // namespace
+
+extern "C" int b200slu_relattn_combine(void* p, long long ld_p, int Tk, int chunk_keys, int nchunk, const float* lse2,
+                                       const void* ctx_chunks, long long chunk_stride, long long ldctx, void* ctx, long long ldout,
+                                       int B, int H, int Tq, void* stream) {
+  B2_CHECK_ARG(B > 0 && H > 0 && Tq > 0 && Tk > 0 && nchunk >= 1 && nchunk <= MAX_CHUNKS && chunk_keys % 8 == 0 &&
+                   (long long)nchunk * chunk_keys >= Tk && ld_p % 8 == 0 && ldctx % 8 == 0 && ldout % 8 == 0 && chunk_stride % 8 == 0,
+               "relattn_combine: 1..%d chunks of a multiple of 8 keys covering Tk, strides multiples of 8 elements", MAX_CHUNKS);
+  B2_CHECK_ARG(((uintptr_t)p % 16) == 0 && ((uintptr_t)ctx_chunks % 16) == 0 && ((uintptr_t)ctx % 16) == 0, "relattn_combine: alignment");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long rows = (long long)H * B * Tq;
+  B2_SCOPE(FAM_ATTN, st, 0, (double)rows * (4.0 * Tk + 4.0 * nchunk + 2.0 * 64 * (nchunk + 1)));
+  relattn_combine_kernel<<<b2_grid_for(rows * 32, 256, 8), 256, 0, st>>>((bf16*)p, ld_p, Tk, chunk_keys, nchunk, lse2, rows,
+                                                                         (const bf16*)ctx_chunks, chunk_stride, ldctx, (bf16*)ctx,
+                                                                         ldout, B, H, Tq);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_sum_chunks_bf16(const void* src, long long chunk_stride, long long ld_src, int nchunk, long long rows,
+                                       int cols, void* dst, long long ld_dst, void* stream) {
+  B2_CHECK_ARG(nchunk >= 1 && rows > 0 && cols > 0 && cols % 8 == 0 && ld_src % 8 == 0 && ld_dst % 8 == 0 && chunk_stride % 8 == 0 &&
+                   ((uintptr_t)src % 16) == 0 && ((uintptr_t)dst % 16) == 0,
+               "sum_chunks: cols / strides multiples of 8 elements, 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 2.0 * rows * cols * (nchunk + 1));
+  sum_chunks_kernel<<<b2_grid_for(rows * (cols >> 3), 256, 8), 256, 0, st>>>((const bf16*)src, chunk_stride, ld_src, nchunk, rows, cols,
+                                                                             (bf16*)dst, ld_dst);
+  B2_LAUNCH_CHECK();
   return 0;
 }

@@ -258,30 +258,64 @@ def softmax_bwd(dpd, p, Tk: int, mode: str, scale: float, ld_bd: int = 0, drop: 
 
 
 # ---- fused attention (scores -> rel_shift -> softmax -> dropout -> context) --------------------------------------
-def relattn_supported(Tq: int, Tk: int, dk: int, mode: str) -> bool:
-    return bool(_lib.lib().b200slu_relattn_supported(Tq, Tk, dk, RELPOS[mode]))
+CHUNK_KEYS = 192  # keys per launch of the fused attention kernels (multiple of 64: a chunk is whole 64-column p blocks)
+
+
+def relattn_supported(Tq: int, Tk: int, dk: int, mode: str, causal: bool = False) -> bool:
+    """The fused attention kernels take any number of keys: up to 192 in one launch, more as key chunks + a combine pass
+    (causal masks only within one launch -- the decoder's token axis is short)."""
+    L = _lib.lib()
+    if Tk <= CHUNK_KEYS:
+        return bool(L.b200slu_relattn_supported(Tq, Tk, dk, RELPOS[mode]))
+    if causal or (RELPOS[mode] and Tq != Tk) or -(-Tk // CHUNK_KEYS) > 16:
+        return False
+    if os.environ.get("B200SLU_ATTN_CHUNKS", "1") == "0":  # A/B measurements against the unfused chain
+        return False
+    return bool(L.b200slu_relattn_chunk_supported(Tq, CHUNK_KEYS, dk, RELPOS[mode]))
+
+
+def _key_chunks(Tk: int):
+    return [(o, min(CHUNK_KEYS, Tk - o)) for o in range(0, Tk, CHUNK_KEYS)]
 
 
 def relattn_fwd(qu, qv, k, v, pos, key_lens, B: int, Tq: int, Tk: int, H: int, mode: str, causal: bool, scale: float,
                 drop: Drop = None, want_pd: bool = True):
     """One kernel for attention.py:281-308 / :98-114.  qu, qv [B*Tq, H*64] (qv, pos only for mode "latest"), k, v
-    [B*Tk, H*64] (column slices of wider buffers are fine) -> (p, p_drop) bf16 [H,B,Tq,round8(Tk)], ctx bf16 [B*Tq, H*64]."""
+    [B*Tk, H*64] (column slices of wider buffers are fine) -> (p, p_drop) bf16 [H,B,Tq,round8(Tk)], ctx bf16 [B*Tq, H*64].
+    More than 192 keys: one launch per key chunk + the combine pass (p_drop is not produced then)."""
     d = k.shape[1]
     ld = round8(Tk)
+    L = _lib.lib()
     p = torch.empty(H, B, Tq, ld, device=k.device, dtype=torch.bfloat16)
     dp, seed, site = _drop(drop)
-    pd = (torch.empty_like(p) if want_pd else None) if dp > 0.0 else p  # the fused backward regenerates dropout(p) from p
     ctx = torch.empty(B * Tq, d, device=k.device, dtype=torch.bfloat16)
     assert qu.stride(0) == (qv.stride(0) if qv is not None else qu.stride(0)) and k.stride(0) == v.stride(0)
-    check(_lib.lib().b200slu_relattn_fwd(ptr(qu), ptr(qv), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(pos),
-                                         pos.stride(0) if pos is not None else 0, ptr(key_lens), B, H, Tq, Tk, RELPOS[mode],
-                                         int(causal), scale, ptr(p), ptr(pd), ld, ptr(ctx), ctx.stride(0), dp, seed, site,
-                                         stream_ptr()), "relattn_fwd")
-    return p, pd, ctx
+    ldpos = pos.stride(0) if pos is not None else 0
+    if Tk <= CHUNK_KEYS:
+        pd = (torch.empty_like(p) if want_pd else None) if dp > 0.0 else p  # the fused backward regenerates dropout(p) from p
+        check(L.b200slu_relattn_fwd(ptr(qu), ptr(qv), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(pos), ldpos, ptr(key_lens), B,
+                                    H, Tq, Tk, RELPOS[mode], int(causal), scale, ptr(p), ptr(pd), ld, ptr(ctx), ctx.stride(0), dp,
+                                    seed, site, stream_ptr()), "relattn_fwd")
+        return p, pd, ctx
+    assert not causal and not (want_pd and dp > 0.0), "key chunks: no causal mask, no stored dropout(p)"
+    chunks = _key_chunks(Tk)
+    ctxc = torch.empty(len(chunks), B * Tq, d, device=k.device, dtype=torch.bfloat16)
+    lse = torch.empty(len(chunks), H * B * Tq, device=k.device, dtype=torch.float32)
+    if ld > Tk:
+        p[..., Tk:].zero_()
+    for c, (off, n) in enumerate(chunks):
+        check(L.b200slu_relattn_fwd_chunk(ptr(qu), ptr(qv), qu.stride(0), ptr(k[off:]), ptr(v[off:]), k.stride(0), ptr(pos), ldpos,
+                                          ptr(key_lens), B, H, Tq, n, RELPOS[mode], 0, scale, ptr(p[..., off:]), ld, ptr(ctxc[c]),
+                                          d, dp, seed, site, off, Tk, ptr(lse[c]), stream_ptr()), "relattn_fwd_chunk")
+    check(L.b200slu_relattn_combine(ptr(p), ld, Tk, CHUNK_KEYS, len(chunks), ptr(lse), ptr(ctxc), B * Tq * d, d, ptr(ctx),
+                                    ctx.stride(0), B, H, Tq, stream_ptr()), "relattn_combine")
+    return p, (None if dp > 0.0 else p), ctx
 
 
 def relattn_bwd_supported(Tq: int, Tk: int, dk: int, mode: str) -> bool:
-    return bool(_lib.lib().b200slu_relattn_bwd_supported(Tq, Tk, dk, RELPOS[mode]))
+    if Tk <= CHUNK_KEYS:
+        return bool(_lib.lib().b200slu_relattn_bwd_supported(Tq, Tk, dk, RELPOS[mode]))
+    return relattn_supported(Tq, Tk, dk, mode)
 
 
 def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: str, scale: float, dq, dk, dv,
@@ -290,19 +324,38 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: 
     :240-263).  dctx, qu, ctx [B*Tq, H*64], k, v [B*Tk, H*64], p bf16 [H,B,Tq,round8(Tk)] (as saved by the forward); writes
     dq [B*Tq, H*64], dk, dv [B*Tk, H*64] (views with their own row strides are fine).  Mode "latest": qv, pos (projected
     positions [2T-1, H*64]) in, dqv (row stride of dq) out, dpos (f32 [2T-1, H*64]) ACCUMULATED.  want_dac: also return dS
-    (bf16, shifted layout [H,B,Tq,round8(Tk)])."""
+    (bf16, shifted layout [H,B,Tq,round8(Tk)]).  More than 192 keys: one launch per key chunk, dq / dqv summed over them."""
     ld = p.shape[-1]
-    dac = torch.empty_like(p) if want_dac else None
+    L = _lib.lib()
     dp, seed, site = _drop(drop)
     assert k.stride(0) == v.stride(0) and dk.stride(0) == dv.stride(0)
-    if RELPOS[mode]:
+    rel = RELPOS[mode]
+    if rel:
         assert qv.stride(0) == qu.stride(0) and dqv.stride(0) == dq.stride(0) and dpos.dtype == torch.float32
-    check(_lib.lib().b200slu_relattn_bwd(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
-                                         ptr(ctx), ctx.stride(0), B, H, Tq, Tk, RELPOS[mode], scale, ptr(dq), dq.stride(0),
-                                         ptr(dk), ptr(dv), dk.stride(0), ptr(dac), dp, seed, site, ptr(qv), ptr(pos),
-                                         pos.stride(0) if pos is not None else 0, ptr(dqv), ptr(dpos),
-                                         dpos.stride(0) if dpos is not None else 0, stream_ptr()), "relattn_bwd")
-    return dac
+    ldpos = pos.stride(0) if pos is not None else 0
+    lddpos = dpos.stride(0) if dpos is not None else 0
+    if Tk <= CHUNK_KEYS:
+        dac = torch.empty_like(p) if want_dac else None
+        check(L.b200slu_relattn_bwd(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
+                                    ptr(ctx), ctx.stride(0), B, H, Tq, Tk, rel, scale, ptr(dq), dq.stride(0), ptr(dk), ptr(dv),
+                                    dk.stride(0), ptr(dac), dp, seed, site, ptr(qv), ptr(pos), ldpos, ptr(dqv), ptr(dpos), lddpos,
+                                    stream_ptr()), "relattn_bwd")
+        return dac
+    assert not want_dac
+    chunks = _key_chunks(Tk)
+    d = H * 64
+    dqc = torch.empty(2 if rel else 1, len(chunks), B * Tq, d, device=k.device, dtype=torch.bfloat16)
+    for c, (off, n) in enumerate(chunks):
+        check(L.b200slu_relattn_bwd_chunk(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k[off:]), ptr(v[off:]), k.stride(0),
+                                          ptr(p[..., off:]), ld, ptr(ctx), ctx.stride(0), B, H, Tq, n, rel, scale, ptr(dqc[0, c]), d,
+                                          ptr(dk[off:]), ptr(dv[off:]), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos,
+                                          ptr(dqc[1, c]) if rel else None, ptr(dpos), lddpos, off, Tk, stream_ptr()),
+              "relattn_bwd_chunk")
+    check(L.b200slu_sum_chunks_bf16(ptr(dqc[0]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dq), dq.stride(0), stream_ptr()), "sum_chunks")
+    if rel:
+        check(L.b200slu_sum_chunks_bf16(ptr(dqc[1]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dqv), dqv.stride(0), stream_ptr()),
+              "sum_chunks")
+    return None
 
 
 def rel_unshift(dac, T: int, mode: str, ld_bd: int):

@@ -437,7 +437,7 @@ def _mha_fwd(xq16, kv_src16, q_w: str, kv_w: str, P, W, a: str, klens, B, Tq, Tk
     da = ctx.drop(p_att, a + ".att")
     scale = 1.0 / math.sqrt(d // H)
     fb = False
-    if K.relattn_supported(Tq, Tk, d // H, "none"):
+    if K.relattn_supported(Tq, Tk, d // H, "none", causal):
         fb = ctx.training and K.relattn_bwd_supported(Tq, Tk, d // H, "none")
         pr, pd, c = K.relattn_fwd(q, None, k, v, None, klens, B, Tq, Tk, H, "none", causal, scale, drop=da, want_pd=not fb)
     else:

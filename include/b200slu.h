@@ -199,6 +199,33 @@ int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long
                         int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk, void* dv, long long lddkv,
                         void* d_ac, float drop_p, unsigned long long seed, unsigned int site, const void* q_v, const void* pos,
                         long long ldpos, void* dq_v, float* dpos_accum, long long lddpos, void* stream);
+/* Any number of keys: the key axis is cut into chunks of <= 192 keys (multiples of 16), one launch of the kernels above per
+ * chunk, and a combine pass turns the per-chunk softmaxes into the softmax over all keys (attention.py:78-95 over the
+ * whole row).  Chunk launch: k, v, p (and dk, dv) point at key / column key_off of tensors with kv_rows keys per utterance;
+ * key_off also shifts the rel-pos window (rel_shift source column = T - 1 - i + key_off + j), the valid length and the
+ * dropout counter, so every element sees the decisions of the single-launch form.  Forward: p's chunk columns receive the
+ * softmax over the chunk, ctx_chunk the chunk's context, lse2 (fp32 [H*B*Tq]) log2 of the chunk's partition sum (-inf when
+ * no key of the chunk is valid).  b200slu_relattn_combine: alpha_c = 2^(lse2_c - log2 sum_c 2^lse2_c); p[.., chunk c] *=
+ * alpha_c in place and ctx = sum_c alpha_c ctx_c (ctx_chunks [nchunk] slabs chunk_stride elements apart, lse2 [nchunk,
+ * H*B*Tq]).  Backward: p = the combined probabilities, ctx = the combined context (for delta = <dO, O>); dk, dv of the
+ * chunk's keys are final, dq_u / dq_v are this chunk's contribution (sum the slabs with b200slu_sum_chunks_bf16),
+ * dpos_accum accumulates over the chunks like over the utterances. */
+int b200slu_relattn_chunk_supported(int Tq, int Tk_chunk, int dk, int relpos_mode);
+int b200slu_relattn_fwd_chunk(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
+                              const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk_chunk,
+                              int relpos_mode, int causal, float scale, void* p, long long ld_p, void* ctx_chunk, long long ldctx,
+                              float drop_p, unsigned long long seed, unsigned int site, int key_off, int kv_rows, float* lse2,
+                              void* stream);
+int b200slu_relattn_combine(void* p, long long ld_p, int Tk, int chunk_keys, int nchunk, const float* lse2, const void* ctx_chunks,
+                            long long chunk_stride, long long ldctx, void* ctx, long long ldout, int B, int H, int Tq, void* stream);
+int b200slu_relattn_bwd_chunk(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
+                              long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H, int Tq,
+                              int Tk_chunk, int relpos_mode, float scale, void* dq_u_chunk, long long lddq, void* dk, void* dv,
+                              long long lddkv, float drop_p, unsigned long long seed, unsigned int site, const void* q_v,
+                              const void* pos, long long ldpos, void* dq_v_chunk, float* dpos_accum, long long lddpos, int key_off,
+                              int kv_rows, void* stream);
+int b200slu_sum_chunks_bf16(const void* src, long long chunk_stride, long long ld_src, int nchunk, long long rows, int cols,
+                            void* dst, long long ld_dst, void* stream);
 /* d(matrix_bd) [H,B,T,ld_bd] (un-shifted) from d(scores) [H,B,T,ld_p] (shifted): the scatter of rel_shift's backward
  * (attention.py:240-263), latest mode. */
 int b200slu_rel_unshift(const void* d_scores, long long ld_p, int H, int B, int T, int relpos_mode, void* d_bd, long long ld_bd,

@@ -252,8 +252,10 @@ def softmax_bwd(dpd, p, Tk, mode, scale, ld_bd=0, drop=None):
     return dac, dbd
 
 
-def relattn_supported(Tq, Tk, dk, mode):
-    return dk == 64 and Tk <= 192 and ((mode == "latest" and Tq == Tk) or mode in (None, "none"))
+def relattn_supported(Tq, Tk, dk, mode, causal=False):
+    if dk != 64 or not ((mode == "latest" and Tq == Tk) or mode in (None, "none")):
+        return False
+    return Tk <= 192 or (not causal and Tk <= 16 * 192)   # longer key axes: key chunks + combine, same arithmetic
 
 
 def relattn_fwd(qu, qv, k, v, pos, key_lens, B, Tq, Tk, H, mode, causal, scale, drop=None, want_pd=True):

@@ -229,6 +229,56 @@ def test_fused_attention_fwd(mode, causal, Tq, Tk):
     close(ctx2, K().attn_f2(upd, args_c[3], B, Tq, Tk, H), 2e-2, "fused ctx (dropout) vs unfused")
 
 
+@pytest.mark.parametrize("drop", [None, (0.1, 99, 5)])
+@pytest.mark.parametrize("mode,Tq,Tk", [("latest", 300, 300), ("latest", 193, 193), ("latest", 468, 468), ("none", 37, 430),
+                                        ("none", 130, 385), ("latest", 384, 384)])
+def test_fused_attention_key_chunks(mode, Tq, Tk, drop):
+    """More than 192 keys: one launch of the fused forward / backward per 192-key chunk + the combine pass, against the
+    statement of the unfused chain over the whole key axis (same dropout decisions: the chunk offset enters the counter)."""
+    H, B, dk = 2, 3, 64
+    d = H * dk
+    rel = mode == "latest"
+    assert K().relattn_supported(Tq, Tk, dk, mode) and K().relattn_bwd_supported(Tq, Tk, dk, mode)
+    qkv = (rnd(B * Tq, 3 * d, seed=1) * 0.7).to(BF)
+    kv = (rnd(B * Tk, 2 * d, seed=2) * 0.7).to(BF)
+    qv = (rnd(B * Tq, d, seed=3) * 0.7).to(BF)
+    Pn = 2 * Tq - 1
+    pos = (rnd(Pn, d, seed=4) * 0.7).to(BF) if rel else None
+    lens = torch.tensor([Tk, max(1, Tk - 200), 150], dtype=torch.int32)   # whole chunks masked for the shorter utterances
+    dctx = rnd(B * Tq, d, seed=5).to(BF)
+    qkv_c, kv_c = qkv.cuda(), kv.cuda()
+    qu_c = qkv_c[:, :d].contiguous() if rel else qkv_c[:, :d]
+    p, _, ctx = K().relattn_fwd(qu_c, qv.cuda() if rel else None, kv_c[:, :d], kv_c[:, d:], pos.cuda() if rel else None, lens.cuda(),
+                                B, Tq, Tk, H, mode, False, 0.125, drop=drop, want_pd=False)
+    wp, wpd, wctx = E.relattn_fwd(qkv[:, :d], qv if rel else None, kv[:, :d], kv[:, d:], pos, lens, B, Tq, Tk, H, mode, False, 0.125,
+                                  drop=drop)
+    close(p[..., :Tk], wp[..., :Tk], 1.5e-2, "p over key chunks")
+    close(ctx, wctx, 2e-2, "ctx over key chunks")
+    assert torch.isfinite(p.float()).all() and (p.shape[-1] == Tk or p.float()[..., Tk:].abs().max().item() == 0)
+    for bi in range(B):
+        if int(lens[bi]) < Tk:
+            assert p[:, bi, :, int(lens[bi]):Tk].abs().max().item() == 0
+    dq = torch.full((B * Tq, 3 * d), 7.0, device="cuda", dtype=BF)
+    dkv = torch.full((B * Tk, 2 * d), 7.0, device="cuda", dtype=BF)
+    dqv = torch.full((B * Tq, 3 * d), 7.0, device="cuda", dtype=BF) if rel else None
+    dpos = torch.ones(Pn, d, device="cuda") if rel else None
+    K().relattn_bwd(dctx.cuda(), qu_c, kv_c[:, :d], kv_c[:, d:], p, ctx, B, Tq, Tk, H, mode, 0.125, dq[:, d:2 * d], dkv[:, :d], dkv[:, d:],
+                    drop=drop, qv=qv.cuda() if rel else None, pos=pos.cuda() if rel else None, dqv=dqv[:, d:2 * d] if rel else None,
+                    dpos=dpos)
+    torch.cuda.synchronize()
+    wdq, wdk, wdv = torch.zeros(B * Tq, d), torch.zeros(B * Tk, d), torch.zeros(B * Tk, d)
+    wdqv, wdpos = (torch.zeros(B * Tq, d), torch.ones(Pn, d)) if rel else (None, None)
+    E.relattn_bwd(dctx, qkv[:, :d], kv[:, :d], kv[:, d:], p.float().cpu(), ctx.float().cpu(), B, Tq, Tk, H, mode, 0.125, wdq, wdk, wdv,
+                  drop=drop, qv=qv if rel else None, pos=pos, dqv=wdqv, dpos=wdpos)
+    close(dq[:, d:2 * d], wdq, 2e-2, "dq_u")
+    close(dkv[:, :d], wdk, 2e-2, "dk")
+    close(dkv[:, d:], wdv, 2e-2, "dv")
+    assert (dq[:, :d] == 7.0).all() and (dq[:, 2 * d:] == 7.0).all()
+    if rel:
+        close(dqv[:, d:2 * d], wdqv, 2e-2, "dq_v")
+        close(dpos, wdpos, 2e-2, "d(projected positions)")
+
+
 @pytest.mark.parametrize("drop", [None, (0.1, 4321, 9)])
 @pytest.mark.parametrize("mode,Tq,Tk", [("latest", 124, 124), ("latest", 155, 155), ("latest", 192, 192), ("latest", 129, 129),
                                         ("latest", 33, 33), ("latest", 64, 64), ("none", 21, 21), ("none", 21, 155),

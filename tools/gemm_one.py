@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from espnet_slurp_b200 import ops
 
 torch.manual_seed(0)
-M, d, F = 9920, 512, 2048
+M, d, F = int(os.environ.get("GEMM_M", 19840)), 512, 2048
 x = torch.randn(M, d, device="cuda").bfloat16()
 h = torch.randn(M, F, device="cuda").bfloat16()
 w1 = (torch.randn(F, d, device="cuda") * 0.05).bfloat16()
