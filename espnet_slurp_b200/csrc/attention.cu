@@ -586,9 +586,12 @@ struct AttnBwdArgs {
   B2Dropout drop;
   long long* dbg;  // tuning only (B200SLU_ATTN_BWD_DEBUG): CTA 0's cycles per phase, summed over its query tiles
   int dbgflags;    // tuning only (B200SLU_ATTN_BWD_FLAGS): 1 = no d(pos) reduce, 2 = no load prefetch
-  // key chunk of a longer key axis (b200slu_relattn_bwd_chunk): keys [key_off, key_off + Tk) of kv_rows per utterance;
-  // k, v, dk, dv and p already point at key / column key_off.  key_off shifts the rel-pos window and the dropout counter.
-  int key_off, kv_rows;
+  // Key chunks of a longer key axis (b200slu_relattn_bwd_chunks): work unit = (chunk, utterance, head); chunk c covers keys
+  // [c * chunk_keys, +min(chunk_keys, Tk - c * chunk_keys)) of the kv_rows keys per utterance (Tk = kv_rows then) and
+  // writes its dq_u / dq_v contribution to slab c (dq_slab elements apart).  The key offset shifts the K / V / p tile
+  // coordinates, the rel-pos window and the dropout counter.  One chunk: chunk_keys = Tk, the plain kernel.
+  int nchunk, chunk_keys, kv_rows;
+  long long dq_slab;
 };
 
 template <bool REL>
@@ -658,16 +661,17 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
   // the skewed tile on V).  Issued one tile AHEAD, as soon as the last MMA that reads those regions has completed, so the
   // load latency hides behind the previous tile's read-out.
   auto issue_loads = [&](int unit_, int qt_) {
-    const int h_ = unit_ % a.H, b_ = unit_ / a.H, i0_ = qt_ * QT;
+    const int bh_ = unit_ % (a.B * a.H), koff_ = (unit_ / (a.B * a.H)) * a.chunk_keys;
+    const int h_ = bh_ % a.H, b_ = bh_ / a.H, i0_ = qt_ * QT;
     mbar_expect_tx(bar_kv, (uint32_t)(2 * TKP * 128));
-    tma_load_3d(s_k, &map_k, bar_kv, h_ * DK, 0, b_);
-    tma_load_3d(s_v, &map_v, bar_kv, h_ * DK, 0, b_);
+    tma_load_3d(s_k, &map_k, bar_kv, h_ * DK, koff_, b_);
+    tma_load_3d(s_v, &map_v, bar_kv, h_ * DK, koff_, b_);
     mbar_expect_tx(bar_q, (uint32_t)(2 * BLK + nblk * BLK + (REL ? a.WIN * 128 : 0)));
     tma_load_3d(s_do, &map_do, bar_q, h_ * DK, i0_, b_);
     tma_load_3d(s_qu, &map_qu, bar_q, h_ * DK, i0_, b_);
-    for (int kb = 0; kb < nblk; ++kb) tma_load_3d(s_pd + kb * BLK, &map_p, bar_q, kb * 64, i0_, h_ * a.B + b_);
+    for (int kb = 0; kb < nblk; ++kb) tma_load_3d(s_pd + kb * BLK, &map_p, bar_q, koff_ + kb * 64, i0_, h_ * a.B + b_);
     if (REL) {
-      const int c0_ = b2_rel_shift_src(i0_ + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + a.key_off;
+      const int c0_ = b2_rel_shift_src(i0_ + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + koff_;
       tma_load_3d(s_pos, &map_pos, bar_q, h_ * DK, c0_, 0);
       tma_load_3d(s_pos + (a.WIN / 2) * 128, &map_pos, bar_q, h_ * DK, c0_ + a.WIN / 2, 0);
     }
@@ -681,7 +685,9 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
   const uint32_t s_stg = sbase + a.off_stg;
 
   for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-    const int h = unit % a.H, b = unit / a.H;
+    const int bh = unit % (a.B * a.H), chunk = unit / (a.B * a.H);
+    const int h = bh % a.H, b = bh / a.H;
+    const int key_off = chunk * a.chunk_keys, tk_c = min(a.chunk_keys, a.Tk - key_off);  // this unit's keys
     for (int qt = 0; qt < nqt; ++qt) {
       const int i0 = qt * QT, i = i0 + r;
       const bool row_ok = i < a.Tq;
@@ -689,7 +695,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
       const uint32_t par = n_q & 1u;
       if ((a.dbgflags & 2) && tid == 0 && !(unit == (int)blockIdx.x && qt == 0)) issue_loads(unit, qt);
       // first position row of the window this tile reaches (the forward's window); may be negative: zero-filled
-      const int c0 = REL ? b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + a.key_off : 0;
+      const int c0 = REL ? b2_rel_shift_src(i0 + QT - 1, 0, a.Tq, B200SLU_RELPOS_LATEST).col + key_off : 0;
       // this thread's half (32 columns) of its row of the forward output, for delta
       uint4 cx[4];
       if (row_ok) {
@@ -775,7 +781,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
 #pragma unroll
               for (int g = 0; g < 2; ++g) {
                 float m8[8];
-                dropout_mul8(dk, (unsigned long long)(rg * a.ld_p + a.key_off + j0 + g * 8) >> 3, dk.inv, m8);
+                dropout_mul8(dk, (unsigned long long)(rg * a.ld_p + key_off + j0 + g * 8) >> 3, dk.inv, m8);
 #pragma unroll
                 for (int e = 0; e < 8; ++e) mul[g * 8 + e] = m8[e];
               }
@@ -844,8 +850,8 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
           tmem_ld32(tlane + BWD_DK_COL + m * DK + hs * 32, ok_);
           tmem_ld32(tlane + BWD_DV_COL + m * DK + hs * 32, ov_);
           tmem_ld_wait();
-          if (j < a.Tk) {
-            const long long row = ((long long)b * a.kv_rows + j) * a.lddkv + h * DK + hs * 32;
+          if (j < tk_c) {
+            const long long row = ((long long)b * a.kv_rows + key_off + j) * a.lddkv + h * DK + hs * 32;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               float v[8];
@@ -870,7 +876,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
         tmem_ld32(tlane + hs * 32, o);
         tmem_ld_wait();
         if (row_ok) {
-          bf16* dst = a.dq + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
+          bf16* dst = a.dq + chunk * a.dq_slab + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             float v[8];
@@ -955,7 +961,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
           tmem_ld32(tlane + BWD_DQV_COL + hs * 32, o);
           tmem_ld_wait();
           if (row_ok) {
-            bf16* dst = a.dqv + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
+            bf16* dst = a.dqv + chunk * a.dq_slab + ((long long)b * a.Tq + i) * a.lddq + h * DK + hs * 32;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               float v[8];
@@ -970,7 +976,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
         // instruction covers four whole 128-byte lines instead of 32 scattered 16-byte pieces (row-per-lane
         // red.global.add.v4 measured 6200 cycles per tile).  Only a __syncwarp between the two halves.
         const int rows_here = min(QT, a.Tq - i0);
-        const int wlo = QT - rows_here, whi = QT - 1 + a.Tk;  // window rows [wlo, whi) can be non-zero
+        const int wlo = QT - rows_here, whi = QT - 1 + tk_c;  // window rows [wlo, whi) can be non-zero
         const uint32_t patch = s_stg + (uint32_t)warp * 4096u;
         for (int m = 0; m < nmt; ++m) {
           const int w0 = m * QT + q * 32;  // first window row of this warp's slice
@@ -1208,13 +1214,15 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
                             int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
                             void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
                             unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
-                            float* dpos_accum, long long lddpos, int key_off, int kv_rows, void* stream) {
+                            float* dpos_accum, long long lddpos, int chunk_keys, long long dq_slab, void* stream) {
+  // Tk = all keys of an utterance; chunk_keys = keys per work unit (Tk itself for the one-chunk form)
   B2_CHECK_ARG(B > 0 && H > 0, "relattn_bwd: empty problem");
-  B2_CHECK_ARG(b200slu_relattn_chunk_supported(Tq, Tk, DK, relpos_mode) && key_off >= 0 && key_off % 16 == 0 &&
-                   kv_rows >= key_off + Tk && ld_p >= key_off + Tk && (key_off == 0 || d_ac == nullptr),
-               "relattn_bwd: supports d_k = 64, <= %d keys per launch, rel-pos mode latest or none, key_off %% 16 == 0 (got Tq=%d "
-               "Tk=%d mode=%d key_off=%d kv_rows=%d)", MAX_TK, Tq, Tk, relpos_mode, key_off, kv_rows);
-  B2_CHECK_ARG(relpos_mode != B200SLU_RELPOS_LATEST || kv_rows == Tq, "relattn_bwd: rel-pos mode attends over the queries' own axis");
+  const int nchunk = chunk_keys > 0 ? (Tk + chunk_keys - 1) / chunk_keys : 0;
+  B2_CHECK_ARG(chunk_keys >= 1 && b200slu_relattn_chunk_supported(Tq, chunk_keys, DK, relpos_mode) &&
+                   (nchunk == 1 || (chunk_keys % 64 == 0 && d_ac == nullptr && dq_slab % 8 == 0)) && ld_p >= Tk,
+               "relattn_bwd: supports d_k = 64, <= %d keys per chunk (whole 64-key blocks when there are several), rel-pos mode latest "
+               "or none (got Tq=%d Tk=%d mode=%d chunk_keys=%d)", MAX_TK, Tq, Tk, relpos_mode, chunk_keys);
+  B2_CHECK_ARG(relpos_mode != B200SLU_RELPOS_LATEST || Tk == Tq, "relattn_bwd: rel-pos mode attends over the queries' own axis");
   const bool rel = relpos_mode == B200SLU_RELPOS_LATEST;
   B2_CHECK_ARG(d_ctx && q_u && k && v && p && ctx && dq_u && dk_out && dv_out, "relattn_bwd: null operand");
   B2_CHECK_ARG(!rel || (q_v && pos && dq_v && dpos_accum), "relattn_bwd: rel-pos mode needs q_v, pos, dq_v and dpos_accum");
@@ -1230,14 +1238,14 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
   cudaStream_t st = (cudaStream_t)stream;
   AttnBwdArgs a{};
   a.B = B; a.H = H; a.Tq = Tq; a.Tk = Tk;
-  a.TKP = (Tk + 15) / 16 * 16;
+  a.TKP = (chunk_keys + 15) / 16 * 16;
   a.WIN = a.TKP + QT;
   a.scale = scale;
   a.ctx = (const bf16*)ctx; a.ldctx = ldctx;
   a.dq = (bf16*)dq_u; a.dk = (bf16*)dk_out; a.dv = (bf16*)dv_out; a.dac = (bf16*)d_ac;
   a.lddq = lddq; a.lddkv = lddkv; a.ld_p = ld_p;
   a.dqv = (bf16*)dq_v; a.dpos = dpos_accum; a.lddpos = lddpos;
-  a.key_off = key_off; a.kv_rows = kv_rows;
+  a.nchunk = nchunk; a.chunk_keys = chunk_keys; a.kv_rows = Tk; a.dq_slab = dq_slab;
   // [pd tile | dO | Q_u | V] [dS tile] [K, later Q_v] [position window].  The first group is dead once dQ_u / dK / dV are
   // issued: the skewed d(bd) tile is built over it (dS, its source, stays).  An M = 128 MN-major read over the last key /
   // window tile may run past the blocks that exist into the next region: never faulting (bounded below), never stored.
@@ -1269,9 +1277,9 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
   const int d = H * DK;
   B2_TRY(make_map3(&mdo, d_ctx, d, Tq, lddo, B, (long long)Tq * lddo, QT));
   B2_TRY(make_map3(&mqu, q_u, d, Tq, ldq, B, (long long)Tq * ldq, QT));
-  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)kv_rows * ldkv, a.TKP));
-  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)kv_rows * ldkv, a.TKP));
-  B2_TRY(make_map3(&mp, p, ld_p - key_off, Tq, ld_p, (long long)H * B, (long long)Tq * ld_p, QT));
+  B2_TRY(make_map3(&mk, k, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  B2_TRY(make_map3(&mv, v, d, Tk, ldkv, B, (long long)Tk * ldkv, a.TKP));
+  B2_TRY(make_map3(&mp, p, ld_p, Tq, ld_p, (long long)H * B, (long long)Tq * ld_p, QT));
   if (rel) {
     B2_TRY(make_map3(&mqv, q_v, d, Tq, ldq, B, (long long)Tq * ldq, QT));
     B2_TRY(make_map3(&mpos, pos, d, 2 * Tq - 1, ldpos, 1, 0, a.WIN / 2));
@@ -1285,10 +1293,10 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
     B2_CUDA(cudaFuncSetAttribute(relattn_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     b2_device_mark(configured);
   }
-  const int units = B * H, sms = b2_num_sms();
-  B2_SCOPE(FAM_ATTN, st, (double)units * (8.0 * Tq * Tk * DK + (rel ? 4.0 * Tq * (2.0 * Tq - 1) * DK : 0.0)),
-           (double)units * (2.0 * DK * (3.0 * Tq + 2.0 * Tk) + 2.0 * Tq * Tk + 2.0 * DK * (Tq + 2.0 * Tk) +
-                            (rel ? 2.0 * DK * 2.0 * Tq : 0.0) + (d_ac ? 2.0 * Tq * Tk : 0.0)));
+  const int units = B * H * nchunk, sms = b2_num_sms();
+  B2_SCOPE(FAM_ATTN, st, (double)B * H * (8.0 * Tq * Tk * DK + (rel ? 4.0 * Tq * (2.0 * Tq - 1) * DK : 0.0)),
+           (double)B * H * (nchunk * 2.0 * DK * 3.0 * Tq + 2.0 * DK * 2.0 * Tk + 2.0 * Tq * Tk + 2.0 * DK * (nchunk * Tq + 2.0 * Tk) +
+                            (rel ? 2.0 * DK * 2.0 * Tq * nchunk : 0.0) + (d_ac ? 2.0 * Tq * Tk : 0.0)));
   const dim3 grid((unsigned)(units < sms ? units : sms));
   static const bool dbg = getenv("B200SLU_ATTN_BWD_DEBUG") != nullptr && atoi(getenv("B200SLU_ATTN_BWD_DEBUG")) != 0;
   if (dbg) {
@@ -1321,19 +1329,19 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
                "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
                Tq, Tk, relpos_mode);
   return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u, lddq, dk_out,
-                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, 0, Tk, stream);
+                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, Tk, 0, stream);
 }
 
-extern "C" int b200slu_relattn_bwd_chunk(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k,
-                                         const void* v, long long ldkv, const void* p, long long ld_p, const void* ctx,
-                                         long long ldctx, int B, int H, int Tq, int Tk_chunk, int relpos_mode, float scale,
-                                         void* dq_u_chunk, long long lddq, void* dk_out, void* dv_out, long long lddkv, float drop_p,
-                                         unsigned long long seed, unsigned int site, const void* q_v, const void* pos,
-                                         long long ldpos, void* dq_v_chunk, float* dpos_accum, long long lddpos, int key_off,
-                                         int kv_rows, void* stream) {
-  return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk_chunk, relpos_mode, scale, dq_u_chunk,
-                          lddq, dk_out, dv_out, lddkv, nullptr, drop_p, seed, site, q_v, pos, ldpos, dq_v_chunk, dpos_accum, lddpos,
-                          key_off, kv_rows, stream);
+extern "C" int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k,
+                                          const void* v, long long ldkv, const void* p, long long ld_p, const void* ctx,
+                                          long long ldctx, int B, int H, int Tq, int Tk, int chunk_keys, int relpos_mode,
+                                          float scale, void* dq_u_slabs, long long lddq, long long dq_slab, void* dk_out,
+                                          void* dv_out, long long lddkv, float drop_p, unsigned long long seed, unsigned int site,
+                                          const void* q_v, const void* pos, long long ldpos, void* dq_v_slabs, float* dpos_accum,
+                                          long long lddpos, void* stream) {
+  return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u_slabs, lddq,
+                          dk_out, dv_out, lddkv, nullptr, drop_p, seed, site, q_v, pos, ldpos, dq_v_slabs, dpos_accum, lddpos,
+                          chunk_keys, dq_slab, stream);
 }
 
 // ----------------------------------------------------------------------------- key chunks -> one softmax

@@ -345,12 +345,10 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: 
     chunks = _key_chunks(Tk)
     d = H * 64
     dqc = torch.empty(2 if rel else 1, len(chunks), B * Tq, d, device=k.device, dtype=torch.bfloat16)
-    for c, (off, n) in enumerate(chunks):
-        check(L.b200slu_relattn_bwd_chunk(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k[off:]), ptr(v[off:]), k.stride(0),
-                                          ptr(p[..., off:]), ld, ptr(ctx), ctx.stride(0), B, H, Tq, n, rel, scale, ptr(dqc[0, c]), d,
-                                          ptr(dk[off:]), ptr(dv[off:]), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos,
-                                          ptr(dqc[1, c]) if rel else None, ptr(dpos), lddpos, off, Tk, stream_ptr()),
-              "relattn_bwd_chunk")
+    check(L.b200slu_relattn_bwd_chunks(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
+                                       ptr(ctx), ctx.stride(0), B, H, Tq, Tk, CHUNK_KEYS, rel, scale, ptr(dqc[0]), d, B * Tq * d,
+                                       ptr(dk), ptr(dv), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos,
+                                       ptr(dqc[1]) if rel else None, ptr(dpos), lddpos, stream_ptr()), "relattn_bwd_chunks")
     check(L.b200slu_sum_chunks_bf16(ptr(dqc[0]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dq), dq.stride(0), stream_ptr()), "sum_chunks")
     if rel:
         check(L.b200slu_sum_chunks_bf16(ptr(dqc[1]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dqv), dqv.stride(0), stream_ptr()),

@@ -207,9 +207,10 @@ int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long
  * softmax over the chunk, ctx_chunk the chunk's context, lse2 (fp32 [H*B*Tq]) log2 of the chunk's partition sum (-inf when
  * no key of the chunk is valid).  b200slu_relattn_combine: alpha_c = 2^(lse2_c - log2 sum_c 2^lse2_c); p[.., chunk c] *=
  * alpha_c in place and ctx = sum_c alpha_c ctx_c (ctx_chunks [nchunk] slabs chunk_stride elements apart, lse2 [nchunk,
- * H*B*Tq]).  Backward: p = the combined probabilities, ctx = the combined context (for delta = <dO, O>); dk, dv of the
- * chunk's keys are final, dq_u / dq_v are this chunk's contribution (sum the slabs with b200slu_sum_chunks_bf16),
- * dpos_accum accumulates over the chunks like over the utterances. */
+ * H*B*Tq]).  Backward (b200slu_relattn_bwd_chunks: ONE launch, work unit = (chunk, utterance, head), chunk_keys a multiple
+ * of 64; k, v, p, dk, dv are the whole tensors): p = the combined probabilities, ctx = the combined context (for delta =
+ * <dO, O>); dk, dv are final, dq_u / dq_v come out as one slab per chunk, dq_slab elements apart (sum them with
+ * b200slu_sum_chunks_bf16); dpos_accum accumulates over the chunks like over the utterances. */
 int b200slu_relattn_chunk_supported(int Tq, int Tk_chunk, int dk, int relpos_mode);
 int b200slu_relattn_fwd_chunk(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
                               const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk_chunk,
@@ -218,12 +219,12 @@ int b200slu_relattn_fwd_chunk(const void* qu, const void* qv, long long ldq, con
                               void* stream);
 int b200slu_relattn_combine(void* p, long long ld_p, int Tk, int chunk_keys, int nchunk, const float* lse2, const void* ctx_chunks,
                             long long chunk_stride, long long ldctx, void* ctx, long long ldout, int B, int H, int Tq, void* stream);
-int b200slu_relattn_bwd_chunk(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
-                              long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H, int Tq,
-                              int Tk_chunk, int relpos_mode, float scale, void* dq_u_chunk, long long lddq, void* dk, void* dv,
-                              long long lddkv, float drop_p, unsigned long long seed, unsigned int site, const void* q_v,
-                              const void* pos, long long ldpos, void* dq_v_chunk, float* dpos_accum, long long lddpos, int key_off,
-                              int kv_rows, void* stream);
+int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k, const void* v,
+                               long long ldkv, const void* p, long long ld_p, const void* ctx, long long ldctx, int B, int H, int Tq,
+                               int Tk, int chunk_keys, int relpos_mode, float scale, void* dq_u_slabs, long long lddq,
+                               long long dq_slab, void* dk, void* dv, long long lddkv, float drop_p, unsigned long long seed,
+                               unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v_slabs,
+                               float* dpos_accum, long long lddpos, void* stream);
 int b200slu_sum_chunks_bf16(const void* src, long long chunk_stride, long long ld_src, int nchunk, long long rows, int cols,
                             void* dst, long long ld_dst, void* stream);
 /* d(matrix_bd) [H,B,T,ld_bd] (un-shifted) from d(scores) [H,B,T,ld_p] (shifted): the scatter of rel_shift's backward
