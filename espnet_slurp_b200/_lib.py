@@ -11,7 +11,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb200slu.so")
+# B200SLU_LIB: another build of the same library (A/B measurements of compile-time tuning choices only)
+LIB_PATH = os.environ.get("B200SLU_LIB") or os.path.join(HERE, "libb200slu.so")
 
 
 class Epilogue(C.Structure):

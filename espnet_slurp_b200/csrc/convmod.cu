@@ -25,12 +25,15 @@ constexpr int KMAX = 31;  // cnn_module_kernel upper bound (SLURP/LibriSpeech: 3
 template <int TT, bool BWD>
 __device__ __forceinline__ void stage_tiles(const bf16* __restrict__ pw1, const bf16* __restrict__ d_dw, int b, int T, int C,
                                             int t0, int c0, int K, float (*sg)[CC], float (*sd)[CC]) {
-  constexpr int U = ((TT + KMAX - 1) * (CC / 8) + 255) / 256;  // items per thread of a 256-thread block
+  constexpr int UT = ((TT + KMAX - 1) * (CC / 8) + 255) / 256;  // items per thread of a 256-thread block
+  constexpr int U = UT > 5 ? (UT + 1) / 2 : UT;                 // ... in two rounds when that is many registers in flight
   const int pad = (K - 1) / 2, nitems = (TT + K - 1) * (CC / 8);
+#pragma unroll 1
+  for (int base = 0; base < UT * 256; base += U * 256) {
   uint4 ra[U], rg[U], rd[U];
 #pragma unroll
   for (int u = 0; u < U; ++u) {
-    const int it = threadIdx.x + u * 256;
+    const int it = base + threadIdx.x + u * 256;
     const int f = it / (CC / 8), cg = it - f * (CC / 8);
     const int t = t0 - pad + f, c = c0 + cg * 8;
     ra[u] = rg[u] = rd[u] = make_uint4(0u, 0u, 0u, 0u);
@@ -43,7 +46,7 @@ __device__ __forceinline__ void stage_tiles(const bf16* __restrict__ pw1, const 
   }
 #pragma unroll
   for (int u = 0; u < U; ++u) {
-    const int it = threadIdx.x + u * 256;
+    const int it = base + threadIdx.x + u * 256;
     if (it < nitems) {
       const int f = it / (CC / 8), cg = it - f * (CC / 8);
       float a[8], gt[8], g[8];
@@ -67,75 +70,117 @@ __device__ __forceinline__ void stage_tiles(const bf16* __restrict__ pw1, const 
       }
     }
   }
+  }
 }
 
-// Each thread owns one channel and, per 32-frame sub-tile, FR = 8 consecutive output frames: the K + 7 staged inputs
-// it needs are read from shared memory once into a sliding register window (4.75 LDS per output instead of K),
-// weights stay in registers for the whole tile.
-constexpr int FR = 8;
+// Each thread owns a PAIR of neighbouring channels and, per sub-tile, FR consecutive output frames: the K + FR - 1 staged
+// inputs it needs are read from shared memory once (one 8-byte load per frame) into a sliding window, the taps of both
+// channels stay in registers as pairs and every multiply-add is a packed fma.rn.f32x2 (FFMA2: the FMA pipe's rate of
+// scalar code at half the issue slots -- tools/ffma2_rate.cu -- which is what these kernels ran out of: ncu had them at
+// IPC 2.5 with the FMA pipe 39 % busy).  Block = 32 channel pairs x 8 frame lanes.
+template <int TT>
+struct DwGeom {
+  static constexpr int FR = (TT % 64 == 0) ? 8 : 4;   // frames per thread and sub-tile
+  static constexpr int SUB = 8 * FR;                  // frames per sub-tile (8 frame lanes)
+  static_assert(TT % SUB == 0, "tile = whole sub-tiles");
+};
 
 template <int TT, int KT>
-__global__ void __launch_bounds__(256) glu_dw_fwd_kernel(const bf16* __restrict__ pw1, const float* __restrict__ w,
-                                                         const float* __restrict__ bias, int B, int T, int C, int Krt,
-                                                         bf16* __restrict__ out, float* __restrict__ sums) {
-  static_assert(TT % (4 * FR) == 0, "tile = whole sub-tiles of 4 frame lanes x FR frames");
-  __shared__ __align__(16) float sm[TT + KMAX - 1][CC];
-  __shared__ float red[2][4][CC];
+__global__ void __launch_bounds__(256, 2) glu_dw_fwd_kernel(const bf16* __restrict__ pw1, const float* __restrict__ w,
+                                                            const float* __restrict__ bias, int B, int T, int C, int Krt,
+                                                            bf16* __restrict__ out, float* __restrict__ sums) {
+  constexpr int FR = DwGeom<TT>::FR, SUB = DwGeom<TT>::SUB;
+  extern __shared__ __align__(16) float dyn_smem[];
+  float (*sm)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                           // glu halo tile [TT+KMAX-1][CC]
+  float (*red)[8][CC] = reinterpret_cast<float (*)[8][CC]>(dyn_smem + (TT + KMAX - 1) * CC);  // [2][8 frame lanes][CC]
   const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
-  const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;  // 4 frame lanes x FR frames
-  const int c = c0 + cl;
-  float wr[KMAX];
+  const int cp = threadIdx.x & 31, fr = threadIdx.x >> 5;  // channel pair, frame lane
+  const int c = c0 + 2 * cp;
+  const bool cok = c < C;  // C is even: the pair is in or out together
+  // The block's 64 x K taps are contiguous in w: fetched coalesced through shared memory (the halo tile's space).  A
+  // per-thread gather w[c * K + k] touches 32 cache lines per load instruction -- 16 k line requests per block, which took
+  // longer than the block's two tiles of arithmetic.
+  {
+    float* wt = dyn_smem;
+    const int nw = min(CC, C - c0) * K;
+    constexpr int WU = (CC * KMAX + 255) / 256;
+    float tmp[WU];
 #pragma unroll
-  for (int k = 0; k < KMAX; ++k) wr[k] = (c < C && k < K) ? w[c * K + k] : 0.f;
-  const float bs = c < C ? bias[c] : 0.f;
+    for (int u = 0; u < WU; ++u) {  // all loads in flight before the first store
+      const int it = threadIdx.x + u * 256;
+      tmp[u] = it < nw ? w[(long long)c0 * K + it] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < WU; ++u) {
+      const int it = threadIdx.x + u * 256;
+      if (it < nw) wt[it] = tmp[u];
+    }
+    __syncthreads();
+  }
+  float2 wr[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k)
+    wr[k] = (cok && k < K) ? make_float2(dyn_smem[(2 * cp) * K + k], dyn_smem[(2 * cp + 1) * K + k]) : make_float2(0.f, 0.f);
+  const float2 bs = cok ? make_float2(bias[c], bias[c + 1]) : make_float2(0.f, 0.f);
   const int ntt = (T + TT - 1) / TT;
-  float s1 = 0.f, s2 = 0.f;
+  float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
   // Each block walks its (utterance, time tile) units and keeps the BatchNorm partial sums in registers across them:
   // the atomics on `sums` are per block (grid.y per channel), not per tile -- same-address atomics retire serially.
   for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
-  const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
-  __syncthreads();  // previous tile fully consumed
-  stage_tiles<TT, false>(pw1, nullptr, b, T, C, t0, c0, K, sm, nullptr);
-  __syncthreads();
-  if (c < C) {
+    const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
+    __syncthreads();  // previous tile fully consumed
+    stage_tiles<TT, false>(pw1, nullptr, b, T, C, t0, c0, K, sm, nullptr);
+    __syncthreads();
+    if (cok) {
 #pragma unroll 1
-    for (int sub = 0; sub < TT / (4 * FR); ++sub) {
-      const int f0 = sub * 4 * FR + fr * FR;
-      if (t0 + f0 >= T) break;
-      float acc[FR];
+      for (int sub = 0; sub < TT / SUB; ++sub) {
+        const int f0 = sub * SUB + fr * FR;
+        if (t0 + f0 >= T) break;
+        float2 acc[FR];
 #pragma unroll
-      for (int o = 0; o < FR; ++o) acc[o] = bs;
+        for (int o = 0; o < FR; ++o) acc[o] = bs;
 #pragma unroll
-      for (int j = 0; j < FR + KMAX - 1; ++j) {
-        if (KT > 0 ? (j < FR + KT - 1) : (j < FR + K - 1)) {
-          const float v = sm[f0 + j][cl];
+        for (int j = 0; j < FR + KMAX - 1; ++j) {
+          if (KT > 0 ? (j < FR + KT - 1) : (j < FR + K - 1)) {
+            const float2 v = *reinterpret_cast<const float2*>(&sm[f0 + j][2 * cp]);
 #pragma unroll
-          for (int o = 0; o < FR; ++o)
-            if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) acc[o] += wr[j - o] * v;  // wr[k] = 0 for k >= K
+            for (int o = 0; o < FR; ++o)
+              if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) acc[o] = b2_fma2(wr[j - o], v, acc[o]);  // wr[k] = 0 for k >= K
+          }
         }
-      }
 #pragma unroll
-      for (int o = 0; o < FR; ++o) {
-        const int t = t0 + f0 + o;
-        if (t < T) {
-          out[((long long)b * T + t) * C + c] = __float2bfloat16(acc[o]);
-          s1 += acc[o];
-          s2 += acc[o] * acc[o];
+        for (int o = 0; o < FR; ++o) {
+          const int t = t0 + f0 + o;
+          if (t < T) {
+            *reinterpret_cast<uint32_t*>(out + ((long long)b * T + t) * C + c) = pack_bf16x2(acc[o].x, acc[o].y);
+            s1.x += acc[o].x;
+            s1.y += acc[o].y;
+            s2 = b2_fma2(acc[o], acc[o], s2);
+          }
         }
       }
     }
   }
-  }
-  red[0][fr][cl] = s1;
-  red[1][fr][cl] = s2;
+  *reinterpret_cast<float2*>(&red[0][fr][2 * cp]) = s1;
+  *reinterpret_cast<float2*>(&red[1][fr][2 * cp]) = s2;
   __syncthreads();
-  if (fr == 0 && c < C && sums != nullptr) {
-    atomicAdd(sums + c, red[0][0][cl] + red[0][1][cl] + red[0][2][cl] + red[0][3][cl]);
-    atomicAdd(sums + C + c, red[1][0][cl] + red[1][1][cl] + red[1][2][cl] + red[1][3][cl]);
+  if (threadIdx.x < CC && c0 + threadIdx.x < C && sums != nullptr) {
+    float a = 0.f, q = 0.f;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) {
+      a += red[0][l][threadIdx.x];
+      q += red[1][l][threadIdx.x];
+    }
+    atomicAdd(sums + c0 + threadIdx.x, a);
+    atomicAdd(sums + C + c0 + threadIdx.x, q);
   }
 }
 
+// (One channel per thread, scalar FMAs: the channel-pair / FFMA2 form that helps the forward was measured SLOWER here --
+// 87.7 against 81.5 us -- its two passes per tile re-walk the sub-tiles and the kernel is bound by the staging round trips
+// and barriers, not by FMA issue.)
+constexpr int FR1 = 8;
 // Backward: grid (channel tiles, utterance chunks); each block walks all its (utterance, time tile) pairs and keeps the
 // depthwise weight gradient in registers across them, so the global atomics are per block, not per tile.
 template <int TT, int KT>
@@ -176,45 +221,45 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
      }
      float accb = 0.f;
 #pragma unroll 1
-     for (int sub = 0; sub < TT / (4 * FR); ++sub) {
-      const int f0 = sub * 4 * FR + fr * FR;
+     for (int sub = 0; sub < TT / (4 * FR1); ++sub) {
+      const int f0 = sub * 4 * FR1 + fr * FR1;
       if (t0 + f0 >= T) break;
-      float dg[FR], dv[FR];
+      float dg[FR1], dv[FR1];
       // the GLU inputs of the thread's own frames (for d_a, d_gate) are fetched now; their latency hides under the taps
-      bf16 pa[FR], pg[FR];
+      bf16 pa[FR1], pg[FR1];
 #pragma unroll
-      for (int o = 0; o < FR; ++o) {
+      for (int o = 0; o < FR1; ++o) {
         const int t = min(t0 + f0 + o, T - 1);
         const bf16* row = pw1 + ((long long)b * T + t) * (2 * C);
         pa[o] = row[c];
         pg[o] = row[C + c];
       }
 #pragma unroll
-      for (int o = 0; o < FR; ++o) {
+      for (int o = 0; o < FR1; ++o) {
         dg[o] = 0.f;
         dv[o] = sd[f0 + o + pad][cl];  // d_dw at the thread's own frames (0 beyond T by staging)
         accb += dv[o];
       }
 #pragma unroll
-      for (int j = 0; j < FR + KMAX - 1; ++j) {
-        if (KT > 0 ? (j < FR + KT - 1) : (j < FR + K - 1)) {
+      for (int j = 0; j < FR1 + KMAX - 1; ++j) {
+        if (KT > 0 ? (j < FR1 + KT - 1) : (j < FR1 + K - 1)) {
           // d_glu[f0+o] = sum_k w[k] * d_dw[f0 + o - k + pad]  = sum over staged row j = o + (K-1) - k
           const float dj = sd[f0 + j][cl];
           const float gj = sg[f0 + j][cl];
 #pragma unroll
-          for (int o = 0; o < FR; ++o) {
+          for (int o = 0; o < FR1; ++o) {
             // forward tap index of staged row j for output o: k = j - o (glu[f0+o+k] feeds out[f0+o])
             if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) acc[j - o] += dv[o] * gj;
           }
 #pragma unroll
-          for (int o = 0; o < FR; ++o) {
+          for (int o = 0; o < FR1; ++o) {
             // backward: d_dw[f0+o - k + pad] sits in staged row j = o + (K-1) - k  ->  w[k] = wrev[j - o]
             if (j - o >= 0 && j - o < (KT > 0 ? KT : KMAX)) dg[o] += wrev[j - o] * dj;
           }
         }
       }
 #pragma unroll
-      for (int o = 0; o < FR; ++o) {
+      for (int o = 0; o < FR1; ++o) {
         const int t = t0 + f0 + o;
         if (t < T) {
           const float a = __bfloat162float(pa[o]), gt = __bfloat162float(pg[o]);
@@ -420,11 +465,18 @@ __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __r
 
 // Frames per tile for K = 31: every tile stages TT + 30 frames and pays two block barriers, so pick the tile length that
 // stages the fewest frames for this T (T = 124: one 128-frame tile, 158 staged, instead of two 96-frame tiles, 252).
-int dw_tile_frames(int T) {
+// blocks per SM the grids are sized for (two are resident: 128 registers, <= 97 KB of shared memory)
+int dw_blocks_per_sm() {
+  static const int v = getenv("B200SLU_DW_BPS") ? atoi(getenv("B200SLU_DW_BPS")) : 2;  // tuning only
+  return v > 0 ? v : 2;
+}
+
+int dw_tile_frames(int T, bool allow192) {
   static const int forced = getenv("B200SLU_DW_TT") ? atoi(getenv("B200SLU_DW_TT")) : 0;  // tuning only
-  if (forced == 32 || forced == 96 || forced == 128) return forced;
+  if (forced == 32 || forced == 96 || forced == 128 || (forced == 192 && allow192)) return forced;
   if (T <= 64) return 32;
-  const int c96 = ((T + 95) / 96) * (96 + 30), c128 = ((T + 127) / 128) * (128 + 30);
+  const int c96 = ((T + 95) / 96) * (96 + 30), c128 = ((T + 127) / 128) * (128 + 30), c192 = ((T + 191) / 192) * (192 + 30);
+  if (allow192 && c192 <= c128 && c192 <= c96) return 192;  // forward only: the backward's two tiles would not fit twice per SM
   return c128 <= c96 ? 128 : 96;
 }
 
@@ -441,14 +493,22 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
 #define B2_FWD(TT_, KT_)                                                                                              \
   do {                                                                                                                \
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                          \
-    int gy = (4 * b2_num_sms() + ctiles - 1) / ctiles;                                                                \
+    int gy = (dw_blocks_per_sm() * b2_num_sms() + ctiles - 1) / ctiles;                                               \
     if (gy > units) gy = units;                                                                                       \
-    glu_dw_fwd_kernel<TT_, KT_><<<dim3(ctiles, gy), 256, 0, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out,  \
-                                                                  bn_sums);                                           \
+    const size_t smem = (size_t)((TT_ + KMAX - 1) * CC + 2 * 8 * CC) * sizeof(float);                                 \
+    auto kern = glu_dw_fwd_kernel<TT_, KT_>;                                                                          \
+    static unsigned long long cfg = 0;                                                                                \
+    if (!b2_device_done(cfg)) {                                                                                       \
+      B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                    \
+      b2_device_mark(cfg);                                                                                            \
+    }                                                                                                                 \
+    kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out, bn_sums);            \
   } while (0)
   if (K == 31) {
-    const int tt = dw_tile_frames(T);
-    if (tt == 128) B2_FWD(128, 31);
+    // one tile per utterance up to 192 frames (halo 30 / T), else the tiling with the least staged frames
+    const int tt = dw_tile_frames(T, true);
+    if (tt == 192) B2_FWD(192, 31);
+    else if (tt == 128) B2_FWD(128, 31);
     else if (tt == 96) B2_FWD(96, 31);
     else B2_FWD(32, 31);
   } else {
@@ -468,7 +528,7 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
 #define B2_BWD(TT_, KT_)                                                                                                     \
   do {                                                                                                                       \
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                                 \
-    int gy = (2 * b2_num_sms() + ctiles - 1) / ctiles;                                                                       \
+    int gy = (dw_blocks_per_sm() * b2_num_sms() + ctiles - 1) / ctiles;                                                      \
     if (gy > units) gy = units;                                                                                              \
     const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 2) + KMAX * CC) * sizeof(float);                               \
     auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
@@ -481,7 +541,7 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
                                               dbias_accum);                                                                  \
   } while (0)
   if (K == 31) {
-    const int tt = dw_tile_frames(T);
+    const int tt = dw_tile_frames(T, false);
     if (tt == 128) B2_BWD(128, 31);
     else if (tt == 96) B2_BWD(96, 31);
     else B2_BWD(32, 31);
