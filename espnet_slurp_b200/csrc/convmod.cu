@@ -73,6 +73,54 @@ __device__ __forceinline__ void stage_tiles(const bf16* __restrict__ pw1, const 
   }
 }
 
+// Asynchronous form of the forward's staging: the raw bf16 halves (a | gate) of the NEXT tile are copied global -> shared
+// with cp.async (no registers held, zero-fill outside [0, T)) while the current tile is being computed; a conversion pass
+// then turns them into the fp32 GLU tile.  One HBM round trip per tile leaves the critical path.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+template <int TT>
+__device__ __forceinline__ void issue_raw_tile(const bf16* __restrict__ pw1, int b, int T, int C, int t0, int c0, int K,
+                                               uint4* raw_a, uint4* raw_g) {
+  constexpr int UT = ((TT + KMAX - 1) * (CC / 8) + 255) / 256;
+  const int pad = (K - 1) / 2, nitems = (TT + K - 1) * (CC / 8);
+#pragma unroll
+  for (int u = 0; u < UT; ++u) {
+    const int it = threadIdx.x + u * 256;
+    if (it < nitems) {
+      const int f = it / (CC / 8), cg = it - f * (CC / 8);
+      const int t = t0 - pad + f, c = c0 + cg * 8;
+      const bool ok = t >= 0 && t < T && c < C;
+      const bf16* row = pw1 + ((long long)b * T + (ok ? t : 0)) * (2 * C) + (ok ? c : 0);
+      cp_async16((uint32_t)__cvta_generic_to_shared(raw_a + it), row, ok ? 16 : 0);
+      cp_async16((uint32_t)__cvta_generic_to_shared(raw_g + it), row + C, ok ? 16 : 0);
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int TT>
+__device__ __forceinline__ void convert_raw_tile(const uint4* raw_a, const uint4* raw_g, int K, float (*sg)[CC]) {
+  constexpr int UT = ((TT + KMAX - 1) * (CC / 8) + 255) / 256;
+  const int nitems = (TT + K - 1) * (CC / 8);
+#pragma unroll
+  for (int u = 0; u < UT; ++u) {
+    const int it = threadIdx.x + u * 256;
+    if (it < nitems) {
+      const int f = it / (CC / 8), cg = it - f * (CC / 8);
+      float a[8], gt[8], g[8];
+      unpack8_bf16(raw_a[it], a);
+      unpack8_bf16(raw_g[it], gt);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) g[q] = a[q] * sigmoidf_(gt[q]);  // 0 * sigmoid(0) = 0 outside the utterance
+      const int h = (cg >> 2) & 1;  // see stage_tiles: every store instruction touches 32 distinct banks
+      float4* dst = reinterpret_cast<float4*>(&sg[f][cg * 8]);
+      const float4 lo = make_float4(g[0], g[1], g[2], g[3]), hi = make_float4(g[4], g[5], g[6], g[7]);
+      dst[h] = h ? hi : lo;
+      dst[h ^ 1] = h ? lo : hi;
+    }
+  }
+}
+
 // Each thread owns a PAIR of neighbouring channels and, per sub-tile, FR consecutive output frames: the K + FR - 1 staged
 // inputs it needs are read from shared memory once (one 8-byte load per frame) into a sliding window, the taps of both
 // channels stay in registers as pairs and every multiply-add is a packed fma.rn.f32x2 (FFMA2: the FMA pipe's rate of
@@ -93,6 +141,8 @@ __global__ void __launch_bounds__(256, 2) glu_dw_fwd_kernel(const bf16* __restri
   extern __shared__ __align__(16) float dyn_smem[];
   float (*sm)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                           // glu halo tile [TT+KMAX-1][CC]
   float (*red)[8][CC] = reinterpret_cast<float (*)[8][CC]>(dyn_smem + (TT + KMAX - 1) * CC);  // [2][8 frame lanes][CC]
+  uint4* raw_a = reinterpret_cast<uint4*>(dyn_smem + (TT + KMAX - 1) * CC + 2 * 8 * CC);      // raw bf16 a half, next tile
+  uint4* raw_g = raw_a + (TT + KMAX - 1) * (CC / 8);                                          // ... gate half
   const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
   const int cp = threadIdx.x & 31, fr = threadIdx.x >> 5;  // channel pair, frame lane
@@ -127,11 +177,17 @@ __global__ void __launch_bounds__(256, 2) glu_dw_fwd_kernel(const bf16* __restri
   float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
   // Each block walks its (utterance, time tile) units and keeps the BatchNorm partial sums in registers across them:
   // the atomics on `sums` are per block (grid.y per channel), not per tile -- same-address atomics retire serially.
+  if ((int)blockIdx.y < B * ntt) issue_raw_tile<TT>(pw1, blockIdx.y / ntt, T, C, (blockIdx.y % ntt) * TT, c0, K, raw_a, raw_g);
   for (int unit = blockIdx.y; unit < B * ntt; unit += gridDim.y) {
     const int b = unit / ntt, t0 = (unit - b * ntt) * TT;
-    __syncthreads();  // previous tile fully consumed
-    stage_tiles<TT, false>(pw1, nullptr, b, T, C, t0, c0, K, sm, nullptr);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();  // this tile's raw halves have landed (every thread's copies); the previous tile is fully consumed
+    convert_raw_tile<TT>(raw_a, raw_g, K, sm);
     __syncthreads();
+    {  // the raw buffers are free again: the next tile's copies fly under this tile's arithmetic
+      const int nx = unit + gridDim.y;
+      if (nx < B * ntt) issue_raw_tile<TT>(pw1, nx / ntt, T, C, (nx % ntt) * TT, c0, K, raw_a, raw_g);
+    }
     if (cok) {
 #pragma unroll 1
       for (int sub = 0; sub < TT / SUB; ++sub) {
@@ -495,7 +551,7 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                          \
     int gy = (dw_blocks_per_sm() * b2_num_sms() + ctiles - 1) / ctiles;                                               \
     if (gy > units) gy = units;                                                                                       \
-    const size_t smem = (size_t)((TT_ + KMAX - 1) * CC + 2 * 8 * CC) * sizeof(float);                                 \
+    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + 2 * 8 * CC) * sizeof(float);                             \
     auto kern = glu_dw_fwd_kernel<TT_, KT_>;                                                                          \
     static unsigned long long cfg = 0;                                                                                \
     if (!b2_device_done(cfg)) {                                                                                       \
@@ -505,10 +561,9 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
     kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out, bn_sums);            \
   } while (0)
   if (K == 31) {
-    // one tile per utterance up to 192 frames (halo 30 / T), else the tiling with the least staged frames
-    const int tt = dw_tile_frames(T, true);
-    if (tt == 192) B2_FWD(192, 31);
-    else if (tt == 128) B2_FWD(128, 31);
+    // the tiling with the least staged frames
+    const int tt = dw_tile_frames(T, false);
+    if (tt == 128) B2_FWD(128, 31);
     else if (tt == 96) B2_FWD(96, 31);
     else B2_FWD(32, 31);
   } else {
