@@ -33,6 +33,10 @@ extern "C" int b200slu_set_step_params(const void* dev_ptr) {
   return 0;
 }
 
+// SMs the persistent kernels size their grids for.  b200slu_set_sm_budget(n) leaves the others to whatever else runs on
+// the device (the data-parallel trainer: NCCL's CTAs during the overlapped all-reduce -- a persistent grid of all 148 SMs
+// would have its last CTAs wait for NCCL's to leave, and, being statically partitioned, end that much later).
+static int g_sm_budget[64] = {};
 int b2_num_sms() {
   static int n[64] = {};
   const int dev = b2_current_device();
@@ -40,7 +44,14 @@ int b2_num_sms() {
   if (v == 0) {
     if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
   }
-  return v;
+  const int lim = g_sm_budget[dev & 63];
+  return (lim > 0 && lim < v) ? lim : v;
+}
+
+extern "C" int b200slu_set_sm_budget(int sms) {
+  B2_CHECK_ARG(sms >= 0, "set_sm_budget: sms >= 0 (0 = all)");
+  g_sm_budget[b2_current_device() & 63] = sms > 0 ? (sms < 8 ? 8 : (sms & ~1)) : 0;  // even: CTA pairs
+  return 0;
 }
 
 static __device__ __align__(256) long long g_debug_scratch[4096];

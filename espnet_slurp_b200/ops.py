@@ -625,6 +625,11 @@ def adam_step_sched(params, grads, exp_avg, exp_avg_sq, base_lr: float, warmup_s
                                              ptr(state4), stream_ptr()), "adam_step_sched")
 
 
+def set_sm_budget(sms: int):
+    """SMs the persistent kernels size their grids for on the current device (0 = all)."""
+    check(_lib.lib().b200slu_set_sm_budget(int(sms)), "set_sm_budget")
+
+
 def set_step_params(dev_tensor):
     """Register (or with None unregister) the 24-byte device buffer {u64 seed; f32 lr, bc1, bc2, pad}."""
     check(_lib.lib().b200slu_set_step_params(ptr(dev_tensor)), "set_step_params")

@@ -30,6 +30,7 @@ More than one rank (the reference's DDP overlaps its bucketed all-reduce with th
 """
 from __future__ import annotations
 
+import os
 from collections import OrderedDict
 from typing import Dict, Optional
 
@@ -84,6 +85,8 @@ class TrainStep:
         # (step.encoder_bwd): those parameters then belong to the last bucket, not to "heads"
         late = ("ctc.",) if cfg.enc.interctc_use_conditioning else ()
         self.reducer = GradReducer(self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
+        # SMs left to the compute kernels while a gradient bucket is being all-reduced (0 = all; tuning: B200SLU_DP_SM_BUDGET)
+        self.sm_budget = int(os.environ.get("B200SLU_DP_SM_BUDGET", "0"))
         self.buckets: "OrderedDict[tuple, _Bucket]" = OrderedDict()
         # per-step device record {u64 dropout seed; f32 lr, bias correction 1, bias correction 2, pad}: a ring of pinned
         # host slots so that the asynchronous copy of step s is never overwritten by the host preparing step s + 1
@@ -172,12 +175,16 @@ class TrainStep:
                 chain.append((cur[0], stage))
                 cur[0] = torch.cuda.CUDAGraph()
                 cur[0].capture_begin(pool=chain[0][0].pool())
+                # from here on a bucket's all-reduce runs beside the kernels: size the persistent grids for the SMs NCCL
+                # leaves (a grid of all SMs would wait for NCCL's CTAs and, statically partitioned, end that much later)
+                ops.set_sm_budget(self.sm_budget)
 
         with torch.cuda.stream(side):
             cur[0].capture_begin()
             self._body(b, overlap=False, on_ready=cut)
             cur[0].capture_end()
             chain.append((cur[0], None))
+        ops.set_sm_budget(0)
         torch.cuda.current_stream().wait_stream(side)
         b.graph = chain
 

@@ -348,6 +348,11 @@ int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, f
                             float warmup_steps, float beta1, float beta2, float eps, float weight_decay, float grad_inv_scale,
                             float max_norm, double* state4, void* stream);
 
+/* Number of SMs the persistent kernels (GEMM, attention, LayerNorm backward) launch their grids for on the current device;
+ * 0 = all (default).  Grids are fixed at launch / graph-capture time.  Used by the data-parallel trainer to leave a few SMs
+ * to NCCL's kernels while the gradient all-reduce overlaps the backward. */
+int b200slu_set_sm_budget(int sms);
+
 #ifdef __cplusplus
 }
 #endif
