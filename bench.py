@@ -315,6 +315,7 @@ class Trainer:
         if os.environ.get("B200SLU_BENCH_FORCE_CUTS"):  # tuning: the chain-of-graphs capture on one GPU (cost of the cuts alone)
             self.ts.force_cuts = tuple(s for s, _, _ in self.ts.reducer.stages if s != "front")
         self.host_batches, self.dev_batches, self.flens, self.done = [], [], [], []
+        self.prepared = None
         self.gen = torch.Generator().manual_seed(99 + rank)
         for i in range(4):
             wav, lens, text, tl = make_batch(args.batch, cfg.vocab, 1234 + rank * 100 + i, args.min_sec, args.max_sec, args.tok)
@@ -339,20 +340,36 @@ class Trainer:
     def drop_graphs(self):
         self.ts.drop_graphs()
 
-    def step(self, i, e2e=False):
+    def _host_prepare(self, j):
+        hb = self.host_batches[j]
+        if self.done[j] is not None:
+            self.done[j].synchronize()  # the previous H2D copy out of these pinned buffers has finished
+        for k, v in specaug_draws(self.flens[j], hb["wav"].shape[1] // self.cfg.hop + 1, gen=self.gen).items():
+            hb[k].copy_(v)
+        return hb
+
+    def step(self, i, e2e=False, more=False):
         # e2e: what a training loop pays per step -- the SpecAug draws are made on the host (128 per-utterance randint pairs,
         # time_warp.py:28-29, + the mask draws) inside the timed region, the inputs come from pinned HOST memory (H2D inside
         # the timed region) and the losses are read back (D2H)
+        # (D2H).  Like a DataLoader with pinned memory, the NEXT step's batch is prepared and its H2D copy started
+        # (TrainStep.prefetch, copy stream) while this step runs; every step's draws and copies are inside the timed region
+        # (the first step of a region copies inline, the last one prefetches nothing).
         if e2e:
             j = i % 4
-            hb = self.host_batches[j]
-            if self.done[j] is not None:
-                self.done[j].synchronize()  # the previous H2D copy out of these pinned buffers has finished
-            for k, v in specaug_draws(self.flens[j], hb["wav"].shape[1] // self.cfg.hop + 1, gen=self.gen).items():
-                hb[k].copy_(v)
+            if self.prepared != i:
+                hb = self._host_prepare(j)
+            else:
+                hb = self.host_batches[j]
             self.ts(hb, fetch_loss=True)
-            self.done[j] = torch.cuda.Event()
-            self.done[j].record()
+            if self.prepared != i:
+                self.done[j] = torch.cuda.Event()
+                self.done[j].record()
+            self.prepared = None
+            if more:
+                jn = (i + 1) % 4
+                self.done[jn] = self.ts.prefetch(self._host_prepare(jn))
+                self.prepared = i + 1
         else:
             self.ts(self.dev_batches[i % 4], fetch_loss=False)
 
@@ -394,7 +411,7 @@ def run_ours(args):
         e0.record()
         last = None
         for i in range(n):
-            last = tr.step(i, e2e=e2e)
+            last = tr.step(i, e2e=e2e, more=i + 1 < n)
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")

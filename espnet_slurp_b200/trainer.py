@@ -52,6 +52,10 @@ class _Bucket:
         self.res: Optional[torch.Tensor] = None
         self.graph = None  # once captured: list of (CUDAGraph, stage whose gradient bucket is final after it or None)
         self.eager_steps = 0
+        # prefetch(): two device staging sets filled on the copy stream, alternating; `free[i]` = the D2D that last read set i
+        self.staging = [None, None]
+        self.free = [None, None]
+        self.next_set = 0
 
 
 class TrainStep:
@@ -98,6 +102,7 @@ class TrainStep:
         ops.set_step_params(self.sp_dev)
         self._closed = False
         self.loss_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+        self._prefetched, self._h2d = None, None
         self.last: Optional[_Bucket] = None
 
     # warmup_lr.py:43-50
@@ -229,8 +234,21 @@ class TrainStep:
         if self.sp_events[slot] is None:
             self.sp_events[slot] = torch.cuda.Event()
         self.sp_events[slot].record()
-        for k, v in batch.items():
-            b.inp[k].copy_(v, non_blocking=True)
+        pf = self._prefetched
+        if pf is not None and pf[0] is batch and pf[1] is b:
+            # the copy stream brought this batch over while the previous step ran: one device-to-device pass into the
+            # graph's input buffers (41 MB: ~12 us) instead of the H2D copy on the critical path
+            _, _, i, ready = pf
+            torch.cuda.current_stream().wait_event(ready)
+            for k in batch:
+                b.inp[k].copy_(b.staging[i][k], non_blocking=True)
+            if b.free[i] is None:
+                b.free[i] = torch.cuda.Event()
+            b.free[i].record()
+        else:
+            for k, v in batch.items():
+                b.inp[k].copy_(v, non_blocking=True)
+        self._prefetched = None
         self.reducer.begin()
         if b.graph is not None:
             for g, stage in b.graph:
@@ -250,6 +268,28 @@ class TrainStep:
         if fetch_loss:
             self.loss_host.copy_(res, non_blocking=True)
         return res
+
+    def prefetch(self, batch: Dict[str, torch.Tensor]) -> torch.cuda.Event:
+        """Start the host-to-device copy of the NEXT step's batch (pinned host tensors) on a copy stream, so that it runs
+        under the current step's kernels; the next __call__ with this same dict picks the staged copy up.  Returns the
+        event after which the host buffers may be rewritten.  What a data loader's pinned-memory prefetch does in the
+        reference's loop (`trainer.py:464-475` iterates a DataLoader with `pin_memory`)."""
+        b = self._bucket(batch)
+        if self._h2d is None:
+            self._h2d = torch.cuda.Stream(device=self.dev)
+        i = b.next_set
+        b.next_set ^= 1
+        if b.staging[i] is None:
+            b.staging[i] = {k: torch.empty(v.shape, dtype=v.dtype, device=self.dev) for k, v in batch.items()}
+        if b.free[i] is not None:
+            self._h2d.wait_event(b.free[i])  # the step that last used this staging set has copied it out
+        with torch.cuda.stream(self._h2d):
+            for k, v in batch.items():
+                b.staging[i][k].copy_(v, non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record()
+        self._prefetched = (batch, b, i, ready)
+        return ready
 
     def optimizer_state_dict(self) -> Dict[str, Dict[str, torch.Tensor]]:
         """Adam's state per parameter NAME in torch.optim.Adam's vocabulary (step, exp_avg, exp_avg_sq, reference shapes): what

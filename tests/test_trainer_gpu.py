@@ -222,3 +222,37 @@ def test_skipped_step_does_not_advance_schedule_and_state_exports():
     # parameters whose gradient is mathematically zero move by +-lr on that noise and are left out
     worst = max(float((sa[k] - sb[k]).abs().max()) for k in sd if not k.endswith(("linear_k.bias", "depthwise_conv.bias")))
     assert worst < 2e-5, worst
+
+
+def test_prefetched_batches_give_the_same_steps():
+    """TrainStep.prefetch: the next batch's H2D copy on the copy stream + a device-to-device pass into the graph's inputs
+    must be indistinguishable from the inline copy, over alternating shapes and reused pinned buffers."""
+    from espnet_slurp_b200.trainer import TrainStep
+    cfg, ocfg = _cfg()
+    sd = make_sd(ocfg.enc, ocfg.dec, 30, seed=8)
+    a = TrainStep(cfg, sd, use_graph=True, lr=2e-3, warmup_steps=4)
+    b = TrainStep(cfg, sd, use_graph=True, lr=2e-3, warmup_steps=4)
+    shapes = [(3, 8000, 5), (2, 6000, 4)]
+    pinned = [{k: v.pin_memory() for k, v in _batch(*shapes[i % 2], seed=60 + i).items()} for i in range(2)]
+    ready = [None, None]
+    nxt = None
+    for i in range(6):
+        fresh = _batch(*shapes[i % 2], seed=70 + i)
+        la = a({k: v.cuda() for k, v in fresh.items()}).clone()
+        hb = pinned[i % 2]
+        if nxt is None:  # first step: inline copy from the pinned buffers
+            for k, v in fresh.items():
+                hb[k].copy_(v)
+        lb = b(hb).clone()
+        if i + 1 < 6:  # prepare and prefetch the next batch while this step runs
+            j = (i + 1) % 2
+            if ready[j] is not None:
+                ready[j].synchronize()
+            for k, v in _batch(*shapes[j], seed=70 + i + 1).items():
+                pinned[j][k].copy_(v)
+            ready[j] = b.prefetch(pinned[j])
+            nxt = i + 1
+        torch.cuda.synchronize()
+        # two runs of the same steps differ by the order of the split-K reduce-adds (1e-4 relative after a few Adam steps);
+        # a stale or half-copied batch would be a different utterance set: losses apart by several percent
+        np.testing.assert_allclose(la[:3].cpu().numpy(), lb[:3].cpu().numpy(), rtol=3e-3, atol=1e-4)
