@@ -85,7 +85,7 @@ _SIGNATURES = {
                                   _I, _I, _P, _P],
     "b200slu_relattn_combine": [_P, _L, _I, _I, _I, _P, _P, _L, _L, _P, _L, _I, _I, _I, _P],
     "b200slu_relattn_bwd_chunks": [_P, _L, _P, _L, _P, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _L, _L, _P, _P, _L, _F,
-                                   _U64, _U32, _P, _P, _L, _P, _P, _L, _P],
+                                   _U64, _U32, _P, _P, _L, _P, _P, _L, _I, _I, _P],
     "b200slu_sum_chunks_bf16": [_P, _L, _L, _I, _L, _I, _P, _L, _P],
     "b200slu_rel_unshift": [_P, _L, _I, _I, _I, _I, _P, _L, _P],
     "b200slu_rel_shift_index": [_I, _I, _I, _I],

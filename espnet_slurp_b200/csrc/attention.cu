@@ -590,7 +590,7 @@ struct AttnBwdArgs {
   // [c * chunk_keys, +min(chunk_keys, Tk - c * chunk_keys)) of the kv_rows keys per utterance (Tk = kv_rows then) and
   // writes its dq_u / dq_v contribution to slab c (dq_slab elements apart).  The key offset shifts the K / V / p tile
   // coordinates, the rel-pos window and the dropout counter.  One chunk: chunk_keys = Tk, the plain kernel.
-  int nchunk, chunk_keys, kv_rows;
+  int nchunk, chunk_keys, kv_rows, key_begin, key_end;  // chunk c covers keys key_begin + c * chunk_keys ... (< key_end)
   long long dq_slab;
 };
 
@@ -661,7 +661,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
   // the skewed tile on V).  Issued one tile AHEAD, as soon as the last MMA that reads those regions has completed, so the
   // load latency hides behind the previous tile's read-out.
   auto issue_loads = [&](int unit_, int qt_) {
-    const int bh_ = unit_ % (a.B * a.H), koff_ = (unit_ / (a.B * a.H)) * a.chunk_keys;
+    const int bh_ = unit_ % (a.B * a.H), koff_ = a.key_begin + (unit_ / (a.B * a.H)) * a.chunk_keys;
     const int h_ = bh_ % a.H, b_ = bh_ / a.H, i0_ = qt_ * QT;
     mbar_expect_tx(bar_kv, (uint32_t)(2 * TKP * 128));
     tma_load_3d(s_k, &map_k, bar_kv, h_ * DK, koff_, b_);
@@ -687,7 +687,7 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
   for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
     const int bh = unit % (a.B * a.H), chunk = unit / (a.B * a.H);
     const int h = bh % a.H, b = bh / a.H;
-    const int key_off = chunk * a.chunk_keys, tk_c = min(a.chunk_keys, a.Tk - key_off);  // this unit's keys
+    const int key_off = a.key_begin + chunk * a.chunk_keys, tk_c = min(a.chunk_keys, a.key_end - key_off);  // this unit's keys
     for (int qt = 0; qt < nqt; ++qt) {
       const int i0 = qt * QT, i = i0 + r;
       const bool row_ok = i < a.Tq;
@@ -1214,12 +1214,16 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
                             int Tq, int Tk, int relpos_mode, float scale, void* dq_u, long long lddq, void* dk_out,
                             void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
                             unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
-                            float* dpos_accum, long long lddpos, int chunk_keys, long long dq_slab, void* stream) {
-  // Tk = all keys of an utterance; chunk_keys = keys per work unit (Tk itself for the one-chunk form)
+                            float* dpos_accum, long long lddpos, int chunk_keys, long long dq_slab, int key_begin,
+                            int key_end, void* stream) {
+  // Tk = all keys of an utterance; this launch covers keys [key_begin, key_end) in chunks of chunk_keys (one work unit
+  // each; [0, Tk) in one chunk for the plain form)
   B2_CHECK_ARG(B > 0 && H > 0, "relattn_bwd: empty problem");
-  const int nchunk = chunk_keys > 0 ? (Tk + chunk_keys - 1) / chunk_keys : 0;
-  B2_CHECK_ARG(chunk_keys >= 1 && b200slu_relattn_chunk_supported(Tq, chunk_keys, DK, relpos_mode) &&
-                   (nchunk == 1 || (chunk_keys % 64 == 0 && d_ac == nullptr && dq_slab % 8 == 0)) && ld_p >= Tk,
+  const int nchunk = chunk_keys > 0 && key_begin >= 0 && key_begin < key_end && key_end <= Tk
+                         ? (key_end - key_begin + chunk_keys - 1) / chunk_keys : 0;
+  B2_CHECK_ARG(chunk_keys >= 1 && nchunk >= 1 && b200slu_relattn_chunk_supported(Tq, chunk_keys, DK, relpos_mode) &&
+                   ((nchunk == 1 && key_begin == 0 && key_end == Tk) || (chunk_keys % 64 == 0 && key_begin % 64 == 0 && d_ac == nullptr && dq_slab % 8 == 0)) &&
+                   ld_p >= Tk,
                "relattn_bwd: supports d_k = 64, <= %d keys per chunk (whole 64-key blocks when there are several), rel-pos mode latest "
                "or none (got Tq=%d Tk=%d mode=%d chunk_keys=%d)", MAX_TK, Tq, Tk, relpos_mode, chunk_keys);
   B2_CHECK_ARG(relpos_mode != B200SLU_RELPOS_LATEST || Tk == Tq, "relattn_bwd: rel-pos mode attends over the queries' own axis");
@@ -1245,7 +1249,7 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
   a.dq = (bf16*)dq_u; a.dk = (bf16*)dk_out; a.dv = (bf16*)dv_out; a.dac = (bf16*)d_ac;
   a.lddq = lddq; a.lddkv = lddkv; a.ld_p = ld_p;
   a.dqv = (bf16*)dq_v; a.dpos = dpos_accum; a.lddpos = lddpos;
-  a.nchunk = nchunk; a.chunk_keys = chunk_keys; a.kv_rows = Tk; a.dq_slab = dq_slab;
+  a.nchunk = nchunk; a.chunk_keys = chunk_keys; a.kv_rows = Tk; a.dq_slab = dq_slab; a.key_begin = key_begin; a.key_end = key_end;
   // [pd tile | dO | Q_u | V] [dS tile] [K, later Q_v] [position window].  The first group is dead once dQ_u / dK / dV are
   // issued: the skewed d(bd) tile is built over it (dS, its source, stays).  An M = 128 MN-major read over the last key /
   // window tile may run past the blocks that exist into the next region: never faulting (bounded below), never stored.
@@ -1329,7 +1333,7 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
                "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
                Tq, Tk, relpos_mode);
   return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u, lddq, dk_out,
-                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, Tk, 0, stream);
+                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, Tk, 0, 0, Tk, stream);
 }
 
 extern "C" int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k,
@@ -1338,10 +1342,10 @@ extern "C" int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, con
                                           float scale, void* dq_u_slabs, long long lddq, long long dq_slab, void* dk_out,
                                           void* dv_out, long long lddkv, float drop_p, unsigned long long seed, unsigned int site,
                                           const void* q_v, const void* pos, long long ldpos, void* dq_v_slabs, float* dpos_accum,
-                                          long long lddpos, void* stream) {
+                                          long long lddpos, int key_begin, int key_end, void* stream) {
   return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u_slabs, lddq,
                           dk_out, dv_out, lddkv, nullptr, drop_p, seed, site, q_v, pos, ldpos, dq_v_slabs, dpos_accum, lddpos,
-                          chunk_keys, dq_slab, stream);
+                          chunk_keys, dq_slab, key_begin, key_end, stream);
 }
 
 // ----------------------------------------------------------------------------- key chunks -> one softmax

@@ -345,10 +345,16 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: 
     chunks = _key_chunks(Tk)
     d = H * 64
     dqc = torch.empty(2 if rel else 1, len(chunks), B * Tq, d, device=k.device, dtype=torch.bfloat16)
-    check(L.b200slu_relattn_bwd_chunks(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
-                                       ptr(ctx), ctx.stride(0), B, H, Tq, Tk, CHUNK_KEYS, rel, scale, ptr(dqc[0]), d, B * Tq * d,
-                                       ptr(dk), ptr(dv), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos,
-                                       ptr(dqc[1]) if rel else None, ptr(dpos), lddpos, stream_ptr()), "relattn_bwd_chunks")
+    # the full chunks in one launch; a short last chunk in its own, sized to its keys (whole 64-key blocks)
+    nfull = Tk // CHUNK_KEYS
+    tail = Tk - nfull * CHUNK_KEYS
+    for begin, end, ck, c0 in ([(0, Tk, CHUNK_KEYS, 0)] if tail == 0 else
+                               [(0, nfull * CHUNK_KEYS, CHUNK_KEYS, 0), (nfull * CHUNK_KEYS, Tk, -(-tail // 64) * 64, nfull)]):
+        check(L.b200slu_relattn_bwd_chunks(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
+                                           ptr(ctx), ctx.stride(0), B, H, Tq, Tk, ck, rel, scale, ptr(dqc[0, c0]), d,
+                                           B * Tq * d, ptr(dk), ptr(dv), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos,
+                                           ptr(dqc[1, c0]) if rel else None, ptr(dpos), lddpos, begin, end, stream_ptr()),
+              "relattn_bwd_chunks")
     check(L.b200slu_sum_chunks_bf16(ptr(dqc[0]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dq), dq.stride(0), stream_ptr()), "sum_chunks")
     if rel:
         check(L.b200slu_sum_chunks_bf16(ptr(dqc[1]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dqv), dqv.stride(0), stream_ptr()),

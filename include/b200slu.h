@@ -207,8 +207,9 @@ int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long
  * softmax over the chunk, ctx_chunk the chunk's context, lse2 (fp32 [H*B*Tq]) log2 of the chunk's partition sum (-inf when
  * no key of the chunk is valid).  b200slu_relattn_combine: alpha_c = 2^(lse2_c - log2 sum_c 2^lse2_c); p[.., chunk c] *=
  * alpha_c in place and ctx = sum_c alpha_c ctx_c (ctx_chunks [nchunk] slabs chunk_stride elements apart, lse2 [nchunk,
- * H*B*Tq]).  Backward (b200slu_relattn_bwd_chunks: ONE launch, work unit = (chunk, utterance, head), chunk_keys a multiple
- * of 64; k, v, p, dk, dv are the whole tensors): p = the combined probabilities, ctx = the combined context (for delta =
+ * H*B*Tq]).  Backward (b200slu_relattn_bwd_chunks: ONE launch over the keys [key_begin, key_end), work unit = (chunk, utterance,
+ * head), chunk_keys and key_begin multiples of 64 -- a short last chunk gets its own launch with a smaller chunk_keys so
+ * that it does not pay for 192 keys; k, v, p, dk, dv are the whole tensors, the slab pointers those of the launch's first chunk): p = the combined probabilities, ctx = the combined context (for delta =
  * <dO, O>); dk, dv are final, dq_u / dq_v come out as one slab per chunk, dq_slab elements apart (sum them with
  * b200slu_sum_chunks_bf16); dpos_accum accumulates over the chunks like over the utterances. */
 int b200slu_relattn_chunk_supported(int Tq, int Tk_chunk, int dk, int relpos_mode);
@@ -224,7 +225,7 @@ int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, const void* q_
                                int Tk, int chunk_keys, int relpos_mode, float scale, void* dq_u_slabs, long long lddq,
                                long long dq_slab, void* dk, void* dv, long long lddkv, float drop_p, unsigned long long seed,
                                unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v_slabs,
-                               float* dpos_accum, long long lddpos, void* stream);
+                               float* dpos_accum, long long lddpos, int key_begin, int key_end, void* stream);
 int b200slu_sum_chunks_bf16(const void* src, long long chunk_stride, long long ld_src, int nchunk, long long rows, int cols,
                             void* dst, long long ld_dst, void* stream);
 /* d(matrix_bd) [H,B,T,ld_bd] (un-shifted) from d(scores) [H,B,T,ld_p] (shifted): the scatter of rel_shift's backward
