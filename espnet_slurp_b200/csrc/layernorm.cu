@@ -71,6 +71,102 @@ __global__ void __launch_bounds__(256) ln_fwd_kernel(const float* __restrict__ x
   }
 }
 
+// Forward with the rows streamed through a per-warp ring of shared-memory slots (1-D bulk copies on mbarriers, NBUF rows
+// ahead), like ln_bwd_pipe_kernel below: 16 warps x 4 x 2 KB in flight per SM instead of one round trip per warp and row.
+constexpr int LNF_WARPS = 16, LNF_NBUF = 4;
+template <int NG>
+__global__ void __launch_bounds__(LNF_WARPS * 32, 1) ln_fwd_pipe_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                                       const float* __restrict__ beta, int M, int D, float eps,
+                                                                       bf16* __restrict__ y16, float* __restrict__ y32,
+                                                                       float* __restrict__ stats) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ngroups = D >> 3;
+  const uint32_t slot = (uint32_t)D * 4u;
+  const uint32_t sbase = smem_u32(smraw);
+  const uint32_t bar0 = sbase + (uint32_t)(warp * LNF_NBUF) * 8u;
+  const uint32_t ring = 1024u + (uint32_t)(warp * LNF_NBUF) * slot;  // barriers live in the first KB
+  if (lane == 0) {
+    for (int b = 0; b < LNF_NBUF; ++b) mbar_init(bar0 + b * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const long long W = (long long)gridDim.x * LNF_WARPS, gw = (long long)blockIdx.x * LNF_WARPS + warp;
+  auto issue = [&](long long row, int b) {
+    mbar_expect_tx(bar0 + b * 8, slot);
+    bulk_g2s(sbase + ring + (uint32_t)b * slot, x + row * D, slot, bar0 + b * 8);
+  };
+  if (lane == 0) {
+    for (int b = 0; b < LNF_NBUF; ++b)
+      if (gw + b * W < M) issue(gw + b * W, b);
+  }
+  float ga[NG][8], be[NG][8];
+#pragma unroll
+  for (int i = 0; i < NG; ++i) {
+    const int g = lane + 32 * i;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ga[i][j] = be[i][j] = 0.f;
+    if (g < ngroups) {
+      load8_f32(gamma + g * 8, ga[i]);
+      load8_f32(beta + g * 8, be[i]);
+    }
+  }
+  int b = 0;
+  uint32_t ph = 0;
+  for (long long row = gw; row < M; row += W) {
+    mbar_wait(bar0 + b * 8, ph);
+    const float* sl = reinterpret_cast<const float*>(smraw + ring + (uint32_t)b * slot);
+    float v[NG][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+      if (g < ngroups) {
+        load8_f32(sl + g * 8, v[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += v[i][j];
+      }
+    }
+    __syncwarp();
+    if (lane == 0 && row + (long long)LNF_NBUF * W < M) issue(row + (long long)LNF_NBUF * W, b);
+    if (++b == LNF_NBUF) {
+      b = 0;
+      ph ^= 1u;
+    }
+    const float mean = warp_sum(s) / (float)D;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float d = v[i][j] - mean;
+          q += d * d;
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) / (float)D + eps);
+    if (lane == 0 && stats != nullptr) {
+      stats[row * 2] = mean;
+      stats[row * 2 + 1] = rstd;
+    }
+#pragma unroll
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * ga[i][j] + be[i][j];
+        if (y16 != nullptr) store8_bf16(y16 + row * D + g * 8, o);
+        if (y32 != nullptr) store8_f32(y32 + row * D + g * 8, o);
+      }
+    }
+  }
+}
+
 template <int NG, bool DY_F32, bool GSUM>
 __global__ void __launch_bounds__(NG <= 2 ? 384 : 256, 1) ln_bwd_kernel(const void* __restrict__ dy_, const float* __restrict__ x,
                                                      const float* __restrict__ gamma, const float* __restrict__ stats,
@@ -376,6 +472,21 @@ extern "C" int b200slu_layernorm_fwd(const float* x, const float* gamma, const f
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = b2_grid_for((long long)M * 32, 256, 8);
   B2_SCOPE(FAM_LN, st, 0, (double)M * D * (4.0 + (y_bf16 ? 2.0 : 0.0) + (y_f32 ? 4.0 : 0.0)));
+  static const bool fpipe_off = getenv("B200SLU_LN_PIPE") && atoi(getenv("B200SLU_LN_PIPE")) == 0;  // tuning / A-B only
+  if (!fpipe_off && D <= 512 && ((uintptr_t)x % 16) == 0 && M >= 4 * LNF_WARPS) {
+    const size_t psmem = 1024 + (size_t)LNF_WARPS * LNF_NBUF * D * 4;
+    const int pgrid = (int)min((long long)b2_num_sms(), ((long long)M + LNF_WARPS - 1) / LNF_WARPS);
+    static unsigned long long configured = 0;  // per device
+    if (!b2_device_done(configured)) {
+      B2_CUDA(cudaFuncSetAttribute(ln_fwd_pipe_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+      B2_CUDA(cudaFuncSetAttribute(ln_fwd_pipe_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+      b2_device_mark(configured);
+    }
+    if (D <= 256) ln_fwd_pipe_kernel<1><<<pgrid, LNF_WARPS * 32, psmem, st>>>(x, gamma, beta, M, D, eps, (bf16*)y_bf16, y_f32, stats);
+    else ln_fwd_pipe_kernel<2><<<pgrid, LNF_WARPS * 32, psmem, st>>>(x, gamma, beta, M, D, eps, (bf16*)y_bf16, y_f32, stats);
+    B2_LAUNCH_CHECK();
+    return 0;
+  }
 #define LN_F(NG) ln_fwd_kernel<NG><<<grid, 256, 0, st>>>(x, gamma, beta, M, D, eps, (bf16*)y_bf16, y_f32, stats)
   if (D <= 256) LN_F(1);
   else if (D <= 512) LN_F(2);
