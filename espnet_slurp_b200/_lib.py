@@ -71,6 +71,7 @@ _SIGNATURES = {
     "b200slu_colsum_bf16": [_P, _I, _I, _L, _P, _P],
     "b200slu_pos_bias_fwd": [_P, _L, _P, _P, _I, _I, _P, _P, _P],
     "b200slu_pos_bias_bwd": [_P, _P, _I, _I, _P, _L, _P, _P, _P],
+    "b200slu_pos_bias_bwd_q": [_P, _P, _I, _I, _P, _L, _P, _P, _P, _P],
     "b200slu_embed_fwd": [_P, _P, _P, _I, _I, _I, _F, _P, _F, _U64, _U32, _P],
     "b200slu_embed_bwd": [_P, _P, _I, _I, _F, _P, _F, _U64, _U32, _P],
     "b200slu_softmax_fwd": [_P, _L, _P, _L, _P, _I, _I, _I, _I, _I, _I, _F, _P, _P, _L, _F, _U64, _U32, _P],
@@ -85,7 +86,7 @@ _SIGNATURES = {
                                   _I, _I, _P, _P],
     "b200slu_relattn_combine": [_P, _L, _I, _I, _I, _P, _P, _L, _L, _P, _L, _I, _I, _I, _P],
     "b200slu_relattn_bwd_chunks": [_P, _L, _P, _L, _P, _P, _L, _P, _L, _P, _L, _I, _I, _I, _I, _I, _I, _F, _P, _L, _L, _P, _P, _L, _F,
-                                   _U64, _U32, _P, _P, _L, _P, _P, _L, _I, _I, _P],
+                                   _U64, _U32, _P, _P, _L, _P, _P, _L, _I, _I, _P, _P, _P],
     "b200slu_sum_chunks_bf16": [_P, _L, _L, _I, _L, _I, _P, _L, _P],
     "b200slu_rel_unshift": [_P, _L, _I, _I, _I, _I, _P, _L, _P],
     "b200slu_rel_shift_index": [_I, _I, _I, _I],

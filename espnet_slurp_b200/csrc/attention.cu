@@ -591,8 +591,25 @@ struct AttnBwdArgs {
   // writes its dq_u / dq_v contribution to slab c (dq_slab elements apart).  The key offset shifts the K / V / p tile
   // coordinates, the rel-pos window and the dropout counter.  One chunk: chunk_keys = Tk, the plain kernel.
   int nchunk, chunk_keys, kv_rows, key_begin, key_end;  // chunk c covers keys key_begin + c * chunk_keys ... (< key_end)
+  float *dk_colsum, *dv_colsum;  // optional fp32 [H*64] accumulators: column sums of dk / dv = the bias gradients of the K / V
+                                 // projections (saves the column-sum pass over dqkv)
   long long dq_slab;
 };
+
+// Column sums over a warp's 32 rows of a [32 rows (lanes)] x [32 columns (registers)] tile: a butterfly reduce-scatter,
+// 31 shuffles; lane l returns the sum of column l.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = up ? v[i] : v[i + off], keep = up ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
 
 template <bool REL>
 __global__ void __launch_bounds__(NTHREADS, 1)
@@ -862,6 +879,17 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
               for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(ov_[g * 8 + e]);
               store8_bf16(a.dv + row + g * 8, v);
             }
+          }
+          if (a.dk_colsum != nullptr) {  // warp-uniform
+            float ck[32], cv[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              ck[e] = j < tk_c ? __uint_as_float(ok_[e]) : 0.f;
+              cv[e] = j < tk_c ? __uint_as_float(ov_[e]) : 0.f;
+            }
+            const float sk = warp_colsum32(ck, lane), sv = warp_colsum32(cv, lane);
+            atomicAdd(a.dk_colsum + h * DK + hs * 32 + lane, sk);
+            atomicAdd(a.dv_colsum + h * DK + hs * 32 + lane, sv);
           }
         }
       };
@@ -1215,7 +1243,7 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
                             void* dv_out, long long lddkv, void* d_ac, float drop_p, unsigned long long seed,
                             unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v,
                             float* dpos_accum, long long lddpos, int chunk_keys, long long dq_slab, int key_begin,
-                            int key_end, void* stream) {
+                            int key_end, float* dk_colsum, float* dv_colsum, void* stream) {
   // Tk = all keys of an utterance; this launch covers keys [key_begin, key_end) in chunks of chunk_keys (one work unit
   // each; [0, Tk) in one chunk for the plain form)
   B2_CHECK_ARG(B > 0 && H > 0, "relattn_bwd: empty problem");
@@ -1250,6 +1278,8 @@ static int relattn_bwd_impl(const void* d_ctx, long long lddo, const void* q_u, 
   a.lddq = lddq; a.lddkv = lddkv; a.ld_p = ld_p;
   a.dqv = (bf16*)dq_v; a.dpos = dpos_accum; a.lddpos = lddpos;
   a.nchunk = nchunk; a.chunk_keys = chunk_keys; a.kv_rows = Tk; a.dq_slab = dq_slab; a.key_begin = key_begin; a.key_end = key_end;
+  B2_CHECK_ARG((dk_colsum == nullptr) == (dv_colsum == nullptr), "relattn_bwd: dk_colsum and dv_colsum come together");
+  a.dk_colsum = dk_colsum; a.dv_colsum = dv_colsum;
   // [pd tile | dO | Q_u | V] [dS tile] [K, later Q_v] [position window].  The first group is dead once dQ_u / dK / dV are
   // issued: the skewed d(bd) tile is built over it (dS, its source, stays).  An M = 128 MN-major read over the last key /
   // window tile may run past the blocks that exist into the next region: never faulting (bounded below), never stored.
@@ -1333,7 +1363,7 @@ extern "C" int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void
                "relattn_bwd: supports d_k = 64, keys <= %d, rel-pos mode latest (Tq == Tk) or none (got Tq=%d Tk=%d mode=%d)", MAX_TK,
                Tq, Tk, relpos_mode);
   return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u, lddq, dk_out,
-                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, Tk, 0, 0, Tk, stream);
+                          dv_out, lddkv, d_ac, drop_p, seed, site, q_v, pos, ldpos, dq_v, dpos_accum, lddpos, Tk, 0, 0, Tk, nullptr, nullptr, stream);
 }
 
 extern "C" int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, const void* q_u, long long ldq, const void* k,
@@ -1342,10 +1372,11 @@ extern "C" int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, con
                                           float scale, void* dq_u_slabs, long long lddq, long long dq_slab, void* dk_out,
                                           void* dv_out, long long lddkv, float drop_p, unsigned long long seed, unsigned int site,
                                           const void* q_v, const void* pos, long long ldpos, void* dq_v_slabs, float* dpos_accum,
-                                          long long lddpos, int key_begin, int key_end, void* stream) {
+                                          long long lddpos, int key_begin, int key_end, float* dk_colsum_accum,
+                                          float* dv_colsum_accum, void* stream) {
   return relattn_bwd_impl(d_ctx, lddo, q_u, ldq, k, v, ldkv, p, ld_p, ctx, ldctx, B, H, Tq, Tk, relpos_mode, scale, dq_u_slabs, lddq,
                           dk_out, dv_out, lddkv, nullptr, drop_p, seed, site, q_v, pos, ldpos, dq_v_slabs, dpos_accum, lddpos,
-                          chunk_keys, dq_slab, key_begin, key_end, stream);
+                          chunk_keys, dq_slab, key_begin, key_end, dk_colsum_accum, dv_colsum_accum, stream);
 }
 
 // ----------------------------------------------------------------------------- key chunks -> one softmax

@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(256) pos_bias_fwd_kernel(const bf16* __restric
 // dq = dq_u + dq_v (written into the fused dqkv rows); du += colsum(dq_u); dv += colsum(dq_v)
 __global__ void __launch_bounds__(512, 1) pos_bias_bwd_kernel(const bf16* __restrict__ dqu, const bf16* __restrict__ dqv, int M,
                                                               int d, bf16* __restrict__ dq, long long lddq,
-                                                              float* __restrict__ du, float* __restrict__ dv) {
+                                                              float* __restrict__ du, float* __restrict__ dv,
+                                                              float* __restrict__ dbq) {
   __shared__ float red[2][CS_ROWS][CS_COLS + 1];
   const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
   const int g = blockIdx.x * CS_TX + tx;
@@ -155,6 +156,12 @@ __global__ void __launch_bounds__(512, 1) pos_bias_bwd_kernel(const bf16* __rest
   }
   colsum_block_reduce(au, red[0], tx, ty, d, du);
   colsum_block_reduce(av, red[1], tx, ty, d, dv);
+  if (dbq != nullptr) {  // colsum(dq) = colsum(dq_u) + colsum(dq_v): the q part of the fused projection's bias gradient
+#pragma unroll
+    for (int j = 0; j < 8; ++j) au[j] += av[j];
+    __syncthreads();  // red[0] has been read out by the first reduction
+    colsum_block_reduce(au, red[0], tx, ty, d, dbq);
+  }
 }
 
 // x[r, :] = dropout(emb[tok[r], :] * scale + pe[r % L, :])   (fp32 residual stream)
@@ -273,8 +280,8 @@ extern "C" int b200slu_pos_bias_fwd(const void* q, long long ldq, const float* p
   return 0;
 }
 
-extern "C" int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
-                                    float* dv_accum, void* stream) {
+extern "C" int b200slu_pos_bias_bwd_q(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
+                                      float* dv_accum, float* dq_colsum_accum, void* stream) {
   B2_CHECK_ARG(M > 0 && d % 8 == 0 && lddq % 8 == 0, "pos_bias_bwd: d and lddq must be multiples of 8");
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((d + CS_COLS - 1) / CS_COLS, 1);
@@ -282,9 +289,15 @@ extern "C" int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, i
   const int cap = (b2_num_sms() + grid.x - 1) / grid.x;  // one 512-thread block per SM
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * d);
-  pos_bias_bwd_kernel<<<grid, 512, 0, st>>>((const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum, dv_accum);
+  pos_bias_bwd_kernel<<<grid, 512, 0, st>>>((const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum, dv_accum,
+                                            dq_colsum_accum);
   B2_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
+                                    float* dv_accum, void* stream) {
+  return b200slu_pos_bias_bwd_q(dq_u, dq_v, M, d, dq, lddq, du_accum, dv_accum, nullptr, stream);
 }
 
 extern "C" int b200slu_embed_fwd(const float* emb, const int* tokens, const float* pe, int R, int L, int d, float scale, float* x,

@@ -213,10 +213,11 @@ def pos_bias_fwd(q, u, v):
     return qu, qv
 
 
-def pos_bias_bwd(dqu, dqv, dq_out, du, dv):
+def pos_bias_bwd(dqu, dqv, dq_out, du, dv, dq_colsum=None):
+    """dq = dqu + dqv; du += colsum(dqu); dv += colsum(dqv); dq_colsum (optional, f32 [d]) += colsum(dq)."""
     M, d = dqu.shape
-    check(_lib.lib().b200slu_pos_bias_bwd(ptr(dqu), ptr(dqv), M, d, ptr(dq_out), dq_out.stride(0), ptr(du), ptr(dv),
-                                          stream_ptr()), "pos_bias_bwd")
+    check(_lib.lib().b200slu_pos_bias_bwd_q(ptr(dqu), ptr(dqv), M, d, ptr(dq_out), dq_out.stride(0), ptr(du), ptr(dv),
+                                            ptr(dq_colsum), stream_ptr()), "pos_bias_bwd")
 
 
 def embed_fwd(emb, tokens, pe, L: int, scale: float, drop: Drop = None):
@@ -319,12 +320,14 @@ def relattn_bwd_supported(Tq: int, Tk: int, dk: int, mode: str) -> bool:
 
 
 def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: str, scale: float, dq, dk, dv,
-                drop: Drop = None, want_dac: bool = False, qv=None, pos=None, dqv=None, dpos=None):
+                drop: Drop = None, want_dac: bool = False, qv=None, pos=None, dqv=None, dpos=None, dk_colsum=None,
+                dv_colsum=None):
     """One kernel for the backward of the attention core (autograd through attention.py:78-95, :297-302 / :111-113, rel_shift
     :240-263).  dctx, qu, ctx [B*Tq, H*64], k, v [B*Tk, H*64], p bf16 [H,B,Tq,round8(Tk)] (as saved by the forward); writes
     dq [B*Tq, H*64], dk, dv [B*Tk, H*64] (views with their own row strides are fine).  Mode "latest": qv, pos (projected
     positions [2T-1, H*64]) in, dqv (row stride of dq) out, dpos (f32 [2T-1, H*64]) ACCUMULATED.  want_dac: also return dS
-    (bf16, shifted layout [H,B,Tq,round8(Tk)]).  More than 192 keys: one launch per key chunk, dq / dqv summed over them."""
+    (bf16, shifted layout [H,B,Tq,round8(Tk)]).  More than 192 keys: one launch per key chunk, dq / dqv summed over them.
+    dk_colsum / dv_colsum (f32 [H*64], accumulated): column sums of dk / dv = the K / V projections' bias gradients."""
     ld = p.shape[-1]
     L = _lib.lib()
     dp, seed, site = _drop(drop)
@@ -334,6 +337,14 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: 
         assert qv.stride(0) == qu.stride(0) and dqv.stride(0) == dq.stride(0) and dpos.dtype == torch.float32
     ldpos = pos.stride(0) if pos is not None else 0
     lddpos = dpos.stride(0) if dpos is not None else 0
+    if Tk <= CHUNK_KEYS and dk_colsum is not None:
+        assert not want_dac and dv_colsum is not None
+        check(L.b200slu_relattn_bwd_chunks(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
+                                           ptr(ctx), ctx.stride(0), B, H, Tq, Tk, Tk, rel, scale, ptr(dq), dq.stride(0), 0,
+                                           ptr(dk), ptr(dv), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos, ptr(dqv),
+                                           ptr(dpos), lddpos, 0, Tk, ptr(dk_colsum), ptr(dv_colsum), stream_ptr()),
+              "relattn_bwd_chunks")
+        return None
     if Tk <= CHUNK_KEYS:
         dac = torch.empty_like(p) if want_dac else None
         check(L.b200slu_relattn_bwd(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
@@ -353,7 +364,8 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: 
         check(L.b200slu_relattn_bwd_chunks(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
                                            ptr(ctx), ctx.stride(0), B, H, Tq, Tk, ck, rel, scale, ptr(dqc[0, c0]), d,
                                            B * Tq * d, ptr(dk), ptr(dv), dk.stride(0), dp, seed, site, ptr(qv), ptr(pos), ldpos,
-                                           ptr(dqc[1, c0]) if rel else None, ptr(dpos), lddpos, begin, end, stream_ptr()),
+                                           ptr(dqc[1, c0]) if rel else None, ptr(dpos), lddpos, begin, end, ptr(dk_colsum),
+                                           ptr(dv_colsum), stream_ptr()),
               "relattn_bwd_chunks")
     check(L.b200slu_sum_chunks_bf16(ptr(dqc[0]), B * Tq * d, d, len(chunks), B * Tq, d, ptr(dq), dq.stride(0), stream_ptr()), "sum_chunks")
     if rel:

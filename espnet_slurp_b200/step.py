@@ -214,8 +214,10 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
         # gradient of the projected positions come out of ONE kernel
         dqu = torch.empty(B * T, d, device=x.device, dtype=dc.dtype)
         dqv = torch.empty_like(dqu)
+        # ... and the K / V parts of linear_qkv's bias gradient (column sums of dk, dv) on the way out of tensor memory
+        gb = G[a + ".linear_qkv.bias"]
         K.relattn_bwd(dc, qu, k, v, pr, c, B, T, T, H, cfg.rel_pos_type, scale, dqu, dqkv[:, d:2 * d], dqkv[:, 2 * d:], drop=da,
-                      qv=qv, pos=pp, dqv=dqv, dpos=dpp)
+                      qv=qv, pos=pp, dqv=dqv, dpos=dpp, dk_colsum=gb[d:2 * d], dv_colsum=gb[2 * d:])
     else:
         dpd = K.attn_f1(dc, v, B, T, T, H)
         K.attn_f3(pd, dc, B, T, T, H, out=dqkv[:, 2 * d:])
@@ -225,8 +227,12 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
         dqv = K.attn_f2(dbd, pp, B, T, Pn, H, y_bcast=True)
         K.attn_f4(dbd, qv, B, T, Pn, H, dpp)
     K.gemm(K.cast_bf16(dpp), pos16, trans=True, out=G[a + ".linear_pos.weight"], accumulate=True)
-    K.pos_bias_bwd(dqu, dqv, dqkv[:, :d], G[a + ".pos_bias_u"].reshape(-1), G[a + ".pos_bias_v"].reshape(-1))
-    K.colsum(dqkv, G[a + ".linear_qkv.bias"])
+    if fb:  # colsum(dq) = colsum(dq_u) + colsum(dq_v) comes with the position-bias gradients: no pass over dqkv
+        K.pos_bias_bwd(dqu, dqv, dqkv[:, :d], G[a + ".pos_bias_u"].reshape(-1), G[a + ".pos_bias_v"].reshape(-1),
+                       dq_colsum=G[a + ".linear_qkv.bias"][:d])
+    else:
+        K.pos_bias_bwd(dqu, dqv, dqkv[:, :d], G[a + ".pos_bias_u"].reshape(-1), G[a + ".pos_bias_v"].reshape(-1))
+        K.colsum(dqkv, G[a + ".linear_qkv.bias"])
     K.gemm(dqkv, ln, trans=True, out=G[a + ".linear_qkv.weight"], accumulate=True)
     dln = K.gemm(dqkv, W[a + ".linear_qkv.weight"], trans_b=True)
     return _ln_bwd(dln, x, P, G, norm, st, dy, nxt)

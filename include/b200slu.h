@@ -155,6 +155,9 @@ int b200slu_pos_bias_fwd(const void* q, long long ldq, const float* pos_bias_u, 
                          void* q_u, void* q_v, void* stream);
 int b200slu_pos_bias_bwd(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
                          float* dv_accum, void* stream);
+/* the same, also accumulating colsum(dq) = colsum(dq_u) + colsum(dq_v) (the q part of linear_q's bias gradient) */
+int b200slu_pos_bias_bwd_q(const void* dq_u, const void* dq_v, int M, int d, void* dq, long long lddq, float* du_accum,
+                           float* dv_accum, float* dq_colsum_accum, void* stream);
 /* decoder input: x = dropout(emb[tok] * scale + pe[pos]) (transformer_decoder.py:72-77, embedding.py:82-94) */
 int b200slu_embed_fwd(const float* emb, const int* tokens, const float* pe, int R, int L, int d, float scale, float* x,
                       float drop_p, unsigned long long seed, unsigned int site, void* stream);
@@ -211,7 +214,10 @@ int b200slu_relattn_bwd(const void* d_ctx, long long lddo, const void* q_u, long
  * head), chunk_keys and key_begin multiples of 64 -- a short last chunk gets its own launch with a smaller chunk_keys so
  * that it does not pay for 192 keys; k, v, p, dk, dv are the whole tensors, the slab pointers those of the launch's first chunk): p = the combined probabilities, ctx = the combined context (for delta =
  * <dO, O>); dk, dv are final, dq_u / dq_v come out as one slab per chunk, dq_slab elements apart (sum them with
- * b200slu_sum_chunks_bf16); dpos_accum accumulates over the chunks like over the utterances. */
+ * b200slu_sum_chunks_bf16); dpos_accum accumulates over the chunks like over the utterances.  dk_colsum_accum /
+ * dv_colsum_accum (optional, fp32 [H*64], accumulated): the column sums of dk / dv over all rows, i.e. the bias gradients of
+ * the K and V projections, taken from the fp32 accumulators on their way out (also valid with ONE chunk of Tk <= 192 keys:
+ * chunk_keys = Tk, key range [0, Tk), dq_slab = 0). */
 int b200slu_relattn_chunk_supported(int Tq, int Tk_chunk, int dk, int relpos_mode);
 int b200slu_relattn_fwd_chunk(const void* qu, const void* qv, long long ldq, const void* k, const void* v, long long ldkv,
                               const void* pos, long long ldpos, const int* key_lens, int B, int H, int Tq, int Tk_chunk,
@@ -225,7 +231,8 @@ int b200slu_relattn_bwd_chunks(const void* d_ctx, long long lddo, const void* q_
                                int Tk, int chunk_keys, int relpos_mode, float scale, void* dq_u_slabs, long long lddq,
                                long long dq_slab, void* dk, void* dv, long long lddkv, float drop_p, unsigned long long seed,
                                unsigned int site, const void* q_v, const void* pos, long long ldpos, void* dq_v_slabs,
-                               float* dpos_accum, long long lddpos, int key_begin, int key_end, void* stream);
+                               float* dpos_accum, long long lddpos, int key_begin, int key_end, float* dk_colsum_accum,
+                               float* dv_colsum_accum, void* stream);
 int b200slu_sum_chunks_bf16(const void* src, long long chunk_stride, long long ld_src, int nchunk, long long rows, int cols,
                             void* dst, long long ld_dst, void* stream);
 /* d(matrix_bd) [H,B,T,ld_bd] (un-shifted) from d(scores) [H,B,T,ld_p] (shifted): the scatter of rel_shift's backward

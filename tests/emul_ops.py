@@ -182,10 +182,12 @@ def pos_bias_fwd(q, u, v):
     return _r(q.float() + u), _r(q.float() + v)
 
 
-def pos_bias_bwd(dqu, dqv, dq_out, du, dv):
+def pos_bias_bwd(dqu, dqv, dq_out, du, dv, dq_colsum=None):
     dq_out.copy_((dqu.float() + dqv.float()).to(dq_out.dtype))
     du += dqu.float().sum(0)
     dv += dqv.float().sum(0)
+    if dq_colsum is not None:
+        dq_colsum += dqu.float().sum(0) + dqv.float().sum(0)
 
 
 def embed_fwd(emb, tokens, pe, L, scale, drop=None):
@@ -274,7 +276,7 @@ def relattn_bwd_supported(Tq, Tk, dk, mode):
 
 
 def relattn_bwd(dctx, qu, k, v, p, ctx, B, Tq, Tk, H, mode, scale, dq, dk, dv, drop=None, want_dac=False, qv=None, pos=None,
-                dqv=None, dpos=None):
+                dqv=None, dpos=None, dk_colsum=None, dv_colsum=None):
     """the fused backward = the unfused chain: dPd = dO v^T, dS = p (m dPd - <dO, O>) scale, dq = dS k, dk = dS^T q, dv = pd^T dO,
     and in rel-pos mode d(bd) = unshift(dS), dq_v = d(bd) pos, dpos += d(bd)^T q_v"""
     dpd = attn_f1(dctx, v, B, Tq, Tk, H)
@@ -291,6 +293,9 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B, Tq, Tk, H, mode, scale, dq, dk, dv, d
     attn_f2(ds, k, B, Tq, Tk, H, out=dq)
     attn_f3(ds, qu, B, Tq, Tk, H, out=dk)
     attn_f3(_r(pd), dctx, B, Tq, Tk, H, out=dv)
+    if dk_colsum is not None:  # from the fp32 accumulators in the kernel; here from the rounded rows (bf16-level difference)
+        dk_colsum += dk.float().sum(0)
+        dv_colsum += dv.float().sum(0)
     if mode == "latest":
         Pn = pos.shape[0]
         dbd = rel_unshift(ds, Tq, mode, round8(Pn))

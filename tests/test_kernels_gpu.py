@@ -231,7 +231,7 @@ def test_fused_attention_fwd(mode, causal, Tq, Tk):
 
 @pytest.mark.parametrize("drop", [None, (0.1, 99, 5)])
 @pytest.mark.parametrize("mode,Tq,Tk", [("latest", 300, 300), ("latest", 193, 193), ("latest", 468, 468), ("none", 37, 430),
-                                        ("none", 130, 385), ("latest", 384, 384)])
+                                        ("none", 130, 385), ("latest", 384, 384), ("latest", 155, 155), ("none", 21, 99)])
 def test_fused_attention_key_chunks(mode, Tq, Tk, drop):
     """More than 192 keys: one launch of the fused forward / backward per 192-key chunk + the combine pass, against the
     statement of the unfused chain over the whole key axis (same dropout decisions: the chunk offset enters the counter)."""
@@ -262,9 +262,10 @@ def test_fused_attention_key_chunks(mode, Tq, Tk, drop):
     dkv = torch.full((B * Tk, 2 * d), 7.0, device="cuda", dtype=BF)
     dqv = torch.full((B * Tq, 3 * d), 7.0, device="cuda", dtype=BF) if rel else None
     dpos = torch.ones(Pn, d, device="cuda") if rel else None
+    cks, cvs = torch.ones(d, device="cuda"), torch.ones(d, device="cuda")   # bias gradients of the K / V projections, accumulated
     K().relattn_bwd(dctx.cuda(), qu_c, kv_c[:, :d], kv_c[:, d:], p, ctx, B, Tq, Tk, H, mode, 0.125, dq[:, d:2 * d], dkv[:, :d], dkv[:, d:],
                     drop=drop, qv=qv.cuda() if rel else None, pos=pos.cuda() if rel else None, dqv=dqv[:, d:2 * d] if rel else None,
-                    dpos=dpos)
+                    dpos=dpos, dk_colsum=cks, dv_colsum=cvs)
     torch.cuda.synchronize()
     wdq, wdk, wdv = torch.zeros(B * Tq, d), torch.zeros(B * Tk, d), torch.zeros(B * Tk, d)
     wdqv, wdpos = (torch.zeros(B * Tq, d), torch.ones(Pn, d)) if rel else (None, None)
@@ -274,6 +275,8 @@ def test_fused_attention_key_chunks(mode, Tq, Tk, drop):
     close(dkv[:, :d], wdk, 2e-2, "dk")
     close(dkv[:, d:], wdv, 2e-2, "dv")
     assert (dq[:, :d] == 7.0).all() and (dq[:, 2 * d:] == 7.0).all()
+    close(cks, 1.0 + wdk.sum(0), 2e-2, "colsum(dk)")
+    close(cvs, 1.0 + wdv.sum(0), 2e-2, "colsum(dv)")
     if rel:
         close(dqv[:, d:2 * d], wdqv, 2e-2, "dq_v")
         close(dpos, wdpos, 2e-2, "d(projected positions)")
