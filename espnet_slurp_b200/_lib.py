@@ -92,6 +92,7 @@ _SIGNATURES = {
     "b200slu_rel_shift_index": [_I, _I, _I, _I],
     "b200slu_glu_dwconv_fwd": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P],
     "b200slu_glu_dwconv_bwd": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P],
+    "b200slu_glu_dwconv_bwd_b": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200slu_bn_finalize": [_P, _I, _L, _F, _F, _P, _P, _P, _P, _P],
     "b200slu_bn_swish_fwd": [_P, _P, _P, _P, _L, _I, _P, _P],
     "b200slu_bn_swish_bwd": [_P, _P, _P, _P, _P, _L, _I, _P, _P, _P, _P, _P],

@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(256, 2) glu_dw_fwd_kernel(const bf16* __restri
   {
     float* wt = dyn_smem;
     const int nw = min(CC, C - c0) * K;
-    constexpr int WU = (CC * KMAX + 255) / 256;
+    constexpr int WU = (CC * KMAX + 455) / 256;
     float tmp[WU];
 #pragma unroll
     for (int u = 0; u < WU; ++u) {  // all loads in flight before the first store
@@ -243,22 +243,22 @@ template <int TT, int KT>
 __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict__ d_dw, const bf16* __restrict__ pw1,
                                                          const float* __restrict__ w, int B, int T, int C, int Krt,
                                                          bf16* __restrict__ d_pw1, float* __restrict__ dw_accum,
-                                                         float* __restrict__ dbias_accum) {
+                                                         float* __restrict__ dbias_accum, float* __restrict__ dpw1_colsum) {
   extern __shared__ __align__(16) float dyn_smem[];
   float (*sg)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                             // glu halo tile  [TT+KMAX-1][CC]
   float (*sd)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + (TT + KMAX - 1) * CC);      // d_dw halo tile
   // dW partial (+ dbias); rows padded to an odd stride so that the 32 channels of a warp hit 32 different banks
-  float (*swg)[KMAX + 2] = reinterpret_cast<float (*)[KMAX + 2]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);
+  float (*swg)[KMAX + 4] = reinterpret_cast<float (*)[KMAX + 4]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);
   // reversed taps [KMAX][CC]: swr[m][ch] = w[ch][K-1-m] (0 for m >= K); re-read per tile so that the staging phase has the
   // whole register file for its loads in flight
-  float (*swr)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + 2 * (TT + KMAX - 1) * CC + CC * (KMAX + 2));
+  float (*swr)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + 2 * (TT + KMAX - 1) * CC + CC * (KMAX + 4));
   const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
   const int pad = (K - 1) / 2;
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;
   const int c = c0 + cl;
   const int ntt = (T + TT - 1) / TT;
-  for (int it = threadIdx.x; it < CC * (KMAX + 2); it += blockDim.x) (&swg[0][0])[it] = 0.f;
+  for (int it = threadIdx.x; it < CC * (KMAX + 4); it += blockDim.x) (&swg[0][0])[it] = 0.f;
   for (int it = threadIdx.x; it < KMAX * CC; it += blockDim.x) {
     const int m = it / CC, ch = it - m * CC;
     swr[m][ch] = (c0 + ch < C && m < K) ? w[(c0 + ch) * K + (K - 1 - m)] : 0.f;
@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
        wrev[k] = swr[k][cl];
        acc[k] = 0.f;
      }
-     float accb = 0.f;
+     float accb = 0.f, acca = 0.f, accg = 0.f;  // column sums of d_dw (depthwise bias) and of the two halves of d_pw1 (pw1's bias)
 #pragma unroll 1
      for (int sub = 0; sub < TT / (4 * FR1); ++sub) {
       const int f0 = sub * 4 * FR1 + fr * FR1;
@@ -321,8 +321,11 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
           const float a = __bfloat162float(pa[o]), gt = __bfloat162float(pg[o]);
           const float sgm = sigmoidf_(gt);
           bf16* drow = d_pw1 + ((long long)b * T + t) * (2 * C);
-          drow[c] = __float2bfloat16(dg[o] * sgm);
-          drow[C + c] = __float2bfloat16(dg[o] * a * sgm * (1.f - sgm));
+          const float da = dg[o] * sgm, dgate = dg[o] * a * sgm * (1.f - sgm);
+          drow[c] = __float2bfloat16(da);
+          drow[C + c] = __float2bfloat16(dgate);
+          acca += da;
+          accg += dgate;
         }
       }
      }
@@ -331,6 +334,10 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
      for (int k = 0; k < KMAX; ++k)
        if (k < K) atomicAdd(&swg[cl][k], acc[k]);
      atomicAdd(&swg[cl][KMAX], accb);
+     if (dpw1_colsum != nullptr) {
+       atomicAdd(&swg[cl][KMAX + 1], acca);
+       atomicAdd(&swg[cl][KMAX + 2], accg);
+     }
     }
   }
   __syncthreads();
@@ -338,7 +345,13 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
     const int ch = it / K, k = it - ch * K;
     if (c0 + ch < C) atomicAdd(dw_accum + (long long)(c0 + ch) * K + k, swg[ch][k]);
   }
-  if (threadIdx.x < CC && c0 + threadIdx.x < C) atomicAdd(dbias_accum + c0 + threadIdx.x, swg[threadIdx.x][KMAX]);
+  if (threadIdx.x < CC && c0 + threadIdx.x < C) {
+    atomicAdd(dbias_accum + c0 + threadIdx.x, swg[threadIdx.x][KMAX]);
+    if (dpw1_colsum != nullptr) {  // bias gradient of pointwise_conv1 = column sums of d_pw1: no separate pass over it
+      atomicAdd(dpw1_colsum + c0 + threadIdx.x, swg[threadIdx.x][KMAX + 1]);
+      atomicAdd(dpw1_colsum + C + c0 + threadIdx.x, swg[threadIdx.x][KMAX + 2]);
+    }
+  }
 }
 
 // BatchNorm1d training statistics: mean / rstd from the fp32 sums, running-stat update (momentum,
@@ -574,8 +587,15 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
   return 0;
 }
 
+extern "C" int b200slu_glu_dwconv_bwd_b(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
+                                        float* dw_accum, float* dbias_accum, float* dpw1_colsum_accum, void* stream);
 extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
                                       float* dw_accum, float* dbias_accum, void* stream) {
+  return b200slu_glu_dwconv_bwd_b(d_out, pw1, w, B, T, C, K, d_pw1, dw_accum, dbias_accum, nullptr, stream);
+}
+
+extern "C" int b200slu_glu_dwconv_bwd_b(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
+                                        float* dw_accum, float* dbias_accum, float* dpw1_colsum_accum, void* stream) {
   B2_CHECK_ARG(B > 0 && T > 0 && C % 8 == 0 && K % 2 == 1 && K <= KMAX, "glu_dwconv_bwd: C %% 8 == 0, odd K <= %d", KMAX);
   B2_CHECK_ARG(B <= 65535, "glu_dwconv_bwd: B too large");
   cudaStream_t st = (cudaStream_t)stream;
@@ -585,7 +605,7 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                                 \
     int gy = (dw_blocks_per_sm() * b2_num_sms() + ctiles - 1) / ctiles;                                                      \
     if (gy > units) gy = units;                                                                                              \
-    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 2) + KMAX * CC) * sizeof(float);                               \
+    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 4) + KMAX * CC) * sizeof(float);                               \
     auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
     static unsigned long long cfg = 0;                                                                                                 \
     if (!b2_device_done(cfg)) {                                                                                                              \
@@ -593,7 +613,7 @@ extern "C" int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const 
       b2_device_mark(cfg);                                                                                                            \
     }                                                                                                                        \
     kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,  \
-                                              dbias_accum);                                                                  \
+                                              dbias_accum, dpw1_colsum_accum);                                               \
   } while (0)
   if (K == 31) {
     const int tt = dw_tile_frames(T, false);

@@ -392,11 +392,12 @@ def glu_dwconv_fwd(pw1, w, bias, B: int, T: int, K: int):
     return out, sums
 
 
-def glu_dwconv_bwd(d_out, pw1, w, B: int, T: int, K: int, dw, dbias):
+def glu_dwconv_bwd(d_out, pw1, w, B: int, T: int, K: int, dw, dbias, dpw1_colsum=None):
+    """... dpw1_colsum (optional, f32 [2C], accumulated): column sums of d_pw1 = pointwise_conv1's bias gradient."""
     Cc = pw1.shape[1] // 2
     d_pw1 = torch.empty(B * T, 2 * Cc, device=pw1.device, dtype=torch.bfloat16)
-    check(_lib.lib().b200slu_glu_dwconv_bwd(ptr(d_out), ptr(pw1), ptr(w), B, T, Cc, K, ptr(d_pw1), ptr(dw), ptr(dbias),
-                                            stream_ptr()), "glu_dwconv_bwd")
+    check(_lib.lib().b200slu_glu_dwconv_bwd_b(ptr(d_out), ptr(pw1), ptr(w), B, T, Cc, K, ptr(d_pw1), ptr(dw), ptr(dbias),
+                                              ptr(dpw1_colsum), stream_ptr()), "glu_dwconv_bwd")
     return d_pw1
 
 

@@ -277,9 +277,9 @@ def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: i
     ddw = K.bn_swish_bwd(dbs, dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"], G[cm + ".norm.weight"],
                          G[cm + ".norm.bias"])
     wdw = P[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel)
+    # ... which also accumulates pointwise_conv1's bias gradient (the column sums of d_pw1)
     dpw1 = K.glu_dwconv_bwd(ddw, pw1, wdw, B, T, cfg.kernel, G[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel),
-                            G[cm + ".depthwise_conv.bias"])
-    K.colsum(dpw1, G[cm + ".pointwise_conv1.bias"])
+                            G[cm + ".depthwise_conv.bias"], dpw1_colsum=G[cm + ".pointwise_conv1.bias"])
     K.gemm(dpw1, ln, trans=True, out=G[cm + ".pointwise_conv1.weight"], accumulate=True)
     dln = K.gemm(dpw1, W[cm + ".pointwise_conv1.weight"], trans_b=True)
     return _ln_bwd(dln, x, P, G, norm, st, dy, nxt)

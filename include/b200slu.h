@@ -248,6 +248,9 @@ int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const float* bias, i
                            float* bn_sums_zeroed /* [2C] */, void* stream);
 int b200slu_glu_dwconv_bwd(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
                            float* dw_accum, float* dbias_accum, void* stream);
+/* the same, also accumulating the column sums of d_pw1 (fp32 [2C]) = the bias gradient of pointwise_conv1 */
+int b200slu_glu_dwconv_bwd_b(const void* d_out, const void* pw1, const float* w, int B, int T, int C, int K, void* d_pw1,
+                             float* dw_accum, float* dbias_accum, float* dpw1_colsum_accum, void* stream);
 int b200slu_bn_finalize(const float* sums, int C, long long n, float eps, float momentum, float* mean_rstd /* [2C] */,
                         float* running_mean, float* running_var, long long* num_batches_tracked, void* stream);
 int b200slu_bn_swish_fwd(const void* x, const float* mean_rstd, const float* gamma, const float* beta, long long M, int C,

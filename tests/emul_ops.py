@@ -319,7 +319,7 @@ def glu_dwconv_fwd(pw1, w, bias, B, T, K):
     return _r(y), torch.cat([y.sum(0), (y * y).sum(0)])
 
 
-def glu_dwconv_bwd(d_out, pw1, w, B, T, K, dw, dbias):
+def glu_dwconv_bwd(d_out, pw1, w, B, T, K, dw, dbias, dpw1_colsum=None):
     C = pw1.shape[1] // 2
     x = pw1.float().reshape(B, T, 2 * C).requires_grad_(True)
     wl = w.detach().clone().reshape(C, 1, K).requires_grad_(True)
@@ -329,6 +329,8 @@ def glu_dwconv_bwd(d_out, pw1, w, B, T, K, dw, dbias):
     y.backward(d_out.float())
     dw += wl.grad.reshape(dw.shape)
     dbias += bl.grad
+    if dpw1_colsum is not None:
+        dpw1_colsum += x.grad.reshape(B * T, 2 * C).sum(0)
     return _r(x.grad.reshape(B * T, 2 * C))
 
 

@@ -374,10 +374,12 @@ def test_conv_module_middle(B, T, C, Kk):
     close(dg, wg, 1e-3, "bn dgamma")
     close(db, wb, 1e-3, "bn dbeta")
     dwg, dbg = torch.zeros(C, Kk, device="cuda"), torch.zeros(C, device="cuda")
-    dpw1 = K().glu_dwconv_bwd(dy.cuda(), pw1.cuda(), w.cuda(), B, T, Kk, dwg, dbg)
-    wdw, wdb = torch.zeros(C, Kk), torch.zeros(C)
-    wdpw1 = E.glu_dwconv_bwd(dy, pw1, w, B, T, Kk, wdw, wdb)
+    dps = torch.ones(2 * C, device="cuda")   # pointwise_conv1's bias gradient, accumulated
+    dpw1 = K().glu_dwconv_bwd(dy.cuda(), pw1.cuda(), w.cuda(), B, T, Kk, dwg, dbg, dpw1_colsum=dps)
+    wdw, wdb, wps = torch.zeros(C, Kk), torch.zeros(C), torch.ones(2 * C)
+    wdpw1 = E.glu_dwconv_bwd(dy, pw1, w, B, T, Kk, wdw, wdb, dpw1_colsum=wps)
     close(dpw1, wdpw1, 1e-2, "d_pw1")
+    close(dps, wps, 1e-3, "colsum(d_pw1)")
     close(dwg, wdw, 1e-3, "d_dw_weight")
     close(dbg, wdb, 1e-3, "d_dw_bias")
 
