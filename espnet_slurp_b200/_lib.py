@@ -33,6 +33,7 @@ class Epilogue(C.Structure):
         ("ld_residual", C.c_longlong),
         ("out_f32", C.c_int),
         ("accumulate", C.c_int),
+        ("out_colsum_accum", C.c_void_p),
     ]
 
 

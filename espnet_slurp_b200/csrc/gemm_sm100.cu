@@ -58,6 +58,7 @@ struct EpiArgs {
   long long* dbg_out;
   B2Dropout drop;
   ConvArgs cv;
+  float* colsum;  // EF_COLSUM: fp32 [N] += column sums of the bf16 output
 };
 
 // Epilogue feature bits.  A kernel instantiated with EF != EF_GENERIC has its epilogue resolved at compile time: the
@@ -65,7 +66,7 @@ struct EpiArgs {
 // load-constant / test / branch decisions per feature does not fit into (measured: 840 cycles per slice).
 enum : uint32_t {
   EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
-  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_SCATTER = 8192u, EF_GENERIC = 1u << 31
+  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_SCATTER = 8192u, EF_COLSUM = 16384u, EF_GENERIC = 1u << 31
 };
 // Epilogue warps: 2 per TMEM lane quadrant for the register-heavy epilogues (168 registers each).
 // 16 warps (4 per quadrant, 64 columns each) halve the epilogue time of the light epilogues (bias-only: 6500 -> 3300
@@ -657,6 +658,28 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           fence_async_smem();  // generic-proxy writes of every lane -> visible to the async proxy
           __syncwarp();
           const int bcol = (F & EF_F32) ? c0c : c0c - 32;  // first column of the box
+          if (F & EF_COLSUM) {
+            // column sums of the staged 32 x 64 bf16 box: lane l owns columns 2l, 2l+1 (16-byte chunk l / 4 of every row,
+            // XOR-swizzled with the row: the 32 lanes of a load hit 32 different banks); rows past M hold stale data
+            const int nrows = min(32, M - row0);
+            const uint32_t cbase = so + (uint32_t)(lane & 3) * 4u;
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int rr = 0; rr < 32; ++rr) {
+              if (rr < nrows) {
+                uint32_t w;
+                asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(cbase + (uint32_t)rr * 128u + ((((uint32_t)lane >> 2) ^ (uint32_t)(rr & 7)) << 4)));
+                const float2 f2 = unpack_bf16x2(w);
+                s0 += f2.x;
+                s1 += f2.y;
+              }
+            }
+            const int col = bcol + 2 * lane;
+            if (col < N && nrows > 0) {
+              atomicAdd(ep.colsum + col, s0);
+              atomicAdd(ep.colsum + col + 1, s1);
+            }
+          }
           if (lane == 0) {
             if (bcol < N && row0 < M) {
               if (F & EF_ACC) tma_reduce_add_4d(&map_c, so, bcol, row0, bi, bo);
@@ -835,6 +858,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     ep.out_f32 = e->out_f32;
     ep.accumulate = e->accumulate;
     ep.drop = b2_make_drop(e->dropout_p, e->dropout_seed, e->dropout_site);
+    ep.colsum = e->out_colsum_accum;
     ep.debug = gemm_debug_env();
   }
   {
@@ -850,6 +874,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     if (ep.res != nullptr) f |= EF_RES;
     if (ep.out_f32) f |= EF_F32;
     if (ep.accumulate) f |= EF_ACC;
+    if (ep.colsum != nullptr) f |= EF_COLSUM;
     // residual boxes through TMA (specialised fp32-output kernels only): whole 32-column boxes, 16-byte aligned rows
     static const bool res_tma_off = getenv("B200SLU_GEMM_RES_TMA") && atoi(getenv("B200SLU_GEMM_RES_TMA")) == 0;  // tuning only
     if ((f & EF_RES) && (f & EF_F32) && !(f & (EF_ACC | EF_DACT)) && nbatch == 1 && N % 32 == 0 && ep.ldres % 4 == 0 &&
@@ -863,6 +888,8 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
                "gemm: batched mode supports only bias / activation / alpha epilogues");
   B2_CHECK_ARG(!(ep.drop.p > 0.f) || N % 8 == 0, "gemm: dropout epilogue needs N %% 8 == 0");
   B2_CHECK_ARG(!ep.accumulate || ep.out_f32, "gemm: accumulate needs fp32 output");
+  B2_CHECK_ARG(ep.colsum == nullptr || (!ep.out_f32 && N % 64 == 0 && nbatch == 1 && ep.pre_out == nullptr),
+               "gemm: out_colsum_accum needs an unbatched bf16 output with N %% 64 == 0 and no act_grad_out");
   B2_CHECK_ARG(ep.pre_out == nullptr || (!ep.out_f32 && g->ldc % 8 == 0 && ((uintptr_t)ep.pre_out % 16) == 0),
                "gemm: act_grad_out needs a bf16 output and shares its row stride");
   const int vec = ep.out_f32 ? 4 : 8;
@@ -978,6 +1005,7 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
       if (!dbg_generic) {
         B2_CASE(256, 3, false, true, 0u);
         B2_CASE(256, 3, false, true, EF_AUX_MUL);
+        B2_CASE(256, 3, false, true, EF_AUX_MUL | EF_COLSUM);
         B2_CASE(256, 3, false, true, EF_AUX_RELU);
         B2_CASE(256, 3, false, true, EF_RES | EF_F32);
         B2_CASE(256, 3, false, true, EF_RES | EF_F32 | EF_RES_TMA);

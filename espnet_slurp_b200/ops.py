@@ -35,7 +35,7 @@ def round8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
-def _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre_act_out, out, accumulate, drop):
+def _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre_act_out, out, accumulate, drop, colsum_out=None):
     ep = Epilogue()
     ep.bias = ptr(bias)
     ep.act = ACT[act]
@@ -52,6 +52,9 @@ def _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre_act_out,
         ep.ld_residual = residual.stride(0)
     ep.out_f32 = 1 if out.dtype == torch.float32 else 0
     ep.accumulate = 1 if accumulate else 0
+    if colsum_out is not None:
+        assert colsum_out.dtype == torch.float32 and out.dtype == torch.bfloat16
+        ep.out_colsum_accum = colsum_out.data_ptr()
     return ep
 
 
@@ -60,12 +63,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans: bool = False, trans_a: Opti
          alpha: float = 1.0, residual: Optional[torch.Tensor] = None, act_grad_input: Optional[torch.Tensor] = None,
          act_grad: Optional[str] = None, act_grad_out=False, out_dtype=torch.bfloat16,
          out: Optional[torch.Tensor] = None, accumulate: bool = False, drop: Drop = None,
-         dropout_p: float = 0.0, seed: int = 0, site: int = 0):
+         dropout_p: float = 0.0, seed: int = 0, site: int = 0, colsum_out: Optional[torch.Tensor] = None):
     """C[M,N] = op(A) op(B)^T with the fused epilogue of b200slu_epilogue_t.
 
     trans_a=False: a is [M,K]; True: a is [K,M].  trans_b=False: b is [N,K]; True: b is [K,N].
     (``trans`` sets both.)  ``act_grad_out`` (True = allocate, or a bf16 [M,N] tensor) receives act'(y) times the
     element's dropout multiplier; feed it back as ``act_grad_input`` with ``act_grad="mul"`` in the dgrad GEMM.
+    ``colsum_out`` (f32 [N], accumulated): column sums of the bf16 output, from the epilogue's staged tiles.
     """
     pre_act_out = act_grad_out
     ta = trans if trans_a is None else trans_a
@@ -86,7 +90,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, trans: bool = False, trans_a: Opti
         assert pre.stride(0) == out.stride(0)
     if drop is None and dropout_p > 0.0:
         drop = (dropout_p, seed, site)
-    ep = _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre, out, accumulate, drop)
+    ep = _epilogue(bias, act, alpha, residual, act_grad_input, act_grad, pre, out, accumulate, drop, colsum_out)
     g = GemmDesc()
     g.trans_a, g.trans_b = int(ta), int(tb)
     g.M, g.N, g.K = M, N, K

@@ -159,8 +159,12 @@ def ffn_bwd(dy, saved, P, W, G, g=None, nxt=None):
     x, ln, st, hpre, h, d1, d2, pre, norm, act, scale = saved
     g = _head_g(dy, g, (scale, d2, G[pre + ".w_2.bias"]))
     K.gemm(g, h, trans=True, out=G[pre + ".w_2.weight"], accumulate=True)
-    dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad="mul")  # hpre = act' * dropout mask
-    K.colsum(dh, G[pre + ".w_1.bias"])
+    # hpre = act' * dropout mask; w_1's bias gradient = the column sums of dh, taken from the epilogue's staged tiles
+    fuse = hpre.shape[1] % 64 == 0  # (whole 64-column boxes; the tiny fixtures take the separate pass)
+    dh = K.gemm(g, W[pre + ".w_2.weight"], trans_b=True, act_grad_input=hpre, act_grad="mul",
+                colsum_out=G[pre + ".w_1.bias"] if fuse else None)
+    if not fuse:
+        K.colsum(dh, G[pre + ".w_1.bias"])
     K.gemm(dh, ln, trans=True, out=G[pre + ".w_1.weight"], accumulate=True)
     dln = K.gemm(dh, W[pre + ".w_1.weight"], trans_b=True)
     return _ln_bwd(dln, x, P, G, norm, st, dy, nxt)

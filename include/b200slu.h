@@ -98,6 +98,9 @@ typedef struct {
   long long ld_residual;
   int out_f32;
   int accumulate;
+  float* out_colsum_accum; /* optional f32 [N]: += column sums of the (bf16-rounded) output C -- the bias gradient of the
+                              Linear whose dY this GEMM produces, taken from the staged tile instead of a pass over C
+                              (bf16 output, N % 64 == 0, unbatched) */
 } b200slu_epilogue_t;
 
 /* trans=0: C[M,N] = A[M,K] . B[N,K]^T   (A, B row-major bf16, K contiguous)          fwd / dgrad

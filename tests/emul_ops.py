@@ -60,7 +60,7 @@ def _act_grad(x, act):
 
 def gemm(a, b, *, trans=False, trans_a=None, trans_b=None, bias=None, act=None, alpha=1.0, residual=None,
          act_grad_input=None, act_grad=None, act_grad_out=False, out_dtype=None, out=None, accumulate=False, drop=None,
-         dropout_p=0.0, seed=0, site=0):
+         dropout_p=0.0, seed=0, site=0, colsum_out=None):
     if drop is None and dropout_p > 0.0:
         drop = (dropout_p, seed, site)
     ta = trans if trans_a is None else trans_a
@@ -96,6 +96,8 @@ def gemm(a, b, *, trans=False, trans_a=None, trans_b=None, bias=None, act=None, 
         if dt == BF and exact:
             dt = F32
         res = y.to(dt)
+    if colsum_out is not None:  # of the output as stored
+        colsum_out += res.float()[:, :N].sum(0)
     return (res, pre) if pre_act_out is True else res
 
 

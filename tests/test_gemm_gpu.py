@@ -134,3 +134,21 @@ def test_gemm_dropout_statistics_and_determinism():
     keep = (o1 != 0).float().mean().item()
     assert abs(keep - 0.9) < 0.005, keep
     assert abs(o1.max().item() - 64 / 0.9) < 1e-3
+
+
+@pytest.mark.parametrize("M,N,K_", [(1000, 512, 264), (19, 64, 64), (4100, 2048, 512)])
+def test_gemm_output_colsum(M, N, K_):
+    """out_colsum_accum: the column sums of the bf16 output, taken from the staged tiles in the epilogue, equal the sums of
+    the output that was stored (fp32 accumulation of bf16 values; accumulated onto the buffer's contents)."""
+    from espnet_slurp_b200 import ops
+    g = torch.Generator().manual_seed(M + N)
+    a = torch.randn(M, K_, generator=g).bfloat16()
+    w = (torch.randn(K_, N, generator=g) * 0.1).bfloat16()
+    aux = torch.rand(M, N, generator=g).bfloat16()
+    for kw in (dict(), dict(act_grad_input=aux.cuda(), act_grad="mul")):
+        cs = torch.full((N,), 2.0, device="cuda")
+        out = ops.gemm(a.cuda(), w.cuda(), trans_b=True, colsum_out=cs, **kw)
+        want = 2.0 + out.float().sum(0)
+        torch.testing.assert_close(cs, want, rtol=2e-4, atol=2e-3 * float(out.float().abs().max()))
+        ref = ops.gemm(a.cuda(), w.cuda(), trans_b=True, **kw)
+        assert torch.equal(out, ref)
