@@ -66,7 +66,7 @@ struct EpiArgs {
 // load-constant / test / branch decisions per feature does not fit into (measured: 840 cycles per slice).
 enum : uint32_t {
   EF_BIAS = 1u, EF_SWISH = 2u, EF_RELU = 4u, EF_DACT = 8u, EF_DROP = 16u, EF_ALPHA = 32u, EF_AUX_MUL = 64u,
-  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_SCATTER = 8192u, EF_COLSUM = 16384u, EF_GENERIC = 1u << 31
+  EF_AUX_SWISH = 128u, EF_AUX_RELU = 256u, EF_RES = 512u, EF_F32 = 1024u, EF_ACC = 2048u, EF_RES_TMA = 4096u, EF_SCATTER = 8192u, EF_COLSUM = 16384u, EF_AUX_TMA = 32768u, EF_GENERIC = 1u << 31
 };
 // Epilogue warps: 2 per TMEM lane quadrant for the register-heavy epilogues (168 registers each).
 // 16 warps (4 per quadrant, 64 columns each) halve the epilogue time of the light epilogues (bias-only: 6500 -> 3300
@@ -86,7 +86,7 @@ __host__ __device__ constexpr int num_threads(uint32_t ef, int bn, int cg) { ret
 // TMA round trip (free stage -> L2 -> full stage ~ 2000+ cycles against 512 cycles of MMA per stage), so bytes in
 // flight are what buys tensor-pipe utilisation.
 __host__ __device__ constexpr int stg_bufs(uint32_t ef, int bn, int cg) {
-  return epi_warps(ef, bn, cg) == 16 ? 1 : ((ef & (EF_DACT | EF_GENERIC)) || ((ef & EF_F32) && !(ef & EF_ACC))) ? 2 : 1;
+  return epi_warps(ef, bn, cg) == 16 ? 1 : ((ef & (EF_DACT | EF_GENERIC | EF_AUX_TMA)) || ((ef & EF_F32) && !(ef & EF_ACC))) ? 2 : 1;
 }
 template <int BN, int CG>
 __host__ __device__ constexpr int num_stages(uint32_t ef) {
@@ -200,7 +200,7 @@ __device__ __forceinline__ void epi_prefetch(uint32_t rt_flags, const EpiRow& er
   if (col0 + 16 <= N) {
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
-      if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) p.x[g] = *reinterpret_cast<const uint4*>(er.aux + col0 + g * 8);
+      if ((F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) && !(F & EF_AUX_TMA)) p.x[g] = *reinterpret_cast<const uint4*>(er.aux + col0 + g * 8);
       if ((F & EF_RES) && !(F & EF_RES_TMA)) load8_f32(er.res + col0 + g * 8, p.r[g]);
     }
   }
@@ -231,7 +231,14 @@ __device__ __forceinline__ void epilogue_slice(uint32_t rt_flags, const EpiArgs&
       lds128(stg_out + rowoff + ((ch ^ sw) << 4), r[0], r[1], r[2], r[3]);
       lds128(stg_out + rowoff + (((ch + 1) ^ sw) << 4), r[4], r[5], r[6], r[7]);
     }
-    if (whole) {
+    if (F & EF_AUX_TMA) {
+      // the saved-derivative box was TMA-loaded into the very staging box the results go to: same lane, same 16-byte chunk
+      const uint32_t ch = (uint32_t)((sl & 3) * 2 + g);
+      uint32_t a0, a1, a2, a3;
+      lds128u(stg_out + rowoff + ((ch ^ sw) << 4), a0, a1, a2, a3);
+      const float2 x0 = unpack_bf16x2(a0), x1 = unpack_bf16x2(a1), x2 = unpack_bf16x2(a2), x3 = unpack_bf16x2(a3);
+      x[0] = x0.x; x[1] = x0.y; x[2] = x1.x; x[3] = x1.y; x[4] = x2.x; x[5] = x2.y; x[6] = x3.x; x[7] = x3.y;
+    } else if (whole) {
       if (F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU)) {
         const float2 x0 = unpack_bf16x2(pre.x[g].x), x1 = unpack_bf16x2(pre.x[g].y), x2 = unpack_bf16x2(pre.x[g].z),
                      x3 = unpack_bf16x2(pre.x[g].w);
@@ -566,8 +573,11 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       constexpr bool RT = !(EFC & EF_GENERIC) && (EFC & EF_RES_TMA) != 0;
       static_assert(!RT || (STGB == 2 && (EFC & EF_F32) && !(EFC & (EF_DACT | EF_ACC))), "TMA residual: fp32 output, two staging boxes");
       const uint32_t rbar = bar_res + ew * 16;
-      if (RT && lane == 0) {
-        bulk_wait_read<1>();  // the store that last read this buffer (two pairs ago) is done with it
+      // The saved-derivative operand (EF_AUX_TMA) takes the same road, in 64-column bf16 boxes (one per two slice pairs).
+      constexpr bool AT = !(EFC & EF_GENERIC) && (EFC & EF_AUX_TMA) != 0;
+      static_assert(!AT || (STGB == 2 && !(EFC & (EF_F32 | EF_DACT | EF_ACC | EF_RES))), "TMA saved derivative: bf16 output, two staging boxes");
+      if ((RT || AT) && lane == 0) {
+        bulk_wait_read<1>();  // the store that last read this buffer (two boxes ago) is done with it
         const uint32_t bsel = nflush & 1u;
         mbar_expect_tx(rbar + bsel * 8, 4096);
         tma_load_4d(bsel ? stg1 : stg0, &map_d, rbar + bsel * 8, colw, row0, 0, 0);
@@ -610,6 +620,16 @@ gemm_bf16_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_consta
             tma_load_4d(bn ? stg1 : stg0, &map_d, rbar + bn * 8, c2c, row0, 0, 0);
           }
           mbar_wait(rbar + (nflush & 1u) * 8, (nflush >> 1) & 1u);
+        } else if (AT) {
+          if (box_start) {
+            if (lane == 0 && cp + 2 < NPAIR) {  // next box's saved derivative -> the other buffer, once its last store has read it
+              bulk_wait_read<0>();
+              const uint32_t bn = (nflush + 1u) & 1u;
+              mbar_expect_tx(rbar + bn * 8, 4096);
+              tma_load_4d(bn ? stg1 : stg0, &map_d, rbar + bn * 8, c0c + 64, row0, 0, 0);
+            }
+            mbar_wait(rbar + (nflush & 1u) * 8, (nflush >> 1) & 1u);
+          }
         } else if (box_start && !(!(EFC & EF_GENERIC) && (EFC & EF_SCATTER) != 0)) {
           // the bulk store that last read this staging box must have finished reading it
           if (lane == 0) {
@@ -880,6 +900,11 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     if ((f & EF_RES) && (f & EF_F32) && !(f & (EF_ACC | EF_DACT)) && nbatch == 1 && N % 32 == 0 && ep.ldres % 4 == 0 &&
         ((uintptr_t)ep.res % 16) == 0 && !res_tma_off)
       f |= EF_RES_TMA;
+    // saved-derivative boxes through TMA (specialised bf16-output dgrad kernels only): whole 64-column boxes
+    static const bool aux_tma_off = getenv("B200SLU_GEMM_AUX_TMA") && atoi(getenv("B200SLU_GEMM_AUX_TMA")) == 0;  // tuning only
+    if ((f & (EF_AUX_MUL | EF_AUX_RELU)) && !(f & (EF_F32 | EF_ACC | EF_DACT | EF_RES)) && nbatch == 1 && N % 64 == 0 && ep.ldaux % 8 == 0 &&
+        ((uintptr_t)ep.aux % 16) == 0 && !aux_tma_off)
+      f |= EF_AUX_TMA;
     ep.flags = f;
   }
   B2_CHECK_ARG(e == nullptr || e->act == B200SLU_ACT_NONE || e->act == B200SLU_ACT_SWISH || e->act == B200SLU_ACT_RELU,
@@ -947,6 +972,12 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
   }
   const int kb_per = (num_kb + splits - 1) / splits;
   splits = (num_kb + kb_per - 1) / kb_per;
+  if (ep.flags & EF_AUX_TMA) {  // implemented by the two specialised dgrad kernels below only
+    const uint32_t base = ep.flags & ~EF_AUX_TMA;
+    const bool ok = bn == 256 && !g->trans_a && g->trans_b && (ep.debug & ~16) == 0 &&
+                    (base == EF_AUX_MUL || base == (EF_AUX_MUL | EF_COLSUM) || base == EF_AUX_RELU);
+    if (!ok) ep.flags = base;
+  }
   if (ep.flags & EF_RES_TMA) {  // only the specialised kernels below implement it; anything else keeps the register path
     const uint32_t base = ep.flags & ~EF_RES_TMA;
     const bool ok = bn == 256 && !g->trans_a && (ep.debug & ~16) == 0 &&
@@ -973,6 +1004,8 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
     B2_TRY(make_map(&md, ep.pre_out, M, N, g->ldc, 1, 0, 1, 0, 64, 32, 2));
   else if (ep.flags & EF_RES_TMA)
     B2_TRY(make_map(&md, ep.res, M, N, ep.ldres, 1, 0, 1, 0, 32, 32, 4));  // residual boxes share the second-output slot
+  else if (ep.flags & EF_AUX_TMA)
+    B2_TRY(make_map(&md, ep.aux, M, N, ep.ldaux, 1, 0, 1, 0, 64, 32, 2));  // ... and so do the saved-derivative boxes
   else
     md = mc;
   // Specialised epilogues for the hot GEMMs of the train step; anything else runs the generic kernel.
@@ -1006,6 +1039,9 @@ int b2_gemm_ex(const b200slu_gemm_t* g, const b200slu_epilogue_t* e, cudaStream_
         B2_CASE(256, 3, false, true, 0u);
         B2_CASE(256, 3, false, true, EF_AUX_MUL);
         B2_CASE(256, 3, false, true, EF_AUX_MUL | EF_COLSUM);
+        B2_CASE(256, 3, false, true, EF_AUX_MUL | EF_AUX_TMA);
+        B2_CASE(256, 3, false, true, EF_AUX_RELU | EF_AUX_TMA);
+        B2_CASE(256, 3, false, true, EF_AUX_MUL | EF_COLSUM | EF_AUX_TMA);
         B2_CASE(256, 3, false, true, EF_AUX_RELU);
         B2_CASE(256, 3, false, true, EF_RES | EF_F32);
         B2_CASE(256, 3, false, true, EF_RES | EF_F32 | EF_RES_TMA);
