@@ -264,6 +264,7 @@ def softmax_bwd(dpd, p, Tk: int, mode: str, scale: float, ld_bd: int = 0, drop: 
 
 # ---- fused attention (scores -> rel_shift -> softmax -> dropout -> context) --------------------------------------
 CHUNK_KEYS = 192  # keys per launch of the fused attention kernels (multiple of 64: a chunk is whole 64-column p blocks)
+TAIL_MIN_UNITS = 128  # (utterance, head) units from which a short last key chunk gets a backward launch of its own
 
 
 def relattn_supported(Tq: int, Tk: int, dk: int, mode: str, causal: bool = False) -> bool:
@@ -363,6 +364,8 @@ def relattn_bwd(dctx, qu, k, v, p, ctx, B: int, Tq: int, Tk: int, H: int, mode: 
     # the full chunks in one launch; a short last chunk in its own, sized to its keys (whole 64-key blocks)
     nfull = Tk // CHUNK_KEYS
     tail = Tk - nfull * CHUNK_KEYS
+    if -(-tail // 64) * 64 >= CHUNK_KEYS or B * H < TAIL_MIN_UNITS:
+        tail = 0  # nothing to save, or too few (utterance, head) units to fill the machine with a launch of its own
     for begin, end, ck, c0 in ([(0, Tk, CHUNK_KEYS, 0)] if tail == 0 else
                                [(0, nfull * CHUNK_KEYS, CHUNK_KEYS, 0), (nfull * CHUNK_KEYS, Tk, -(-tail // 64) * 64, nfull)]):
         check(L.b200slu_relattn_bwd_chunks(ptr(dctx), dctx.stride(0), ptr(qu), qu.stride(0), ptr(k), ptr(v), k.stride(0), ptr(p), ld,
