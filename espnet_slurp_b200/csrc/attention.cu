@@ -846,9 +846,11 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
           umma_bf16(tmem_base, make_smem_desc(s_ds + (uint32_t)(ks >> 2) * BLK + (ks & 3) * 32, 16, 1024),
                     make_smem_desc(s_k + ks * 2048, 64 * DK * 2, 1024), id_q, ks != 0);
         const uint32_t id_t = make_idesc(DK, 1, 1, QT);  // A = dS^T / pd^T (MN-major), B = Q_u / dO rows (MN-major)
+        // the contraction runs over the tile's query rows: a last tile with few valid rows (27 of 128 at T = 155) issues
+        // only the k-steps that hold any (each tcgen05.mma costs ~115 cycles of issue whatever its shape)
+        const int kkn = (min(QT, a.Tq - i0) + 15) >> 4;
         for (int m = 0; m < nkt; ++m) {
-#pragma unroll
-          for (int kk = 0; kk < QT / 16; ++kk) {
+          for (int kk = 0; kk < kkn; ++kk) {
             const uint32_t acc = (qt != 0 || kk != 0) ? 1u : 0u;
             umma_bf16(tmem_base + BWD_DK_COL + m * DK, make_smem_desc(s_ds + (uint32_t)m * 2 * BLK + kk * 2048, BLK, 1024),
                       make_smem_desc(s_qu + kk * 2048, 64 * DK * 2, 1024), id_t, acc);
@@ -971,9 +973,9 @@ relattn_bwd_kernel(const __grid_constant__ CUtensorMap map_do, const __grid_cons
             umma_bf16(tmem_base + BWD_DQV_COL, make_smem_desc(s_dbd + (uint32_t)(ks >> 2) * BLK + (ks & 3) * 32, 16, 1024),
                       make_smem_desc(s_pos + ks * 2048, 64 * DK * 2, 1024), id_q, ks != 0);
           const uint32_t id_t = make_idesc(DK, 1, 1, QT);  // dP_window = d(bd)^T . Q_v
+          const int kkn = (min(QT, a.Tq - i0) + 15) >> 4;
           for (int m = 0; m < nmt; ++m) {
-#pragma unroll
-            for (int kk = 0; kk < QT / 16; ++kk)
+            for (int kk = 0; kk < kkn; ++kk)
               umma_bf16(tmem_base + m * DK, make_smem_desc(s_dbd + (uint32_t)m * 2 * BLK + kk * 2048, BLK, 1024),
                         make_smem_desc(s_qv + kk * 2048, 64 * DK * 2, 1024), id_t, kk != 0);
           }
