@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(256, 2) glu_dw_fwd_kernel(const bf16* __restri
                                                             const float* __restrict__ bias, int B, int T, int C, int Krt,
                                                             bf16* __restrict__ out, float* __restrict__ sums) {
   constexpr int FR = DwGeom<TT>::FR, SUB = DwGeom<TT>::SUB;
+  b2_pdl_entry();
   extern __shared__ __align__(16) float dyn_smem[];
   float (*sm)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                           // glu halo tile [TT+KMAX-1][CC]
   float (*red)[8][CC] = reinterpret_cast<float (*)[8][CC]>(dyn_smem + (TT + KMAX - 1) * CC);  // [2][8 frame lanes][CC]
@@ -244,6 +245,7 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
                                                          const float* __restrict__ w, int B, int T, int C, int Krt,
                                                          bf16* __restrict__ d_pw1, float* __restrict__ dw_accum,
                                                          float* __restrict__ dbias_accum, float* __restrict__ dpw1_colsum) {
+  b2_pdl_entry();
   extern __shared__ __align__(16) float dyn_smem[];
   float (*sg)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                             // glu halo tile  [TT+KMAX-1][CC]
   float (*sd)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + (TT + KMAX - 1) * CC);      // d_dw halo tile
@@ -359,6 +361,7 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
 __global__ void bn_finalize_kernel(const float* __restrict__ sums, int C, float n, float eps, float momentum,
                                    float* __restrict__ mean_rstd, float* __restrict__ running_mean,
                                    float* __restrict__ running_var, long long* __restrict__ num_batches) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < C; c += gridDim.x * blockDim.x) {
     const float mean = sums[c] / n;
     const float var = fmaxf(sums[C + c] / n - mean * mean, 0.f);
@@ -378,6 +381,7 @@ constexpr int BN_U = 4;
 __global__ void __launch_bounds__(256) bn_swish_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ mean_rstd,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
                                                            long long M, int C, bf16* __restrict__ y) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   const int cg = blockIdx.x * 64 + (threadIdx.x & 63), rl = threadIdx.x >> 6;
   if (cg * 8 >= C) return;
   const int c = cg * 8;
@@ -426,6 +430,7 @@ __global__ void __launch_bounds__(512, 1) bn_swish_bwd_reduce_kernel(const bf16*
                                                                      const float* __restrict__ gamma,
                                                                      const float* __restrict__ beta, int M, int C,
                                                                      float* __restrict__ sums2) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   // narrow column strips (common.cuh): few blocks per output column, one vector atomic per four columns
   __shared__ float red[2][CS_ROWS][CS_COLS + 1];
   const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
@@ -476,6 +481,7 @@ __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __r
                                                                  const float* __restrict__ sums2, long long M, int C,
                                                                  bf16* __restrict__ dx, float* __restrict__ dgamma,
                                                                  float* __restrict__ dbeta) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   const int cg = blockIdx.x * 64 + (threadIdx.x & 63), rl = threadIdx.x >> 6;
   if (cg * 8 < C) {
     const int c = cg * 8;
@@ -571,7 +577,7 @@ extern "C" int b200slu_glu_dwconv_fwd(const void* pw1, const float* w, const flo
       B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                    \
       b2_device_mark(cfg);                                                                                            \
     }                                                                                                                 \
-    kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out, bn_sums);            \
+    B2_CUDA(b2_launch(kern, dim3(ctiles, gy), dim3(256), smem, st, (const bf16*)pw1, w, bias, B, T, C, K, (bf16*)out, bn_sums)); \
   } while (0)
   if (K == 31) {
     // the tiling with the least staged frames
@@ -612,8 +618,8 @@ extern "C" int b200slu_glu_dwconv_bwd_b(const void* d_out, const void* pw1, cons
       B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                           \
       b2_device_mark(cfg);                                                                                                            \
     }                                                                                                                        \
-    kern<<<dim3(ctiles, gy), 256, smem, st>>>((const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K, (bf16*)d_pw1, dw_accum,  \
-                                              dbias_accum, dpw1_colsum_accum);                                               \
+    B2_CUDA(b2_launch(kern, dim3(ctiles, gy), dim3(256), smem, st, (const bf16*)d_out, (const bf16*)pw1, w, B, T, C, K,       \
+                      (bf16*)d_pw1, dw_accum, dbias_accum, dpw1_colsum_accum));                                              \
   } while (0)
   if (K == 31) {
     const int tt = dw_tile_frames(T, false);
@@ -633,8 +639,8 @@ extern "C" int b200slu_bn_finalize(const float* sums, int C, long long n, float 
   B2_CHECK_ARG(C > 0 && n > 0, "bn_finalize: empty");
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_CONVMOD, st, 0, 24.0 * C);
-  bn_finalize_kernel<<<(C + 255) / 256, 256, 0, st>>>(sums, C, (float)n, eps, momentum, mean_rstd, running_mean, running_var,
-                                                      num_batches_tracked);
+  B2_CUDA(b2_launch(bn_finalize_kernel, dim3((C + 255) / 256), dim3(256), 0, st, sums, C, (float)n, eps, momentum, mean_rstd,
+                    running_mean, running_var, num_batches_tracked));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -649,7 +655,7 @@ extern "C" int b200slu_bn_swish_fwd(const void* x, const float* mean_rstd, const
     const long long gy = (M + 4 * BN_U - 1) / (4 * BN_U);
     const long long cap = (8LL * b2_num_sms() + grid.x - 1) / grid.x;
     grid.y = (unsigned)(gy < cap ? gy : cap);
-    bn_swish_fwd_kernel<<<grid, 256, 0, st>>>((const bf16*)x, mean_rstd, gamma, beta, M, C, (bf16*)y);
+    B2_CUDA(b2_launch(bn_swish_fwd_kernel, grid, dim3(256), 0, st, (const bf16*)x, mean_rstd, gamma, beta, M, C, (bf16*)y));
   }
   B2_LAUNCH_CHECK();
   return 0;
@@ -665,16 +671,16 @@ extern "C" int b200slu_bn_swish_bwd(const void* dy, const void* x, const float* 
   const int cap = (b2_num_sms() + grid.x - 1) / grid.x;  // one 512-thread block (128 registers) per SM
   grid.y = (unsigned)(gy < cap ? gy : cap);
   B2_SCOPE(FAM_CONVMOD, st, 0, 10.0 * M * C);
-  bn_swish_bwd_reduce_kernel<<<grid, 512, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, (int)M, C,
-                                                   sums2_zeroed);
+  B2_CUDA(b2_launch(bn_swish_bwd_reduce_kernel, grid, dim3(512), 0, st, (const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, (int)M,
+                    C, sums2_zeroed));
   B2_LAUNCH_CHECK();
   {
     dim3 ga((C + 511) / 512, 1);
     const long long gya = (M + 4 * BN_U - 1) / (4 * BN_U);
     const long long capa = (4LL * b2_num_sms() + ga.x - 1) / ga.x;
     ga.y = (unsigned)(gya < capa ? gya : capa);
-    bn_swish_bwd_apply_kernel<<<ga, 256, 0, st>>>((const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta, sums2_zeroed, M, C,
-                                                  (bf16*)dx, dgamma_accum, dbeta_accum);
+    B2_CUDA(b2_launch(bn_swish_bwd_apply_kernel, ga, dim3(256), 0, st, (const bf16*)dy, (const bf16*)x, mean_rstd, gamma, beta,
+                      sums2_zeroed, M, C, (bf16*)dx, dgamma_accum, dbeta_accum));
   }
   B2_LAUNCH_CHECK();
   return 0;

@@ -9,6 +9,7 @@ namespace {
 
 __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, bf16* __restrict__ y, long long n, float alpha,
                                                    B2Dropout drop) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   const long long ng = n >> 3;
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < ng; g += (long long)gridDim.x * blockDim.x) {
     float v[8];
@@ -29,6 +30,7 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, 
 __global__ void __launch_bounds__(512, 2) cast_colsum_kernel(const float* __restrict__ x, bf16* __restrict__ y, int M,
                                                                       int N, float alpha, B2Dropout drop,
                                                                       float* __restrict__ out) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   __shared__ float red[CS_ROWS][CS_COLS + 1];
   const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
   const int g = blockIdx.x * CS_TX + tx;  // column group of 8 (N % 8 == 0)
@@ -71,6 +73,7 @@ __global__ void __launch_bounds__(512, 2) cast_colsum_kernel(const float* __rest
 // out[n] += sum_m dy[m, n]   (dy bf16, row stride ld)
 __global__ void __launch_bounds__(512, 2) colsum_kernel(const bf16* __restrict__ dy, int M, int N, long long ld,
                                                                  float* __restrict__ out) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   __shared__ float red[CS_ROWS][CS_COLS + 1];
   const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
   const int g = blockIdx.x * CS_TX + tx;  // column group of 8
@@ -100,6 +103,7 @@ __global__ void __launch_bounds__(512, 2) colsum_kernel(const bf16* __restrict__
 __global__ void __launch_bounds__(256) pos_bias_fwd_kernel(const bf16* __restrict__ q, long long ldq, const float* __restrict__ u,
                                                            const float* __restrict__ v, long long M, int d,
                                                            bf16* __restrict__ qu, bf16* __restrict__ qv) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   const int gpr = d >> 3;
   const long long total = M * gpr;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -123,6 +127,7 @@ __global__ void __launch_bounds__(512, 1) pos_bias_bwd_kernel(const bf16* __rest
                                                               int d, bf16* __restrict__ dq, long long lddq,
                                                               float* __restrict__ du, float* __restrict__ dv,
                                                               float* __restrict__ dbq) {
+  b2_pdl_entry();  // programmatic dependent launch: see common.cuh
   __shared__ float red[2][CS_ROWS][CS_COLS + 1];
   const int tx = threadIdx.x & (CS_TX - 1), ty = threadIdx.x / CS_TX;
   const int g = blockIdx.x * CS_TX + tx;
@@ -226,7 +231,7 @@ extern "C" int b200slu_cast_bf16(const float* x, void* y, long long n, float alp
   B2_CHECK_ARG(!(drop_p > 0.f) || n % 8 == 0, "cast_bf16: dropout needs n %% 8 == 0");
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * n);
-  cast_kernel<<<b2_grid_for(n >> 3, 256), 256, 0, st>>>(x, (bf16*)y, n, alpha, b2_make_drop(drop_p, seed, site));
+  B2_CUDA(b2_launch(cast_kernel, dim3(b2_grid_for(n >> 3, 256)), dim3(256), 0, st, x, (bf16*)y, n, alpha, b2_make_drop(drop_p, seed, site)));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -251,7 +256,7 @@ extern "C" int b200slu_cast_colsum_bf16(const float* x, void* y, int M, int N, f
   const int cap = (colsum_blocks_per_sm() * b2_num_sms() + grid.x - 1) / grid.x;
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * N);
-  cast_colsum_kernel<<<grid, 512, 0, st>>>(x, (bf16*)y, M, N, alpha, b2_make_drop(drop_p, seed, site), colsum_accum);
+  B2_CUDA(b2_launch(cast_colsum_kernel, grid, dim3(512), 0, st, x, (bf16*)y, M, N, alpha, b2_make_drop(drop_p, seed, site), colsum_accum));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -264,7 +269,7 @@ extern "C" int b200slu_colsum_bf16(const void* dy, int M, int N, long long ld, f
   const int cap = (colsum_blocks_per_sm() * b2_num_sms() + grid.x - 1) / grid.x;
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 2.0 * M * N);
-  colsum_kernel<<<grid, 512, 0, st>>>((const bf16*)dy, M, N, ld, out_accum);
+  B2_CUDA(b2_launch(colsum_kernel, grid, dim3(512), 0, st, (const bf16*)dy, M, N, ld, out_accum));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -274,8 +279,8 @@ extern "C" int b200slu_pos_bias_fwd(const void* q, long long ldq, const float* p
   B2_CHECK_ARG(M > 0 && d % 8 == 0 && ldq % 8 == 0, "pos_bias_fwd: d and ldq must be multiples of 8");
   cudaStream_t st = (cudaStream_t)stream;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * d);
-  pos_bias_fwd_kernel<<<b2_grid_for((long long)M * (d >> 3), 256), 256, 0, st>>>((const bf16*)q, ldq, pos_bias_u, pos_bias_v, M,
-                                                                                  d, (bf16*)q_u, (bf16*)q_v);
+  B2_CUDA(b2_launch(pos_bias_fwd_kernel, dim3(b2_grid_for((long long)M * (d >> 3), 256)), dim3(256), 0, st, (const bf16*)q, ldq,
+                    pos_bias_u, pos_bias_v, M, d, (bf16*)q_u, (bf16*)q_v));
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -289,8 +294,8 @@ extern "C" int b200slu_pos_bias_bwd_q(const void* dq_u, const void* dq_v, int M,
   const int cap = (b2_num_sms() + grid.x - 1) / grid.x;  // one 512-thread block per SM
   grid.y = gy < cap ? gy : cap;
   B2_SCOPE(FAM_ELEMWISE, st, 0, 6.0 * M * d);
-  pos_bias_bwd_kernel<<<grid, 512, 0, st>>>((const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum, dv_accum,
-                                            dq_colsum_accum);
+  B2_CUDA(b2_launch(pos_bias_bwd_kernel, grid, dim3(512), 0, st, (const bf16*)dq_u, (const bf16*)dq_v, M, d, (bf16*)dq, lddq, du_accum,
+                    dv_accum, dq_colsum_accum));
   B2_LAUNCH_CHECK();
   return 0;
 }

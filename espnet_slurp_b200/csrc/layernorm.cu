@@ -86,11 +86,13 @@ __global__ void __launch_bounds__(LNF_WARPS * 32, 1) ln_fwd_pipe_kernel(const fl
   const uint32_t sbase = smem_u32(smraw);
   const uint32_t bar0 = sbase + (uint32_t)(warp * LNF_NBUF) * 8u;
   const uint32_t ring = 1024u + (uint32_t)(warp * LNF_NBUF) * slot;  // barriers live in the first KB
+  b2_pdl_launch_dependents();  // the next kernel may start launching; it waits for this one before touching memory
   if (lane == 0) {
     for (int b = 0; b < LNF_NBUF; ++b) mbar_init(bar0 + b * 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  b2_pdl_wait();  // barrier set-up overlapped the predecessor's tail; its results are needed from here on
   const long long W = (long long)gridDim.x * LNF_WARPS, gw = (long long)blockIdx.x * LNF_WARPS + warp;
   auto issue = [&](long long row, int b) {
     mbar_expect_tx(bar0 + b * 8, slot);
@@ -316,12 +318,14 @@ __global__ void __launch_bounds__(LNP_WARPS * 32, 1) ln_bwd_pipe_kernel(const vo
   const uint32_t bar0 = smem_u32(smraw) + 3u * D * 4u + (uint32_t)(warp * nbuf) * 8u;
   const uint32_t ring_off = (3u * D * 4u + (uint32_t)(LNP_WARPS * nbuf) * 8u + 127u) & ~127u;
   const uint32_t buf0 = ring_off + (uint32_t)(warp * nbuf) * slot;  // byte offset of this warp's first slot
+  b2_pdl_launch_dependents();
   for (int i = threadIdx.x; i < 3 * D; i += blockDim.x) sm[i] = 0.f;
   if (lane == 0) {
     for (int b = 0; b < nbuf; ++b) mbar_init(bar0 + b * 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  b2_pdl_wait();
   const long long W = (long long)gridDim.x * LNP_WARPS, gw = (long long)blockIdx.x * LNP_WARPS + warp;
   const uint32_t sbase = smem_u32(smraw);
   auto issue = [&](long long row, int b) {  // one lane
@@ -459,7 +463,8 @@ int launch_ln_bwd_pipe(const void* dy, const float* x, const float* gamma, const
   }
   const long long warps = M;
   const int grid = (int)min((long long)b2_num_sms(), (warps + LNP_WARPS - 1) / LNP_WARPS);
-  kern<<<grid, LNP_WARPS * 32, smem, st>>>(dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta, g16, g_alpha, drop, gsum, nbuf);
+  B2_CUDA(b2_launch(kern, dim3(grid), dim3(LNP_WARPS * 32), smem, st, dy, x, gamma, stats, dx_add, M, D, dx, dgamma, dbeta, g16, g_alpha,
+                    drop, gsum, nbuf));
   return 0;
 }
 
@@ -482,8 +487,12 @@ extern "C" int b200slu_layernorm_fwd(const float* x, const float* gamma, const f
       B2_CUDA(cudaFuncSetAttribute(ln_fwd_pipe_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
       b2_device_mark(configured);
     }
-    if (D <= 256) ln_fwd_pipe_kernel<1><<<pgrid, LNF_WARPS * 32, psmem, st>>>(x, gamma, beta, M, D, eps, (bf16*)y_bf16, y_f32, stats);
-    else ln_fwd_pipe_kernel<2><<<pgrid, LNF_WARPS * 32, psmem, st>>>(x, gamma, beta, M, D, eps, (bf16*)y_bf16, y_f32, stats);
+    if (D <= 256)
+      B2_CUDA(b2_launch(ln_fwd_pipe_kernel<1>, dim3(pgrid), dim3(LNF_WARPS * 32), psmem, st, x, gamma, beta, M, D, eps, (bf16*)y_bf16,
+                        y_f32, stats));
+    else
+      B2_CUDA(b2_launch(ln_fwd_pipe_kernel<2>, dim3(pgrid), dim3(LNF_WARPS * 32), psmem, st, x, gamma, beta, M, D, eps, (bf16*)y_bf16,
+                        y_f32, stats));
     B2_LAUNCH_CHECK();
     return 0;
   }
