@@ -68,6 +68,8 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=8)
     ap.add_argument("--dp-mode", default="graph", choices=["graph", "graph_serial", "eager_overlap"],
                     help="N > 1: how the gradient all-reduce meets the CUDA graph (see espnet_slurp_b200/trainer.py)")
+    ap.add_argument("--dp-comm", default=None, choices=["peer", "nccl"],
+                    help="N > 1: gradient buckets over peer memory by the copy engines (default) or ncclAllReduce")
     a = ap.parse_args()
     w = WORKLOADS[a.workload]
     for k in ("batch", "vocab", "rel_pos", "min_sec", "max_sec", "enc_blocks", "dec_blocks"):
@@ -311,7 +313,8 @@ class Trainer:
         dev = torch.device("cuda", torch.cuda.current_device())
         # Graph capture is driven explicitly below (eager_steps_before_capture is never reached) so that the launches of
         # one eager step can be counted first.
-        self.ts = TrainStep(cfg, make_state_dict(cfg), rank, world, dp_mode=args.dp_mode, use_graph=False)
+        self.ts = TrainStep(cfg, make_state_dict(cfg), rank, world, dp_mode=args.dp_mode, use_graph=False,
+                            dp_comm=args.dp_comm)
         if os.environ.get("B200SLU_BENCH_FORCE_CUTS"):  # tuning: the chain-of-graphs capture on one GPU (cost of the cuts alone)
             self.ts.force_cuts = tuple(s for s, _, _ in self.ts.reducer.stages if s != "front")
         self.host_batches, self.dev_batches, self.flens, self.done = [], [], [], []
@@ -496,6 +499,9 @@ def run_ours(args):
                                + ("" if args.no_graph else "; whole step replayed as CUDA graph(s)"),
                    "name": args.workload, "batch_per_gpu": args.batch, "global_batch": args.batch * world,
                    "parallelism": f"dp{world}", "dp_mode": args.dp_mode if world > 1 else None,
+                   "dp_comm": ({"peer": "gradient buckets over NVLink peer memory by the copy engines (dist.PeerReducer)",
+                                "nccl": "ncclAllReduce per bucket (dist.GradReducer)"}[tr.ts.dp_comm]
+                               + ("; " + tr.ts.dp_comm_note if getattr(tr.ts, "dp_comm_note", None) else "")) if world > 1 else None,
                    "l2": "per-step working set (activations + 1.3 GB of weights/grads/moments) >> 126 MB L2; 4 rotating batches"},
         "e2e": {"value": round(total_audio / (ms_e2e * 1e-3), 1), "unit": "audio-sec/sec", "ms_per_step": round(ms_e2e / args.steps, 3),
                 "h2d_bytes_per_step": tr.h2d_bytes, "d2h_bytes_per_step": 16,

@@ -79,6 +79,32 @@ __global__ void adam_advance_kernel(double* __restrict__ state) {
   if (state[2] == 1.0) state[3] += 1.0;
 }
 
+// dst[i] += sum_k src[k * stride + i] (fp32, fixed order k = 0..nshards-1): the local reduction of the peer-memory
+// gradient exchange (dist.PeerReducer) -- the shards the copy engines pulled from the other ranks are added onto this
+// rank's own slice.  Streaming, 16-byte accesses; runs beside the backward on the communication stream, so the grid is
+// kept to a fraction of the SMs.
+__global__ void __launch_bounds__(256) add_shards_kernel(float* __restrict__ dst, const float* __restrict__ src, long long stride,
+                                                         int nshards, long long n) {
+  const long long n4 = n >> 2, step = (long long)gridDim.x * 256;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += step) {
+    float4 a = reinterpret_cast<const float4*>(dst)[i];
+    for (int k = 0; k < nshards; ++k) {
+      const float4 b = __ldcs(reinterpret_cast<const float4*>(src + k * stride) + i);
+      a.x += b.x;
+      a.y += b.y;
+      a.z += b.z;
+      a.w += b.w;
+    }
+    reinterpret_cast<float4*>(dst)[i] = a;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {  // ragged tail
+    const long long i = (n4 << 2) + threadIdx.x;
+    float a = dst[i];
+    for (int k = 0; k < nshards; ++k) a += src[k * stride + i];
+    dst[i] = a;
+  }
+}
+
 }  // namespace
 
 // state: 3 doubles on the device (zeroed here).  grad_inv_scale multiplies every gradient first (e.g. 1/accum_grad).
@@ -118,6 +144,20 @@ extern "C" int b200slu_adam_step_sched(float* params, const float* grads, float*
                                                       weight_decay, 1.f, 1.f, grad_inv_scale, max_norm, state4, nullptr, warmup_steps);
   B2_LAUNCH_CHECK();
   adam_advance_kernel<<<1, 1, 0, st>>>(state4);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200slu_add_shards_f32(float* dst, const float* src, long long shard_stride, int nshards, long long n, void* stream) {
+  B2_CHECK_ARG(n > 0 && nshards >= 1 && shard_stride >= n && shard_stride % 4 == 0 && ((uintptr_t)dst % 16) == 0 &&
+                   ((uintptr_t)src % 16) == 0,
+               "add_shards: n > 0, shards of stride >= n (multiple of 4 floats), 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2_SCOPE(FAM_ELEMWISE, st, 0, 4.0 * n * (nshards + 2));
+  int grid = b2_grid_for(n >> 2, 256, 4);
+  if (grid > 64) grid = 64;
+  if (grid < 1) grid = 1;
+  add_shards_kernel<<<grid, 256, 0, st>>>(dst, src, shard_stride, nshards, n);
   B2_LAUNCH_CHECK();
   return 0;
 }

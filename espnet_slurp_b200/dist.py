@@ -146,3 +146,96 @@ class GradReducer:
         for h in self.handles:
             h.wait()
         self.handles = []
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# The same exchange without a single SM held by communication: peer memory + copy engines
+# ----------------------------------------------------------------------------------------------------------------------
+def shard_range(lo: int, hi: int, world: int, rank: int, align: int = 8) -> Tuple[int, int]:
+    """Rank ``rank``'s slice of the bucket [lo, hi): ``world`` consecutive pieces of ceil((hi - lo) / world) elements rounded
+    up to ``align`` (the last ones may be short or empty)."""
+    m = -(-(hi - lo) // world)
+    m = -(-m // align) * align
+    a = min(lo + rank * m, hi)
+    return a, min(a + m, hi)
+
+
+def peer_grad_alloc(device):
+    """Allocator of the flat gradient buffer for ``ParamPack(grad_alloc=...)``: memory every rank of the node can map
+    (CUDA virtual-memory handles exchanged by torch's symmetric-memory rendezvous)."""
+    import torch.distributed._symmetric_memory as symm
+
+    return lambda n: symm.empty(n, dtype=torch.float32, device=device)
+
+
+class PeerReducer(GradReducer):
+    """GradReducer's bucket plan and call protocol, exchanged over NVLink PEER MEMORY by the COPY ENGINES.
+
+    Why: the step's persistent kernels size their grids for all 148 SMs and fill the shared memory of each (the GEMM's
+    operand ring takes the whole 227 KB), so a communication kernel cannot share an SM with them -- while an NCCL kernel
+    holds some SMs, the CTAs assigned to those SMs start late and the whole statically partitioned kernel ends late
+    (~1.0-1.5 ms per step whatever N is).  Here the flat gradient buffer lives in memory all ranks
+    map (``peer_grad_alloc``) and a bucket [lo, hi) is reduced as
+
+        barrier                      every rank's bucket is final (a one-CTA flag kernel, torch symmetric-memory barrier)
+        pull   (N-1 DMA copies)      this rank's slice of the bucket, from every other rank's buffer into local staging
+        add    (one small kernel)    own slice += staged slices (ops.add_shards_f32, fixed order)
+        push   (N-1 DMA copies)      the reduced slice into every other rank's buffer
+
+    on the communication stream; one more barrier at the end makes all pushes visible before clip + Adam.  Rank r alone
+    computes slice r and every rank receives those very bits, so the replicas stay bit-identical.  No slice is written
+    while anyone may still read it: only rank r reads slice r of the others (its pulls precede its pushes in stream
+    order), and the closing barrier orders everything before the next step clears the buffer."""
+
+    def __init__(self, pack, world: Optional[int] = None, group=None, bucket_bytes: int = 64 << 20, overlap: bool = True,
+                 late_prefixes: Sequence[str] = ()):
+        super().__init__(pack, world, group, bucket_bytes, overlap, late_prefixes)
+        if self.world == 1:
+            return
+        import torch.distributed._symmetric_memory as symm
+
+        self.hdl = symm.rendezvous(pack.gflat, group if group is not None else dist.group.WORLD)
+        self.rank = self.hdl.rank
+        assert self.hdl.world_size == self.world
+        self.peer = [pack.gflat if r == self.rank else self.hdl.get_buffer(r, (pack.total,), torch.float32)
+                     for r in range(self.world)]
+        self.shard_max = max(shard_range(lo, hi, self.world, 0)[1] - lo for _, lo, hi in self.stages)
+        self.staging = torch.empty((self.world - 1) * self.shard_max, device=pack.gflat.device, dtype=torch.float32)
+        # above the compute stream: the flag and add kernels are tiny and take the first SM slot that frees up
+        self.comm = torch.cuda.Stream(device=pack.gflat.device, priority=-1)
+
+    def ready(self, stage: str):
+        if self.world == 1:
+            return
+        if not self.overlap and stage != "front":
+            return
+        upto = max((i for i, (s, _, _) in enumerate(self.stages) if s == stage), default=-1)
+        if stage == "front":
+            upto = len(self.stages) - 1
+        if upto < self._issued:
+            return
+        from . import ops
+
+        self.comm.wait_stream(torch.cuda.current_stream())
+        g, W, r, sm = self.pack.gflat, self.world, self.rank, self.shard_max
+        with torch.cuda.stream(self.comm):
+            for i in range(self._issued, upto + 1):
+                _, lo, hi = self.stages[i]
+                a, b = shard_range(lo, hi, W, r)
+                self.hdl.barrier(channel=0)
+                if b > a:
+                    others = [(r + s) % W for s in range(1, W)]
+                    for k, p in enumerate(others):
+                        self.staging[k * sm: k * sm + (b - a)].copy_(self.peer[p][a:b], non_blocking=True)
+                    ops.add_shards_f32(g[a:b], self.staging, sm, W - 1)
+                    for p in others:
+                        self.peer[p][a:b].copy_(g[a:b], non_blocking=True)
+        self._issued = upto + 1
+
+    def finish(self):
+        if self.world == 1:
+            return
+        self.ready("front")
+        with torch.cuda.stream(self.comm):
+            self.hdl.barrier(channel=1)
+        torch.cuda.current_stream().wait_stream(self.comm)

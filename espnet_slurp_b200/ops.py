@@ -390,10 +390,12 @@ def rel_unshift(dac, T: int, mode: str, ld_bd: int):
 
 
 # ---- conv module --------------------------------------------------------------------------------------------------
-def glu_dwconv_fwd(pw1, w, bias, B: int, T: int, K: int):
+def glu_dwconv_fwd(pw1, w, bias, B: int, T: int, K: int, sums=None):
+    """sums: zeroed f32 [2 C] the kernel adds the BatchNorm sums into (allocated here when None)."""
     Cc = pw1.shape[1] // 2
     out = torch.empty(B * T, Cc, device=pw1.device, dtype=torch.bfloat16)
-    sums = torch.zeros(2 * Cc, device=pw1.device, dtype=torch.float32)
+    if sums is None:
+        sums = torch.zeros(2 * Cc, device=pw1.device, dtype=torch.float32)
     check(_lib.lib().b200slu_glu_dwconv_fwd(ptr(pw1), ptr(w), ptr(bias), B, T, Cc, K, ptr(out), ptr(sums), stream_ptr()),
           "glu_dwconv_fwd")
     return out, sums
@@ -424,10 +426,11 @@ def bn_swish_fwd(x, mean_rstd, gamma, beta):
     return y
 
 
-def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta):
+def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta, scratch=None):
+    """scratch: zeroed f32 [2 C] for the two channel sums of the backward (allocated here when None)."""
     M, Cc = x.shape
     dx = torch.empty(M, Cc, device=x.device, dtype=torch.bfloat16)
-    sums2 = torch.zeros(2 * Cc, device=x.device, dtype=torch.float32)
+    sums2 = scratch if scratch is not None else torch.zeros(2 * Cc, device=x.device, dtype=torch.float32)
     check(_lib.lib().b200slu_bn_swish_bwd(ptr(dy), ptr(x), ptr(mean_rstd), ptr(gamma), ptr(beta), M, Cc, ptr(sums2), ptr(dx),
                                           ptr(dgamma), ptr(dbeta), stream_ptr()), "bn_swish_bwd")
     return dx
@@ -649,6 +652,12 @@ def adam_step_sched(params, grads, exp_avg, exp_avg_sq, base_lr: float, warmup_s
     check(_lib.lib().b200slu_adam_step_sched(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), base_lr,
                                              float(warmup_steps), betas[0], betas[1], eps, weight_decay, grad_inv_scale, max_norm,
                                              ptr(state4), stream_ptr()), "adam_step_sched")
+
+
+def add_shards_f32(dst, src, shard_stride: int, nshards: int):
+    """dst += sum_k src[k * shard_stride : k * shard_stride + dst.numel()] (fp32, in place, fixed order)."""
+    check(_lib.lib().b200slu_add_shards_f32(ptr(dst), ptr(src), int(shard_stride), int(nshards), dst.numel(), stream_ptr()),
+          "add_shards_f32")
 
 
 def set_sm_budget(sms: int):

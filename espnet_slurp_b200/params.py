@@ -44,10 +44,12 @@ def _order(names: List[str]) -> List[str]:
 
 
 class ParamPack:
-    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, adopt: bool = False, lowp=torch.bfloat16):
+    def __init__(self, tensors: Dict[str, torch.Tensor], device=None, adopt: bool = False, lowp=torch.bfloat16,
+                 grad_alloc=None):
         """tensors: name -> fp32 parameter (reference names / shapes).  adopt=True re-points each given tensor's
         ``.data`` at its flat view (use with nn.Parameters).  lowp: storage type of the GEMM-operand copy (bf16; fp32 only
-        in the CPU tests of the orchestration)."""
+        in the CPU tests of the orchestration).  grad_alloc(n): allocator of the flat fp32 gradient buffer (data-parallel
+        runs place it in memory the other ranks can map: dist.peer_grad_alloc); zeroed here."""
         names = _order([k for k, v in tensors.items() if v.is_floating_point()])
         device = device if device is not None else next(iter(tensors.values())).device
         self.device = device
@@ -58,7 +60,7 @@ class ParamPack:
         self.total = off
         self.flat32 = torch.zeros(off, device=device, dtype=torch.float32)
         self.flat16 = torch.zeros(off, device=device, dtype=lowp)
-        self.gflat = torch.zeros(off, device=device, dtype=torch.float32)
+        self.gflat = torch.zeros(off, device=device, dtype=torch.float32) if grad_alloc is None else grad_alloc(off).zero_()
         self.names, self.offs = names, offs
         self.shapes = {n: tuple(tensors[n].shape) for n in names}
         self.P: Dict[str, torch.Tensor] = {}

@@ -86,6 +86,26 @@ class StepCtx:
 
 
 # ------------------------------------------------------------------------------------------------------------------
+# zeroed accumulators: the small f32 buffers kernels ADD into (BatchNorm sums, d(projected positions)) are cut out of one
+# buffer that is cleared by one fill per step instead of three fills per encoder block
+# ------------------------------------------------------------------------------------------------------------------
+_ZEROS = [None, 0]  # (f32 buffer, floats handed out)
+
+
+def _zeros_begin(device, floats: int):
+    _ZEROS[0], _ZEROS[1] = torch.zeros(floats, device=device, dtype=F32), 0
+
+
+def _zeros(n: int, device):
+    """n zeroed floats (16-byte aligned piece of the step's buffer; a fresh tensor once that is used up)."""
+    buf, used = _ZEROS
+    if buf is None or buf.device != device or used + n > buf.numel():
+        return torch.zeros(n, device=device, dtype=F32)
+    _ZEROS[1] = used + (n + 3) // 4 * 4
+    return buf[used:used + n]
+
+
+# ------------------------------------------------------------------------------------------------------------------
 # position tables (constants; built once per length with torch, like the reference's extend_pe)
 # ------------------------------------------------------------------------------------------------------------------
 _PE_CACHE: Dict[tuple, torch.Tensor] = {}
@@ -212,7 +232,7 @@ def relmha_bwd(dy, saved, pos16, P, W, G, p: str, norm: str, cfg: EncCfg, B: int
     K.gemm(g, c, trans=True, out=G[a + ".linear_out.weight"], accumulate=True)
     dc = K.gemm(g, W[a + ".linear_out.weight"], trans_b=True)
     dqkv = torch.empty_like(qkv)
-    dpp = torch.zeros(Pn, d, device=x.device, dtype=F32)
+    dpp = _zeros(Pn * d, x.device).view(Pn, d)
     if fb:
         # fused backward (keys <= 192): dP, dS, dropout(p) and d(matrix_bd) stay on the SM; dq_u, dq_v, dk, dv and the
         # gradient of the projected positions come out of ONE kernel
@@ -250,7 +270,7 @@ def convmod_fwd(x, P, W, p: str, norm: str, cfg: EncCfg, B: int, T: int, ctx: St
     ln, _, st = K.layernorm_fwd(x, P[norm + ".weight"], P[norm + ".bias"])
     pw1 = K.gemm(ln, W[cm + ".pointwise_conv1.weight"], bias=P[cm + ".pointwise_conv1.bias"])
     wdw = P[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel)
-    dw, sums = K.glu_dwconv_fwd(pw1, wdw, P[cm + ".depthwise_conv.bias"], B, T, cfg.kernel)
+    dw, sums = K.glu_dwconv_fwd(pw1, wdw, P[cm + ".depthwise_conv.bias"], B, T, cfg.kernel, sums=_zeros(2 * cfg.d, x.device))
     rm = rv = nb = None
     if bn_buffers is not None and ctx.training:
         rm, rv, nb = bn_buffers[cm + ".norm.running_mean"], bn_buffers[cm + ".norm.running_var"], \
@@ -279,7 +299,7 @@ def convmod_bwd(dy, saved, P, W, G, p: str, norm: str, cfg: EncCfg, B: int, T: i
     K.gemm(g, bs, trans=True, out=G[cm + ".pointwise_conv2.weight"], accumulate=True)
     dbs = K.gemm(g, W[cm + ".pointwise_conv2.weight"], trans_b=True)
     ddw = K.bn_swish_bwd(dbs, dw, mr, P[cm + ".norm.weight"], P[cm + ".norm.bias"], G[cm + ".norm.weight"],
-                         G[cm + ".norm.bias"])
+                         G[cm + ".norm.bias"], scratch=_zeros(2 * cfg.d, dy.device))
     wdw = P[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel)
     # ... which also accumulates pointwise_conv1's bias gradient (the column sums of d_pw1)
     dpw1 = K.glu_dwconv_bwd(ddw, pw1, wdw, B, T, cfg.kernel, G[cm + ".depthwise_conv.weight"].reshape(cfg.d, cfg.kernel),
@@ -348,6 +368,7 @@ def encoder_fwd(feats, flens, P, W, cfg: EncCfg, ctx: StepCtx, p: str = "encoder
     pos16 = K.cast_bf16(pos_table(cfg.rel_pos_type, T if cfg.rel_pos_type == "latest" else Pn, cfg.d, feats.device), drop=dpe)
     olens = torch.clamp((flens + 3) // 4, max=T).to(torch.int32)  # mask[:, :, :-2:2][:, :, :-2:2] (subsampling.py:87)
     layers, inter = [], []
+    _zeros_begin(feats.device, cfg.blocks * (4 * cfg.d + (Pn * cfg.d if ctx.training else 0)))
     for n in range(cfg.blocks):
         x, s = enc_layer_fwd(x, pos16, olens, P, W, f"{p}.encoders.{n}", cfg, B, T, ctx, bn_buffers)
         layers.append(s)

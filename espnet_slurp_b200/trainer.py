@@ -17,8 +17,13 @@ samplers come in a handful of padded shapes (length-bucketed batching: `batch_ty
 the graphs are cached per shape ("length buckets") with least-recently-used eviction: the first step of a new shape runs
 eagerly (one-time kernel attribute setup), the next one is captured, later ones replay.
 
-More than one rank (the reference's DDP overlaps its bucketed all-reduce with the backward, trainer.py:221-236):
-  dp_mode="graph" (default)   the step is captured as a CHAIN of graphs that share one memory pool, cut where a gradient
+More than one rank (the reference's DDP overlaps its bucketed all-reduce with the backward, trainer.py:221-236).  The
+exchange itself is dp_comm="peer" (default; dist.PeerReducer: the buckets travel over NVLink peer memory on the copy
+engines, no SM is held by communication) or dp_comm="nccl" (dist.GradReducer: ncclAllReduce per bucket):
+  dp_mode="graph" (default)   dp_comm="peer": ONE graph per batch shape as on a single GPU -- the exchange of each bucket
+                              (flag kernel, DMA copies, one add kernel) is captured as a parallel branch that forks where
+                              step.py reports the bucket final and joins before clip + Adam.
+                              dp_comm="nccl": the step is captured as a CHAIN of graphs that share one memory pool, cut where a gradient
                               bucket of dist.GradReducer becomes final (decoder + CTC head, then every few encoder blocks,
                               last to first).  Between two replays the host issues that bucket's NCCL all-reduce on the
                               communication stream, so it runs under the next segment's kernels; only the small front
@@ -38,7 +43,7 @@ import numpy as np
 import torch
 
 from . import ops, params as bparams, step as bstep
-from .dist import GradReducer
+from .dist import GradReducer, PeerReducer, peer_grad_alloc
 from .melbank import mel_matrix
 
 _DRAW_KEYS = ("center", "warped", "fmask", "tmask")
@@ -61,15 +66,28 @@ class _Bucket:
 class TrainStep:
     def __init__(self, cfg: bstep.ModelCfg, state_dict: Dict[str, torch.Tensor], rank: int = 0, world: int = 1,
                  dp_mode: str = "graph", use_graph: bool = True, lr: float = 1e-3, warmup_steps: int = 25000,
-                 max_norm: float = 5.0, max_buckets: int = 4, eager_steps_before_capture: int = 1):
+                 max_norm: float = 5.0, max_buckets: int = 4, eager_steps_before_capture: int = 1,
+                 dp_comm: Optional[str] = None):
+        """dp_comm (more than one rank): "peer" = gradient buckets exchanged by the copy engines over peer memory
+        (dist.PeerReducer), "nccl" = ncclAllReduce per bucket (dist.GradReducer); default: env B200SLU_DP_COMM or "peer",
+        falling back to "nccl" (recorded in ``self.dp_comm``) when the ranks cannot map each other's memory."""
         assert dp_mode in ("graph", "graph_serial", "eager_overlap"), dp_mode
         dev = torch.device("cuda", torch.cuda.current_device())
         self.cfg, self.rank, self.world, self.dev, self.dp_mode = cfg, rank, world, dev, dp_mode
         self.use_graph = use_graph and not (world > 1 and dp_mode == "eager_overlap")
         self.base_lr, self.warmup_steps, self.max_norm = lr, warmup_steps, max_norm
         self.max_buckets, self.eager_before = max_buckets, eager_steps_before_capture
+        self.dp_comm = (dp_comm or os.environ.get("B200SLU_DP_COMM", "peer")) if world > 1 else None
+        assert self.dp_comm in (None, "peer", "nccl"), self.dp_comm
+        galloc = None
+        if self.dp_comm == "peer":
+            try:
+                galloc = peer_grad_alloc(dev)
+                galloc(8)
+            except Exception as e:  # no symmetric-memory support in this build / on this node
+                self.dp_comm, self.dp_comm_note, galloc = "nccl", "peer memory unavailable: %r" % (e,), None
         self.pack = bparams.ParamPack({k: v.to(dev) for k, v in state_dict.items() if v.dtype == torch.float32
-                                       and "running_" not in k and not k.endswith("melmat")})
+                                       and "running_" not in k and not k.endswith("melmat")}, grad_alloc=galloc)
         n = self.pack.total
         self.m = torch.zeros(n, device=dev)       # Adam moments over the flat fp32 parameter buffer
         self.v = torch.zeros(n, device=dev)
@@ -88,7 +106,13 @@ class TrainStep:
         # with self-conditioning the encoder backward still adds to ctc.ctc_lo's gradient after the heads are done
         # (step.encoder_bwd): those parameters then belong to the last bucket, not to "heads"
         late = ("ctc.",) if cfg.enc.interctc_use_conditioning else ()
-        self.reducer = GradReducer(self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
+        self.reducer = (PeerReducer if self.dp_comm == "peer" else GradReducer)(
+            self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
+        # The peer-memory exchange is made of plain stream work (flag kernels, DMA copies, one add kernel), so it is captured
+        # WITH the step: one graph per batch shape as on a single GPU, the exchange a parallel branch of it, clip + Adam at
+        # its end.  (B200SLU_DP_PEER_CHAIN=1: the chain of graphs with the exchange issued between replays, as with NCCL.)
+        self.peer_one_graph = (self.dp_comm == "peer" and dp_mode == "graph"
+                               and os.environ.get("B200SLU_DP_PEER_CHAIN", "0") != "1")
         # SMs left to the compute kernels while a gradient bucket is being all-reduced (0 = all; tuning: B200SLU_DP_SM_BUDGET)
         self.sm_budget = int(os.environ.get("B200SLU_DP_SM_BUDGET", "0"))
         self.buckets: "OrderedDict[tuple, _Bucket]" = OrderedDict()
@@ -150,16 +174,17 @@ class TrainStep:
 
     def capture(self, b: Optional[_Bucket] = None):
         """Record the whole step of this bucket (weight cast -> front-end -> forward -> backward [-> clip + Adam when
-        single-GPU]) as ONE CUDA graph.  Called automatically by __call__; public for benchmarks that want control."""
+        single-GPU or when the gradient exchange is captured with it]) as ONE CUDA graph.  Called automatically by __call__; public for benchmarks that want control."""
         b = b if b is not None else self.last
         ops.set_step_params(self.sp_dev)
         torch.cuda.synchronize()
-        self.graph_has_tail = self.world == 1
+        self.graph_has_tail = self.world == 1 or self.peer_one_graph
         cuts = self._cut_stages()
         if not cuts:
             g = torch.cuda.CUDAGraph()
+            self.reducer.begin()
             with torch.cuda.graph(g):
-                self._body(b, overlap=False)
+                self._body(b, overlap=self.peer_one_graph)
                 if self.graph_has_tail:
                     self._tail()
             b.graph = [(g, None)]
@@ -196,7 +221,7 @@ class TrainStep:
     def _cut_stages(self):
         """Stages after which the captured step is cut (dp_mode "graph", more than one rank): every bucket of the reducer's
         plan except the last one, which is reduced after the last segment anyway."""
-        if self.world == 1 or self.dp_mode != "graph":
+        if self.world == 1 or self.dp_mode != "graph" or self.peer_one_graph:
             return set(getattr(self, "force_cuts", ()))  # tests cut a single-GPU step to check the chain replays identically
         return {s for s, _, _ in self.reducer.stages if s != "front"}
 

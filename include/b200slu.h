@@ -362,6 +362,12 @@ int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, f
                             float warmup_steps, float beta1, float beta2, float eps, float weight_decay, float grad_inv_scale,
                             float max_norm, double* state4, void* stream);
 
+/* Local reduction of the peer-memory gradient exchange (8e; reference: DistributedDataParallel's all-reduce,
+ * espnet2/train/trainer.py:221-236): dst[i] += sum_k src[k * shard_stride + i], k = 0 .. nshards-1 in that order, fp32.
+ * The shards are the other ranks' copies of this rank's slice of a gradient bucket, pulled over NVLink by the copy
+ * engines (espnet_slurp_b200/dist.py PeerReducer). */
+int b200slu_add_shards_f32(float* dst, const float* src, long long shard_stride, int nshards, long long n, void* stream);
+
 /* Number of SMs the persistent kernels (GEMM, attention, LayerNorm backward) launch their grids for on the current device;
  * 0 = all (default).  Grids are fixed at launch / graph-capture time.  Used by the data-parallel trainer to leave a few SMs
  * to NCCL's kernels while the gradient all-reduce overlaps the backward. */

@@ -313,7 +313,7 @@ def rel_unshift(dac, T, mode, ld_bd):
     return _r(bd.grad)
 
 
-def glu_dwconv_fwd(pw1, w, bias, B, T, K):
+def glu_dwconv_fwd(pw1, w, bias, B, T, K, sums=None):
     C = pw1.shape[1] // 2
     x = pw1.float().reshape(B, T, 2 * C)
     g = x[..., :C] * torch.sigmoid(x[..., C:])
@@ -353,7 +353,7 @@ def bn_swish_fwd(x, mean_rstd, gamma, beta):
     return _r(z * torch.sigmoid(z))
 
 
-def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta):
+def bn_swish_bwd(dy, x, mean_rstd, gamma, beta, dgamma, dbeta, scratch=None):
     C = x.shape[1]
     xh = (x.float() - mean_rstd[:C]) * mean_rstd[C:]
     z = xh * gamma + beta

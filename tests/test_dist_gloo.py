@@ -130,3 +130,19 @@ def test_shard_batch_matches_reference_rule():
     assert sorted(sum((bdist.shard_batch(keys, r, 3) for r in range(3)), [])) == sorted(keys)
     with pytest.raises(RuntimeError):
         bdist.shard_batch(keys[:2], 0, 3)
+
+
+def test_peer_reducer_slices_partition_each_bucket():
+    """dist.shard_range: the ranks' slices of a bucket are disjoint, ordered, 8-element aligned and cover it exactly
+    (also when the bucket is shorter than world * 8 elements and some slices are empty)."""
+    from espnet_slurp_b200 import dist as bdist
+    for lo, hi in ((0, 8), (16, 16 + 7 * 8), (1024, 1024 + 109_000_008), (8, 8 + 24)):
+        for world in (2, 3, 8):
+            pos, sizes = lo, []
+            for r in range(world):
+                a, b = bdist.shard_range(lo, hi, world, r)
+                assert a == pos and a <= b <= hi and (a - lo) % 8 == 0
+                pos = b
+                sizes.append(b - a)
+            assert pos == hi
+            assert max(sizes) == bdist.shard_range(lo, hi, world, 0)[1] - lo  # rank 0's slice is the staging size

@@ -1,0 +1,91 @@
+"""dist.PeerReducer (gradient buckets exchanged by the copy engines over peer memory) against ncclAllReduce on the same
+buffers: two processes, two GPUs (skipped on a one-GPU box; `gpurun --gpus 2 -- python -m pytest tests/test_peer_reduce_gpu.py`).
+The slice arithmetic is covered on the CPU in test_dist_gloo.py."""
+import os
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+class _Pack:
+    """The part of params.ParamPack the reducers read: names, offsets, sizes, the flat gradient buffer."""
+
+    def __init__(self, sizes, alloc):
+        self.names = list(sizes)
+        self.offs, off = {}, 0
+        for n in self.names:
+            self.offs[n] = off
+            off += (sizes[n] + 7) // 8 * 8
+        self.total, self._sizes = off, sizes
+        self.gflat = alloc(off).zero_()
+
+    def shapes_numel(self, n):
+        return self._sizes[n]
+
+
+def _worker(rank, world, port, scale, out):
+    import torch.distributed as dist
+    from espnet_slurp_b200 import dist as bdist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        sizes = {"encoder.embed.conv.0.weight": 2304 * scale + 5, "encoder.after_norm.weight": 512}
+        for b in range(4):
+            sizes["encoder.encoders.%d.feed_forward.w_1.weight" % b] = 100003 * scale
+            sizes["encoder.encoders.%d.norm_ff.bias" % b] = 512
+        sizes["decoder.output_layer.weight"] = 77777 * scale
+        sizes["ctc.ctc_lo.bias"] = 600
+        pack = _Pack(sizes, bdist.peer_grad_alloc(dev))
+        red = bdist.PeerReducer(pack, world, bucket_bytes=(100003 * scale * 4 * 3) // 2)
+        assert len(red.stages) >= 3, red.stages
+        gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+        worst = 0.0
+        for it in range(3):
+            pack.gflat.copy_(torch.randn(pack.total, device=dev, generator=gen))
+            want = pack.gflat.clone()
+            dist.all_reduce(want)
+            torch.cuda.synchronize()
+            dist.barrier()
+            red.begin()
+            for stage in ["heads"] + ["enc%d" % b for b in (3, 2, 1, 0)]:
+                red.ready(stage)
+            red.finish()
+            torch.cuda.synchronize()
+            worst = max(worst, float((pack.gflat - want).abs().max()))
+            # every replica holds the same bits
+            mine = pack.gflat.view(torch.int32).to(torch.int64).sum().reshape(1)
+            both = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(both, mine)
+            assert all(int(b) == int(both[0]) for b in both), both
+        assert worst < 1e-5, worst
+        if out is not None and rank == 0:
+            out.put(worst)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_peer_reducer_matches_nccl_all_reduce():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, 29611, 1, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+    for p in procs:
+        if p.is_alive():
+            p.terminate()
+            pytest.fail("peer reducer worker hung")
+        assert p.exitcode == 0
+    assert out.get(timeout=5) < 1e-5

@@ -2,6 +2,7 @@
 
 Each case is replayed from a CUDA graph over ROT rotating buffer sets (working set >> 126 MB L2) and reported as
 algorithmic GB/s against the measured HBM copy peak (MEASURED_PEAKS.json).  python tools/membound.py [case-substring]
+(MB_ONCE=1: two plain launches per case and no timing, for `ncu --set full`)
 """
 import json, os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -113,6 +114,12 @@ sel = sys.argv[1] if len(sys.argv) > 1 else ""
 print("peak %.0f GB/s (MEASURED_PEAKS hbm burst)" % peak)
 for name, nbytes, make in cases:
     if sel not in name:
+        continue
+    if os.environ.get("MB_ONCE"):  # one plain launch per case: the ncu --set full target
+        fns = [make() for _ in range(2)]
+        for f in fns:
+            f()
+        torch.cuda.synchronize()
         continue
     fns = [make() for _ in range(ROT)]
     for f in fns:
