@@ -203,6 +203,25 @@ class PeerReducer(GradReducer):
         self.staging = torch.empty((self.world - 1) * self.shard_max, device=pack.gflat.device, dtype=torch.float32)
         # above the compute stream: the flag and add kernels are tiny and take the first SM slot that frees up
         self.comm = torch.cuda.Stream(device=pack.gflat.device, priority=-1)
+        # the N-1 copies of a phase are independent: dealt over a few streams they run on several copy engines at once
+        # (what matters for the last, exposed bucket)
+        self.lanes = [self.comm] + [torch.cuda.Stream(device=pack.gflat.device, priority=-1)
+                                    for _ in range(min(self.world - 2, 3))]
+
+    def _fan(self, copies):
+        """Run the (dst, src) copies of one phase after everything queued on the communication stream, on all lanes;
+        the communication stream continues after the last of them."""
+        if len(self.lanes) > 1:
+            start = torch.cuda.Event()
+            start.record(self.comm)
+        for k, (dst, src) in enumerate(copies):
+            lane = self.lanes[k % len(self.lanes)]
+            if lane is not self.comm and k < len(self.lanes):
+                lane.wait_event(start)
+            with torch.cuda.stream(lane):
+                dst.copy_(src, non_blocking=True)
+        for lane in self.lanes[1:min(len(self.lanes), len(copies))]:
+            self.comm.wait_stream(lane)
 
     def ready(self, stage: str):
         if self.world == 1:
@@ -225,11 +244,9 @@ class PeerReducer(GradReducer):
                 self.hdl.barrier(channel=0)
                 if b > a:
                     others = [(r + s) % W for s in range(1, W)]
-                    for k, p in enumerate(others):
-                        self.staging[k * sm: k * sm + (b - a)].copy_(self.peer[p][a:b], non_blocking=True)
+                    self._fan([(self.staging[k * sm: k * sm + (b - a)], self.peer[p][a:b]) for k, p in enumerate(others)])
                     ops.add_shards_f32(g[a:b], self.staging, sm, W - 1)
-                    for p in others:
-                        self.peer[p][a:b].copy_(g[a:b], non_blocking=True)
+                    self._fan([(self.peer[p][a:b], g[a:b]) for p in others])
         self._issued = upto + 1
 
     def finish(self):

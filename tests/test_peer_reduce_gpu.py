@@ -1,5 +1,5 @@
 """dist.PeerReducer (gradient buckets exchanged by the copy engines over peer memory) against ncclAllReduce on the same
-buffers: two processes, two GPUs (skipped on a one-GPU box; `gpurun --gpus 2 -- python -m pytest tests/test_peer_reduce_gpu.py`).
+buffers: one process per visible GPU, at least two (skipped on a one-GPU box; `gpurun --gpus 2 -- python -m pytest tests/test_peer_reduce_gpu.py`).
 The slice arithmetic is covered on the CPU in test_dist_gloo.py."""
 import os
 import sys
@@ -78,7 +78,8 @@ def test_peer_reducer_matches_nccl_all_reduce():
 
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, 29611, 1, out)) for r in range(2)]
+    world = min(torch.cuda.device_count(), 8)  # more than two ranks also deal a phase's copies over several streams
+    procs = [ctx.Process(target=_worker, args=(r, world, 29611, 1, out)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
