@@ -1,4 +1,5 @@
-"""Data-parallel plumbing of the train step: one process per GPU, torch.distributed (NCCL over NVLink/NVSwitch).
+"""Data-parallel plumbing of the train step: one process per GPU, torch.distributed for the rendezvous; the gradient
+exchange runs over NVLink peer memory on the copy engines (PeerReducer, below) or as ncclAllReduce buckets (GradReducer).
 
 Mirrors what the reference does with DistributedDataParallel:
   * each global mini-batch is dealt ``batch[rank::world_size]`` (espnet2/tasks/abs_task.py:1534-1542),
