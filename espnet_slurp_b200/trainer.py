@@ -106,8 +106,14 @@ class TrainStep:
         # with self-conditioning the encoder backward still adds to ctc.ctc_lo's gradient after the heads are done
         # (step.encoder_bwd): those parameters then belong to the last bucket, not to "heads"
         late = ("ctc.",) if cfg.enc.interctc_use_conditioning else ()
-        self.reducer = (PeerReducer if self.dp_comm == "peer" else GradReducer)(
-            self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
+        self.reducer = None
+        if self.dp_comm == "peer":
+            try:
+                self.reducer = PeerReducer(self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
+            except Exception as e:  # the rendezvous is collective and fails on every rank alike (no peer access, no fabric)
+                self.dp_comm, self.dp_comm_note = "nccl", "peer memory unavailable: %r" % (e,)
+        if self.reducer is None:
+            self.reducer = GradReducer(self.pack, world, overlap=(dp_mode != "graph_serial"), late_prefixes=late)
         # The peer-memory exchange is made of plain stream work (flag kernels, DMA copies, one add kernel), so it is captured
         # WITH the step: one graph per batch shape as on a single GPU, the exchange a parallel branch of it, clip + Adam at
         # its end.  (B200SLU_DP_PEER_CHAIN=1: the chain of graphs with the exchange issued between replays, as with NCCL.)
