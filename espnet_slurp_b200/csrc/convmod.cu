@@ -238,6 +238,10 @@ __global__ void __launch_bounds__(256, 2) glu_dw_fwd_kernel(const bf16* __restri
 // 87.7 against 81.5 us -- its two passes per tile re-walk the sub-tiles and the kernel is bound by the staging round trips
 // and barriers, not by FMA issue.)
 constexpr int FR1 = 8;
+template <int TT>
+struct DwBwdGeom {
+  static constexpr int NP = TT <= 96 ? 4 : 1;  // private copies of the block's dW / bias partials (one per frame lane)
+};
 // Backward: grid (channel tiles, utterance chunks); each block walks all its (utterance, time tile) pairs and keeps the
 // depthwise weight gradient in registers across them, so the global atomics are per block, not per tile.
 template <int TT, int KT>
@@ -249,18 +253,22 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
   extern __shared__ __align__(16) float dyn_smem[];
   float (*sg)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem);                             // glu halo tile  [TT+KMAX-1][CC]
   float (*sd)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + (TT + KMAX - 1) * CC);      // d_dw halo tile
-  // dW partial (+ dbias); rows padded to an odd stride so that the 32 channels of a warp hit 32 different banks
-  float (*swg)[KMAX + 4] = reinterpret_cast<float (*)[KMAX + 4]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);
+  // dW partial (+ dbias); rows padded to an odd stride so that the 32 channels of a warp hit 32 different banks.  NP = 4: one
+  // private copy per frame lane, so a tile's partials join the block's with plain read-modify-writes -- as shared-memory
+  // atomics (a compare-and-swap loop per float, four lanes per address) that flush was 11 % of the kernel's instructions
+  // and 28 % of its stall samples.  The 128-frame tile has no room for the copies (two blocks per SM) and keeps the atomics.
+  constexpr int NP = DwBwdGeom<TT>::NP;
+  float (*swg)[KMAX + 4] = reinterpret_cast<float (*)[KMAX + 4]>(dyn_smem + 2 * (TT + KMAX - 1) * CC);  // [NP * CC][KMAX + 4]
   // reversed taps [KMAX][CC]: swr[m][ch] = w[ch][K-1-m] (0 for m >= K); re-read per tile so that the staging phase has the
   // whole register file for its loads in flight
-  float (*swr)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + 2 * (TT + KMAX - 1) * CC + CC * (KMAX + 4));
+  float (*swr)[CC] = reinterpret_cast<float (*)[CC]>(dyn_smem + 2 * (TT + KMAX - 1) * CC + NP * CC * (KMAX + 4));
   const int K = KT > 0 ? KT : Krt;
   const int c0 = blockIdx.x * CC;
   const int pad = (K - 1) / 2;
   const int cl = threadIdx.x & (CC - 1), fr = threadIdx.x >> 6;
   const int c = c0 + cl;
   const int ntt = (T + TT - 1) / TT;
-  for (int it = threadIdx.x; it < CC * (KMAX + 4); it += blockDim.x) (&swg[0][0])[it] = 0.f;
+  for (int it = threadIdx.x; it < NP * CC * (KMAX + 4); it += blockDim.x) (&swg[0][0])[it] = 0.f;
   for (int it = threadIdx.x; it < KMAX * CC; it += blockDim.x) {
     const int m = it / CC, ch = it - m * CC;
     swr[m][ch] = (c0 + ch < C && m < K) ? w[(c0 + ch) * K + (K - 1 - m)] : 0.f;
@@ -331,27 +339,43 @@ __global__ void __launch_bounds__(256) glu_dw_bwd_kernel(const bf16* __restrict_
         }
       }
      }
-     // this tile's weight / bias gradient partials join the block's (4 frame lanes per address)
+     // this tile's weight / bias gradient partials join the block's
+     if (NP == 4) {
+       float* mine = swg[fr * CC + cl];  // this thread's own row: no other thread touches it
 #pragma unroll
-     for (int k = 0; k < KMAX; ++k)
-       if (k < K) atomicAdd(&swg[cl][k], acc[k]);
-     atomicAdd(&swg[cl][KMAX], accb);
-     if (dpw1_colsum != nullptr) {
-       atomicAdd(&swg[cl][KMAX + 1], acca);
-       atomicAdd(&swg[cl][KMAX + 2], accg);
+       for (int k = 0; k < KMAX; ++k)
+         if (k < K) mine[k] += acc[k];
+       mine[KMAX] += accb;
+       mine[KMAX + 1] += acca;
+       mine[KMAX + 2] += accg;
+     } else {  // 4 frame lanes per address
+#pragma unroll
+       for (int k = 0; k < KMAX; ++k)
+         if (k < K) atomicAdd(&swg[cl][k], acc[k]);
+       atomicAdd(&swg[cl][KMAX], accb);
+       if (dpw1_colsum != nullptr) {
+         atomicAdd(&swg[cl][KMAX + 1], acca);
+         atomicAdd(&swg[cl][KMAX + 2], accg);
+       }
      }
     }
   }
   __syncthreads();
+  auto total = [&](int ch, int k) {
+    float v = swg[ch][k];
+#pragma unroll
+    for (int q = 1; q < NP; ++q) v += swg[q * CC + ch][k];
+    return v;
+  };
   for (int it = threadIdx.x; it < CC * K; it += blockDim.x) {
     const int ch = it / K, k = it - ch * K;
-    if (c0 + ch < C) atomicAdd(dw_accum + (long long)(c0 + ch) * K + k, swg[ch][k]);
+    if (c0 + ch < C) atomicAdd(dw_accum + (long long)(c0 + ch) * K + k, total(ch, k));
   }
   if (threadIdx.x < CC && c0 + threadIdx.x < C) {
-    atomicAdd(dbias_accum + c0 + threadIdx.x, swg[threadIdx.x][KMAX]);
+    atomicAdd(dbias_accum + c0 + threadIdx.x, total(threadIdx.x, KMAX));
     if (dpw1_colsum != nullptr) {  // bias gradient of pointwise_conv1 = column sums of d_pw1: no separate pass over it
-      atomicAdd(dpw1_colsum + c0 + threadIdx.x, swg[threadIdx.x][KMAX + 1]);
-      atomicAdd(dpw1_colsum + C + c0 + threadIdx.x, swg[threadIdx.x][KMAX + 2]);
+      atomicAdd(dpw1_colsum + c0 + threadIdx.x, total(threadIdx.x, KMAX + 1));
+      atomicAdd(dpw1_colsum + C + c0 + threadIdx.x, total(threadIdx.x, KMAX + 2));
     }
   }
 }
@@ -611,7 +635,7 @@ extern "C" int b200slu_glu_dwconv_bwd_b(const void* d_out, const void* pw1, cons
     const int ctiles = (C + CC - 1) / CC, units = B * ((T + TT_ - 1) / TT_);                                                 \
     int gy = (dw_blocks_per_sm() * b2_num_sms() + ctiles - 1) / ctiles;                                                      \
     if (gy > units) gy = units;                                                                                              \
-    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + CC * (KMAX + 4) + KMAX * CC) * sizeof(float);                               \
+    const size_t smem = (size_t)(2 * (TT_ + KMAX - 1) * CC + DwBwdGeom<TT_>::NP * CC * (KMAX + 4) + KMAX * CC) * sizeof(float);          \
     auto kern = glu_dw_bwd_kernel<TT_, KT_>;                                                                                 \
     static unsigned long long cfg = 0;                                                                                                 \
     if (!b2_device_done(cfg)) {                                                                                                              \
