@@ -120,6 +120,31 @@ __device__ __forceinline__ float2 b2_fma2(float2 a, float2 b, float2 c) {
   return *reinterpret_cast<float2*>(&d);
 }
 
+// ... and the packed add / multiply (FADD2 / FMUL2): same rounding as the scalar instructions, half the issue slots
+__device__ __forceinline__ float2 b2_add2(float2 a, float2 b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 b2_mul2(float2 a, float2 b) {
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<unsigned long long*>(&a)), "l"(*reinterpret_cast<unsigned long long*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+// sigmoid of a pair: 0.5 * tanh(0.5 x) + 0.5 per component (sigmoidf_ above), two MUFU.TANH and two packed instructions
+__device__ __forceinline__ float2 b2_sigmoid2(float2 x) {
+  const float2 half = make_float2(0.5f, 0.5f);
+  const float2 h = b2_mul2(x, half);
+  float2 t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t.x) : "f"(h.x));
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t.y) : "f"(h.y));
+  return b2_fma2(t, half, half);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);

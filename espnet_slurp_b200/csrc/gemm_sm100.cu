@@ -127,28 +127,36 @@ template <uint32_t EF>
 __device__ __forceinline__ void epi_math8(uint32_t rt_flags, const EpiArgs& ep, const B2DropKey& dk, float alpha,
                                           unsigned long long e0, int col, float (&v)[8], const float (&b)[8],
                                           const float (&x)[8], const float (&r)[8], float (&d)[8]) {
+  // Packed fp32 throughout (FADD2 / FMUL2 / FFMA2 on neighbouring columns): the FMA pipe's rate of scalar code at half the
+  // issue slots, and issue slots are what the K = 512 epilogues run out of (two epilogue warps per scheduler).
   const uint32_t F = (EF & EF_GENERIC) ? rt_flags : EF;
+  const float2 one = make_float2(1.f, 1.f), mone = make_float2(-1.f, -1.f);
+  // the residual add folds into the keep multiply (one FFMA2) when nothing sits between them
+  const bool res_in_drop = (F & EF_DROP) && !(F & EF_DACT) && (F & EF_RES) && !(F & (EF_AUX_MUL | EF_AUX_SWISH | EF_AUX_RELU));
+  float2 V[4], D[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) V[q] = make_float2(v[2 * q], v[2 * q + 1]);
   if (F & EF_BIAS) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] += b[j];
+    for (int q = 0; q < 4; ++q) V[q] = b2_add2(V[q], make_float2(b[2 * q], b[2 * q + 1]));
   }
   if (F & EF_SWISH) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float sg = sigmoidf_(v[j]);
-      const float t = v[j] * sg;           // swish
-      d[j] = fmaf(t, 1.f - sg, sg);        // swish' = sg + swish * (1 - sg)
-      v[j] = t;
+    for (int q = 0; q < 4; ++q) {
+      const float2 sg = b2_sigmoid2(V[q]);
+      const float2 t = b2_mul2(V[q], sg);                 // swish
+      D[q] = b2_fma2(t, b2_fma2(sg, mone, one), sg);      // swish' = sg + swish * (1 - sg)
+      V[q] = t;
     }
   } else if (F & EF_RELU) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      d[j] = v[j] > 0.f ? 1.f : 0.f;
-      v[j] = fmaxf(v[j], 0.f);
+    for (int q = 0; q < 4; ++q) {
+      D[q] = make_float2(V[q].x > 0.f ? 1.f : 0.f, V[q].y > 0.f ? 1.f : 0.f);
+      V[q] = make_float2(fmaxf(V[q].x, 0.f), fmaxf(V[q].y, 0.f));
     }
   } else {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) d[j] = 1.f;
+    for (int q = 0; q < 4; ++q) D[q] = one;
   }
   if (F & EF_DROP) {
     // alpha rides on the keep multiplier (the host clears EF_ALPHA when EF_DROP is set)
@@ -156,36 +164,57 @@ __device__ __forceinline__ void epi_math8(uint32_t rt_flags, const EpiArgs& ep, 
     if (F & EF_DACT) {
       dropout_mul8(dk, (e0 + (unsigned long long)col) >> 3, dk.inv, mul);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        d[j] *= mul[j];
-        v[j] *= mul[j];
+      for (int q = 0; q < 4; ++q) {
+        const float2 m = make_float2(mul[2 * q], mul[2 * q + 1]);
+        D[q] = b2_mul2(D[q], m);
+        V[q] = b2_mul2(V[q], m);
       }
       if (alpha != 1.f) {
+        const float2 al = make_float2(alpha, alpha);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] *= alpha;
+        for (int q = 0; q < 4; ++q) V[q] = b2_mul2(V[q], al);
       }
     } else {
       dropout_mul8(dk, (e0 + (unsigned long long)col) >> 3, dk.inv * alpha, mul);
+      if (res_in_drop) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] *= mul[j];
+        for (int q = 0; q < 4; ++q)
+          V[q] = b2_fma2(V[q], make_float2(mul[2 * q], mul[2 * q + 1]), make_float2(r[2 * q], r[2 * q + 1]));
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) V[q] = b2_mul2(V[q], make_float2(mul[2 * q], mul[2 * q + 1]));
+      }
     }
   } else if (F & EF_ALPHA) {
+    const float2 al = make_float2(alpha, alpha);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] *= alpha;
+    for (int q = 0; q < 4; ++q) V[q] = b2_mul2(V[q], al);
   }
   if (F & EF_AUX_MUL) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] *= x[j];
+    for (int q = 0; q < 4; ++q) V[q] = b2_mul2(V[q], make_float2(x[2 * q], x[2 * q + 1]));
   } else if (F & EF_AUX_SWISH) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] *= swish_gradf_(x[j]);
+    for (int q = 0; q < 4; ++q) {
+      const float2 xx = make_float2(x[2 * q], x[2 * q + 1]);
+      const float2 sg = b2_sigmoid2(xx);
+      // swish'(x) = sg * (1 + x * (1 - sg))   (swish_gradf_)
+      V[q] = b2_mul2(V[q], b2_mul2(sg, b2_fma2(xx, b2_fma2(sg, mone, one), one)));
+    }
   } else if (F & EF_AUX_RELU) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = x[j] > 0.f ? v[j] : 0.f;
+    for (int q = 0; q < 4; ++q) V[q] = make_float2(x[2 * q] > 0.f ? V[q].x : 0.f, x[2 * q + 1] > 0.f ? V[q].y : 0.f);
   }
-  if (F & EF_RES) {
+  if ((F & EF_RES) && !res_in_drop) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] += r[j];
+    for (int q = 0; q < 4; ++q) V[q] = b2_add2(V[q], make_float2(r[2 * q], r[2 * q + 1]));
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    v[2 * q] = V[q].x;
+    v[2 * q + 1] = V[q].y;
+    d[2 * q] = D[q].x;
+    d[2 * q + 1] = D[q].y;
   }
 }
 
