@@ -472,7 +472,7 @@ def run_ours(args):
     tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)  # kernels are timed inside a long step -> sustained figure
     roof = None
     traffic = None
-    for name in ("r2b_step_ncu_summary.json", "r2_step_ncu_summary.json", "r1_step_ncu_summary.json"):
+    for name in ("r2c_step_ncu_summary.json", "r2b_step_ncu_summary.json", "r2_step_ncu_summary.json", "r1_step_ncu_summary.json"):
         try:  # DRAM bytes per GEMM launch from the committed ncu capture of this command (tools/ncu_step_summary.py)
             tj = json.load(open(os.path.join(ROOT, "profiles", name)))
             if tj.get("batch_per_gpu") == args.batch and args.workload == "slurp":
