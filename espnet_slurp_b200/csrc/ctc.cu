@@ -122,6 +122,61 @@ __global__ void __launch_bounds__(256) ctc_prep_kernel(const float* __restrict__
   for (int s = threadIdx.x; s < S; s += blockDim.x) e[s] = (row[ext_label(lab, s, blank)] - lse) * LOG2E;  // log2 units
 }
 
+// Small vocabularies (V <= 2048: the SLURP / LibriSpeech-BPE heads): ONE WARP per frame, 8 frames per block in flight, each
+// warp walking frames grid-stride.  A 500-entry row is 2 KB -- half the threads of a 256-thread block had nothing to load
+// and every frame paid three block barriers and a block launch; here the reductions are warp shuffles and a row's loads
+// are all issued before the first one is used.  (V = 500, T = 1000, B = 64: prep + grad 265 -> see DESIGN.md section 5.)
+constexpr int CTC_WPB = 8;      // warps (= frames in flight) per block
+constexpr int CTC_WARP_V = 2048;       // prep: the warp form wins up to here (V = 2000: forward 417 -> 370 us at T = 1000)
+constexpr int CTC_WARP_V_GRAD = 1024;  // grad: beyond this the block form is ahead (a warp then walks 16 chunks per lane in turn)
+__global__ void __launch_bounds__(32 * CTC_WPB) ctc_prep_warp_kernel(const float* __restrict__ logits, long long ldv, int T, int V,
+                                                                    const int* __restrict__ hlens, const int* __restrict__ labels,
+                                                                    int Lmax, const int* __restrict__ llens, int blank,
+                                                                    float* __restrict__ lse_out, float* __restrict__ em, int Smax,
+                                                                    long long nframes) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (long long r = (long long)blockIdx.x * CTC_WPB + w; r < nframes; r += (long long)gridDim.x * CTC_WPB) {
+    const int b = (int)(r / T), t = (int)(r - (long long)b * T);
+    if (t >= hlens[b]) continue;
+    const float* row = logits + r * ldv;
+    float m = NEG_BIG, sm = 0.f;
+    constexpr int U = 4;  // 16-byte loads in flight per lane and round (V <= 512: the whole row in one round)
+    for (int v0 = lane * 4; v0 < V; v0 += 128 * U) {
+      float x[U][4];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 128;
+        if (v + 4 <= V) {
+          const float4 q = *reinterpret_cast<const float4*>(row + v);
+          x[u][0] = q.x; x[u][1] = q.y; x[u][2] = q.z; x[u][3] = q.w;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) x[u][j] = v + j < V ? row[v + j] : NEG_BIG;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float lm = fmaxf(fmaxf(x[u][0], x[u][1]), fmaxf(x[u][2], x[u][3]));
+        if (lm > m) {
+          sm *= ex2_((m - lm) * LOG2E);
+          m = lm;
+        }
+        const float mb = m * LOG2E;
+        sm += ex2_(fmaf(x[u][0], LOG2E, -mb)) + ex2_(fmaf(x[u][1], LOG2E, -mb)) + ex2_(fmaf(x[u][2], LOG2E, -mb)) +
+              ex2_(fmaf(x[u][3], LOG2E, -mb));
+      }
+    }
+    const float mx = warp_max(m);
+    const float sum = warp_sum(sm * ex2_((m - mx) * LOG2E));  // lanes that saw no element hold (NEG_BIG, 0) -> 0
+    const float lse = mx + logf(sum);
+    if (lane == 0) lse_out[r] = lse;
+    const int S = 2 * llens[b] + 1;
+    const int* lab = labels + (long long)b * Lmax;
+    float* e = em + r * Smax;
+    for (int s = lane; s < S; s += 32) e[s] = (row[ext_label(lab, s, blank)] - lse) * LOG2E;  // log2 units
+  }
+}
+
 // ---- 2. lattice: block = 2 warps per utterance -------------------------------------------------
 // max over the warp in one instruction: order-preserving float -> int map, redux.sync, map back
 __device__ __forceinline__ float warp_max_fast(float x) {
@@ -521,6 +576,80 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const float* __restrict__
   }
 }
 
+// The same for small vocabularies: one warp per frame, its occupancy row in its own slice of shared memory.  The blank's
+// occupancy (every other lattice state) is a warp reduction; only the label states go through shared-memory atomics
+// (repeated labels collide there -- with the blank included, a frame of a 300-label utterance queued 301 adds on one word).
+__global__ void __launch_bounds__(32 * CTC_WPB) ctc_grad_warp_kernel(const float* __restrict__ logits, long long ldv, int T, int V,
+                                                                    const int* __restrict__ hlens, const int* __restrict__ labels,
+                                                                    int Lmax, const int* __restrict__ llens, int blank,
+                                                                    const float* __restrict__ lse_in, const float* __restrict__ em,
+                                                                    const float* __restrict__ alpha, const float* __restrict__ beta,
+                                                                    int Smax, const int* __restrict__ feasible, float scale,
+                                                                    float* __restrict__ g32, bf16* __restrict__ g16, long long ldg,
+                                                                    long long nframes, int Vs) {
+  extern __shared__ __align__(16) float occ_all[];  // [CTC_WPB][Vs]
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float* occ = occ_all + (long long)w * Vs;
+  const int Vp = (int)ldg;
+  for (long long r = (long long)blockIdx.x * CTC_WPB + w; r < nframes; r += (long long)gridDim.x * CTC_WPB) {
+    const int b = (int)(r / T), t = (int)(r - (long long)b * T);
+    if (t >= hlens[b] || !feasible[b]) {
+      for (int v = lane * 4; v < Vp; v += 128) {
+        if (g32 != nullptr) *reinterpret_cast<float4*>(g32 + r * ldg + v) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g16 != nullptr) *reinterpret_cast<uint2*>(g16 + r * ldg + v) = make_uint2(0u, 0u);
+      }
+      continue;
+    }
+    for (int v = lane * 4; v < Vs; v += 128) *reinterpret_cast<float4*>(occ + v) = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int S = 2 * llens[b] + 1;
+    const int* lab = labels + (long long)b * Lmax;
+    const float* ar = alpha + r * Smax;
+    const float* br = beta + r * Smax;
+    const float* er = em + r * Smax;
+    // the row of the logits is requested now; it is consumed after the lattice terms
+    const float* row = logits + r * ldv;
+    // frame-local normaliser Z = lse_s(alpha~ + beta~ - em)
+    float mx = NEG_INF;
+    for (int s = lane; s < S; s += 32) mx = fmaxf(mx, ar[s] + br[s] - er[s]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int s = lane; s < S; s += 32) sum += ex2_(ar[s] + br[s] - er[s] - mx);  // log2 domain; impossible states -> 0
+    sum = warp_sum(sum);
+    const float inv = sum > 0.f ? 1.f / sum : 0.f;
+    __syncwarp();  // occ[] zeroed by every lane before anyone adds into it
+    float ob = 0.f;
+    for (int s = lane; s < S; s += 32) {
+      const float o = ex2_(ar[s] + br[s] - er[s] - mx) * inv;
+      if (s & 1) {
+        if (o > 0.f) atomicAdd(&occ[lab[s >> 1]], o);
+      } else {
+        ob += o;
+      }
+    }
+    ob = warp_sum(ob);
+    if (lane == 0 && ob > 0.f) atomicAdd(&occ[blank], ob);
+    __syncwarp();
+    const float lse2 = lse_in[r] * LOG2E;
+    for (int v = lane * 4; v < Vp; v += 128) {
+      float g[4];
+      if (v + 4 <= V) {
+        const float4 x = *reinterpret_cast<const float4*>(row + v);
+        const float4 oc = *reinterpret_cast<const float4*>(occ + v);
+        g[0] = scale * (ex2_(fmaf(x.x, LOG2E, -lse2)) - oc.x);
+        g[1] = scale * (ex2_(fmaf(x.y, LOG2E, -lse2)) - oc.y);
+        g[2] = scale * (ex2_(fmaf(x.z, LOG2E, -lse2)) - oc.z);
+        g[3] = scale * (ex2_(fmaf(x.w, LOG2E, -lse2)) - oc.w);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[j] = v + j < V ? scale * (ex2_(fmaf(row[v + j], LOG2E, -lse2)) - occ[v + j]) : 0.f;
+      }
+      if (g32 != nullptr) *reinterpret_cast<float4*>(g32 + r * ldg + v) = make_float4(g[0], g[1], g[2], g[3]);
+      if (g16 != nullptr) *reinterpret_cast<uint2*>(g16 + r * ldg + v) = make_uint2(pack_bf16x2(g[0], g[1]), pack_bf16x2(g[2], g[3]));
+    }
+    __syncwarp();  // the row is read by every lane before the next frame clears it
+  }
+}
+
 long long ws_floats(int B, int T, int Lmax) {
   const long long Smax = 2LL * Lmax + 1;
   return 3LL * B * T * Smax + (long long)B * T + B + 8;  // em, alpha, beta, lse, nll_raw (+ pad)
@@ -555,8 +684,16 @@ extern "C" int b200slu_ctc_fwd(const float* logits, long long ldv, int B, int T,
   float *em = ws, *alpha = ws + n, *beta = ws + 2 * n, *lse = ws + 3 * n, *nll_raw = lse + (long long)B * T;
   int* feasible = (int*)(ws + ws_floats(B, T, Lmax));
   B2_SCOPE(FAM_CTC, st, 0, 4.0 * B * T * V + 20.0 * n);
-  ctc_prep_kernel<<<dim3(T, B), 256, 0, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, lse, em,
-                                              Smax);
+  static const int no_warp = getenv("B200SLU_CTC_NO_WARP") != nullptr;  // A/B: the block-per-frame kernels at any V
+  if (!no_warp && V <= CTC_WARP_V && ldv % 4 == 0 && ((uintptr_t)logits % 16) == 0) {
+    const long long nframes = (long long)B * T;
+    const int grid = b2_grid_for(nframes * 32, 32 * CTC_WPB, 8);
+    ctc_prep_warp_kernel<<<grid, 32 * CTC_WPB, 0, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, lse,
+                                                        em, Smax, nframes);
+  } else {
+    ctc_prep_kernel<<<dim3(T, B), 256, 0, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, lse, em,
+                                                Smax);
+  }
   B2_LAUNCH_CHECK();
   // D = frames of emission prefetch: the recursion is a latency chain (~170 cycles per frame at C = 2), the emission
   // rows come from L2 / HBM (~1000-2500 cycles away once the logits have streamed through L2), so D * frame time has
@@ -614,9 +751,26 @@ extern "C" int b200slu_ctc_bwd(const float* logits, long long ldv, int B, int T,
   B2_SCOPE(FAM_CTC, st, 0, (double)B * T * V * (4.0 + (grad_f32 ? 4.0 : 0.0) + (grad_bf16 ? 2.0 : 0.0)) + 12.0 * n);
   const bool vec4 = ldv % 4 == 0 && ldg % 4 == 0 && ((uintptr_t)logits % 16) == 0 &&
                     (grad_f32 == nullptr || ((uintptr_t)grad_f32 % 16) == 0) && (grad_bf16 == nullptr || ((uintptr_t)grad_bf16 % 8) == 0);
-  ctc_grad_kernel<<<dim3(T, B), 256, (size_t)V * 4, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank,
-                                                          lse, em, alpha, beta, Smax, feasible, scale, grad_f32, (bf16*)grad_bf16,
-                                                          ldg, vec4);
+  static const int no_warp = getenv("B200SLU_CTC_NO_WARP") != nullptr;
+  if (!no_warp && V <= CTC_WARP_V_GRAD && vec4) {
+    static unsigned long long cfgw = 0;
+    if (!b2_device_done(cfgw)) {
+      B2_CUDA(cudaFuncSetAttribute(ctc_grad_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CTC_WPB * CTC_WARP_V_GRAD * 4));
+      b2_device_mark(cfgw);
+    }
+    const long long nframes = (long long)B * T;
+    const int Vs = (V + 3) / 4 * 4;
+    const size_t smem = (size_t)CTC_WPB * Vs * 4;
+    const int per_sm = smem <= 16 * 1024 ? 8 : 6;
+    const int grid = b2_grid_for(nframes * 32, 32 * CTC_WPB, per_sm);
+    ctc_grad_warp_kernel<<<grid, 32 * CTC_WPB, smem, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank, lse,
+                                                           em, alpha, beta, Smax, feasible, scale, grad_f32, (bf16*)grad_bf16, ldg,
+                                                           nframes, Vs);
+  } else {
+    ctc_grad_kernel<<<dim3(T, B), 256, (size_t)V * 4, st>>>(logits, ldv, T, V, hlens, labels, Lmax > 0 ? Lmax : 1, label_lens, blank,
+                                                            lse, em, alpha, beta, Smax, feasible, scale, grad_f32, (bf16*)grad_bf16,
+                                                            ldg, vec4);
+  }
   B2_LAUNCH_CHECK();
   return 0;
 }
