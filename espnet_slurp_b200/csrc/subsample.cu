@@ -45,14 +45,22 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
         for (int k = 0; k < 9; ++k) wr[k][j] = make_float2(wf[(2 * j) * 9 + k], wf[(2 * j + 1) * 9 + k]);
       }
     }
+    // pixel p = tl * F1 + f of the block's nt x F1 output rows; the walk steps (tl, f), the staged-input offset and the
+    // output pointers instead of dividing per pixel (the division and the 64-bit index were 27 % of the instructions)
+    int tl = pl / F1, f = pl - tl * F1;
+    const float* sxp = sx + (2 * tl) * F + 2 * f;
+    const long long pix0 = ((long long)b * T1 + tb) * F1;
+    bf16* hp = h1 + (pix0 + pl) * C + cg * 8;
+    unsigned char* bp = relu_bits != nullptr ? reinterpret_cast<unsigned char*>(relu_bits) + (pix0 + pl) * (C >> 3) + cg : nullptr;
+    const long long hstep = (long long)npl * C;
+    const int bstep = npl * (C >> 3), wrap = 2 * F - 2 * F1;
     for (int p = pl; p < nt * F1; p += npl) {
-      const int tl = p / F1, f = p - tl * F1;
       float2 acc2[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc2[j] = bs[j];
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
-        const float xv = sx[(2 * tl + k / 3) * F + 2 * f + (k % 3)];
+        const float xv = sxp[(k / 3) * F + (k % 3)];
         const float2 xx = make_float2(xv, xv);
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc2[j] = b2_fma2(xx, wr[k][j], acc2[j]);
@@ -60,9 +68,9 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
       uint32_t pk[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) pk[j] = pack_bf16x2(fmaxf(acc2[j].x, 0.f), fmaxf(acc2[j].y, 0.f));
-      const long long pix = ((long long)b * T1 + tb + tl) * F1 + f;
-      *reinterpret_cast<uint4*>(h1 + pix * C + cg * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-      if (relu_bits != nullptr) {
+      *reinterpret_cast<uint4*>(hp) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      hp += hstep;
+      if (bp != nullptr) {
         // bit c of the pixel's C-bit row = (h1[c] > 0): what conv.2's dgrad needs of h1, at 1/16 of the bytes.  Taken
         // from the stored bf16 pairs (non-negative after the ReLU, so > 0 <=> != 0): adding 0x7fff to a half sets its top
         // bit iff it is nonzero and cannot carry into the neighbour.
@@ -70,7 +78,14 @@ __global__ void __launch_bounds__(256) conv1_fwd_kernel(const float* __restrict_
 #pragma unroll
         for (int j = 0; j < 4; ++j) x |= ((pk[j] + 0x7fff7fffu) & 0x80008000u) >> (15 - 2 * j);  // halves of pair j -> bits 2j, 2j+16
         // one byte per lane: a warp's 32 bytes are contiguous (little-endian words: byte cg % 4 of word cg / 4)
-        reinterpret_cast<unsigned char*>(relu_bits)[pix * (C >> 3) + cg] = (unsigned char)((x | (x >> 15)) & 0xffu);
+        *bp = (unsigned char)((x | (x >> 15)) & 0xffu);
+        bp += bstep;
+      }
+      f += npl;
+      sxp += 2 * npl;
+      while (f >= F1) {  // next output row: two input rows down, back to the row's start
+        f -= F1;
+        sxp += wrap;
       }
     }
   }
