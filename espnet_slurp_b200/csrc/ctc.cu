@@ -543,10 +543,19 @@ __global__ void __launch_bounds__(256) ctc_grad_kernel(const float* __restrict__
   for (int s = threadIdx.x; s < S; s += blockDim.x) sum += ex2_(ar[s] + br[s] - er[s] - mx);  // log2 domain; impossible states -> 0
   sum = block_sum(sum, red);  // contains the barriers that also order the occ[] zeroing
   const float inv = sum > 0.f ? 1.f / sum : 0.f;
+  // the blank's occupancy (every other state: up to 301 adds on one word) is a block reduction; the label states go
+  // through shared-memory atomics (repeated labels collide there)
+  float ob = 0.f;
   for (int s = threadIdx.x; s < S; s += blockDim.x) {
     const float o = ex2_(ar[s] + br[s] - er[s] - mx) * inv;
-    if (o > 0.f) atomicAdd(&occ[ext_label(lab, s, blank)], o);
+    if (s & 1) {
+      if (o > 0.f) atomicAdd(&occ[lab[s >> 1]], o);
+    } else {
+      ob += o;
+    }
   }
+  ob = block_sum(ob, red);  // (its barriers also order the atomics above before the reads below)
+  if (threadIdx.x == 0 && ob > 0.f) atomicAdd(&occ[blank], ob);
   __syncthreads();
   const float lse2 = lse_in[r] * LOG2E;
   const float* row = logits + r * ldv;

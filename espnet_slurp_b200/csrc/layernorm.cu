@@ -422,17 +422,34 @@ __global__ void __launch_bounds__(LNP_WARPS * 32, 1) ln_bwd_pipe_kernel(const vo
       }
     }
   }
+  // Each warp's column partials go to its OWN (now idle) row slots -- every copy it issued has been consumed, and nbuf >= 2
+  // slots of >= 6 D bytes hold the 3 x D floats -- with plain vector stores; the block then sums the 12 copies column-wise.
+  // (As shared-memory atomics -- a compare-and-swap loop per float, twelve warps per address -- this was 14 % of the
+  // kernel's stall samples.)
+  {
+    float* mine = reinterpret_cast<float*>(smraw + buf0);
 #pragma unroll
-  for (int i = 0; i < NG; ++i) {
-    const int g = lane + 32 * i;
-    if (g < ngroups) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        atomicAdd(&sm[g * 8 + j], dg[i][j]);
-        atomicAdd(&sm[D + g * 8 + j], db[i][j]);
-        if (GSUM) atomicAdd(&sm[2 * D + g * 8 + j], dc[i][j]);
+    for (int i = 0; i < NG; ++i) {
+      const int g = lane + 32 * i;
+      if (g < ngroups) {
+        store8_f32(mine + g * 8, dg[i]);
+        store8_f32(mine + D + g * 8, db[i]);
+        if (GSUM) store8_f32(mine + 2 * D + g * 8, dc[i]);
       }
     }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < (GSUM ? 3 : 2) * (D >> 2); i += blockDim.x) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int w = 0; w < LNP_WARPS; ++w) {
+      const float4 v = reinterpret_cast<const float4*>(smraw + ring_off + (uint32_t)(w * nbuf) * slot)[i];
+      t.x += v.x;
+      t.y += v.y;
+      t.z += v.z;
+      t.w += v.w;
+    }
+    reinterpret_cast<float4*>(sm)[i] = t;
   }
   __syncthreads();
   const bool vec4 = (((uintptr_t)dgamma | (uintptr_t)dbeta | (GSUM ? (uintptr_t)gsum : 0)) & 15) == 0 && (D & 3) == 0;
