@@ -145,6 +145,13 @@ __device__ __forceinline__ float2 b2_sigmoid2(float2 x) {
   return b2_fma2(t, half, half);
 }
 
+// d/dx [x * sigmoid(x)] of a pair: s * (1 + x * (1 - s))   (swish_gradf_ above)
+__device__ __forceinline__ float2 b2_swish_grad2(float2 x) {
+  const float2 one = make_float2(1.f, 1.f), mone = make_float2(-1.f, -1.f);
+  const float2 s = b2_sigmoid2(x);
+  return b2_mul2(s, b2_fma2(x, b2_fma2(s, mone, one), one));
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);

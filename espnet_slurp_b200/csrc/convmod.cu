@@ -437,10 +437,11 @@ __global__ void __launch_bounds__(256) bn_swish_fwd_kernel(const bf16* __restric
         const uint32_t w4[4] = {raw[u].x, raw[u].y, raw[u].z, raw[u].w};
         float v[8];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float2 p2 = unpack_bf16x2(w4[q]);
-          v[2 * q] = swishf_(fmaf(p2.x, sc[2 * q], sh[2 * q]));
-          v[2 * q + 1] = swishf_(fmaf(p2.y, sc[2 * q + 1], sh[2 * q + 1]));
+        for (int q = 0; q < 4; ++q) {  // packed fp32 on channel pairs: half the issue slots of the scalar form
+          const float2 z = b2_fma2(unpack_bf16x2(w4[q]), make_float2(sc[2 * q], sc[2 * q + 1]), make_float2(sh[2 * q], sh[2 * q + 1]));
+          const float2 y2 = b2_mul2(z, b2_sigmoid2(z));
+          v[2 * q] = y2.x;
+          v[2 * q + 1] = y2.y;
         }
         store8_bf16(y + r * C + c, v);
       }
@@ -480,17 +481,15 @@ __global__ void __launch_bounds__(512, 1) bn_swish_bwd_reduce_kernel(const bf16*
       for (int u = 0; u < U; ++u) {
         const uint32_t wd[4] = {rd[u].x, rd[u].y, rd[u].z, rd[u].w}, wx[4] = {rx[u].x, rx[u].y, rx[u].z, rx[u].w};
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < 4; ++q) {  // packed fp32 on channel pairs (the kernel is issue-bound, not bandwidth-bound)
           const float2 d2 = unpack_bf16x2(wd[q]), x2 = unpack_bf16x2(wx[q]);
-          const float dd[2] = {d2.x, d2.y}, xx[2] = {x2.x, x2.y};
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int j = 2 * q + h;
-            const float xh = (xx[h] - mu[j]) * rs[j];
-            const float dz = dd[h] * swish_gradf_(ga[j] * xh + be[j]);
-            a1[j] += dz;
-            a2[j] += dz * xh;
-          }
+          const float2 xh = b2_mul2(b2_add2(x2, make_float2(-mu[2 * q], -mu[2 * q + 1])), make_float2(rs[2 * q], rs[2 * q + 1]));
+          const float2 z = b2_fma2(make_float2(ga[2 * q], ga[2 * q + 1]), xh, make_float2(be[2 * q], be[2 * q + 1]));
+          const float2 dz = b2_mul2(d2, b2_swish_grad2(z));
+          const float2 s1 = b2_add2(make_float2(a1[2 * q], a1[2 * q + 1]), dz);
+          const float2 s2 = b2_fma2(dz, xh, make_float2(a2[2 * q], a2[2 * q + 1]));
+          a1[2 * q] = s1.x; a1[2 * q + 1] = s1.y;
+          a2[2 * q] = s2.x; a2[2 * q + 1] = s2.y;
         }
       }
     }
@@ -499,7 +498,7 @@ __global__ void __launch_bounds__(512, 1) bn_swish_bwd_reduce_kernel(const bf16*
   colsum_block_reduce(a2, red[1], tx, ty, C, sums2 + C);
 }
 
-__global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+__global__ void __launch_bounds__(256, 2) bn_swish_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
                                                                  const float* __restrict__ mean_rstd,
                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                  const float* __restrict__ sums2, long long M, int C,
@@ -517,10 +516,12 @@ __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __r
     load8_f32(beta + c, be);
     load8_f32(sums2 + c, k1);
     load8_f32(sums2 + C + c, k2);
+    float gr[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       k1[j] *= invn;
       k2[j] *= invn;
+      gr[j] = ga[j] * rs[j];
     }
     const long long step = (long long)gridDim.y * 4;
     for (long long r0 = (long long)blockIdx.y * 4 + rl; r0 < M; r0 += BN_U * step) {
@@ -540,14 +541,14 @@ __global__ void __launch_bounds__(256) bn_swish_bwd_apply_kernel(const bf16* __r
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const float2 d2 = unpack_bf16x2(wd[q]), x2 = unpack_bf16x2(wx[q]);
-            const float dd[2] = {d2.x, d2.y}, xx[2] = {x2.x, x2.y};
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const int j = 2 * q + h;
-              const float xh = (xx[h] - mu[j]) * rs[j];
-              const float dz = dd[h] * swish_gradf_(fmaf(ga[j], xh, be[j]));
-              o[j] = ga[j] * rs[j] * (dz - k1[j] - xh * k2[j]);
-            }
+            const float2 xh = b2_mul2(b2_add2(x2, make_float2(-mu[2 * q], -mu[2 * q + 1])), make_float2(rs[2 * q], rs[2 * q + 1]));
+            const float2 z = b2_fma2(make_float2(ga[2 * q], ga[2 * q + 1]), xh, make_float2(be[2 * q], be[2 * q + 1]));
+            const float2 dz = b2_mul2(d2, b2_swish_grad2(z));
+            // ga * rs * (dz - k1 - xh * k2)
+            const float2 t = b2_fma2(xh, make_float2(-k2[2 * q], -k2[2 * q + 1]), b2_add2(dz, make_float2(-k1[2 * q], -k1[2 * q + 1])));
+            const float2 o2 = b2_mul2(make_float2(gr[2 * q], gr[2 * q + 1]), t);
+            o[2 * q] = o2.x;
+            o[2 * q + 1] = o2.y;
           }
           store8_bf16(dx + r * C + c, o);
         }
