@@ -62,15 +62,34 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   if (max_norm > 0.f) coef *= fminf(1.f, max_norm / (norm + 1e-6f));
   const float step_size = lr / bc1;
   const float inv_sqrt_bc2 = rsqrtf(bc2);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    float gi = g[i] * coef;
-    const float pi = p[i];
+  auto upd = [&](float gi, float& pi, float& mi, float& vi) {
+    gi *= coef;
     if (weight_decay != 0.f) gi += weight_decay * pi;
-    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
-    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+    mi = beta1 * mi + (1.f - beta1) * gi;
+    vi = beta2 * vi + (1.f - beta2) * gi * gi;
+    pi = pi - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+  };
+  // 16-byte accesses over the aligned body (the flat buffers are; 28 bytes move per parameter and nothing else happens
+  // here, so this kernel is as fast as its loads and stores are wide), scalar tail
+  const bool vec = ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
+  const long long n4 = vec ? (n >> 2) : 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 G = reinterpret_cast<const float4*>(g)[i];
+    float4 P = reinterpret_cast<float4*>(p)[i], Mo = reinterpret_cast<float4*>(m)[i], V = reinterpret_cast<float4*>(v)[i];
+    upd(G.x, P.x, Mo.x, V.x);
+    upd(G.y, P.y, Mo.y, V.y);
+    upd(G.z, P.z, Mo.z, V.z);
+    upd(G.w, P.w, Mo.w, V.w);
+    reinterpret_cast<float4*>(m)[i] = Mo;
+    reinterpret_cast<float4*>(v)[i] = V;
+    reinterpret_cast<float4*>(p)[i] = P;
+  }
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float pi = p[i], mi = m[i], vi = v[i];
+    upd(g[i], pi, mi, vi);
     m[i] = mi;
     v[i] = vi;
-    p[i] = pi - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+    p[i] = pi;
   }
 }
 
@@ -120,7 +139,7 @@ extern "C" int b200slu_adam_step(float* params, const float* grads, float* exp_a
   sumsq_kernel<<<b2_grid_for(n >> 2, 256, 4), 256, 0, st>>>(grads, n, grad_inv_scale, state3);
   B2_LAUNCH_CHECK();
   const float bc1 = step >= 1 ? 1.f - powf(beta1, (float)step) : 1.f, bc2 = step >= 1 ? 1.f - powf(beta2, (float)step) : 1.f;
-  adam_kernel<<<b2_grid_for(n, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
+  adam_kernel<<<b2_grid_for((n + 3) >> 2, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
                                                       bc1, bc2, grad_inv_scale, max_norm, state3,
                                                       step >= 1 ? nullptr : b2_step_params(), 0.f);
   B2_LAUNCH_CHECK();
@@ -140,7 +159,7 @@ extern "C" int b200slu_adam_step_sched(float* params, const float* grads, float*
   B2_SCOPE(FAM_ELEMWISE, st, 0, 32.0 * n);
   sumsq_kernel<<<b2_grid_for(n >> 2, 256, 4), 256, 0, st>>>(grads, n, grad_inv_scale, state4);
   B2_LAUNCH_CHECK();
-  adam_kernel<<<b2_grid_for(n, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, base_lr, beta1, beta2, eps,
+  adam_kernel<<<b2_grid_for((n + 3) >> 2, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, base_lr, beta1, beta2, eps,
                                                       weight_decay, 1.f, 1.f, grad_inv_scale, max_norm, state4, nullptr, warmup_steps);
   B2_LAUNCH_CHECK();
   adam_advance_kernel<<<1, 1, 0, st>>>(state4);
