@@ -119,6 +119,7 @@ _SIGNATURES = {
     "b200slu_adam_step": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _I, _F, _F, _P, _P],
     "b200slu_set_sm_budget": [_I],
     "b200slu_adam_step_sched": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _F, _F, _F, _P, _P],
+    "b200slu_adam_step_sched_lp": [_P, _P, _P, _P, _L, _F, _F, _F, _F, _F, _F, _F, _F, _P, _P, _P],
     "b200slu_add_shards_f32": [_P, _P, _L, _I, _L, _P],
     "b200slu_lsm_static_max_rows": [],
     "b200slu_lsm_loss_fwd_bwd_static": [_P, _L, _L, _I, _P, _I, _F, _F, _P, _P, _P, _L, _P],

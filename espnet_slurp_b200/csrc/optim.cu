@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    float* __restrict__ v, long long n, float lr, float beta1, float beta2,
                                                    float eps, float weight_decay, float bc1, float bc2, float inv_scale,
                                                    float max_norm, double* __restrict__ state,
-                                                   const B2StepParams* __restrict__ sp, float warmup) {
+                                                   const B2StepParams* __restrict__ sp, float warmup, bf16* __restrict__ p16) {
   if (sp != nullptr) {  // per-step values live on the device (CUDA-graph replay): lr, 1 - beta1^t, 1 - beta2^t
     lr = sp->lr;
     bc1 = sp->bc1;
@@ -83,6 +83,8 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
     reinterpret_cast<float4*>(m)[i] = Mo;
     reinterpret_cast<float4*>(v)[i] = V;
     reinterpret_cast<float4*>(p)[i] = P;
+    // the GEMM-operand copy of the new parameters, written here instead of by a cast pass over all of them next step
+    if (p16 != nullptr) reinterpret_cast<uint2*>(p16)[i] = make_uint2(pack_bf16x2(P.x, P.y), pack_bf16x2(P.z, P.w));
   }
   for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     float pi = p[i], mi = m[i], vi = v[i];
@@ -90,6 +92,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
     m[i] = mi;
     v[i] = vi;
     p[i] = pi;
+    if (p16 != nullptr) p16[i] = __float2bfloat16(pi);
   }
 }
 
@@ -141,7 +144,7 @@ extern "C" int b200slu_adam_step(float* params, const float* grads, float* exp_a
   const float bc1 = step >= 1 ? 1.f - powf(beta1, (float)step) : 1.f, bc2 = step >= 1 ? 1.f - powf(beta2, (float)step) : 1.f;
   adam_kernel<<<b2_grid_for((n + 3) >> 2, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
                                                       bc1, bc2, grad_inv_scale, max_norm, state3,
-                                                      step >= 1 ? nullptr : b2_step_params(), 0.f);
+                                                      step >= 1 ? nullptr : b2_step_params(), 0.f, nullptr);
   B2_LAUNCH_CHECK();
   return 0;
 }
@@ -150,21 +153,41 @@ extern "C" int b200slu_adam_step(float* params, const float* grads, float* exp_a
 // here), number of APPLIED updates so far (persistent: the caller zeroes it once)}.  lr_t = base_lr * warmup^0.5 *
 // min(t^-0.5, t * warmup^-1.5) and the bias corrections use t = state4[3] + 1; a non-finite gradient norm skips the update
 // AND leaves t unchanged.  Nothing depends on a host value, so the call is capturable in a CUDA graph as is.
-extern "C" int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n,
-                                       float base_lr, float warmup_steps, float beta1, float beta2, float eps, float weight_decay,
-                                       float grad_inv_scale, float max_norm, double* state4, void* stream) {
+static int adam_step_sched_impl(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float base_lr,
+                                float warmup_steps, float beta1, float beta2, float eps, float weight_decay, float grad_inv_scale,
+                                float max_norm, double* state4, void* params_bf16, void* stream) {
   B2_CHECK_ARG(n > 0 && warmup_steps > 0.f && ((uintptr_t)grads % 16) == 0, "adam_step_sched: n > 0, warmup_steps > 0, aligned grads");
+  B2_CHECK_ARG(((uintptr_t)params_bf16 % 8) == 0, "adam_step_sched: the bf16 copy must be 8-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   B2_CUDA(cudaMemsetAsync(state4, 0, 3 * sizeof(double), st));
   B2_SCOPE(FAM_ELEMWISE, st, 0, 32.0 * n);
   sumsq_kernel<<<b2_grid_for(n >> 2, 256, 4), 256, 0, st>>>(grads, n, grad_inv_scale, state4);
   B2_LAUNCH_CHECK();
   adam_kernel<<<b2_grid_for((n + 3) >> 2, 256, 8), 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, base_lr, beta1, beta2, eps,
-                                                      weight_decay, 1.f, 1.f, grad_inv_scale, max_norm, state4, nullptr, warmup_steps);
+                                                      weight_decay, 1.f, 1.f, grad_inv_scale, max_norm, state4, nullptr, warmup_steps,
+                                                      (bf16*)params_bf16);
   B2_LAUNCH_CHECK();
   adam_advance_kernel<<<1, 1, 0, st>>>(state4);
   B2_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n,
+                                       float base_lr, float warmup_steps, float beta1, float beta2, float eps, float weight_decay,
+                                       float grad_inv_scale, float max_norm, double* state4, void* stream) {
+  return adam_step_sched_impl(params, grads, exp_avg, exp_avg_sq, n, base_lr, warmup_steps, beta1, beta2, eps, weight_decay,
+                              grad_inv_scale, max_norm, state4, nullptr, stream);
+}
+
+// ... and the bf16 copy of the updated parameters written in the same pass (what the next step's GEMMs read): saves the
+// cast pass over all parameters at the start of every step.  A skipped update leaves both copies as they were.
+extern "C" int b200slu_adam_step_sched_lp(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n,
+                                          float base_lr, float warmup_steps, float beta1, float beta2, float eps,
+                                          float weight_decay, float grad_inv_scale, float max_norm, double* state4,
+                                          void* params_bf16, void* stream) {
+  B2_CHECK_ARG(params_bf16 != nullptr, "adam_step_sched_lp: no bf16 destination");
+  return adam_step_sched_impl(params, grads, exp_avg, exp_avg_sq, n, base_lr, warmup_steps, beta1, beta2, eps, weight_decay,
+                              grad_inv_scale, max_norm, state4, params_bf16, stream);
 }
 
 extern "C" int b200slu_add_shards_f32(float* dst, const float* src, long long shard_stride, int nshards, long long n, void* stream) {

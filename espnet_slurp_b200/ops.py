@@ -646,9 +646,17 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, lr: float, step: int, state3, 
 
 
 def adam_step_sched(params, grads, exp_avg, exp_avg_sq, base_lr: float, warmup_steps: float, state4, betas=(0.9, 0.999),
-                    eps: float = 1e-8, weight_decay: float = 0.0, grad_inv_scale: float = 1.0, max_norm: float = 5.0):
+                    eps: float = 1e-8, weight_decay: float = 0.0, grad_inv_scale: float = 1.0, max_norm: float = 5.0,
+                    params_bf16=None):
     """clip + Adam + WarmupLR with the step count on the device: state4 = float64[4] (sumsq, grad norm, applied flag, number of
-    applied updates so far -- persistent).  A non-finite gradient norm skips the update and does not advance the schedule."""
+    applied updates so far -- persistent).  A non-finite gradient norm skips the update and does not advance the schedule.
+    params_bf16: bf16 tensor of the same length that receives the updated parameters in the same pass."""
+    if params_bf16 is not None:
+        assert params_bf16.dtype == torch.bfloat16 and params_bf16.numel() == params.numel()
+        check(_lib.lib().b200slu_adam_step_sched_lp(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), base_lr,
+                                                    float(warmup_steps), betas[0], betas[1], eps, weight_decay, grad_inv_scale,
+                                                    max_norm, ptr(state4), ptr(params_bf16), stream_ptr()), "adam_step_sched_lp")
+        return
     check(_lib.lib().b200slu_adam_step_sched(ptr(params), ptr(grads), ptr(exp_avg), ptr(exp_avg_sq), params.numel(), base_lr,
                                              float(warmup_steps), betas[0], betas[1], eps, weight_decay, grad_inv_scale, max_norm,
                                              ptr(state4), stream_ptr()), "adam_step_sched")

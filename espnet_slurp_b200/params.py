@@ -111,9 +111,11 @@ class ParamPack:
                 self.G[n] = torch.zeros(d_, CF, device=device, dtype=torch.float32)
 
     # -- per step -----------------------------------------------------------------------------------------------
-    def refresh(self):
-        """bf16 copies of the current fp32 masters (one cast kernel + the two re-layouts)."""
-        _step.K.cast_bf16(self.flat32, out=self.flat16)
+    def refresh(self, cast: bool = True):
+        """bf16 copies of the current fp32 masters (one cast kernel + the two re-layouts).  cast=False: ``flat16`` is
+        current already (the optimizer kernel wrote it with the update); only the re-layouts are redone."""
+        if cast:
+            _step.K.cast_bf16(self.flat32, out=self.flat16)
         for n, sp in self.special.items():
             o, num = self.offs[n], 1
             for s in self.shapes[n]:

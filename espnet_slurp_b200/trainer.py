@@ -103,6 +103,7 @@ class TrainStep:
             self.bn[p + "num_batches_tracked"] = nb.to(dev).long().reshape(1).clone() if nb is not None else \
                 torch.zeros(1, device=dev, dtype=torch.long)
         self.step_no = 0
+        self.pack.refresh()  # the bf16 operand copies; from here on the optimizer kernel keeps them current
         # with self-conditioning the encoder backward still adds to ctc.ctc_lo's gradient after the heads are done
         # (step.encoder_bwd): those parameters then belong to the last bucket, not to "heads"
         late = ("ctc.",) if cfg.enc.interctc_use_conditioning else ()
@@ -158,7 +159,8 @@ class TrainStep:
     # ---- the step body: only device-resident inputs (the bucket's static buffers, the 24-byte record) -> capturable
     def _body(self, b: _Bucket, overlap: bool, on_ready=None):
         pack, cfg, inp = self.pack, self.cfg, b.inp
-        pack.refresh()
+        # flat16 is kept current by the optimizer kernel (_tail); only the two re-laid-out weights are rebuilt per step
+        pack.refresh(cast=False)
         pack.zero_grad()
         draws = {k: inp[k] for k in _DRAW_KEYS if k in inp}
         feats, flens = bstep.frontend_fwd(inp["wav"], inp["lens"], self.mel, cfg, draws)
@@ -176,7 +178,7 @@ class TrainStep:
         # WarmupLR and Adam's bias corrections are evaluated in the kernel from the device-side count of APPLIED updates: a
         # step skipped for a non-finite gradient norm advances neither (trainer.py:651-690), and nothing here is a host value
         ops.adam_step_sched(self.pack.flat32, self.pack.gflat, self.m, self.v, self.base_lr, self.warmup_steps, self.state,
-                            grad_inv_scale=1.0 / self.world, max_norm=self.max_norm)
+                            grad_inv_scale=1.0 / self.world, max_norm=self.max_norm, params_bf16=self.pack.flat16)
 
     def capture(self, b: Optional[_Bucket] = None):
         """Record the whole step of this bucket (weight cast -> front-end -> forward -> backward [-> clip + Adam when

@@ -362,6 +362,12 @@ int b200slu_adam_step_sched(float* params, const float* grads, float* exp_avg, f
                             float warmup_steps, float beta1, float beta2, float eps, float weight_decay, float grad_inv_scale,
                             float max_norm, double* state4, void* stream);
 
+/* The same, also writing the bf16 copy of the updated parameters (the GEMM operands of the next step; the reference's
+ * autocast re-casts every weight per use, torch/amp autocast_mode) in the same pass. */
+int b200slu_adam_step_sched_lp(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float base_lr,
+                               float warmup_steps, float beta1, float beta2, float eps, float weight_decay, float grad_inv_scale,
+                               float max_norm, double* state4, void* params_bf16, void* stream);
+
 /* Local reduction of the peer-memory gradient exchange (8e; reference: DistributedDataParallel's all-reduce,
  * espnet2/train/trainer.py:221-236): dst[i] += sum_k src[k * shard_stride + i], k = 0 .. nshards-1 in that order, fp32.
  * The shards are the other ranks' copies of this rank's slice of a gradient bucket, pulled over NVLink by the copy
